@@ -1,0 +1,88 @@
+"""Synthetic inputs for the nodal projection.
+
+The formulas are the reference's initial conditions, evaluated at cell centres with numpy:
+  taylor_green      /root/reference/src/prob/prob_init_fluid.cpp:150-160
+  double_shear      /root/reference/src/prob/prob_init_fluid.cpp:470-475   (probtype 21)
+  rayleigh_taylor   /root/reference/src/prob/prob_init_fluid.cpp:295-321   (density; sigma = dt/rho)
+plus the perturbations SURVEY.md 8d adds so that the projection is non-trivial.
+Arrays are C-order [k, j, i]; velocity is [3, k, j, i].
+"""
+import numpy as np
+
+PERIODIC, DIRICHLET, NEUMANN = 0, 1, 2
+TWOPI = 2.0 * 3.1415926535897932
+
+
+def cell_centres(ncell, prob_lo, prob_hi, koff=0, nz_local=None):
+    """Cell-centre coordinate arrays (z, y, x) broadcastable to [k, j, i].  koff/nz_local select a z-slab."""
+    nx, ny, nz = ncell
+    dx = [(prob_hi[d] - prob_lo[d]) / ncell[d] for d in range(3)]
+    nzl = nz if nz_local is None else nz_local
+    x = prob_lo[0] + (np.arange(nx) + 0.5) * dx[0]
+    y = prob_lo[1] + (np.arange(ny) + 0.5) * dx[1]
+    z = prob_lo[2] + (np.arange(koff, koff + nzl) + 0.5) * dx[2]
+    return z[:, None, None], y[None, :, None], x[None, None, :]
+
+
+def _perturb(x, y, z, Lz=1.0):
+    return 0.1 * np.sin(TWOPI * x) * np.sin(TWOPI * y) * np.sin(TWOPI * z / Lz)
+
+
+def taylor_green(ncell, prob_lo=(0, 0, 0), prob_hi=(1, 1, 1), **kw):
+    """Config 1: TGV + perturbation, sigma = 1, periodic."""
+    z, y, x = cell_centres(ncell, prob_lo, prob_hi, **kw)
+    p = _perturb(x, y, z)
+    u = np.sin(TWOPI * x) * np.cos(TWOPI * y) + p
+    v = -np.cos(TWOPI * x) * np.sin(TWOPI * y) + p
+    w = 0.0 * x * y + p
+    shape = np.broadcast_shapes(z.shape, y.shape, x.shape)
+    vel = np.stack([np.broadcast_to(a, shape) for a in (u, v, w)]).astype(np.float64)
+    return dict(vel=np.ascontiguousarray(vel), sigma=np.ones(shape), bclo=(0, 0, 0), bchi=(0, 0, 0),
+                prob_lo=tuple(prob_lo), prob_hi=tuple(prob_hi))
+
+
+def double_shear(ncell, prob_lo=(0, 0, 0), prob_hi=(1, 1, 1), zwave=False, **kw):
+    """Configs 2/3: double shear layer (probtype 21), sigma = 1, periodic.
+    zwave adds w = 0.05 sin(2 pi x) sin(2 pi z / Lz) (config 3, so z is non-trivial across slabs)."""
+    z, y, x = cell_centres(ncell, prob_lo, prob_hi, **kw)
+    shape = np.broadcast_shapes(z.shape, y.shape, x.shape)
+    u = np.tanh(30.0 * (0.25 - np.abs(y - 0.5)))
+    v = 0.05 * np.sin(TWOPI * x)
+    Lz = prob_hi[2] - prob_lo[2]
+    w = 0.05 * np.sin(TWOPI * x) * np.sin(TWOPI * z / Lz) if zwave else 0.0 * x
+    vel = np.stack([np.broadcast_to(a, shape) for a in (u, v, w)]).astype(np.float64)
+    return dict(vel=np.ascontiguousarray(vel), sigma=np.ones(shape), bclo=(0, 0, 0), bchi=(0, 0, 0),
+                prob_lo=tuple(prob_lo), prob_hi=tuple(prob_hi))
+
+
+def rayleigh_taylor(ncell, prob_lo=(0, 0, 0), prob_hi=(0.5, 0.5, 1.0), dt=1.0, **kw):
+    """Config 4: variable density (ratio 4), periodic x/y, slip walls in z (Neumann); sigma = dt/rho.
+    u* = gravity kick (0, 0, -0.1 dt) + perturbation."""
+    z, y, x = cell_centres(ncell, prob_lo, prob_hi, **kw)
+    shape = np.broadcast_shapes(z.shape, y.shape, x.shape)
+    rho_1, rho_2, width = 0.5, 2.0, 0.005
+    splitx, splity = 0.5 * (prob_lo[0] + prob_hi[0]), 0.5 * (prob_lo[1] + prob_hi[1])
+    L_x = prob_hi[0] - prob_lo[0]
+    r2d = np.minimum(np.hypot(x - splitx, y - splity), 0.5 * L_x)
+    pertheight = 0.5 - 0.01 * np.cos(2.0 * np.pi * r2d / L_x)
+    rho = rho_1 + ((rho_2 - rho_1) / 2.0) * (1.0 + np.tanh((z - pertheight) / width))
+    rho = np.broadcast_to(rho, shape)
+    Lx, Ly, Lz = [prob_hi[d] - prob_lo[d] for d in range(3)]
+    p = 0.1 * np.sin(TWOPI * x / Lx) * np.sin(TWOPI * y / Ly) * np.sin(TWOPI * z / Lz)
+    vel = np.stack([np.broadcast_to(p, shape), np.broadcast_to(p, shape),
+                    np.broadcast_to(-0.1 * dt + p, shape)]).astype(np.float64)
+    return dict(vel=np.ascontiguousarray(vel), sigma=np.ascontiguousarray(dt / rho), bclo=(0, 0, NEUMANN),
+                bchi=(0, 0, NEUMANN), prob_lo=tuple(prob_lo), prob_hi=tuple(prob_hi))
+
+
+def random_fields(ncell, seed=0):
+    """Kernel-level parity inputs: phi ~ N(0,1) nodal, sigma ~ U[0.5, 2]."""
+    rng = np.random.default_rng(seed)
+    nx, ny, nz = ncell
+    phi = rng.standard_normal((nz + 1, ny + 1, nx + 1))
+    sigma = rng.uniform(0.5, 2.0, (nz, ny, nx))
+    vel = rng.standard_normal((3, nz, ny, nx))
+    return dict(phi=phi, sigma=sigma, vel=vel)
+
+
+PROBLEMS = {"taylor_green": taylor_green, "double_shear": double_shear, "rayleigh_taylor": rayleigh_taylor}
