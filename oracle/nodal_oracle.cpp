@@ -322,7 +322,23 @@ static void fsmooth_lex(const Level& L, MF& x, const MF& rhs, int nsweeps)
 // each plane k ascending, for colour c = 2*(j&1)+(i&1) (box-local indices) ascending, update all
 // nodes of that colour.  A node is owned by a box unless it lies on the box's high face and that
 // face is not a non-periodic domain boundary.
-struct TileSpec { int t[3]; };
+struct TileSpec { int t[3]; int variant = 0; int overlap = 1; };
+// Experimental orderings (variant > 0) used only to study smoothing rates: nodes are
+// visited in ascending key order, nodes with equal keys are updated simultaneously (Jacobi).
+static long order_key(int variant, int ns, int i, int j, int k, int ni, int nj, int nk)
+{
+    const long B = 1L<<12;
+    switch (variant) {
+    case 1: { long c = 2*(j&1)+(i&1); return (ns&1) ? ((nk-1-k)*4 + (3-c)) : (k*4 + c); }   // symmetric
+    case 2: { long c = 4*(k&1)+2*(j&1)+(i&1); return c; }                                   // 8-colour
+    case 3: return ((long)k*B + j)*2 + (i&1);                                               // row-seq, rb in i
+    case 4: return ((long)k*B + j)*B + i;                                                   // lexicographic
+    case 5: { long c = (i+j+k)&1; return c; }                                               // red-black hybrid
+    case 6: return 0;                                                                       // Jacobi
+    case 7: { long c = 2*(j&1)+(i&1); return (long)c*B + k; }                               // 4-colour columns, k-seq inside
+    default: return 0;
+    }
+}
 static void owned_range(const Level& L, const IBox& cb, IBox& o)
 {
     o = valid_of(cb, true);
@@ -336,17 +352,46 @@ static void fsmooth_tiled(const Level& L, MF& x, const MF& rhs, int nsweeps, con
     StencilCoef c(L.dxinv);
     MF out = x;   // frozen input stays in x; results go to out
     for (size_t b = 0; b < L.boxes.size(); ++b) {
-        IBox o; owned_range(L, L.boxes[b], o);
+        // All VALID nodes are relaxed, duplicates included (they are overwritten by their owner in
+        // nodal_sync afterwards) — the same one-node overlap between neighbouring boxes / periodic
+        // images that AMReX's box-by-box Gauss-Seidel has.
+        IBox o = valid_of(L.boxes[b], true);
         int nt[3]; for (int d=0; d<3; ++d) nt[d] = (o.hi[d]-o.lo[d]+1 + ts.t[d]-1)/ts.t[d];
         const Fab& xin = x.f[b]; const Fab& sf = L.sigma.f[b]; const Fab& rf = rhs.f[b]; Fab& xo = out.f[b];
         parallel_for(nt[0]*nt[1]*nt[2], [&](int t) {
             int t0 = t % nt[0], t1 = (t/nt[0]) % nt[1], t2 = t/(nt[0]*nt[1]);
             IBox tb;
             tb.lo[0]=o.lo[0]+t0*ts.t[0]; tb.lo[1]=o.lo[1]+t1*ts.t[1]; tb.lo[2]=o.lo[2]+t2*ts.t[2];
-            for (int d=0; d<3; ++d) tb.hi[d] = std::min(tb.lo[d]+ts.t[d]-1, o.hi[d]);
+            IBox wb = tb;    // nodes this tile WRITES: [lo, lo+t-1]
+            for (int d=0; d<3; ++d) wb.hi[d] = std::min(tb.lo[d]+ts.t[d]-1, o.hi[d]);
+            // nodes this tile RELAXES: one more on the high side (shared with the next tile, which owns it)
+            for (int d=0; d<3; ++d) tb.hi[d] = std::min(tb.lo[d]+ts.t[d]-1+ts.overlap, o.hi[d]);
             Fab w; w.define(grow(tb,1), 1);
             for (int k=w.r.lo[2]; k<=w.r.hi[2]; ++k) for (int j=w.r.lo[1]; j<=w.r.hi[1]; ++j) for (int i=w.r.lo[0]; i<=w.r.hi[0]; ++i)
                 w(i,j,k) = xin(i,j,k);
+            if (ts.variant > 0) {
+                struct Nd { long key; int i,j,k; };
+                const int ni=tb.hi[0]-tb.lo[0]+1, nj=tb.hi[1]-tb.lo[1]+1, nk=tb.hi[2]-tb.lo[2]+1;
+                for (int ns = 0; ns < nsweeps; ++ns) {
+                    std::vector<Nd> nds; nds.reserve((size_t)ni*nj*nk);
+                    for (int k=tb.lo[2]; k<=tb.hi[2]; ++k) for (int j=tb.lo[1]; j<=tb.hi[1]; ++j) for (int i=tb.lo[0]; i<=tb.hi[0]; ++i)
+                        nds.push_back({order_key(ts.variant, ns, i-tb.lo[0], j-tb.lo[1], k-tb.lo[2], ni,nj,nk), i,j,k});
+                    std::stable_sort(nds.begin(), nds.end(), [](const Nd& a, const Nd& b){ return a.key < b.key; });
+                    std::vector<double> tmp;
+                    for (size_t a = 0; a < nds.size();) {
+                        size_t e = a; while (e < nds.size() && nds[e].key == nds[a].key) ++e;
+                        tmp.resize(e-a);
+                        for (size_t q = a; q < e; ++q) {
+                            int i=nds[q].i, j=nds[q].j, k=nds[q].k;
+                            if (L.is_dirichlet(i,j,k)) { tmp[q-a] = 0.0; continue; }
+                            Sig8 g(sf.ptr(i,j,k), sf.sy, sf.sz);
+                            tmp[q-a] = (rf(i,j,k) - offdiag_node(c, g, w.ptr(i,j,k), w.sy, w.sz)) / diag_node(c, g);
+                        }
+                        for (size_t q = a; q < e; ++q) w(nds[q].i,nds[q].j,nds[q].k) = tmp[q-a];
+                        a = e;
+                    }
+                }
+            } else
             for (int ns = 0; ns < nsweeps; ++ns)
             for (int k=tb.lo[2]; k<=tb.hi[2]; ++k)
             for (int col = 0; col < 4; ++col)
@@ -362,7 +407,7 @@ static void fsmooth_tiled(const Level& L, MF& x, const MF& rhs, int nsweeps, con
                     xp[0] = (rf(i,j,k) - off) / s0;
                 }
             }
-            for (int k=tb.lo[2]; k<=tb.hi[2]; ++k) for (int j=tb.lo[1]; j<=tb.hi[1]; ++j) for (int i=tb.lo[0]; i<=tb.hi[0]; ++i)
+            for (int k=wb.lo[2]; k<=wb.hi[2]; ++k) for (int j=wb.lo[1]; j<=wb.hi[1]; ++j) for (int i=wb.lo[0]; i<=wb.hi[0]; ++i)
                 xo(i,j,k) = w(i,j,k);
         });
     }
@@ -586,6 +631,8 @@ struct Options {
     int interp_sigma_weighted = 1;
     int bottom_normalize = 1;         // MLCGSolver calls Lp.normalize (divide by the diagonal)
     int agg_level = -1;               // TILED only: from this MG level on, one box covers the domain
+    int tile_variant = 0;             // experimental orderings, see order_key()
+    int tile_overlap = 1;             // tiles share their high-face nodes with the next tile (like boxes do)
 };
 
 struct Stats {
@@ -653,7 +700,7 @@ struct Solver {
         const Level& L = lev[l];
         apply_bc(L, x, skip_fillboundary);
         if (opt.smoother == LEX) fsmooth_lex(L, x, b, opt.smooth_sweeps);
-        else { TileSpec ts{{opt.tile[0],opt.tile[1],opt.tile[2]}}; fsmooth_tiled(L, x, b, opt.smooth_sweeps, ts); }
+        else { TileSpec ts{{opt.tile[0],opt.tile[1],opt.tile[2]}, opt.tile_variant, opt.tile_overlap}; fsmooth_tiled(L, x, b, opt.smooth_sweeps, ts); }
         nodal_sync(L, x);
     }
     // MLNodeLinOp::apply = applyBC + Fapply
@@ -940,7 +987,7 @@ extern "C" {
 struct orc_options {
     int max_coarsening_level, maxiter, bottom_maxiter, nu1, nu2, nuf, nub, smooth_sweeps, bottom_solver;
     double bottom_rtol, bottom_atol;
-    int verbose, smoother, tile[3], interp_sigma_weighted, bottom_normalize, agg_level, nthreads;
+    int verbose, smoother, tile[3], interp_sigma_weighted, bottom_normalize, agg_level, nthreads, tile_variant, tile_overlap;
 };
 struct orc_stats {
     int n_vcycles, bottom_iters_total, status, n_levels;
@@ -955,7 +1002,7 @@ void orc_default_options(orc_options* o) {
     o->nu1=d.nu1; o->nu2=d.nu2; o->nuf=d.nuf; o->nub=d.nub; o->smooth_sweeps=d.smooth_sweeps; o->bottom_solver=d.bottom_solver;
     o->bottom_rtol=d.bottom_rtol; o->bottom_atol=d.bottom_atol; o->verbose=0; o->smoother=LEX;
     o->tile[0]=d.tile[0]; o->tile[1]=d.tile[1]; o->tile[2]=d.tile[2];
-    o->interp_sigma_weighted=1; o->bottom_normalize=1; o->agg_level=-1; o->nthreads=1;
+    o->interp_sigma_weighted=1; o->bottom_normalize=1; o->agg_level=-1; o->nthreads=1; o->tile_variant=0; o->tile_overlap=1;
 }
 
 void* orc_create(const int* ncell, const double* plo, const double* phi, const int* bclo, const int* bchi,
@@ -966,7 +1013,7 @@ void* orc_create(const int* ncell, const double* plo, const double* phi, const i
     op.nu1=o->nu1; op.nu2=o->nu2; op.nuf=o->nuf; op.nub=o->nub; op.smooth_sweeps=o->smooth_sweeps; op.bottom_solver=o->bottom_solver;
     op.bottom_rtol=o->bottom_rtol; op.bottom_atol=o->bottom_atol; op.verbose=o->verbose; op.smoother=o->smoother;
     op.tile[0]=o->tile[0]; op.tile[1]=o->tile[1]; op.tile[2]=o->tile[2];
-    op.interp_sigma_weighted=o->interp_sigma_weighted; op.bottom_normalize=o->bottom_normalize; op.agg_level=o->agg_level;
+    op.interp_sigma_weighted=o->interp_sigma_weighted; op.bottom_normalize=o->bottom_normalize; op.agg_level=o->agg_level; op.tile_variant=o->tile_variant; op.tile_overlap=o->tile_overlap;
     g_nthreads = std::max(1, o->nthreads);
     auto* s = new Solver();
     s->define(ncell, plo, phi, bclo, bchi, nboxes, boxes, op);
