@@ -1,0 +1,127 @@
+// np_capi.cu — the extern "C" boundary declared in include/nodalproj.h.
+#include "np_solver.h"
+#include "np_kernels.cuh"
+#include <new>
+
+
+
+
+extern "C" {
+
+void np_default_options(np_options* o)
+{
+    o->max_coarsening_level = 30; o->maxiter = 100; o->bottom_maxiter = 100;
+    o->num_pre_smooth = 2; o->num_post_smooth = 2; o->num_final_smooth = 8;
+    o->bottom_solver = NP_BOTTOM_BICGCG; o->verbose = 0; o->bottom_verbose = 0;
+    o->bottom_rtol = 1e-4; o->bottom_atol = -1.0;
+    o->smooth_zchunk = 0; o->interp_sigma_weighted = 1; o->bottom_normalize = 1;
+    o->agg_min_local_nz = 16; o->use_graph = 1; o->const_sigma_fastpath = 1;
+}
+
+int np_create(np_handle** h, const np_geom* geom, int nboxes_global, const np_box* all_boxes,
+              const int* owner_rank, int my_rank, int nranks, void* nccl_comm_or_null, const np_options* opt)
+{
+    if (!h || !geom || !all_boxes || !owner_rank || nranks < 1 || my_rank < 0 || my_rank >= nranks) return NP_ERR_INVALID;
+    np_options o; if (opt) o = *opt; else np_default_options(&o);
+    np_handle* p = new (std::nothrow) np_handle();
+    if (!p) return NP_ERR_INVALID;
+    NpComm c;
+    if (nranks > 1) {
+        np_comm_fill_nccl(c, nccl_comm_or_null);
+        if (!c.sendrecv) { delete p; return NP_ERR_NCCL; }
+    }
+    int rc = p->S.create(geom, nboxes_global, all_boxes, owner_rank, my_rank, nranks, c, &o);
+    if (rc) { p->S.destroy(); delete p; return rc; }
+    *h = p;
+    return NP_OK;
+}
+
+int np_set_bc(np_handle* h, const int lo[3], const int hi[3]) { return h ? h->S.set_bc(lo, hi) : NP_ERR_INVALID; }
+
+int np_project(np_handle* h, int nlocal, np_fab* vel, const np_fab* sigma, double rtol, double atol, void* cuda_stream, np_stats* out)
+{
+    if (!h || nlocal != 1 || !vel || !sigma || !vel->p || !sigma->p) return NP_ERR_INVALID;
+    h->S.stream = (np_stream_t)cuda_stream;
+    int rc = h->S.project(vel, sigma, rtol, atol);
+    if (out) *out = h->S.stats;
+    return rc;
+}
+
+int np_last_stats(np_handle* h, np_stats* out) { if (!h || !out) return NP_ERR_INVALID; *out = h->S.stats; return NP_OK; }
+
+int np_get_phi(np_handle* h, int local_box, np_fab* out)
+{
+    if (!h || local_box != 0 || !out) return NP_ERR_INVALID;
+    if (!h->S.have_result) return NP_ERR_STATE;
+    out->p = h->S.phi_out; out->ngrow = 1; out->ncomp = 1;
+    return NP_OK;
+}
+int np_get_gradphi(np_handle* h, int local_box, np_fab* out)
+{
+    if (!h || local_box != 0 || !out) return NP_ERR_INVALID;
+    if (!h->S.have_result) return NP_ERR_STATE;
+    out->p = h->S.gphi; out->ngrow = 1; out->ncomp = 3;
+    return NP_OK;
+}
+
+// copy internal results into a caller fab (host or device, any ngrow): interior (+ min(ngrow,1) ghosts)
+int np_copy_phi(np_handle* h, int local_box, np_fab* dst)
+{
+    if (!h || local_box != 0 || !dst || !dst->p) return NP_ERR_INVALID;
+    NpSolver& S = h->S;
+    if (!S.have_result) return NP_ERR_STATE;
+    const LevelDev& d = S.lev[0].d;
+    FabView v = S.view_nodal(*dst, 0);
+    double* dev; bool staged;
+    if (S.import_fab(*dst, v.sn, &dev, &staged)) return NP_ERR_CUDA;
+    v.p = dev;
+    const int g = dst->ngrow > 0 ? 1 : 0;
+    NP_LAUNCH(false, (k_copy_nodal<true>), dim3((d.n[0] + 1 + 2*g + 31) / 32, (d.n[1] + 1 + 2*g + 7) / 8, d.n[2] + 1 + 2*g), NP_BLK, 0, S.stream, d, S.sol, v, g);
+    S.export_fab(*dst, v.sn, dev, staged);
+    np_rt::stream_sync(S.stream);
+    return NP_OK;
+}
+int np_copy_gradphi(np_handle* h, int local_box, np_fab* dst)
+{
+    if (!h || local_box != 0 || !dst || !dst->p || dst->ncomp < 3) return NP_ERR_INVALID;
+    NpSolver& S = h->S;
+    if (!S.have_result) return NP_ERR_STATE;
+    const LevelDev& d = S.lev[0].d;
+    FabView v = S.view_cell(*dst, 0, 3);
+    double* dev; bool staged;
+    if (S.import_fab(*dst, v.sn * 3, &dev, &staged)) return NP_ERR_CUDA;
+    v.p = dev;
+    FabView gv; gv.p = S.gphi; gv.ng = 1; gv.sy = d.n[0] + 2; gv.sz = gv.sy * (d.n[1] + 2); gv.sn = gv.sz * (d.n[2] + 2);
+    const int g = dst->ngrow > 0 ? 1 : 0;
+    NP_LAUNCH(false, k_copy_cell, dim3((d.n[0] + 2*g + 31) / 32, (d.n[1] + 2*g + 7) / 8, d.n[2] + 2*g), NP_BLK, 0, S.stream, d.n[0], d.n[1], v, gv, 3, g);
+    S.export_fab(*dst, v.sn * 3, dev, staged);
+    np_rt::stream_sync(S.stream);
+    return NP_OK;
+}
+
+void np_destroy(np_handle* h) { if (h) { h->S.destroy(); delete h; } }
+
+const char* np_strerror(int code)
+{
+    switch (code) {
+    case NP_OK: return "ok";
+    case NP_ERR_INVALID: return "nodalproj: invalid argument or unsupported box layout";
+    case NP_ERR_NO_DEVICE: return "nodalproj: no CUDA device (there is no CPU fallback)";
+    case NP_ERR_CUDA: return "nodalproj: CUDA error";
+    case NP_ERR_NCCL: return "nodalproj: NCCL / communication error";
+    case NP_ERR_NOT_CONVERGED: return "MLMG failed to converge";
+    case NP_ERR_DIVERGED: return "MLMG failing so lets stop here";
+    case NP_ERR_STATE: return "nodalproj: call order";
+    default: return "nodalproj: unknown error";
+    }
+}
+
+int np_num_levels(np_handle* h) { return h ? (int)h->S.lev.size() : 0; }
+int np_level_ncell(np_handle* h, int l, int n[3])
+{
+    if (!h || l < 0 || l >= (int)h->S.lev.size()) return NP_ERR_INVALID;
+    for (int d = 0; d < 3; ++d) n[d] = h->S.lev[l].d.n[d];
+    return NP_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,820 @@
+// np_kernels.cuh — the fp64 kernels of the nodal projection, written for sm_100a.
+//
+// Kernel families:
+//   K1 k_divu            nodal divergence of the cell velocity     (amrex::mlndlap_divu + impose_neumann_bc)
+//   K2 k_adotx           y = A x  /  y = b - A x, 27-point variable-sigma operator (mlndlap_adotx_aa)
+//   K3 k_smooth_tiled    Gauss-Seidel smoother, two sweeps fused in one pass (mlndlap_gauss_seidel_aa)
+//   K4 k_restrict        full-weighting restriction                (mlndlap_restriction)
+//   K5 k_interp_add      prolongation + add                        (mlndlap_interpadd_aa)
+//   K6 k_bottom_*        BiCGStab / CG on the coarsest level in one CTA (MLCGSolver)
+//   K7 k_mknewu          u -= sigma grad(phi), gradphi = grad(phi) (mlndlap_mknewu + NodalProjector::project)
+//   K8 k_avgdown_sigma   8->1 arithmetic coarsening of sigma, k_fill_sigma ghost fill
+// plus boundary fill (FillBoundary + nodalSync + mlndlap_applybc in one pass), reductions and copies.
+// The reference has no file for any of these (the arithmetic is in AMReX); the call site they serve is
+// /root/reference/src/projection/incflo_apply_nodal_projection.cpp:153.
+#pragma once
+#include "np_types.h"
+#include <math.h>
+
+// ------------------------------------------------------------------------------------------------
+// Stencil on generic accessors.  X(di,dj,dk): nodal value at offset from the node.  S(a,b,c): sigma of the
+// cell at offset a,b,c in {-1,0} from CELL (i,j,k).
+// ------------------------------------------------------------------------------------------------
+struct Sig8 {
+    double mmm, pmm, mpm, ppm, mmp, pmp, mpp, ppp;   // x,y,z side: m = -1, p = 0
+};
+template <class SA> __device__ __forceinline__ Sig8 np_load_sig(const SA& s) {
+    Sig8 g;
+    g.mmm = s(-1,-1,-1); g.pmm = s(0,-1,-1); g.mpm = s(-1,0,-1); g.ppm = s(0,0,-1);
+    g.mmp = s(-1,-1,0);  g.pmp = s(0,-1,0);  g.mpp = s(-1,0,0);  g.ppp = s(0,0,0);
+    return g;
+}
+__device__ __forceinline__ double np_diag(const NpCoef& c, const Sig8& g) {
+    return -4.0 * c.fxyz * (((g.mmm + g.pmm) + (g.mpm + g.ppm)) + ((g.mmp + g.pmp) + (g.mpp + g.ppp)));
+}
+template <class XA> __device__ __forceinline__ double np_offdiag(const NpCoef& c, const Sig8& g, const XA& x) {
+    double corners = x(-1,-1,-1)*g.mmm + x(1,-1,-1)*g.pmm + x(-1,1,-1)*g.mpm + x(1,1,-1)*g.ppm
+                   + x(-1,-1, 1)*g.mmp + x(1,-1, 1)*g.pmp + x(-1,1, 1)*g.mpp + x(1,1, 1)*g.ppp;
+    double eyz = x(0,-1,-1)*(g.mmm+g.pmm) + x(0,1,-1)*(g.mpm+g.ppm) + x(0,-1,1)*(g.mmp+g.pmp) + x(0,1,1)*(g.mpp+g.ppp);
+    double exz = x(-1,0,-1)*(g.mmm+g.mpm) + x(1,0,-1)*(g.pmm+g.ppm) + x(-1,0,1)*(g.mmp+g.mpp) + x(1,0,1)*(g.pmp+g.ppp);
+    double exy = x(-1,-1,0)*(g.mmm+g.mmp) + x(1,-1,0)*(g.pmm+g.pmp) + x(-1,1,0)*(g.mpm+g.mpp) + x(1,1,0)*(g.ppm+g.ppp);
+    double fx = x(-1,0,0)*((g.mmm+g.mpm)+(g.mmp+g.mpp)) + x(1,0,0)*((g.pmm+g.ppm)+(g.pmp+g.ppp));
+    double fy = x(0,-1,0)*((g.mmm+g.pmm)+(g.mmp+g.pmp)) + x(0,1,0)*((g.mpm+g.ppm)+(g.mpp+g.ppp));
+    double fz = x(0,0,-1)*((g.mmm+g.pmm)+(g.mpm+g.ppm)) + x(0,0,1)*((g.mmp+g.pmp)+(g.mpp+g.ppp));
+    return c.fxyz*corners + c.fmx2y2z*eyz + c.f2xmy2z*exz + c.f2x2ymz*exy
+         + c.f4xm2ym2z*fx + c.fm2x4ym2z*fy + c.fm2xm2y4z*fz;
+}
+// constant sigma: the 26 neighbours collapse into 7 weight classes (weights already multiplied by sigma)
+template <class XA> __device__ __forceinline__ double np_offdiag_const(const NpCoef& c, double sg, const XA& x) {
+    double corners = ((x(-1,-1,-1) + x(1,-1,-1)) + (x(-1,1,-1) + x(1,1,-1))) + ((x(-1,-1,1) + x(1,-1,1)) + (x(-1,1,1) + x(1,1,1)));
+    double eyz = (x(0,-1,-1) + x(0,1,-1)) + (x(0,-1,1) + x(0,1,1));
+    double exz = (x(-1,0,-1) + x(1,0,-1)) + (x(-1,0,1) + x(1,0,1));
+    double exy = (x(-1,-1,0) + x(1,-1,0)) + (x(-1,1,0) + x(1,1,0));
+    double fx = x(-1,0,0) + x(1,0,0), fy = x(0,-1,0) + x(0,1,0), fz = x(0,0,-1) + x(0,0,1);
+    return sg * (c.fxyz*corners + 2.0*(c.fmx2y2z*eyz + c.f2xmy2z*exz + c.f2x2ymz*exy)
+               + 4.0*(c.f4xm2ym2z*fx + c.fm2x4ym2z*fy + c.fm2xm2y4z*fz));
+}
+__device__ __forceinline__ double np_diag_const(const NpCoef& c, double sg) { return -32.0 * c.fxyz * sg; }
+
+struct GlobX {   // nodal array in HBM, pointer at the node
+    const double* p; long long sy, sz;
+    __device__ __forceinline__ double operator()(int di, int dj, int dk) const { return p[di + sy*dj + sz*dk]; }
+};
+struct GlobS {   // cell array in HBM, pointer at cell (i,j,k)
+    const double* p; long long sy, sz;
+    __device__ __forceinline__ double operator()(int a, int b, int c) const { return p[a + sy*b + sz*c]; }
+};
+
+// ------------------------------------------------------------------------------------------------
+// Block reductions (warp shuffles, then one smem pass; every thread of the block must call them)
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ double np_warp_sum(double v) {
+    for (int m = 16; m > 0; m >>= 1) v += __shfl_xor_sync(0xffffffffu, v, m);
+    return v;
+}
+__device__ __forceinline__ double np_warp_max(double v) {
+    for (int m = 16; m > 0; m >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, m));
+    return v;
+}
+// result valid in every thread; fixed summation order -> deterministic
+template <bool IS_MAX> __device__ __forceinline__ double np_block_reduce(double v) {
+    __shared__ double red[33];
+    const int tid = threadIdx.x + blockDim.x * (threadIdx.y + blockDim.y * threadIdx.z);
+    const int nth = blockDim.x * blockDim.y * blockDim.z;
+    v = IS_MAX ? np_warp_max(v) : np_warp_sum(v);
+    __syncthreads();                       // protect red[] from a previous call
+    if ((tid & 31) == 0) red[tid >> 5] = v;
+    __syncthreads();
+    if (tid == 0) {
+        double a = red[0];
+        for (int w = 1; w < (nth + 31) / 32; ++w) a = IS_MAX ? fmax(a, red[w]) : a + red[w];
+        red[32] = a;
+    }
+    __syncthreads();
+    return red[32];
+}
+
+// ------------------------------------------------------------------------------------------------
+// Boundary fill: FillBoundary(periodic) + nodalSync (high duplicates <- owner) + mlndlap_applybc
+// (Neumann mirror) in ONE pass over the shell.  Sources are owned nodes, destinations are not, so the
+// pass is race-free.  zmode 0: z handled like x,y.  zmode 1: rank-interior z faces are filled by the
+// halo exchange; only x,y (on planes lo_k..hi_k) and domain-end z mirrors are done here.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_fill_boundary(LevelDev L, double* x)
+{
+    const int e0 = L.n[0] + 3, e1 = L.n[1] + 3, e2 = L.n[2] + 3;     // extended extents
+    // three slab groups of 3 planes each: i in {-1,n,n+1}, j in {...}, k in {...}
+    const long long g0 = 3LL * e1 * e2, g1 = 3LL * e0 * e2, g2 = 3LL * e0 * e1;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < g0 + g1 + g2;
+         t += (long long)gridDim.x * blockDim.x) {
+        int i, j, k;
+        if (t < g0)           { long long q = t;           int s = (int)(q % 3); q /= 3; j = (int)(q % e1) - 1; k = (int)(q / e1) - 1; i = s == 0 ? -1 : L.n[0] + s - 1; }
+        else if (t < g0 + g1) { long long q = t - g0;      int s = (int)(q % 3); q /= 3; i = (int)(q % e0) - 1; k = (int)(q / e0) - 1; j = s == 0 ? -1 : L.n[1] + s - 1; }
+        else                  { long long q = t - g0 - g1; int s = (int)(q % 3); q /= 3; i = (int)(q % e0) - 1; j = (int)(q / e0) - 1; k = s == 0 ? -1 : L.n[2] + s - 1; }
+        const int si = np_map_index(i, L.n[0], L.map_lo[0], L.map_hi[0]);
+        const int sj = np_map_index(j, L.n[1], L.map_lo[1], L.map_hi[1]);
+        const int sk = np_map_index(k, L.n[2], L.map_lo[2], L.map_hi[2]);
+        if (si == i && sj == j && sk == k) continue;
+        // a source must be a valid node; (mapped) indices that stay outside belong to Dirichlet /
+        // rank-interior faces and are left alone
+        if (si < 0 || si > L.n[0] || sj < 0 || sj > L.n[1] || sk < 0 || sk > L.n[2]) continue;
+        x[np_noff(L, i, j, k)] = x[np_noff(L, si, sj, sk)];
+    }
+}
+
+// sigma ghost layer: periodic wrap, else copy of the adjacent interior cell (MLNodeLaplacian::FillBoundaryCoeff)
+// fill_z = 0 leaves the z ghost layers to the halo exchange (rank-interior faces).
+__global__ void __launch_bounds__(256) k_fill_sigma(LevelDev L, double* s, int per0, int per1, int per2, int zlo_local, int zhi_local)
+{
+    const int e0 = L.n[0] + 2, e1 = L.n[1] + 2, e2 = L.n[2] + 2;
+    const long long g0 = 2LL * e1 * e2, g1 = 2LL * e0 * e2, g2 = 2LL * e0 * e1;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < g0 + g1 + g2;
+         t += (long long)gridDim.x * blockDim.x) {
+        int i, j, k;
+        if (t < g0)           { long long q = t;           int sd = (int)(q % 2); q /= 2; j = (int)(q % e1) - 1; k = (int)(q / e1) - 1; i = sd ? L.n[0] : -1; }
+        else if (t < g0 + g1) { long long q = t - g0;      int sd = (int)(q % 2); q /= 2; i = (int)(q % e0) - 1; k = (int)(q / e0) - 1; j = sd ? L.n[1] : -1; }
+        else                  { long long q = t - g0 - g1; int sd = (int)(q % 2); q /= 2; i = (int)(q % e0) - 1; j = (int)(q / e0) - 1; k = sd ? L.n[2] : -1; }
+        int si = i, sj = j, sk = k;
+        if (i < 0) si = per0 ? i + L.n[0] : 0; else if (i >= L.n[0]) si = per0 ? i - L.n[0] : L.n[0] - 1;
+        if (j < 0) sj = per1 ? j + L.n[1] : 0; else if (j >= L.n[1]) sj = per1 ? j - L.n[1] : L.n[1] - 1;
+        if (k < 0)          { if (!zlo_local) continue; sk = per2 ? k + L.n[2] : 0; }
+        else if (k >= L.n[2]) { if (!zhi_local) continue; sk = per2 ? k - L.n[2] : L.n[2] - 1; }
+        s[np_coff(L, i, j, k)] = s[np_coff(L, si, sj, sk)];
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K2: y = A x (MODE 0) or y = b - A x (MODE 1) on all valid nodes.  Optional per-block inf-norm of y.
+// One thread per node, x fastest; neighbours come through L1/L2.
+// ------------------------------------------------------------------------------------------------
+template <int MODE, bool CS, bool NORM>
+__global__ void __launch_bounds__(256) k_adotx(LevelDev L, double* __restrict__ y, const double* __restrict__ x,
+                                               const double* __restrict__ b, const double* __restrict__ sig,
+                                               double* __restrict__ block_max)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    const int k = blockIdx.z;
+    double v = 0.0;
+    const bool active = (i <= L.n[0] && j <= L.n[1]);
+    if (active) {
+        const long long o = np_noff(L, i, j, k);
+        if (!np_is_dirichlet(L, i, j, k)) {
+            GlobX xa{x + o, L.nsy, L.nsz};
+            double ax;
+            if (CS) {
+                ax = xa(0,0,0) * np_diag_const(L.c, L.sigma0) + np_offdiag_const(L.c, L.sigma0, xa);
+            } else {
+                GlobS sa{sig + np_coff(L, i, j, k), L.csy, L.csz};
+                Sig8 g = np_load_sig(sa);
+                ax = xa(0,0,0) * np_diag(L.c, g) + np_offdiag(L.c, g, xa);
+            }
+            v = (MODE == 1) ? b[o] - ax : ax;
+        }
+        y[o] = v;
+    }
+    if (NORM) {
+        double m = np_block_reduce<true>(fabs(v));
+        if (threadIdx.x == 0 && threadIdx.y == 0)
+            block_max[blockIdx.x + gridDim.x * (blockIdx.y + (long long)gridDim.y * blockIdx.z)] = m;
+    }
+}
+
+// second stage of a reduction: one block folds `n` partials into out[slot] (max or sum), fixed order
+template <bool IS_MAX> __global__ void __launch_bounds__(256) k_reduce_final(const double* __restrict__ part, long long n, double* out, int slot)
+{
+    double v = 0.0;
+    for (long long t = threadIdx.x; t < n; t += blockDim.x) v = IS_MAX ? fmax(v, part[t]) : v + part[t];
+    v = np_block_reduce<IS_MAX>(v);
+    if (threadIdx.x == 0) out[slot] = v;
+}
+
+// inf-norm partials of a nodal array over valid nodes
+__global__ void __launch_bounds__(256) k_norminf(LevelDev L, const double* __restrict__ x, double* __restrict__ block_max)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    const int k = blockIdx.z;
+    double v = 0.0;
+    if (i <= L.n[0] && j <= L.n[1]) v = fabs(x[np_noff(L, i, j, k)]);
+    double m = np_block_reduce<true>(v);
+    if (threadIdx.x == 0 && threadIdx.y == 0)
+        block_max[blockIdx.x + gridDim.x * (blockIdx.y + (long long)gridDim.y * blockIdx.z)] = m;
+}
+
+// dot-mask weighted sums over OWNED nodes: part0 = sum w*x*y (y may be null -> sum w*x), part1 = sum w
+__global__ void __launch_bounds__(256) k_wdot(LevelDev L, const double* __restrict__ x, const double* __restrict__ y,
+                                              double* __restrict__ part0, double* __restrict__ part1)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    const int k = blockIdx.z;
+    double a = 0.0, w = 0.0;
+    if (i <= L.owned_hi[0] && j <= L.owned_hi[1] && k <= L.owned_hi[2]) {
+        w = np_neumann_weight(L, i, j, k);
+        const long long o = np_noff(L, i, j, k);
+        a = w * x[o] * (y ? y[o] : 1.0);
+    }
+    double sa = np_block_reduce<false>(a);
+    double sw = np_block_reduce<false>(w);
+    if (threadIdx.x == 0 && threadIdx.y == 0) {
+        const long long bidx = blockIdx.x + gridDim.x * (blockIdx.y + (long long)gridDim.y * blockIdx.z);
+        part0[bidx] = sa; part1[bidx] = sw;
+    }
+}
+
+// x[valid] -= scal[0]/scal[1]   (MLNodeLinOp::fixSolvabilityByOffset; scalars stay on the device)
+__global__ void __launch_bounds__(256) k_sub_offset(LevelDev L, double* __restrict__ x, const double* __restrict__ scal)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    const int k = blockIdx.z;
+    if (i <= L.n[0] && j <= L.n[1]) x[np_noff(L, i, j, k)] -= scal[0] / scal[1];
+}
+
+// y[valid] += x[valid]
+__global__ void __launch_bounds__(256) k_add(LevelDev L, double* __restrict__ y, const double* __restrict__ x)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    const int k = blockIdx.z;
+    if (i <= L.n[0] && j <= L.n[1]) { const long long o = np_noff(L, i, j, k); y[o] += x[o]; }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K3: the smoother.  DESIGN.md "smoother semantics":
+//   * the valid nodes of the box are cut into tiles that WRITE (NP_TW x NP_TW x zc) nodes and RELAX one
+//     more node on each high side (shared with the next tile, which owns it) — the same one-node overlap
+//     AMReX's boxes have — with everything outside the relaxed region frozen at its pre-smooth value;
+//   * inside a tile: sweep 1 then sweep 2 (the two sweeps of one Fsmooth), each visiting planes k
+//     ascending and, inside a plane, the four colours c = 2*(j&1)+(i&1) ascending (Gauss-Seidel).
+// One CTA owns one tile column chunk and streams it through shared memory once: sweep 2 runs two
+// planes behind sweep 1 (plane t-2 only needs sweep-1 values of planes <= t-1), so both sweeps cost one
+// pass over HBM.  Ring buffers: 5 nodal planes (34x34 incl. halo), 4 sigma layers (33x33).
+// ------------------------------------------------------------------------------------------------
+#define NP_TW 31                 // written nodes per tile side
+#define NP_TR 32                 // relaxed nodes per tile side
+#define NP_TP 34                 // plane extent incl. halo
+#define NP_XP 35                 // smem pitch of a nodal plane row
+#define NP_SP 33                 // smem pitch of a sigma layer row (33 cells)
+#define NP_XPLANE (NP_TP * NP_XP)
+#define NP_SLAYER (NP_SP * NP_SP)
+#define NP_XRING 5
+#define NP_SRING 4
+
+struct SmemX {   // nodal ring in shared memory, pointer at the node in the centre plane
+    const double* m; const double* c; const double* p;
+    __device__ __forceinline__ double operator()(int di, int dj, int dk) const {
+        const double* q = dk < 0 ? m : (dk > 0 ? p : c);
+        return q[di + NP_XP * dj];
+    }
+};
+struct SmemS {   // sigma ring, pointers at local cell (li, lj) in the lower / upper layer
+    const double* lo; const double* hi;
+    __device__ __forceinline__ double operator()(int a, int b, int c) const {
+        const double* q = c < 0 ? lo : hi;
+        return q[a + NP_SP * b];
+    }
+};
+
+template <bool CS>
+__global__ void __launch_bounds__(256, 2) k_smooth_tiled(LevelDev L, double* __restrict__ xout, const double* __restrict__ xin,
+                                                         const double* __restrict__ rhs, const double* __restrict__ sig, int zc)
+{
+    NP_DYN_SMEM(double, smem);
+    double* xr = smem;                                   // NP_XRING planes
+    double* sr = smem + NP_XRING * NP_XPLANE;            // NP_SRING layers
+    const int tid = threadIdx.x;
+    const int i0 = blockIdx.x * NP_TW, j0 = blockIdx.y * NP_TW, kb = blockIdx.z * zc;
+    const int nk  = min(kb + zc, L.n[2]) - kb + 1;       // relaxed planes p = 0..nk-1 (global k = kb+p)
+    const int nkw = min(kb + zc - 1, L.n[2]) - kb + 1;   // written planes
+    const int wi = min(NP_TW, L.n[0] - i0 + 1), wj = min(NP_TW, L.n[1] - j0 + 1);   // written extents
+    const int a = tid & 15, bq = tid >> 4;               // this thread's 2x2 node block
+
+    auto load_plane = [&](int p) {       // p in [-1, nk]
+        double* dst = xr + ((p + 1) % NP_XRING) * NP_XPLANE;
+        const int k = kb + p;
+        for (int q = tid; q < NP_TP * NP_TP; q += 256) {
+            const int li = q % NP_TP, lj = q / NP_TP;
+            const int i = i0 - 1 + li, j = j0 - 1 + lj;
+            double v = 0.0;
+            if (i <= L.n[0] + 1 && j <= L.n[1] + 1 && k <= L.n[2] + 1) v = xin[np_noff(L, i, j, k)];
+            dst[li + NP_XP * lj] = v;
+        }
+    };
+    auto load_sigma = [&](int q) {       // layer q in [-1, nk-1]: cells between planes q and q+1
+        if (CS) return;
+        double* dst = sr + ((q + 1) % NP_SRING) * NP_SLAYER;
+        const int kc = kb + q;
+        for (int t = tid; t < NP_SP * NP_SP; t += 256) {
+            const int ci = t % NP_SP, cj = t / NP_SP;
+            const int i = i0 - 1 + ci, j = j0 - 1 + cj;
+            double v = 0.0;
+            if (i <= L.n[0] && j <= L.n[1] && kc <= L.n[2]) v = sig[np_coff(L, i, j, kc)];
+            dst[ci + NP_SP * cj] = v;
+        }
+    };
+    auto relax = [&](int p, int col) {   // one colour of plane p
+        const int li = 1 + 2 * a + (col & 1), lj = 1 + 2 * bq + (col >> 1);
+        const int i = i0 + li - 1, j = j0 + lj - 1, k = kb + p;
+        if (i > L.n[0] || j > L.n[1]) return;
+        double* xc = xr + ((p + 1) % NP_XRING) * NP_XPLANE + li + NP_XP * lj;
+        if (np_is_dirichlet(L, i, j, k)) { *xc = 0.0; return; }
+        const double* xm = xr + ((p + 0) % NP_XRING) * NP_XPLANE + li + NP_XP * lj;
+        const double* xp = xr + ((p + 2) % NP_XRING) * NP_XPLANE + li + NP_XP * lj;
+        SmemX xa{xm, xc, xp};
+        const double r = rhs[np_noff(L, i, j, k)];
+        if (CS) {
+            *xc = (r - np_offdiag_const(L.c, L.sigma0, xa)) / np_diag_const(L.c, L.sigma0);
+        } else {
+            // node li touches local cells li-1, li; SmemS is anchored at the HIGH cell (li, lj)
+            const double* slo = sr + ((p + 0) % NP_SRING) * NP_SLAYER + li + NP_SP * lj;   // layer p-1
+            const double* shi = sr + ((p + 1) % NP_SRING) * NP_SLAYER + li + NP_SP * lj;   // layer p
+            SmemS sa{slo, shi};
+            Sig8 g = np_load_sig(sa);
+            *xc = (r - np_offdiag(L.c, g, xa)) / np_diag(L.c, g);
+        }
+    };
+
+    load_plane(-1); load_plane(0); load_sigma(-1);
+    for (int t = 0; t <= nk + 1; ++t) {
+        if (t + 1 <= nk) load_plane(t + 1);
+        if (t <= nk - 1) load_sigma(t);
+        __syncthreads();
+        for (int col = 0; col < 4; ++col) {
+            if (t <= nk - 1) relax(t, col);                       // sweep 1 on plane t
+            if (t >= 2 && t - 2 <= nk - 1) relax(t - 2, col);     // sweep 2 on plane t-2
+            __syncthreads();
+        }
+        const int pw = t - 2;                                     // plane pw is final
+        if (pw >= 0 && pw < nkw) {
+            const double* src = xr + ((pw + 1) % NP_XRING) * NP_XPLANE;
+            const int k = kb + pw;
+            for (int q = tid; q < wi * wj; q += 256) {
+                const int li = q % wi, lj = q / wi;
+                xout[np_noff(L, i0 + li, j0 + lj, k)] = src[(li + 1) + NP_XP * (lj + 1)];
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K4: restriction, one thread per coarse valid node.  Lf: fine level (for the Dirichlet test), Lc: coarse.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_restrict(LevelDev Lc, LevelDev Lf, double* __restrict__ crse, const double* __restrict__ fine)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    const int k = blockIdx.z;
+    if (i > Lc.n[0] || j > Lc.n[1]) return;
+    double v = 0.0;
+    if (!np_is_dirichlet(Lf, 2*i, 2*j, 2*k)) {
+        GlobX f{fine + np_noff(Lf, 2*i, 2*j, 2*k), Lf.nsy, Lf.nsz};
+        double faces = (f(-1,0,0) + f(1,0,0)) + (f(0,-1,0) + f(0,1,0)) + (f(0,0,-1) + f(0,0,1));
+        double edges = ((f(-1,-1,0) + f(1,-1,0)) + (f(-1,1,0) + f(1,1,0)))
+                     + ((f(-1,0,-1) + f(1,0,-1)) + (f(-1,0,1) + f(1,0,1)))
+                     + ((f(0,-1,-1) + f(0,1,-1)) + (f(0,-1,1) + f(0,1,1)));
+        double corners = ((f(-1,-1,-1) + f(1,-1,-1)) + (f(-1,1,-1) + f(1,1,-1)))
+                       + ((f(-1,-1,1) + f(1,-1,1)) + (f(-1,1,1) + f(1,1,1)));
+        v = 0.125 * f(0,0,0) + 0.0625 * faces + 0.03125 * edges + 0.015625 * corners;
+    }
+    crse[np_noff(Lc, i, j, k)] = v;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K5: fine += P(crse).  WEIGHTED: sigma-weighted lines/faces/centres (amrex aa_interp_line_* etc.);
+// otherwise plain trilinear (identical when sigma is uniform).  koff2: coarse plane index of fine
+// plane 0 is koffc (non-zero only when the coarse level is a replicated copy of the whole domain).
+// ------------------------------------------------------------------------------------------------
+struct InterpCtx {
+    const double* c; long long csy_n, csz_n;      // coarse nodal array, pointer at coarse node (0,0,0) incl. k offset
+    const double* s; long long ssy, ssz;          // fine sigma, pointer at fine cell (0,0,0)
+    __device__ __forceinline__ double crse(int i, int j, int k) const { return c[(i >> 1) + csy_n * (j >> 1) + csz_n * (k >> 1)]; }
+    __device__ __forceinline__ double sg(int i, int j, int k) const { return s[i + ssy * j + ssz * k]; }
+    // 4 fine cells on the low (side 0) / high (side 1) side of fine node (i,j,k) along d
+    __device__ __forceinline__ double quad(int i, int j, int k, int d, int side) const {
+        if (d == 0) { int q = i - 1 + side; return (sg(q,j-1,k-1) + sg(q,j,k-1)) + (sg(q,j-1,k) + sg(q,j,k)); }
+        if (d == 1) { int q = j - 1 + side; return (sg(i-1,q,k-1) + sg(i,q,k-1)) + (sg(i-1,q,k) + sg(i,q,k)); }
+        int q = k - 1 + side; return (sg(i-1,j-1,q) + sg(i,j-1,q)) + (sg(i-1,j,q) + sg(i,j,q));
+    }
+    __device__ __forceinline__ double line(int i, int j, int k, int d) const {
+        const double w1 = quad(i,j,k,d,0), w2 = quad(i,j,k,d,1);
+        const int di = d == 0, dj = d == 1, dk = d == 2;
+        return (w1 * crse(i-di, j-dj, k-dk) + w2 * crse(i+di, j+dj, k+dk)) / (w1 + w2);
+    }
+    __device__ __forceinline__ double face(int i, int j, int k, int da, int db) const {
+        const double wa0 = quad(i,j,k,da,0), wa1 = quad(i,j,k,da,1), wb0 = quad(i,j,k,db,0), wb1 = quad(i,j,k,db,1);
+        const int ai = da == 0, aj = da == 1, ak = da == 2, bi = db == 0, bj = db == 1, bk = db == 2;
+        return (wa0 * line(i-ai, j-aj, k-ak, db) + wa1 * line(i+ai, j+aj, k+ak, db)
+              + wb0 * line(i-bi, j-bj, k-bk, da) + wb1 * line(i+bi, j+bj, k+bk, da)) / ((wa0 + wa1) + (wb0 + wb1));
+    }
+    __device__ __forceinline__ double centre(int i, int j, int k) const {
+        const double x0 = quad(i,j,k,0,0), x1 = quad(i,j,k,0,1), y0 = quad(i,j,k,1,0), y1 = quad(i,j,k,1,1),
+                     z0 = quad(i,j,k,2,0), z1 = quad(i,j,k,2,1);
+        const double num = (x0 * face(i-1,j,k,1,2) + x1 * face(i+1,j,k,1,2))
+                         + (y0 * face(i,j-1,k,2,0) + y1 * face(i,j+1,k,2,0))
+                         + (z0 * face(i,j,k-1,0,1) + z1 * face(i,j,k+1,0,1));
+        return num / (((x0 + x1) + (y0 + y1)) + (z0 + z1));
+    }
+};
+
+template <bool WEIGHTED>
+__global__ void __launch_bounds__(256) k_interp_add(LevelDev Lf, LevelDev Lc, double* __restrict__ fine, const double* __restrict__ crse,
+                                                    const double* __restrict__ sig, int koffc)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    const int k = blockIdx.z;
+    if (i > Lf.n[0] || j > Lf.n[1]) return;
+    if (np_is_dirichlet(Lf, i, j, k)) return;
+    InterpCtx ctx{crse + np_noff(Lc, 0, 0, koffc), Lc.nsy, Lc.nsz, WEIGHTED ? sig + np_coff(Lf, 0, 0, 0) : nullptr, Lf.csy, Lf.csz};
+    const int ox = i & 1, oy = j & 1, oz = k & 1;
+    const int nodd = ox + oy + oz;
+    double v;
+    if (nodd == 0) v = ctx.crse(i, j, k);
+    else if (!WEIGHTED) {
+        double s = 0.0;
+        for (int c2 = 0; c2 <= oz; ++c2) for (int c1 = 0; c1 <= oy; ++c1) for (int c0 = 0; c0 <= ox; ++c0)
+            s += ctx.crse(i - ox + 2*c0, j - oy + 2*c1, k - oz + 2*c2);
+        v = s / (double)(1 << nodd);
+    }
+    else if (nodd == 1) v = ctx.line(i, j, k, ox ? 0 : (oy ? 1 : 2));
+    else if (nodd == 2) v = (ox && oy) ? ctx.face(i, j, k, 0, 1) : ((ox && oz) ? ctx.face(i, j, k, 2, 0) : ctx.face(i, j, k, 1, 2));
+    else v = ctx.centre(i, j, k);
+    fine[np_noff(Lf, i, j, k)] += v;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K8: sigma coarsening (arithmetic mean of the 8 children), interior cells only
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_avgdown_sigma(LevelDev Lc, LevelDev Lf, double* __restrict__ sc, const double* __restrict__ sf)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    const int k = blockIdx.z;
+    if (i >= Lc.n[0] || j >= Lc.n[1]) return;
+    const double* p = sf + np_coff(Lf, 2*i, 2*j, 2*k);
+    const long long y = Lf.csy, z = Lf.csz;
+    sc[np_coff(Lc, i, j, k)] = 0.125 * (((p[0] + p[1]) + (p[y] + p[y+1])) + ((p[z] + p[z+1]) + (p[z+y] + p[z+y+1])));
+}
+
+// copy the caller's sigma fab (interior) into the level-0 sigma array and produce per-block min / max
+__global__ void __launch_bounds__(256) k_copy_sigma_in(LevelDev L, double* __restrict__ s, FabView src,
+                                                      double* __restrict__ bmin, double* __restrict__ bmax)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    const int k = blockIdx.z;
+    double v = 0.0; bool act = (i < L.n[0] && j < L.n[1]);
+    if (act) { v = src.p[np_foff(src, i, j, k, 0)]; s[np_coff(L, i, j, k)] = v; }
+    double mx = np_block_reduce<true>(act ? v : -1e300);
+    double mn = -np_block_reduce<true>(act ? -v : -1e300);
+    if (threadIdx.x == 0 && threadIdx.y == 0) {
+        const long long bidx = blockIdx.x + gridDim.x * (blockIdx.y + (long long)gridDim.y * blockIdx.z);
+        bmin[bidx] = mn; bmax[bidx] = mx;
+    }
+}
+__global__ void __launch_bounds__(256) k_reduce_minmax(const double* __restrict__ bmin, const double* __restrict__ bmax, long long n, double* out)
+{
+    double mx = -1e300, mn = 1e300;
+    for (long long t = threadIdx.x; t < n; t += blockDim.x) { mx = fmax(mx, bmax[t]); mn = fmin(mn, bmin[t]); }
+    mx = np_block_reduce<true>(mx);
+    mn = -np_block_reduce<true>(-mn);
+    if (threadIdx.x == 0) { out[0] = mn; out[1] = mx; }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Velocity ghost fill (1 layer, periodic x/y[/z]) on the caller's fab — what compRHS's
+// vel.FillBoundary does.  Physical ghosts (inflow data / zeros) are left untouched.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_fill_vel(LevelDev L, FabView u, int per0, int per1, int per2)
+{
+    const int e0 = L.n[0] + 2, e1 = L.n[1] + 2, e2 = L.n[2] + 2;
+    const long long g0 = 2LL * e1 * e2, g1 = 2LL * e0 * e2, g2 = 2LL * e0 * e1;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < g0 + g1 + g2;
+         t += (long long)gridDim.x * blockDim.x) {
+        int i, j, k;
+        if (t < g0)           { long long q = t;           int sd = (int)(q % 2); q /= 2; j = (int)(q % e1) - 1; k = (int)(q / e1) - 1; i = sd ? L.n[0] : -1; }
+        else if (t < g0 + g1) { long long q = t - g0;      int sd = (int)(q % 2); q /= 2; i = (int)(q % e0) - 1; k = (int)(q / e0) - 1; j = sd ? L.n[1] : -1; }
+        else                  { long long q = t - g0 - g1; int sd = (int)(q % 2); q /= 2; i = (int)(q % e0) - 1; j = (int)(q / e0) - 1; k = sd ? L.n[2] : -1; }
+        int si = i, sj = j, sk = k;
+        if (i < 0 || i >= L.n[0]) { if (!per0) continue; si = i < 0 ? i + L.n[0] : i - L.n[0]; }
+        if (j < 0 || j >= L.n[1]) { if (!per1) continue; sj = j < 0 ? j + L.n[1] : j - L.n[1]; }
+        if (k < 0 || k >= L.n[2]) { if (!per2) continue; sk = k < 0 ? k + L.n[2] : k - L.n[2]; }
+        for (int n = 0; n < 3; ++n) u.p[np_foff(u, i, j, k, n)] = u.p[np_foff(u, si, sj, sk, n)];
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K1: rhs = div(u) at valid nodes, with the Neumann conventions of mlndlap_divu / impose_neumann_bc
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_divu(LevelDev L, double* __restrict__ rhs, FabView u)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    const int k = blockIdx.z;
+    if (i > L.n[0] || j > L.n[1]) return;
+    double acc = 0.0;
+    if (!np_is_dirichlet(L, i, j, k)) {
+        // z?lo / z?hi: weight of the cells on the low / high side of the node (0 outside a Neumann wall)
+        const double zxl = (L.face[0] == NP_FACE_NEUMANN && i == 0) ? 0.0 : 1.0, zxh = (L.face[3] == NP_FACE_NEUMANN && i == L.n[0]) ? 0.0 : 1.0;
+        const double zyl = (L.face[1] == NP_FACE_NEUMANN && j == 0) ? 0.0 : 1.0, zyh = (L.face[4] == NP_FACE_NEUMANN && j == L.n[1]) ? 0.0 : 1.0;
+        const double zzl = (L.face[2] == NP_FACE_NEUMANN && k == 0) ? 0.0 : 1.0, zzh = (L.face[5] == NP_FACE_NEUMANN && k == L.n[2]) ? 0.0 : 1.0;
+        const double* p = u.p + np_foff(u, i, j, k, 0);
+        const long long y = u.sy, z = u.sz;
+        const double* ux = p; const double* uy = p + u.sn; const double* uz = p + 2 * u.sn;
+        // cells (a,b,c), a,b,c in {-1,0}: offset a + y*b + z*c
+        double sx = zyl*zzl*(ux[-y-z] - ux[-1-y-z]) + zyh*zzl*(ux[-z] - ux[-1-z]) + zyl*zzh*(ux[-y] - ux[-1-y]) + zyh*zzh*(ux[0] - ux[-1]);
+        double sy_ = zxl*zzl*(uy[-1-z] - uy[-1-y-z]) + zxh*zzl*(uy[-z] - uy[-y-z]) + zxl*zzh*(uy[-1] - uy[-1-y]) + zxh*zzh*(uy[0] - uy[-y]);
+        double sz_ = zxl*zyl*(uz[-1-y] - uz[-1-y-z]) + zxh*zyl*(uz[-y] - uz[-y-z]) + zxl*zyh*(uz[-1] - uz[-1-z]) + zxh*zyh*(uz[0] - uz[-z]);
+        acc = 0.25 * (L.dxinv[0] * sx + L.dxinv[1] * sy_ + L.dxinv[2] * sz_);
+        if (zxl == 0.0) acc *= 2.0;
+        if (zxh == 0.0) acc *= 2.0;
+        if (zyl == 0.0) acc *= 2.0;
+        if (zyh == 0.0) acc *= 2.0;
+        if (zzl == 0.0) acc *= 2.0;
+        if (zzh == 0.0) acc *= 2.0;
+    }
+    rhs[np_noff(L, i, j, k)] = acc;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K7: u -= sigma * grad(phi), gradphi = grad(phi); one thread per cell, all three outputs in one pass
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_mknewu(LevelDev L, FabView u, FabView g, const double* __restrict__ phi, const double* __restrict__ sig)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    const int k = blockIdx.z;
+    if (i >= L.n[0] || j >= L.n[1]) return;
+    const double* q = phi + np_noff(L, i, j, k);
+    const long long y = L.nsy, z = L.nsz;
+    const double gx = 0.25 * L.dxinv[0] * (((q[1] - q[0]) + (q[1+y] - q[y])) + ((q[1+z] - q[z]) + (q[1+y+z] - q[y+z])));
+    const double gy = 0.25 * L.dxinv[1] * (((q[y] - q[0]) + (q[1+y] - q[1])) + ((q[y+z] - q[z]) + (q[1+y+z] - q[1+z])));
+    const double gz = 0.25 * L.dxinv[2] * (((q[z] - q[0]) + (q[1+z] - q[1])) + ((q[y+z] - q[y]) + (q[1+y+z] - q[1+y])));
+    const double s = L.const_sigma ? L.sigma0 : sig[np_coff(L, i, j, k)];
+    double* up = u.p + np_foff(u, i, j, k, 0);
+    up[0] -= s * gx; up[u.sn] -= s * gy; up[2 * u.sn] -= s * gz;
+    double* gp = g.p + np_foff(g, i, j, k, 0);
+    gp[0] = gx; gp[g.sn] = gy; gp[2 * g.sn] = gz;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Copies between the padded internal nodal layout and a caller fab (1 comp).  ng_copy ghost layers of the
+// fab are transferred too (clamped to 1).
+// ------------------------------------------------------------------------------------------------
+template <bool TO_FAB>
+__global__ void __launch_bounds__(256) k_copy_nodal(LevelDev L, double* __restrict__ x, FabView f, int ngc)
+{
+    const int i = (int)(blockIdx.x * blockDim.x + threadIdx.x) - ngc;
+    const int j = (int)(blockIdx.y * blockDim.y + threadIdx.y) - ngc;
+    const int k = (int)blockIdx.z - ngc;
+    if (i > L.n[0] + ngc || j > L.n[1] + ngc) return;
+    if (TO_FAB) f.p[np_foff(f, i, j, k, 0)] = x[np_noff(L, i, j, k)];
+    else        x[np_noff(L, i, j, k)] = f.p[np_foff(f, i, j, k, 0)];
+}
+// cell fab -> cell fab (ncomp components, interior + ngc ghosts), used for host-staged / copy-out paths
+__global__ void __launch_bounds__(256) k_copy_cell(int n0, int n1, FabView dst, FabView src, int ncomp, int ngc)
+{
+    const int i = (int)(blockIdx.x * blockDim.x + threadIdx.x) - ngc;
+    const int j = (int)(blockIdx.y * blockDim.y + threadIdx.y) - ngc;
+    const int k = (int)blockIdx.z - ngc;
+    if (i >= n0 + ngc || j >= n1 + ngc) return;
+    for (int n = 0; n < ncomp; ++n) dst.p[np_foff(dst, i, j, k, n)] = src.p[np_foff(src, i, j, k, n)];
+}
+__global__ void __launch_bounds__(256) k_copy_sigma_out(LevelDev L, const double* __restrict__ s, FabView dst)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    const int k = blockIdx.z;
+    if (i >= L.n[0] || j >= L.n[1]) return;
+    dst.p[np_foff(dst, i, j, k, 0)] = L.const_sigma ? L.sigma0 : s[np_coff(L, i, j, k)];
+}
+
+// ------------------------------------------------------------------------------------------------
+// K6: bottom solver — the whole BiCGStab / CG iteration of amrex::MLCGSolver in ONE CTA: the coarsest
+// level is tiny (3^3 .. 33^3 nodes), so the ~7 reductions and 2 operator applications per iteration are
+// block barriers instead of kernel launches / allreduces.  Vectors live in HBM (L2-resident).
+// ------------------------------------------------------------------------------------------------
+struct BottomArgs {
+    LevelDev L;
+    double* x; const double* b;             // solution (out), right-hand side (in; not modified)
+    double *r, *rh, *p, *v, *s, *t, *bb;    // work arrays (full nodal arrays with ghosts)
+    const double* sig;
+    int maxiter; double eps_rel, eps_abs;
+    int singular, normalize, type;          // type: 0 BiCGStab, 1 CG
+    int* out;                               // out[0] = ret code, out[1] = iterations
+};
+
+struct BottomCtx {
+    const BottomArgs& A;
+    int tid, nth;
+    long long nvalid;
+    __device__ BottomCtx(const BottomArgs& a) : A(a) {
+        tid = threadIdx.x; nth = blockDim.x;
+        nvalid = (long long)(a.L.n[0] + 1) * (a.L.n[1] + 1) * (a.L.n[2] + 1);
+    }
+    __device__ __forceinline__ void ijk(long long q, int& i, int& j, int& k) const {
+        const int e0 = A.L.n[0] + 1, e1 = A.L.n[1] + 1;
+        i = (int)(q % e0); j = (int)((q / e0) % e1); k = (int)(q / ((long long)e0 * e1));
+    }
+    __device__ void fill(double* x) const {
+        const LevelDev& L = A.L;
+        const int e0 = L.n[0] + 3, e1 = L.n[1] + 3, e2 = L.n[2] + 3;
+        for (long long q = tid; q < (long long)e0 * e1 * e2; q += nth) {
+            const int i = (int)(q % e0) - 1, j = (int)((q / e0) % e1) - 1, k = (int)(q / ((long long)e0 * e1)) - 1;
+            const int si = np_map_index(i, L.n[0], L.map_lo[0], L.map_hi[0]);
+            const int sj = np_map_index(j, L.n[1], L.map_lo[1], L.map_hi[1]);
+            const int sk = np_map_index(k, L.n[2], L.map_lo[2], L.map_hi[2]);
+            if (si == i && sj == j && sk == k) continue;
+            if (si < 0 || si > L.n[0] || sj < 0 || sj > L.n[1] || sk < 0 || sk > L.n[2]) continue;
+            x[np_noff(L, i, j, k)] = x[np_noff(L, si, sj, sk)];
+        }
+        __syncthreads();
+    }
+    // y = A x (x gets its ghosts filled), optionally divided by the diagonal (MLCGSolver's Lp.normalize)
+    __device__ void apply(double* y, double* x, bool normalize) const {
+        const LevelDev& L = A.L;
+        fill(x);
+        for (long long q = tid; q < nvalid; q += nth) {
+            int i, j, k; ijk(q, i, j, k);
+            const long long o = np_noff(L, i, j, k);
+            double val = 0.0;
+            if (!np_is_dirichlet(L, i, j, k)) {
+                GlobX xa{x + o, L.nsy, L.nsz};
+                double d, off;
+                if (L.const_sigma) { d = np_diag_const(L.c, L.sigma0); off = np_offdiag_const(L.c, L.sigma0, xa); }
+                else {
+                    GlobS sa{A.sig + np_coff(L, i, j, k), L.csy, L.csz};
+                    Sig8 g = np_load_sig(sa);
+                    d = np_diag(L.c, g); off = np_offdiag(L.c, g, xa);
+                }
+                val = xa(0,0,0) * d + off;
+                if (normalize) val /= d;
+            }
+            y[o] = val;
+        }
+        __syncthreads();
+    }
+    __device__ void normalize_vec(double* x) const {
+        const LevelDev& L = A.L;
+        for (long long q = tid; q < nvalid; q += nth) {
+            int i, j, k; ijk(q, i, j, k);
+            const long long o = np_noff(L, i, j, k);
+            if (np_is_dirichlet(L, i, j, k)) { x[o] = 0.0; continue; }
+            double d;
+            if (L.const_sigma) d = np_diag_const(L.c, L.sigma0);
+            else { GlobS sa{A.sig + np_coff(L, i, j, k), L.csy, L.csz}; Sig8 g = np_load_sig(sa); d = np_diag(L.c, g); }
+            x[o] /= d;
+        }
+        __syncthreads();
+    }
+    __device__ double dot(const double* x, const double* y) const {
+        const LevelDev& L = A.L;
+        double a = 0.0;
+        for (long long q = tid; q < nvalid; q += nth) {
+            int i, j, k; ijk(q, i, j, k);
+            if (i > L.owned_hi[0] || j > L.owned_hi[1] || k > L.owned_hi[2]) continue;
+            const long long o = np_noff(L, i, j, k);
+            a += np_neumann_weight(L, i, j, k) * x[o] * y[o];
+        }
+        return np_block_reduce<false>(a);
+    }
+    __device__ double norminf(const double* x) const {
+        const LevelDev& L = A.L;
+        double a = 0.0;
+        for (long long q = tid; q < nvalid; q += nth) { int i, j, k; ijk(q, i, j, k); a = fmax(a, fabs(x[np_noff(L, i, j, k)])); }
+        return np_block_reduce<true>(a);
+    }
+    __device__ double wsum(const double* x, double& wtot) const {
+        const LevelDev& L = A.L;
+        double a = 0.0, w = 0.0;
+        for (long long q = tid; q < nvalid; q += nth) {
+            int i, j, k; ijk(q, i, j, k);
+            if (i > L.owned_hi[0] || j > L.owned_hi[1] || k > L.owned_hi[2]) continue;
+            const double ww = np_neumann_weight(L, i, j, k);
+            a += ww * x[np_noff(L, i, j, k)]; w += ww;
+        }
+        a = np_block_reduce<false>(a); wtot = np_block_reduce<false>(w);
+        return a;
+    }
+};
+
+__global__ void __launch_bounds__(1024) k_bottom_solve(BottomArgs A)
+{
+    BottomCtx C(A);
+    const LevelDev& L = A.L;
+    const int tid = C.tid, nth = C.nth;
+    const long long ntot = L.ntot;
+    // bb = b (made solvable when the operator is singular: MLMG::bottomSolve -> makeSolvable)
+    for (long long q = tid; q < ntot; q += nth) { A.bb[q] = A.b[q]; A.x[q] = 0.0; A.p[q] = 0.0; A.s[q] = 0.0; }
+    __syncthreads();
+    if (A.singular) {
+        double wtot; double sum = C.wsum(A.bb, wtot);
+        const double off = sum / wtot;
+        for (long long q = tid; q < C.nvalid; q += nth) { int i, j, k; C.ijk(q, i, j, k); A.bb[np_noff(L, i, j, k)] -= off; }
+        __syncthreads();
+    }
+    int ret = 0, iter = 1;
+    double rnorm, rnorm0;
+    if (A.type == 0) {
+        // ---------------- BiCGStab (MLCGSolver::solve_bicgstab), initial guess 0 -> r = b ----------------
+        for (long long q = tid; q < C.nvalid; q += nth) { int i, j, k; C.ijk(q, i, j, k); const long long o = np_noff(L, i, j, k); A.r[o] = A.bb[o]; }
+        __syncthreads();
+        if (A.normalize) C.normalize_vec(A.r);
+        for (long long q = tid; q < C.nvalid; q += nth) { int i, j, k; C.ijk(q, i, j, k); const long long o = np_noff(L, i, j, k); A.rh[o] = A.r[o]; }
+        __syncthreads();
+        rnorm = C.norminf(A.r); rnorm0 = rnorm;
+        if (rnorm0 == 0.0 || rnorm0 < A.eps_abs) { if (tid == 0) { A.out[0] = 0; A.out[1] = 0; } return; }
+        double rho_1 = 0.0, alpha = 0.0, omega = 0.0;
+        for (; iter <= A.maxiter; ++iter) {
+            const double rho = C.dot(A.rh, A.r);
+            if (rho == 0.0) { ret = 1; break; }
+            if (iter == 1) {
+                for (long long q = tid; q < C.nvalid; q += nth) { int i, j, k; C.ijk(q, i, j, k); const long long o = np_noff(L, i, j, k); A.p[o] = A.r[o]; }
+            } else {
+                const double beta = (rho / rho_1) * (alpha / omega);
+                for (long long q = tid; q < C.nvalid; q += nth) { int i, j, k; C.ijk(q, i, j, k); const long long o = np_noff(L, i, j, k);
+                    const double pv = A.p[o] - omega * A.v[o]; A.p[o] = A.r[o] + beta * pv; }
+            }
+            __syncthreads();
+            C.apply(A.v, A.p, A.normalize);
+            const double rhTv = C.dot(A.rh, A.v);
+            if (rhTv != 0.0) alpha = rho / rhTv; else { ret = 2; break; }
+            for (long long q = tid; q < C.nvalid; q += nth) { int i, j, k; C.ijk(q, i, j, k); const long long o = np_noff(L, i, j, k);
+                A.x[o] += alpha * A.p[o]; A.s[o] = A.r[o] - alpha * A.v[o]; }
+            __syncthreads();
+            rnorm = C.norminf(A.s);
+            if (rnorm < A.eps_rel * rnorm0 || rnorm < A.eps_abs) break;
+            C.apply(A.t, A.s, A.normalize);
+            const double tt = C.dot(A.t, A.t), ts = C.dot(A.t, A.s);
+            if (tt != 0.0) omega = ts / tt; else { ret = 3; break; }
+            for (long long q = tid; q < C.nvalid; q += nth) { int i, j, k; C.ijk(q, i, j, k); const long long o = np_noff(L, i, j, k);
+                A.x[o] += omega * A.s[o]; A.r[o] = A.s[o] - omega * A.t[o]; }
+            __syncthreads();
+            rnorm = C.norminf(A.r);
+            if (rnorm < A.eps_rel * rnorm0 || rnorm < A.eps_abs) break;
+            if (omega == 0.0) { ret = 4; break; }
+            rho_1 = rho;
+        }
+    } else {
+        // ---------------- CG (MLCGSolver::solve_cg) ----------------
+        for (long long q = tid; q < C.nvalid; q += nth) { int i, j, k; C.ijk(q, i, j, k); const long long o = np_noff(L, i, j, k); A.r[o] = A.bb[o]; }
+        __syncthreads();
+        rnorm = C.norminf(A.r); rnorm0 = rnorm;
+        if (rnorm0 == 0.0 || rnorm0 < A.eps_abs) { if (tid == 0) { A.out[0] = 0; A.out[1] = 0; } return; }
+        double rho_1 = 0.0;
+        for (; iter <= A.maxiter; ++iter) {
+            const double rho = C.dot(A.r, A.r);
+            if (rho == 0.0) { ret = 1; break; }
+            if (iter == 1) {
+                for (long long q = tid; q < C.nvalid; q += nth) { int i, j, k; C.ijk(q, i, j, k); const long long o = np_noff(L, i, j, k); A.p[o] = A.r[o]; }
+            } else {
+                const double beta = rho / rho_1;
+                for (long long q = tid; q < C.nvalid; q += nth) { int i, j, k; C.ijk(q, i, j, k); const long long o = np_noff(L, i, j, k); A.p[o] = A.r[o] + beta * A.p[o]; }
+            }
+            __syncthreads();
+            C.apply(A.v, A.p, false);
+            const double pw = C.dot(A.p, A.v);
+            double alpha;
+            if (pw != 0.0) alpha = rho / pw; else { ret = 1; break; }
+            for (long long q = tid; q < C.nvalid; q += nth) { int i, j, k; C.ijk(q, i, j, k); const long long o = np_noff(L, i, j, k);
+                A.x[o] += alpha * A.p[o]; A.r[o] -= alpha * A.v[o]; }
+            __syncthreads();
+            rnorm = C.norminf(A.r);
+            if (rnorm < A.eps_rel * rnorm0 || rnorm < A.eps_abs) break;
+            rho_1 = rho;
+        }
+    }
+    if (ret == 0 && rnorm > A.eps_rel * rnorm0 && rnorm > A.eps_abs) ret = 8;
+    if (!((ret == 0 || ret == 8) && rnorm < rnorm0)) {
+        for (long long q = tid; q < ntot; q += nth) A.x[q] = 0.0;     // sol = sorig (= 0)
+    }
+    if (tid == 0) { A.out[0] = ret; A.out[1] = iter < A.maxiter ? iter : A.maxiter; }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Multi-GPU agglomeration: every rank contributed its local coarse slab (layout Ll, ntot_l / ctot_l
+// elements per rank) to an all-gather; these kernels assemble the replicated whole-domain level Lg.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_assemble_nodal(LevelDev Lg, LevelDev Ll, double* __restrict__ dst, const double* __restrict__ recv, int nranks)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    const int K = blockIdx.z;
+    if (i > Lg.n[0] || j > Lg.n[1]) return;
+    int r = K / Ll.n[2]; if (r > nranks - 1) r = nranks - 1;
+    const int kl = K - r * Ll.n[2];
+    dst[np_noff(Lg, i, j, K)] = recv[(long long)r * Ll.ntot + np_noff(Ll, i, j, kl)];
+}
+__global__ void __launch_bounds__(256) k_assemble_cell(LevelDev Lg, LevelDev Ll, double* __restrict__ dst, const double* __restrict__ recv)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    const int K = blockIdx.z;
+    if (i >= Lg.n[0] || j >= Lg.n[1]) return;
+    const int r = K / Ll.n[2];
+    const int kl = K - r * Ll.n[2];
+    dst[np_coff(Lg, i, j, K)] = recv[(long long)r * Ll.ctot + np_coff(Ll, i, j, kl)];
+}
+__global__ void k_negate_one(double* p) { if (threadIdx.x == 0 && blockIdx.x == 0) p[0] = -p[0]; }

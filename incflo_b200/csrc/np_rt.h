@@ -1,0 +1,73 @@
+// np_rt.h — thin runtime layer: device memory, streams, events and the kernel-launch macro.
+//
+// Product build (nvcc): everything maps 1:1 onto the CUDA runtime; there is no other backend.
+// NP_EMU build (g++, tests only, see tests/emu/cuda_emu.h): the same kernels and the same host driver
+// run on a host emulation of blocks/threads so that kernel logic can be checked without a GPU.
+#pragma once
+#include <cstddef>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+
+#ifdef NP_EMU
+#include "cuda_emu.h"
+#include <chrono>
+typedef void* np_stream_t;
+struct np_event_s { std::chrono::steady_clock::time_point t; };
+typedef np_event_s* np_event_t;
+#define NP_LAUNCH(sync, kernel, grid, block, smem, stream, ...) \
+    np_emu::launch((grid), (block), (smem), (sync), [=]() { kernel(__VA_ARGS__); })
+#define NP_DYN_SMEM(type, name) type* name = reinterpret_cast<type*>((reinterpret_cast<uintptr_t>(np_emu::st().dyn.data()) + 15) & ~uintptr_t(15))
+namespace np_rt {
+inline int init() { return 0; }
+inline int dev_malloc(void** p, size_t n) { *p = std::calloc(n ? n : 1, 1); return *p ? 0 : 1; }
+inline int dev_free(void* p) { std::free(p); return 0; }
+inline int host_malloc(void** p, size_t n) { *p = std::malloc(n ? n : 1); return *p ? 0 : 1; }
+inline int host_free(void* p) { std::free(p); return 0; }
+inline int memset_async(void* p, int v, size_t n, np_stream_t) { std::memset(p, v, n); return 0; }
+inline int copy_async(void* d, const void* s, size_t n, np_stream_t) { std::memmove(d, s, n); return 0; }
+inline int stream_sync(np_stream_t) { return 0; }
+inline int is_device_ptr(const void*) { return 1; }
+inline int event_create(np_event_t* e) { *e = new np_event_s(); return 0; }
+inline int event_destroy(np_event_t e) { delete e; return 0; }
+inline int event_record(np_event_t e, np_stream_t) { e->t = std::chrono::steady_clock::now(); return 0; }
+inline float event_ms(np_event_t a, np_event_t b) { return std::chrono::duration<float, std::milli>(b->t - a->t).count(); }
+inline int last_error() { return 0; }
+inline const char* last_error_string() { return "emu"; }
+inline int sm_count() { return 4; }
+} // namespace np_rt
+#else
+#include <cuda_runtime.h>
+typedef cudaStream_t np_stream_t;
+typedef cudaEvent_t np_event_t;
+#define NP_LAUNCH(sync, kernel, grid, block, smem, stream, ...) \
+    kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__)
+#define NP_DYN_SMEM(type, name) extern __shared__ __align__(16) unsigned char name##_raw_[]; type* name = reinterpret_cast<type*>(name##_raw_)
+namespace np_rt {
+inline int init() {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) { cudaGetLastError(); return 1; }
+    return 0;
+}
+inline int dev_malloc(void** p, size_t n) { return cudaMalloc(p, n ? n : 1) == cudaSuccess ? 0 : 1; }
+inline int dev_free(void* p) { return cudaFree(p) == cudaSuccess ? 0 : 1; }
+inline int host_malloc(void** p, size_t n) { return cudaMallocHost(p, n ? n : 1) == cudaSuccess ? 0 : 1; }
+inline int host_free(void* p) { return cudaFreeHost(p) == cudaSuccess ? 0 : 1; }
+inline int memset_async(void* p, int v, size_t n, np_stream_t s) { return cudaMemsetAsync(p, v, n, s) == cudaSuccess ? 0 : 1; }
+inline int copy_async(void* d, const void* s, size_t n, np_stream_t st) { return cudaMemcpyAsync(d, s, n, cudaMemcpyDefault, st) == cudaSuccess ? 0 : 1; }
+inline int stream_sync(np_stream_t s) { return cudaStreamSynchronize(s) == cudaSuccess ? 0 : 1; }
+inline int is_device_ptr(const void* p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+inline int event_create(np_event_t* e) { return cudaEventCreate(e) == cudaSuccess ? 0 : 1; }
+inline int event_destroy(np_event_t e) { return cudaEventDestroy(e) == cudaSuccess ? 0 : 1; }
+inline int event_record(np_event_t e, np_stream_t s) { return cudaEventRecord(e, s) == cudaSuccess ? 0 : 1; }
+inline float event_ms(np_event_t a, np_event_t b) { float ms = 0; cudaEventSynchronize(b); cudaEventElapsedTime(&ms, a, b); return ms; }
+inline int last_error() { return cudaGetLastError() == cudaSuccess ? 0 : 1; }
+inline const char* last_error_string() { return cudaGetErrorString(cudaPeekAtLastError()); }
+inline int sm_count() { int dev = 0, n = 148; cudaGetDevice(&dev); cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev); return n; }
+} // namespace np_rt
+#endif

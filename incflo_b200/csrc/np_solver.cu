@@ -1,0 +1,584 @@
+// np_solver.cu — host driver: hierarchy, V-cycle (amrex::MLMG::solve / mgVcycle / bottomSolve restated as
+// launch sequences), projection (amrex::NodalProjector::project).  Reference call site:
+// /root/reference/src/projection/incflo_apply_nodal_projection.cpp:148-166.
+#include "np_solver.h"
+#include "np_kernels.cuh"
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+
+static inline int shell_blocks(long long n) { long long b = (n + 255) / 256; return (int)std::min<long long>(std::max<long long>(b, 1), 4096); }
+
+static int alloc_d(double** p, long long n) {
+    void* q = nullptr;
+    if (np_rt::dev_malloc(&q, (size_t)n * sizeof(double))) return NP_ERR_CUDA;
+    *p = (double*)q;
+    return 0;
+}
+
+// written planes per smoother z-chunk: chunks of about `target` planes, never a sliver
+static int pick_zchunk(int nnodes_z, int target) {
+    int nch = std::max(1, (nnodes_z + target / 2) / target);
+    return (nnodes_z + nch - 1) / nch;
+}
+
+static void fill_coef(LevelDev& d) {
+    const double fx = d.dxinv[0]*d.dxinv[0]/36.0, fy = d.dxinv[1]*d.dxinv[1]/36.0, fz = d.dxinv[2]*d.dxinv[2]/36.0;
+    d.c.fxyz = fx+fy+fz;
+    d.c.fmx2y2z = -fx+2*fy+2*fz; d.c.f2xmy2z = 2*fx-fy+2*fz; d.c.f2x2ymz = 2*fx+2*fy-fz;
+    d.c.f4xm2ym2z = 4*fx-2*fy-2*fz; d.c.fm2x4ym2z = -2*fx+4*fy-2*fz; d.c.fm2xm2y4z = -2*fx-2*fy+4*fz;
+}
+
+static void set_dims(LevelDev& d, int n0, int n1, int n2) {
+    d.n[0] = n0; d.n[1] = n1; d.n[2] = n2;
+    d.nsy = (n0 + 3 + 1) & ~1LL; d.nsz = d.nsy * (n1 + 3); d.ntot = d.nsz * (n2 + 3);
+    d.csy = (n0 + 2 + 1) & ~1LL; d.csz = d.csy * (n1 + 2); d.ctot = d.csz * (n2 + 2);
+}
+
+void NpSolver::zero(double* p, long long n) { np_rt::memset_async(p, 0, (size_t)n * sizeof(double), stream); }
+
+int NpSolver::create(const np_geom* g, int nboxes, const np_box* boxes, const int* owner, int my_rank, int nranks,
+                     const NpComm& c, const np_options* o)
+{
+    if (np_rt::init()) return NP_ERR_NO_DEVICE;
+    geom = *g; opt = *o; comm = c; comm.rank = my_rank; comm.nranks = nranks;
+    // ---- box layout: one box (nranks == 1) or equal z-slabs ordered by rank ----
+    if (nboxes != nranks) return NP_ERR_INVALID;
+    const int nzl = g->ncell[2] / nranks;
+    if (nzl * nranks != g->ncell[2]) return NP_ERR_INVALID;
+    for (int r = 0; r < nranks; ++r) {
+        const np_box& b = boxes[r];
+        if (owner[r] != r) return NP_ERR_INVALID;
+        if (b.lo[0] != 0 || b.lo[1] != 0 || b.hi[0] != g->ncell[0]-1 || b.hi[1] != g->ncell[1]-1) return NP_ERR_INVALID;
+        if (b.lo[2] != r*nzl || b.hi[2] != (r+1)*nzl-1) return NP_ERR_INVALID;
+    }
+    nloc[0] = g->ncell[0]; nloc[1] = g->ncell[1]; nloc[2] = nzl; koff = my_rank * nzl;
+    for (int d = 0; d < 3; ++d) { bclo[d] = bchi[d] = g->periodic[d] ? NP_BC_PERIODIC : NP_BC_NEUMANN; }
+
+    // ---- MG levels (MLLinOp::defineGrids: coarsen by 2 while every box stays coarsenable, min width 2) ----
+    lev.clear();
+    int n[3] = {nloc[0], nloc[1], nloc[2]};
+    int nglob2 = g->ncell[2];
+    double dxinv[3];
+    for (int d = 0; d < 3; ++d) dxinv[d] = g->ncell[d] / (g->prob_hi[d] - g->prob_lo[d]);
+    int ko = koff;
+    bool replicated = false;
+    for (;;) {
+        NpLevel L;
+        set_dims(L.d, n[0], n[1], n[2]);
+        for (int d = 0; d < 3; ++d) L.d.dxinv[d] = dxinv[d];
+        fill_coef(L.d);
+        L.d.const_sigma = 0; L.d.sigma0 = 1.0;
+        L.koff = ko; L.nglob2 = nglob2; L.replicated = replicated;
+        L.zc = opt.smooth_zchunk > 0 ? opt.smooth_zchunk : pick_zchunk(n[2] + 1, 64);
+        lev.push_back(L);
+        if ((int)lev.size() > opt.max_coarsening_level) break;
+        // multi-GPU: below agg_min_local_nz the next level is replicated on every rank (whole domain)
+        int nn[3] = {n[0], n[1], n[2]};
+        bool to_replica = false;
+        if (nranks > 1 && !replicated && n[2] / 2 < opt.agg_min_local_nz) { to_replica = true; nn[2] = nglob2; }
+        bool ok = true;
+        for (int d = 0; d < 3; ++d) if (nn[d] % 2 || nn[d] < 4) ok = false;
+        if (!replicated && nranks > 1 && !to_replica && (n[2] % 2 || n[2] < 4)) ok = false;
+        if (!ok) break;
+        if (to_replica) { replicated = true; agg_lev = (int)lev.size(); ko = 0; }
+        n[0] = nn[0] / 2; n[1] = nn[1] / 2; n[2] = nn[2] / 2; nglob2 /= 2; if (!to_replica) ko /= 2;
+        for (int d = 0; d < 3; ++d) dxinv[d] *= 0.5;
+    }
+    // ---- allocations ----
+    if (np_rt::last_error()) {}
+    for (auto& L : lev) {
+        if (alloc_d(&L.sigma, L.d.ctot) || alloc_d(&L.res, L.d.ntot) || alloc_d(&L.cor, L.d.ntot)
+            || alloc_d(&L.cor_alt, L.d.ntot) || alloc_d(&L.rescor, L.d.ntot)) return NP_ERR_CUDA;
+        zero(L.res, L.d.ntot); zero(L.cor, L.d.ntot); zero(L.cor_alt, L.d.ntot); zero(L.rescor, L.d.ntot);
+        zero(L.sigma, L.d.ctot);
+    }
+    const LevelDev& d0 = lev[0].d;
+    if (alloc_d(&sol, d0.ntot) || alloc_d(&rhs, d0.ntot)) return NP_ERR_CUDA;
+    zero(sol, d0.ntot); zero(rhs, d0.ntot);
+    const long long gcell = (long long)(d0.n[0]+2) * (d0.n[1]+2) * (d0.n[2]+2) * 3;
+    const long long pnod = (long long)(d0.n[0]+3) * (d0.n[1]+3) * (d0.n[2]+3);
+    if (alloc_d(&gphi, gcell) || alloc_d(&phi_out, pnod)) return NP_ERR_CUDA;
+    zero(gphi, gcell); zero(phi_out, pnod);
+    npart = nblocks(grid_nodes(d0)) + 16;
+    if (alloc_d(&part0, npart) || alloc_d(&part1, npart) || alloc_d(&scal, 64)) return NP_ERR_CUDA;
+    void* q = nullptr;
+    if (np_rt::host_malloc(&q, 64 * sizeof(double))) return NP_ERR_CUDA;
+    h_scal = (double*)q;
+    if (np_rt::dev_malloc(&q, 8 * sizeof(int))) return NP_ERR_CUDA;
+    bot_out = (int*)q;
+    if (np_rt::host_malloc(&q, 8 * sizeof(int))) return NP_ERR_CUDA;
+    h_bot_out = (int*)q;
+    const LevelDev& db = lev.back().d;
+    for (int w = 0; w < 7; ++w) { if (alloc_d(&bw[w], db.ntot)) return NP_ERR_CUDA; zero(bw[w], db.ntot); }
+    if (agg_lev >= 0) {
+        // all-gather staging for the first replicated level: one local coarse slab per rank
+        LevelDev dl = lev[agg_lev - 1].d;
+        set_dims(dl, dl.n[0] / 2, dl.n[1] / 2, dl.n[2] / 2);
+        const long long m = std::max(dl.ntot, dl.ctot);
+        if (alloc_d(&agg_send, m) || alloc_d(&agg_recv, m * nranks)) return NP_ERR_CUDA;
+        zero(agg_send, m); zero(agg_recv, m * nranks);
+    }
+    for (int e = 0; e < 4; ++e) np_rt::event_create(&ev[e]);
+    for (auto& L : lev) setup_level_bc(L);
+#ifndef NP_EMU
+    cudaFuncSetAttribute(k_smooth_tiled<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         (int)((NP_XRING * NP_XPLANE + NP_SRING * NP_SLAYER) * sizeof(double)));
+    cudaFuncSetAttribute(k_smooth_tiled<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         (int)((NP_XRING * NP_XPLANE + NP_SRING * NP_SLAYER) * sizeof(double)));
+#endif
+    np_rt::stream_sync(stream);
+    return np_rt::last_error() ? NP_ERR_CUDA : NP_OK;
+}
+
+void NpSolver::destroy()
+{
+    np_rt::stream_sync(stream);
+    for (auto& L : lev) { np_rt::dev_free(L.sigma); np_rt::dev_free(L.res); np_rt::dev_free(L.cor); np_rt::dev_free(L.cor_alt); np_rt::dev_free(L.rescor); }
+    lev.clear();
+    double* ds[] = {sol, rhs, gphi, phi_out, part0, part1, scal, xbuf_lo, xbuf_hi, agg_send, agg_recv, stage_vel, stage_sig};
+    for (double* p : ds) if (p) np_rt::dev_free(p);
+    for (int w = 0; w < 7; ++w) if (bw[w]) np_rt::dev_free(bw[w]);
+    if (h_scal) np_rt::host_free(h_scal);
+    if (bot_out) np_rt::dev_free(bot_out);
+    if (h_bot_out) np_rt::host_free(h_bot_out);
+    for (int e = 0; e < 4; ++e) if (ev[e]) np_rt::event_destroy(ev[e]);
+}
+
+// Per-level face types and ghost maps from the domain BCs and this rank's position in the slab stack.
+void NpSolver::setup_level_bc(NpLevel& L)
+{
+    LevelDev& d = L.d;
+    const bool sharded = comm.nranks > 1 && !L.replicated;
+    for (int dim = 0; dim < 3; ++dim) {
+        bool lo_dom = true, hi_dom = true;
+        if (dim == 2 && sharded) { lo_dom = (L.koff == 0); hi_dom = (L.koff + d.n[2] == L.nglob2); }
+        const int blo = bclo[dim], bhi = bchi[dim];
+        d.face[dim]     = (lo_dom && blo != NP_BC_PERIODIC) ? (blo == NP_BC_DIRICHLET ? NP_FACE_DIRICHLET : NP_FACE_NEUMANN) : NP_FACE_NONE;
+        d.face[dim + 3] = (hi_dom && bhi != NP_BC_PERIODIC) ? (bhi == NP_BC_DIRICHLET ? NP_FACE_DIRICHLET : NP_FACE_NEUMANN) : NP_FACE_NONE;
+        const bool remote = (dim == 2 && sharded);
+        d.map_lo[dim] = d.face[dim] == NP_FACE_NEUMANN ? NP_MAP_MIRROR
+                      : (blo == NP_BC_PERIODIC && !remote ? NP_MAP_PERIODIC : NP_MAP_NONE);
+        d.map_hi[dim] = d.face[dim + 3] == NP_FACE_NEUMANN ? NP_MAP_MIRROR
+                      : (bhi == NP_BC_PERIODIC && !remote ? NP_MAP_PERIODIC : NP_MAP_NONE);
+        // the high face is a duplicate when it is periodic or shared with the next rank
+        const bool hi_dup = (bhi == NP_BC_PERIODIC) || (remote && !hi_dom);
+        d.owned_hi[dim] = hi_dup ? d.n[dim] - 1 : d.n[dim];
+    }
+}
+
+int NpSolver::set_bc(const int lo[3], const int hi[3])
+{
+    for (int d = 0; d < 3; ++d) {
+        if ((lo[d] == NP_BC_PERIODIC) != (hi[d] == NP_BC_PERIODIC)) return NP_ERR_INVALID;
+        if ((lo[d] == NP_BC_PERIODIC) != (geom.periodic[d] != 0)) return NP_ERR_INVALID;
+        if (lo[d] < 0 || lo[d] > 2 || hi[d] < 0 || hi[d] > 2) return NP_ERR_INVALID;
+        bclo[d] = lo[d]; bchi[d] = hi[d];
+    }
+    singular = true;
+    for (int d = 0; d < 3; ++d) if (bclo[d] == NP_BC_DIRICHLET || bchi[d] == NP_BC_DIRICHLET) singular = false;
+    for (auto& L : lev) setup_level_bc(L);
+    return NP_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Building blocks
+// ------------------------------------------------------------------------------------------------
+static inline bool is_sharded(const NpSolver& S, const NpLevel& L) { return S.comm.nranks > 1 && !L.replicated; }
+
+// ring neighbours of this rank for a z-periodic / non-periodic slab stack
+static void z_neighbours(const NpSolver& S, int& lo, int& hi) {
+    const int r = S.comm.rank, R = S.comm.nranks;
+    const bool per = S.bclo[2] == NP_BC_PERIODIC;
+    lo = r > 0 ? r - 1 : (per ? R - 1 : -1);
+    hi = r < R - 1 ? r + 1 : (per ? 0 : -1);
+}
+
+// FillBoundary + nodalSync + applyBC on one nodal array
+void NpSolver::fill(int l, double* x)
+{
+    NpLevel& L = lev[l];
+    const LevelDev& d = L.d;
+    const long long nshell = 3LL * ((long long)(d.n[1]+3)*(d.n[2]+3) + (long long)(d.n[0]+3)*(d.n[2]+3) + (long long)(d.n[0]+3)*(d.n[1]+3));
+    NP_LAUNCH(false, k_fill_boundary, dim3(shell_blocks(nshell)), dim3(256), 0, stream, d, x); ++launches;
+    if (is_sharded(*this, L)) {
+        int lo, hi; z_neighbours(*this, lo, hi);
+        const long long pl = d.nsz;
+        // to the lower rank: my planes 0,1 (its n2, n2+1); to the upper rank: my plane n2-1 (its -1)
+        int rc = comm.sendrecv(comm.ctx, x + pl * 1, 2 * pl, x + 0, pl,
+                               x + pl * (long long)d.n[2], pl, x + pl * (long long)(d.n[2] + 1), 2 * pl, lo, hi, (void*)stream);
+        if (rc) err = NP_ERR_NCCL;
+    }
+}
+
+void NpSolver::apply(int l, double* y, double* x)
+{
+    fill(l, x);
+    const LevelDev& d = lev[l].d;
+    if (d.const_sigma) NP_LAUNCH(true, (k_adotx<0, true, false>), grid_nodes(d), NP_BLK, 0, stream, d, y, x, (const double*)nullptr, lev[l].sigma, (double*)nullptr);
+    else               NP_LAUNCH(true, (k_adotx<0, false, false>), grid_nodes(d), NP_BLK, 0, stream, d, y, x, (const double*)nullptr, lev[l].sigma, (double*)nullptr);
+    ++launches;
+}
+
+// y = b - A x; with_norm leaves per-block maxima of |y| in part0 (see finish_norm)
+void NpSolver::residual(int l, double* y, double* x, const double* b, bool with_norm)
+{
+    fill(l, x);
+    const LevelDev& d = lev[l].d;
+    if (d.const_sigma) {
+        if (with_norm) NP_LAUNCH(true, (k_adotx<1, true, true>), grid_nodes(d), NP_BLK, 0, stream, d, y, x, b, lev[l].sigma, part0);
+        else           NP_LAUNCH(true, (k_adotx<1, true, false>), grid_nodes(d), NP_BLK, 0, stream, d, y, x, b, lev[l].sigma, part0);
+    } else {
+        if (with_norm) NP_LAUNCH(true, (k_adotx<1, false, true>), grid_nodes(d), NP_BLK, 0, stream, d, y, x, b, lev[l].sigma, part0);
+        else           NP_LAUNCH(true, (k_adotx<1, false, false>), grid_nodes(d), NP_BLK, 0, stream, d, y, x, b, lev[l].sigma, part0);
+    }
+    ++launches;
+}
+
+// fold the per-block maxima left in part0 by a NORM kernel on level l; returns the global inf-norm
+double NpSolver::finish_norm(int l)
+{
+    const LevelDev& d = lev[l].d;
+    NP_LAUNCH(true, (k_reduce_final<true>), dim3(1), dim3(256), 0, stream, (const double*)part0, nblocks(grid_nodes(d)), scal, 0); ++launches;
+    if (is_sharded(*this, lev[l])) { if (comm.allreduce(comm.ctx, scal, 1, 1, (void*)stream)) err = NP_ERR_NCCL; }
+    np_rt::copy_async(h_scal, scal, sizeof(double), stream);
+    np_rt::stream_sync(stream);
+    return h_scal[0];
+}
+
+double NpSolver::norminf(int l, const double* x)
+{
+    const LevelDev& d = lev[l].d;
+    NP_LAUNCH(true, k_norminf, grid_nodes(d), NP_BLK, 0, stream, d, x, part0); ++launches;
+    return finish_norm(l);
+}
+
+// MLMG::makeSolvable on level l: x -= (sum w x)/(sum w) over owned nodes, scalars never leave the device
+void NpSolver::make_solvable(int l, double* x)
+{
+    const LevelDev& d = lev[l].d;
+    const long long nb = nblocks(grid_nodes(d));
+    NP_LAUNCH(true, k_wdot, grid_nodes(d), NP_BLK, 0, stream, d, (const double*)x, (const double*)nullptr, part0, part1); ++launches;
+    NP_LAUNCH(true, (k_reduce_final<false>), dim3(1), dim3(256), 0, stream, (const double*)part0, nb, scal, 2); ++launches;
+    NP_LAUNCH(true, (k_reduce_final<false>), dim3(1), dim3(256), 0, stream, (const double*)part1, nb, scal, 3); ++launches;
+    if (is_sharded(*this, lev[l])) { if (comm.allreduce(comm.ctx, scal + 2, 2, 0, (void*)stream)) err = NP_ERR_NCCL; }
+    NP_LAUNCH(false, k_sub_offset, grid_nodes(d), NP_BLK, 0, stream, d, x, (const double*)(scal + 2)); ++launches;
+}
+
+// one Fsmooth (two GS sweeps) on lev[l].cor with rhs lev[l].res, then sync + ghost fill of the result
+void NpSolver::smooth(int l, bool skip_fill)
+{
+    NpLevel& L = lev[l];
+    const LevelDev& d = L.d;
+    if (!skip_fill && !L.cor_ghost_clean) fill(l, L.cor);
+    const dim3 grid((d.n[0] + 1 + NP_TW - 1) / NP_TW, (d.n[1] + 1 + NP_TW - 1) / NP_TW, (d.n[2] + 1 + L.zc - 1) / L.zc);
+    const size_t smem = (NP_XRING * NP_XPLANE + NP_SRING * NP_SLAYER) * sizeof(double);
+    if (d.const_sigma) NP_LAUNCH(true, (k_smooth_tiled<true>), grid, dim3(256), smem, stream, d, L.cor_alt, (const double*)L.cor, (const double*)L.res, (const double*)L.sigma, L.zc);
+    else               NP_LAUNCH(true, (k_smooth_tiled<false>), grid, dim3(256), smem, stream, d, L.cor_alt, (const double*)L.cor, (const double*)L.res, (const double*)L.sigma, L.zc);
+    ++launches;
+    std::swap(L.cor, L.cor_alt);
+    fill(l, L.cor);                 // nodalSync (+ the ghosts the next operation needs)
+    L.cor_ghost_clean = true;
+}
+
+// res[lc] = R(fine), fine on level lc-1 (its ghosts are filled here: restriction's applyBC)
+void NpSolver::restrict_to(int lc, double* crse, double* fine)
+{
+    fill(lc - 1, fine);
+    const LevelDev& dc = lev[lc].d; const LevelDev& df = lev[lc - 1].d;
+    if (lev[lc].replicated && !lev[lc - 1].replicated) { restrict_to_replica(lc, crse, fine); return; }
+    NP_LAUNCH(false, k_restrict, grid_nodes(dc), NP_BLK, 0, stream, dc, df, crse, (const double*)fine); ++launches;
+}
+
+void NpSolver::interp_add(int lf, double* fine, const double* crse)
+{
+    const LevelDev& df = lev[lf].d; const LevelDev& dc = lev[lf + 1].d;
+    const int koffc = (lev[lf + 1].replicated && !lev[lf].replicated) ? lev[lf].koff / 2 : 0;
+    if (opt.interp_sigma_weighted && !df.const_sigma)
+        NP_LAUNCH(false, (k_interp_add<true>), grid_nodes(df), NP_BLK, 0, stream, df, dc, fine, crse, (const double*)lev[lf].sigma, koffc);
+    else
+        NP_LAUNCH(false, (k_interp_add<false>), grid_nodes(df), NP_BLK, 0, stream, df, dc, fine, crse, (const double*)lev[lf].sigma, koffc);
+    ++launches;
+}
+
+// MLMG::bottomSolve: x = cor[bottom] <- solve(res[bottom]).  Returns the number of Krylov iterations.
+int NpSolver::bottom_solve()
+{
+    const int l = (int)lev.size() - 1;
+    NpLevel& L = lev[l];
+    int iters = 0;
+    auto run = [&](int type) -> int {
+        BottomArgs a;
+        a.L = L.d; a.x = L.cor; a.b = L.res;
+        a.r = bw[0]; a.rh = bw[1]; a.p = bw[2]; a.v = bw[3]; a.s = bw[4]; a.t = bw[5]; a.bb = bw[6];
+        a.sig = L.sigma; a.maxiter = opt.bottom_maxiter; a.eps_rel = opt.bottom_rtol; a.eps_abs = opt.bottom_atol;
+        a.singular = singular ? 1 : 0; a.normalize = opt.bottom_normalize; a.type = type; a.out = bot_out;
+        const long long nv = (long long)(L.d.n[0] + 1) * (L.d.n[1] + 1) * (L.d.n[2] + 1);
+        int nth = (int)std::min<long long>(1024, std::max<long long>(64, ((nv + 31) / 32) * 32));
+        NP_LAUNCH(true, k_bottom_solve, dim3(1), dim3(nth), 0, stream, a); ++launches;
+        np_rt::copy_async(h_bot_out, bot_out, 2 * sizeof(int), stream);
+        np_rt::stream_sync(stream);
+        iters += h_bot_out[1];
+        return h_bot_out[0];
+    };
+    if (opt.bottom_solver == NP_BOTTOM_SMOOTHER) {
+        zero(L.cor, L.d.ntot); L.cor_ghost_clean = true;
+        for (int i = 0; i < opt.num_final_smooth; ++i) smooth(l, i == 0);
+        return 0;
+    }
+    int type = (opt.bottom_solver == NP_BOTTOM_CG || (opt.bottom_solver == NP_BOTTOM_BICGCG && bicg_failed_switch)) ? 1 : 0;
+    int ret = run(type);
+    if (ret != 0 && ret != 9) {
+        if (opt.bottom_verbose) std::printf("MLMG: Bottom solve failed (ret = %d)\n", ret);
+        if (opt.bottom_solver == NP_BOTTOM_BICGCG) {
+            const int other = 1 - type;
+            ret = run(other);
+            if (ret == 0) bicg_failed_switch = (other == 1);
+        }
+        if (ret != 0) zero(L.cor, L.d.ntot);
+    }
+    L.cor_ghost_clean = false;
+    if (ret != 0) for (int i = 0; i < opt.num_final_smooth; ++i) smooth(l, false);
+    return iters;
+}
+
+// MLMG::mgVcycle(0,0) on res[0]: leaves the correction in cor[0]
+void NpSolver::vcycle()
+{
+    const int nl = (int)lev.size();
+    for (int l = 0; l < nl - 1; ++l) {
+        NpLevel& L = lev[l];
+        zero(L.cor, L.d.ntot); L.cor_ghost_clean = true;
+        for (int i = 0; i < opt.num_pre_smooth; ++i) smooth(l, i == 0);
+        residual(l, L.rescor, L.cor, L.res, false);                 // computeResOfCorrection
+        restrict_to(l + 1, lev[l + 1].res, L.rescor);
+    }
+    stats.bottom_iters_total += bottom_solve();
+    for (int l = nl - 2; l >= 0; --l) {
+        NpLevel& L = lev[l];
+        interp_add(l, L.cor, lev[l + 1].cor);                       // addInterpCorrection
+        L.cor_ghost_clean = false;
+        for (int i = 0; i < opt.num_post_smooth; ++i) smooth(l, false);
+    }
+}
+
+// MLMG::solve with the zero initial guess NodalProjector uses
+int NpSolver::solve(double rtol, double atol)
+{
+    NpLevel& L0 = lev[0];
+    const LevelDev& d0 = L0.d;
+    zero(sol, d0.ntot);
+    bicg_failed_switch = false;
+    stats.bottom_iters_total = 0; stats.n_vcycles = 0; stats.status = NP_OK; stats.n_levels = (int)lev.size();
+    for (int i = 0; i < 128; ++i) stats.res_history[i] = 0.0;
+    if (singular) make_solvable(0, rhs);
+    const double rhsnorm0 = norminf(0, rhs);
+    residual(0, L0.res, sol, rhs, true);
+    const double resnorm0 = finish_norm(0);
+    const double max_norm = rhsnorm0 >= resnorm0 ? rhsnorm0 : resnorm0;
+    const double res_target = std::max(atol, std::max(rtol, 1e-16) * max_norm);
+    stats.rhs_norm0 = rhsnorm0; stats.res_norm0 = resnorm0; stats.res_norm_final = resnorm0;
+    if (!(resnorm0 == resnorm0)) { stats.status = NP_ERR_DIVERGED; return stats.status; }
+    if (resnorm0 <= res_target) return NP_OK;
+    bool converged = false;
+    for (int iter = 0; iter < opt.maxiter; ++iter) {
+        if (singular) make_solvable(0, L0.res);
+        vcycle();
+        NP_LAUNCH(false, k_add, grid_nodes(d0), NP_BLK, 0, stream, d0, sol, (const double*)L0.cor); ++launches;
+        residual(0, L0.res, sol, rhs, true);
+        const double rn = finish_norm(0);
+        if (iter < 128) stats.res_history[iter] = rn;
+        stats.n_vcycles = iter + 1; stats.res_norm_final = rn;
+        if (opt.verbose >= 2 && comm.rank == 0) std::printf("MLMG: Iteration %3d Fine resid/bnorm = %.6e\n", iter + 1, rn / max_norm);
+        if (err) { stats.status = err; return err; }
+        if (rn <= res_target) { converged = true; break; }
+        if (!(rn == rn) || rn > 1e20 * max_norm) { stats.status = NP_ERR_DIVERGED; return stats.status; }
+    }
+    if (!converged) stats.status = NP_ERR_NOT_CONVERGED;
+    return stats.status;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Multi-GPU: the first replicated level is assembled from every rank's local coarse slab
+// ------------------------------------------------------------------------------------------------
+static LevelDev local_coarse_of(const NpLevel& F)
+{
+    LevelDev dl = F.d;
+    set_dims(dl, F.d.n[0] / 2, F.d.n[1] / 2, F.d.n[2] / 2);
+    return dl;
+}
+void NpSolver::restrict_to_replica(int lc, double* crse, const double* fine)
+{
+    const LevelDev dl = local_coarse_of(lev[lc - 1]);
+    const LevelDev& dc = lev[lc].d;
+    NP_LAUNCH(false, k_restrict, grid_nodes(dl), NP_BLK, 0, stream, dl, lev[lc - 1].d, agg_send, fine); ++launches;
+    if (comm.allgather(comm.ctx, agg_send, agg_recv, dl.ntot, (void*)stream)) err = NP_ERR_NCCL;
+    NP_LAUNCH(false, k_assemble_nodal, grid_nodes(dc), NP_BLK, 0, stream, dc, dl, crse, (const double*)agg_recv, comm.nranks); ++launches;
+}
+void NpSolver::avgdown_sigma_to_replica(int lc)
+{
+    const LevelDev dl = local_coarse_of(lev[lc - 1]);
+    const LevelDev& dc = lev[lc].d;
+    NP_LAUNCH(false, k_avgdown_sigma, grid_cells(dl), NP_BLK, 0, stream, dl, lev[lc - 1].d, agg_send, (const double*)lev[lc - 1].sigma); ++launches;
+    if (comm.allgather(comm.ctx, agg_send, agg_recv, dl.ctot, (void*)stream)) err = NP_ERR_NCCL;
+    NP_LAUNCH(false, k_assemble_cell, grid_cells(dc), NP_BLK, 0, stream, dc, dl, lev[lc].sigma, (const double*)agg_recv); ++launches;
+}
+
+// ------------------------------------------------------------------------------------------------
+// sigma on every level (MLNodeLaplacian::setSigma + averageDownCoeffs + FillBoundaryCoeff)
+// ------------------------------------------------------------------------------------------------
+static void fill_sigma_level(NpSolver& S, int l)
+{
+    NpLevel& L = S.lev[l];
+    const LevelDev& d = L.d;
+    const bool sh = is_sharded(S, L);
+    const int per0 = S.bclo[0] == NP_BC_PERIODIC, per1 = S.bclo[1] == NP_BC_PERIODIC, per2 = S.bclo[2] == NP_BC_PERIODIC;
+    int zlo_local = 1, zhi_local = 1, p2 = per2;
+    if (sh) {
+        p2 = 0;
+        zlo_local = (!per2 && L.koff == 0);
+        zhi_local = (!per2 && L.koff + d.n[2] == L.nglob2);
+    }
+    const long long nshell = 2LL * ((long long)(d.n[1]+2)*(d.n[2]+2) + (long long)(d.n[0]+2)*(d.n[2]+2) + (long long)(d.n[0]+2)*(d.n[1]+2));
+    NP_LAUNCH(false, k_fill_sigma, dim3(shell_blocks(nshell)), dim3(256), 0, S.stream, d, L.sigma, per0, per1, p2, zlo_local, zhi_local); ++S.launches;
+    if (sh) {
+        int lo, hi; z_neighbours(S, lo, hi);
+        const long long pl = d.csz;
+        if (S.comm.sendrecv(S.comm.ctx, L.sigma + pl * 1, pl, L.sigma + 0, pl,
+                            L.sigma + pl * (long long)d.n[2], pl, L.sigma + pl * (long long)(d.n[2] + 1), pl, lo, hi, (void*)S.stream)) S.err = NP_ERR_NCCL;
+    }
+}
+
+int NpSolver::set_sigma(const FabView& s)
+{
+    const LevelDev& d0 = lev[0].d;
+    const long long nb = nblocks(grid_cells(d0));
+    NP_LAUNCH(true, k_copy_sigma_in, grid_cells(d0), NP_BLK, 0, stream, d0, lev[0].sigma, s, part0, part1); ++launches;
+    NP_LAUNCH(true, k_reduce_minmax, dim3(1), dim3(256), 0, stream, (const double*)part0, (const double*)part1, nb, scal + 4); ++launches;
+    NP_LAUNCH(false, k_negate_one, dim3(1), dim3(32), 0, stream, scal + 4); ++launches;   // (-min, max): one max-allreduce
+    if (comm.nranks > 1) { if (comm.allreduce(comm.ctx, scal + 4, 2, 1, (void*)stream)) err = NP_ERR_NCCL; }
+    np_rt::copy_async(h_scal + 4, scal + 4, 2 * sizeof(double), stream);
+    np_rt::stream_sync(stream);
+    const double smin = -h_scal[4], smax = h_scal[5];
+    const bool is_const = opt.const_sigma_fastpath && (smin == smax);
+    stats.sigma_is_const = is_const ? 1 : 0;
+    for (auto& L : lev) { L.d.const_sigma = is_const ? 1 : 0; L.d.sigma0 = smin; }
+    if (!is_const) {
+        fill_sigma_level(*this, 0);
+        for (int l = 1; l < (int)lev.size(); ++l) {
+            if (lev[l].replicated && !lev[l - 1].replicated) avgdown_sigma_to_replica(l);
+            else { NP_LAUNCH(false, k_avgdown_sigma, grid_cells(lev[l].d), NP_BLK, 0, stream, lev[l].d, lev[l - 1].d, lev[l].sigma, (const double*)lev[l - 1].sigma); ++launches; }
+            fill_sigma_level(*this, l);
+        }
+    }
+    have_sigma = true;
+    return err ? err : NP_OK;
+}
+
+FabView NpSolver::view_nodal(const np_fab& f, int l) const
+{
+    const LevelDev& d = lev[l].d;
+    FabView v; v.p = f.p; v.ng = f.ngrow;
+    v.sy = d.n[0] + 1 + 2 * f.ngrow; v.sz = v.sy * (d.n[1] + 1 + 2 * f.ngrow); v.sn = v.sz * (d.n[2] + 1 + 2 * f.ngrow);
+    return v;
+}
+FabView NpSolver::view_cell(const np_fab& f, int l, int ncomp) const
+{
+    const LevelDev& d = lev[l].d;
+    FabView v; v.p = f.p; v.ng = f.ngrow;
+    v.sy = d.n[0] + 2 * f.ngrow; v.sz = v.sy * (d.n[1] + 2 * f.ngrow); v.sn = v.sz * (d.n[2] + 2 * f.ngrow);
+    (void)ncomp;
+    return v;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Host-pointer staging: a caller built without CUDA hands host fabs; they are copied to the device
+// (cudaMemcpyAsync, pinned or pageable) and back.
+// ------------------------------------------------------------------------------------------------
+int NpSolver::import_fab(const np_fab& f, long long nelem, double** dev, bool* staged)
+{
+    if (np_rt::is_device_ptr(f.p)) { *dev = f.p; *staged = false; return NP_OK; }
+#ifdef NP_EMU
+    *dev = f.p; *staged = false; return NP_OK;
+#else
+    if (alloc_d(dev, nelem)) return NP_ERR_CUDA;
+    np_rt::copy_async(*dev, f.p, (size_t)nelem * sizeof(double), stream);
+    *staged = true;
+    return NP_OK;
+#endif
+}
+int NpSolver::export_fab(const np_fab& f, long long nelem, double* dev, bool staged)
+{
+    if (!staged) return NP_OK;
+    np_rt::copy_async(f.p, dev, (size_t)nelem * sizeof(double), stream);
+    np_rt::stream_sync(stream);
+    np_rt::dev_free(dev);
+    return NP_OK;
+}
+
+// periodic / rank-neighbour ghost layer of a 3-component cell fab (vel.FillBoundary, fluxes.FillBoundary)
+void np_fill_cell3(NpSolver& S, FabView u)
+{
+    NpLevel& L = S.lev[0];
+    const LevelDev& d = L.d;
+    const bool sh = is_sharded(S, L);
+    const int per0 = S.bclo[0] == NP_BC_PERIODIC, per1 = S.bclo[1] == NP_BC_PERIODIC, per2 = S.bclo[2] == NP_BC_PERIODIC;
+    const long long nshell = 2LL * ((long long)(d.n[1]+2)*(d.n[2]+2) + (long long)(d.n[0]+2)*(d.n[2]+2) + (long long)(d.n[0]+2)*(d.n[1]+2));
+    NP_LAUNCH(false, k_fill_vel, dim3(shell_blocks(nshell)), dim3(256), 0, S.stream, d, u, per0, per1, sh ? 0 : per2); ++S.launches;
+    if (sh) {
+        int lo, hi; z_neighbours(S, lo, hi);
+        // whole z-layers of the fab (all ghosts in x,y included) are contiguous per component
+        for (int n = 0; n < 3; ++n) {
+            double* base = u.p + u.sn * n;
+            const long long pl = u.sz;
+            const int g = u.ng;
+            if (S.comm.sendrecv(S.comm.ctx, base + pl * g, pl, base + pl * (g - 1), pl,
+                                base + pl * (long long)(g + d.n[2] - 1), pl, base + pl * (long long)(g + d.n[2]), pl,
+                                lo, hi, (void*)S.stream)) S.err = NP_ERR_NCCL;
+        }
+    }
+}
+
+// amrex::NodalProjector::project(rtol, atol)
+int NpSolver::project(np_fab* vel, const np_fab* sigma, double rtol, double atol)
+{
+    if (vel->ngrow < 1 || vel->ncomp < 3 || sigma->ncomp < 1) return NP_ERR_INVALID;
+    err = 0; launches = 0; have_result = false;
+    const LevelDev& d0 = lev[0].d;
+    np_rt::event_record(ev[0], stream);
+    // ---- inputs ----
+    FabView uv = view_cell(*vel, 0, 3), sv = view_cell(*sigma, 0, 1);
+    const long long nvel = uv.sn * 3, nsig = sv.sn;
+    double *dvel = nullptr, *dsig = nullptr; bool st_vel = false, st_sig = false;
+    if (import_fab(*vel, nvel, &dvel, &st_vel) || import_fab(*sigma, nsig, &dsig, &st_sig)) return NP_ERR_CUDA;
+    uv.p = dvel; sv.p = dsig;
+    int rc = set_sigma(sv);
+    if (st_sig) { np_rt::stream_sync(stream); np_rt::dev_free(dsig); }
+    if (rc) return rc;
+    // ---- rhs = div(u*) ----
+    np_fill_cell3(*this, uv);
+    NP_LAUNCH(false, k_divu, grid_nodes(d0), NP_BLK, 0, stream, d0, rhs, uv); ++launches;
+    np_rt::event_record(ev[1], stream);
+    // ---- solve ----
+    rc = solve(rtol, atol);
+    np_rt::event_record(ev[2], stream);
+    // ---- u = u* - sigma grad(phi); gradphi; phi ----
+    FabView gv; gv.p = gphi; gv.ng = 1; gv.sy = d0.n[0] + 2; gv.sz = gv.sy * (d0.n[1] + 2); gv.sn = gv.sz * (d0.n[2] + 2);
+    NP_LAUNCH(false, k_mknewu, grid_cells(d0), NP_BLK, 0, stream, d0, uv, gv, (const double*)sol, (const double*)lev[0].sigma); ++launches;
+    np_fill_cell3(*this, gv);
+    fill(0, sol);
+    FabView pv; pv.p = phi_out; pv.ng = 1; pv.sy = d0.n[0] + 3; pv.sz = pv.sy * (d0.n[1] + 3); pv.sn = pv.sz * (d0.n[2] + 3);
+    NP_LAUNCH(false, (k_copy_nodal<true>), dim3((d0.n[0] + 3 + 31) / 32, (d0.n[1] + 3 + 7) / 8, d0.n[2] + 3), NP_BLK, 0, stream, d0, sol, pv, 1); ++launches;
+    export_fab(*vel, nvel, dvel, st_vel);
+    np_rt::event_record(ev[3], stream);
+    np_rt::stream_sync(stream);
+    stats.ms_setup = np_rt::event_ms(ev[0], ev[1]);
+    stats.ms_solve = np_rt::event_ms(ev[1], ev[2]);
+    stats.ms_finish = np_rt::event_ms(ev[2], ev[3]);
+    stats.ms_total = np_rt::event_ms(ev[0], ev[3]);
+    stats.kernel_launches = launches;
+    if (np_rt::last_error()) { stats.status = NP_ERR_CUDA; return NP_ERR_CUDA; }
+    if (err) { stats.status = err; return err; }
+    have_result = true;
+    return rc;
+}

@@ -1,0 +1,103 @@
+// np_solver.h — host side of the nodal projection: MG hierarchy, V-cycle control (amrex::MLMG),
+// projection driver (amrex::NodalProjector::project).  All arithmetic is in np_kernels.cuh.
+#pragma once
+#include "np_types.h"
+#include "../../include/nodalproj.h"
+#include <vector>
+
+// Halo exchange / reductions between ranks.  Product build: NCCL (np_comm.cu).  The emulation build used
+// by the CPU tests plugs in callbacks (tests drive them over torch.distributed/gloo).
+struct NpComm {
+    int rank = 0, nranks = 1;
+    void* nccl = nullptr;
+    // ring neighbours exchange contiguous runs of doubles; rank -1 = no neighbour on that side
+    int (*sendrecv)(void* ctx, const double* send_lo, long long nsend_lo, double* recv_lo, long long nrecv_lo,
+                    const double* send_hi, long long nsend_hi, double* recv_hi, long long nrecv_hi,
+                    int lo_rank, int hi_rank, void* stream) = nullptr;
+    int (*allreduce)(void* ctx, double* buf, int n, int op /*0 sum, 1 max*/, void* stream) = nullptr;
+    int (*allgather)(void* ctx, const double* send, double* recv, long long cnt, void* stream) = nullptr;
+    void* ctx = nullptr;
+};
+
+struct NpLevel {
+    LevelDev d{};
+    double* sigma = nullptr;
+    double *res = nullptr, *cor = nullptr, *cor_alt = nullptr, *rescor = nullptr;
+    int zc = 65;                    // smoother: written planes per z-chunk
+    bool cor_ghost_clean = false;
+    bool replicated = false;        // multi-GPU: this level holds the whole domain on every rank
+    int koff = 0;                   // global z index of local cell 0
+    int nglob2 = 0;                 // global cells in z
+};
+
+struct NpSolver {
+    np_options opt{};
+    np_geom geom{};
+    int bclo[3] = {0,0,0}, bchi[3] = {0,0,0};
+    NpComm comm;
+    int nloc[3] = {0,0,0};
+    int koff = 0;
+    std::vector<NpLevel> lev;
+    int agg_lev = -1;               // first replicated level (multi-GPU), -1: none
+    // level-0 extras
+    double *sol = nullptr, *rhs = nullptr;
+    double *gphi = nullptr;         // cell, 3 comp, 1 ghost, FArrayBox layout
+    double *phi_out = nullptr;      // nodal, 1 ghost, FArrayBox layout (unpadded)
+    // scratch
+    double *part0 = nullptr, *part1 = nullptr; long long npart = 0;
+    double *scal = nullptr;         // device scalars
+    double *h_scal = nullptr;       // pinned mirror
+    int *bot_out = nullptr, *h_bot_out = nullptr;
+    double *bw[7] = {nullptr,nullptr,nullptr,nullptr,nullptr,nullptr,nullptr};   // bottom work arrays
+    double *xbuf_lo = nullptr, *xbuf_hi = nullptr;   // exchange staging
+    double *agg_send = nullptr, *agg_recv = nullptr;
+    // host staging (caller passes host pointers)
+    double *stage_vel = nullptr, *stage_sig = nullptr; long long stage_vel_n = 0, stage_sig_n = 0;
+    np_stream_t stream = 0;
+    np_event_t ev[4] = {0,0,0,0};
+    np_stats stats{};
+    bool have_sigma = false, have_result = false, singular = true;
+    bool bicg_failed_switch = false;
+    long long launches = 0;
+    int err = 0;
+
+    int create(const np_geom* g, int nboxes, const np_box* boxes, const int* owner, int my_rank, int nranks,
+               const NpComm& c, const np_options* o);
+    void destroy();
+    int set_bc(const int lo[3], const int hi[3]);
+    void setup_level_bc(NpLevel& L);
+
+    // building blocks (device pointers, internal layout)
+    void fill(int l, double* x);
+    void apply(int l, double* y, double* x);                       // fills x's ghosts first
+    void residual(int l, double* y, double* x, const double* b, bool with_norm);
+    void smooth(int l, bool skip_fill);                            // on lev[l].cor / res
+    void restrict_to(int lc, double* crse, double* fine);          // fine gets its ghosts filled
+    void restrict_to_replica(int lc, double* crse, const double* fine);
+    void avgdown_sigma_to_replica(int lc);
+    void interp_add(int lf, double* fine, const double* crse);
+    void make_solvable(int l, double* x);
+    double norminf(int l, const double* x);
+    double finish_norm(int l);                                     // reduce part0 partial maxima -> host
+    int bottom_solve();
+    void vcycle();
+    int solve(double rtol, double atol);
+    int set_sigma(const FabView& s);
+    int project(np_fab* vel, const np_fab* sigma, double rtol, double atol);
+    void zero(double* p, long long n);
+    FabView view_nodal(const np_fab& f, int l) const;
+    FabView view_cell(const np_fab& f, int l, int ncomp) const;
+    // host-pointer staging helpers for hooks
+    int import_fab(const np_fab& f, long long nelem, double** dev, bool* staged);
+    int export_fab(const np_fab& f, long long nelem, double* dev, bool staged);
+};
+
+struct np_handle { NpSolver S; };
+
+#define NP_BLK dim3(32, 8, 1)
+static inline dim3 grid_nodes(const LevelDev& L) { return dim3((L.n[0] + 1 + 31) / 32, (L.n[1] + 1 + 7) / 8, L.n[2] + 1); }
+static inline dim3 grid_cells(const LevelDev& L) { return dim3((L.n[0] + 31) / 32, (L.n[1] + 7) / 8, L.n[2]); }
+static inline long long nblocks(dim3 g) { return (long long)g.x * g.y * g.z; }
+
+void np_fill_cell3(NpSolver& S, FabView u);                 // np_solver.cu
+void np_comm_fill_nccl(NpComm& c, void* nccl_comm);          // np_comm.cu (product) / np_comm_emu.cpp (tests)

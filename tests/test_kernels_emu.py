@@ -1,0 +1,110 @@
+"""Kernel logic vs the oracle, on CPU.
+
+The product sources (incflo_b200/csrc) are compiled against a host emulation of the CUDA execution model
+(tests/emu, TEST-ONLY) and called through the same C ABI as on the GPU.  This checks index maps, tile /
+halo / pipeline schedules and the MG driver before GPU time is spent; the same comparisons run on the
+B200 in tests/test_gpu_parity.py.  Bit-level equality is not expected (different summation order), so
+every comparison carries an explicit tolerance relative to the field's size.
+"""
+import numpy as np
+import pytest
+
+import nphelp
+from oracle.oracle import Oracle, TILED
+
+BIG = 1 << 30
+P, D, N = 0, 1, 2
+BCS = [((P, P, P), (P, P, P)), ((N, N, N), (N, N, N)), ((P, N, D), (P, N, N)), ((D, P, N), (N, P, D))]
+
+
+def relerr(a, b):
+    return np.abs(a - b).max() / max(np.abs(b).max(), 1e-300)
+
+
+def make(ncell, bclo, bchi, sigma, prob_hi=(1.0, 1.0, 1.0), **opts):
+    drv = nphelp.Driver(ncell, (0, 0, 0), prob_hi, bclo, bchi, lib=nphelp.emu_lib(), **opts)
+    drv.set_sigma(sigma)
+    orc = Oracle(ncell, (0, 0, 0), prob_hi, bclo, bchi, smoother=TILED, tile=(31, 31, BIG), tile_z_target=64)
+    orc.set_sigma(sigma)
+    orc.prepare_sigma()
+    return drv, orc
+
+
+def nodal(rng, shape, bclo, bchi):
+    return nphelp.zero_dirichlet(nphelp.periodic_consistent(rng.standard_normal(shape), bclo), bclo, bchi)
+
+
+@pytest.mark.parametrize("bclo,bchi", BCS)
+@pytest.mark.parametrize("const_sigma", [False, True])
+def test_apply_restrict_interp_sigma(bclo, bchi, const_sigma):
+    rng = np.random.default_rng(7)
+    ncell = (16, 8, 12)
+    sigma = np.full((12, 8, 16), 0.7) if const_sigma else rng.uniform(0.5, 2.0, (12, 8, 16))
+    drv, orc = make(ncell, bclo, bchi, sigma, prob_hi=(1.6, 0.4, 2.4))
+    assert drv.P.num_levels == orc.num_levels
+    for l in range(orc.num_levels):
+        assert drv.P.level_ncell(l) == orc.level_ncell(l)
+        assert relerr(drv.get_sigma(l), orc.get_sigma(l)) < 1e-14
+        x = nodal(rng, orc.nshape(l), bclo, bchi)
+        assert relerr(drv.apply(l, x), orc.apply(l, x)) < 1e-13
+    for l in range(1, orc.num_levels):
+        f = nodal(rng, orc.nshape(l - 1), bclo, bchi)
+        c = nodal(rng, orc.nshape(l), bclo, bchi)
+        assert relerr(drv.restrict(l, f), orc.restrict(l, f)) < 1e-14
+        assert relerr(drv.interp_add(l - 1, f, c), orc.interp_add(l - 1, f, c)) < 1e-13
+
+
+@pytest.mark.parametrize("bclo,bchi", BCS)
+@pytest.mark.parametrize("ncell", [(16, 16, 16), (40, 36, 8)])
+def test_smoother_matches_oracle_tiled_order(bclo, bchi, ncell):
+    """Same ordering (overlapped 31x31 tiles, k-sequential, 4 colours, 2 sweeps) -> same iterates."""
+    rng = np.random.default_rng(11)
+    sigma = rng.uniform(0.5, 2.0, ncell[::-1])
+    drv, orc = make(ncell, bclo, bchi, sigma)
+    x = nodal(rng, orc.nshape(0), bclo, bchi)
+    r = nodal(rng, orc.nshape(0), bclo, bchi)
+    assert relerr(drv.smooth(0, x, r, 2), orc.smooth(0, x, r, 2)) < 1e-13
+
+
+def test_smoother_z_chunks():
+    rng = np.random.default_rng(12)
+    ncell = (8, 8, 96)                      # 97 planes -> two z-chunks of 49
+    bclo = bchi = (P, P, N)
+    sigma = rng.uniform(0.5, 2.0, ncell[::-1])
+    drv, orc = make(ncell, bclo, bchi, sigma)
+    x = nodal(rng, orc.nshape(0), bclo, bchi)
+    r = nodal(rng, orc.nshape(0), bclo, bchi)
+    assert relerr(drv.smooth(0, x, r, 1), orc.smooth(0, x, r, 1)) < 1e-13
+
+
+@pytest.mark.parametrize("bclo,bchi", BCS)
+def test_divu_mknewu_dot(bclo, bchi):
+    rng = np.random.default_rng(5)
+    ncell = (8, 12, 16)
+    sigma = rng.uniform(0.5, 2.0, ncell[::-1])
+    drv, orc = make(ncell, bclo, bchi, sigma, prob_hi=(0.8, 0.6, 3.2))
+    u = rng.standard_normal((3,) + ncell[::-1])
+    orc.set_vel(u)
+    assert relerr(drv.divu(u), orc.divu()) < 1e-13
+    phi = nodal(rng, orc.nshape(0), bclo, bchi)
+    u2, g2 = drv.mknewu(phi, u)
+    uo, go = orc.mknewu(phi, u)
+    assert relerr(u2, uo) < 1e-13 and relerr(g2, go) < 1e-13
+    y = nodal(rng, orc.nshape(0), bclo, bchi)
+    assert abs(drv.dot(0, phi, y) - orc.dot(0, phi, y)) < 1e-11 * np.abs(phi).sum()
+
+
+@pytest.mark.parametrize("bclo,bchi", BCS)
+def test_bottom_solver_and_vcycle(bclo, bchi):
+    rng = np.random.default_rng(3)
+    ncell = (16, 16, 32)
+    sigma = rng.uniform(0.5, 2.0, ncell[::-1])
+    drv, orc = make(ncell, bclo, bchi, sigma)
+    lb = orc.num_levels - 1
+    b = nodal(rng, orc.nshape(lb), bclo, bchi)
+    xg, itg = drv.bottom_solve(b)
+    xo, ito = orc.bottom_solve(b)
+    assert itg == ito
+    assert relerr(xg, xo) < 1e-9
+    r0 = nodal(rng, orc.nshape(0), bclo, bchi)
+    assert relerr(drv.vcycle(r0), orc.vcycle(r0)) < 1e-9

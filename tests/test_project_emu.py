@@ -1,0 +1,95 @@
+"""Whole projection (np_project through the C ABI) vs the oracle, on the CPU emulation build.
+
+Two comparisons per configuration (SURVEY.md 8c "parity definition"):
+  * oracle with the SAME smoother ordering (TILED)      -> same V-cycle count, iterates equal to round-off
+  * oracle with the reference's ordering (LEX, AMReX CPU) -> u, grad(phi), phi-mean within 1e-10 relative L2
+    at a tolerance both reach (1e-13), V-cycle counts within +-1.
+"""
+import numpy as np
+import pytest
+
+import nphelp
+from incflo_b200 import problems
+from oracle.oracle import Oracle, TILED, LEX
+
+BIG = 1 << 30
+
+
+def l2rel(a, b):
+    return np.linalg.norm(a - b) / np.linalg.norm(b)
+
+
+def run_oracle(ncell, prob, rtol, atol, **kw):
+    o = Oracle(ncell, prob["prob_lo"], prob["prob_hi"], prob["bclo"], prob["bchi"], **kw)
+    o.set_sigma(prob["sigma"])
+    o.set_vel(prob["vel"])
+    st = o.project(rtol, atol)
+    return st, o.get_vel(), o.get_phi(), o.get_gradphi()
+
+
+CASES = [("taylor_green", (32, 32, 32), {}), ("rayleigh_taylor", (16, 16, 32), {}),
+         ("double_shear", (32, 32, 16), dict(zwave=True, prob_hi=(1.0, 1.0, 0.5)))]
+
+
+@pytest.mark.parametrize("name,ncell,kw", CASES)
+def test_project_same_ordering(name, ncell, kw):
+    prob = problems.PROBLEMS[name](ncell, **kw)
+    drv = nphelp.Driver(ncell, prob["prob_lo"], prob["prob_hi"], prob["bclo"], prob["bchi"], lib=nphelp.emu_lib())
+    st, u, phi, gp = drv.project(prob["vel"], prob["sigma"], 1e-11, 1e-14)
+    so, uo, po, go = run_oracle(ncell, prob, 1e-11, 1e-14, smoother=TILED, tile=(31, 31, BIG), tile_z_target=64)
+    assert st.status == 0 and so.status == 0
+    assert st.n_vcycles == so.n_vcycles and st.n_levels == so.n_levels
+    assert st.bottom_iters_total == so.bottom_iters_total
+    for i in range(st.n_vcycles):
+        assert abs(st.res_history[i] - so.res_history[i]) <= 1e-6 * so.res_history[i] + 1e-14 * so.rhs_norm0
+    assert l2rel(u, uo) < 1e-12 and l2rel(gp, go) < 1e-10
+    assert l2rel(phi - phi.mean(), po - po.mean()) < 1e-10
+    assert st.sigma_is_const == (1 if name != "rayleigh_taylor" else 0)
+
+
+@pytest.mark.parametrize("name,ncell,kw", CASES[:2])
+def test_project_vs_reference_ordering(name, ncell, kw):
+    prob = problems.PROBLEMS[name](ncell, **kw)
+    drv = nphelp.Driver(ncell, prob["prob_lo"], prob["prob_hi"], prob["bclo"], prob["bchi"], lib=nphelp.emu_lib())
+    st, u, phi, gp = drv.project(prob["vel"], prob["sigma"], 1e-13, 0.0)
+    so, uo, po, go = run_oracle(ncell, prob, 1e-13, 0.0, smoother=LEX)
+    assert st.status == 0 and so.status == 0
+    assert abs(st.n_vcycles - so.n_vcycles) <= 1
+    assert l2rel(u, uo) < 1e-10 and l2rel(gp, go) < 1e-10
+    assert l2rel(phi - phi.mean(), po - po.mean()) < 1e-10
+
+
+def test_project_dirichlet_outflow_with_inflow_ghosts():
+    """x: mass inflow (Neumann, ghost cells carry u_in) / pressure outflow (Dirichlet); y walls; z periodic."""
+    rng = np.random.default_rng(2)
+    ncell = (32, 16, 8)
+    bclo, bchi = (2, 2, 0), (1, 2, 0)
+    sigma = rng.uniform(0.5, 2.0, ncell[::-1])
+    vel = 0.1 * rng.standard_normal((3,) + ncell[::-1])
+    vel[0] += 1.0
+    y = (np.arange(16) + 0.5) / 16
+    uin = 6 * y * (1 - y)                      # prob_set_inflow_velocity, probtype 31
+
+    def ghosts(fv):                            # Fab with 1 ghost: [comp, k, j, i]
+        fv.data[0, 1:-1, 1:-1, 0] = uin[None, :]
+
+    drv = nphelp.Driver(ncell, (0, 0, 0), (2.0, 1.0, 0.5), bclo, bchi, lib=nphelp.emu_lib())
+    st, u, phi, gp = drv.project(vel, sigma, 1e-11, 1e-14, ghost_setter=ghosts)
+    o = Oracle(ncell, (0, 0, 0), (2.0, 1.0, 0.5), bclo, bchi, smoother=TILED, tile=(31, 31, BIG), tile_z_target=64)
+    o.set_sigma(sigma)
+    o.set_vel(vel)
+    for k in range(8):
+        for j in range(16):
+            o.set_vel_ghost(-1, j, k, 0, uin[j])
+    so = o.project(1e-11, 1e-14)
+    assert st.status == 0 and st.n_vcycles == so.n_vcycles
+    assert l2rel(u, o.get_vel()) < 1e-11 and l2rel(gp, o.get_gradphi()) < 1e-10 and l2rel(phi, o.get_phi()) < 1e-10
+
+
+def test_not_converged_is_reported():
+    prob = problems.taylor_green((16, 16, 16))
+    drv = nphelp.Driver((16, 16, 16), lib=nphelp.emu_lib(), maxiter=1)
+    st, *_ = drv.project(prob["vel"], prob["sigma"], 1e-11, 1e-14, raise_on_fail=False)
+    assert st.status == 5 and st.n_vcycles == 1
+    with pytest.raises(Exception):
+        drv.project(prob["vel"], prob["sigma"], 1e-11, 1e-14)
