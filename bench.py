@@ -1,0 +1,342 @@
+#!/usr/bin/env python
+"""bench.py — nodal-projection throughput on B200 (BASELINE.json metric), one JSON line on rank 0.
+
+A "step" is one whole nodal projection (np_project through the C ABI: sigma hierarchy, divergence,
+MLMG solve to rtol 1e-11, velocity correction, grad(phi), phi) of one synthetic velocity field.
+
+Workload (config.workload): BASELINE.json configs[2] — 512^3 cells PER GPU, z-slab sharded, periodic,
+constant density, double-shear-layer field (+ z-wave so the slabs couple).  At N=1 this is the
+"512^3 single-level nodal projection on 1 B200" the north_star target is quoted on.  --ncell 256 gives
+configs[1].  Inputs (GBs) are far larger than the 126 MB L2, so no explicit L2 flush is needed.
+
+  value   DOF/s per V-cycle = (unique fine-level nodal unknowns, all ranks) / (timed region / V-cycles
+          run in it).  The timed region is K complete np_project calls with inputs resident in HBM
+          (plus the device-to-device restore of u*, which the in-place projection needs each step).
+  e2e     same metric through the same C-ABI call with HOST (pinned) fabs: u*, sigma host->device and
+          u, phi, grad(phi) device->host inside the timed region, every step.
+  roofline  the dominant kernel (level-0 smoother, 2 Gauss-Seidel sweeps per launch), timed live with
+          CUDA events around each of its launches inside the timed region (np_options.profile_kernels).
+  cpu_baseline  the oracle (CPU restatement of the reference algorithm, lexicographic GS, AMReX-default
+          32^3 boxes, all host cores) on a bounded sample; N=1 only.
+  --impl reference   times that CPU restatement alone (the reference's own build is unavailable: AMReX
+          is not in /root/reference and there is no MPI).
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "nodal_projection_dof_per_s_per_vcycle"
+UNIT = "DOF/s per V-cycle"
+RTOL, ATOL = 1e-11, 1e-14
+
+
+def read_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def read_traffic(const_sigma):
+    """ncu-measured DRAM bytes per launch of the dominant kernel, if a capture was summarised."""
+    p = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return d.get("k_smooth_const" if const_sigma else "k_smooth_var")
+    return None
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, smmax, pw, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); smmax.append(float(f[1])); pw.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(smmax), "power_w_max": max(pw),
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ---------------------------------------------------------------------------------------------------
+# CPU arm: the oracle (restatement of the reference's algorithm) on the host cores
+# ---------------------------------------------------------------------------------------------------
+def cpu_projection(n, reps, warmup):
+    """Project the double-shear(+z-wave) field at n^3 with the oracle.  Reference-faithful settings:
+    lexicographic GS box by box, AMReX's default max_grid_size 32, box-parallel over all host cores."""
+    from incflo_b200 import problems
+    from oracle.oracle import Oracle, LEX, chop_boxes
+    cores = os.cpu_count() or 1
+    ncell = (n, n, n)
+    prob = problems.double_shear(ncell, zwave=True)
+    times, vc = [], 0
+    for it in range(warmup + reps):
+        o = Oracle(ncell, prob["prob_lo"], prob["prob_hi"], prob["bclo"], prob["bchi"],
+                   boxes=chop_boxes(ncell, 32), smoother=LEX, nthreads=cores)
+        o.set_sigma(prob["sigma"])
+        o.set_vel(prob["vel"])
+        t0 = time.perf_counter()
+        st = o.project(RTOL, ATOL)
+        dt = time.perf_counter() - t0
+        o.close()
+        if st.status != 0:
+            raise RuntimeError("oracle did not converge")
+        if it >= warmup:
+            times.append(dt); vc += st.n_vcycles
+    total = sum(times)
+    return dict(value=(n ** 3) * vc / total, cores=cores, vcycles=vc // reps, seconds=total, ms_per_step=1e3 * total / reps,
+                sample=f"double_shear+zwave {n}^3 periodic, one level, 32^3 boxes (AMReX default max_grid_size), "
+                       f"lexicographic GS, rtol {RTOL:g}; {reps} projection(s), {total:.1f} s")
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    n = args.cpu_ncell
+    r = cpu_projection(n, args.steps, min(args.warmup, 1))
+    line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": r["ms_per_step"], "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(args, args.gpus, sample=r["sample"]),
+            "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"]},
+            "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0,
+            "note": "reference incflo+AMReX MPI build unavailable on this box (AMReX absent from /root/reference, no MPI); "
+                    "this is oracle/, the CPU restatement of the same algorithm"}
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, G, sample=None):
+    n = args.ncell
+    c = {"workload": f"BASELINE configs[2]: synthetic {n}^3 cells per GPU, {n}x{n}x{n * G} domain in {G} z-slab(s), "
+                     f"periodic, constant density (sigma=1), double_shear_layer + z-wave, rtol {RTOL:g} atol {ATOL:g}",
+         "ncell_per_gpu": [n, n, n], "boxes": f"one {n}^3 box per GPU", "vel_ngrow": args.vel_ngrow,
+         "l2": "inputs (>= 1 GB per array at 512^3) exceed the 126 MB L2; no explicit flush"}
+    if sample:
+        c["cpu_sample"] = sample
+    return c
+
+
+# ---------------------------------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------------------------------
+def run_gpu(args):
+    import ctypes as C
+    import torch
+    import torch.distributed as dist
+    from incflo_b200 import capi, problems
+    from incflo_b200.projector import Fab, Geometry, LPInfo, NodalProjector
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; incflo_b200 has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dev = f"cuda:{local}"
+    L = capi.load()
+    comm = None
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device(dev))
+        idbuf = torch.zeros(128, dtype=torch.uint8)
+        if rank == 0:
+            raw = (C.c_ubyte * 128)()
+            capi.check(L, L.np_nccl_unique_id(raw))
+            idbuf = torch.tensor(list(raw), dtype=torch.uint8)
+        idd = idbuf.to(dev)
+        dist.broadcast(idd, 0)
+        raw = (C.c_ubyte * 128)(*idd.cpu().tolist())
+        cptr = C.c_void_p()
+        capi.check(L, L.np_nccl_comm_create(C.byref(cptr), raw, rank, world))
+        comm = cptr.value
+
+    n, G, g = args.ncell, world, args.vel_ngrow
+    ncell = (n, n, n * G)
+    prob_hi = (1.0, 1.0, float(G))
+    koff = rank * n
+    vel0 = problems.double_shear_torch(ncell, prob_hi, koff, n, dev, ngrow=g)     # pristine u*
+    vel = Fab(vel0.clone(), g)
+    sig = Fab(torch.ones((1, n, n, n), dtype=torch.float64, device=dev), 0)
+    geom = Geometry(ncell, (0, 0, 0), prob_hi, (1, 1, 1))
+    boxes = [((0, 0, r * n), (n - 1, n - 1, (r + 1) * n - 1)) for r in range(G)]
+    P = NodalProjector(vel, sig, geom, LPInfo(), boxes=boxes, rank=rank, nranks=world, nccl_comm=comm, lib=L,
+                       profile_kernels=1)
+    P.setDomainBC((0, 0, 0), (0, 0, 0))
+    dof = n * n * n * G
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step():
+        vel.data.copy_(vel0)
+        return P.project(RTOL, ATOL, stream=stream)
+
+    for _ in range(args.warmup):
+        step()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    vcycles = launches = 0
+    ms_smooth = n_smooth = 0.0
+    ms_solve = 0.0
+    hist = None
+    for _ in range(args.steps):
+        st = step()
+        vcycles += st.n_vcycles; launches += st.kernel_launches
+        ms_smooth += st.ms_smooth0; n_smooth += st.n_smooth0; ms_solve += st.ms_solve
+        hist = [st.res_history[i] / max(st.rhs_norm0, 1e-300) for i in range(st.n_vcycles)]
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    clk = clocks.stop() if rank == 0 else None
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    const_sigma = bool(st.sigma_is_const)
+    levels = st.n_levels
+
+    # ---- e2e: host (pinned) fabs through the same C-ABI call; H2D + D2H inside the timed region ----
+    e2e = None
+    if not args.no_e2e:
+        hv0 = vel0.cpu()                                            # pristine host copy (pageable)
+        hv = Fab(torch.empty_like(hv0).pin_memory(), g)
+        hs = Fab(torch.ones((1, n, n, n), dtype=torch.float64).pin_memory(), 0)
+        hphi = Fab(torch.zeros((1, n + 1, n + 1, n + 1), dtype=torch.float64).pin_memory(), 0, nodal=True)
+        hgp = Fab(torch.zeros((3, n, n, n), dtype=torch.float64).pin_memory(), 0)
+        P.vel, P.sigma = hv, hs
+        h2d = hv.data.numel() * 8 + hs.data.numel() * 8
+        d2h = hv.data.numel() * 8 + hphi.data.numel() * 8 + hgp.data.numel() * 8
+        tot_ms, tot_vc = 0.0, 0
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        for it in range(1 + args.e2e_steps):
+            hv.data.copy_(hv0)                                      # untimed host-side reset of the in/out buffer
+            barrier()
+            a.record()
+            st2 = P.project(RTOL, ATOL, stream=stream)
+            capi.check(L, L.np_copy_phi(P.h, 0, C.byref(hphi.c())))
+            capi.check(L, L.np_copy_gradphi(P.h, 0, C.byref(hgp.c())))
+            b.record()
+            barrier()
+            if it >= 1:
+                tm = torch.tensor([a.elapsed_time(b)], dtype=torch.float64, device=dev)
+                if world > 1:
+                    dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+                tot_ms += float(tm.item()); tot_vc += st2.n_vcycles
+        e2e = {"value": dof * tot_vc / (tot_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+               "steps": args.e2e_steps, "ms_per_step": tot_ms / args.e2e_steps}
+
+    if rank == 0:
+        peak, peak_src = read_peaks()
+        nodes = (n + 1) ** 3
+        per_node = 2 * (24 if const_sigma else 32)                  # 2 GS sweeps x (read cor, rhs[, sigma]; write cor)
+        alg_bytes = per_node * nodes
+        avg_ms = ms_smooth / max(n_smooth, 1)
+        achieved = alg_bytes / (avg_ms * 1e-3) / 1e9 if avg_ms > 0 else 0.0
+        compulsory = (24 if const_sigma else 32) * nodes            # what the fused 2-sweep pass must move
+        roof = {"bound": "hbm", "kernel": f"k_smooth_tiled<{'const' if const_sigma else 'var'} sigma> level 0",
+                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": read_traffic(const_sigma),
+                "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes, "avg_launch_ms": avg_ms,
+                "launches_timed": int(n_smooth), "share_of_step": ms_smooth / ms,
+                "fused_pass_bytes_per_launch": compulsory,
+                "frac_fused_pass": compulsory / (avg_ms * 1e-3) / 1e9 / peak if avg_ms > 0 else 0.0,
+                "vcycle_algorithmic": {"bytes_per_dof": 342 if const_sigma else 432,
+                                       "achieved_gbs": (342 if const_sigma else 432) * dof / G * vcycles / (ms_solve * 1e-3) / 1e9,
+                                       "note": "SURVEY 8(d) accounting over the solve phase, per GPU"}}
+        roof["vcycle_algorithmic"]["frac"] = roof["vcycle_algorithmic"]["achieved_gbs"] / peak
+        line = {"metric": METRIC, "value": dof * vcycles / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_config(args, G),
+                "vcycles_per_step": vcycles / args.steps, "mg_levels": levels, "ms_per_vcycle": ms / vcycles,
+                "ms_solve_per_vcycle": ms_solve / vcycles, "rel_res_history": hist,
+                "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof}
+        if world == 1 and not args.no_cpu:
+            r = cpu_projection(args.cpu_ncell, 1, 0)
+            line["cpu_baseline"] = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port",
+                                    "sample": r["sample"], "vcycles": r["vcycles"]}
+        print(json.dumps(line), flush=True)
+    P.close()
+    if world > 1:
+        if comm:
+            L.np_nccl_comm_destroy(C.c_void_p(comm))
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--ncell", type=int, default=512, help="cells per side per GPU (512: configs[2]; 256: configs[1])")
+    ap.add_argument("--vel-ngrow", type=int, default=2, help="ghost layers of the velocity fab (incflo nghost_state: 2 MOL / 3 Godunov)")
+    ap.add_argument("--cpu-ncell", type=int, default=128, help="size of the bounded CPU sample")
+    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()

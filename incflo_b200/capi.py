@@ -34,7 +34,8 @@ class np_options(C.Structure):
                 ("bottom_solver", C.c_int), ("verbose", C.c_int), ("bottom_verbose", C.c_int),
                 ("bottom_rtol", C.c_double), ("bottom_atol", C.c_double),
                 ("smooth_zchunk", C.c_int), ("interp_sigma_weighted", C.c_int), ("bottom_normalize", C.c_int),
-                ("agg_min_local_nz", C.c_int), ("use_graph", C.c_int), ("const_sigma_fastpath", C.c_int)]
+                ("agg_min_local_nz", C.c_int), ("use_graph", C.c_int), ("const_sigma_fastpath", C.c_int),
+                ("profile_kernels", C.c_int)]
 
 
 class np_stats(C.Structure):
@@ -42,7 +43,8 @@ class np_stats(C.Structure):
                 ("rhs_norm0", C.c_double), ("res_norm0", C.c_double), ("res_norm_final", C.c_double),
                 ("res_history", C.c_double * 128),
                 ("ms_setup", C.c_double), ("ms_solve", C.c_double), ("ms_finish", C.c_double), ("ms_total", C.c_double),
-                ("kernel_launches", C.c_longlong), ("sigma_is_const", C.c_int)]
+                ("kernel_launches", C.c_longlong), ("sigma_is_const", C.c_int),
+                ("n_smooth0", C.c_int), ("ms_smooth0", C.c_double)]
 
 
 # every symbol include/nodalproj.h declares

@@ -120,6 +120,7 @@ int NpSolver::create(const np_geom* g, int nboxes, const np_box* boxes, const in
         zero(agg_send, m); zero(agg_recv, m * nranks);
     }
     for (int e = 0; e < 4; ++e) np_rt::event_create(&ev[e]);
+    if (opt.profile_kernels) { prof_ev.resize(2048); for (auto& e : prof_ev) np_rt::event_create(&e); }
     for (auto& L : lev) setup_level_bc(L);
 #ifndef NP_EMU
     cudaFuncSetAttribute(k_smooth_tiled<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -143,6 +144,8 @@ void NpSolver::destroy()
     if (bot_out) np_rt::dev_free(bot_out);
     if (h_bot_out) np_rt::host_free(h_bot_out);
     for (int e = 0; e < 4; ++e) if (ev[e]) np_rt::event_destroy(ev[e]);
+    for (auto& e : prof_ev) np_rt::event_destroy(e);
+    prof_ev.clear();
 }
 
 // Per-level face types and ghost maps from the domain BCs and this rank's position in the slab stack.
@@ -273,9 +276,12 @@ void NpSolver::smooth(int l, bool skip_fill)
     if (!skip_fill && !L.cor_ghost_clean) fill(l, L.cor);
     const dim3 grid((d.n[0] + 1 + NP_TW - 1) / NP_TW, (d.n[1] + 1 + NP_TW - 1) / NP_TW, (d.n[2] + 1 + L.zc - 1) / L.zc);
     const size_t smem = (NP_XRING * NP_XPLANE + NP_SRING * NP_SLAYER) * sizeof(double);
+    const bool prof = (l == 0 && opt.profile_kernels && prof_n + 2 <= (int)prof_ev.size());
+    if (prof) np_rt::event_record(prof_ev[prof_n], stream);
     if (d.const_sigma) NP_LAUNCH(true, (k_smooth_tiled<true>), grid, dim3(256), smem, stream, d, L.cor_alt, (const double*)L.cor, (const double*)L.res, (const double*)L.sigma, L.zc);
     else               NP_LAUNCH(true, (k_smooth_tiled<false>), grid, dim3(256), smem, stream, d, L.cor_alt, (const double*)L.cor, (const double*)L.res, (const double*)L.sigma, L.zc);
     ++launches;
+    if (prof) { np_rt::event_record(prof_ev[prof_n + 1], stream); prof_n += 2; }
     std::swap(L.cor, L.cor_alt);
     fill(l, L.cor);                 // nodalSync (+ the ghosts the next operation needs)
     L.cor_ghost_clean = true;
@@ -543,7 +549,7 @@ void np_fill_cell3(NpSolver& S, FabView u)
 int NpSolver::project(np_fab* vel, const np_fab* sigma, double rtol, double atol)
 {
     if (vel->ngrow < 1 || vel->ncomp < 3 || sigma->ncomp < 1) return NP_ERR_INVALID;
-    err = 0; launches = 0; have_result = false;
+    err = 0; launches = 0; have_result = false; prof_n = 0;
     const LevelDev& d0 = lev[0].d;
     np_rt::event_record(ev[0], stream);
     // ---- inputs ----
@@ -577,6 +583,8 @@ int NpSolver::project(np_fab* vel, const np_fab* sigma, double rtol, double atol
     stats.ms_finish = np_rt::event_ms(ev[2], ev[3]);
     stats.ms_total = np_rt::event_ms(ev[0], ev[3]);
     stats.kernel_launches = launches;
+    stats.n_smooth0 = prof_n / 2; stats.ms_smooth0 = 0.0;
+    for (int e = 0; e < prof_n; e += 2) stats.ms_smooth0 += np_rt::event_ms(prof_ev[e], prof_ev[e + 1]);
     if (np_rt::last_error()) { stats.status = NP_ERR_CUDA; return NP_ERR_CUDA; }
     if (err) { stats.status = err; return err; }
     have_result = true;

@@ -55,6 +55,8 @@ struct NpSolver {
     double *stage_vel = nullptr, *stage_sig = nullptr; long long stage_vel_n = 0, stage_sig_n = 0;
     np_stream_t stream = 0;
     np_event_t ev[4] = {0,0,0,0};
+    std::vector<np_event_t> prof_ev;   // profile_kernels: start/stop pairs around level-0 smoother launches
+    int prof_n = 0;
     np_stats stats{};
     bool have_sigma = false, have_result = false, singular = true;
     bool bicg_failed_switch = false;

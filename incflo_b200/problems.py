@@ -86,3 +86,23 @@ def random_fields(ncell, seed=0):
 
 
 PROBLEMS = {"taylor_green": taylor_green, "double_shear": double_shear, "rayleigh_taylor": rayleigh_taylor}
+
+
+def double_shear_torch(ncell, prob_hi, koff, nz_local, device, ngrow=1, zwave=True):
+    """Config 3 field (double_shear(zwave=True)) built directly on `device` for one z-slab, as the
+    [3, nz+2g, ny+2g, nx+2g] storage of a velocity fab with zero ghosts.  Same formulas as double_shear."""
+    import torch
+    nx, ny, nz = ncell
+    g = ngrow
+    dx = [prob_hi[d] / ncell[d] for d in range(3)]
+    f64 = dict(dtype=torch.float64, device=device)
+    x = ((torch.arange(nx, **f64) + 0.5) * dx[0])[None, None, :]
+    y = ((torch.arange(ny, **f64) + 0.5) * dx[1])[None, :, None]
+    z = ((torch.arange(koff, koff + nz_local, **f64) + 0.5) * dx[2])[:, None, None]
+    vel = torch.zeros((3, nz_local + 2 * g, ny + 2 * g, nx + 2 * g), **f64)
+    inner = (slice(g, g + nz_local), slice(g, g + ny), slice(g, g + nx))
+    vel[0][inner] = torch.tanh(30.0 * (0.25 - torch.abs(y - 0.5))).expand(nz_local, ny, nx)
+    vel[1][inner] = (0.05 * torch.sin(TWOPI * x)).expand(nz_local, ny, nx)
+    if zwave:
+        vel[2][inner] = 0.05 * torch.sin(TWOPI * x) * torch.sin(TWOPI * z / prob_hi[2])
+    return vel

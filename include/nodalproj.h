@@ -76,6 +76,7 @@ typedef struct {
     int agg_min_local_nz;       /* multi-GPU: replicate MG levels whose slab is thinner than this; default 16 */
     int use_graph;              /* capture the V-cycle in a CUDA graph; default 1 */
     int const_sigma_fastpath;   /* use the constant-coefficient kernels when sigma is uniform; default 1 */
+    int profile_kernels;        /* bracket every level-0 smoother launch with CUDA events (np_stats.ms_smooth0); default 0 */
 } np_options;
 
 typedef struct {
@@ -86,6 +87,9 @@ typedef struct {
     double ms_setup, ms_solve, ms_finish, ms_total;
     long long kernel_launches;   /* kernels of this library launched inside the last np_project */
     int sigma_is_const;
+    /* profile_kernels: summed device time and count of the level-0 smoother launches of the last np_project */
+    int n_smooth0;
+    double ms_smooth0;
 } np_stats;
 
 void np_default_options(np_options* o);

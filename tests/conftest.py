@@ -8,3 +8,23 @@ if ROOT not in sys.path:
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+
+
+import pytest  # noqa: E402
+
+
+@pytest.fixture(params=["emu", pytest.param("gpu", marks=pytest.mark.gpu)])
+def backend(request):
+    """Which build of the product sources a parity test drives through the C ABI.
+
+    emu: TEST-ONLY host emulation of the CUDA execution model (tests/emu) -> runs on CPU, checks logic.
+    gpu: the product, incflo_b200/libnodalproj.so, on cuda:0 with device-resident fabs (zero copy).
+    """
+    import nphelp
+    if request.param == "emu":
+        return dict(lib=nphelp.emu_lib(), like="numpy")
+    import torch
+    from incflo_b200 import capi
+    assert torch.cuda.is_available(), "gpu-marked test needs a CUDA device"
+    torch.cuda.set_device(0)
+    return dict(lib=capi.load(), like="cuda", device="cuda:0")

@@ -124,6 +124,15 @@ class Driver:
         return st, fv.numpy_valid(), phi, gp
 
 
+def assign(dst, arr):
+    """dst[...] = arr for a numpy view or a torch (CPU / CUDA) view."""
+    if hasattr(dst, "copy_"):
+        import torch
+        dst.copy_(torch.from_numpy(np.ascontiguousarray(arr, dtype=np.float64)))
+    else:
+        dst[...] = arr
+
+
 def periodic_consistent(x, bclo):
     """Make a full nodal array consistent on periodic images (high face = low face)."""
     x = np.array(x)

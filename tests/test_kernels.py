@@ -21,8 +21,8 @@ def relerr(a, b):
     return np.abs(a - b).max() / max(np.abs(b).max(), 1e-300)
 
 
-def make(ncell, bclo, bchi, sigma, prob_hi=(1.0, 1.0, 1.0), **opts):
-    drv = nphelp.Driver(ncell, (0, 0, 0), prob_hi, bclo, bchi, lib=nphelp.emu_lib(), **opts)
+def make(backend, ncell, bclo, bchi, sigma, prob_hi=(1.0, 1.0, 1.0), **opts):
+    drv = nphelp.Driver(ncell, (0, 0, 0), prob_hi, bclo, bchi, **backend, **opts)
     drv.set_sigma(sigma)
     orc = Oracle(ncell, (0, 0, 0), prob_hi, bclo, bchi, smoother=TILED, tile=(31, 31, BIG), tile_z_target=64)
     orc.set_sigma(sigma)
@@ -36,11 +36,11 @@ def nodal(rng, shape, bclo, bchi):
 
 @pytest.mark.parametrize("bclo,bchi", BCS)
 @pytest.mark.parametrize("const_sigma", [False, True])
-def test_apply_restrict_interp_sigma(bclo, bchi, const_sigma):
+def test_apply_restrict_interp_sigma(backend, bclo, bchi, const_sigma):
     rng = np.random.default_rng(7)
     ncell = (16, 8, 12)
     sigma = np.full((12, 8, 16), 0.7) if const_sigma else rng.uniform(0.5, 2.0, (12, 8, 16))
-    drv, orc = make(ncell, bclo, bchi, sigma, prob_hi=(1.6, 0.4, 2.4))
+    drv, orc = make(backend, ncell, bclo, bchi, sigma, prob_hi=(1.6, 0.4, 2.4))
     assert drv.P.num_levels == orc.num_levels
     for l in range(orc.num_levels):
         assert drv.P.level_ncell(l) == orc.level_ncell(l)
@@ -56,33 +56,33 @@ def test_apply_restrict_interp_sigma(bclo, bchi, const_sigma):
 
 @pytest.mark.parametrize("bclo,bchi", BCS)
 @pytest.mark.parametrize("ncell", [(16, 16, 16), (40, 36, 8)])
-def test_smoother_matches_oracle_tiled_order(bclo, bchi, ncell):
+def test_smoother_matches_oracle_tiled_order(backend, bclo, bchi, ncell):
     """Same ordering (overlapped 31x31 tiles, k-sequential, 4 colours, 2 sweeps) -> same iterates."""
     rng = np.random.default_rng(11)
     sigma = rng.uniform(0.5, 2.0, ncell[::-1])
-    drv, orc = make(ncell, bclo, bchi, sigma)
+    drv, orc = make(backend, ncell, bclo, bchi, sigma)
     x = nodal(rng, orc.nshape(0), bclo, bchi)
     r = nodal(rng, orc.nshape(0), bclo, bchi)
     assert relerr(drv.smooth(0, x, r, 2), orc.smooth(0, x, r, 2)) < 1e-13
 
 
-def test_smoother_z_chunks():
+def test_smoother_z_chunks(backend):
     rng = np.random.default_rng(12)
     ncell = (8, 8, 96)                      # 97 planes -> two z-chunks of 49
     bclo = bchi = (P, P, N)
     sigma = rng.uniform(0.5, 2.0, ncell[::-1])
-    drv, orc = make(ncell, bclo, bchi, sigma)
+    drv, orc = make(backend, ncell, bclo, bchi, sigma)
     x = nodal(rng, orc.nshape(0), bclo, bchi)
     r = nodal(rng, orc.nshape(0), bclo, bchi)
     assert relerr(drv.smooth(0, x, r, 1), orc.smooth(0, x, r, 1)) < 1e-13
 
 
 @pytest.mark.parametrize("bclo,bchi", BCS)
-def test_divu_mknewu_dot(bclo, bchi):
+def test_divu_mknewu_dot(backend, bclo, bchi):
     rng = np.random.default_rng(5)
     ncell = (8, 12, 16)
     sigma = rng.uniform(0.5, 2.0, ncell[::-1])
-    drv, orc = make(ncell, bclo, bchi, sigma, prob_hi=(0.8, 0.6, 3.2))
+    drv, orc = make(backend, ncell, bclo, bchi, sigma, prob_hi=(0.8, 0.6, 3.2))
     u = rng.standard_normal((3,) + ncell[::-1])
     orc.set_vel(u)
     assert relerr(drv.divu(u), orc.divu()) < 1e-13
@@ -95,11 +95,11 @@ def test_divu_mknewu_dot(bclo, bchi):
 
 
 @pytest.mark.parametrize("bclo,bchi", BCS)
-def test_bottom_solver_and_vcycle(bclo, bchi):
+def test_bottom_solver_and_vcycle(backend, bclo, bchi):
     rng = np.random.default_rng(3)
     ncell = (16, 16, 32)
     sigma = rng.uniform(0.5, 2.0, ncell[::-1])
-    drv, orc = make(ncell, bclo, bchi, sigma)
+    drv, orc = make(backend, ncell, bclo, bchi, sigma)
     lb = orc.num_levels - 1
     b = nodal(rng, orc.nshape(lb), bclo, bchi)
     xg, itg = drv.bottom_solve(b)
