@@ -243,117 +243,263 @@ __global__ void __launch_bounds__(256) k_add(LevelDev L, double* __restrict__ y,
 
 // ------------------------------------------------------------------------------------------------
 // K3: the smoother.  DESIGN.md "smoother semantics":
-//   * the valid nodes of the box are cut into tiles that WRITE (NP_TW x NP_TW x zc) nodes and RELAX one
-//     more node on each high side (shared with the next tile, which owns it) — the same one-node overlap
+//   * the valid nodes of the box are cut into tiles that WRITE (63 x 31 x zc) nodes and RELAX one more
+//     node on each high side (shared with the next tile, which owns it) — the same one-node overlap
 //     AMReX's boxes have — with everything outside the relaxed region frozen at its pre-smooth value;
 //   * inside a tile: sweep 1 then sweep 2 (the two sweeps of one Fsmooth), each visiting planes k
 //     ascending and, inside a plane, the four colours c = 2*(j&1)+(i&1) ascending (Gauss-Seidel).
-// One CTA owns one tile column chunk and streams it through shared memory once: sweep 2 runs two
-// planes behind sweep 1 (plane t-2 only needs sweep-1 values of planes <= t-1), so both sweeps cost one
-// pass over HBM.  Ring buffers: 5 nodal planes (34x34 incl. halo), 4 sigma layers (33x33).
+// One CTA owns one tile column chunk and streams it through shared memory ONCE: warps 0-3 run sweep 1
+// on plane t while warps 4-7 run sweep 2 on plane t-2 (which only needs sweep-1 values of planes
+// <= t-1), so both sweeps cost one pass over HBM.  A ring of six planes lives in shared memory, filled
+// by cp.async one plane ahead; every plane holds the frozen halo and the latest in-tile values.
+// Each thread owns a 2 x 8 (x,y) block of nodes in registers.  Planes are stored with even and odd
+// columns in separate arrays so that the own pair, the left and the right halo column are all
+// conflict-free 64-bit shared loads.
+// Constant sigma: x_new = B - (a_fx*(W+E) + a_fy*(S+N) + a_exy*(4 in-plane diagonals)), where
+// B = rhs/diag - (9-point stencil of x[k-1]+x[k+1]) is formed once per plane before the colour loop
+// and all weights are pre-divided by the diagonal on the host (no division in the kernel).
 // ------------------------------------------------------------------------------------------------
-#define NP_TW 31                 // written nodes per tile side
-#define NP_TR 32                 // relaxed nodes per tile side
-#define NP_TP 34                 // plane extent incl. halo
-#define NP_XP 35                 // smem pitch of a nodal plane row
-#define NP_SP 33                 // smem pitch of a sigma layer row (33 cells)
-#define NP_XPLANE (NP_TP * NP_XP)
-#define NP_SLAYER (NP_SP * NP_SP)
-#define NP_XRING 5
-#define NP_SRING 4
+#define GS_TX 64                 // relaxed nodes per tile in x
+#define GS_TY 32                 // relaxed nodes per tile in y
+#define GS_WX 63                 // written nodes per tile in x
+#define GS_WY 31
+#define GS_HP 34                 // pitch of a half-row (even or odd columns)
+#define GS_HALF (34 * 34 + 4)    // doubles per half-plane; +4 puts the odd array 16 banks away from the even one
+#define GS_PLANE (2 * GS_HALF)
+#define GS_RING 6
+#define GS_SMEM_BYTES (GS_RING * GS_PLANE * 8)
 
-struct SmemX {   // nodal ring in shared memory, pointer at the node in the centre plane
-    const double* m; const double* c; const double* p;
+struct GsCoef { double a_fx, a_fy, a_exy, a_fz, a_exz, a_eyz, a_c, dinv; };
+
+__device__ __forceinline__ void np_cp_async8(double* smem_dst, const double* gsrc, bool valid)
+{
+#ifdef NP_EMU
+    *smem_dst = valid ? *gsrc : 0.0;
+#else
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    const int sz = valid ? 8 : 0;
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;\n" :: "r"(d), "l"(gsrc), "r"(sz) : "memory");
+#endif
+}
+__device__ __forceinline__ void np_cp_async_commit()
+{
+#ifndef NP_EMU
+    asm volatile("cp.async.commit_group;\n" ::: "memory");
+#endif
+}
+__device__ __forceinline__ void np_cp_async_wait_all()
+{
+#ifndef NP_EMU
+    asm volatile("cp.async.wait_all;\n" ::: "memory");
+#endif
+}
+
+// nodal value at tile-local (li, lj) of a split-layout plane; li in [-1, 64], lj in [-1, 32]
+__device__ __forceinline__ int gs_idx(int li, int lj) { const int g = li + 2; return ((g & 1) ? GS_HALF : 0) + (lj + 1) * GS_HP + (g >> 1); }
+struct GsSmemX {   // 27-point accessor around tile-local node (li, lj) for the variable-sigma path
+    const double* m; const double* c; const double* p; int li, lj;
     __device__ __forceinline__ double operator()(int di, int dj, int dk) const {
         const double* q = dk < 0 ? m : (dk > 0 ? p : c);
-        return q[di + NP_XP * dj];
-    }
-};
-struct SmemS {   // sigma ring, pointers at local cell (li, lj) in the lower / upper layer
-    const double* lo; const double* hi;
-    __device__ __forceinline__ double operator()(int a, int b, int c) const {
-        const double* q = c < 0 ? lo : hi;
-        return q[a + NP_SP * b];
+        return q[gs_idx(li + di, lj + dj)];
     }
 };
 
 template <bool CS>
-__global__ void __launch_bounds__(256, 2) k_smooth_tiled(LevelDev L, double* __restrict__ xout, const double* __restrict__ xin,
+__global__ void __launch_bounds__(256, CS ? 2 : 1) k_gs2(LevelDev L, GsCoef C, double* __restrict__ xout, const double* __restrict__ xin,
                                                          const double* __restrict__ rhs, const double* __restrict__ sig, int zc)
 {
-    NP_DYN_SMEM(double, smem);
-    double* xr = smem;                                   // NP_XRING planes
-    double* sr = smem + NP_XRING * NP_XPLANE;            // NP_SRING layers
-    const int tid = threadIdx.x;
-    const int i0 = blockIdx.x * NP_TW, j0 = blockIdx.y * NP_TW, kb = blockIdx.z * zc;
+    NP_DYN_SMEM(double, ring);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int grp = warp >> 2;                           // 0: first sweep (plane t), 1: second sweep (plane t-2)
+    const int wy = warp & 3;                             // tile rows 8*wy .. 8*wy+7
+    const int i0 = blockIdx.x * GS_WX, j0 = blockIdx.y * GS_WY, kb = blockIdx.z * zc;
     const int nk  = min(kb + zc, L.n[2]) - kb + 1;       // relaxed planes p = 0..nk-1 (global k = kb+p)
     const int nkw = min(kb + zc - 1, L.n[2]) - kb + 1;   // written planes
-    const int wi = min(NP_TW, L.n[0] - i0 + 1), wj = min(NP_TW, L.n[1] - j0 + 1);   // written extents
-    const int a = tid & 15, bq = tid >> 4;               // this thread's 2x2 node block
+    const int gi = i0 + 2 * lane, gj = j0 + 8 * wy;      // first node of this thread's 2 x 8 block
+    const int row0 = 8 * wy + 1;                         // smem row of block row 0
 
-    auto load_plane = [&](int p) {       // p in [-1, nk]
-        double* dst = xr + ((p + 1) % NP_XRING) * NP_XPLANE;
-        const int k = kb + p;
-        for (int q = tid; q < NP_TP * NP_TP; q += 256) {
-            const int li = q % NP_TP, lj = q / NP_TP;
-            const int i = i0 - 1 + li, j = j0 - 1 + lj;
-            double v = 0.0;
-            if (i <= L.n[0] + 1 && j <= L.n[1] + 1 && k <= L.n[2] + 1) v = xin[np_noff(L, i, j, k)];
-            dst[li + NP_XP * lj] = v;
+    // per-thread node masks, bit a*8+r: relaxed (valid node), Dirichlet in x/y, written by this tile
+    unsigned act = 0, dir = 0, wrt = 0;
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+            const int i = gi + a, j = gj + r;
+            const bool v = (i <= L.n[0] && j <= L.n[1]);
+            const bool dd = v && ((L.face[0] == NP_FACE_DIRICHLET && i == 0) || (L.face[3] == NP_FACE_DIRICHLET && i == L.n[0])
+                               || (L.face[1] == NP_FACE_DIRICHLET && j == 0) || (L.face[4] == NP_FACE_DIRICHLET && j == L.n[1]));
+            const bool w = v && (2 * lane + a < GS_WX) && (8 * wy + r < GS_WY);
+            act |= (unsigned)v << (a * 8 + r); dir |= (unsigned)dd << (a * 8 + r); wrt |= (unsigned)w << (a * 8 + r);
         }
-    };
-    auto load_sigma = [&](int q) {       // layer q in [-1, nk-1]: cells between planes q and q+1
-        if (CS) return;
-        double* dst = sr + ((q + 1) % NP_SRING) * NP_SLAYER;
-        const int kc = kb + q;
-        for (int t = tid; t < NP_SP * NP_SP; t += 256) {
-            const int ci = t % NP_SP, cj = t / NP_SP;
-            const int i = i0 - 1 + ci, j = j0 - 1 + cj;
-            double v = 0.0;
-            if (i <= L.n[0] && j <= L.n[1] && kc <= L.n[2]) v = sig[np_coff(L, i, j, kc)];
-            dst[ci + NP_SP * cj] = v;
-        }
-    };
-    auto relax = [&](int p, int col) {   // one colour of plane p
-        const int li = 1 + 2 * a + (col & 1), lj = 1 + 2 * bq + (col >> 1);
-        const int i = i0 + li - 1, j = j0 + lj - 1, k = kb + p;
-        if (i > L.n[0] || j > L.n[1]) return;
-        double* xc = xr + ((p + 1) % NP_XRING) * NP_XPLANE + li + NP_XP * lj;
-        if (np_is_dirichlet(L, i, j, k)) { *xc = 0.0; return; }
-        const double* xm = xr + ((p + 0) % NP_XRING) * NP_XPLANE + li + NP_XP * lj;
-        const double* xp = xr + ((p + 2) % NP_XRING) * NP_XPLANE + li + NP_XP * lj;
-        SmemX xa{xm, xc, xp};
-        const double r = rhs[np_noff(L, i, j, k)];
-        if (CS) {
-            *xc = (r - np_offdiag_const(L.c, L.sigma0, xa)) / np_diag_const(L.c, L.sigma0);
-        } else {
-            // node li touches local cells li-1, li; SmemS is anchored at the HIGH cell (li, lj)
-            const double* slo = sr + ((p + 0) % NP_SRING) * NP_SLAYER + li + NP_SP * lj;   // layer p-1
-            const double* shi = sr + ((p + 1) % NP_SRING) * NP_SLAYER + li + NP_SP * lj;   // layer p
-            SmemS sa{slo, shi};
-            Sig8 g = np_load_sig(sa);
-            *xc = (r - np_offdiag(L.c, g, xa)) / np_diag(L.c, g);
+
+    auto slot = [&](int p) -> double* { return ring + ((p + 1) % GS_RING) * GS_PLANE; };     // p >= -1
+    auto load_plane = [&](int p) {                       // planes -1 .. nk (halo planes included)
+        double* dst = slot(p);
+        const long long kof = L.nsz * (long long)(kb + p + 1);
+        for (int e = tid; e < 34 * 66; e += 256) {
+            const int row = e / 66, g = e - row * 66 + 1;
+            const int i = i0 + g - 2, j = j0 + row - 1;
+            const bool valid = (i <= L.n[0] + 1 && j <= L.n[1] + 1);
+            const double* src = valid ? xin + (kof + L.nsy * (long long)(j + 1) + (i + 1)) : xin;
+            np_cp_async8(dst + ((g & 1) ? GS_HALF : 0) + row * GS_HP + (g >> 1), src, valid);
         }
     };
 
-    load_plane(-1); load_plane(0); load_sigma(-1);
+    load_plane(-1); load_plane(0); load_plane(1);
+    np_cp_async_commit(); np_cp_async_wait_all();
+    __syncthreads();
+
+    double x[2][8], B[2][8];
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+        for (int r = 0; r < 8; ++r) { x[a][r] = 0.0; B[a][r] = 0.0; }
+
     for (int t = 0; t <= nk + 1; ++t) {
-        if (t + 1 <= nk) load_plane(t + 1);
-        if (t <= nk - 1) load_sigma(t);
-        __syncthreads();
-        for (int col = 0; col < 4; ++col) {
-            if (t <= nk - 1) relax(t, col);                       // sweep 1 on plane t
-            if (t >= 2 && t - 2 <= nk - 1) relax(t - 2, col);     // sweep 2 on plane t-2
-            __syncthreads();
-        }
-        const int pw = t - 2;                                     // plane pw is final
-        if (pw >= 0 && pw < nkw) {
-            const double* src = xr + ((pw + 1) % NP_XRING) * NP_XPLANE;
-            const int k = kb + pw;
-            for (int q = tid; q < wi * wj; q += 256) {
-                const int li = q % wi, lj = q / wi;
-                xout[np_noff(L, i0 + li, j0 + lj, k)] = src[(li + 1) + NP_XP * (lj + 1)];
+        if (t + 2 <= nk) load_plane(t + 2);
+        np_cp_async_commit();
+        const int p = t - 2 * grp;
+        const bool on = (p >= 0 && p <= nk - 1);
+        const int k = kb + p;
+        double* Pc = on ? slot(p) : ring;
+        const bool zdir = on && ((L.face[2] == NP_FACE_DIRICHLET && k == 0) || (L.face[5] == NP_FACE_DIRICHLET && k == L.n[2]));
+        const unsigned dmask = zdir ? act : dir;
+        const long long gbase = on ? np_noff(L, gi, gj, k) : 0;
+
+        if (CS) {
+            if (on) {
+                // ---- B = rhs/diag - (out-of-plane part): 9-point stencil of S = x[k-1] + x[k+1] ----
+                double rv[2][8];
+#pragma unroll
+                for (int a = 0; a < 2; ++a)
+#pragma unroll
+                    for (int r = 0; r < 8; ++r)
+                        rv[a][r] = ((act >> (a * 8 + r)) & 1u) ? rhs[gbase + a + L.nsy * r] : 0.0;
+                const double* Pm = slot(p - 1); const double* Pp = slot(p + 1);
+#pragma unroll
+                for (int rr = -1; rr <= 8; ++rr) {
+                    const int ro = (row0 + rr) * GS_HP + lane;
+                    const double sL = Pm[GS_HALF + ro] + Pp[GS_HALF + ro];
+                    const double s0 = Pm[ro + 1] + Pp[ro + 1];
+                    const double s1 = Pm[GS_HALF + ro + 1] + Pp[GS_HALF + ro + 1];
+                    const double sR = Pm[ro + 2] + Pp[ro + 2];
+                    const double h0 = sL + s1, h1 = s0 + sR;
+                    const double q0 = C.a_eyz * s0 + C.a_c * h0, q1 = C.a_eyz * s1 + C.a_c * h1;
+                    if (rr >= 0 && rr <= 7) {
+                        // row rr's own contribution; B[.][rr] already holds q of row rr-1 (set below)
+                        B[0][rr] -= C.a_fz * s0 + C.a_exz * h0;
+                        B[1][rr] -= C.a_fz * s1 + C.a_exz * h1;
+                    }
+                    if (rr - 1 >= 0 && rr - 1 <= 7) { B[0][rr - 1] -= q0; B[1][rr - 1] -= q1; }
+                    if (rr + 1 >= 0 && rr + 1 <= 7) { B[0][rr + 1] = -q0; B[1][rr + 1] = -q1; }   // first touch of row rr+1
+                }
+#pragma unroll
+                for (int a = 0; a < 2; ++a)
+#pragma unroll
+                    for (int r = 0; r < 8; ++r) B[a][r] = rv[a][r] * C.dinv + B[a][r];
+                // ---- own values of plane p ----
+#pragma unroll
+                for (int r = 0; r < 8; ++r) {
+                    x[0][r] = Pc[(row0 + r) * GS_HP + lane + 1];
+                    x[1][r] = Pc[GS_HALF + (row0 + r) * GS_HP + lane + 1];
+                }
             }
+            double t0 = 0.0, t1 = 0.0, d0 = 0.0, d1 = 0.0;
+            // ---- colour 0: a = 0, r even ----
+            if (on) {
+                double xl[9];
+#pragma unroll
+                for (int q = 0; q < 9; ++q) xl[q] = Pc[GS_HALF + (row0 - 1 + q) * GS_HP + lane];      // rows -1..7
+                t0 = Pc[(row0 - 1) * GS_HP + lane + 1]; t1 = Pc[GS_HALF + (row0 - 1) * GS_HP + lane + 1];
+#pragma unroll
+                for (int r = 0; r < 8; r += 2) {
+                    const double up0 = r == 0 ? t0 : x[0][r - 1], up1 = r == 0 ? t1 : x[1][r - 1];
+                    const double v = B[0][r] - (C.a_fx * (xl[r + 1] + x[1][r]) + C.a_fy * (up0 + x[0][r + 1])
+                                              + C.a_exy * ((xl[r] + xl[r + 2]) + (up1 + x[1][r + 1])));
+                    if ((act >> r) & 1u) x[0][r] = ((dmask >> r) & 1u) ? 0.0 : v;
+                    Pc[(row0 + r) * GS_HP + lane + 1] = x[0][r];
+                }
+            }
+            __syncthreads();
+            // ---- colour 1: a = 1, r even ----
+            if (on) {
+                double xr[9];
+#pragma unroll
+                for (int q = 0; q < 9; ++q) xr[q] = Pc[(row0 - 1 + q) * GS_HP + lane + 2];            // rows -1..7
+#pragma unroll
+                for (int r = 0; r < 8; r += 2) {
+                    const double up0 = r == 0 ? t0 : x[0][r - 1], up1 = r == 0 ? t1 : x[1][r - 1];
+                    const double v = B[1][r] - (C.a_fx * (x[0][r] + xr[r + 1]) + C.a_fy * (up1 + x[1][r + 1])
+                                              + C.a_exy * ((up0 + x[0][r + 1]) + (xr[r] + xr[r + 2])));
+                    if ((act >> (8 + r)) & 1u) x[1][r] = ((dmask >> (8 + r)) & 1u) ? 0.0 : v;
+                    Pc[GS_HALF + (row0 + r) * GS_HP + lane + 1] = x[1][r];
+                }
+            }
+            __syncthreads();
+            // ---- colour 2: a = 0, r odd ----
+            if (on) {
+                double xl[9];
+#pragma unroll
+                for (int q = 0; q < 9; ++q) xl[q] = Pc[GS_HALF + (row0 + q) * GS_HP + lane];          // rows 0..8
+                d0 = Pc[(row0 + 8) * GS_HP + lane + 1]; d1 = Pc[GS_HALF + (row0 + 8) * GS_HP + lane + 1];
+#pragma unroll
+                for (int r = 1; r < 8; r += 2) {
+                    const double dn0 = r == 7 ? d0 : x[0][r + 1], dn1 = r == 7 ? d1 : x[1][r + 1];
+                    const double v = B[0][r] - (C.a_fx * (xl[r] + x[1][r]) + C.a_fy * (x[0][r - 1] + dn0)
+                                              + C.a_exy * ((xl[r - 1] + xl[r + 1]) + (x[1][r - 1] + dn1)));
+                    if ((act >> r) & 1u) x[0][r] = ((dmask >> r) & 1u) ? 0.0 : v;
+                    Pc[(row0 + r) * GS_HP + lane + 1] = x[0][r];
+                }
+            }
+            __syncthreads();
+            // ---- colour 3: a = 1, r odd ----
+            if (on) {
+                double xr[9];
+#pragma unroll
+                for (int q = 0; q < 9; ++q) xr[q] = Pc[(row0 + q) * GS_HP + lane + 2];                // rows 0..8
+#pragma unroll
+                for (int r = 1; r < 8; r += 2) {
+                    const double dn0 = r == 7 ? d0 : x[0][r + 1], dn1 = r == 7 ? d1 : x[1][r + 1];
+                    const double v = B[1][r] - (C.a_fx * (x[0][r] + xr[r]) + C.a_fy * (x[1][r - 1] + dn1)
+                                              + C.a_exy * ((x[0][r - 1] + dn0) + (xr[r - 1] + xr[r + 1])));
+                    if ((act >> (8 + r)) & 1u) x[1][r] = ((dmask >> (8 + r)) & 1u) ? 0.0 : v;
+                    Pc[GS_HALF + (row0 + r) * GS_HP + lane + 1] = x[1][r];
+                }
+            }
+        } else {
+            // ---- variable sigma: every update gathers its 26 neighbours from the ring and its 8 cells from L1/L2 ----
+            const double* Pm = on ? slot(p - 1) : ring; const double* Pp = on ? slot(p + 1) : ring;
+#pragma unroll
+            for (int col = 0; col < 4; ++col) {
+                if (on) {
+                    const int a = col & 1;
+#pragma unroll
+                    for (int r = (col >> 1); r < 8; r += 2) {
+                        const int bit = a * 8 + r;
+                        if ((act >> bit) & 1u) {
+                            double v = 0.0;
+                            if (!((dmask >> bit) & 1u)) {
+                                GsSmemX xa{Pm, Pc, Pp, 2 * lane + a, 8 * wy + r};
+                                GlobS sa{sig + np_coff(L, gi + a, gj + r, k), L.csy, L.csz};
+                                const Sig8 g = np_load_sig(sa);
+                                v = (rhs[gbase + a + L.nsy * r] - np_offdiag(L.c, g, xa)) / np_diag(L.c, g);
+                            }
+                            x[a][r] = v;
+                            Pc[gs_idx(2 * lane + a, 8 * wy + r)] = v;
+                        } else x[a][r] = Pc[gs_idx(2 * lane + a, 8 * wy + r)];
+                    }
+                }
+                if (col < 3) __syncthreads();
+            }
+        }
+        np_cp_async_wait_all();
+        __syncthreads();
+        if (on && grp == 1 && p < nkw) {
+#pragma unroll
+            for (int a = 0; a < 2; ++a)
+#pragma unroll
+                for (int r = 0; r < 8; ++r)
+                    if ((wrt >> (a * 8 + r)) & 1u) xout[gbase + a + L.nsy * r] = x[a][r];
         }
     }
 }

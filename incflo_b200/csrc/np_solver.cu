@@ -21,6 +21,14 @@ static int pick_zchunk(int nnodes_z, int target) {
     int nch = std::max(1, (nnodes_z + target / 2) / target);
     return (nnodes_z + nch - 1) / nch;
 }
+// Smoother z-chunk of a level: enough chunks to give the 148 SMs about four CTAs each, 8..32 planes per
+// chunk.  Part of the smoother's definition (DESIGN.md "smoother semantics"); the oracle restates it.
+static int gs_zchunk(int nx_nodes, int ny_nodes, int nz_nodes) {
+    const int ncols = ((nx_nodes + GS_WX - 1) / GS_WX) * ((ny_nodes + GS_WY - 1) / GS_WY);
+    const int nch_want = (592 + ncols - 1) / ncols;
+    const int target = std::min(32, std::max(8, nz_nodes / nch_want));
+    return pick_zchunk(nz_nodes, target);
+}
 
 static void fill_coef(LevelDev& d) {
     const double fx = d.dxinv[0]*d.dxinv[0]/36.0, fy = d.dxinv[1]*d.dxinv[1]/36.0, fz = d.dxinv[2]*d.dxinv[2]/36.0;
@@ -70,7 +78,7 @@ int NpSolver::create(const np_geom* g, int nboxes, const np_box* boxes, const in
         fill_coef(L.d);
         L.d.const_sigma = 0; L.d.sigma0 = 1.0;
         L.koff = ko; L.nglob2 = nglob2; L.replicated = replicated;
-        L.zc = opt.smooth_zchunk > 0 ? opt.smooth_zchunk : pick_zchunk(n[2] + 1, 64);
+        L.zc = opt.smooth_zchunk > 0 ? opt.smooth_zchunk : gs_zchunk(n[0] + 1, n[1] + 1, n[2] + 1);
         lev.push_back(L);
         if ((int)lev.size() > opt.max_coarsening_level) break;
         // multi-GPU: below agg_min_local_nz the next level is replicated on every rank (whole domain)
@@ -123,10 +131,8 @@ int NpSolver::create(const np_geom* g, int nboxes, const np_box* boxes, const in
     if (opt.profile_kernels) { prof_ev.resize(2048); for (auto& e : prof_ev) np_rt::event_create(&e); }
     for (auto& L : lev) setup_level_bc(L);
 #ifndef NP_EMU
-    cudaFuncSetAttribute(k_smooth_tiled<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                         (int)((NP_XRING * NP_XPLANE + NP_SRING * NP_SLAYER) * sizeof(double)));
-    cudaFuncSetAttribute(k_smooth_tiled<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                         (int)((NP_XRING * NP_XPLANE + NP_SRING * NP_SLAYER) * sizeof(double)));
+    cudaFuncSetAttribute(k_gs2<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GS_SMEM_BYTES);
+    cudaFuncSetAttribute(k_gs2<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GS_SMEM_BYTES);
 #endif
     np_rt::stream_sync(stream);
     return np_rt::last_error() ? NP_ERR_CUDA : NP_OK;
@@ -274,12 +280,22 @@ void NpSolver::smooth(int l, bool skip_fill)
     NpLevel& L = lev[l];
     const LevelDev& d = L.d;
     if (!skip_fill && !L.cor_ghost_clean) fill(l, L.cor);
-    const dim3 grid((d.n[0] + 1 + NP_TW - 1) / NP_TW, (d.n[1] + 1 + NP_TW - 1) / NP_TW, (d.n[2] + 1 + L.zc - 1) / L.zc);
-    const size_t smem = (NP_XRING * NP_XPLANE + NP_SRING * NP_SLAYER) * sizeof(double);
+    const dim3 grid((d.n[0] + 1 + GS_WX - 1) / GS_WX, (d.n[1] + 1 + GS_WY - 1) / GS_WY, (d.n[2] + 1 + L.zc - 1) / L.zc);
+    const size_t smem = GS_SMEM_BYTES;
     const bool prof = (l == 0 && opt.profile_kernels && prof_n + 2 <= (int)prof_ev.size());
     if (prof) np_rt::event_record(prof_ev[prof_n], stream);
-    if (d.const_sigma) NP_LAUNCH(true, (k_smooth_tiled<true>), grid, dim3(256), smem, stream, d, L.cor_alt, (const double*)L.cor, (const double*)L.res, (const double*)L.sigma, L.zc);
-    else               NP_LAUNCH(true, (k_smooth_tiled<false>), grid, dim3(256), smem, stream, d, L.cor_alt, (const double*)L.cor, (const double*)L.res, (const double*)L.sigma, L.zc);
+    GsCoef gc{};
+    if (d.const_sigma) {
+        // constant sigma: the 26 neighbours fall into 7 weight classes; everything is pre-divided by the diagonal
+        const double sg = d.sigma0, dinv = 1.0 / (-32.0 * d.c.fxyz * sg);
+        gc.dinv = dinv;
+        gc.a_fx = 4.0 * d.c.f4xm2ym2z * sg * dinv; gc.a_fy = 4.0 * d.c.fm2x4ym2z * sg * dinv; gc.a_fz = 4.0 * d.c.fm2xm2y4z * sg * dinv;
+        gc.a_exy = 2.0 * d.c.f2x2ymz * sg * dinv; gc.a_exz = 2.0 * d.c.f2xmy2z * sg * dinv; gc.a_eyz = 2.0 * d.c.fmx2y2z * sg * dinv;
+        gc.a_c = d.c.fxyz * sg * dinv;
+        NP_LAUNCH(true, (k_gs2<true>), grid, dim3(256), smem, stream, d, gc, L.cor_alt, (const double*)L.cor, (const double*)L.res, (const double*)L.sigma, L.zc);
+    } else {
+        NP_LAUNCH(true, (k_gs2<false>), grid, dim3(256), smem, stream, d, gc, L.cor_alt, (const double*)L.cor, (const double*)L.res, (const double*)L.sigma, L.zc);
+    }
     ++launches;
     if (prof) { np_rt::event_record(prof_ev[prof_n + 1], stream); prof_n += 2; }
     std::swap(L.cor, L.cor_alt);

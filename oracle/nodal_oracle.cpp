@@ -322,7 +322,7 @@ static void fsmooth_lex(const Level& L, MF& x, const MF& rhs, int nsweeps)
 // each plane k ascending, for colour c = 2*(j&1)+(i&1) (tile-local indices) ascending, update all
 // nodes of that colour.  A node is owned by a box unless it lies on the box's high face and that
 // face is not a non-periodic domain boundary.
-struct TileSpec { int t[3]; int variant = 0; int overlap = 1; int z_target = 0; };
+struct TileSpec { int t[3]; int variant = 0; int overlap = 1; int z_target = 0; int owned_only = 0; };
 // Experimental orderings (variant > 0) used only to study smoothing rates: nodes are
 // visited in ascending key order, nodes with equal keys are updated simultaneously (Jacobi).
 static long order_key(int variant, int ns, int i, int j, int k, int ni, int nj, int nk)
@@ -356,10 +356,17 @@ static void fsmooth_tiled(const Level& L, MF& x, const MF& rhs, int nsweeps, con
         // nodal_sync afterwards) — the same one-node overlap between neighbouring boxes / periodic
         // images that AMReX's box-by-box Gauss-Seidel has.
         IBox o = valid_of(L.boxes[b], true);
+        if (ts_in.owned_only) owned_range(L, L.boxes[b], o);   // duplicates stay frozen; nodal_sync refreshes them
         TileSpec ts = ts_in;
-        if (ts.z_target > 0) {       // incflo_b200/csrc/np_solver.cu pick_zchunk
+        if (ts.z_target != 0) {      // the GPU driver's rule (incflo_b200/csrc/np_solver.cu gs_zchunk / pick_zchunk)
             const int nn = o.hi[2]-o.lo[2]+1;
-            const int nch = std::max(1, (nn + ts.z_target/2) / ts.z_target);
+            int target = ts.z_target;
+            if (target < 0) {        // enough z-chunks to fill the GPU, between 8 and 32 planes each
+                const int ncols = ((o.hi[0]-o.lo[0]+1 + ts.t[0]-1)/ts.t[0]) * ((o.hi[1]-o.lo[1]+1 + ts.t[1]-1)/ts.t[1]);
+                const int nch_want = (592 + ncols - 1) / ncols;
+                target = std::min(32, std::max(8, nn / nch_want));
+            }
+            const int nch = std::max(1, (nn + target/2) / target);
             ts.t[2] = (nn + nch - 1) / nch;
         }
         int nt[3]; for (int d=0; d<3; ++d) nt[d] = (o.hi[d]-o.lo[d]+1 + ts.t[d]-1)/ts.t[d];
@@ -640,6 +647,7 @@ struct Options {
     int tile_variant = 0;             // experimental orderings, see order_key()
     int tile_z_target = 0;            // >0: z tile = pick_zchunk(nodes_z, target), the GPU driver's rule
     int tile_overlap = 1;             // tiles share their high-face nodes with the next tile (like boxes do)
+    int tile_owned_only = 0;          // 1: only owned nodes are relaxed (periodic / shared high-face duplicates stay frozen)
 };
 
 struct Stats {
@@ -707,7 +715,7 @@ struct Solver {
         const Level& L = lev[l];
         apply_bc(L, x, skip_fillboundary);
         if (opt.smoother == LEX) fsmooth_lex(L, x, b, opt.smooth_sweeps);
-        else { TileSpec ts{{opt.tile[0],opt.tile[1],opt.tile[2]}, opt.tile_variant, opt.tile_overlap, opt.tile_z_target}; fsmooth_tiled(L, x, b, opt.smooth_sweeps, ts); }
+        else { TileSpec ts{{opt.tile[0],opt.tile[1],opt.tile[2]}, opt.tile_variant, opt.tile_overlap, opt.tile_z_target, opt.tile_owned_only}; fsmooth_tiled(L, x, b, opt.smooth_sweeps, ts); }
         nodal_sync(L, x);
     }
     // MLNodeLinOp::apply = applyBC + Fapply
@@ -994,7 +1002,7 @@ extern "C" {
 struct orc_options {
     int max_coarsening_level, maxiter, bottom_maxiter, nu1, nu2, nuf, nub, smooth_sweeps, bottom_solver;
     double bottom_rtol, bottom_atol;
-    int verbose, smoother, tile[3], interp_sigma_weighted, bottom_normalize, agg_level, nthreads, tile_variant, tile_overlap, tile_z_target;
+    int verbose, smoother, tile[3], interp_sigma_weighted, bottom_normalize, agg_level, nthreads, tile_variant, tile_overlap, tile_z_target, tile_owned_only;
 };
 struct orc_stats {
     int n_vcycles, bottom_iters_total, status, n_levels;
@@ -1009,7 +1017,7 @@ void orc_default_options(orc_options* o) {
     o->nu1=d.nu1; o->nu2=d.nu2; o->nuf=d.nuf; o->nub=d.nub; o->smooth_sweeps=d.smooth_sweeps; o->bottom_solver=d.bottom_solver;
     o->bottom_rtol=d.bottom_rtol; o->bottom_atol=d.bottom_atol; o->verbose=0; o->smoother=LEX;
     o->tile[0]=d.tile[0]; o->tile[1]=d.tile[1]; o->tile[2]=d.tile[2];
-    o->interp_sigma_weighted=1; o->bottom_normalize=1; o->agg_level=-1; o->nthreads=1; o->tile_variant=0; o->tile_overlap=1; o->tile_z_target=0;
+    o->interp_sigma_weighted=1; o->bottom_normalize=1; o->agg_level=-1; o->nthreads=1; o->tile_variant=0; o->tile_overlap=1; o->tile_z_target=0; o->tile_owned_only=0;
 }
 
 void* orc_create(const int* ncell, const double* plo, const double* phi, const int* bclo, const int* bchi,
@@ -1020,7 +1028,7 @@ void* orc_create(const int* ncell, const double* plo, const double* phi, const i
     op.nu1=o->nu1; op.nu2=o->nu2; op.nuf=o->nuf; op.nub=o->nub; op.smooth_sweeps=o->smooth_sweeps; op.bottom_solver=o->bottom_solver;
     op.bottom_rtol=o->bottom_rtol; op.bottom_atol=o->bottom_atol; op.verbose=o->verbose; op.smoother=o->smoother;
     op.tile[0]=o->tile[0]; op.tile[1]=o->tile[1]; op.tile[2]=o->tile[2];
-    op.interp_sigma_weighted=o->interp_sigma_weighted; op.bottom_normalize=o->bottom_normalize; op.agg_level=o->agg_level; op.tile_variant=o->tile_variant; op.tile_overlap=o->tile_overlap; op.tile_z_target=o->tile_z_target;
+    op.interp_sigma_weighted=o->interp_sigma_weighted; op.bottom_normalize=o->bottom_normalize; op.agg_level=o->agg_level; op.tile_variant=o->tile_variant; op.tile_overlap=o->tile_overlap; op.tile_z_target=o->tile_z_target; op.tile_owned_only=o->tile_owned_only;
     g_nthreads = std::max(1, o->nthreads);
     auto* s = new Solver();
     s->define(ncell, plo, phi, bclo, bchi, nboxes, boxes, op);

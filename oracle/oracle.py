@@ -27,7 +27,8 @@ class Options(C.Structure):
                 ("bottom_rtol", C.c_double), ("bottom_atol", C.c_double),
                 ("verbose", C.c_int), ("smoother", C.c_int), ("tile", C.c_int * 3),
                 ("interp_sigma_weighted", C.c_int), ("bottom_normalize", C.c_int),
-                ("agg_level", C.c_int), ("nthreads", C.c_int), ("tile_variant", C.c_int), ("tile_overlap", C.c_int), ("tile_z_target", C.c_int)]
+                ("agg_level", C.c_int), ("nthreads", C.c_int), ("tile_variant", C.c_int), ("tile_overlap", C.c_int), ("tile_z_target", C.c_int),
+                ("tile_owned_only", C.c_int)]
 
 
 class Stats(C.Structure):

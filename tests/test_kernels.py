@@ -24,7 +24,7 @@ def relerr(a, b):
 def make(backend, ncell, bclo, bchi, sigma, prob_hi=(1.0, 1.0, 1.0), **opts):
     drv = nphelp.Driver(ncell, (0, 0, 0), prob_hi, bclo, bchi, **backend, **opts)
     drv.set_sigma(sigma)
-    orc = Oracle(ncell, (0, 0, 0), prob_hi, bclo, bchi, smoother=TILED, tile=(31, 31, BIG), tile_z_target=64)
+    orc = Oracle(ncell, (0, 0, 0), prob_hi, bclo, bchi, smoother=TILED, tile=(63, 31, BIG), tile_z_target=-1)
     orc.set_sigma(sigma)
     orc.prepare_sigma()
     return drv, orc
@@ -55,22 +55,24 @@ def test_apply_restrict_interp_sigma(backend, bclo, bchi, const_sigma):
 
 
 @pytest.mark.parametrize("bclo,bchi", BCS)
-@pytest.mark.parametrize("ncell", [(16, 16, 16), (40, 36, 8)])
-def test_smoother_matches_oracle_tiled_order(backend, bclo, bchi, ncell):
-    """Same ordering (overlapped 31x31 tiles, k-sequential, 4 colours, 2 sweeps) -> same iterates."""
+@pytest.mark.parametrize("ncell", [(16, 16, 16), (70, 36, 8)])
+@pytest.mark.parametrize("const_sigma", [False, True])
+def test_smoother_matches_oracle_tiled_order(backend, bclo, bchi, ncell, const_sigma):
+    """Same ordering (overlapped 63x31 tiles, k-sequential, 4 colours, 2 sweeps) -> same iterates."""
     rng = np.random.default_rng(11)
-    sigma = rng.uniform(0.5, 2.0, ncell[::-1])
-    drv, orc = make(backend, ncell, bclo, bchi, sigma)
+    sigma = np.full(ncell[::-1], 1.3) if const_sigma else rng.uniform(0.5, 2.0, ncell[::-1])
+    drv, orc = make(backend, ncell, bclo, bchi, sigma, prob_hi=(1.0, 0.7, 0.4))
     x = nodal(rng, orc.nshape(0), bclo, bchi)
     r = nodal(rng, orc.nshape(0), bclo, bchi)
     assert relerr(drv.smooth(0, x, r, 2), orc.smooth(0, x, r, 2)) < 1e-13
 
 
-def test_smoother_z_chunks(backend):
+@pytest.mark.parametrize("const_sigma", [False, True])
+def test_smoother_z_chunks(backend, const_sigma):
     rng = np.random.default_rng(12)
-    ncell = (8, 8, 96)                      # 97 planes -> two z-chunks of 49
+    ncell = (8, 8, 96)                      # 97 planes -> several z-chunks
     bclo = bchi = (P, P, N)
-    sigma = rng.uniform(0.5, 2.0, ncell[::-1])
+    sigma = np.full(ncell[::-1], 0.8) if const_sigma else rng.uniform(0.5, 2.0, ncell[::-1])
     drv, orc = make(backend, ncell, bclo, bchi, sigma)
     x = nodal(rng, orc.nshape(0), bclo, bchi)
     r = nodal(rng, orc.nshape(0), bclo, bchi)

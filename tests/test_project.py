@@ -36,7 +36,7 @@ def test_project_same_ordering(backend, name, ncell, kw):
     prob = problems.PROBLEMS[name](ncell, **kw)
     drv = nphelp.Driver(ncell, prob["prob_lo"], prob["prob_hi"], prob["bclo"], prob["bchi"], **backend)
     st, u, phi, gp = drv.project(prob["vel"], prob["sigma"], 1e-11, 1e-14)
-    so, uo, po, go = run_oracle(ncell, prob, 1e-11, 1e-14, smoother=TILED, tile=(31, 31, BIG), tile_z_target=64)
+    so, uo, po, go = run_oracle(ncell, prob, 1e-11, 1e-14, smoother=TILED, tile=(63, 31, BIG), tile_z_target=-1)
     assert st.status == 0 and so.status == 0
     assert st.n_vcycles == so.n_vcycles and st.n_levels == so.n_levels
     assert st.bottom_iters_total == so.bottom_iters_total
@@ -75,7 +75,7 @@ def test_project_dirichlet_outflow_with_inflow_ghosts(backend):
 
     drv = nphelp.Driver(ncell, (0, 0, 0), (2.0, 1.0, 0.5), bclo, bchi, **backend)
     st, u, phi, gp = drv.project(vel, sigma, 1e-11, 1e-14, ghost_setter=ghosts)
-    o = Oracle(ncell, (0, 0, 0), (2.0, 1.0, 0.5), bclo, bchi, smoother=TILED, tile=(31, 31, BIG), tile_z_target=64)
+    o = Oracle(ncell, (0, 0, 0), (2.0, 1.0, 0.5), bclo, bchi, smoother=TILED, tile=(63, 31, BIG), tile_z_target=-1)
     o.set_sigma(sigma)
     o.set_vel(vel)
     for k in range(8):
