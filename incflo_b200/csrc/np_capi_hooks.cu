@@ -94,7 +94,8 @@ int np_smooth(np_handle* h, int l, np_fab* x, const np_fab* rhs, int ncalls)
     int rc = fab_in(S, l, x, L.cor); if (rc) return rc;
     rc = fab_in(S, l, rhs, L.res); if (rc) return rc;
     L.cor_ghost_clean = false;
-    for (int i = 0; i < ncalls; ++i) S.smooth(l, false);
+    S.lvl0_off = nullptr;
+    for (int i = 0; i < ncalls; ++i) S.smooth(l, false, nullptr);
     return fab_out(S, l, L.cor, x);
 }
 
@@ -170,8 +171,9 @@ int np_vcycle(np_handle* h, const np_fab* res0, np_fab* cor0)
     NpSolver& S = h->S; if (!S.have_sigma) return NP_ERR_STATE;
     int rc = fab_in(S, 0, res0, S.lev[0].res); if (rc) return rc;
     S.bicg_failed_switch = false;
+    S.lvl0_off = nullptr;
     if (S.singular) S.make_solvable(0, S.lev[0].res);
-    S.vcycle();
+    S.vcycle(false);
     return fab_out(S, 0, S.lev[0].cor, cor0);
 }
 

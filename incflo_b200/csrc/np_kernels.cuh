@@ -149,8 +149,8 @@ __global__ void __launch_bounds__(256) k_fill_sigma(LevelDev L, double* s, int p
 // ------------------------------------------------------------------------------------------------
 template <int MODE, bool CS, bool NORM>
 __global__ void __launch_bounds__(256) k_adotx(LevelDev L, double* __restrict__ y, const double* __restrict__ x,
-                                               const double* __restrict__ b, const double* __restrict__ sig,
-                                               double* __restrict__ block_max)
+                                               const double* __restrict__ b, const double* __restrict__ boff, const double* __restrict__ sig,
+                                               double* __restrict__ block_max, double* __restrict__ block_sum)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int j = blockIdx.y * blockDim.y + threadIdx.y;
@@ -169,16 +169,33 @@ __global__ void __launch_bounds__(256) k_adotx(LevelDev L, double* __restrict__ 
                 Sig8 g = np_load_sig(sa);
                 ax = xa(0,0,0) * np_diag(L.c, g) + np_offdiag(L.c, g, xa);
             }
-            v = (MODE == 1) ? b[o] - ax : ax;
+            v = (MODE == 1) ? (b[o] - (boff ? boff[0] : 0.0)) - ax : ax;
         }
         y[o] = v;
     }
     if (NORM) {
-        double m = np_block_reduce<true>(fabs(v));
-        if (threadIdx.x == 0 && threadIdx.y == 0)
-            block_max[blockIdx.x + gridDim.x * (blockIdx.y + (long long)gridDim.y * blockIdx.z)] = m;
+        const bool owned = active && i <= L.owned_hi[0] && j <= L.owned_hi[1] && k <= L.owned_hi[2];
+        const double m = np_block_reduce<true>(fabs(v));
+        const double sm = np_block_reduce<false>(owned ? np_neumann_weight(L, i, j, k) * v : 0.0);
+        if (threadIdx.x == 0 && threadIdx.y == 0) {
+            const long long bidx = blockIdx.x + gridDim.x * (blockIdx.y + (long long)gridDim.y * blockIdx.z);
+            block_max[bidx] = m; block_sum[bidx] = sm;
+        }
     }
 }
+
+// final stage after a reducing kernel: scal[0] = max(part_max), scal[2] = sum(part_sum) (fixed order),
+// and with want_off scal[6] = scal[2] / wtot, the solvability offset (MLNodeLinOp::fixSolvabilityByOffset)
+__global__ void __launch_bounds__(1024) k_reduce_norm_off(const double* __restrict__ part_max, const double* __restrict__ part_sum,
+                                                          long long n, double* scal, double wtot, int want_off)
+{
+    double m = 0.0, sm = 0.0;
+    for (long long t = threadIdx.x; t < n; t += blockDim.x) { m = fmax(m, part_max[t]); if (want_off) sm += part_sum[t]; }
+    m = np_block_reduce<true>(m);
+    sm = np_block_reduce<false>(sm);
+    if (threadIdx.x == 0) { scal[0] = m; if (want_off) { scal[2] = sm; scal[6] = sm / wtot; } }
+}
+__global__ void k_set_offset(double* scal, double wtot) { if (threadIdx.x == 0 && blockIdx.x == 0) scal[6] = scal[2] / wtot; }
 
 // second stage of a reduction: one block folds `n` partials into out[slot] (max or sum), fixed order
 template <bool IS_MAX> __global__ void __launch_bounds__(256) k_reduce_final(const double* __restrict__ part, long long n, double* out, int slot)
@@ -270,6 +287,13 @@ __global__ void __launch_bounds__(256) k_add(LevelDev L, double* __restrict__ y,
 #define GS_SMEM_BYTES (GS_RING * GS_PLANE * 8)
 
 struct GsCoef { double a_fx, a_fy, a_exy, a_fz, a_exz, a_eyz, a_c, dinv; };
+struct GsArgs {
+    GsCoef c;
+    double* xout; const double* xin; const double* rhs; const double* sig;
+    const double* boff;      // optional device scalar subtracted from rhs (lazy makeSolvable), or null
+    const double* addto;     // optional: xout = addto + result (xout may alias addto), or null
+    int zc, zero_in;         // z-chunk; 1: xin is known to be zero and is not read
+};
 
 __device__ __forceinline__ void np_cp_async8(double* smem_dst, const double* gsrc, bool valid)
 {
@@ -305,10 +329,14 @@ struct GsSmemX {   // 27-point accessor around tile-local node (li, lj) for the 
 };
 
 template <bool CS>
-__global__ void __launch_bounds__(256, CS ? 2 : 1) k_gs2(LevelDev L, GsCoef C, double* __restrict__ xout, const double* __restrict__ xin,
-                                                         const double* __restrict__ rhs, const double* __restrict__ sig, int zc)
+__global__ void __launch_bounds__(256, CS ? 2 : 1) k_gs2(LevelDev L, GsArgs A)
 {
     NP_DYN_SMEM(double, ring);
+    const GsCoef& C = A.c;
+    double* __restrict__ xout = A.xout; const double* __restrict__ xin = A.xin;
+    const double* __restrict__ rhs = A.rhs; const double* __restrict__ sig = A.sig;
+    const int zc = A.zc;
+    const double roff = A.boff ? A.boff[0] : 0.0;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int grp = warp >> 2;                           // 0: first sweep (plane t), 1: second sweep (plane t-2)
     const int wy = warp & 3;                             // tile rows 8*wy .. 8*wy+7
@@ -339,7 +367,7 @@ __global__ void __launch_bounds__(256, CS ? 2 : 1) k_gs2(LevelDev L, GsCoef C, d
         for (int e = tid; e < 34 * 66; e += 256) {
             const int row = e / 66, g = e - row * 66 + 1;
             const int i = i0 + g - 2, j = j0 + row - 1;
-            const bool valid = (i <= L.n[0] + 1 && j <= L.n[1] + 1);
+            const bool valid = (i <= L.n[0] + 1 && j <= L.n[1] + 1) && !A.zero_in;
             const double* src = valid ? xin + (kof + L.nsy * (long long)(j + 1) + (i + 1)) : xin;
             np_cp_async8(dst + ((g & 1) ? GS_HALF : 0) + row * GS_HP + (g >> 1), src, valid);
         }
@@ -374,7 +402,7 @@ __global__ void __launch_bounds__(256, CS ? 2 : 1) k_gs2(LevelDev L, GsCoef C, d
                 for (int a = 0; a < 2; ++a)
 #pragma unroll
                     for (int r = 0; r < 8; ++r)
-                        rv[a][r] = ((act >> (a * 8 + r)) & 1u) ? rhs[gbase + a + L.nsy * r] : 0.0;
+                        rv[a][r] = ((act >> (a * 8 + r)) & 1u) ? rhs[gbase + a + L.nsy * r] - roff : 0.0;
                 const double* Pm = slot(p - 1); const double* Pp = slot(p + 1);
 #pragma unroll
                 for (int rr = -1; rr <= 8; ++rr) {
@@ -482,7 +510,7 @@ __global__ void __launch_bounds__(256, CS ? 2 : 1) k_gs2(LevelDev L, GsCoef C, d
                                 GsSmemX xa{Pm, Pc, Pp, 2 * lane + a, 8 * wy + r};
                                 GlobS sa{sig + np_coff(L, gi + a, gj + r, k), L.csy, L.csz};
                                 const Sig8 g = np_load_sig(sa);
-                                v = (rhs[gbase + a + L.nsy * r] - np_offdiag(L.c, g, xa)) / np_diag(L.c, g);
+                                v = ((rhs[gbase + a + L.nsy * r] - roff) - np_offdiag(L.c, g, xa)) / np_diag(L.c, g);
                             }
                             x[a][r] = v;
                             Pc[gs_idx(2 * lane + a, 8 * wy + r)] = v;
@@ -499,7 +527,145 @@ __global__ void __launch_bounds__(256, CS ? 2 : 1) k_gs2(LevelDev L, GsCoef C, d
             for (int a = 0; a < 2; ++a)
 #pragma unroll
                 for (int r = 0; r < 8; ++r)
-                    if ((wrt >> (a * 8 + r)) & 1u) xout[gbase + a + L.nsy * r] = x[a][r];
+                    if ((wrt >> (a * 8 + r)) & 1u) {
+                        const long long o = gbase + a + L.nsy * r;
+                        xout[o] = A.addto ? A.addto[o] + x[a][r] : x[a][r];
+                    }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K2, constant sigma: y = A x  (MODE 0)  or  y = (b - *boff) - A x  (MODE 1), marching in z.
+// One CTA owns a 64 x 32 column chunk; each plane of x is staged ONCE in shared memory (cp.async, two
+// planes ahead, split even/odd layout as in k_gs2); each thread owns a 2 x 4 block of nodes and keeps,
+// per node, the in-plane 9-point sums of the last three planes in registers:
+//     y[k] = U[k] + V[k-1] + V[k+1],   U = same-plane weights (incl. diagonal), V = adjacent-plane weights.
+// REDUCE: per-CTA partials of max|y| (all valid nodes) and sum(w*y) (owned nodes, dot-mask weights) —
+// the residual norm and the solvability offset of the next V-cycle come out of the same pass.
+// ------------------------------------------------------------------------------------------------
+#define ST_RING 3
+#define ST_SMEM_BYTES (ST_RING * GS_PLANE * 8)
+struct StCoef { double d, w_fx, w_fy, w_exy, w_fz, w_exz, w_eyz, w_c; };
+
+template <int MODE, bool REDUCE>
+__global__ void __launch_bounds__(256, 2) k_stencil_cs(LevelDev L, StCoef C, double* __restrict__ y, const double* __restrict__ x,
+                                                       const double* __restrict__ b, const double* __restrict__ boff,
+                                                       double* __restrict__ part_max, double* __restrict__ part_sum, int zc)
+{
+    NP_DYN_SMEM(double, ring);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int i0 = blockIdx.x * GS_TX, j0 = blockIdx.y * GS_TY, kb = blockIdx.z * zc;
+    const int nkl = min(kb + zc - 1, L.n[2]) - kb + 1;       // output planes kb .. kb+nkl-1
+    const int gi = i0 + 2 * lane, gj = j0 + 4 * warp;
+    const int row0 = 4 * warp + 1;
+    const double off = (MODE == 1 && boff) ? boff[0] : 0.0;
+
+    unsigned act = 0, dir = 0;
+    double wgt[2][4];
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            const int i = gi + a, j = gj + r;
+            const bool v = (i <= L.n[0] && j <= L.n[1]);
+            const bool dd = v && ((L.face[0] == NP_FACE_DIRICHLET && i == 0) || (L.face[3] == NP_FACE_DIRICHLET && i == L.n[0])
+                               || (L.face[1] == NP_FACE_DIRICHLET && j == 0) || (L.face[4] == NP_FACE_DIRICHLET && j == L.n[1]));
+            act |= (unsigned)v << (a * 4 + r); dir |= (unsigned)dd << (a * 4 + r);
+            double w = 0.0;
+            if (REDUCE && v && i <= L.owned_hi[0] && j <= L.owned_hi[1]) {
+                w = 1.0;
+                if (L.face[0] == NP_FACE_NEUMANN && i == 0) w *= 0.5;
+                if (L.face[3] == NP_FACE_NEUMANN && i == L.n[0]) w *= 0.5;
+                if (L.face[1] == NP_FACE_NEUMANN && j == 0) w *= 0.5;
+                if (L.face[4] == NP_FACE_NEUMANN && j == L.n[1]) w *= 0.5;
+            }
+            wgt[a][r] = w;
+        }
+
+    auto load_plane = [&](int k) {                       // global plane k in [-1, n2+1]
+        double* dst = ring + ((k + 1) % ST_RING) * GS_PLANE;
+        const long long kof = L.nsz * (long long)(k + 1);
+        for (int e = tid; e < 34 * 66; e += 256) {
+            const int row = e / 66, g = e - row * 66 + 1;
+            const int i = i0 + g - 2, j = j0 + row - 1;
+            const bool valid = (i <= L.n[0] + 1 && j <= L.n[1] + 1);
+            const double* src = valid ? x + (kof + L.nsy * (long long)(j + 1) + (i + 1)) : x;
+            np_cp_async8(dst + ((g & 1) ? GS_HALF : 0) + row * GS_HP + (g >> 1), src, valid);
+        }
+    };
+
+    double Vm[2][4], Vc[2][4], Uc[2][4];
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+        for (int r = 0; r < 4; ++r) { Vm[a][r] = 0.0; Vc[a][r] = 0.0; Uc[a][r] = 0.0; }
+    double tmax = 0.0, tsum = 0.0;
+
+    load_plane(kb - 1); np_cp_async_commit();
+    load_plane(kb);     np_cp_async_commit();
+    for (int s = 0; s <= nkl + 1; ++s) {
+        const int q = kb - 1 + s;                        // plane arriving this step
+        // planes q (needed now) and q+1 were issued; keep at most the newest group in flight
+#ifndef NP_EMU
+        if (s <= nkl) asm volatile("cp.async.wait_group 1;\n" ::: "memory"); else asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+#endif
+        __syncthreads();                                 // plane q visible; everyone is done reading plane q-1
+        if (s + 2 <= nkl + 1) load_plane(q + 2);         // goes into the slot of plane q-1
+        np_cp_async_commit();
+        const double* P = ring + ((q + 1) % ST_RING) * GS_PLANE;
+        double c0[6], c1[6], h0[6], h1[6];
+#pragma unroll
+        for (int rr = 0; rr < 6; ++rr) {
+            const int ro = (row0 - 1 + rr) * GS_HP + lane;
+            const double xl = P[GS_HALF + ro], x0 = P[ro + 1], x1 = P[GS_HALF + ro + 1], xr = P[ro + 2];
+            c0[rr] = x0; c1[rr] = x1; h0[rr] = xl + x1; h1[rr] = x0 + xr;
+        }
+        double Un[2][4], Vn[2][4];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            const double cc0 = c0[r] + c0[r + 2], hh0 = h0[r] + h0[r + 2], cc1 = c1[r] + c1[r + 2], hh1 = h1[r] + h1[r + 2];
+            Un[0][r] = C.d * c0[r + 1] + C.w_fx * h0[r + 1] + C.w_fy * cc0 + C.w_exy * hh0;
+            Un[1][r] = C.d * c1[r + 1] + C.w_fx * h1[r + 1] + C.w_fy * cc1 + C.w_exy * hh1;
+            Vn[0][r] = C.w_fz * c0[r + 1] + C.w_exz * h0[r + 1] + C.w_eyz * cc0 + C.w_c * hh0;
+            Vn[1][r] = C.w_fz * c1[r + 1] + C.w_exz * h1[r + 1] + C.w_eyz * cc1 + C.w_c * hh1;
+        }
+        if (s >= 2) {                                    // output plane k = q-1
+            const int k = q - 1;
+            const bool zdir = (L.face[2] == NP_FACE_DIRICHLET && k == 0) || (L.face[5] == NP_FACE_DIRICHLET && k == L.n[2]);
+            double wz = 1.0;
+            if (REDUCE) {
+                if (k > L.owned_hi[2]) wz = 0.0;
+                if ((L.face[2] == NP_FACE_NEUMANN && k == 0) || (L.face[5] == NP_FACE_NEUMANN && k == L.n[2])) wz *= 0.5;
+            }
+            const long long gbase = np_noff(L, gi, gj, k);
+#pragma unroll
+            for (int a = 0; a < 2; ++a)
+#pragma unroll
+                for (int r = 0; r < 4; ++r) {
+                    if ((act >> (a * 4 + r)) & 1u) {
+                        const long long o = gbase + a + L.nsy * r;
+                        double v = 0.0;
+                        if (!(zdir || ((dir >> (a * 4 + r)) & 1u))) {
+                            const double ax = Uc[a][r] + (Vm[a][r] + Vn[a][r]);
+                            v = (MODE == 1) ? (b[o] - off) - ax : ax;
+                        }
+                        y[o] = v;
+                        if (REDUCE) { tmax = fmax(tmax, fabs(v)); tsum += (wgt[a][r] * wz) * v; }
+                    }
+                }
+        }
+#pragma unroll
+        for (int a = 0; a < 2; ++a)
+#pragma unroll
+            for (int r = 0; r < 4; ++r) { Vm[a][r] = Vc[a][r]; Vc[a][r] = Vn[a][r]; Uc[a][r] = Un[a][r]; }
+    }
+    if (REDUCE) {
+        const double m = np_block_reduce<true>(tmax);
+        const double sm = np_block_reduce<false>(tsum);
+        if (tid == 0) {
+            const long long bidx = blockIdx.x + gridDim.x * (blockIdx.y + (long long)gridDim.y * blockIdx.z);
+            part_max[bidx] = m; part_sum[bidx] = sm;
         }
     }
 }

@@ -133,6 +133,9 @@ int NpSolver::create(const np_geom* g, int nboxes, const np_box* boxes, const in
 #ifndef NP_EMU
     cudaFuncSetAttribute(k_gs2<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GS_SMEM_BYTES);
     cudaFuncSetAttribute(k_gs2<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GS_SMEM_BYTES);
+    cudaFuncSetAttribute(k_stencil_cs<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ST_SMEM_BYTES);
+    cudaFuncSetAttribute(k_stencil_cs<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ST_SMEM_BYTES);
+    cudaFuncSetAttribute(k_stencil_cs<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ST_SMEM_BYTES);
 #endif
     np_rt::stream_sync(stream);
     return np_rt::last_error() ? NP_ERR_CUDA : NP_OK;
@@ -220,36 +223,72 @@ void NpSolver::fill(int l, double* x)
     }
 }
 
+// stencil z-chunk: enough CTAs for ~6 per SM, 4..64 output planes each (two extra planes are staged per chunk)
+static int st_zchunk(const LevelDev& d) {
+    const int ncols = ((d.n[0] + GS_TX) / GS_TX) * ((d.n[1] + GS_TY) / GS_TY);
+    const int nch_want = (888 + ncols - 1) / ncols;
+    const int nn = d.n[2] + 1;
+    return std::min(64, std::max(4, (nn + nch_want - 1) / nch_want));
+}
+static StCoef st_coef(const LevelDev& d) {
+    const double sg = d.sigma0;
+    StCoef c;
+    c.d = -32.0 * d.c.fxyz * sg;
+    c.w_fx = 4.0 * d.c.f4xm2ym2z * sg; c.w_fy = 4.0 * d.c.fm2x4ym2z * sg; c.w_fz = 4.0 * d.c.fm2xm2y4z * sg;
+    c.w_exy = 2.0 * d.c.f2x2ymz * sg; c.w_exz = 2.0 * d.c.f2xmy2z * sg; c.w_eyz = 2.0 * d.c.fmx2y2z * sg;
+    c.w_c = d.c.fxyz * sg;
+    return c;
+}
+
 void NpSolver::apply(int l, double* y, double* x)
 {
     fill(l, x);
     const LevelDev& d = lev[l].d;
-    if (d.const_sigma) NP_LAUNCH(true, (k_adotx<0, true, false>), grid_nodes(d), NP_BLK, 0, stream, d, y, x, (const double*)nullptr, lev[l].sigma, (double*)nullptr);
-    else               NP_LAUNCH(true, (k_adotx<0, false, false>), grid_nodes(d), NP_BLK, 0, stream, d, y, x, (const double*)nullptr, lev[l].sigma, (double*)nullptr);
-    ++launches;
-}
-
-// y = b - A x; with_norm leaves per-block maxima of |y| in part0 (see finish_norm)
-void NpSolver::residual(int l, double* y, double* x, const double* b, bool with_norm)
-{
-    fill(l, x);
-    const LevelDev& d = lev[l].d;
     if (d.const_sigma) {
-        if (with_norm) NP_LAUNCH(true, (k_adotx<1, true, true>), grid_nodes(d), NP_BLK, 0, stream, d, y, x, b, lev[l].sigma, part0);
-        else           NP_LAUNCH(true, (k_adotx<1, true, false>), grid_nodes(d), NP_BLK, 0, stream, d, y, x, b, lev[l].sigma, part0);
+        const int zc = st_zchunk(d);
+        const dim3 grid((d.n[0] + GS_TX) / GS_TX, (d.n[1] + GS_TY) / GS_TY, (d.n[2] + zc) / zc);
+        NP_LAUNCH(true, (k_stencil_cs<0, false>), grid, dim3(256), ST_SMEM_BYTES, stream, d, st_coef(d), y, (const double*)x,
+                  (const double*)nullptr, (const double*)nullptr, part0, part1, zc);
     } else {
-        if (with_norm) NP_LAUNCH(true, (k_adotx<1, false, true>), grid_nodes(d), NP_BLK, 0, stream, d, y, x, b, lev[l].sigma, part0);
-        else           NP_LAUNCH(true, (k_adotx<1, false, false>), grid_nodes(d), NP_BLK, 0, stream, d, y, x, b, lev[l].sigma, part0);
+        NP_LAUNCH(true, (k_adotx<0, false, false>), grid_nodes(d), NP_BLK, 0, stream, d, y, x, (const double*)nullptr, (const double*)nullptr, lev[l].sigma, part0, part1);
     }
     ++launches;
 }
 
-// fold the per-block maxima left in part0 by a NORM kernel on level l; returns the global inf-norm
-double NpSolver::finish_norm(int l)
+// y = (b - *boff) - A x.  with_red leaves per-CTA partials in part0 (max |y|) and part1 (dot-mask weighted
+// sum of y) for finish_norm: the inf-norm and the next solvability offset come out of the residual pass.
+void NpSolver::residual(int l, double* y, double* x, const double* b, bool with_red, const double* boff)
 {
+    fill(l, x);
     const LevelDev& d = lev[l].d;
-    NP_LAUNCH(true, (k_reduce_final<true>), dim3(1), dim3(256), 0, stream, (const double*)part0, nblocks(grid_nodes(d)), scal, 0); ++launches;
-    if (is_sharded(*this, lev[l])) { if (comm.allreduce(comm.ctx, scal, 1, 1, (void*)stream)) err = NP_ERR_NCCL; }
+    if (d.const_sigma) {
+        const int zc = st_zchunk(d);
+        const dim3 grid((d.n[0] + GS_TX) / GS_TX, (d.n[1] + GS_TY) / GS_TY, (d.n[2] + zc) / zc);
+        const StCoef c = st_coef(d);
+        if (with_red) NP_LAUNCH(true, (k_stencil_cs<1, true>), grid, dim3(256), ST_SMEM_BYTES, stream, d, c, y, (const double*)x, b, boff, part0, part1, zc);
+        else          NP_LAUNCH(true, (k_stencil_cs<1, false>), grid, dim3(256), ST_SMEM_BYTES, stream, d, c, y, (const double*)x, b, boff, part0, part1, zc);
+        red_n = nblocks(grid);
+    } else {
+        if (with_red) NP_LAUNCH(true, (k_adotx<1, false, true>), grid_nodes(d), NP_BLK, 0, stream, d, y, x, b, boff, lev[l].sigma, part0, part1);
+        else          NP_LAUNCH(true, (k_adotx<1, false, false>), grid_nodes(d), NP_BLK, 0, stream, d, y, x, b, boff, lev[l].sigma, part0, part1);
+        red_n = nblocks(grid_nodes(d));
+    }
+    ++launches;
+}
+
+// fold the partials left by a reducing kernel on level l: returns the global inf-norm; with want_off the
+// solvability offset sum(w*y)/sum(w) of the same array is left on the device in scal[6]
+double NpSolver::finish_norm(int l, bool want_off)
+{
+    const bool sh = is_sharded(*this, lev[l]);
+    NP_LAUNCH(true, k_reduce_norm_off, dim3(1), dim3(1024), 0, stream, (const double*)part0, (const double*)part1, red_n, scal, wtot, want_off ? 1 : 0); ++launches;
+    if (sh) {
+        if (comm.allreduce(comm.ctx, scal, 1, 1, (void*)stream)) err = NP_ERR_NCCL;
+        if (want_off) {
+            if (comm.allreduce(comm.ctx, scal + 2, 1, 0, (void*)stream)) err = NP_ERR_NCCL;
+            NP_LAUNCH(false, k_set_offset, dim3(1), dim3(32), 0, stream, scal, wtot); ++launches;
+        }
+    }
     np_rt::copy_async(h_scal, scal, sizeof(double), stream);
     np_rt::stream_sync(stream);
     return h_scal[0];
@@ -259,7 +298,8 @@ double NpSolver::norminf(int l, const double* x)
 {
     const LevelDev& d = lev[l].d;
     NP_LAUNCH(true, k_norminf, grid_nodes(d), NP_BLK, 0, stream, d, x, part0); ++launches;
-    return finish_norm(l);
+    red_n = nblocks(grid_nodes(d));
+    return finish_norm(l, false);
 }
 
 // MLMG::makeSolvable on level l: x -= (sum w x)/(sum w) over owned nodes, scalars never leave the device
@@ -274,30 +314,36 @@ void NpSolver::make_solvable(int l, double* x)
     NP_LAUNCH(false, k_sub_offset, grid_nodes(d), NP_BLK, 0, stream, d, x, (const double*)(scal + 2)); ++launches;
 }
 
-// one Fsmooth (two GS sweeps) on lev[l].cor with rhs lev[l].res, then sync + ghost fill of the result
-void NpSolver::smooth(int l, bool skip_fill)
+// one Fsmooth (two GS sweeps) on lev[l].cor with rhs lev[l].res (- *lvl0_off on level 0), then sync + ghost
+// fill of the result.  zero_in: the input is known to be zero and is not read.  add_to: the result is not
+// stored as the correction but added to `add_to` in place (MLMG's sol += cor folded into the last smooth).
+void NpSolver::smooth(int l, bool zero_in, double* add_to)
 {
     NpLevel& L = lev[l];
     const LevelDev& d = L.d;
-    if (!skip_fill && !L.cor_ghost_clean) fill(l, L.cor);
+    if (!zero_in && !L.cor_ghost_clean) fill(l, L.cor);
     const dim3 grid((d.n[0] + 1 + GS_WX - 1) / GS_WX, (d.n[1] + 1 + GS_WY - 1) / GS_WY, (d.n[2] + 1 + L.zc - 1) / L.zc);
     const size_t smem = GS_SMEM_BYTES;
     const bool prof = (l == 0 && opt.profile_kernels && prof_n + 2 <= (int)prof_ev.size());
     if (prof) np_rt::event_record(prof_ev[prof_n], stream);
-    GsCoef gc{};
+    GsArgs ga{};
+    ga.xout = add_to ? add_to : L.cor_alt; ga.xin = L.cor; ga.rhs = L.res; ga.sig = L.sigma;
+    ga.boff = (l == 0) ? lvl0_off : nullptr; ga.addto = add_to; ga.zc = L.zc; ga.zero_in = zero_in ? 1 : 0;
     if (d.const_sigma) {
         // constant sigma: the 26 neighbours fall into 7 weight classes; everything is pre-divided by the diagonal
         const double sg = d.sigma0, dinv = 1.0 / (-32.0 * d.c.fxyz * sg);
+        GsCoef& gc = ga.c;
         gc.dinv = dinv;
         gc.a_fx = 4.0 * d.c.f4xm2ym2z * sg * dinv; gc.a_fy = 4.0 * d.c.fm2x4ym2z * sg * dinv; gc.a_fz = 4.0 * d.c.fm2xm2y4z * sg * dinv;
         gc.a_exy = 2.0 * d.c.f2x2ymz * sg * dinv; gc.a_exz = 2.0 * d.c.f2xmy2z * sg * dinv; gc.a_eyz = 2.0 * d.c.fmx2y2z * sg * dinv;
         gc.a_c = d.c.fxyz * sg * dinv;
-        NP_LAUNCH(true, (k_gs2<true>), grid, dim3(256), smem, stream, d, gc, L.cor_alt, (const double*)L.cor, (const double*)L.res, (const double*)L.sigma, L.zc);
+        NP_LAUNCH(true, (k_gs2<true>), grid, dim3(256), smem, stream, d, ga);
     } else {
-        NP_LAUNCH(true, (k_gs2<false>), grid, dim3(256), smem, stream, d, gc, L.cor_alt, (const double*)L.cor, (const double*)L.res, (const double*)L.sigma, L.zc);
+        NP_LAUNCH(true, (k_gs2<false>), grid, dim3(256), smem, stream, d, ga);
     }
     ++launches;
     if (prof) { np_rt::event_record(prof_ev[prof_n + 1], stream); prof_n += 2; }
+    if (add_to) { L.cor_ghost_clean = false; return; }
     std::swap(L.cor, L.cor_alt);
     fill(l, L.cor);                 // nodalSync (+ the ghosts the next operation needs)
     L.cor_ghost_clean = true;
@@ -344,8 +390,7 @@ int NpSolver::bottom_solve()
         return h_bot_out[0];
     };
     if (opt.bottom_solver == NP_BOTTOM_SMOOTHER) {
-        zero(L.cor, L.d.ntot); L.cor_ghost_clean = true;
-        for (int i = 0; i < opt.num_final_smooth; ++i) smooth(l, i == 0);
+        for (int i = 0; i < opt.num_final_smooth; ++i) smooth(l, i == 0, nullptr);
         return 0;
     }
     int type = (opt.bottom_solver == NP_BOTTOM_CG || (opt.bottom_solver == NP_BOTTOM_BICGCG && bicg_failed_switch)) ? 1 : 0;
@@ -360,19 +405,20 @@ int NpSolver::bottom_solve()
         if (ret != 0) zero(L.cor, L.d.ntot);
     }
     L.cor_ghost_clean = false;
-    if (ret != 0) for (int i = 0; i < opt.num_final_smooth; ++i) smooth(l, false);
+    if (ret != 0) for (int i = 0; i < opt.num_final_smooth; ++i) smooth(l, false, nullptr);
     return iters;
 }
 
-// MLMG::mgVcycle(0,0) on res[0]: leaves the correction in cor[0]
-void NpSolver::vcycle()
+// MLMG::mgVcycle(0,0) on res[0] (- *lvl0_off): leaves the correction in cor[0], or, with add_to_sol, adds it
+// to sol inside the last post-smooth (MLMG::oneIter's sol += cor)
+void NpSolver::vcycle(bool add_to_sol)
 {
     const int nl = (int)lev.size();
     for (int l = 0; l < nl - 1; ++l) {
         NpLevel& L = lev[l];
-        zero(L.cor, L.d.ntot); L.cor_ghost_clean = true;
-        for (int i = 0; i < opt.num_pre_smooth; ++i) smooth(l, i == 0);
-        residual(l, L.rescor, L.cor, L.res, false);                 // computeResOfCorrection
+        if (opt.num_pre_smooth == 0) { zero(L.cor, L.d.ntot); L.cor_ghost_clean = true; }
+        for (int i = 0; i < opt.num_pre_smooth; ++i) smooth(l, i == 0, nullptr);      // cor = 0 is implied by zero_in
+        residual(l, L.rescor, L.cor, L.res, false, l == 0 ? lvl0_off : nullptr);   // computeResOfCorrection
         restrict_to(l + 1, lev[l + 1].res, L.rescor);
     }
     stats.bottom_iters_total += bottom_solve();
@@ -380,8 +426,11 @@ void NpSolver::vcycle()
         NpLevel& L = lev[l];
         interp_add(l, L.cor, lev[l + 1].cor);                       // addInterpCorrection
         L.cor_ghost_clean = false;
-        for (int i = 0; i < opt.num_post_smooth; ++i) smooth(l, false);
+        for (int i = 0; i < opt.num_post_smooth; ++i)
+            smooth(l, false, (add_to_sol && l == 0 && i == opt.num_post_smooth - 1) ? sol : nullptr);
     }
+    if (nl == 1 && add_to_sol) { NP_LAUNCH(false, k_add, grid_nodes(lev[0].d), NP_BLK, 0, stream, lev[0].d, sol, (const double*)lev[0].cor); ++launches; }
+    else if (add_to_sol && opt.num_post_smooth == 0) { NP_LAUNCH(false, k_add, grid_nodes(lev[0].d), NP_BLK, 0, stream, lev[0].d, sol, (const double*)lev[0].cor); ++launches; }
 }
 
 // MLMG::solve with the zero initial guess NodalProjector uses
@@ -393,10 +442,13 @@ int NpSolver::solve(double rtol, double atol)
     bicg_failed_switch = false;
     stats.bottom_iters_total = 0; stats.n_vcycles = 0; stats.status = NP_OK; stats.n_levels = (int)lev.size();
     for (int i = 0; i < 128; ++i) stats.res_history[i] = 0.0;
+    wtot = 1.0;
+    for (int dd = 0; dd < 3; ++dd) wtot *= (double)geom.ncell[dd];   // sum of the dot-mask weights (periodic / Neumann dims)
+    lvl0_off = nullptr;
     if (singular) make_solvable(0, rhs);
     const double rhsnorm0 = norminf(0, rhs);
-    residual(0, L0.res, sol, rhs, true);
-    const double resnorm0 = finish_norm(0);
+    residual(0, L0.res, sol, rhs, true, nullptr);
+    const double resnorm0 = finish_norm(0, singular);
     const double max_norm = rhsnorm0 >= resnorm0 ? rhsnorm0 : resnorm0;
     const double res_target = std::max(atol, std::max(rtol, 1e-16) * max_norm);
     stats.rhs_norm0 = rhsnorm0; stats.res_norm0 = resnorm0; stats.res_norm_final = resnorm0;
@@ -404,11 +456,13 @@ int NpSolver::solve(double rtol, double atol)
     if (resnorm0 <= res_target) return NP_OK;
     bool converged = false;
     for (int iter = 0; iter < opt.maxiter; ++iter) {
-        if (singular) make_solvable(0, L0.res);
-        vcycle();
-        NP_LAUNCH(false, k_add, grid_nodes(d0), NP_BLK, 0, stream, d0, sol, (const double*)L0.cor); ++launches;
-        residual(0, L0.res, sol, rhs, true);
-        const double rn = finish_norm(0);
+        // MLMG makes the residual solvable before every V-cycle; here the offset (scal[6], left by finish_norm)
+        // is subtracted on the fly by the level-0 consumers of res instead of in a separate pass
+        lvl0_off = singular ? scal + 6 : nullptr;
+        vcycle(true);
+        lvl0_off = nullptr;
+        residual(0, L0.res, sol, rhs, true, nullptr);
+        const double rn = finish_norm(0, singular);
         if (iter < 128) stats.res_history[iter] = rn;
         stats.n_vcycles = iter + 1; stats.res_norm_final = rn;
         if (opt.verbose >= 2 && comm.rank == 0) std::printf("MLMG: Iteration %3d Fine resid/bnorm = %.6e\n", iter + 1, rn / max_norm);

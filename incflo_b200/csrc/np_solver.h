@@ -61,6 +61,9 @@ struct NpSolver {
     bool have_sigma = false, have_result = false, singular = true;
     bool bicg_failed_switch = false;
     long long launches = 0;
+    long long red_n = 0;            // number of partials the last reducing kernel left in part0 / part1
+    double wtot = 1.0;              // sum of the dot-mask weights over the domain (singular problems)
+    const double* lvl0_off = nullptr;   // device scalar subtracted from lev[0].res by its consumers (lazy makeSolvable)
     int err = 0;
 
     int create(const np_geom* g, int nboxes, const np_box* boxes, const int* owner, int my_rank, int nranks,
@@ -72,17 +75,17 @@ struct NpSolver {
     // building blocks (device pointers, internal layout)
     void fill(int l, double* x);
     void apply(int l, double* y, double* x);                       // fills x's ghosts first
-    void residual(int l, double* y, double* x, const double* b, bool with_norm);
-    void smooth(int l, bool skip_fill);                            // on lev[l].cor / res
+    void residual(int l, double* y, double* x, const double* b, bool with_red, const double* boff);
+    void smooth(int l, bool zero_in, double* add_to);              // on lev[l].cor / res
     void restrict_to(int lc, double* crse, double* fine);          // fine gets its ghosts filled
     void restrict_to_replica(int lc, double* crse, const double* fine);
     void avgdown_sigma_to_replica(int lc);
     void interp_add(int lf, double* fine, const double* crse);
     void make_solvable(int l, double* x);
     double norminf(int l, const double* x);
-    double finish_norm(int l);                                     // reduce part0 partial maxima -> host
+    double finish_norm(int l, bool want_off);                      // reduce the partials of the last reducing kernel -> host
     int bottom_solve();
-    void vcycle();
+    void vcycle(bool add_to_sol);
     int solve(double rtol, double atol);
     int set_sigma(const FabView& s);
     int project(np_fab* vel, const np_fab* sigma, double rtol, double atol);
