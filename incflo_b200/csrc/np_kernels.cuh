@@ -305,6 +305,12 @@ __device__ __forceinline__ void np_cp_async8(double* smem_dst, const double* gsr
     asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;\n" :: "r"(d), "l"(gsrc), "r"(sz) : "memory");
 #endif
 }
+__device__ __forceinline__ void np_prefetch_l1(const void* p)
+{
+#ifndef NP_EMU
+    asm volatile("prefetch.global.L1 [%0];\n" :: "l"(p));
+#endif
+}
 __device__ __forceinline__ void np_cp_async_commit()
 {
 #ifndef NP_EMU
@@ -328,6 +334,110 @@ struct GsSmemX {   // 27-point accessor around tile-local node (li, lj) for the 
     }
 };
 
+// Cooperative plane loader shared by k_gs2 and k_stencil_cs: 198 of the 256 threads each own one of the 66
+// columns (tile halo included) of three interleaved row sets, so a plane costs 12 cp.async per thread with
+// one add per address.  Source offsets are relative to the plane, destinations are split-layout slots.
+struct GsLoader {
+    int src0, dst0, nrow_ok;     // first element; rows (counted from this thread's first) that exist
+    bool active;
+    __device__ __forceinline__ void init(const LevelDev& L, int tid, int i0, int j0, bool zero_in) {
+        const int c = tid % 66, r0 = tid / 66;           // column slot g = c+1, first row r0 (0..2); tid >= 198 idle
+        const int g = c + 1, i = i0 + g - 2;
+        active = (tid < 198);
+        // row index `row` (0..33) is node j = j0 + row - 1; it exists when j <= n1 + 1
+        const int rows_exist = min(34, L.n[1] + 3 - j0);            // rows 0 .. rows_exist-1 exist
+        nrow_ok = (i <= L.n[0] + 1 && !zero_in) ? rows_exist : 0;
+        src0 = (int)(L.nsy * (long long)(j0 + r0) + (i + 1));      // row r0 -> j+1 = j0 + r0
+        dst0 = ((g & 1) ? GS_HALF : 0) + r0 * GS_HP + (g >> 1);
+        if (!active) { src0 = 0; nrow_ok = 0; }
+        row_first = r0;
+    }
+    int row_first;
+    __device__ __forceinline__ void load(double* dst_plane, const double* src_plane, long long nsy) const {
+        if (!active) return;
+        const double* sp = src_plane + src0;
+        double* dp = dst_plane + dst0;
+#pragma unroll
+        for (int it = 0; it < 12; ++it) {
+            const int row = row_first + 3 * it;
+            if (row < 34) {
+                const bool valid = row < nrow_ok;
+                np_cp_async8(dp, valid ? sp : src_plane, valid);
+            }
+            sp += 3 * nsy; dp += 3 * GS_HP;
+        }
+    }
+};
+
+// The four colour steps of one plane for a thread's 2 x 8 block (constant sigma).  MASKED: the tile has
+// nodes outside the domain or on Dirichlet faces, which keep their value / are set to zero.
+template <bool MASKED>
+__device__ __forceinline__ void gs_colours_cs(bool on, double (&x)[2][8], const double (&B)[2][8], double* Pc, const GsCoef& C,
+                                              int ofs, unsigned act, unsigned dmask)
+{
+    // ofs = row0 * GS_HP + lane: (row r, own even column) is Pc[ofs + r*GS_HP + 1], own odd column adds GS_HALF,
+    // left halo column Pc[GS_HALF + ofs + r*GS_HP], right halo column Pc[ofs + r*GS_HP + 2]
+    double t0 = 0.0, t1 = 0.0, d0 = 0.0, d1 = 0.0;
+    const double nfx = -C.a_fx, nfy = -C.a_fy, nxy = -C.a_exy;
+    // ---- colour 0: a = 0, r even ----
+    if (on) {
+        double xl[9];
+#pragma unroll
+        for (int q = 0; q < 9; ++q) xl[q] = Pc[GS_HALF + ofs + (q - 1) * GS_HP];              // rows -1..7
+        t0 = Pc[ofs - GS_HP + 1]; t1 = Pc[GS_HALF + ofs - GS_HP + 1];
+#pragma unroll
+        for (int r = 0; r < 8; r += 2) {
+            const double up0 = r == 0 ? t0 : x[0][r - 1], up1 = r == 0 ? t1 : x[1][r - 1];
+            const double v = fma(nxy, (xl[r] + xl[r + 2]) + (up1 + x[1][r + 1]), fma(nfy, up0 + x[0][r + 1], fma(nfx, xl[r + 1] + x[1][r], B[0][r])));
+            if (!MASKED) x[0][r] = v; else if ((act >> r) & 1u) x[0][r] = ((dmask >> r) & 1u) ? 0.0 : v;
+            Pc[ofs + r * GS_HP + 1] = x[0][r];
+        }
+    }
+    __syncthreads();
+    // ---- colour 1: a = 1, r even ----
+    if (on) {
+        double xr[9];
+#pragma unroll
+        for (int q = 0; q < 9; ++q) xr[q] = Pc[ofs + (q - 1) * GS_HP + 2];                    // rows -1..7
+#pragma unroll
+        for (int r = 0; r < 8; r += 2) {
+            const double up0 = r == 0 ? t0 : x[0][r - 1], up1 = r == 0 ? t1 : x[1][r - 1];
+            const double v = fma(nxy, (up0 + x[0][r + 1]) + (xr[r] + xr[r + 2]), fma(nfy, up1 + x[1][r + 1], fma(nfx, x[0][r] + xr[r + 1], B[1][r])));
+            if (!MASKED) x[1][r] = v; else if ((act >> (8 + r)) & 1u) x[1][r] = ((dmask >> (8 + r)) & 1u) ? 0.0 : v;
+            Pc[GS_HALF + ofs + r * GS_HP + 1] = x[1][r];
+        }
+    }
+    __syncthreads();
+    // ---- colour 2: a = 0, r odd ----
+    if (on) {
+        double xl[9];
+#pragma unroll
+        for (int q = 0; q < 9; ++q) xl[q] = Pc[GS_HALF + ofs + q * GS_HP];                    // rows 0..8
+        d0 = Pc[ofs + 8 * GS_HP + 1]; d1 = Pc[GS_HALF + ofs + 8 * GS_HP + 1];
+#pragma unroll
+        for (int r = 1; r < 8; r += 2) {
+            const double dn0 = r == 7 ? d0 : x[0][r + 1], dn1 = r == 7 ? d1 : x[1][r + 1];
+            const double v = fma(nxy, (xl[r - 1] + xl[r + 1]) + (x[1][r - 1] + dn1), fma(nfy, x[0][r - 1] + dn0, fma(nfx, xl[r] + x[1][r], B[0][r])));
+            if (!MASKED) x[0][r] = v; else if ((act >> r) & 1u) x[0][r] = ((dmask >> r) & 1u) ? 0.0 : v;
+            Pc[ofs + r * GS_HP + 1] = x[0][r];
+        }
+    }
+    __syncthreads();
+    // ---- colour 3: a = 1, r odd ----
+    if (on) {
+        double xr[9];
+#pragma unroll
+        for (int q = 0; q < 9; ++q) xr[q] = Pc[ofs + q * GS_HP + 2];                          // rows 0..8
+#pragma unroll
+        for (int r = 1; r < 8; r += 2) {
+            const double dn0 = r == 7 ? d0 : x[0][r + 1], dn1 = r == 7 ? d1 : x[1][r + 1];
+            const double v = fma(nxy, (x[0][r - 1] + dn0) + (xr[r - 1] + xr[r + 1]), fma(nfy, x[1][r - 1] + dn1, fma(nfx, x[0][r] + xr[r], B[1][r])));
+            if (!MASKED) x[1][r] = v; else if ((act >> (8 + r)) & 1u) x[1][r] = ((dmask >> (8 + r)) & 1u) ? 0.0 : v;
+            Pc[GS_HALF + ofs + r * GS_HP + 1] = x[1][r];
+        }
+    }
+}
+
 template <bool CS>
 __global__ void __launch_bounds__(256, CS ? 2 : 1) k_gs2(LevelDev L, GsArgs A)
 {
@@ -345,6 +455,7 @@ __global__ void __launch_bounds__(256, CS ? 2 : 1) k_gs2(LevelDev L, GsArgs A)
     const int nkw = min(kb + zc - 1, L.n[2]) - kb + 1;   // written planes
     const int gi = i0 + 2 * lane, gj = j0 + 8 * wy;      // first node of this thread's 2 x 8 block
     const int row0 = 8 * wy + 1;                         // smem row of block row 0
+    const int ofs = row0 * GS_HP + lane;
 
     // per-thread node masks, bit a*8+r: relaxed (valid node), Dirichlet in x/y, written by this tile
     unsigned act = 0, dir = 0, wrt = 0;
@@ -359,19 +470,14 @@ __global__ void __launch_bounds__(256, CS ? 2 : 1) k_gs2(LevelDev L, GsArgs A)
             const bool w = v && (2 * lane + a < GS_WX) && (8 * wy + r < GS_WY);
             act |= (unsigned)v << (a * 8 + r); dir |= (unsigned)dd << (a * 8 + r); wrt |= (unsigned)w << (a * 8 + r);
         }
+    // whole tile inside the domain and no Dirichlet face anywhere: the colour steps need no masks
+    const bool any_dir = L.face[0] == NP_FACE_DIRICHLET || L.face[1] == NP_FACE_DIRICHLET || L.face[2] == NP_FACE_DIRICHLET
+                      || L.face[3] == NP_FACE_DIRICHLET || L.face[4] == NP_FACE_DIRICHLET || L.face[5] == NP_FACE_DIRICHLET;
+    const bool full = (i0 + GS_TX - 1 <= L.n[0]) && (j0 + GS_TY - 1 <= L.n[1]) && !any_dir;
 
+    GsLoader ld; ld.init(L, tid, i0, j0, A.zero_in != 0);
     auto slot = [&](int p) -> double* { return ring + ((p + 1) % GS_RING) * GS_PLANE; };     // p >= -1
-    auto load_plane = [&](int p) {                       // planes -1 .. nk (halo planes included)
-        double* dst = slot(p);
-        const long long kof = L.nsz * (long long)(kb + p + 1);
-        for (int e = tid; e < 34 * 66; e += 256) {
-            const int row = e / 66, g = e - row * 66 + 1;
-            const int i = i0 + g - 2, j = j0 + row - 1;
-            const bool valid = (i <= L.n[0] + 1 && j <= L.n[1] + 1) && !A.zero_in;
-            const double* src = valid ? xin + (kof + L.nsy * (long long)(j + 1) + (i + 1)) : xin;
-            np_cp_async8(dst + ((g & 1) ? GS_HALF : 0) + row * GS_HP + (g >> 1), src, valid);
-        }
-    };
+    auto load_plane = [&](int p) { ld.load(slot(p), xin + L.nsz * (long long)(kb + p + 1), L.nsy); };   // planes -1 .. nk
 
     load_plane(-1); load_plane(0); load_plane(1);
     np_cp_async_commit(); np_cp_async_wait_all();
@@ -393,20 +499,25 @@ __global__ void __launch_bounds__(256, CS ? 2 : 1) k_gs2(LevelDev L, GsArgs A)
         const bool zdir = on && ((L.face[2] == NP_FACE_DIRICHLET && k == 0) || (L.face[5] == NP_FACE_DIRICHLET && k == L.n[2]));
         const unsigned dmask = zdir ? act : dir;
         const long long gbase = on ? np_noff(L, gi, gj, k) : 0;
+        if (A.addto && on && grp == 1 && p < nkw) {     // the add-to values are needed at the end of the step: pull them into L1 now
+#pragma unroll
+            for (int r = 0; r < 8; ++r) np_prefetch_l1(A.addto + gbase + L.nsy * r);
+        }
 
         if (CS) {
             if (on) {
                 // ---- B = rhs/diag - (out-of-plane part): 9-point stencil of S = x[k-1] + x[k+1] ----
-                double rv[2][8];
+                double rv[2][8];                        // issued now, consumed after the stencil below
+                const double* rp = rhs + gbase;
 #pragma unroll
-                for (int a = 0; a < 2; ++a)
-#pragma unroll
-                    for (int r = 0; r < 8; ++r)
-                        rv[a][r] = ((act >> (a * 8 + r)) & 1u) ? rhs[gbase + a + L.nsy * r] - roff : 0.0;
+                for (int r = 0; r < 8; ++r) {
+                    rv[0][r] = (full || ((act >> r) & 1u)) ? rp[L.nsy * r] : roff;
+                    rv[1][r] = (full || ((act >> (8 + r)) & 1u)) ? rp[L.nsy * r + 1] : roff;
+                }
                 const double* Pm = slot(p - 1); const double* Pp = slot(p + 1);
 #pragma unroll
                 for (int rr = -1; rr <= 8; ++rr) {
-                    const int ro = (row0 + rr) * GS_HP + lane;
+                    const int ro = ofs + rr * GS_HP;
                     const double sL = Pm[GS_HALF + ro] + Pp[GS_HALF + ro];
                     const double s0 = Pm[ro + 1] + Pp[ro + 1];
                     const double s1 = Pm[GS_HALF + ro + 1] + Pp[GS_HALF + ro + 1];
@@ -414,86 +525,26 @@ __global__ void __launch_bounds__(256, CS ? 2 : 1) k_gs2(LevelDev L, GsArgs A)
                     const double h0 = sL + s1, h1 = s0 + sR;
                     const double q0 = C.a_eyz * s0 + C.a_c * h0, q1 = C.a_eyz * s1 + C.a_c * h1;
                     if (rr >= 0 && rr <= 7) {
-                        // row rr's own contribution; B[.][rr] already holds q of row rr-1 (set below)
+                        // row rr's own contribution; B[.][rr] already holds -q of row rr-1 (set below)
                         B[0][rr] -= C.a_fz * s0 + C.a_exz * h0;
                         B[1][rr] -= C.a_fz * s1 + C.a_exz * h1;
                     }
                     if (rr - 1 >= 0 && rr - 1 <= 7) { B[0][rr - 1] -= q0; B[1][rr - 1] -= q1; }
                     if (rr + 1 >= 0 && rr + 1 <= 7) { B[0][rr + 1] = -q0; B[1][rr + 1] = -q1; }   // first touch of row rr+1
                 }
-#pragma unroll
-                for (int a = 0; a < 2; ++a)
-#pragma unroll
-                    for (int r = 0; r < 8; ++r) B[a][r] = rv[a][r] * C.dinv + B[a][r];
                 // ---- own values of plane p ----
 #pragma unroll
                 for (int r = 0; r < 8; ++r) {
-                    x[0][r] = Pc[(row0 + r) * GS_HP + lane + 1];
-                    x[1][r] = Pc[GS_HALF + (row0 + r) * GS_HP + lane + 1];
+                    x[0][r] = Pc[ofs + r * GS_HP + 1];
+                    x[1][r] = Pc[GS_HALF + ofs + r * GS_HP + 1];
                 }
+#pragma unroll
+                for (int a = 0; a < 2; ++a)
+#pragma unroll
+                    for (int r = 0; r < 8; ++r) B[a][r] = fma(rv[a][r] - roff, C.dinv, B[a][r]);
             }
-            double t0 = 0.0, t1 = 0.0, d0 = 0.0, d1 = 0.0;
-            // ---- colour 0: a = 0, r even ----
-            if (on) {
-                double xl[9];
-#pragma unroll
-                for (int q = 0; q < 9; ++q) xl[q] = Pc[GS_HALF + (row0 - 1 + q) * GS_HP + lane];      // rows -1..7
-                t0 = Pc[(row0 - 1) * GS_HP + lane + 1]; t1 = Pc[GS_HALF + (row0 - 1) * GS_HP + lane + 1];
-#pragma unroll
-                for (int r = 0; r < 8; r += 2) {
-                    const double up0 = r == 0 ? t0 : x[0][r - 1], up1 = r == 0 ? t1 : x[1][r - 1];
-                    const double v = B[0][r] - (C.a_fx * (xl[r + 1] + x[1][r]) + C.a_fy * (up0 + x[0][r + 1])
-                                              + C.a_exy * ((xl[r] + xl[r + 2]) + (up1 + x[1][r + 1])));
-                    if ((act >> r) & 1u) x[0][r] = ((dmask >> r) & 1u) ? 0.0 : v;
-                    Pc[(row0 + r) * GS_HP + lane + 1] = x[0][r];
-                }
-            }
-            __syncthreads();
-            // ---- colour 1: a = 1, r even ----
-            if (on) {
-                double xr[9];
-#pragma unroll
-                for (int q = 0; q < 9; ++q) xr[q] = Pc[(row0 - 1 + q) * GS_HP + lane + 2];            // rows -1..7
-#pragma unroll
-                for (int r = 0; r < 8; r += 2) {
-                    const double up0 = r == 0 ? t0 : x[0][r - 1], up1 = r == 0 ? t1 : x[1][r - 1];
-                    const double v = B[1][r] - (C.a_fx * (x[0][r] + xr[r + 1]) + C.a_fy * (up1 + x[1][r + 1])
-                                              + C.a_exy * ((up0 + x[0][r + 1]) + (xr[r] + xr[r + 2])));
-                    if ((act >> (8 + r)) & 1u) x[1][r] = ((dmask >> (8 + r)) & 1u) ? 0.0 : v;
-                    Pc[GS_HALF + (row0 + r) * GS_HP + lane + 1] = x[1][r];
-                }
-            }
-            __syncthreads();
-            // ---- colour 2: a = 0, r odd ----
-            if (on) {
-                double xl[9];
-#pragma unroll
-                for (int q = 0; q < 9; ++q) xl[q] = Pc[GS_HALF + (row0 + q) * GS_HP + lane];          // rows 0..8
-                d0 = Pc[(row0 + 8) * GS_HP + lane + 1]; d1 = Pc[GS_HALF + (row0 + 8) * GS_HP + lane + 1];
-#pragma unroll
-                for (int r = 1; r < 8; r += 2) {
-                    const double dn0 = r == 7 ? d0 : x[0][r + 1], dn1 = r == 7 ? d1 : x[1][r + 1];
-                    const double v = B[0][r] - (C.a_fx * (xl[r] + x[1][r]) + C.a_fy * (x[0][r - 1] + dn0)
-                                              + C.a_exy * ((xl[r - 1] + xl[r + 1]) + (x[1][r - 1] + dn1)));
-                    if ((act >> r) & 1u) x[0][r] = ((dmask >> r) & 1u) ? 0.0 : v;
-                    Pc[(row0 + r) * GS_HP + lane + 1] = x[0][r];
-                }
-            }
-            __syncthreads();
-            // ---- colour 3: a = 1, r odd ----
-            if (on) {
-                double xr[9];
-#pragma unroll
-                for (int q = 0; q < 9; ++q) xr[q] = Pc[(row0 + q) * GS_HP + lane + 2];                // rows 0..8
-#pragma unroll
-                for (int r = 1; r < 8; r += 2) {
-                    const double dn0 = r == 7 ? d0 : x[0][r + 1], dn1 = r == 7 ? d1 : x[1][r + 1];
-                    const double v = B[1][r] - (C.a_fx * (x[0][r] + xr[r]) + C.a_fy * (x[1][r - 1] + dn1)
-                                              + C.a_exy * ((x[0][r - 1] + dn0) + (xr[r - 1] + xr[r + 1])));
-                    if ((act >> (8 + r)) & 1u) x[1][r] = ((dmask >> (8 + r)) & 1u) ? 0.0 : v;
-                    Pc[GS_HALF + (row0 + r) * GS_HP + lane + 1] = x[1][r];
-                }
-            }
+            if (full) gs_colours_cs<false>(on, x, B, Pc, C, ofs, act, dmask);
+            else      gs_colours_cs<true>(on, x, B, Pc, C, ofs, act, dmask);
         } else {
             // ---- variable sigma: every update gathers its 26 neighbours from the ring and its 8 cells from L1/L2 ----
             const double* Pm = on ? slot(p - 1) : ring; const double* Pp = on ? slot(p + 1) : ring;
@@ -523,14 +574,27 @@ __global__ void __launch_bounds__(256, CS ? 2 : 1) k_gs2(LevelDev L, GsArgs A)
         np_cp_async_wait_all();
         __syncthreads();
         if (on && grp == 1 && p < nkw) {
+            double* op = xout + gbase;
+            if (A.addto) {
+                const double* ap = A.addto + gbase;
+                double av[2][8];
 #pragma unroll
-            for (int a = 0; a < 2; ++a)
+                for (int r = 0; r < 8; ++r) {
+                    av[0][r] = ((wrt >> r) & 1u) ? ap[L.nsy * r] : 0.0;
+                    av[1][r] = ((wrt >> (8 + r)) & 1u) ? ap[L.nsy * r + 1] : 0.0;
+                }
 #pragma unroll
-                for (int r = 0; r < 8; ++r)
-                    if ((wrt >> (a * 8 + r)) & 1u) {
-                        const long long o = gbase + a + L.nsy * r;
-                        xout[o] = A.addto ? A.addto[o] + x[a][r] : x[a][r];
-                    }
+                for (int r = 0; r < 8; ++r) {
+                    if ((wrt >> r) & 1u) op[L.nsy * r] = av[0][r] + x[0][r];
+                    if ((wrt >> (8 + r)) & 1u) op[L.nsy * r + 1] = av[1][r] + x[1][r];
+                }
+            } else {
+#pragma unroll
+                for (int r = 0; r < 8; ++r) {
+                    if ((wrt >> r) & 1u) op[L.nsy * r] = x[0][r];
+                    if ((wrt >> (8 + r)) & 1u) op[L.nsy * r + 1] = x[1][r];
+                }
+            }
         }
     }
 }
@@ -583,17 +647,8 @@ __global__ void __launch_bounds__(256, 2) k_stencil_cs(LevelDev L, StCoef C, dou
             wgt[a][r] = w;
         }
 
-    auto load_plane = [&](int k) {                       // global plane k in [-1, n2+1]
-        double* dst = ring + ((k + 1) % ST_RING) * GS_PLANE;
-        const long long kof = L.nsz * (long long)(k + 1);
-        for (int e = tid; e < 34 * 66; e += 256) {
-            const int row = e / 66, g = e - row * 66 + 1;
-            const int i = i0 + g - 2, j = j0 + row - 1;
-            const bool valid = (i <= L.n[0] + 1 && j <= L.n[1] + 1);
-            const double* src = valid ? x + (kof + L.nsy * (long long)(j + 1) + (i + 1)) : x;
-            np_cp_async8(dst + ((g & 1) ? GS_HALF : 0) + row * GS_HP + (g >> 1), src, valid);
-        }
-    };
+    GsLoader ld; ld.init(L, tid, i0, j0, false);
+    auto load_plane = [&](int k) { ld.load(ring + ((k + 1) % ST_RING) * GS_PLANE, x + L.nsz * (long long)(k + 1), L.nsy); };   // k in [-1, n2+1]
 
     double Vm[2][4], Vc[2][4], Uc[2][4];
 #pragma unroll
@@ -614,6 +669,16 @@ __global__ void __launch_bounds__(256, 2) k_stencil_cs(LevelDev L, StCoef C, dou
         if (s + 2 <= nkl + 1) load_plane(q + 2);         // goes into the slot of plane q-1
         np_cp_async_commit();
         const double* P = ring + ((q + 1) % ST_RING) * GS_PLANE;
+        // right-hand side of the plane written this step: issued before the shared-memory work, used after it
+        double bv[2][4];
+        const long long gbase = np_noff(L, gi, gj, q - 1);
+        if (MODE == 1 && s >= 2) {
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                bv[0][r] = ((act >> r) & 1u) ? b[gbase + L.nsy * r] : 0.0;
+                bv[1][r] = ((act >> (4 + r)) & 1u) ? b[gbase + L.nsy * r + 1] : 0.0;
+            }
+        }
         double c0[6], c1[6], h0[6], h1[6];
 #pragma unroll
         for (int rr = 0; rr < 6; ++rr) {
@@ -638,7 +703,6 @@ __global__ void __launch_bounds__(256, 2) k_stencil_cs(LevelDev L, StCoef C, dou
                 if (k > L.owned_hi[2]) wz = 0.0;
                 if ((L.face[2] == NP_FACE_NEUMANN && k == 0) || (L.face[5] == NP_FACE_NEUMANN && k == L.n[2])) wz *= 0.5;
             }
-            const long long gbase = np_noff(L, gi, gj, k);
 #pragma unroll
             for (int a = 0; a < 2; ++a)
 #pragma unroll
@@ -648,7 +712,7 @@ __global__ void __launch_bounds__(256, 2) k_stencil_cs(LevelDev L, StCoef C, dou
                         double v = 0.0;
                         if (!(zdir || ((dir >> (a * 4 + r)) & 1u))) {
                             const double ax = Uc[a][r] + (Vm[a][r] + Vn[a][r]);
-                            v = (MODE == 1) ? (b[o] - off) - ax : ax;
+                            v = (MODE == 1) ? (bv[a][r] - off) - ax : ax;
                         }
                         y[o] = v;
                         if (REDUCE) { tmax = fmax(tmax, fabs(v)); tsum += (wgt[a][r] * wz) * v; }
