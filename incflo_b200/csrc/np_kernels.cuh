@@ -820,6 +820,57 @@ __global__ void __launch_bounds__(256) k_interp_add(LevelDev Lf, LevelDev Lc, do
     fine[np_noff(Lf, i, j, k)] += v;
 }
 
+// K5, plain trilinear (constant sigma, or interp_sigma_weighted = 0): one thread per COARSE node (I,J,K) updates the
+// 2x2x2 fine nodes (2I-1..2I, 2J-1..2J, 2K-1..2K) from the coarse nodes (I-1..I, J-1..J, K-1..K); fine pairs in x are
+// 16-byte aligned in the padded layout (node i at offset i+1), so each row is one 128-bit read-modify-write.
+__global__ void __launch_bounds__(256) k_interp_add_tri(LevelDev Lf, LevelDev Lc, double* __restrict__ fine, const double* __restrict__ crse, int koffc)
+{
+    const int I = blockIdx.x * blockDim.x + threadIdx.x;
+    const int J = blockIdx.y * blockDim.y + threadIdx.y;
+    const int K = blockIdx.z;
+    if (I > Lc.n[0] || J > Lc.n[1]) return;
+    const double* c = crse + np_noff(Lc, I, J, K + koffc);
+    const long long cy = Lc.nsy, cz = Lc.nsz;
+    double px[2][2][2];                    // [dz][dy][a]: interpolated in x
+#pragma unroll
+    for (int dz = 0; dz < 2; ++dz)
+#pragma unroll
+        for (int dy = 0; dy < 2; ++dy) {
+            const double lo = c[-1 + cy * (dy - 1) + cz * (dz - 1)], hi = c[cy * (dy - 1) + cz * (dz - 1)];
+            px[dz][dy][0] = 0.5 * (lo + hi); px[dz][dy][1] = hi;
+        }
+    const bool xdir_lo = (Lf.face[0] == NP_FACE_DIRICHLET), xdir_hi = (Lf.face[3] == NP_FACE_DIRICHLET);
+#pragma unroll
+    for (int cc = 0; cc < 2; ++cc) {
+        const int fk = 2 * K - 1 + cc;
+        if (fk < 0) continue;
+        if ((Lf.face[2] == NP_FACE_DIRICHLET && fk == 0) || (Lf.face[5] == NP_FACE_DIRICHLET && fk == Lf.n[2])) continue;
+#pragma unroll
+        for (int bb = 0; bb < 2; ++bb) {
+            const int fj = 2 * J - 1 + bb;
+            if (fj < 0) continue;
+            if ((Lf.face[1] == NP_FACE_DIRICHLET && fj == 0) || (Lf.face[4] == NP_FACE_DIRICHLET && fj == Lf.n[1])) continue;
+            double v[2];
+#pragma unroll
+            for (int a = 0; a < 2; ++a) {
+                const double y0 = bb ? px[0][1][a] : 0.5 * (px[0][0][a] + px[0][1][a]);
+                const double y1 = bb ? px[1][1][a] : 0.5 * (px[1][0][a] + px[1][1][a]);
+                v[a] = cc ? y1 : 0.5 * (y0 + y1);
+            }
+            double* fp = fine + np_noff(Lf, 2 * I - 1, fj, fk);       // offset 2I: 16-byte aligned
+            const bool w0 = (I > 0), w1 = !((xdir_lo && I == 0) || (xdir_hi && 2 * I == Lf.n[0]));
+            if (w0 && w1) {
+                double2 f2 = *reinterpret_cast<double2*>(fp);
+                f2.x += v[0]; f2.y += v[1];
+                *reinterpret_cast<double2*>(fp) = f2;
+            } else {
+                if (w0) fp[0] += v[0];
+                if (w1) fp[1] += v[1];
+            }
+        }
+    }
+}
+
 // ------------------------------------------------------------------------------------------------
 // K8: sigma coarsening (arithmetic mean of the 8 children), interior cells only
 // ------------------------------------------------------------------------------------------------
