@@ -1,0 +1,128 @@
+"""N > 1 host logic on CPU: two ranks (processes) drive the emulation build of the product sources, with the
+halo exchange / allreduce / allgather callbacks carried by torch.distributed (gloo).  Checks the z-slab
+partition, the slab halo exchange, owner / duplicate handling on the shared plane, the replicated coarse
+levels and the reductions against the single-process oracle run on the same two boxes.
+"""
+import ctypes as C
+import os
+import socket
+
+import numpy as np
+import pytest
+
+import nphelp
+from incflo_b200 import problems
+
+BIG = 1 << 30
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, name, ncell, kw, agg_min, outdir):
+    import torch
+    import torch.distributed as dist
+    from incflo_b200.projector import Fab, Geometry, LPInfo, NodalProjector
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    L = nphelp.emu_lib()
+
+    def view(ptr, n):
+        return torch.from_numpy(np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_double)), shape=(n,)))
+
+    SR = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_longlong, C.c_void_p, C.c_longlong, C.c_void_p, C.c_longlong, C.c_void_p,
+                     C.c_longlong, C.c_int, C.c_int)
+    AR = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.c_int)
+    AG = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_longlong)
+
+    def sendrecv(slo, nslo, rlo, nrlo, shi, nshi, rhi, nrhi, lo, hi):
+        reqs = []
+        if lo >= 0:   # "down" messages carry tag 1, "up" messages tag 2
+            reqs.append(dist.isend(view(slo, nslo).clone(), lo, tag=1))
+            reqs.append(dist.irecv(view(rlo, nrlo), lo, tag=2))
+        if hi >= 0:
+            reqs.append(dist.isend(view(shi, nshi).clone(), hi, tag=2))
+            reqs.append(dist.irecv(view(rhi, nrhi), hi, tag=1))
+        for r in reqs:
+            r.wait()
+        return 0
+
+    def allreduce(buf, n, op):
+        t = view(buf, n)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX if op == 1 else dist.ReduceOp.SUM)
+        return 0
+
+    def allgather(send, recv, cnt):
+        out = view(recv, cnt * world)
+        dist.all_gather_into_tensor(out, view(send, cnt).clone())
+        return 0
+
+    cbs = (SR(sendrecv), AR(allreduce), AG(allgather))
+    L.np_emu_set_comm.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    L.np_emu_set_comm(C.cast(cbs[0], C.c_void_p), C.cast(cbs[1], C.c_void_p), C.cast(cbs[2], C.c_void_p))
+
+    nzl = ncell[2] // world
+    prob = problems.PROBLEMS[name](ncell, **kw)
+    sl = slice(rank * nzl, (rank + 1) * nzl)
+    vel = Fab.from_array(prob["vel"][:, sl], 1)
+    sig = Fab.from_array(prob["sigma"][sl], 0)
+    geom = Geometry(ncell, prob["prob_lo"], prob["prob_hi"], [b == 0 for b in prob["bclo"]])
+    boxes = [((0, 0, r * nzl), (ncell[0] - 1, ncell[1] - 1, (r + 1) * nzl - 1)) for r in range(world)]
+    P = NodalProjector(vel, sig, geom, LPInfo(), boxes=boxes, rank=rank, nranks=world, nccl_comm=1, lib=L,
+                       agg_min_local_nz=agg_min)
+    P.setDomainBC(prob["bclo"], prob["bchi"])
+    st = P.project(1e-11, 1e-14)
+    np.savez(os.path.join(outdir, f"r{rank}.npz"), u=vel.numpy_valid(), phi=P.getPhi().numpy_valid()[0],
+             gp=P.getGradPhi().numpy_valid(), vc=st.n_vcycles, nlev=st.n_levels, bot=st.bottom_iters_total,
+             hist=np.array([st.res_history[i] for i in range(st.n_vcycles)]),
+             levels=np.array([P.level_ncell(l) for l in range(P.num_levels)]))
+    P.close()
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("name,ncell,kw,agg_min,agg_level", [
+    ("double_shear", (16, 16, 64), dict(zwave=True, prob_hi=(1.0, 1.0, 4.0)), 16, 2),
+    ("rayleigh_taylor", (16, 16, 32), {}, 4, 3),
+])
+def test_two_ranks_match_oracle(tmp_path, name, ncell, kw, agg_min, agg_level):
+    import torch.multiprocessing as mp
+    from oracle.oracle import Oracle, TILED
+
+    nphelp.emu_lib()           # build once, before the ranks start
+    world = 2
+    mp.spawn(_worker, args=(world, _free_port(), name, ncell, kw, agg_min, str(tmp_path)), nprocs=world, join=True)
+    r = [np.load(tmp_path / f"r{k}.npz") for k in range(world)]
+    nzl = ncell[2] // world
+
+    prob = problems.PROBLEMS[name](ncell, **kw)
+    boxes = [[0, 0, k * nzl, ncell[0] - 1, ncell[1] - 1, (k + 1) * nzl - 1] for k in range(world)]
+    o = Oracle(ncell, prob["prob_lo"], prob["prob_hi"], prob["bclo"], prob["bchi"], boxes=boxes, smoother=TILED,
+               tile=(63, 31, BIG), tile_z_target=-1, agg_level=agg_level)
+    o.set_sigma(prob["sigma"])
+    o.set_vel(prob["vel"])
+    so = o.project(1e-11, 1e-14)
+
+    def l2(a, b):
+        return np.linalg.norm(a - b) / np.linalg.norm(b)
+
+    assert int(r[0]["vc"]) == int(r[1]["vc"]) == so.n_vcycles
+    assert int(r[0]["nlev"]) == so.n_levels
+    # level agg_level is the first whole-domain (replicated) level on the ranks
+    assert r[0]["levels"][agg_level][2] == ncell[2] >> agg_level and r[0]["levels"][agg_level - 1][2] == nzl >> (agg_level - 1)
+    for i in range(so.n_vcycles):
+        assert abs(r[0]["hist"][i] - so.res_history[i]) <= 1e-6 * so.res_history[i] + 1e-14 * so.rhs_norm0
+    u = np.concatenate([r[k]["u"] for k in range(world)], axis=1)
+    gp = np.concatenate([r[k]["gp"] for k in range(world)], axis=1)
+    phi = np.concatenate([r[0]["phi"][:-1], r[1]["phi"]], axis=0)      # the shared plane is duplicated
+    assert np.abs(r[0]["phi"][-1] - r[1]["phi"][0]).max() <= 1e-14 * np.abs(phi).max()
+    assert l2(u, o.get_vel()) < 1e-11 and l2(gp, o.get_gradphi()) < 1e-10
+    po = o.get_phi()
+    assert l2(phi - phi.mean(), po - po.mean()) < 1e-10
