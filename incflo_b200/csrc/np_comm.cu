@@ -56,15 +56,13 @@ int nccl_sendrecv(void* ctx, const double* send_lo, long long nsend_lo, double* 
 {
     NcclApi& N = nccl();
     ncclComm_t comm = (ncclComm_t)ctx; cudaStream_t st = (cudaStream_t)stream;
+    // Order matters when lo_rank == hi_rank (two ranks, periodic): NCCL matches the sends and receives of one
+    // peer pair in issue order, so both sides send [down, up] and receive [from above, from below].
     ncclResult_t rc = N.GroupStart();
-    if (lo_rank >= 0) {
-        if (rc == ncclSuccess_) rc = N.Send(send_lo, (size_t)nsend_lo, ncclFloat64_, lo_rank, comm, st);
-        if (rc == ncclSuccess_) rc = N.Recv(recv_lo, (size_t)nrecv_lo, ncclFloat64_, lo_rank, comm, st);
-    }
-    if (hi_rank >= 0) {
-        if (rc == ncclSuccess_) rc = N.Send(send_hi, (size_t)nsend_hi, ncclFloat64_, hi_rank, comm, st);
-        if (rc == ncclSuccess_) rc = N.Recv(recv_hi, (size_t)nrecv_hi, ncclFloat64_, hi_rank, comm, st);
-    }
+    if (lo_rank >= 0 && rc == ncclSuccess_) rc = N.Send(send_lo, (size_t)nsend_lo, ncclFloat64_, lo_rank, comm, st);
+    if (hi_rank >= 0 && rc == ncclSuccess_) rc = N.Send(send_hi, (size_t)nsend_hi, ncclFloat64_, hi_rank, comm, st);
+    if (hi_rank >= 0 && rc == ncclSuccess_) rc = N.Recv(recv_hi, (size_t)nrecv_hi, ncclFloat64_, hi_rank, comm, st);
+    if (lo_rank >= 0 && rc == ncclSuccess_) rc = N.Recv(recv_lo, (size_t)nrecv_lo, ncclFloat64_, lo_rank, comm, st);
     ncclResult_t rc2 = N.GroupEnd();
     return (rc == ncclSuccess_ && rc2 == ncclSuccess_) ? 0 : 1;
 }
