@@ -1,0 +1,63 @@
+"""The C++ shim (include/NodalProjectorB200.H) driven the way incflo::ApplyProjection drives amrex::NodalProjector,
+compiled against the mock AMReX types (AMReX itself is unavailable here) and linked with
+  * the emulation build of the C ABI on CPU, or
+  * libnodalproj.so on the GPU box (host fabs -> staged inside np_project),
+then compared with the oracle."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import nphelp
+from incflo_b200 import capi, problems
+from oracle.oracle import Oracle, TILED
+
+ROOT = nphelp.ROOT
+
+
+def _build(libpath, exe):
+    libdir, libname = os.path.dirname(libpath), os.path.basename(libpath)[3:-3]
+    subprocess.check_call(["g++", "-std=c++17", "-O1", "-I" + os.path.join(ROOT, "include"), "-I" + os.path.join(ROOT, "tests", "mock_amrex"),
+                           os.path.join(ROOT, "tests", "shim", "shim_driver.cpp"), "-o", exe, "-L" + libdir, "-l" + libname,
+                           "-Wl,-rpath," + libdir])
+
+
+def _run_and_check(libpath, tmp_path, n):
+    exe = str(tmp_path / "shim_driver")
+    out = str(tmp_path / "out.bin")
+    _build(libpath, exe)
+    subprocess.check_call([exe, str(n), out])
+    raw = np.fromfile(out, dtype=np.uint8)
+    hdr = raw[:8].view(np.int32)
+    body = raw[8:].view(np.float64)
+    nc, nn = n ** 3, (n + 1) ** 3
+    u = body[:3 * nc].reshape(3, n, n, n)
+    phi = body[3 * nc:3 * nc + nn].reshape(n + 1, n + 1, n + 1)
+    gp = body[3 * nc + nn:].reshape(3, n, n, n)
+    prob = problems.taylor_green((n, n, n))
+    o = Oracle((n, n, n), smoother=TILED, tile=(63, 31, 1 << 30), tile_z_target=-1)
+    o.set_sigma(prob["sigma"]); o.set_vel(prob["vel"])
+    so = o.project(1e-11, 1e-14)
+    l2 = lambda a, b: np.linalg.norm(a - b) / np.linalg.norm(b)
+    assert hdr[0] == n and hdr[1] == so.n_vcycles
+    po = o.get_phi()
+    assert l2(u, o.get_vel()) < 1e-11 and l2(gp, o.get_gradphi()) < 1e-10 and l2(phi - phi.mean(), po - po.mean()) < 1e-10
+
+
+def test_shim_on_emulation(tmp_path):
+    nphelp.emu_lib()
+    _run_and_check(nphelp.EMU_LIB, tmp_path, 16)
+
+
+@pytest.mark.gpu
+def test_shim_on_gpu(tmp_path):
+    _run_and_check(capi.LIB_PATH, tmp_path, 32)
+
+
+def test_shim_abort_on_mlmg_failure(tmp_path):
+    nphelp.emu_lib()
+    exe = str(tmp_path / "shim_driver")
+    _build(nphelp.EMU_LIB, exe)
+    p = subprocess.run([exe, "16", str(tmp_path / "o.bin"), "1"], capture_output=True, text=True)
+    assert p.returncode == 3 and "MLMG failed to converge" in p.stderr
