@@ -64,39 +64,46 @@ int np_get_gradphi(np_handle* h, int local_box, np_fab* out)
     return NP_OK;
 }
 
-// copy internal results into a caller fab (host or device, any ngrow): interior (+ min(ngrow,1) ghosts)
+// copy internal results into a caller fab (host or device, any ngrow): interior (+ min(ngrow,1) ghosts).
+// Host destination: a fab with ngrow == 1 has exactly the internal layout -> one device-to-host copy; any other
+// ngrow is repacked on the device into the persistent staging buffer first.
+static int copy_out(NpSolver& S, np_fab* dst, const double* src_fab1, bool nodal, int ncomp)
+{
+    const LevelDev& d = S.lev[0].d;
+    FabView v = nodal ? S.view_nodal(*dst, 0) : S.view_cell(*dst, 0, ncomp);
+    const long long nelem = v.sn * ncomp;
+    bool host = false;
+#ifndef NP_EMU
+    host = !np_rt::is_device_ptr(dst->p);
+#endif
+    if (host && dst->ngrow == 1) {
+        np_rt::copy_async(dst->p, src_fab1, (size_t)nelem * sizeof(double), S.stream);
+        np_rt::stream_sync(S.stream);
+        return np_rt::last_error() ? NP_ERR_CUDA : NP_OK;
+    }
+    double* dev = dst->p;
+    if (host && !(dev = S.stage_get(2, nelem))) return NP_ERR_CUDA;
+    v.p = dev;
+    const int g = dst->ngrow > 0 ? 1 : 0;
+    const int off = nodal ? 1 : 0;
+    FabView sv; sv.p = const_cast<double*>(src_fab1); sv.ng = 1; sv.sy = d.n[0] + off + 2; sv.sz = sv.sy * (d.n[1] + off + 2); sv.sn = sv.sz * (d.n[2] + off + 2);
+    NP_LAUNCH(false, k_copy_cell, dim3((d.n[0] + off + 2*g + 31) / 32, (d.n[1] + off + 2*g + 7) / 8, d.n[2] + off + 2*g), NP_BLK, 0, S.stream,
+              d.n[0] + off, d.n[1] + off, v, sv, ncomp, g);
+    if (host) np_rt::copy_async(dst->p, dev, (size_t)nelem * sizeof(double), S.stream);
+    np_rt::stream_sync(S.stream);
+    return np_rt::last_error() ? NP_ERR_CUDA : NP_OK;
+}
 int np_copy_phi(np_handle* h, int local_box, np_fab* dst)
 {
     if (!h || local_box != 0 || !dst || !dst->p) return NP_ERR_INVALID;
-    NpSolver& S = h->S;
-    if (!S.have_result) return NP_ERR_STATE;
-    const LevelDev& d = S.lev[0].d;
-    FabView v = S.view_nodal(*dst, 0);
-    double* dev; bool staged;
-    if (S.import_fab(*dst, v.sn, &dev, &staged)) return NP_ERR_CUDA;
-    v.p = dev;
-    const int g = dst->ngrow > 0 ? 1 : 0;
-    NP_LAUNCH(false, (k_copy_nodal<true>), dim3((d.n[0] + 1 + 2*g + 31) / 32, (d.n[1] + 1 + 2*g + 7) / 8, d.n[2] + 1 + 2*g), NP_BLK, 0, S.stream, d, S.sol, v, g);
-    S.export_fab(*dst, v.sn, dev, staged);
-    np_rt::stream_sync(S.stream);
-    return NP_OK;
+    if (!h->S.have_result) return NP_ERR_STATE;
+    return copy_out(h->S, dst, h->S.phi_out, true, 1);
 }
 int np_copy_gradphi(np_handle* h, int local_box, np_fab* dst)
 {
     if (!h || local_box != 0 || !dst || !dst->p || dst->ncomp < 3) return NP_ERR_INVALID;
-    NpSolver& S = h->S;
-    if (!S.have_result) return NP_ERR_STATE;
-    const LevelDev& d = S.lev[0].d;
-    FabView v = S.view_cell(*dst, 0, 3);
-    double* dev; bool staged;
-    if (S.import_fab(*dst, v.sn * 3, &dev, &staged)) return NP_ERR_CUDA;
-    v.p = dev;
-    FabView gv; gv.p = S.gphi; gv.ng = 1; gv.sy = d.n[0] + 2; gv.sz = gv.sy * (d.n[1] + 2); gv.sn = gv.sz * (d.n[2] + 2);
-    const int g = dst->ngrow > 0 ? 1 : 0;
-    NP_LAUNCH(false, k_copy_cell, dim3((d.n[0] + 2*g + 31) / 32, (d.n[1] + 2*g + 7) / 8, d.n[2] + 2*g), NP_BLK, 0, S.stream, d.n[0], d.n[1], v, gv, 3, g);
-    S.export_fab(*dst, v.sn * 3, dev, staged);
-    np_rt::stream_sync(S.stream);
-    return NP_OK;
+    if (!h->S.have_result) return NP_ERR_STATE;
+    return copy_out(h->S, dst, h->S.gphi, false, 3);
 }
 
 void np_destroy(np_handle* h) { if (h) { h->S.destroy(); delete h; } }

@@ -130,7 +130,7 @@ int np_divu(np_handle* h, const np_fab* vel, np_fab* rhs)
     uv.p = dev;
     // same two launches project() uses
     np_fill_cell3(S, uv);
-    NP_LAUNCH(false, k_divu, grid_nodes(S.lev[0].d), NP_BLK, 0, S.stream, S.lev[0].d, S.rhs, uv);
+    NP_LAUNCH(true, (k_divu<false>), grid_nodes(S.lev[0].d), NP_BLK, 0, S.stream, S.lev[0].d, S.rhs, uv, S.part1);
     np_rt::stream_sync(S.stream);
     if (staged) np_rt::dev_free(dev);
     return fab_out(S, 0, S.rhs, rhs);

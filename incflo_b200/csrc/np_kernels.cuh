@@ -311,6 +311,16 @@ __device__ __forceinline__ void np_prefetch_l1(const void* p)
     asm volatile("prefetch.global.L1 [%0];\n" :: "l"(p));
 #endif
 }
+// barrier among the 128 threads of one warp group (named barrier 1 + grp); the emulation's barrier is CTA-wide
+__device__ __forceinline__ void np_group_barrier(int grp)
+{
+#ifdef NP_EMU
+    __syncthreads();
+#else
+    if (grp == 0) asm volatile("bar.sync 1, 128;\n" ::: "memory");
+    else          asm volatile("bar.sync 2, 128;\n" ::: "memory");
+#endif
+}
 __device__ __forceinline__ void np_cp_async_commit()
 {
 #ifndef NP_EMU
@@ -373,7 +383,7 @@ struct GsLoader {
 // nodes outside the domain or on Dirichlet faces, which keep their value / are set to zero.
 template <bool MASKED>
 __device__ __forceinline__ void gs_colours_cs(bool on, double (&x)[2][8], const double (&B)[2][8], double* Pc, const GsCoef& C,
-                                              int ofs, unsigned act, unsigned dmask)
+                                              int ofs, unsigned act, unsigned dmask, int grp)
 {
     // ofs = row0 * GS_HP + lane: (row r, own even column) is Pc[ofs + r*GS_HP + 1], own odd column adds GS_HALF,
     // left halo column Pc[GS_HALF + ofs + r*GS_HP], right halo column Pc[ofs + r*GS_HP + 2]
@@ -393,7 +403,7 @@ __device__ __forceinline__ void gs_colours_cs(bool on, double (&x)[2][8], const 
             Pc[ofs + r * GS_HP + 1] = x[0][r];
         }
     }
-    __syncthreads();
+    np_group_barrier(grp);   // only this sweep's warps exchange values inside a plane
     // ---- colour 1: a = 1, r even ----
     if (on) {
         double xr[9];
@@ -407,7 +417,7 @@ __device__ __forceinline__ void gs_colours_cs(bool on, double (&x)[2][8], const 
             Pc[GS_HALF + ofs + r * GS_HP + 1] = x[1][r];
         }
     }
-    __syncthreads();
+    np_group_barrier(grp);   // only this sweep's warps exchange values inside a plane
     // ---- colour 2: a = 0, r odd ----
     if (on) {
         double xl[9];
@@ -422,7 +432,7 @@ __device__ __forceinline__ void gs_colours_cs(bool on, double (&x)[2][8], const 
             Pc[ofs + r * GS_HP + 1] = x[0][r];
         }
     }
-    __syncthreads();
+    np_group_barrier(grp);   // only this sweep's warps exchange values inside a plane
     // ---- colour 3: a = 1, r odd ----
     if (on) {
         double xr[9];
@@ -543,8 +553,8 @@ __global__ void __launch_bounds__(256, CS ? 2 : 1) k_gs2(LevelDev L, GsArgs A)
 #pragma unroll
                     for (int r = 0; r < 8; ++r) B[a][r] = fma(rv[a][r] - roff, C.dinv, B[a][r]);
             }
-            if (full) gs_colours_cs<false>(on, x, B, Pc, C, ofs, act, dmask);
-            else      gs_colours_cs<true>(on, x, B, Pc, C, ofs, act, dmask);
+            if (full) gs_colours_cs<false>(on, x, B, Pc, C, ofs, act, dmask, grp);
+            else      gs_colours_cs<true>(on, x, B, Pc, C, ofs, act, dmask, grp);
         } else {
             // ---- variable sigma: every update gathers its 26 neighbours from the ring and its 8 cells from L1/L2 ----
             const double* Pm = on ? slot(p - 1) : ring; const double* Pp = on ? slot(p + 1) : ring;
@@ -935,34 +945,77 @@ __global__ void __launch_bounds__(256) k_fill_vel(LevelDev L, FabView u, int per
 // ------------------------------------------------------------------------------------------------
 // K1: rhs = div(u) at valid nodes, with the Neumann conventions of mlndlap_divu / impose_neumann_bc
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_divu(LevelDev L, double* __restrict__ rhs, FabView u)
+template <bool WSUM>
+__global__ void __launch_bounds__(256) k_divu(LevelDev L, double* __restrict__ rhs, FabView u, double* __restrict__ part_sum)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    const bool inside = (i <= L.n[0] && j <= L.n[1]);
+    double tsum = 0.0;
+    // each block walks the planes k = blockIdx.z, blockIdx.z + gridDim.z, ... so the solvability sum needs few partials
+    for (int k = blockIdx.z; k <= L.n[2]; k += gridDim.z) {
+        if (!inside) continue;
+        double acc = 0.0;
+        if (!np_is_dirichlet(L, i, j, k)) {
+            // z?lo / z?hi: weight of the cells on the low / high side of the node (0 outside a Neumann wall)
+            const double zxl = (L.face[0] == NP_FACE_NEUMANN && i == 0) ? 0.0 : 1.0, zxh = (L.face[3] == NP_FACE_NEUMANN && i == L.n[0]) ? 0.0 : 1.0;
+            const double zyl = (L.face[1] == NP_FACE_NEUMANN && j == 0) ? 0.0 : 1.0, zyh = (L.face[4] == NP_FACE_NEUMANN && j == L.n[1]) ? 0.0 : 1.0;
+            const double zzl = (L.face[2] == NP_FACE_NEUMANN && k == 0) ? 0.0 : 1.0, zzh = (L.face[5] == NP_FACE_NEUMANN && k == L.n[2]) ? 0.0 : 1.0;
+            const double* p = u.p + np_foff(u, i, j, k, 0);
+            const long long y = u.sy, z = u.sz;
+            const double* ux = p; const double* uy = p + u.sn; const double* uz = p + 2 * u.sn;
+            // cells (a,b,c), a,b,c in {-1,0}: offset a + y*b + z*c
+            double sx = zyl*zzl*(ux[-y-z] - ux[-1-y-z]) + zyh*zzl*(ux[-z] - ux[-1-z]) + zyl*zzh*(ux[-y] - ux[-1-y]) + zyh*zzh*(ux[0] - ux[-1]);
+            double sy_ = zxl*zzl*(uy[-1-z] - uy[-1-y-z]) + zxh*zzl*(uy[-z] - uy[-y-z]) + zxl*zzh*(uy[-1] - uy[-1-y]) + zxh*zzh*(uy[0] - uy[-y]);
+            double sz_ = zxl*zyl*(uz[-1-y] - uz[-1-y-z]) + zxh*zyl*(uz[-y] - uz[-y-z]) + zxl*zyh*(uz[-1] - uz[-1-z]) + zxh*zyh*(uz[0] - uz[-z]);
+            acc = 0.25 * (L.dxinv[0] * sx + L.dxinv[1] * sy_ + L.dxinv[2] * sz_);
+            if (zxl == 0.0) acc *= 2.0;
+            if (zxh == 0.0) acc *= 2.0;
+            if (zyl == 0.0) acc *= 2.0;
+            if (zyh == 0.0) acc *= 2.0;
+            if (zzl == 0.0) acc *= 2.0;
+            if (zzh == 0.0) acc *= 2.0;
+        }
+        rhs[np_noff(L, i, j, k)] = acc;
+        if (WSUM && i <= L.owned_hi[0] && j <= L.owned_hi[1] && k <= L.owned_hi[2]) tsum += np_neumann_weight(L, i, j, k) * acc;
+    }
+    if (WSUM) {
+        const double sm = np_block_reduce<false>(tsum);
+        if (threadIdx.x == 0 && threadIdx.y == 0)
+            part_sum[blockIdx.x + gridDim.x * (blockIdx.y + (long long)gridDim.y * blockIdx.z)] = sm;
+    }
+}
+// scal[slot_off] = sum(part) / wtot (single rank), scal[slot_sum] = sum(part): the offset that makes rhs solvable
+__global__ void __launch_bounds__(1024) k_reduce_sum_off(const double* __restrict__ part, long long n, double* scal, int slot_sum, int slot_off, double wtot)
+{
+    double sm = 0.0;
+    for (long long t = threadIdx.x; t < n; t += blockDim.x) sm += part[t];
+    sm = np_block_reduce<false>(sm);
+    if (threadIdx.x == 0) { scal[slot_sum] = sm; scal[slot_off] = sm / wtot; }
+}
+__global__ void k_div_scalar(double* scal, int slot_sum, int slot_off, double wtot) { if (threadIdx.x == 0 && blockIdx.x == 0) scal[slot_off] = scal[slot_sum] / wtot; }
+
+// min / max of the caller's sigma fab (valid cells), plane-strided so that few partials remain
+__global__ void __launch_bounds__(256) k_minmax_cell(int n0, int n1, int n2, FabView src, double* __restrict__ bmin, double* __restrict__ bmax)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    double mx = -1e300, mn = 1e300;
+    if (i < n0 && j < n1)
+        for (int k = blockIdx.z; k < n2; k += gridDim.z) { const double v = src.p[np_foff(src, i, j, k, 0)]; mx = fmax(mx, v); mn = fmin(mn, v); }
+    mx = np_block_reduce<true>(mx);
+    mn = -np_block_reduce<true>(-mn);
+    if (threadIdx.x == 0 && threadIdx.y == 0) {
+        const long long bidx = blockIdx.x + gridDim.x * (blockIdx.y + (long long)gridDim.y * blockIdx.z);
+        bmin[bidx] = mn; bmax[bidx] = mx;
+    }
+}
+__global__ void __launch_bounds__(256) k_copy_sigma_plain(LevelDev L, double* __restrict__ s, FabView src)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int j = blockIdx.y * blockDim.y + threadIdx.y;
     const int k = blockIdx.z;
-    if (i > L.n[0] || j > L.n[1]) return;
-    double acc = 0.0;
-    if (!np_is_dirichlet(L, i, j, k)) {
-        // z?lo / z?hi: weight of the cells on the low / high side of the node (0 outside a Neumann wall)
-        const double zxl = (L.face[0] == NP_FACE_NEUMANN && i == 0) ? 0.0 : 1.0, zxh = (L.face[3] == NP_FACE_NEUMANN && i == L.n[0]) ? 0.0 : 1.0;
-        const double zyl = (L.face[1] == NP_FACE_NEUMANN && j == 0) ? 0.0 : 1.0, zyh = (L.face[4] == NP_FACE_NEUMANN && j == L.n[1]) ? 0.0 : 1.0;
-        const double zzl = (L.face[2] == NP_FACE_NEUMANN && k == 0) ? 0.0 : 1.0, zzh = (L.face[5] == NP_FACE_NEUMANN && k == L.n[2]) ? 0.0 : 1.0;
-        const double* p = u.p + np_foff(u, i, j, k, 0);
-        const long long y = u.sy, z = u.sz;
-        const double* ux = p; const double* uy = p + u.sn; const double* uz = p + 2 * u.sn;
-        // cells (a,b,c), a,b,c in {-1,0}: offset a + y*b + z*c
-        double sx = zyl*zzl*(ux[-y-z] - ux[-1-y-z]) + zyh*zzl*(ux[-z] - ux[-1-z]) + zyl*zzh*(ux[-y] - ux[-1-y]) + zyh*zzh*(ux[0] - ux[-1]);
-        double sy_ = zxl*zzl*(uy[-1-z] - uy[-1-y-z]) + zxh*zzl*(uy[-z] - uy[-y-z]) + zxl*zzh*(uy[-1] - uy[-1-y]) + zxh*zzh*(uy[0] - uy[-y]);
-        double sz_ = zxl*zyl*(uz[-1-y] - uz[-1-y-z]) + zxh*zyl*(uz[-y] - uz[-y-z]) + zxl*zyh*(uz[-1] - uz[-1-z]) + zxh*zyh*(uz[0] - uz[-z]);
-        acc = 0.25 * (L.dxinv[0] * sx + L.dxinv[1] * sy_ + L.dxinv[2] * sz_);
-        if (zxl == 0.0) acc *= 2.0;
-        if (zxh == 0.0) acc *= 2.0;
-        if (zyl == 0.0) acc *= 2.0;
-        if (zyh == 0.0) acc *= 2.0;
-        if (zzl == 0.0) acc *= 2.0;
-        if (zzh == 0.0) acc *= 2.0;
-    }
-    rhs[np_noff(L, i, j, k)] = acc;
+    if (i < L.n[0] && j < L.n[1]) s[np_coff(L, i, j, k)] = src.p[np_foff(src, i, j, k, 0)];
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -146,7 +146,7 @@ void NpSolver::destroy()
     np_rt::stream_sync(stream);
     for (auto& L : lev) { np_rt::dev_free(L.sigma); np_rt::dev_free(L.res); np_rt::dev_free(L.cor); np_rt::dev_free(L.cor_alt); np_rt::dev_free(L.rescor); }
     lev.clear();
-    double* ds[] = {sol, rhs, gphi, phi_out, part0, part1, scal, xbuf_lo, xbuf_hi, agg_send, agg_recv, stage_vel, stage_sig};
+    double* ds[] = {sol, rhs, gphi, phi_out, part0, part1, scal, xbuf_lo, xbuf_hi, agg_send, agg_recv, stage[0], stage[1], stage[2]};
     for (double* p : ds) if (p) np_rt::dev_free(p);
     for (int w = 0; w < 7; ++w) if (bw[w]) np_rt::dev_free(bw[w]);
     if (h_scal) np_rt::host_free(h_scal);
@@ -445,10 +445,24 @@ int NpSolver::solve(double rtol, double atol)
     wtot = 1.0;
     for (int dd = 0; dd < 3; ++dd) wtot *= (double)geom.ncell[dd];   // sum of the dot-mask weights (periodic / Neumann dims)
     lvl0_off = nullptr;
-    if (singular) make_solvable(0, rhs);
-    const double rhsnorm0 = norminf(0, rhs);
-    residual(0, L0.res, sol, rhs, true, nullptr);
+    // MLMG::makeSolvable(rhs): the offset sum(w*rhs)/sum(w) stays a device scalar (scal[7]) that the level-0
+    // residual subtracts on the fly; its partial sums came out of the divergence kernel
+    const double* rhs_off = nullptr;
+    if (singular) {
+        if (divu_npart > 0) {
+            NP_LAUNCH(true, k_reduce_sum_off, dim3(1), dim3(1024), 0, stream, (const double*)part1, divu_npart, scal, 8, 7, wtot); ++launches;
+            if (is_sharded(*this, L0)) {
+                if (comm.allreduce(comm.ctx, scal + 8, 1, 0, (void*)stream)) err = NP_ERR_NCCL;
+                NP_LAUNCH(false, k_div_scalar, dim3(1), dim3(32), 0, stream, scal, 8, 7, wtot); ++launches;
+            }
+            rhs_off = scal + 7;
+            divu_npart = 0;
+        } else make_solvable(0, rhs);
+    }
+    // zero initial guess: the first residual IS the (solvable) rhs, so one pass gives both norms
+    residual(0, L0.res, sol, rhs, true, rhs_off);
     const double resnorm0 = finish_norm(0, singular);
+    const double rhsnorm0 = resnorm0;
     const double max_norm = rhsnorm0 >= resnorm0 ? rhsnorm0 : resnorm0;
     const double res_target = std::max(atol, std::max(rtol, 1e-16) * max_norm);
     stats.rhs_norm0 = rhsnorm0; stats.res_norm0 = resnorm0; stats.res_norm_final = resnorm0;
@@ -461,7 +475,7 @@ int NpSolver::solve(double rtol, double atol)
         lvl0_off = singular ? scal + 6 : nullptr;
         vcycle(true);
         lvl0_off = nullptr;
-        residual(0, L0.res, sol, rhs, true, nullptr);
+        residual(0, L0.res, sol, rhs, true, rhs_off);
         const double rn = finish_norm(0, singular);
         if (iter < 128) stats.res_history[iter] = rn;
         stats.n_vcycles = iter + 1; stats.res_norm_final = rn;
@@ -528,9 +542,10 @@ static void fill_sigma_level(NpSolver& S, int l)
 int NpSolver::set_sigma(const FabView& s)
 {
     const LevelDev& d0 = lev[0].d;
-    const long long nb = nblocks(grid_cells(d0));
-    NP_LAUNCH(true, k_copy_sigma_in, grid_cells(d0), NP_BLK, 0, stream, d0, lev[0].sigma, s, part0, part1); ++launches;
-    NP_LAUNCH(true, k_reduce_minmax, dim3(1), dim3(256), 0, stream, (const double*)part0, (const double*)part1, nb, scal + 4); ++launches;
+    dim3 gmm = grid_cells(d0); gmm.z = std::min<unsigned>(gmm.z, 16u);
+    const long long nbm = nblocks(gmm);
+    NP_LAUNCH(true, k_minmax_cell, gmm, NP_BLK, 0, stream, d0.n[0], d0.n[1], d0.n[2], s, part0, part1); ++launches;
+    NP_LAUNCH(true, k_reduce_minmax, dim3(1), dim3(256), 0, stream, (const double*)part0, (const double*)part1, nbm, scal + 4); ++launches;
     NP_LAUNCH(false, k_negate_one, dim3(1), dim3(32), 0, stream, scal + 4); ++launches;   // (-min, max): one max-allreduce
     if (comm.nranks > 1) { if (comm.allreduce(comm.ctx, scal + 4, 2, 1, (void*)stream)) err = NP_ERR_NCCL; }
     np_rt::copy_async(h_scal + 4, scal + 4, 2 * sizeof(double), stream);
@@ -540,6 +555,7 @@ int NpSolver::set_sigma(const FabView& s)
     stats.sigma_is_const = is_const ? 1 : 0;
     for (auto& L : lev) { L.d.const_sigma = is_const ? 1 : 0; L.d.sigma0 = smin; }
     if (!is_const) {
+        NP_LAUNCH(false, k_copy_sigma_plain, grid_cells(d0), NP_BLK, 0, stream, d0, lev[0].sigma, s); ++launches;
         fill_sigma_level(*this, 0);
         for (int l = 1; l < (int)lev.size(); ++l) {
             if (lev[l].replicated && !lev[l - 1].replicated) avgdown_sigma_to_replica(l);
@@ -583,6 +599,16 @@ int NpSolver::import_fab(const np_fab& f, long long nelem, double** dev, bool* s
     return NP_OK;
 #endif
 }
+// persistent (grow-only) device staging for np_project / np_copy_* with host fabs: slot 0 vel, 1 sigma, 2 outputs
+double* NpSolver::stage_get(int slot, long long n)
+{
+    if (stage_n[slot] < n) {
+        if (stage[slot]) { np_rt::stream_sync(stream); np_rt::dev_free(stage[slot]); stage[slot] = nullptr; stage_n[slot] = 0; }
+        if (alloc_d(&stage[slot], n)) return nullptr;
+        stage_n[slot] = n;
+    }
+    return stage[slot];
+}
 int NpSolver::export_fab(const np_fab& f, long long nelem, double* dev, bool staged)
 {
     if (!staged) return NP_OK;
@@ -625,15 +651,28 @@ int NpSolver::project(np_fab* vel, const np_fab* sigma, double rtol, double atol
     // ---- inputs ----
     FabView uv = view_cell(*vel, 0, 3), sv = view_cell(*sigma, 0, 1);
     const long long nvel = uv.sn * 3, nsig = sv.sn;
-    double *dvel = nullptr, *dsig = nullptr; bool st_vel = false, st_sig = false;
-    if (import_fab(*vel, nvel, &dvel, &st_vel) || import_fab(*sigma, nsig, &dsig, &st_sig)) return NP_ERR_CUDA;
+    double *dvel = vel->p, *dsig = sigma->p; bool st_vel = false, st_sig = false;
+#ifndef NP_EMU
+    if (!np_rt::is_device_ptr(vel->p)) {        // host fabs (CPU build of the caller): stage through persistent device buffers
+        if (!(dvel = stage_get(0, nvel))) return NP_ERR_CUDA;
+        np_rt::copy_async(dvel, vel->p, (size_t)nvel * sizeof(double), stream); st_vel = true;
+    }
+    if (!np_rt::is_device_ptr(sigma->p)) {
+        if (!(dsig = stage_get(1, nsig))) return NP_ERR_CUDA;
+        np_rt::copy_async(dsig, sigma->p, (size_t)nsig * sizeof(double), stream); st_sig = true;
+    }
+#endif
     uv.p = dvel; sv.p = dsig;
     int rc = set_sigma(sv);
-    if (st_sig) { np_rt::stream_sync(stream); np_rt::dev_free(dsig); }
     if (rc) return rc;
     // ---- rhs = div(u*) ----
     np_fill_cell3(*this, uv);
-    NP_LAUNCH(false, k_divu, grid_nodes(d0), NP_BLK, 0, stream, d0, rhs, uv); ++launches;
+    {   // rhs = div(u*) and, for singular problems, the partial sums of its solvability offset in the same pass
+        dim3 gd = grid_nodes(d0); gd.z = std::min<unsigned>(gd.z, 32u);
+        if (singular) { NP_LAUNCH(true, (k_divu<true>), gd, NP_BLK, 0, stream, d0, rhs, uv, part1); divu_npart = nblocks(gd); }
+        else          { NP_LAUNCH(true, (k_divu<false>), gd, NP_BLK, 0, stream, d0, rhs, uv, part1); divu_npart = 0; }
+        ++launches;
+    }
     np_rt::event_record(ev[1], stream);
     // ---- solve ----
     rc = solve(rtol, atol);
@@ -645,7 +684,8 @@ int NpSolver::project(np_fab* vel, const np_fab* sigma, double rtol, double atol
     fill(0, sol);
     FabView pv; pv.p = phi_out; pv.ng = 1; pv.sy = d0.n[0] + 3; pv.sz = pv.sy * (d0.n[1] + 3); pv.sn = pv.sz * (d0.n[2] + 3);
     NP_LAUNCH(false, (k_copy_nodal<true>), dim3((d0.n[0] + 3 + 31) / 32, (d0.n[1] + 3 + 7) / 8, d0.n[2] + 3), NP_BLK, 0, stream, d0, sol, pv, 1); ++launches;
-    export_fab(*vel, nvel, dvel, st_vel);
+    if (st_vel) np_rt::copy_async(vel->p, dvel, (size_t)nvel * sizeof(double), stream);
+    (void)st_sig;
     np_rt::event_record(ev[3], stream);
     np_rt::stream_sync(stream);
     stats.ms_setup = np_rt::event_ms(ev[0], ev[1]);

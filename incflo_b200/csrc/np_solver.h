@@ -52,7 +52,7 @@ struct NpSolver {
     double *xbuf_lo = nullptr, *xbuf_hi = nullptr;   // exchange staging
     double *agg_send = nullptr, *agg_recv = nullptr;
     // host staging (caller passes host pointers)
-    double *stage_vel = nullptr, *stage_sig = nullptr; long long stage_vel_n = 0, stage_sig_n = 0;
+    double* stage[3] = {nullptr, nullptr, nullptr}; long long stage_n[3] = {0, 0, 0};   // persistent device staging
     np_stream_t stream = 0;
     np_event_t ev[4] = {0,0,0,0};
     std::vector<np_event_t> prof_ev;   // profile_kernels: start/stop pairs around level-0 smoother launches
@@ -61,6 +61,7 @@ struct NpSolver {
     bool have_sigma = false, have_result = false, singular = true;
     bool bicg_failed_switch = false;
     long long launches = 0;
+    long long divu_npart = 0;       // partial sums of sum(w*rhs) left in part1 by the divergence kernel (0: none)
     long long red_n = 0;            // number of partials the last reducing kernel left in part0 / part1
     double wtot = 1.0;              // sum of the dot-mask weights over the domain (singular problems)
     const double* lvl0_off = nullptr;   // device scalar subtracted from lev[0].res by its consumers (lazy makeSolvable)
@@ -93,6 +94,7 @@ struct NpSolver {
     FabView view_nodal(const np_fab& f, int l) const;
     FabView view_cell(const np_fab& f, int l, int ncomp) const;
     // host-pointer staging helpers for hooks
+    double* stage_get(int slot, long long n);
     int import_fab(const np_fab& f, long long nelem, double** dev, bool* staged);
     int export_fab(const np_fab& f, long long nelem, double* dev, bool staged);
 };

@@ -93,3 +93,27 @@ def test_not_converged_is_reported(backend):
     assert st.status == 5 and st.n_vcycles == 1
     with pytest.raises(Exception):
         drv.project(prob["vel"], prob["sigma"], 1e-11, 1e-14)
+
+
+@pytest.mark.parametrize("host_out", [False, True])
+def test_copy_out_and_host_fabs(backend, host_out):
+    """np_copy_phi / np_copy_gradphi into caller fabs of other ghost widths; on the GPU also host (numpy) fabs for
+    every argument, i.e. the staged path a CPU build of the caller takes."""
+    import ctypes as C
+    from incflo_b200 import capi
+    from incflo_b200.projector import Fab
+    ncell = (16, 16, 16)
+    prob = problems.taylor_green(ncell)
+    bk = dict(backend)
+    if host_out:
+        bk["like"] = "numpy"                       # GPU backend: host pointers in and out; emulation: same as before
+    drv = nphelp.Driver(ncell, **bk)
+    st, u, phi, gp = drv.project(prob["vel"], prob["sigma"], 1e-11, 1e-14)
+    so, uo, po, go = run_oracle(ncell, prob, 1e-11, 1e-14, smoother=TILED, tile=(63, 31, BIG), tile_z_target=-1)
+    assert st.n_vcycles == so.n_vcycles and l2rel(u, uo) < 1e-12
+    for ng in (0, 1, 2):
+        fp = Fab.zeros(ncell, 1, ng, True, bk["like"], bk.get("device", "cuda"))
+        fg = Fab.zeros(ncell, 3, ng, False, bk["like"], bk.get("device", "cuda"))
+        capi.check(drv.L, drv.L.np_copy_phi(drv.h, 0, C.byref(fp.c())))
+        capi.check(drv.L, drv.L.np_copy_gradphi(drv.h, 0, C.byref(fg.c())))
+        assert np.array_equal(fp.numpy_valid()[0], phi) and np.array_equal(fg.numpy_valid(), gp)
