@@ -52,7 +52,7 @@ SYMBOLS = ["np_default_options", "np_create", "np_set_bc", "np_project", "np_get
            "np_copy_phi", "np_copy_gradphi", "np_destroy", "np_strerror", "np_num_levels", "np_level_ncell",
            "np_last_stats", "np_set_sigma", "np_get_sigma", "np_apply", "np_smooth", "np_restrict",
            "np_interp_add", "np_divu", "np_mknewu", "np_bottom_solve", "np_vcycle", "np_dot",
-           "np_nccl_unique_id", "np_nccl_comm_create", "np_nccl_comm_destroy"]
+           "np_nccl_unique_id", "np_nccl_comm_create", "np_nccl_comm_destroy", "np_is_device_pointer"]
 
 _libs = {}
 
@@ -71,7 +71,7 @@ def load(path=None):
     if not os.path.exists(path):
         raise ImportError(f"{path} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
                           "(incflo_b200 has no CPU fallback)")
-    L = C.CDLL(path, mode=C.RTLD_GLOBAL)
+    L = C.CDLL(path, mode=C.RTLD_LOCAL)
     L.np_strerror.restype = C.c_char_p
     L.np_create.argtypes = [C.POINTER(C.c_void_p), C.POINTER(np_geom), C.c_int, C.POINTER(np_box), C.POINTER(C.c_int),
                             C.c_int, C.c_int, C.c_void_p, C.POINTER(np_options)]
@@ -99,6 +99,7 @@ def load(path=None):
     L.np_nccl_unique_id.argtypes = [C.c_void_p]
     L.np_nccl_comm_create.argtypes = [C.POINTER(C.c_void_p), C.c_void_p, C.c_int, C.c_int]
     L.np_nccl_comm_destroy.argtypes = [C.c_void_p]
+    L.np_is_device_pointer.argtypes = [C.c_void_p]
     _libs[path] = L
     return L
 

@@ -106,6 +106,15 @@ int np_copy_gradphi(np_handle* h, int local_box, np_fab* dst)
     return copy_out(h->S, dst, h->S.gphi, false, 3);
 }
 
+int np_is_device_pointer(const void* p)
+{
+#ifdef NP_EMU
+    (void)p; return 0;
+#else
+    return np_rt::is_device_ptr(p);
+#endif
+}
+
 void np_destroy(np_handle* h) { if (h) { h->S.destroy(); delete h; } }
 
 const char* np_strerror(int code)

@@ -181,9 +181,12 @@ class NodalProjector:
         capi.check(self.L, getter(self.h, 0, C.byref(f)))
         n = [x + (1 if nodal else 0) + 2 * f.ngrow for x in ncell]
         shape = (ncomp, n[2], n[1], n[0])
-        if hasattr(self.vel.data, "data_ptr") and self.vel.data.is_cuda:
-            # zero-copy alias of the projector-owned device buffer (valid until the next project()/close())
-            return Fab(_alias_cuda(f.p, shape, self.vel.data.device), f.ngrow, nodal)
+        if not hasattr(self.L, "np_emu_set_comm"):
+            # the CUDA library hands back DEVICE pointers whatever the inputs were: zero-copy alias of the
+            # projector-owned buffer (valid until the next project()/close())
+            import torch
+            dev = self.vel.data.device if getattr(self.vel.data, "is_cuda", False) else torch.device("cuda", torch.cuda.current_device())
+            return Fab(_alias_cuda(f.p, shape, dev), f.ngrow, nodal)
         arr = np.ctypeslib.as_array(C.cast(f.p, C.POINTER(C.c_double)), shape=shape)
         return Fab(arr, f.ngrow, nodal)
 

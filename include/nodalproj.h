@@ -115,6 +115,10 @@ int np_get_gradphi(np_handle* h, int local_box, np_fab* out);
 int np_copy_phi(np_handle* h, int local_box, np_fab* dst);
 int np_copy_gradphi(np_handle* h, int local_box, np_fab* dst);
 
+/* 1 if p is device (or managed) memory, 0 if it is host memory: tells a shim whether np_get_* aliases are usable
+ * from its side or the results must be fetched with np_copy_*. */
+int np_is_device_pointer(const void* p);
+
 void np_destroy(np_handle* h);
 const char* np_strerror(int code);
 int np_num_levels(np_handle* h);
