@@ -158,8 +158,13 @@ def run_reference(args):
 
 def workload_config(args, G, sample=None):
     n = args.ncell
-    c = {"workload": f"BASELINE configs[2]: synthetic {n}^3 cells per GPU, {n}x{n}x{n * G} domain in {G} z-slab(s), "
-                     f"periodic, constant density (sigma=1), double_shear_layer + z-wave, rtol {RTOL:g} atol {ATOL:g}",
+    if args.workload == "rayleigh_taylor":
+        wl = (f"BASELINE configs[3]: synthetic {n}^3 cells per GPU, {n}x{n}x{n * G} domain in {G} z-slab(s), periodic x/y, "
+              f"slip walls (Neumann) in z, variable density ratio 4 (sigma = dt/rho), gravity kick + perturbation, rtol {RTOL:g} atol {ATOL:g}")
+    else:
+        wl = (f"BASELINE configs[2]: synthetic {n}^3 cells per GPU, {n}x{n}x{n * G} domain in {G} z-slab(s), "
+              f"periodic, constant density (sigma=1), double_shear_layer + z-wave, rtol {RTOL:g} atol {ATOL:g}")
+    c = {"workload": wl,
          "ncell_per_gpu": [n, n, n], "boxes": f"one {n}^3 box per GPU", "vel_ngrow": args.vel_ngrow,
          "l2": "inputs (>= 1 GB per array at 512^3) exceed the 126 MB L2; no explicit flush"}
     if sample:
@@ -205,14 +210,25 @@ def run_gpu(args):
     ncell = (n, n, n * G)
     prob_hi = (1.0, 1.0, float(G))
     koff = rank * n
-    vel0 = problems.double_shear_torch(ncell, prob_hi, koff, n, dev, ngrow=g)     # pristine u*
+    bclo = bchi = (0, 0, 0)
+    if args.workload == "rayleigh_taylor":
+        # BASELINE configs[3]: variable density (ratio 4), sigma = dt/rho, periodic x/y, walls in z; unit-cube cells
+        import numpy as np
+        pr = problems.rayleigh_taylor(ncell, prob_hi=prob_hi, koff=koff, nz_local=n)
+        vel0 = torch.zeros((3, n + 2 * g, n + 2 * g, n + 2 * g), dtype=torch.float64, device=dev)
+        vel0[:, g:g + n, g:g + n, g:g + n] = torch.from_numpy(pr["vel"]).to(dev)
+        sig = Fab(torch.from_numpy(np.ascontiguousarray(pr["sigma"][None])).to(dev), 0)
+        bclo, bchi = pr["bclo"], pr["bchi"]
+        del pr
+    else:
+        vel0 = problems.double_shear_torch(ncell, prob_hi, koff, n, dev, ngrow=g)     # pristine u*
+        sig = Fab(torch.ones((1, n, n, n), dtype=torch.float64, device=dev), 0)
     vel = Fab(vel0.clone(), g)
-    sig = Fab(torch.ones((1, n, n, n), dtype=torch.float64, device=dev), 0)
-    geom = Geometry(ncell, (0, 0, 0), prob_hi, (1, 1, 1))
+    geom = Geometry(ncell, (0, 0, 0), prob_hi, [b == 0 for b in bclo])
     boxes = [((0, 0, r * n), (n - 1, n - 1, (r + 1) * n - 1)) for r in range(G)]
     P = NodalProjector(vel, sig, geom, LPInfo(), boxes=boxes, rank=rank, nranks=world, nccl_comm=comm, lib=L,
                        profile_kernels=1)
-    P.setDomainBC((0, 0, 0), (0, 0, 0))
+    P.setDomainBC(bclo, bchi)
     dof = n * n * n * G
     stream = torch.cuda.current_stream().cuda_stream
 
@@ -258,7 +274,7 @@ def run_gpu(args):
     if not args.no_e2e:
         hv0 = vel0.cpu()                                            # pristine host copy (pageable)
         hv = Fab(torch.empty_like(hv0).pin_memory(), g)
-        hs = Fab(torch.ones((1, n, n, n), dtype=torch.float64).pin_memory(), 0)
+        hs = Fab(sig.data.cpu().pin_memory(), 0)
         hphi = Fab(torch.zeros((1, n + 1, n + 1, n + 1), dtype=torch.float64).pin_memory(), 0, nodal=True)
         hgp = Fab(torch.zeros((3, n, n, n), dtype=torch.float64).pin_memory(), 0)
         P.vel, P.sigma = hv, hs
@@ -328,6 +344,8 @@ def main():
     ap.add_argument("--ncell", type=int, default=512, help="cells per side per GPU (512: configs[2]; 256: configs[1])")
     ap.add_argument("--vel-ngrow", type=int, default=2, help="ghost layers of the velocity fab (incflo nghost_state: 2 MOL / 3 Godunov)")
     ap.add_argument("--cpu-ncell", type=int, default=128, help="size of the bounded CPU sample")
+    ap.add_argument("--workload", default="double_shear", choices=["double_shear", "rayleigh_taylor"],
+                    help="double_shear: BASELINE configs[2] (constant density, default); rayleigh_taylor: configs[3] (variable sigma)")
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")

@@ -448,6 +448,106 @@ __device__ __forceinline__ void gs_colours_cs(bool on, double (&x)[2][8], const 
     }
 }
 
+// Variable sigma: the same four colour steps; V[c][q] = sigma_below + sigma_above of the cell column (c, q) around the
+// thread's block (c = 0..2 <-> cells gi-1..gi+1, q = 0..8 <-> cells gj-1..gj+7), so node (a, r) sees the four columns
+// V[a][r], V[a+1][r], V[a][r+1], V[a+1][r+1].  B holds rhs minus the out-of-plane part; x_new = (B - in-plane) / diag.
+__device__ __forceinline__ double gs_upd_var(const NpCoef& c, double Bv, double v00, double v10, double v01, double v11,
+                                             double xW, double xE, double xS, double xN, double xSW, double xSE, double xNW, double xNE)
+{
+    const double inpl = c.f4xm2ym2z * (xW * (v00 + v01) + xE * (v10 + v11)) + c.fm2x4ym2z * (xS * (v00 + v10) + xN * (v01 + v11))
+                      + c.f2x2ymz * ((xSW * v00 + xSE * v10) + (xNW * v01 + xNE * v11));
+    const double diag = -4.0 * c.fxyz * ((v00 + v10) + (v01 + v11));
+    return (Bv - inpl) / diag;
+}
+__device__ __forceinline__ void gs_colours_var(bool on, double (&x)[2][8], const double (&B)[2][8], const double (&V)[3][9], double* Pc,
+                                               const NpCoef& c, int ofs, unsigned act, unsigned dmask, int grp)
+{
+    double t0 = 0.0, t1 = 0.0, d0 = 0.0, d1 = 0.0;
+    if (on) {   // colour 0: a = 0, r even
+        double xl[9];
+#pragma unroll
+        for (int q = 0; q < 9; ++q) xl[q] = Pc[GS_HALF + ofs + (q - 1) * GS_HP];              // rows -1..7
+        t0 = Pc[ofs - GS_HP + 1]; t1 = Pc[GS_HALF + ofs - GS_HP + 1];
+#pragma unroll
+        for (int r = 0; r < 8; r += 2) {
+            const double up0 = r == 0 ? t0 : x[0][r - 1], up1 = r == 0 ? t1 : x[1][r - 1];
+            const double v = gs_upd_var(c, B[0][r], V[0][r], V[1][r], V[0][r + 1], V[1][r + 1],
+                                        xl[r + 1], x[1][r], up0, x[0][r + 1], xl[r], up1, xl[r + 2], x[1][r + 1]);
+            if ((act >> r) & 1u) x[0][r] = ((dmask >> r) & 1u) ? 0.0 : v;
+            Pc[ofs + r * GS_HP + 1] = x[0][r];
+        }
+    }
+    np_group_barrier(grp);
+    if (on) {   // colour 1: a = 1, r even
+        double xr[9];
+#pragma unroll
+        for (int q = 0; q < 9; ++q) xr[q] = Pc[ofs + (q - 1) * GS_HP + 2];                    // rows -1..7
+#pragma unroll
+        for (int r = 0; r < 8; r += 2) {
+            const double up0 = r == 0 ? t0 : x[0][r - 1], up1 = r == 0 ? t1 : x[1][r - 1];
+            const double v = gs_upd_var(c, B[1][r], V[1][r], V[2][r], V[1][r + 1], V[2][r + 1],
+                                        x[0][r], xr[r + 1], up1, x[1][r + 1], up0, xr[r], x[0][r + 1], xr[r + 2]);
+            if ((act >> (8 + r)) & 1u) x[1][r] = ((dmask >> (8 + r)) & 1u) ? 0.0 : v;
+            Pc[GS_HALF + ofs + r * GS_HP + 1] = x[1][r];
+        }
+    }
+    np_group_barrier(grp);
+    if (on) {   // colour 2: a = 0, r odd
+        double xl[9];
+#pragma unroll
+        for (int q = 0; q < 9; ++q) xl[q] = Pc[GS_HALF + ofs + q * GS_HP];                    // rows 0..8
+        d0 = Pc[ofs + 8 * GS_HP + 1]; d1 = Pc[GS_HALF + ofs + 8 * GS_HP + 1];
+#pragma unroll
+        for (int r = 1; r < 8; r += 2) {
+            const double dn0 = r == 7 ? d0 : x[0][r + 1], dn1 = r == 7 ? d1 : x[1][r + 1];
+            const double v = gs_upd_var(c, B[0][r], V[0][r], V[1][r], V[0][r + 1], V[1][r + 1],
+                                        xl[r], x[1][r], x[0][r - 1], dn0, xl[r - 1], x[1][r - 1], xl[r + 1], dn1);
+            if ((act >> r) & 1u) x[0][r] = ((dmask >> r) & 1u) ? 0.0 : v;
+            Pc[ofs + r * GS_HP + 1] = x[0][r];
+        }
+    }
+    np_group_barrier(grp);
+    if (on) {   // colour 3: a = 1, r odd
+        double xr[9];
+#pragma unroll
+        for (int q = 0; q < 9; ++q) xr[q] = Pc[ofs + q * GS_HP + 2];                          // rows 0..8
+#pragma unroll
+        for (int r = 1; r < 8; r += 2) {
+            const double dn0 = r == 7 ? d0 : x[0][r + 1], dn1 = r == 7 ? d1 : x[1][r + 1];
+            const double v = gs_upd_var(c, B[1][r], V[1][r], V[2][r], V[1][r + 1], V[2][r + 1],
+                                        x[0][r], xr[r], x[1][r - 1], dn1, x[0][r - 1], xr[r - 1], dn0, xr[r + 1]);
+            if ((act >> (8 + r)) & 1u) x[1][r] = ((dmask >> (8 + r)) & 1u) ? 0.0 : v;
+            Pc[GS_HALF + ofs + r * GS_HP + 1] = x[1][r];
+        }
+    }
+}
+
+// out-of-plane part of one neighbouring plane P (x[k-1] or x[k+1]) through the cell layer S between it and plane k
+__device__ __forceinline__ void gs_zpart_var(const NpCoef& c, double (&B)[2][8], const double (&S)[3][9], const double* P, int ofs)
+{
+    double xa[4], xb[4], xc[4];     // node rows r-1, r, r+1; columns: left halo, own even, own odd, right halo
+    {
+        const int ro = ofs - GS_HP;
+        xa[0] = P[GS_HALF + ro]; xa[1] = P[ro + 1]; xa[2] = P[GS_HALF + ro + 1]; xa[3] = P[ro + 2];
+        xb[0] = P[GS_HALF + ofs]; xb[1] = P[ofs + 1]; xb[2] = P[GS_HALF + ofs + 1]; xb[3] = P[ofs + 2];
+    }
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+        const int ro = ofs + (r + 1) * GS_HP;
+        xc[0] = P[GS_HALF + ro]; xc[1] = P[ro + 1]; xc[2] = P[GS_HALF + ro + 1]; xc[3] = P[ro + 2];
+#pragma unroll
+        for (int a = 0; a < 2; ++a) {
+            const double l00 = S[a][r], l10 = S[a + 1][r], l01 = S[a][r + 1], l11 = S[a + 1][r + 1];
+            B[a][r] -= c.fm2xm2y4z * (xb[a + 1] * ((l00 + l10) + (l01 + l11)))
+                     + c.f2xmy2z * (xb[a] * (l00 + l01) + xb[a + 2] * (l10 + l11))
+                     + c.fmx2y2z * (xa[a + 1] * (l00 + l10) + xc[a + 1] * (l01 + l11))
+                     + c.fxyz * ((xa[a] * l00 + xa[a + 2] * l10) + (xc[a] * l01 + xc[a + 2] * l11));
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) { xa[q] = xb[q]; xb[q] = xc[q]; }
+    }
+}
+
 template <bool CS>
 __global__ void __launch_bounds__(256, CS ? 2 : 1) k_gs2(LevelDev L, GsArgs A)
 {
@@ -556,30 +656,55 @@ __global__ void __launch_bounds__(256, CS ? 2 : 1) k_gs2(LevelDev L, GsArgs A)
             if (full) gs_colours_cs<false>(on, x, B, Pc, C, ofs, act, dmask, grp);
             else      gs_colours_cs<true>(on, x, B, Pc, C, ofs, act, dmask, grp);
         } else {
-            // ---- variable sigma: every update gathers its 26 neighbours from the ring and its 8 cells from L1/L2 ----
-            const double* Pm = on ? slot(p - 1) : ring; const double* Pp = on ? slot(p + 1) : ring;
+            // ---- variable sigma: B = rhs - (out-of-plane part through the two cell layers); V = column sums of sigma ----
+            double V[3][9];
+            if (on) {
+                const double* rp = rhs + gbase;
 #pragma unroll
-            for (int col = 0; col < 4; ++col) {
-                if (on) {
-                    const int a = col & 1;
-#pragma unroll
-                    for (int r = (col >> 1); r < 8; r += 2) {
-                        const int bit = a * 8 + r;
-                        if ((act >> bit) & 1u) {
-                            double v = 0.0;
-                            if (!((dmask >> bit) & 1u)) {
-                                GsSmemX xa{Pm, Pc, Pp, 2 * lane + a, 8 * wy + r};
-                                GlobS sa{sig + np_coff(L, gi + a, gj + r, k), L.csy, L.csz};
-                                const Sig8 g = np_load_sig(sa);
-                                v = ((rhs[gbase + a + L.nsy * r] - roff) - np_offdiag(L.c, g, xa)) / np_diag(L.c, g);
-                            }
-                            x[a][r] = v;
-                            Pc[gs_idx(2 * lane + a, 8 * wy + r)] = v;
-                        } else x[a][r] = Pc[gs_idx(2 * lane + a, 8 * wy + r)];
-                    }
+                for (int r = 0; r < 8; ++r) {
+                    B[0][r] = ((act >> r) & 1u) ? rp[L.nsy * r] - roff : 0.0;
+                    B[1][r] = ((act >> (8 + r)) & 1u) ? rp[L.nsy * r + 1] - roff : 0.0;
                 }
-                if (col < 3) __syncthreads();
+                // cells (gi-1+c, gj-1+q) of the layers below (k-1) and above (k) plane k; indices clamped into the array
+                // (clamped cells only feed nodes outside the domain, which are never updated)
+                double S[3][9];
+                const double* sb = sig + L.csz * (long long)k;                  // layer k-1 starts at csz*k
+#pragma unroll
+                for (int c = 0; c < 3; ++c)
+#pragma unroll
+                    for (int q = 0; q < 9; ++q) {
+                        const int ci = min(gi - 1 + c, L.n[0]), cj = min(gj - 1 + q, L.n[1]);
+                        S[c][q] = sb[(ci + 1) + L.csy * (long long)(cj + 1)];
+                    }
+                gs_zpart_var(L.c, B, S, slot(p - 1), ofs);
+#pragma unroll
+                for (int c = 0; c < 3; ++c)
+#pragma unroll
+                    for (int q = 0; q < 9; ++q) V[c][q] = S[c][q];
+#pragma unroll
+                for (int c = 0; c < 3; ++c)
+#pragma unroll
+                    for (int q = 0; q < 9; ++q) {
+                        const int ci = min(gi - 1 + c, L.n[0]), cj = min(gj - 1 + q, L.n[1]);
+                        S[c][q] = sb[L.csz + (ci + 1) + L.csy * (long long)(cj + 1)];
+                    }
+                gs_zpart_var(L.c, B, S, slot(p + 1), ofs);
+#pragma unroll
+                for (int c = 0; c < 3; ++c)
+#pragma unroll
+                    for (int q = 0; q < 9; ++q) V[c][q] += S[c][q];
+#pragma unroll
+                for (int r = 0; r < 8; ++r) {
+                    x[0][r] = Pc[ofs + r * GS_HP + 1];
+                    x[1][r] = Pc[GS_HALF + ofs + r * GS_HP + 1];
+                }
+            } else {
+#pragma unroll
+                for (int c = 0; c < 3; ++c)
+#pragma unroll
+                    for (int q = 0; q < 9; ++q) V[c][q] = 1.0;
             }
+            gs_colours_var(on, x, B, V, Pc, L.c, ofs, act, dmask, grp);
         }
         np_cp_async_wait_all();
         __syncthreads();
@@ -804,30 +929,66 @@ struct InterpCtx {
     }
 };
 
-template <bool WEIGHTED>
-__global__ void __launch_bounds__(256) k_interp_add(LevelDev Lf, LevelDev Lc, double* __restrict__ fine, const double* __restrict__ crse,
-                                                    const double* __restrict__ sig, int koffc)
+// K5, sigma-weighted (mlndlap_interpadd_aa): one thread per COARSE node (I,J,K) owns the 2x2x2 fine nodes
+// (2I+a, 2J+b, 2K+c) and evaluates the coarse cell's 12 edge (line) values once, its 6 face values from those and the
+// centre from the faces — the nested definition of the reference, without recomputing any of it per fine node.
+__device__ __forceinline__ double np_interp_face(const InterpCtx& ctx, int i, int j, int k, int da, int db,
+                                                 double la0, double la1, double lb0, double lb1)
+{   // la0/la1: db-lines at the node's low/high neighbour along da;  lb0/lb1: da-lines at its neighbours along db
+    const double wa0 = ctx.quad(i,j,k,da,0), wa1 = ctx.quad(i,j,k,da,1), wb0 = ctx.quad(i,j,k,db,0), wb1 = ctx.quad(i,j,k,db,1);
+    return (wa0 * la0 + wa1 * la1 + wb0 * lb0 + wb1 * lb1) / ((wa0 + wa1) + (wb0 + wb1));
+}
+__global__ void __launch_bounds__(128) k_interp_add_w(LevelDev Lf, LevelDev Lc, double* __restrict__ fine, const double* __restrict__ crse,
+                                                      const double* __restrict__ sig, int koffc)
 {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    const int j = blockIdx.y * blockDim.y + threadIdx.y;
-    const int k = blockIdx.z;
-    if (i > Lf.n[0] || j > Lf.n[1]) return;
-    if (np_is_dirichlet(Lf, i, j, k)) return;
-    InterpCtx ctx{crse + np_noff(Lc, 0, 0, koffc), Lc.nsy, Lc.nsz, WEIGHTED ? sig + np_coff(Lf, 0, 0, 0) : nullptr, Lf.csy, Lf.csz};
-    const int ox = i & 1, oy = j & 1, oz = k & 1;
-    const int nodd = ox + oy + oz;
-    double v;
-    if (nodd == 0) v = ctx.crse(i, j, k);
-    else if (!WEIGHTED) {
-        double s = 0.0;
-        for (int c2 = 0; c2 <= oz; ++c2) for (int c1 = 0; c1 <= oy; ++c1) for (int c0 = 0; c0 <= ox; ++c0)
-            s += ctx.crse(i - ox + 2*c0, j - oy + 2*c1, k - oz + 2*c2);
-        v = s / (double)(1 << nodd);
+    const int I = blockIdx.x * blockDim.x + threadIdx.x;
+    const int J = blockIdx.y * blockDim.y + threadIdx.y;
+    const int K = blockIdx.z;
+    if (2 * I > Lf.n[0] || 2 * J > Lf.n[1]) return;
+    const int i = 2 * I, j = 2 * J, k = 2 * K;
+    const bool ax = (i + 1 <= Lf.n[0]), ay = (j + 1 <= Lf.n[1]), az = (k + 1 <= Lf.n[2]);
+    InterpCtx ctx{crse + np_noff(Lc, 0, 0, koffc), Lc.nsy, Lc.nsz, sig + np_coff(Lf, 0, 0, 0), Lf.csy, Lf.csz};
+    double v[2][2][2];                     // [c][b][a]
+    v[0][0][0] = ctx.crse(i, j, k);
+    // ---- the 12 edges of the coarse cell ----
+    double lx[2][2], ly[2][2], lz[2][2];   // lx[b][c] at (i+1, j+2b, k+2c); ly[a][c] at (i+2a, j+1, k+2c); lz[a][b] at (i+2a, j+2b, k+1)
+#pragma unroll
+    for (int p = 0; p < 2; ++p)
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+            lx[p][q] = (ax && (p == 0 || ay) && (q == 0 || az)) ? ctx.line(i + 1, j + 2 * p, k + 2 * q, 0) : 0.0;
+            ly[p][q] = (ay && (p == 0 || ax) && (q == 0 || az)) ? ctx.line(i + 2 * p, j + 1, k + 2 * q, 1) : 0.0;
+            lz[p][q] = (az && (p == 0 || ax) && (q == 0 || ay)) ? ctx.line(i + 2 * p, j + 2 * q, k + 1, 2) : 0.0;
+        }
+    v[0][0][1] = lx[0][0]; v[0][1][0] = ly[0][0]; v[1][0][0] = lz[0][0];
+    // ---- its 6 faces (same argument order as the per-node definition: xy -> (0,1), xz -> (2,0), yz -> (1,2)) ----
+    double fxy[2], fxz[2], fyz[2];
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+        fxy[q] = (ax && ay && (q == 0 || az)) ? np_interp_face(ctx, i + 1, j + 1, k + 2 * q, 0, 1, ly[0][q], ly[1][q], lx[0][q], lx[1][q]) : 0.0;
+        fxz[q] = (ax && az && (q == 0 || ay)) ? np_interp_face(ctx, i + 1, j + 2 * q, k + 1, 2, 0, lx[q][0], lx[q][1], lz[0][q], lz[1][q]) : 0.0;
+        fyz[q] = (ay && az && (q == 0 || ax)) ? np_interp_face(ctx, i + 2 * q, j + 1, k + 1, 1, 2, lz[q][0], lz[q][1], ly[q][0], ly[q][1]) : 0.0;
     }
-    else if (nodd == 1) v = ctx.line(i, j, k, ox ? 0 : (oy ? 1 : 2));
-    else if (nodd == 2) v = (ox && oy) ? ctx.face(i, j, k, 0, 1) : ((ox && oz) ? ctx.face(i, j, k, 2, 0) : ctx.face(i, j, k, 1, 2));
-    else v = ctx.centre(i, j, k);
-    fine[np_noff(Lf, i, j, k)] += v;
+    v[0][1][1] = fxy[0]; v[1][0][1] = fxz[0]; v[1][1][0] = fyz[0];
+    // ---- centre ----
+    v[1][1][1] = 0.0;
+    if (ax && ay && az) {
+        const int ic = i + 1, jc = j + 1, kc = k + 1;
+        const double x0 = ctx.quad(ic,jc,kc,0,0), x1 = ctx.quad(ic,jc,kc,0,1), y0 = ctx.quad(ic,jc,kc,1,0), y1 = ctx.quad(ic,jc,kc,1,1),
+                     z0 = ctx.quad(ic,jc,kc,2,0), z1 = ctx.quad(ic,jc,kc,2,1);
+        const double num = (x0 * fyz[0] + x1 * fyz[1]) + (y0 * fxz[0] + y1 * fxz[1]) + (z0 * fxy[0] + z1 * fxy[1]);
+        v[1][1][1] = num / (((x0 + x1) + (y0 + y1)) + (z0 + z1));
+    }
+#pragma unroll
+    for (int c = 0; c < 2; ++c)
+#pragma unroll
+        for (int b = 0; b < 2; ++b)
+#pragma unroll
+            for (int a = 0; a < 2; ++a) {
+                if ((a && !ax) || (b && !ay) || (c && !az)) continue;
+                if (np_is_dirichlet(Lf, i + a, j + b, k + c)) continue;
+                fine[np_noff(Lf, i + a, j + b, k + c)] += v[c][b][a];
+            }
 }
 
 // K5, plain trilinear (constant sigma, or interp_sigma_weighted = 0): one thread per COARSE node (I,J,K) updates the

@@ -363,7 +363,7 @@ void NpSolver::interp_add(int lf, double* fine, const double* crse)
     const LevelDev& df = lev[lf].d; const LevelDev& dc = lev[lf + 1].d;
     const int koffc = (lev[lf + 1].replicated && !lev[lf].replicated) ? lev[lf].koff / 2 : 0;
     if (opt.interp_sigma_weighted && !df.const_sigma)
-        NP_LAUNCH(false, (k_interp_add<true>), grid_nodes(df), NP_BLK, 0, stream, df, dc, fine, crse, (const double*)lev[lf].sigma, koffc);
+        NP_LAUNCH(false, k_interp_add_w, dim3((df.n[0] / 2 + 1 + 31) / 32, (df.n[1] / 2 + 1 + 3) / 4, df.n[2] / 2 + 1), dim3(32, 4, 1), 0, stream, df, dc, fine, crse, (const double*)lev[lf].sigma, koffc);
     else
         NP_LAUNCH(false, k_interp_add_tri, dim3((df.n[0] / 2 + 1 + 31) / 32, (df.n[1] / 2 + 1 + 7) / 8, df.n[2] / 2 + 1), NP_BLK, 0, stream, df, dc, fine, crse, koffc);
     ++launches;
