@@ -747,10 +747,14 @@ __global__ void __launch_bounds__(256, CS ? 2 : 1) k_gs2(LevelDev L, GsArgs A)
 #define ST_SMEM_BYTES (ST_RING * GS_PLANE * 8)
 struct StCoef { double d, w_fx, w_fy, w_exy, w_fz, w_exz, w_eyz, w_c; };
 
-template <int MODE, bool REDUCE>
-__global__ void __launch_bounds__(256, 2) k_stencil_cs(LevelDev L, StCoef C, double* __restrict__ y, const double* __restrict__ x,
-                                                       const double* __restrict__ b, const double* __restrict__ boff,
-                                                       double* __restrict__ part_max, double* __restrict__ part_sum, int zc)
+// CS = false (variable sigma): the same march; the plane arriving at step q contributes, through the cell layers below
+// and above it, D[q] to y[q-1], M[q] to y[q] and UP[q] to y[q+1]:  y[k] = UP[k-1] + M[k] + D[k+1]  (for constant sigma
+// D = UP = V).  Sigma comes through L1 (each cell is used by up to 8 nodes of neighbouring threads).
+template <int MODE, bool REDUCE, bool CS>
+__global__ void __launch_bounds__(256, CS ? 2 : 1) k_stencil(LevelDev L, StCoef C, double* __restrict__ y, const double* __restrict__ x,
+                                                          const double* __restrict__ b, const double* __restrict__ boff,
+                                                          double* __restrict__ part_max, double* __restrict__ part_sum, int zc,
+                                                          const double* __restrict__ sig)
 {
     NP_DYN_SMEM(double, ring);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -814,21 +818,62 @@ __global__ void __launch_bounds__(256, 2) k_stencil_cs(LevelDev L, StCoef C, dou
                 bv[1][r] = ((act >> (4 + r)) & 1u) ? b[gbase + L.nsy * r + 1] : 0.0;
             }
         }
-        double c0[6], c1[6], h0[6], h1[6];
+        double Un[2][4], Vn[2][4], Dn[2][4];             // M[q], UP[q], D[q] of the node block
+        if (CS) {
+            double c0[6], c1[6], h0[6], h1[6];
 #pragma unroll
-        for (int rr = 0; rr < 6; ++rr) {
-            const int ro = (row0 - 1 + rr) * GS_HP + lane;
-            const double xl = P[GS_HALF + ro], x0 = P[ro + 1], x1 = P[GS_HALF + ro + 1], xr = P[ro + 2];
-            c0[rr] = x0; c1[rr] = x1; h0[rr] = xl + x1; h1[rr] = x0 + xr;
-        }
-        double Un[2][4], Vn[2][4];
+            for (int rr = 0; rr < 6; ++rr) {
+                const int ro = (row0 - 1 + rr) * GS_HP + lane;
+                const double xl = P[GS_HALF + ro], x0 = P[ro + 1], x1 = P[GS_HALF + ro + 1], xr = P[ro + 2];
+                c0[rr] = x0; c1[rr] = x1; h0[rr] = xl + x1; h1[rr] = x0 + xr;
+            }
 #pragma unroll
-        for (int r = 0; r < 4; ++r) {
-            const double cc0 = c0[r] + c0[r + 2], hh0 = h0[r] + h0[r + 2], cc1 = c1[r] + c1[r + 2], hh1 = h1[r] + h1[r + 2];
-            Un[0][r] = C.d * c0[r + 1] + C.w_fx * h0[r + 1] + C.w_fy * cc0 + C.w_exy * hh0;
-            Un[1][r] = C.d * c1[r + 1] + C.w_fx * h1[r + 1] + C.w_fy * cc1 + C.w_exy * hh1;
-            Vn[0][r] = C.w_fz * c0[r + 1] + C.w_exz * h0[r + 1] + C.w_eyz * cc0 + C.w_c * hh0;
-            Vn[1][r] = C.w_fz * c1[r + 1] + C.w_exz * h1[r + 1] + C.w_eyz * cc1 + C.w_c * hh1;
+            for (int r = 0; r < 4; ++r) {
+                const double cc0 = c0[r] + c0[r + 2], hh0 = h0[r] + h0[r + 2], cc1 = c1[r] + c1[r + 2], hh1 = h1[r] + h1[r + 2];
+                Un[0][r] = C.d * c0[r + 1] + C.w_fx * h0[r + 1] + C.w_fy * cc0 + C.w_exy * hh0;
+                Un[1][r] = C.d * c1[r + 1] + C.w_fx * h1[r + 1] + C.w_fy * cc1 + C.w_exy * hh1;
+                Vn[0][r] = C.w_fz * c0[r + 1] + C.w_exz * h0[r + 1] + C.w_eyz * cc0 + C.w_c * hh0;
+                Vn[1][r] = C.w_fz * c1[r + 1] + C.w_exz * h1[r + 1] + C.w_eyz * cc1 + C.w_c * hh1;
+                Dn[0][r] = Vn[0][r]; Dn[1][r] = Vn[1][r];
+            }
+        } else {
+            double xw[6][4];                             // node rows -1..4; columns: left halo, own even, own odd, right halo
+#pragma unroll
+            for (int rr = 0; rr < 6; ++rr) {
+                const int ro = (row0 - 1 + rr) * GS_HP + lane;
+                xw[rr][0] = P[GS_HALF + ro]; xw[rr][1] = P[ro + 1]; xw[rr][2] = P[GS_HALF + ro + 1]; xw[rr][3] = P[ro + 2];
+            }
+#pragma unroll
+            for (int a = 0; a < 2; ++a)
+#pragma unroll
+                for (int r = 0; r < 4; ++r) { Un[a][r] = 0.0; }
+#pragma unroll
+            for (int lay = 0; lay < 2; ++lay) {          // 0: cells below plane q (k index q-1), 1: cells above (k index q)
+                const int kc = min(max(q - 1 + lay, -1), L.n[2]);       // clamped layers only feed planes that are not written
+                const double* sb = sig + L.csz * (long long)(kc + 1);
+                double S[3][5];
+#pragma unroll
+                for (int c = 0; c < 3; ++c)
+#pragma unroll
+                    for (int qq = 0; qq < 5; ++qq) {
+                        const int ci = min(gi - 1 + c, L.n[0]), cj = min(gj - 1 + qq, L.n[1]);
+                        S[c][qq] = sb[(ci + 1) + L.csy * (long long)(cj + 1)];
+                    }
+#pragma unroll
+                for (int a = 0; a < 2; ++a)
+#pragma unroll
+                    for (int r = 0; r < 4; ++r) {
+                        const double l00 = S[a][r], l10 = S[a + 1][r], l01 = S[a][r + 1], l11 = S[a + 1][r + 1];
+                        const double p0 = xw[r + 1][a + 1] * ((l00 + l10) + (l01 + l11));
+                        const double px = xw[r + 1][a] * (l00 + l01) + xw[r + 1][a + 2] * (l10 + l11);
+                        const double py = xw[r][a + 1] * (l00 + l10) + xw[r + 2][a + 1] * (l01 + l11);
+                        const double pxy = (xw[r][a] * l00 + xw[r][a + 2] * l10) + (xw[r + 2][a] * l01 + xw[r + 2][a + 2] * l11);
+                        const double cross = L.c.fm2xm2y4z * p0 + L.c.f2xmy2z * px + L.c.fmx2y2z * py + L.c.fxyz * pxy;
+                        const double same = -4.0 * L.c.fxyz * p0 + L.c.f4xm2ym2z * px + L.c.fm2x4ym2z * py + L.c.f2x2ymz * pxy;
+                        Un[a][r] += same;
+                        if (lay == 0) Dn[a][r] = cross; else Vn[a][r] = cross;
+                    }
+            }
         }
         if (s >= 2) {                                    // output plane k = q-1
             const int k = q - 1;
@@ -846,7 +891,7 @@ __global__ void __launch_bounds__(256, 2) k_stencil_cs(LevelDev L, StCoef C, dou
                         const long long o = gbase + a + L.nsy * r;
                         double v = 0.0;
                         if (!(zdir || ((dir >> (a * 4 + r)) & 1u))) {
-                            const double ax = Uc[a][r] + (Vm[a][r] + Vn[a][r]);
+                            const double ax = Uc[a][r] + (Vm[a][r] + Dn[a][r]);
                             v = (MODE == 1) ? (bv[a][r] - off) - ax : ax;
                         }
                         y[o] = v;

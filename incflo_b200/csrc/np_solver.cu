@@ -133,9 +133,12 @@ int NpSolver::create(const np_geom* g, int nboxes, const np_box* boxes, const in
 #ifndef NP_EMU
     cudaFuncSetAttribute(k_gs2<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GS_SMEM_BYTES);
     cudaFuncSetAttribute(k_gs2<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GS_SMEM_BYTES);
-    cudaFuncSetAttribute(k_stencil_cs<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ST_SMEM_BYTES);
-    cudaFuncSetAttribute(k_stencil_cs<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ST_SMEM_BYTES);
-    cudaFuncSetAttribute(k_stencil_cs<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ST_SMEM_BYTES);
+    cudaFuncSetAttribute(k_stencil<0, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ST_SMEM_BYTES);
+    cudaFuncSetAttribute(k_stencil<1, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ST_SMEM_BYTES);
+    cudaFuncSetAttribute(k_stencil<1, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ST_SMEM_BYTES);
+    cudaFuncSetAttribute(k_stencil<0, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ST_SMEM_BYTES);
+    cudaFuncSetAttribute(k_stencil<1, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ST_SMEM_BYTES);
+    cudaFuncSetAttribute(k_stencil<1, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ST_SMEM_BYTES);
 #endif
     np_rt::stream_sync(stream);
     return np_rt::last_error() ? NP_ERR_CUDA : NP_OK;
@@ -244,14 +247,11 @@ void NpSolver::apply(int l, double* y, double* x)
 {
     fill(l, x);
     const LevelDev& d = lev[l].d;
-    if (d.const_sigma) {
-        const int zc = st_zchunk(d);
-        const dim3 grid((d.n[0] + GS_TX) / GS_TX, (d.n[1] + GS_TY) / GS_TY, (d.n[2] + zc) / zc);
-        NP_LAUNCH(true, (k_stencil_cs<0, false>), grid, dim3(256), ST_SMEM_BYTES, stream, d, st_coef(d), y, (const double*)x,
-                  (const double*)nullptr, (const double*)nullptr, part0, part1, zc);
-    } else {
-        NP_LAUNCH(true, (k_adotx<0, false, false>), grid_nodes(d), NP_BLK, 0, stream, d, y, x, (const double*)nullptr, (const double*)nullptr, lev[l].sigma, part0, part1);
-    }
+    const int zc = st_zchunk(d);
+    const dim3 grid((d.n[0] + GS_TX) / GS_TX, (d.n[1] + GS_TY) / GS_TY, (d.n[2] + zc) / zc);
+    const double* nul = nullptr;
+    if (d.const_sigma) NP_LAUNCH(true, (k_stencil<0, false, true>), grid, dim3(256), ST_SMEM_BYTES, stream, d, st_coef(d), y, (const double*)x, nul, nul, part0, part1, zc, nul);
+    else               NP_LAUNCH(true, (k_stencil<0, false, false>), grid, dim3(256), ST_SMEM_BYTES, stream, d, st_coef(d), y, (const double*)x, nul, nul, part0, part1, zc, (const double*)lev[l].sigma);
     ++launches;
 }
 
@@ -261,18 +261,18 @@ void NpSolver::residual(int l, double* y, double* x, const double* b, bool with_
 {
     fill(l, x);
     const LevelDev& d = lev[l].d;
+    const int zc = st_zchunk(d);
+    const dim3 grid((d.n[0] + GS_TX) / GS_TX, (d.n[1] + GS_TY) / GS_TY, (d.n[2] + zc) / zc);
+    const StCoef c = st_coef(d);
+    const double* sg = lev[l].sigma;
     if (d.const_sigma) {
-        const int zc = st_zchunk(d);
-        const dim3 grid((d.n[0] + GS_TX) / GS_TX, (d.n[1] + GS_TY) / GS_TY, (d.n[2] + zc) / zc);
-        const StCoef c = st_coef(d);
-        if (with_red) NP_LAUNCH(true, (k_stencil_cs<1, true>), grid, dim3(256), ST_SMEM_BYTES, stream, d, c, y, (const double*)x, b, boff, part0, part1, zc);
-        else          NP_LAUNCH(true, (k_stencil_cs<1, false>), grid, dim3(256), ST_SMEM_BYTES, stream, d, c, y, (const double*)x, b, boff, part0, part1, zc);
-        red_n = nblocks(grid);
+        if (with_red) NP_LAUNCH(true, (k_stencil<1, true, true>), grid, dim3(256), ST_SMEM_BYTES, stream, d, c, y, (const double*)x, b, boff, part0, part1, zc, sg);
+        else          NP_LAUNCH(true, (k_stencil<1, false, true>), grid, dim3(256), ST_SMEM_BYTES, stream, d, c, y, (const double*)x, b, boff, part0, part1, zc, sg);
     } else {
-        if (with_red) NP_LAUNCH(true, (k_adotx<1, false, true>), grid_nodes(d), NP_BLK, 0, stream, d, y, x, b, boff, lev[l].sigma, part0, part1);
-        else          NP_LAUNCH(true, (k_adotx<1, false, false>), grid_nodes(d), NP_BLK, 0, stream, d, y, x, b, boff, lev[l].sigma, part0, part1);
-        red_n = nblocks(grid_nodes(d));
+        if (with_red) NP_LAUNCH(true, (k_stencil<1, true, false>), grid, dim3(256), ST_SMEM_BYTES, stream, d, c, y, (const double*)x, b, boff, part0, part1, zc, sg);
+        else          NP_LAUNCH(true, (k_stencil<1, false, false>), grid, dim3(256), ST_SMEM_BYTES, stream, d, c, y, (const double*)x, b, boff, part0, part1, zc, sg);
     }
+    red_n = nblocks(grid);
     ++launches;
 }
 
