@@ -349,22 +349,18 @@ struct GsSmemX {   // 27-point accessor around tile-local node (li, lj) for the 
 // one add per address.  Source offsets are relative to the plane, destinations are split-layout slots.
 struct GsLoader {
     int src0, dst0, nrow_ok;     // first element; rows (counted from this thread's first) that exist
-    bool active;
     __device__ __forceinline__ void init(const LevelDev& L, int tid, int i0, int j0, bool zero_in) {
         const int c = tid % 66, r0 = tid / 66;           // column slot g = c+1, first row r0 (0..2); tid >= 198 idle
         const int g = c + 1, i = i0 + g - 2;
-        active = (tid < 198);
         // row index `row` (0..33) is node j = j0 + row - 1; it exists when j <= n1 + 1
         const int rows_exist = min(34, L.n[1] + 3 - j0);            // rows 0 .. rows_exist-1 exist
         nrow_ok = (i <= L.n[0] + 1 && !zero_in) ? rows_exist : 0;
         src0 = (int)(L.nsy * (long long)(j0 + r0) + (i + 1));      // row r0 -> j+1 = j0 + r0
         dst0 = ((g & 1) ? GS_HALF : 0) + r0 * GS_HP + (g >> 1);
-        if (!active) { src0 = 0; nrow_ok = 0; }
-        row_first = r0;
+        row_first = (tid < 198) ? r0 : 34;              // idle threads: no row passes the range test below
     }
     int row_first;
     __device__ __forceinline__ void load(double* dst_plane, const double* src_plane, long long nsy) const {
-        if (!active) return;
         const double* sp = src_plane + src0;
         double* dp = dst_plane + dst0;
 #pragma unroll
@@ -548,10 +544,11 @@ __device__ __forceinline__ void gs_zpart_var(const NpCoef& c, double (&B)[2][8],
     }
 }
 
-template <bool CS>
-__global__ void __launch_bounds__(256, CS ? 2 : 1) k_gs2(LevelDev L, GsArgs A)
+// Body of k_gs2.  FULL: the whole 64 x 32 tile lies inside the domain and no face is Dirichlet, so every node is
+// relaxed and the masks fold away at compile time (only the 63 x 31 write window remains).
+template <bool CS, bool FULL>
+__device__ __forceinline__ void gs2_run(const LevelDev& L, const GsArgs& A, double* ring)
 {
-    NP_DYN_SMEM(double, ring);
     const GsCoef& C = A.c;
     double* __restrict__ xout = A.xout; const double* __restrict__ xin = A.xin;
     const double* __restrict__ rhs = A.rhs; const double* __restrict__ sig = A.sig;
@@ -569,21 +566,23 @@ __global__ void __launch_bounds__(256, CS ? 2 : 1) k_gs2(LevelDev L, GsArgs A)
 
     // per-thread node masks, bit a*8+r: relaxed (valid node), Dirichlet in x/y, written by this tile
     unsigned act = 0, dir = 0, wrt = 0;
+    if (FULL) {
+        act = 0xffffu;
+        wrt = 0xffffu & ~((lane == 31 ? 0xff00u : 0u) | (wy == 3 ? 0x8080u : 0u));
+    } else {
 #pragma unroll
-    for (int a = 0; a < 2; ++a)
+        for (int a = 0; a < 2; ++a)
 #pragma unroll
-        for (int r = 0; r < 8; ++r) {
-            const int i = gi + a, j = gj + r;
-            const bool v = (i <= L.n[0] && j <= L.n[1]);
-            const bool dd = v && ((L.face[0] == NP_FACE_DIRICHLET && i == 0) || (L.face[3] == NP_FACE_DIRICHLET && i == L.n[0])
-                               || (L.face[1] == NP_FACE_DIRICHLET && j == 0) || (L.face[4] == NP_FACE_DIRICHLET && j == L.n[1]));
-            const bool w = v && (2 * lane + a < GS_WX) && (8 * wy + r < GS_WY);
-            act |= (unsigned)v << (a * 8 + r); dir |= (unsigned)dd << (a * 8 + r); wrt |= (unsigned)w << (a * 8 + r);
-        }
-    // whole tile inside the domain and no Dirichlet face anywhere: the colour steps need no masks
-    const bool any_dir = L.face[0] == NP_FACE_DIRICHLET || L.face[1] == NP_FACE_DIRICHLET || L.face[2] == NP_FACE_DIRICHLET
-                      || L.face[3] == NP_FACE_DIRICHLET || L.face[4] == NP_FACE_DIRICHLET || L.face[5] == NP_FACE_DIRICHLET;
-    const bool full = (i0 + GS_TX - 1 <= L.n[0]) && (j0 + GS_TY - 1 <= L.n[1]) && !any_dir;
+            for (int r = 0; r < 8; ++r) {
+                const int i = gi + a, j = gj + r;
+                const bool v = (i <= L.n[0] && j <= L.n[1]);
+                const bool dd = v && ((L.face[0] == NP_FACE_DIRICHLET && i == 0) || (L.face[3] == NP_FACE_DIRICHLET && i == L.n[0])
+                                   || (L.face[1] == NP_FACE_DIRICHLET && j == 0) || (L.face[4] == NP_FACE_DIRICHLET && j == L.n[1]));
+                const bool w = v && (2 * lane + a < GS_WX) && (8 * wy + r < GS_WY);
+                act |= (unsigned)v << (a * 8 + r); dir |= (unsigned)dd << (a * 8 + r); wrt |= (unsigned)w << (a * 8 + r);
+            }
+    }
+    constexpr bool full = FULL;
 
     GsLoader ld; ld.init(L, tid, i0, j0, A.zero_in != 0);
     auto slot = [&](int p) -> double* { return ring + ((p + 1) % GS_RING) * GS_PLANE; };     // p >= -1
@@ -599,6 +598,16 @@ __global__ void __launch_bounds__(256, CS ? 2 : 1) k_gs2(LevelDev L, GsArgs A)
 #pragma unroll
         for (int r = 0; r < 8; ++r) { x[a][r] = 0.0; B[a][r] = 0.0; }
 
+    auto load_rhs = [&](int pn) {                        // B <- raw rhs of plane pn (roff where the node is not relaxed)
+        const double* rp = rhs + np_noff(L, gi, gj, kb + pn);
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+            B[0][r] = (full || ((act >> r) & 1u)) ? rp[L.nsy * r] : roff;
+            B[1][r] = (full || ((act >> (8 + r)) & 1u)) ? rp[L.nsy * r + 1] : roff;
+        }
+    };
+    if (CS && grp == 0) load_rhs(0);
+
     for (int t = 0; t <= nk + 1; ++t) {
         if (t + 2 <= nk) load_plane(t + 2);
         np_cp_async_commit();
@@ -606,7 +615,7 @@ __global__ void __launch_bounds__(256, CS ? 2 : 1) k_gs2(LevelDev L, GsArgs A)
         const bool on = (p >= 0 && p <= nk - 1);
         const int k = kb + p;
         double* Pc = on ? slot(p) : ring;
-        const bool zdir = on && ((L.face[2] == NP_FACE_DIRICHLET && k == 0) || (L.face[5] == NP_FACE_DIRICHLET && k == L.n[2]));
+        const bool zdir = !FULL && on && ((L.face[2] == NP_FACE_DIRICHLET && k == 0) || (L.face[5] == NP_FACE_DIRICHLET && k == L.n[2]));
         const unsigned dmask = zdir ? act : dir;
         const long long gbase = on ? np_noff(L, gi, gj, k) : 0;
         if (A.addto && on && grp == 1 && p < nkw) {     // the add-to values are needed at the end of the step: pull them into L1 now
@@ -617,13 +626,7 @@ __global__ void __launch_bounds__(256, CS ? 2 : 1) k_gs2(LevelDev L, GsArgs A)
         if (CS) {
             if (on) {
                 // ---- B = rhs/diag - (out-of-plane part): 9-point stencil of S = x[k-1] + x[k+1] ----
-                double rv[2][8];                        // issued now, consumed after the stencil below
-                const double* rp = rhs + gbase;
-#pragma unroll
-                for (int r = 0; r < 8; ++r) {
-                    rv[0][r] = (full || ((act >> r) & 1u)) ? rp[L.nsy * r] : roff;
-                    rv[1][r] = (full || ((act >> (8 + r)) & 1u)) ? rp[L.nsy * r + 1] : roff;
-                }
+                // B arrives holding the raw right-hand side of this plane (loaded at the end of the previous step)
                 const double* Pm = slot(p - 1); const double* Pp = slot(p + 1);
 #pragma unroll
                 for (int rr = -1; rr <= 8; ++rr) {
@@ -640,7 +643,9 @@ __global__ void __launch_bounds__(256, CS ? 2 : 1) k_gs2(LevelDev L, GsArgs A)
                         B[1][rr] -= C.a_fz * s1 + C.a_exz * h1;
                     }
                     if (rr - 1 >= 0 && rr - 1 <= 7) { B[0][rr - 1] -= q0; B[1][rr - 1] -= q1; }
-                    if (rr + 1 >= 0 && rr + 1 <= 7) { B[0][rr + 1] = -q0; B[1][rr + 1] = -q1; }   // first touch of row rr+1
+                    if (rr + 1 >= 0 && rr + 1 <= 7) {      // first touch of row rr+1: rhs/diag comes in here
+                        B[0][rr + 1] = fma(B[0][rr + 1] - roff, C.dinv, -q0); B[1][rr + 1] = fma(B[1][rr + 1] - roff, C.dinv, -q1);
+                    }
                 }
                 // ---- own values of plane p ----
 #pragma unroll
@@ -648,13 +653,10 @@ __global__ void __launch_bounds__(256, CS ? 2 : 1) k_gs2(LevelDev L, GsArgs A)
                     x[0][r] = Pc[ofs + r * GS_HP + 1];
                     x[1][r] = Pc[GS_HALF + ofs + r * GS_HP + 1];
                 }
-#pragma unroll
-                for (int a = 0; a < 2; ++a)
-#pragma unroll
-                    for (int r = 0; r < 8; ++r) B[a][r] = fma(rv[a][r] - roff, C.dinv, B[a][r]);
             }
-            if (full) gs_colours_cs<false>(on, x, B, Pc, C, ofs, act, dmask, grp);
-            else      gs_colours_cs<true>(on, x, B, Pc, C, ofs, act, dmask, grp);
+            gs_colours_cs<!FULL>(on, x, B, Pc, C, ofs, act, dmask, grp);
+            // B is free now: fetch the raw right-hand side of this group's next plane so the loads fly across the barrier
+            if (p + 1 >= 0 && p + 1 <= nk - 1) load_rhs(p + 1);
         } else {
             // ---- variable sigma: B = rhs - (out-of-plane part through the two cell layers); V = column sums of sigma ----
             double V[3][9];
@@ -732,6 +734,17 @@ __global__ void __launch_bounds__(256, CS ? 2 : 1) k_gs2(LevelDev L, GsArgs A)
             }
         }
     }
+}
+
+template <bool CS>
+__global__ void __launch_bounds__(256, CS ? 2 : 1) k_gs2(LevelDev L, GsArgs A)
+{
+    NP_DYN_SMEM(double, ring);
+    const bool any_dir = L.face[0] == NP_FACE_DIRICHLET || L.face[1] == NP_FACE_DIRICHLET || L.face[2] == NP_FACE_DIRICHLET
+                      || L.face[3] == NP_FACE_DIRICHLET || L.face[4] == NP_FACE_DIRICHLET || L.face[5] == NP_FACE_DIRICHLET;
+    const bool full = ((int)blockIdx.x * GS_WX + GS_TX - 1 <= L.n[0]) && ((int)blockIdx.y * GS_WY + GS_TY - 1 <= L.n[1]) && !any_dir;
+    if (full) gs2_run<CS, true>(L, A, ring);
+    else      gs2_run<CS, false>(L, A, ring);
 }
 
 // ------------------------------------------------------------------------------------------------
