@@ -399,7 +399,7 @@ __device__ __forceinline__ void gs_colours_cs(bool on, double (&x)[2][8], const 
             Pc[ofs + r * GS_HP + 1] = x[0][r];
         }
     }
-    np_group_barrier(grp);   // only this sweep's warps exchange values inside a plane
+    __syncwarp();            // the next colour's new in-plane neighbours sit in the same row, i.e. the same warp
     // ---- colour 1: a = 1, r even ----
     if (on) {
         double xr[9];
@@ -428,7 +428,7 @@ __device__ __forceinline__ void gs_colours_cs(bool on, double (&x)[2][8], const 
             Pc[ofs + r * GS_HP + 1] = x[0][r];
         }
     }
-    np_group_barrier(grp);   // only this sweep's warps exchange values inside a plane
+    __syncwarp();            // the next colour's new in-plane neighbours sit in the same row, i.e. the same warp
     // ---- colour 3: a = 1, r odd ----
     if (on) {
         double xr[9];
@@ -473,7 +473,7 @@ __device__ __forceinline__ void gs_colours_var(bool on, double (&x)[2][8], const
             Pc[ofs + r * GS_HP + 1] = x[0][r];
         }
     }
-    np_group_barrier(grp);
+    __syncwarp();            // the next colour's new in-plane neighbours sit in the same row, i.e. the same warp
     if (on) {   // colour 1: a = 1, r even
         double xr[9];
 #pragma unroll
@@ -502,7 +502,7 @@ __device__ __forceinline__ void gs_colours_var(bool on, double (&x)[2][8], const
             Pc[ofs + r * GS_HP + 1] = x[0][r];
         }
     }
-    np_group_barrier(grp);
+    __syncwarp();            // the next colour's new in-plane neighbours sit in the same row, i.e. the same warp
     if (on) {   // colour 3: a = 1, r odd
         double xr[9];
 #pragma unroll
@@ -751,8 +751,8 @@ __global__ void __launch_bounds__(256, CS ? 2 : 1) k_gs2(LevelDev L, GsArgs A)
 // K2, constant sigma: y = A x  (MODE 0)  or  y = (b - *boff) - A x  (MODE 1), marching in z.
 // One CTA owns a 64 x 32 column chunk; each plane of x is staged ONCE in shared memory (cp.async, two
 // planes ahead, split even/odd layout as in k_gs2); each thread owns a 2 x 4 block of nodes and keeps,
-// per node, the in-plane 9-point sums of the last three planes in registers:
-//     y[k] = U[k] + V[k-1] + V[k+1],   U = same-plane weights (incl. diagonal), V = adjacent-plane weights.
+// per node, two running values in registers (the pending sum V[k-1] + U[k] and the last V):
+//     y[k] = (V[k-1] + U[k]) + V[k+1],   U = same-plane weights (incl. diagonal), V = adjacent-plane weights.
 // REDUCE: per-CTA partials of max|y| (all valid nodes) and sum(w*y) (owned nodes, dot-mask weights) —
 // the residual norm and the solvability offset of the next V-cycle come out of the same pass.
 // ------------------------------------------------------------------------------------------------
@@ -763,13 +763,24 @@ struct StCoef { double d, w_fx, w_fy, w_exy, w_fz, w_exz, w_eyz, w_c; };
 // CS = false (variable sigma): the same march; the plane arriving at step q contributes, through the cell layers below
 // and above it, D[q] to y[q-1], M[q] to y[q] and UP[q] to y[q+1]:  y[k] = UP[k-1] + M[k] + D[k+1]  (for constant sigma
 // D = UP = V).  Sigma comes through L1 (each cell is used by up to 8 nodes of neighbouring threads).
-template <int MODE, bool REDUCE, bool CS>
-__global__ void __launch_bounds__(256, CS ? 2 : 1) k_stencil(LevelDev L, StCoef C, double* __restrict__ y, const double* __restrict__ x,
-                                                          const double* __restrict__ b, const double* __restrict__ boff,
-                                                          double* __restrict__ part_max, double* __restrict__ part_sum, int zc,
-                                                          const double* __restrict__ sig)
+// x/y factor of the dot-mask weight of node (i, j): 0 when another rank / the periodic image owns it, 1/2 per Neumann face
+__device__ __forceinline__ double np_wgt_xy(const LevelDev& L, int i, int j)
 {
-    NP_DYN_SMEM(double, ring);
+    if (i > L.owned_hi[0] || j > L.owned_hi[1]) return 0.0;
+    double w = 1.0;
+    if (L.face[0] == NP_FACE_NEUMANN && i == 0) w *= 0.5;
+    if (L.face[3] == NP_FACE_NEUMANN && i == L.n[0]) w *= 0.5;
+    if (L.face[1] == NP_FACE_NEUMANN && j == 0) w *= 0.5;
+    if (L.face[4] == NP_FACE_NEUMANN && j == L.n[1]) w *= 0.5;
+    return w;
+}
+// FULL: the tile lies inside the domain, no face is Dirichlet and every dot-mask weight is 1: the masks fold away.
+template <int MODE, bool REDUCE, bool CS, bool FULL>
+__device__ __forceinline__ void st_run(const LevelDev& L, const StCoef& C, double* __restrict__ y, const double* __restrict__ x,
+                                       const double* __restrict__ b, const double* __restrict__ boff,
+                                       double* __restrict__ part_max, double* __restrict__ part_sum, int zc,
+                                       const double* __restrict__ sig, double* ring)
+{
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int i0 = blockIdx.x * GS_TX, j0 = blockIdx.y * GS_TY, kb = blockIdx.z * zc;
     const int nkl = min(kb + zc - 1, L.n[2]) - kb + 1;       // output planes kb .. kb+nkl-1
@@ -777,36 +788,31 @@ __global__ void __launch_bounds__(256, CS ? 2 : 1) k_stencil(LevelDev L, StCoef 
     const int row0 = 4 * warp + 1;
     const double off = (MODE == 1 && boff) ? boff[0] : 0.0;
 
-    unsigned act = 0, dir = 0;
-    double wgt[2][4];
+    unsigned act = FULL ? 0xffu : 0u, dir = 0;
+    bool wone = true;                                    // REDUCE: all eight dot-mask weights of this thread are 1
+    if (!FULL) {
 #pragma unroll
-    for (int a = 0; a < 2; ++a)
+        for (int a = 0; a < 2; ++a)
 #pragma unroll
-        for (int r = 0; r < 4; ++r) {
-            const int i = gi + a, j = gj + r;
-            const bool v = (i <= L.n[0] && j <= L.n[1]);
-            const bool dd = v && ((L.face[0] == NP_FACE_DIRICHLET && i == 0) || (L.face[3] == NP_FACE_DIRICHLET && i == L.n[0])
-                               || (L.face[1] == NP_FACE_DIRICHLET && j == 0) || (L.face[4] == NP_FACE_DIRICHLET && j == L.n[1]));
-            act |= (unsigned)v << (a * 4 + r); dir |= (unsigned)dd << (a * 4 + r);
-            double w = 0.0;
-            if (REDUCE && v && i <= L.owned_hi[0] && j <= L.owned_hi[1]) {
-                w = 1.0;
-                if (L.face[0] == NP_FACE_NEUMANN && i == 0) w *= 0.5;
-                if (L.face[3] == NP_FACE_NEUMANN && i == L.n[0]) w *= 0.5;
-                if (L.face[1] == NP_FACE_NEUMANN && j == 0) w *= 0.5;
-                if (L.face[4] == NP_FACE_NEUMANN && j == L.n[1]) w *= 0.5;
+            for (int r = 0; r < 4; ++r) {
+                const int i = gi + a, j = gj + r;
+                const bool v = (i <= L.n[0] && j <= L.n[1]);
+                const bool dd = v && ((L.face[0] == NP_FACE_DIRICHLET && i == 0) || (L.face[3] == NP_FACE_DIRICHLET && i == L.n[0])
+                                   || (L.face[1] == NP_FACE_DIRICHLET && j == 0) || (L.face[4] == NP_FACE_DIRICHLET && j == L.n[1]));
+                act |= (unsigned)v << (a * 4 + r); dir |= (unsigned)dd << (a * 4 + r);
+                if (REDUCE) wone = wone && (np_wgt_xy(L, i, j) == 1.0);
             }
-            wgt[a][r] = w;
-        }
+    }
 
     GsLoader ld; ld.init(L, tid, i0, j0, false);
     auto load_plane = [&](int k) { ld.load(ring + ((k + 1) % ST_RING) * GS_PLANE, x + L.nsz * (long long)(k + 1), L.nsy); };   // k in [-1, n2+1]
 
-    double Vm[2][4], Vc[2][4], Uc[2][4];
+    // per node: A1 = UP[q-2] + M[q-1] (y[q-1] still waiting for D[q]) and A2 = UP[q-1]
+    double A1[2][4], A2[2][4];
 #pragma unroll
     for (int a = 0; a < 2; ++a)
 #pragma unroll
-        for (int r = 0; r < 4; ++r) { Vm[a][r] = 0.0; Vc[a][r] = 0.0; Uc[a][r] = 0.0; }
+        for (int r = 0; r < 4; ++r) { A1[a][r] = 0.0; A2[a][r] = 0.0; }
     double tmax = 0.0, tsum = 0.0;
 
     load_plane(kb - 1); np_cp_async_commit();
@@ -827,8 +833,8 @@ __global__ void __launch_bounds__(256, CS ? 2 : 1) k_stencil(LevelDev L, StCoef 
         if (MODE == 1 && s >= 2) {
 #pragma unroll
             for (int r = 0; r < 4; ++r) {
-                bv[0][r] = ((act >> r) & 1u) ? b[gbase + L.nsy * r] : 0.0;
-                bv[1][r] = ((act >> (4 + r)) & 1u) ? b[gbase + L.nsy * r + 1] : 0.0;
+                bv[0][r] = (FULL || ((act >> r) & 1u)) ? b[gbase + L.nsy * r] : 0.0;
+                bv[1][r] = (FULL || ((act >> (4 + r)) & 1u)) ? b[gbase + L.nsy * r + 1] : 0.0;
             }
         }
         double Un[2][4], Vn[2][4], Dn[2][4];             // M[q], UP[q], D[q] of the node block
@@ -890,7 +896,7 @@ __global__ void __launch_bounds__(256, CS ? 2 : 1) k_stencil(LevelDev L, StCoef 
         }
         if (s >= 2) {                                    // output plane k = q-1
             const int k = q - 1;
-            const bool zdir = (L.face[2] == NP_FACE_DIRICHLET && k == 0) || (L.face[5] == NP_FACE_DIRICHLET && k == L.n[2]);
+            const bool zdir = !FULL && ((L.face[2] == NP_FACE_DIRICHLET && k == 0) || (L.face[5] == NP_FACE_DIRICHLET && k == L.n[2]));
             double wz = 1.0;
             if (REDUCE) {
                 if (k > L.owned_hi[2]) wz = 0.0;
@@ -900,22 +906,25 @@ __global__ void __launch_bounds__(256, CS ? 2 : 1) k_stencil(LevelDev L, StCoef 
             for (int a = 0; a < 2; ++a)
 #pragma unroll
                 for (int r = 0; r < 4; ++r) {
-                    if ((act >> (a * 4 + r)) & 1u) {
+                    if (FULL || ((act >> (a * 4 + r)) & 1u)) {
                         const long long o = gbase + a + L.nsy * r;
                         double v = 0.0;
-                        if (!(zdir || ((dir >> (a * 4 + r)) & 1u))) {
-                            const double ax = Uc[a][r] + (Vm[a][r] + Dn[a][r]);
+                        if (FULL || !(zdir || ((dir >> (a * 4 + r)) & 1u))) {
+                            const double ax = A1[a][r] + Dn[a][r];
                             v = (MODE == 1) ? (bv[a][r] - off) - ax : ax;
                         }
                         y[o] = v;
-                        if (REDUCE) { tmax = fmax(tmax, fabs(v)); tsum += (wgt[a][r] * wz) * v; }
+                        if (REDUCE) {
+                            tmax = fmax(tmax, fabs(v));
+                            tsum += ((FULL || wone) ? wz : np_wgt_xy(L, gi + a, gj + r) * wz) * v;      // boundary threads redo the weight
+                        }
                     }
                 }
         }
 #pragma unroll
         for (int a = 0; a < 2; ++a)
 #pragma unroll
-            for (int r = 0; r < 4; ++r) { Vm[a][r] = Vc[a][r]; Vc[a][r] = Vn[a][r]; Uc[a][r] = Un[a][r]; }
+            for (int r = 0; r < 4; ++r) { A1[a][r] = A2[a][r] + Un[a][r]; A2[a][r] = Vn[a][r]; }
     }
     if (REDUCE) {
         const double m = np_block_reduce<true>(tmax);
@@ -925,6 +934,26 @@ __global__ void __launch_bounds__(256, CS ? 2 : 1) k_stencil(LevelDev L, StCoef 
             part_max[bidx] = m; part_sum[bidx] = sm;
         }
     }
+}
+
+
+template <int MODE, bool REDUCE, bool CS>
+__global__ void __launch_bounds__(256, CS ? 2 : 1) k_stencil(LevelDev L, StCoef C, double* __restrict__ y, const double* __restrict__ x,
+                                                          const double* __restrict__ b, const double* __restrict__ boff,
+                                                          double* __restrict__ part_max, double* __restrict__ part_sum, int zc,
+                                                          const double* __restrict__ sig)
+{
+    NP_DYN_SMEM(double, ring);
+    const int i0 = blockIdx.x * GS_TX, j0 = blockIdx.y * GS_TY, i1 = i0 + GS_TX - 1, j1 = j0 + GS_TY - 1;
+    bool full = i1 <= L.n[0] && j1 <= L.n[1];
+#pragma unroll
+    for (int f = 0; f < 6; ++f) full = full && L.face[f] != NP_FACE_DIRICHLET;
+    if (REDUCE)
+        full = full && i1 <= L.owned_hi[0] && j1 <= L.owned_hi[1]
+            && !(L.face[0] == NP_FACE_NEUMANN && i0 == 0) && !(L.face[3] == NP_FACE_NEUMANN && i1 == L.n[0])
+            && !(L.face[1] == NP_FACE_NEUMANN && j0 == 0) && !(L.face[4] == NP_FACE_NEUMANN && j1 == L.n[1]);
+    if (full) st_run<MODE, REDUCE, CS, true>(L, C, y, x, b, boff, part_max, part_sum, zc, sig, ring);
+    else      st_run<MODE, REDUCE, CS, false>(L, C, y, x, b, boff, part_max, part_sum, zc, sig, ring);
 }
 
 // ------------------------------------------------------------------------------------------------
