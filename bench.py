@@ -227,7 +227,7 @@ def run_gpu(args):
     geom = Geometry(ncell, (0, 0, 0), prob_hi, [b == 0 for b in bclo])
     boxes = [((0, 0, r * n), (n - 1, n - 1, (r + 1) * n - 1)) for r in range(G)]
     P = NodalProjector(vel, sig, geom, LPInfo(), boxes=boxes, rank=rank, nranks=world, nccl_comm=comm, lib=L,
-                       profile_kernels=1)
+                       profile_kernels=1, smooth_zchunk=args.smooth_zchunk)
     P.setDomainBC(bclo, bchi)
     dof = n * n * n * G
     stream = torch.cuda.current_stream().cuda_stream
@@ -349,6 +349,7 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--smooth-zchunk", type=int, default=0, help="experiment knob: fixed smoother z-chunk on every level (0: the level rule)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -627,13 +627,19 @@ __device__ __forceinline__ void gs2_run(const LevelDev& L, const GsArgs& A, doub
             if (on) {
                 // ---- B = rhs/diag - (out-of-plane part): 9-point stencil of S = x[k-1] + x[k+1] ----
                 // B arrives holding the raw right-hand side of this plane (loaded at the end of the previous step)
+                // x still holds this thread's block of plane p-1 as the previous step left it (first plane: fetch it)
                 const double* Pm = slot(p - 1); const double* Pp = slot(p + 1);
+                if (p == 0) {
+#pragma unroll
+                    for (int r = 0; r < 8; ++r) { x[0][r] = Pm[ofs + r * GS_HP + 1]; x[1][r] = Pm[GS_HALF + ofs + r * GS_HP + 1]; }
+                }
 #pragma unroll
                 for (int rr = -1; rr <= 8; ++rr) {
                     const int ro = ofs + rr * GS_HP;
+                    const bool own = (rr >= 0 && rr <= 7);
                     const double sL = Pm[GS_HALF + ro] + Pp[GS_HALF + ro];
-                    const double s0 = Pm[ro + 1] + Pp[ro + 1];
-                    const double s1 = Pm[GS_HALF + ro + 1] + Pp[GS_HALF + ro + 1];
+                    const double s0 = (own ? x[0][rr & 7] : Pm[ro + 1]) + Pp[ro + 1];
+                    const double s1 = (own ? x[1][rr & 7] : Pm[GS_HALF + ro + 1]) + Pp[GS_HALF + ro + 1];
                     const double sR = Pm[ro + 2] + Pp[ro + 2];
                     const double h0 = sL + s1, h1 = s0 + sR;
                     const double q0 = C.a_eyz * s0 + C.a_c * h0, q1 = C.a_eyz * s1 + C.a_c * h1;

@@ -21,13 +21,23 @@ static int pick_zchunk(int nnodes_z, int target) {
     int nch = std::max(1, (nnodes_z + target / 2) / target);
     return (nnodes_z + nch - 1) / nch;
 }
-// Smoother z-chunk of a level: enough chunks to give the 148 SMs about four CTAs each, 8..32 planes per
-// chunk.  Part of the smoother's definition (DESIGN.md "smoother semantics"); the oracle restates it.
+// Smoother z-chunk of a level.  Small levels (one wave of 2 x 148 CTAs holds them with chunks of <= 32 planes): as many
+// chunks as fit the wave, down to 4 planes each, because a CTA marches through its planes one after the other and
+// the chunk length is the launch latency.  Large levels: enough chunks to give the 148 SMs about four CTAs each,
+// 8..32 planes per chunk.  The result is rounded up to an even number: chunk interfaces (frozen during a smooth) then
+// coincide with coarse-grid planes, which measurably improves the V-cycle contraction.
+// Part of the smoother's definition; the oracle restates it.
 static int gs_zchunk(int nx_nodes, int ny_nodes, int nz_nodes) {
     const int ncols = ((nx_nodes + GS_WX - 1) / GS_WX) * ((ny_nodes + GS_WY - 1) / GS_WY);
-    const int nch_want = (592 + ncols - 1) / ncols;
-    const int target = std::min(32, std::max(8, nz_nodes / nch_want));
-    return pick_zchunk(nz_nodes, target);
+    const int nch1 = std::min(296 / ncols, std::max(1, nz_nodes / 4));
+    int zc = 0;
+    if (nch1 >= 1 && (nz_nodes + nch1 - 1) / nch1 <= 32) zc = (nz_nodes + nch1 - 1) / nch1;
+    else {
+        const int nch_want = (592 + ncols - 1) / ncols;
+        const int target = std::min(32, std::max(8, nz_nodes / nch_want));
+        zc = pick_zchunk(nz_nodes, target);
+    }
+    return zc + (zc & 1);
 }
 
 static void fill_coef(LevelDev& d) {

@@ -360,14 +360,19 @@ static void fsmooth_tiled(const Level& L, MF& x, const MF& rhs, int nsweeps, con
         TileSpec ts = ts_in;
         if (ts.z_target != 0) {      // the GPU driver's rule (incflo_b200/csrc/np_solver.cu gs_zchunk / pick_zchunk)
             const int nn = o.hi[2]-o.lo[2]+1;
-            int target = ts.z_target;
-            if (target < 0) {        // enough z-chunks to fill the GPU, between 8 and 32 planes each
+            int target = ts.z_target, zc_small = 0;
+            if (target < 0) {
                 const int ncols = ((o.hi[0]-o.lo[0]+1 + ts.t[0]-1)/ts.t[0]) * ((o.hi[1]-o.lo[1]+1 + ts.t[1]-1)/ts.t[1]);
+                // small levels: as many chunks as fit one wave of 296 CTAs, at least 4 planes each
+                const int nch1 = std::min(296 / ncols, std::max(1, nn / 4));
+                if (nch1 >= 1 && (nn + nch1 - 1) / nch1 <= 32) zc_small = (nn + nch1 - 1) / nch1;
+                // large levels: enough z-chunks to fill the GPU, between 8 and 32 planes each
                 const int nch_want = (592 + ncols - 1) / ncols;
                 target = std::min(32, std::max(8, nn / nch_want));
             }
             const int nch = std::max(1, (nn + target/2) / target);
-            ts.t[2] = (nn + nch - 1) / nch;
+            ts.t[2] = zc_small > 0 ? zc_small : (nn + nch - 1) / nch;
+            if (ts.z_target < 0) ts.t[2] += ts.t[2] & 1;      // even: chunk interfaces on coarse-grid planes
         }
         int nt[3]; for (int d=0; d<3; ++d) nt[d] = (o.hi[d]-o.lo[d]+1 + ts.t[d]-1)/ts.t[d];
         const Fab& xin = x.f[b]; const Fab& sf = L.sigma.f[b]; const Fab& rf = rhs.f[b]; Fab& xo = out.f[b];
