@@ -69,7 +69,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -78,7 +78,11 @@ class ClockSampler:
 
     def _read(self):
         for ln in self.proc.stdout:
-            self.lines.append(ln.strip())
+            self.lines.append((time.time(), ln.strip()))
+
+    def mark(self):
+        """Start of the timed region: samples taken before this (warm-up, also under load) are only a fallback."""
+        self.t_mark = time.time()
 
     def stop(self):
         if not self.proc:
@@ -88,9 +92,14 @@ class ClockSampler:
             self.proc.wait(timeout=5)
         except Exception:
             self.proc.kill()
+        t_mark = getattr(self, "t_mark", 0.0)
+        timed = [ln for (t, ln) in self.lines if t >= t_mark]
+        window = "timed region"
+        if not timed:                         # region shorter than the sampling period: use the warm-up samples
+            timed, window = [ln for (_, ln) in self.lines][-5:], "warm-up steps just before the timed region"
         sm, smmax, pw, reasons = [], [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        for ln in timed:
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 7:
                 continue
@@ -104,7 +113,7 @@ class ClockSampler:
         if not sm:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
         return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(smmax), "power_w_max": max(pw),
-                "samples": len(sm), "reasons": sorted(reasons)}
+                "samples": len(sm), "window": window, "reasons": sorted(reasons)}
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -227,7 +236,7 @@ def run_gpu(args):
     geom = Geometry(ncell, (0, 0, 0), prob_hi, [b == 0 for b in bclo])
     boxes = [((0, 0, r * n), (n - 1, n - 1, (r + 1) * n - 1)) for r in range(G)]
     P = NodalProjector(vel, sig, geom, LPInfo(), boxes=boxes, rank=rank, nranks=world, nccl_comm=comm, lib=L,
-                       profile_kernels=1, smooth_zchunk=args.smooth_zchunk)
+                       profile_kernels=1, smooth_zchunk=args.smooth_zchunk, verbose=args.verbose)
     P.setDomainBC(bclo, bchi)
     dof = n * n * n * G
     stream = torch.cuda.current_stream().cuda_stream
@@ -241,12 +250,13 @@ def run_gpu(args):
         vel.data.copy_(vel0)
         return P.project(RTOL, ATOL, stream=stream)
 
-    for _ in range(args.warmup):
-        step()
     clocks = ClockSampler(local)
     if rank == 0:
-        clocks.start()
+        clocks.start()                        # nvidia-smi needs a moment to come up: start it before the warm-up
+    for _ in range(args.warmup):
+        step()
     barrier()
+    clocks.mark()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     vcycles = launches = 0
@@ -350,6 +360,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--smooth-zchunk", type=int, default=0, help="experiment knob: fixed smoother z-chunk on every level (0: the level rule)")
+    ap.add_argument("--verbose", type=int, default=0, help="nodal_proj.verbose (4: per-launch smoother times on stderr)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -305,6 +305,15 @@ __device__ __forceinline__ void np_cp_async8(double* smem_dst, const double* gsr
     asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;\n" :: "r"(d), "l"(gsrc), "r"(sz) : "memory");
 #endif
 }
+__device__ __forceinline__ void np_cp_async8_all(double* smem_dst, const double* gsrc)
+{
+#ifdef NP_EMU
+    *smem_dst = *gsrc;
+#else
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" :: "r"(d), "l"(gsrc) : "memory");
+#endif
+}
 __device__ __forceinline__ void np_prefetch_l1(const void* p)
 {
 #ifndef NP_EMU
@@ -360,17 +369,23 @@ struct GsLoader {
         row_first = (tid < 198) ? r0 : 34;              // idle threads: no row passes the range test below
     }
     int row_first;
+    // ALLVALID: every row and column of the tile plane exists (full tile, input is read): no zero-fill, no range tests
+    template <bool ALLVALID>
     __device__ __forceinline__ void load(double* dst_plane, const double* src_plane, long long nsy) const {
+        if (row_first >= 34) return;                         // idle threads: skip (a branch; warp 7 never enters)
         const double* sp = src_plane + src0;
         double* dp = dst_plane + dst0;
+        const long long step = 3 * nsy;
 #pragma unroll
         for (int it = 0; it < 12; ++it) {
-            const int row = row_first + 3 * it;
-            if (row < 34) {
-                const bool valid = row < nrow_ok;
-                np_cp_async8(dp, valid ? sp : src_plane, valid);
+            if (it < 11 || row_first == 0) {                 // rows row_first + 3*it < 34
+                if (ALLVALID) np_cp_async8_all(dp + 3 * GS_HP * it, sp);
+                else {
+                    const bool valid = row_first + 3 * it < nrow_ok;
+                    np_cp_async8(dp + 3 * GS_HP * it, valid ? sp : src_plane, valid);
+                }
             }
-            sp += 3 * nsy; dp += 3 * GS_HP;
+            sp += step;
         }
     }
 };
@@ -586,7 +601,10 @@ __device__ __forceinline__ void gs2_run(const LevelDev& L, const GsArgs& A, doub
 
     GsLoader ld; ld.init(L, tid, i0, j0, A.zero_in != 0);
     auto slot = [&](int p) -> double* { return ring + ((p + 1) % GS_RING) * GS_PLANE; };     // p >= -1
-    auto load_plane = [&](int p) { ld.load(slot(p), xin + L.nsz * (long long)(kb + p + 1), L.nsy); };   // planes -1 .. nk
+    auto load_plane = [&](int p) {                                                           // planes -1 .. nk
+        if (FULL && !A.zero_in) ld.template load<true>(slot(p), xin + L.nsz * (long long)(kb + p + 1), L.nsy);
+        else                    ld.template load<false>(slot(p), xin + L.nsz * (long long)(kb + p + 1), L.nsy);
+    };
 
     load_plane(-1); load_plane(0); load_plane(1);
     np_cp_async_commit(); np_cp_async_wait_all();
@@ -811,7 +829,7 @@ __device__ __forceinline__ void st_run(const LevelDev& L, const StCoef& C, doubl
     }
 
     GsLoader ld; ld.init(L, tid, i0, j0, false);
-    auto load_plane = [&](int k) { ld.load(ring + ((k + 1) % ST_RING) * GS_PLANE, x + L.nsz * (long long)(k + 1), L.nsy); };   // k in [-1, n2+1]
+    auto load_plane = [&](int k) { ld.template load<FULL>(ring + ((k + 1) % ST_RING) * GS_PLANE, x + L.nsz * (long long)(k + 1), L.nsy); };   // k in [-1, n2+1]
 
     // per node: A1 = UP[q-2] + M[q-1] (y[q-1] still waiting for D[q]) and A2 = UP[q-1]
     double A1[2][4], A2[2][4];

@@ -705,6 +705,11 @@ int NpSolver::project(np_fab* vel, const np_fab* sigma, double rtol, double atol
     stats.kernel_launches = launches;
     stats.n_smooth0 = prof_n / 2; stats.ms_smooth0 = 0.0;
     for (int e = 0; e < prof_n; e += 2) stats.ms_smooth0 += np_rt::event_ms(prof_ev[e], prof_ev[e + 1]);
+    if (opt.verbose >= 4) {     // per-launch times of the level-0 smoother (first V-cycle: zero-input, plain, plain, add-to)
+        fprintf(stderr, "[nodalproj] level-0 smoother launches (ms):");
+        for (int e = 0; e < prof_n && e < 32; e += 2) fprintf(stderr, " %.3f", np_rt::event_ms(prof_ev[e], prof_ev[e + 1]));
+        fprintf(stderr, "\n");
+    }
     if (np_rt::last_error()) { stats.status = NP_ERR_CUDA; return NP_ERR_CUDA; }
     if (err) { stats.status = err; return err; }
     have_result = true;
