@@ -459,6 +459,21 @@ __device__ __forceinline__ void gs_colours_cs(bool on, double (&x)[2][8], const 
     }
 }
 
+// 1/d for a normal, non-zero d to within an ulp or two: hardware seed (20 bits) + two Newton steps.  A full IEEE
+// division costs several times as much in fp64 and sits on the critical path of every Gauss-Seidel update.
+__device__ __forceinline__ double np_rcp(double d)
+{
+#ifdef NP_EMU
+    return 1.0 / d;
+#else
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
+    double e = fma(-d, r, 1.0);
+    r = fma(r, e, r);
+    e = fma(-d, r, 1.0);
+    return fma(r, e, r);
+#endif
+}
 // Variable sigma: the same four colour steps; V[c][q] = sigma_below + sigma_above of the cell column (c, q) around the
 // thread's block (c = 0..2 <-> cells gi-1..gi+1, q = 0..8 <-> cells gj-1..gj+7), so node (a, r) sees the four columns
 // V[a][r], V[a+1][r], V[a][r+1], V[a+1][r+1].  B holds rhs minus the out-of-plane part; x_new = (B - in-plane) / diag.
@@ -468,7 +483,7 @@ __device__ __forceinline__ double gs_upd_var(const NpCoef& c, double Bv, double 
     const double inpl = c.f4xm2ym2z * (xW * (v00 + v01) + xE * (v10 + v11)) + c.fm2x4ym2z * (xS * (v00 + v10) + xN * (v01 + v11))
                       + c.f2x2ymz * ((xSW * v00 + xSE * v10) + (xNW * v01 + xNE * v11));
     const double diag = -4.0 * c.fxyz * ((v00 + v10) + (v01 + v11));
-    return (Bv - inpl) / diag;
+    return (Bv - inpl) * np_rcp(diag);
 }
 __device__ __forceinline__ void gs_colours_var(bool on, double (&x)[2][8], const double (&B)[2][8], const double (&V)[3][9], double* Pc,
                                                const NpCoef& c, int ofs, unsigned act, unsigned dmask, int grp)
@@ -1022,13 +1037,13 @@ struct InterpCtx {
     __device__ __forceinline__ double line(int i, int j, int k, int d) const {
         const double w1 = quad(i,j,k,d,0), w2 = quad(i,j,k,d,1);
         const int di = d == 0, dj = d == 1, dk = d == 2;
-        return (w1 * crse(i-di, j-dj, k-dk) + w2 * crse(i+di, j+dj, k+dk)) / (w1 + w2);
+        return (w1 * crse(i-di, j-dj, k-dk) + w2 * crse(i+di, j+dj, k+dk)) * np_rcp(w1 + w2);
     }
     __device__ __forceinline__ double face(int i, int j, int k, int da, int db) const {
         const double wa0 = quad(i,j,k,da,0), wa1 = quad(i,j,k,da,1), wb0 = quad(i,j,k,db,0), wb1 = quad(i,j,k,db,1);
         const int ai = da == 0, aj = da == 1, ak = da == 2, bi = db == 0, bj = db == 1, bk = db == 2;
         return (wa0 * line(i-ai, j-aj, k-ak, db) + wa1 * line(i+ai, j+aj, k+ak, db)
-              + wb0 * line(i-bi, j-bj, k-bk, da) + wb1 * line(i+bi, j+bj, k+bk, da)) / ((wa0 + wa1) + (wb0 + wb1));
+              + wb0 * line(i-bi, j-bj, k-bk, da) + wb1 * line(i+bi, j+bj, k+bk, da)) * np_rcp((wa0 + wa1) + (wb0 + wb1));
     }
     __device__ __forceinline__ double centre(int i, int j, int k) const {
         const double x0 = quad(i,j,k,0,0), x1 = quad(i,j,k,0,1), y0 = quad(i,j,k,1,0), y1 = quad(i,j,k,1,1),
@@ -1036,7 +1051,7 @@ struct InterpCtx {
         const double num = (x0 * face(i-1,j,k,1,2) + x1 * face(i+1,j,k,1,2))
                          + (y0 * face(i,j-1,k,2,0) + y1 * face(i,j+1,k,2,0))
                          + (z0 * face(i,j,k-1,0,1) + z1 * face(i,j,k+1,0,1));
-        return num / (((x0 + x1) + (y0 + y1)) + (z0 + z1));
+        return num * np_rcp(((x0 + x1) + (y0 + y1)) + (z0 + z1));
     }
 };
 
@@ -1047,7 +1062,7 @@ __device__ __forceinline__ double np_interp_face(const InterpCtx& ctx, int i, in
                                                  double la0, double la1, double lb0, double lb1)
 {   // la0/la1: db-lines at the node's low/high neighbour along da;  lb0/lb1: da-lines at its neighbours along db
     const double wa0 = ctx.quad(i,j,k,da,0), wa1 = ctx.quad(i,j,k,da,1), wb0 = ctx.quad(i,j,k,db,0), wb1 = ctx.quad(i,j,k,db,1);
-    return (wa0 * la0 + wa1 * la1 + wb0 * lb0 + wb1 * lb1) / ((wa0 + wa1) + (wb0 + wb1));
+    return (wa0 * la0 + wa1 * la1 + wb0 * lb0 + wb1 * lb1) * np_rcp((wa0 + wa1) + (wb0 + wb1));
 }
 __global__ void __launch_bounds__(128) k_interp_add_w(LevelDev Lf, LevelDev Lc, double* __restrict__ fine, const double* __restrict__ crse,
                                                       const double* __restrict__ sig, int koffc)
@@ -1088,7 +1103,7 @@ __global__ void __launch_bounds__(128) k_interp_add_w(LevelDev Lf, LevelDev Lc, 
         const double x0 = ctx.quad(ic,jc,kc,0,0), x1 = ctx.quad(ic,jc,kc,0,1), y0 = ctx.quad(ic,jc,kc,1,0), y1 = ctx.quad(ic,jc,kc,1,1),
                      z0 = ctx.quad(ic,jc,kc,2,0), z1 = ctx.quad(ic,jc,kc,2,1);
         const double num = (x0 * fyz[0] + x1 * fyz[1]) + (y0 * fxz[0] + y1 * fxz[1]) + (z0 * fxy[0] + z1 * fxy[1]);
-        v[1][1][1] = num / (((x0 + x1) + (y0 + y1)) + (z0 + z1));
+        v[1][1][1] = num * np_rcp(((x0 + x1) + (y0 + y1)) + (z0 + z1));
     }
 #pragma unroll
     for (int c = 0; c < 2; ++c)
