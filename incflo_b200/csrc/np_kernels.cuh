@@ -699,6 +699,15 @@ __device__ __forceinline__ void gs2_run(const LevelDev& L, const GsArgs& A, doub
         } else {
             // ---- variable sigma: B = rhs - (out-of-plane part through the two cell layers); V = column sums of sigma ----
             double V[3][9];
+            if (on && p + 1 <= nk - 1) {
+                // this thread's next plane: pull its right-hand side and the sigma layer above it into L1 while this plane is
+                // being relaxed (one CTA per SM leaves a large L1), so the loads at the top of the next step are hits
+#pragma unroll
+                for (int r = 0; r < 8; ++r) np_prefetch_l1(rhs + gbase + L.nsz + L.nsy * r);
+                const double* sn = sig + L.csz * (long long)(k + 2) + (min(gi, L.n[0]) + 1);
+#pragma unroll
+                for (int q = 0; q < 9; ++q) np_prefetch_l1(sn + L.csy * (long long)(min(gj - 1 + q, L.n[1]) + 1));
+            }
             if (on) {
                 const double* rp = rhs + gbase;
 #pragma unroll
