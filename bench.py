@@ -53,7 +53,7 @@ def read_traffic(const_sigma):
     if os.path.exists(p):
         with open(p) as f:
             d = json.load(f)
-        return d.get("k_smooth_const" if const_sigma else "k_smooth_var")
+        return d.get("k_gs2_const" if const_sigma else "k_gs2_var")
     return None
 
 
@@ -317,7 +317,7 @@ def run_gpu(args):
         avg_ms = ms_smooth / max(n_smooth, 1)
         achieved = alg_bytes / (avg_ms * 1e-3) / 1e9 if avg_ms > 0 else 0.0
         compulsory = (24 if const_sigma else 32) * nodes            # what the fused 2-sweep pass must move
-        roof = {"bound": "hbm", "kernel": f"k_smooth_tiled<{'const' if const_sigma else 'var'} sigma> level 0",
+        roof = {"bound": "hbm", "kernel": f"k_gs2<{'const' if const_sigma else 'variable'} sigma> (fused 2-sweep Gauss-Seidel), level 0",
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": read_traffic(const_sigma),
                 "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes, "avg_launch_ms": avg_ms,
                 "launches_timed": int(n_smooth), "share_of_step": ms_smooth / ms,
