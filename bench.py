@@ -236,7 +236,9 @@ def run_gpu(args):
     geom = Geometry(ncell, (0, 0, 0), prob_hi, [b == 0 for b in bclo])
     boxes = [((0, 0, r * n), (n - 1, n - 1, (r + 1) * n - 1)) for r in range(G)]
     P = NodalProjector(vel, sig, geom, LPInfo(), boxes=boxes, rank=rank, nranks=world, nccl_comm=comm, lib=L,
-                       profile_kernels=1, smooth_zchunk=args.smooth_zchunk, verbose=args.verbose)
+                       profile_kernels=1, smooth_zchunk=args.smooth_zchunk, verbose=args.verbose,
+                       **({"agg_min_local_nz": args.agg_min_local_nz} if args.agg_min_local_nz > 0 else {}),
+                       **({"overlap_halo": 0} if args.no_overlap else {}))
     P.setDomainBC(bclo, bchi)
     dof = n * n * n * G
     stream = torch.cuda.current_stream().cuda_stream
@@ -360,6 +362,8 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--smooth-zchunk", type=int, default=0, help="experiment knob: fixed smoother z-chunk on every level (0: the level rule)")
+    ap.add_argument("--agg-min-local-nz", type=int, default=0, help="experiment knob: replicate MG levels whose slab is thinner than this (0: library default)")
+    ap.add_argument("--no-overlap", action="store_true", help="experiment knob: halo exchange on the solver stream (overlap_halo=0)")
     ap.add_argument("--verbose", type=int, default=0, help="nodal_proj.verbose (4: per-launch smoother times on stderr)")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -122,6 +122,26 @@ __global__ void __launch_bounds__(256) k_fill_boundary(LevelDev L, double* x)
     }
 }
 
+// The x / y part of k_fill_boundary for nk planes starting at k0 only: what the planes handed to a neighbour rank need
+// before they leave (the halo exchange sends whole planes, ghost columns included).
+__global__ void __launch_bounds__(256) k_fill_xy_planes(LevelDev L, double* x, int k0, int nk)
+{
+    const int e0 = L.n[0] + 3, e1 = L.n[1] + 3;
+    const long long per = 3LL * e1 + 3LL * e0;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < per * nk; t += (long long)gridDim.x * blockDim.x) {
+        const int k = k0 + (int)(t / per);
+        long long q = t % per;
+        int i, j;
+        if (q < 3LL * e1) { const int s = (int)(q % 3); j = (int)(q / 3) - 1; i = s == 0 ? -1 : L.n[0] + s - 1; }
+        else { q -= 3LL * e1; const int s = (int)(q % 3); i = (int)(q / 3) - 1; j = s == 0 ? -1 : L.n[1] + s - 1; }
+        const int si = np_map_index(i, L.n[0], L.map_lo[0], L.map_hi[0]);
+        const int sj = np_map_index(j, L.n[1], L.map_lo[1], L.map_hi[1]);
+        if (si == i && sj == j) continue;
+        if (si < 0 || si > L.n[0] || sj < 0 || sj > L.n[1]) continue;
+        x[np_noff(L, i, j, k)] = x[np_noff(L, si, sj, k)];
+    }
+}
+
 // sigma ghost layer: periodic wrap, else copy of the adjacent interior cell (MLNodeLaplacian::FillBoundaryCoeff)
 // fill_z = 0 leaves the z ghost layers to the halo exchange (rank-interior faces).
 __global__ void __launch_bounds__(256) k_fill_sigma(LevelDev L, double* s, int per0, int per1, int per2, int zlo_local, int zhi_local)
@@ -293,6 +313,7 @@ struct GsArgs {
     const double* boff;      // optional device scalar subtracted from rhs (lazy makeSolvable), or null
     const double* addto;     // optional: xout = addto + result (xout may alias addto), or null
     int zc, zero_in;         // z-chunk; 1: xin is known to be zero and is not read
+    int zmap0, zmapS;        // z-chunk of a CTA = zmap0 + blockIdx.z * zmapS (a launch may cover only the end chunks)
 };
 
 __device__ __forceinline__ void np_cp_async8(double* smem_dst, const double* gsrc, bool valid)
@@ -587,7 +608,7 @@ __device__ __forceinline__ void gs2_run(const LevelDev& L, const GsArgs& A, doub
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int grp = warp >> 2;                           // 0: first sweep (plane t), 1: second sweep (plane t-2)
     const int wy = warp & 3;                             // tile rows 8*wy .. 8*wy+7
-    const int i0 = blockIdx.x * GS_WX, j0 = blockIdx.y * GS_WY, kb = blockIdx.z * zc;
+    const int i0 = blockIdx.x * GS_WX, j0 = blockIdx.y * GS_WY, kb = (A.zmap0 + (int)blockIdx.z * A.zmapS) * zc;
     const int nk  = min(kb + zc, L.n[2]) - kb + 1;       // relaxed planes p = 0..nk-1 (global k = kb+p)
     const int nkw = min(kb + zc - 1, L.n[2]) - kb + 1;   // written planes
     const int gi = i0 + 2 * lane, gj = j0 + 8 * wy;      // first node of this thread's 2 x 8 block

@@ -28,6 +28,9 @@ inline int host_free(void* p) { std::free(p); return 0; }
 inline int memset_async(void* p, int v, size_t n, np_stream_t) { std::memset(p, v, n); return 0; }
 inline int copy_async(void* d, const void* s, size_t n, np_stream_t) { std::memmove(d, s, n); return 0; }
 inline int stream_sync(np_stream_t) { return 0; }
+inline int stream_create(np_stream_t* s) { *s = nullptr; return 0; }
+inline int stream_destroy(np_stream_t) { return 0; }
+inline int stream_wait_event(np_stream_t, np_event_t) { return 0; }     // the emulation runs everything in program order
 inline int is_device_ptr(const void*) { return 1; }
 inline int event_create(np_event_t* e) { *e = new np_event_s(); return 0; }
 inline int event_destroy(np_event_t e) { delete e; return 0; }
@@ -57,6 +60,9 @@ inline int host_free(void* p) { return cudaFreeHost(p) == cudaSuccess ? 0 : 1; }
 inline int memset_async(void* p, int v, size_t n, np_stream_t s) { return cudaMemsetAsync(p, v, n, s) == cudaSuccess ? 0 : 1; }
 inline int copy_async(void* d, const void* s, size_t n, np_stream_t st) { return cudaMemcpyAsync(d, s, n, cudaMemcpyDefault, st) == cudaSuccess ? 0 : 1; }
 inline int stream_sync(np_stream_t s) { return cudaStreamSynchronize(s) == cudaSuccess ? 0 : 1; }
+inline int stream_create(np_stream_t* s) { return cudaStreamCreateWithFlags(s, cudaStreamNonBlocking) == cudaSuccess ? 0 : 1; }
+inline int stream_destroy(np_stream_t s) { return cudaStreamDestroy(s) == cudaSuccess ? 0 : 1; }
+inline int stream_wait_event(np_stream_t s, np_event_t e) { return cudaStreamWaitEvent(s, e, 0) == cudaSuccess ? 0 : 1; }
 inline int is_device_ptr(const void* p) {
     cudaPointerAttributes a;
     if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return 0; }

@@ -138,6 +138,10 @@ int NpSolver::create(const np_geom* g, int nboxes, const np_box* boxes, const in
         zero(agg_send, m); zero(agg_recv, m * nranks);
     }
     for (int e = 0; e < 4; ++e) np_rt::event_create(&ev[e]);
+    if (nranks > 1 && opt.overlap_halo) {
+        have_comm_stream = np_rt::stream_create(&comm_stream) == 0;
+        np_rt::event_create(&ev_halo[0]); np_rt::event_create(&ev_halo[1]);
+    }
     if (opt.profile_kernels) { prof_ev.resize(2048); for (auto& e : prof_ev) np_rt::event_create(&e); }
     for (auto& L : lev) setup_level_bc(L);
 #ifndef NP_EMU
@@ -166,6 +170,8 @@ void NpSolver::destroy()
     if (bot_out) np_rt::dev_free(bot_out);
     if (h_bot_out) np_rt::host_free(h_bot_out);
     for (int e = 0; e < 4; ++e) if (ev[e]) np_rt::event_destroy(ev[e]);
+    if (have_comm_stream) { np_rt::stream_sync(comm_stream); np_rt::stream_destroy(comm_stream); have_comm_stream = false; }
+    for (int e = 0; e < 2; ++e) if (ev_halo[e]) { np_rt::event_destroy(ev_halo[e]); ev_halo[e] = 0; }
     for (auto& e : prof_ev) np_rt::event_destroy(e);
     prof_ev.clear();
 }
@@ -269,7 +275,7 @@ void NpSolver::apply(int l, double* y, double* x)
 // sum of y) for finish_norm: the inf-norm and the next solvability offset come out of the residual pass.
 void NpSolver::residual(int l, double* y, double* x, const double* b, bool with_red, const double* boff)
 {
-    fill(l, x);
+    if (!(x == lev[l].cor && lev[l].cor_ghost_clean)) fill(l, x);      // a smooth leaves the correction with clean ghosts
     const LevelDev& d = lev[l].d;
     const int zc = st_zchunk(d);
     const dim3 grid((d.n[0] + GS_TX) / GS_TX, (d.n[1] + GS_TY) / GS_TY, (d.n[2] + zc) / zc);
@@ -339,6 +345,7 @@ void NpSolver::smooth(int l, bool zero_in, double* add_to)
     GsArgs ga{};
     ga.xout = add_to ? add_to : L.cor_alt; ga.xin = L.cor; ga.rhs = L.res; ga.sig = L.sigma;
     ga.boff = (l == 0) ? lvl0_off : nullptr; ga.addto = add_to; ga.zc = L.zc; ga.zero_in = zero_in ? 1 : 0;
+    ga.zmap0 = 0; ga.zmapS = 1;
     if (d.const_sigma) {
         // constant sigma: the 26 neighbours fall into 7 weight classes; everything is pre-divided by the diagonal
         const double sg = d.sigma0, dinv = 1.0 / (-32.0 * d.c.fxyz * sg);
@@ -347,11 +354,44 @@ void NpSolver::smooth(int l, bool zero_in, double* add_to)
         gc.a_fx = 4.0 * d.c.f4xm2ym2z * sg * dinv; gc.a_fy = 4.0 * d.c.fm2x4ym2z * sg * dinv; gc.a_fz = 4.0 * d.c.fm2xm2y4z * sg * dinv;
         gc.a_exy = 2.0 * d.c.f2x2ymz * sg * dinv; gc.a_exz = 2.0 * d.c.f2xmy2z * sg * dinv; gc.a_eyz = 2.0 * d.c.fmx2y2z * sg * dinv;
         gc.a_c = d.c.fxyz * sg * dinv;
-        NP_LAUNCH(true, (k_gs2<true>), grid, dim3(256), smem, stream, d, ga);
-    } else {
-        NP_LAUNCH(true, (k_gs2<false>), grid, dim3(256), smem, stream, d, ga);
     }
-    ++launches;
+    auto launch = [&](int nz) {
+        const dim3 g(grid.x, grid.y, nz);
+        if (d.const_sigma) NP_LAUNCH(true, (k_gs2<true>), g, dim3(256), smem, stream, d, ga);
+        else               NP_LAUNCH(true, (k_gs2<false>), g, dim3(256), smem, stream, d, ga);
+        ++launches;
+    };
+    // Sharded level: relax the two end z-chunks first and ship their planes to the neighbours on the comm stream while
+    // the interior chunks are relaxed (FillBoundary overlapped with the interior work).  The end chunks write the
+    // planes that are sent (k = 0, 1, n2-1) as long as a chunk has two planes, which gs_zchunk guarantees.
+    const int nch = (int)grid.z;
+    // (only where the interior launch still fills the GPU several times over: on a one-wave level the split would double the latency)
+    const bool split = !add_to && have_comm_stream && is_sharded(*this, L) && nch >= 3 && L.zc >= 2
+                    && (opt.overlap_halo < 0 || (long long)grid.x * grid.y * (nch - 2) >= 4LL * 2 * np_rt::sm_count())
+                    && (long long)(nch - 1) * L.zc <= d.n[2] - 1;          // the last chunk holds plane n2-1
+    if (split) {
+        ga.zmap0 = 0; ga.zmapS = nch - 1; launch(2);
+        np_rt::event_record(ev_halo[0], stream);
+        np_rt::stream_wait_event(comm_stream, ev_halo[0]);
+        double* xo = L.cor_alt;
+        const long long per = 3LL * (d.n[1] + 3) + 3LL * (d.n[0] + 3);
+        NP_LAUNCH(false, k_fill_xy_planes, dim3(shell_blocks(per * 2)), dim3(256), 0, comm_stream, d, xo, 0, 2); ++launches;
+        NP_LAUNCH(false, k_fill_xy_planes, dim3(shell_blocks(per)), dim3(256), 0, comm_stream, d, xo, d.n[2] - 1, 1); ++launches;
+        int lo, hi; z_neighbours(*this, lo, hi);
+        const long long pl = d.nsz;
+        if (comm.sendrecv(comm.ctx, xo + pl * 1, 2 * pl, xo + 0, pl, xo + pl * (long long)d.n[2], pl,
+                          xo + pl * (long long)(d.n[2] + 1), 2 * pl, lo, hi, (void*)comm_stream)) err = NP_ERR_NCCL;
+        np_rt::event_record(ev_halo[1], comm_stream);
+        ga.zmap0 = 1; ga.zmapS = 1; launch(nch - 2);
+        if (prof) { np_rt::event_record(prof_ev[prof_n + 1], stream); prof_n += 2; }
+        std::swap(L.cor, L.cor_alt);
+        np_rt::stream_wait_event(stream, ev_halo[1]);
+        const long long nshell = 3LL * ((long long)(d.n[1]+3)*(d.n[2]+3) + (long long)(d.n[0]+3)*(d.n[2]+3) + (long long)(d.n[0]+3)*(d.n[1]+3));
+        NP_LAUNCH(false, k_fill_boundary, dim3(shell_blocks(nshell)), dim3(256), 0, stream, d, L.cor); ++launches;
+        L.cor_ghost_clean = true;
+        return;
+    }
+    launch(nch);
     if (prof) { np_rt::event_record(prof_ev[prof_n + 1], stream); prof_n += 2; }
     if (add_to) { L.cor_ghost_clean = false; return; }
     std::swap(L.cor, L.cor_alt);

@@ -55,6 +55,9 @@ struct NpSolver {
     double* stage[3] = {nullptr, nullptr, nullptr}; long long stage_n[3] = {0, 0, 0};   // persistent device staging
     np_stream_t stream = 0;
     np_event_t ev[4] = {0,0,0,0};
+    np_stream_t comm_stream = 0;       // multi-GPU: halo exchange of the end chunks runs here, beside the interior chunks
+    np_event_t ev_halo[2] = {0, 0};    // [0] end chunks done (solver stream), [1] exchange done (comm stream)
+    bool have_comm_stream = false;
     std::vector<np_event_t> prof_ev;   // profile_kernels: start/stop pairs around level-0 smoother launches
     int prof_n = 0;
     np_stats stats{};

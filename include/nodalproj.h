@@ -73,10 +73,14 @@ typedef struct {
     int smooth_zchunk;          /* written planes per smoother tile in z; <=0: chosen per level */
     int interp_sigma_weighted;  /* 1: mlndlap_interpadd_aa weights (default); 0: plain trilinear */
     int bottom_normalize;       /* 1: MLCGSolver's Lp.normalize (default) */
-    int agg_min_local_nz;       /* multi-GPU: replicate MG levels whose slab is thinner than this; default 16 */
-    int use_graph;              /* capture the V-cycle in a CUDA graph; default 1 */
+    int agg_min_local_nz;       /* multi-GPU: replicate MG levels whose slab is thinner than this; default 64 */
+    int use_graph;              /* reserved (CUDA-graph capture of the V-cycle is not implemented); ignored */
     int const_sigma_fastpath;   /* use the constant-coefficient kernels when sigma is uniform; default 1 */
     int profile_kernels;        /* bracket every level-0 smoother launch with CUDA events (np_stats.ms_smooth0); default 0 */
+    int overlap_halo;           /* multi-GPU: smooth the end z-chunks first and exchange their planes on a second stream
+                                   while the interior chunks are relaxed (levels of >= 4 waves of CTAs only); default 0:
+                                   measured 1.4 % slower than the plain order on 2 B200s; < 0: on every
+                                   sharded level with three or more chunks (tests) */
 } np_options;
 
 typedef struct {

@@ -24,7 +24,7 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, name, ncell, kw, agg_min, outdir):
+def _worker(rank, world, port, name, ncell, kw, agg_min, overlap, outdir):
     import torch
     import torch.distributed as dist
     from incflo_b200.projector import Fab, Geometry, LPInfo, NodalProjector
@@ -76,7 +76,7 @@ def _worker(rank, world, port, name, ncell, kw, agg_min, outdir):
     geom = Geometry(ncell, prob["prob_lo"], prob["prob_hi"], [b == 0 for b in prob["bclo"]])
     boxes = [((0, 0, r * nzl), (ncell[0] - 1, ncell[1] - 1, (r + 1) * nzl - 1)) for r in range(world)]
     P = NodalProjector(vel, sig, geom, LPInfo(), boxes=boxes, rank=rank, nranks=world, nccl_comm=1, lib=L,
-                       agg_min_local_nz=agg_min)
+                       agg_min_local_nz=agg_min, overlap_halo=overlap)
     P.setDomainBC(prob["bclo"], prob["bchi"])
     st = P.project(1e-11, 1e-14)
     np.savez(os.path.join(outdir, f"r{rank}.npz"), u=vel.numpy_valid(), phi=P.getPhi().numpy_valid()[0],
@@ -88,17 +88,18 @@ def _worker(rank, world, port, name, ncell, kw, agg_min, outdir):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("name,ncell,kw,agg_min,agg_level", [
-    ("double_shear", (16, 16, 64), dict(zwave=True, prob_hi=(1.0, 1.0, 4.0)), 16, 2),
-    ("rayleigh_taylor", (16, 16, 32), {}, 4, 3),
+@pytest.mark.parametrize("name,ncell,kw,agg_min,agg_level,overlap", [
+    ("double_shear", (16, 16, 64), dict(zwave=True, prob_hi=(1.0, 1.0, 4.0)), 16, 2, 0),
+    ("double_shear", (16, 16, 64), dict(zwave=True, prob_hi=(1.0, 1.0, 4.0)), 16, 2, -1),   # end chunks first + exchange beside the interior
+    ("rayleigh_taylor", (16, 16, 32), {}, 4, 3, -1),
 ])
-def test_two_ranks_match_oracle(tmp_path, name, ncell, kw, agg_min, agg_level):
+def test_two_ranks_match_oracle(tmp_path, name, ncell, kw, agg_min, agg_level, overlap):
     import torch.multiprocessing as mp
     from oracle.oracle import Oracle, TILED
 
     nphelp.emu_lib()           # build once, before the ranks start
     world = 2
-    mp.spawn(_worker, args=(world, _free_port(), name, ncell, kw, agg_min, str(tmp_path)), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, _free_port(), name, ncell, kw, agg_min, overlap, str(tmp_path)), nprocs=world, join=True)
     r = [np.load(tmp_path / f"r{k}.npz") for k in range(world)]
     nzl = ncell[2] // world
 
