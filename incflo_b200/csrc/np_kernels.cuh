@@ -2,8 +2,8 @@
 //
 // Kernel families:
 //   K1 k_divu            nodal divergence of the cell velocity     (amrex::mlndlap_divu + impose_neumann_bc)
-//   K2 k_adotx           y = A x  /  y = b - A x, 27-point variable-sigma operator (mlndlap_adotx_aa)
-//   K3 k_smooth_tiled    Gauss-Seidel smoother, two sweeps fused in one pass (mlndlap_gauss_seidel_aa)
+//   K2 k_stencil         y = A x  /  y = (b - off) - A x marching in z, constant or variable sigma (mlndlap_adotx_aa)
+//   K3 k_gs2             Gauss-Seidel smoother, two sweeps fused in one pass (mlndlap_gauss_seidel_aa)
 //   K4 k_restrict        full-weighting restriction                (mlndlap_restriction)
 //   K5 k_interp_add      prolongation + add                        (mlndlap_interpadd_aa)
 //   K6 k_bottom_*        BiCGStab / CG on the coarsest level in one CTA (MLCGSolver)
@@ -160,47 +160,6 @@ __global__ void __launch_bounds__(256) k_fill_sigma(LevelDev L, double* s, int p
         if (k < 0)          { if (!zlo_local) continue; sk = per2 ? k + L.n[2] : 0; }
         else if (k >= L.n[2]) { if (!zhi_local) continue; sk = per2 ? k - L.n[2] : L.n[2] - 1; }
         s[np_coff(L, i, j, k)] = s[np_coff(L, si, sj, sk)];
-    }
-}
-
-// ------------------------------------------------------------------------------------------------
-// K2: y = A x (MODE 0) or y = b - A x (MODE 1) on all valid nodes.  Optional per-block inf-norm of y.
-// One thread per node, x fastest; neighbours come through L1/L2.
-// ------------------------------------------------------------------------------------------------
-template <int MODE, bool CS, bool NORM>
-__global__ void __launch_bounds__(256) k_adotx(LevelDev L, double* __restrict__ y, const double* __restrict__ x,
-                                               const double* __restrict__ b, const double* __restrict__ boff, const double* __restrict__ sig,
-                                               double* __restrict__ block_max, double* __restrict__ block_sum)
-{
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    const int j = blockIdx.y * blockDim.y + threadIdx.y;
-    const int k = blockIdx.z;
-    double v = 0.0;
-    const bool active = (i <= L.n[0] && j <= L.n[1]);
-    if (active) {
-        const long long o = np_noff(L, i, j, k);
-        if (!np_is_dirichlet(L, i, j, k)) {
-            GlobX xa{x + o, L.nsy, L.nsz};
-            double ax;
-            if (CS) {
-                ax = xa(0,0,0) * np_diag_const(L.c, L.sigma0) + np_offdiag_const(L.c, L.sigma0, xa);
-            } else {
-                GlobS sa{sig + np_coff(L, i, j, k), L.csy, L.csz};
-                Sig8 g = np_load_sig(sa);
-                ax = xa(0,0,0) * np_diag(L.c, g) + np_offdiag(L.c, g, xa);
-            }
-            v = (MODE == 1) ? (b[o] - (boff ? boff[0] : 0.0)) - ax : ax;
-        }
-        y[o] = v;
-    }
-    if (NORM) {
-        const bool owned = active && i <= L.owned_hi[0] && j <= L.owned_hi[1] && k <= L.owned_hi[2];
-        const double m = np_block_reduce<true>(fabs(v));
-        const double sm = np_block_reduce<false>(owned ? np_neumann_weight(L, i, j, k) * v : 0.0);
-        if (threadIdx.x == 0 && threadIdx.y == 0) {
-            const long long bidx = blockIdx.x + gridDim.x * (blockIdx.y + (long long)gridDim.y * blockIdx.z);
-            block_max[bidx] = m; block_sum[bidx] = sm;
-        }
     }
 }
 
@@ -363,16 +322,6 @@ __device__ __forceinline__ void np_cp_async_wait_all()
     asm volatile("cp.async.wait_all;\n" ::: "memory");
 #endif
 }
-
-// nodal value at tile-local (li, lj) of a split-layout plane; li in [-1, 64], lj in [-1, 32]
-__device__ __forceinline__ int gs_idx(int li, int lj) { const int g = li + 2; return ((g & 1) ? GS_HALF : 0) + (lj + 1) * GS_HP + (g >> 1); }
-struct GsSmemX {   // 27-point accessor around tile-local node (li, lj) for the variable-sigma path
-    const double* m; const double* c; const double* p; int li, lj;
-    __device__ __forceinline__ double operator()(int di, int dj, int dk) const {
-        const double* q = dk < 0 ? m : (dk > 0 ? p : c);
-        return q[gs_idx(li + di, lj + dj)];
-    }
-};
 
 // Cooperative plane loader shared by k_gs2 and k_stencil_cs: 198 of the 256 threads each own one of the 66
 // columns (tile halo included) of three interleaved row sets, so a plane costs 12 cp.async per thread with
@@ -1212,22 +1161,6 @@ __global__ void __launch_bounds__(256) k_avgdown_sigma(LevelDev Lc, LevelDev Lf,
     sc[np_coff(Lc, i, j, k)] = 0.125 * (((p[0] + p[1]) + (p[y] + p[y+1])) + ((p[z] + p[z+1]) + (p[z+y] + p[z+y+1])));
 }
 
-// copy the caller's sigma fab (interior) into the level-0 sigma array and produce per-block min / max
-__global__ void __launch_bounds__(256) k_copy_sigma_in(LevelDev L, double* __restrict__ s, FabView src,
-                                                      double* __restrict__ bmin, double* __restrict__ bmax)
-{
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    const int j = blockIdx.y * blockDim.y + threadIdx.y;
-    const int k = blockIdx.z;
-    double v = 0.0; bool act = (i < L.n[0] && j < L.n[1]);
-    if (act) { v = src.p[np_foff(src, i, j, k, 0)]; s[np_coff(L, i, j, k)] = v; }
-    double mx = np_block_reduce<true>(act ? v : -1e300);
-    double mn = -np_block_reduce<true>(act ? -v : -1e300);
-    if (threadIdx.x == 0 && threadIdx.y == 0) {
-        const long long bidx = blockIdx.x + gridDim.x * (blockIdx.y + (long long)gridDim.y * blockIdx.z);
-        bmin[bidx] = mn; bmax[bidx] = mx;
-    }
-}
 __global__ void __launch_bounds__(256) k_reduce_minmax(const double* __restrict__ bmin, const double* __restrict__ bmax, long long n, double* out)
 {
     double mx = -1e300, mn = 1e300;
