@@ -355,7 +355,7 @@ def main():
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--ncell", type=int, default=512, help="cells per side per GPU (512: configs[2]; 256: configs[1])")
     ap.add_argument("--vel-ngrow", type=int, default=2, help="ghost layers of the velocity fab (incflo nghost_state: 2 MOL / 3 Godunov)")
-    ap.add_argument("--cpu-ncell", type=int, default=128, help="size of the bounded CPU sample")
+    ap.add_argument("--cpu-ncell", type=int, default=256, help="size of the bounded CPU sample")
     ap.add_argument("--workload", default="double_shear", choices=["double_shear", "rayleigh_taylor"],
                     help="double_shear: BASELINE configs[2] (constant density, default); rayleigh_taylor: configs[3] (variable sigma)")
     ap.add_argument("--e2e-steps", type=int, default=2)
