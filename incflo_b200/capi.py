@@ -47,8 +47,13 @@ class np_stats(C.Structure):
                 ("n_smooth0", C.c_int), ("ms_smooth0", C.c_double)]
 
 
+class np_apply_args(C.Structure):
+    _fields_ = [("scaling_factor", C.c_double), ("incremental", C.c_int), ("proj_for_small_dt", C.c_int),
+                ("zero_vel_ghosts", C.c_int)]
+
+
 # every symbol include/nodalproj.h declares
-SYMBOLS = ["np_default_options", "np_create", "np_set_bc", "np_project", "np_get_phi", "np_get_gradphi",
+SYMBOLS = ["np_default_options", "np_create", "np_set_bc", "np_project", "np_apply_projection", "np_get_phi", "np_get_gradphi",
            "np_copy_phi", "np_copy_gradphi", "np_destroy", "np_strerror", "np_num_levels", "np_level_ncell",
            "np_last_stats", "np_set_sigma", "np_get_sigma", "np_apply", "np_smooth", "np_restrict",
            "np_interp_add", "np_divu", "np_mknewu", "np_bottom_solve", "np_vcycle", "np_dot",
@@ -78,6 +83,9 @@ def load(path=None):
     L.np_set_bc.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
     L.np_project.argtypes = [C.c_void_p, C.c_int, C.POINTER(np_fab), C.POINTER(np_fab), C.c_double, C.c_double,
                              C.c_void_p, C.POINTER(np_stats)]
+    L.np_apply_projection.argtypes = [C.c_void_p, C.POINTER(np_fab), C.POINTER(np_fab), C.POINTER(np_fab), C.POINTER(np_fab),
+                                      C.POINTER(np_fab), C.POINTER(np_apply_args), C.c_double, C.c_double, C.c_void_p,
+                                      C.POINTER(np_stats)]
     for name in ("np_get_phi", "np_get_gradphi", "np_copy_phi", "np_copy_gradphi"):
         getattr(L, name).argtypes = [C.c_void_p, C.c_int, C.POINTER(np_fab)]
     L.np_destroy.argtypes = [C.c_void_p]

@@ -47,6 +47,16 @@ int np_project(np_handle* h, int nlocal, np_fab* vel, const np_fab* sigma, doubl
     return rc;
 }
 
+int np_apply_projection(np_handle* h, np_fab* vel, const np_fab* vel_old, const np_fab* density, np_fab* gp, np_fab* p,
+                        const np_apply_args* args, double rtol, double atol, void* cuda_stream, np_stats* out)
+{
+    if (!h || !vel || !density || !gp || !p || !args || !vel->p || !density->p || !gp->p || !p->p) return NP_ERR_INVALID;
+    h->S.stream = (np_stream_t)cuda_stream;
+    int rc = h->S.apply_projection(vel, vel_old, density, gp, p, args, rtol, atol);
+    if (out) *out = h->S.stats;
+    return rc;
+}
+
 int np_last_stats(np_handle* h, np_stats* out) { if (!h || !out) return NP_ERR_INVALID; *out = h->S.stats; return NP_OK; }
 
 int np_get_phi(np_handle* h, int local_box, np_fab* out)

@@ -1290,6 +1290,93 @@ __global__ void __launch_bounds__(256) k_mknewu(LevelDev L, FabView u, FabView g
 }
 
 // ------------------------------------------------------------------------------------------------
+// K9: the caller's pointwise passes around the projection (incflo::ApplyProjection,
+// /root/reference/src/projection/incflo_apply_nodal_projection.cpp:79-131 before, :156-203 after), folded into two
+// kernels so that u, rho, gp are streamed once on each side and the caller's sigma MultiFab never exists.
+//   pre  (:79-131): u += gp * scaling/rho unless incremental; u -= u_old for the incremental / small-dt forms;
+//                   sigma = scaling/rho goes straight into the level-0 coefficient array; per-block min / max of sigma.
+//   post (:153-203): u -= sigma grad(phi) (+ u_old); gp = grad(phi) or gp += grad(phi); p = phi or p += phi.
+// ------------------------------------------------------------------------------------------------
+struct ApPre { double scaling; int add_gp, sub_old; };
+__global__ void __launch_bounds__(256) k_apply_pre(LevelDev L, FabView u, FabView uo, FabView rho, FabView gp, double* __restrict__ sig,
+                                                   ApPre a, double* __restrict__ bmin, double* __restrict__ bmax)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    const int k = blockIdx.z;
+    double mx = -1e300, mn = 1e300;
+    if (i < L.n[0] && j < L.n[1]) {
+        const double s = a.scaling / rho.p[np_foff(rho, i, j, k, 0)];
+        sig[np_coff(L, i, j, k)] = s;
+        mx = s; mn = s;
+        if (a.add_gp || a.sub_old) {
+            double* up = u.p + np_foff(u, i, j, k, 0);
+#pragma unroll
+            for (int n = 0; n < 3; ++n) {
+                double v = up[u.sn * n];
+                if (a.add_gp) v += gp.p[np_foff(gp, i, j, k, n)] * s;
+                if (a.sub_old) v -= uo.p[np_foff(uo, i, j, k, n)];
+                up[u.sn * n] = v;
+            }
+        }
+    }
+    mx = np_block_reduce<true>(mx);
+    mn = -np_block_reduce<true>(-mn);
+    if (threadIdx.x == 0 && threadIdx.y == 0) {
+        const long long bidx = blockIdx.x + gridDim.x * (blockIdx.y + (long long)gridDim.y * blockIdx.z);
+        bmin[bidx] = mn; bmax[bidx] = mx;
+    }
+}
+// MultiFab::setBndry(0) on a 3-component cell fab: every ghost cell of every layer (:142)
+__global__ void __launch_bounds__(256) k_zero_cell_ghosts(int n0, int n1, int n2, FabView u)
+{
+    const int g = u.ng;
+    const int i = (int)(blockIdx.x * blockDim.x + threadIdx.x) - g;
+    const int j = (int)(blockIdx.y * blockDim.y + threadIdx.y) - g;
+    const int k = (int)blockIdx.z - g;
+    if (i >= n0 + g || j >= n1 + g) return;
+    if (i >= 0 && i < n0 && j >= 0 && j < n1 && k >= 0 && k < n2) return;
+    double* up = u.p + np_foff(u, i, j, k, 0);
+    up[0] = 0.0; up[u.sn] = 0.0; up[2 * u.sn] = 0.0;
+}
+struct ApPost { int add_old, accumulate; };
+__global__ void __launch_bounds__(256) k_apply_post(LevelDev L, FabView u, FabView uo, FabView g, const double* __restrict__ phi,
+                                                    const double* __restrict__ sig, ApPost a)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    const int k = blockIdx.z;
+    if (i >= L.n[0] || j >= L.n[1]) return;
+    const double* q = phi + np_noff(L, i, j, k);
+    const long long y = L.nsy, z = L.nsz;
+    double gr[3];
+    gr[0] = 0.25 * L.dxinv[0] * (((q[1] - q[0]) + (q[1+y] - q[y])) + ((q[1+z] - q[z]) + (q[1+y+z] - q[y+z])));
+    gr[1] = 0.25 * L.dxinv[1] * (((q[y] - q[0]) + (q[1+y] - q[1])) + ((q[y+z] - q[z]) + (q[1+y+z] - q[1+z])));
+    gr[2] = 0.25 * L.dxinv[2] * (((q[z] - q[0]) + (q[1+z] - q[1])) + ((q[y+z] - q[y]) + (q[1+y+z] - q[1+y])));
+    const double s = L.const_sigma ? L.sigma0 : sig[np_coff(L, i, j, k)];
+    double* up = u.p + np_foff(u, i, j, k, 0);
+    double* gp = g.p + np_foff(g, i, j, k, 0);
+#pragma unroll
+    for (int n = 0; n < 3; ++n) {
+        double v = up[u.sn * n] - s * gr[n];
+        if (a.add_old) v += uo.p[np_foff(uo, i, j, k, n)];
+        up[u.sn * n] = v;
+        gp[g.sn * n] = a.accumulate ? gp[g.sn * n] + gr[n] : gr[n];
+    }
+}
+// p = phi or p += phi on the valid nodes of the caller's nodal fab (:187-200)
+__global__ void __launch_bounds__(256) k_apply_post_p(LevelDev L, const double* __restrict__ phi, FabView p, int accumulate)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    const int k = blockIdx.z;
+    if (i > L.n[0] || j > L.n[1]) return;
+    double* pp = p.p + np_foff(p, i, j, k, 0);
+    const double v = phi[np_noff(L, i, j, k)];
+    *pp = accumulate ? *pp + v : v;
+}
+
+// ------------------------------------------------------------------------------------------------
 // Copies between the padded internal nodal layout and a caller fab (1 comp).  ng_copy ghost layers of the
 // fab are transferred too (clamped to 1).
 // ------------------------------------------------------------------------------------------------

@@ -593,8 +593,16 @@ int NpSolver::set_sigma(const FabView& s)
 {
     const LevelDev& d0 = lev[0].d;
     dim3 gmm = grid_cells(d0); gmm.z = std::min<unsigned>(gmm.z, 16u);
-    const long long nbm = nblocks(gmm);
     NP_LAUNCH(true, k_minmax_cell, gmm, NP_BLK, 0, stream, d0.n[0], d0.n[1], d0.n[2], s, part0, part1); ++launches;
+    return finish_sigma(nblocks(gmm), &s);
+}
+
+// second half of setSigma: min / max partials are in part0 / part1.  Uniform sigma selects the constant-coefficient
+// kernels (nothing is stored); otherwise level 0 is filled from `src` (null: its interior is already in place), its
+// ghosts are set and the coarse levels are averaged down (averageDownCoeffs + FillBoundaryCoeff).
+int NpSolver::finish_sigma(long long nbm, const FabView* src)
+{
+    const LevelDev& d0 = lev[0].d;
     NP_LAUNCH(true, k_reduce_minmax, dim3(1), dim3(256), 0, stream, (const double*)part0, (const double*)part1, nbm, scal + 4); ++launches;
     NP_LAUNCH(false, k_negate_one, dim3(1), dim3(32), 0, stream, scal + 4); ++launches;   // (-min, max): one max-allreduce
     if (comm.nranks > 1) { if (comm.allreduce(comm.ctx, scal + 4, 2, 1, (void*)stream)) err = NP_ERR_NCCL; }
@@ -605,7 +613,7 @@ int NpSolver::set_sigma(const FabView& s)
     stats.sigma_is_const = is_const ? 1 : 0;
     for (auto& L : lev) { L.d.const_sigma = is_const ? 1 : 0; L.d.sigma0 = smin; }
     if (!is_const) {
-        NP_LAUNCH(false, k_copy_sigma_plain, grid_cells(d0), NP_BLK, 0, stream, d0, lev[0].sigma, s); ++launches;
+        if (src) { NP_LAUNCH(false, k_copy_sigma_plain, grid_cells(d0), NP_BLK, 0, stream, d0, lev[0].sigma, *src); ++launches; }
         fill_sigma_level(*this, 0);
         for (int l = 1; l < (int)lev.size(); ++l) {
             if (lev[l].replicated && !lev[l - 1].replicated) avgdown_sigma_to_replica(l);
@@ -692,6 +700,25 @@ void np_fill_cell3(NpSolver& S, FabView u)
 }
 
 // amrex::NodalProjector::project(rtol, atol)
+// device-timed phases and launch counts of the call that just ended (events ev[0..2] were recorded on the way)
+void NpSolver::finish_stats()
+{
+    np_rt::event_record(ev[3], stream);
+    np_rt::stream_sync(stream);
+    stats.ms_setup = np_rt::event_ms(ev[0], ev[1]);
+    stats.ms_solve = np_rt::event_ms(ev[1], ev[2]);
+    stats.ms_finish = np_rt::event_ms(ev[2], ev[3]);
+    stats.ms_total = np_rt::event_ms(ev[0], ev[3]);
+    stats.kernel_launches = launches;
+    stats.n_smooth0 = prof_n / 2; stats.ms_smooth0 = 0.0;
+    for (int e = 0; e < prof_n; e += 2) stats.ms_smooth0 += np_rt::event_ms(prof_ev[e], prof_ev[e + 1]);
+    if (opt.verbose >= 4) {     // per-launch times of the level-0 smoother (first V-cycle: zero-input, plain, plain, add-to)
+        fprintf(stderr, "[nodalproj] level-0 smoother launches (ms):");
+        for (int e = 0; e < prof_n && e < 32; e += 2) fprintf(stderr, " %.3f", np_rt::event_ms(prof_ev[e], prof_ev[e + 1]));
+        fprintf(stderr, "\n");
+    }
+}
+
 int NpSolver::project(np_fab* vel, const np_fab* sigma, double rtol, double atol)
 {
     if (vel->ngrow < 1 || vel->ncomp < 3 || sigma->ncomp < 1) return NP_ERR_INVALID;
@@ -736,22 +763,59 @@ int NpSolver::project(np_fab* vel, const np_fab* sigma, double rtol, double atol
     NP_LAUNCH(false, (k_copy_nodal<true>), dim3((d0.n[0] + 3 + 31) / 32, (d0.n[1] + 3 + 7) / 8, d0.n[2] + 3), NP_BLK, 0, stream, d0, sol, pv, 1); ++launches;
     if (st_vel) np_rt::copy_async(vel->p, dvel, (size_t)nvel * sizeof(double), stream);
     (void)st_sig;
-    np_rt::event_record(ev[3], stream);
-    np_rt::stream_sync(stream);
-    stats.ms_setup = np_rt::event_ms(ev[0], ev[1]);
-    stats.ms_solve = np_rt::event_ms(ev[1], ev[2]);
-    stats.ms_finish = np_rt::event_ms(ev[2], ev[3]);
-    stats.ms_total = np_rt::event_ms(ev[0], ev[3]);
-    stats.kernel_launches = launches;
-    stats.n_smooth0 = prof_n / 2; stats.ms_smooth0 = 0.0;
-    for (int e = 0; e < prof_n; e += 2) stats.ms_smooth0 += np_rt::event_ms(prof_ev[e], prof_ev[e + 1]);
-    if (opt.verbose >= 4) {     // per-launch times of the level-0 smoother (first V-cycle: zero-input, plain, plain, add-to)
-        fprintf(stderr, "[nodalproj] level-0 smoother launches (ms):");
-        for (int e = 0; e < prof_n && e < 32; e += 2) fprintf(stderr, " %.3f", np_rt::event_ms(prof_ev[e], prof_ev[e + 1]));
-        fprintf(stderr, "\n");
-    }
+    finish_stats();
     if (np_rt::last_error()) { stats.status = NP_ERR_CUDA; return NP_ERR_CUDA; }
     if (err) { stats.status = err; return err; }
     have_result = true;
     return rc;
 }
+
+// incflo::ApplyProjection for one level in one call: the pointwise passes the caller runs before
+// and after NodalProjector::project (/root/reference/src/projection/incflo_apply_nodal_projection.cpp:79-131, :156-203)
+// are folded into the solver's first and last kernels; sigma = scaling/rho is never materialised as a caller fab.
+int NpSolver::apply_projection(np_fab* vel, const np_fab* vel_old, const np_fab* rho, np_fab* gp, np_fab* p,
+                               const np_apply_args* a, double rtol, double atol)
+{
+    const bool use_old = a->incremental || a->proj_for_small_dt;
+    if (vel->ngrow < 1 || vel->ncomp < 3 || rho->ncomp < 1 || gp->ncomp < 3 || p->ncomp < 1) return NP_ERR_INVALID;
+    if (use_old && (!vel_old || !vel_old->p || vel_old->ncomp < 3)) return NP_ERR_INVALID;
+    // device fabs only (a CUDA build of the caller); a CPU caller keeps its own passes and uses np_project
+    if (!np_rt::is_device_ptr(vel->p) || !np_rt::is_device_ptr(rho->p) || !np_rt::is_device_ptr(gp->p) || !np_rt::is_device_ptr(p->p)
+        || (use_old && !np_rt::is_device_ptr(vel_old->p))) return NP_ERR_INVALID;
+    err = 0; launches = 0; have_result = false; prof_n = 0;
+    const LevelDev& d0 = lev[0].d;
+    np_rt::event_record(ev[0], stream);
+    FabView uv = view_cell(*vel, 0, 3), rv = view_cell(*rho, 0, 1), gv = view_cell(*gp, 0, 3), pv = view_nodal(*p, 0);
+    FabView ov = use_old ? view_cell(*vel_old, 0, 3) : uv;
+    // ---- before: u += gp*scaling/rho, u -= u_old, sigma = scaling/rho, setBndry(0) ----
+    ApPre pre; pre.scaling = a->scaling_factor; pre.add_gp = a->incremental ? 0 : 1; pre.sub_old = use_old ? 1 : 0;
+    NP_LAUNCH(true, k_apply_pre, grid_cells(d0), NP_BLK, 0, stream, d0, uv, ov, rv, gv, lev[0].sigma, pre, part0, part1); ++launches;
+    if (a->zero_vel_ghosts) {
+        const int g = uv.ng;
+        NP_LAUNCH(false, k_zero_cell_ghosts, dim3((d0.n[0] + 2 * g + 31) / 32, (d0.n[1] + 2 * g + 7) / 8, d0.n[2] + 2 * g), NP_BLK, 0, stream,
+                  d0.n[0], d0.n[1], d0.n[2], uv); ++launches;
+    }
+    int rc = finish_sigma(nblocks(grid_cells(d0)), nullptr);
+    if (rc) return rc;
+    // ---- rhs = div(u*) ----
+    np_fill_cell3(*this, uv);
+    {
+        dim3 gd = grid_nodes(d0); gd.z = std::min<unsigned>(gd.z, 32u);
+        if (singular) { NP_LAUNCH(true, (k_divu<true>), gd, NP_BLK, 0, stream, d0, rhs, uv, part1); divu_npart = nblocks(gd); }
+        else          { NP_LAUNCH(true, (k_divu<false>), gd, NP_BLK, 0, stream, d0, rhs, uv, part1); divu_npart = 0; }
+        ++launches;
+    }
+    np_rt::event_record(ev[1], stream);
+    rc = solve(rtol, atol);
+    np_rt::event_record(ev[2], stream);
+    // ---- after: u -= sigma grad(phi) (+ u_old), gp (+)= grad(phi), p (+)= phi ----
+    ApPost post; post.add_old = use_old ? 1 : 0; post.accumulate = a->incremental ? 1 : 0;
+    NP_LAUNCH(false, k_apply_post, grid_cells(d0), NP_BLK, 0, stream, d0, uv, ov, gv, (const double*)sol, (const double*)lev[0].sigma, post); ++launches;
+    fill(0, sol);
+    NP_LAUNCH(false, k_apply_post_p, grid_nodes(d0), NP_BLK, 0, stream, d0, (const double*)sol, pv, post.accumulate); ++launches;
+    finish_stats();
+    if (np_rt::last_error()) { stats.status = NP_ERR_CUDA; return NP_ERR_CUDA; }
+    if (err) { stats.status = err; return err; }
+    return rc;
+}
+

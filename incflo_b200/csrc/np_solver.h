@@ -92,7 +92,11 @@ struct NpSolver {
     void vcycle(bool add_to_sol);
     int solve(double rtol, double atol);
     int set_sigma(const FabView& s);
+    int finish_sigma(long long nbm, const FabView* src);
+    void finish_stats();
     int project(np_fab* vel, const np_fab* sigma, double rtol, double atol);
+    int apply_projection(np_fab* vel, const np_fab* vel_old, const np_fab* rho, np_fab* gp, np_fab* p, const np_apply_args* a,
+                         double rtol, double atol);
     void zero(double* p, long long n);
     FabView view_nodal(const np_fab& f, int l) const;
     FabView view_cell(const np_fab& f, int l, int ncomp) const;

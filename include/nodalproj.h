@@ -111,6 +111,28 @@ int np_set_bc(np_handle* h, const int lo[3], const int hi[3]);
 int np_project(np_handle* h, int nlocal, np_fab* vel, const np_fab* sigma,
                double rtol, double atol, void* cuda_stream, np_stats* out);
 
+/* ---- incflo::ApplyProjection for one level in ONE call.  Replaces the body of
+ * /root/reference/src/projection/incflo_apply_nodal_projection.cpp:57-224 between the verbose prints: the caller's
+ * pointwise passes (u += gp*scaling/rho :79-105, u -= u_old :107-114, sigma = scaling/rho :116-131, setBndry(0) :142,
+ * u += u_old :155-162, gp/p = or += grad(phi)/phi :168-203) run inside the library's first and last kernels, so u, rho
+ * and gp are streamed once on either side of the solve and no sigma MultiFab exists.  Device fabs only.
+ *   vel      cell, 3 comp, >= 1 ghost   in: u*           out: u^{n+1}
+ *   vel_old  cell, 3 comp               u^n; required when incremental or proj_for_small_dt, else may be NULL
+ *   density  cell, 1 comp               rho
+ *   gp       cell, 3 comp               in: grad(p) of the last step   out: grad(phi) (incremental: += grad(phi))
+ *   p        nodal, 1 comp              out: phi (incremental: += phi)
+ * Inflow faces: set_inflow_velocity (:143-145) stays with the caller - pass zero_vel_ghosts = 0 and hand in `vel`
+ * with its ghost cells already zeroed and the inflow layer filled (the pre-pass only touches valid cells).
+ * np_get_phi / np_get_gradphi are not valid after this call (the results went straight to p and gp). */
+typedef struct {
+    double scaling_factor;      /* ApplyProjection's scaling_factor (dt, or dt/2 for the predictor of the initial iterations) */
+    int incremental;            /* ApplyProjection's `incremental` */
+    int proj_for_small_dt;      /* time > 0 && dt < 0.1 * prev_dt, decided by the caller (:65) */
+    int zero_vel_ghosts;        /* 1: vel.setBndry(0) here (:142); 0: the caller prepared the ghost cells (inflow) */
+} np_apply_args;
+int np_apply_projection(np_handle* h, np_fab* vel, const np_fab* vel_old, const np_fab* density, np_fab* gp, np_fab* p,
+                        const np_apply_args* args, double rtol, double atol, void* cuda_stream, np_stats* out);
+
 /* Borrowed device pointers, valid until the next np_project / np_destroy.
  * phi: nodal, 1 comp, 1 ghost.  gradphi: cell, 3 comp, 1 ghost. */
 int np_get_phi(np_handle* h, int local_box, np_fab* out);
