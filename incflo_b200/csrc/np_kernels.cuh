@@ -1195,6 +1195,10 @@ __global__ void __launch_bounds__(256) k_fill_vel(LevelDev L, FabView u, int per
 // ------------------------------------------------------------------------------------------------
 // K1: rhs = div(u) at valid nodes, with the Neumann conventions of mlndlap_divu / impose_neumann_bc
 // ------------------------------------------------------------------------------------------------
+// Each block marches through a contiguous run of node planes: the cell layer between two node planes is read once and
+// its three in-layer sums (x-differences, y-differences, z-values over the 4 cells around the node column) serve the
+// node plane below and the one above:  rhs(k) = 1/4 [ dxinv_x (zzl Dx(k-1) + zzh Dx(k)) + dxinv_y (zzl Dy(k-1) + zzh Dy(k))
+//                                                    + dxinv_z (Sz(k) - Sz(k-1)) ]  (x2 per Neumann face, mlndlap_impose_neumann_bc).
 template <bool WSUM>
 __global__ void __launch_bounds__(256) k_divu(LevelDev L, double* __restrict__ rhs, FabView u, double* __restrict__ part_sum)
 {
@@ -1202,32 +1206,42 @@ __global__ void __launch_bounds__(256) k_divu(LevelDev L, double* __restrict__ r
     const int j = blockIdx.y * blockDim.y + threadIdx.y;
     const bool inside = (i <= L.n[0] && j <= L.n[1]);
     double tsum = 0.0;
-    // each block walks the planes k = blockIdx.z, blockIdx.z + gridDim.z, ... so the solvability sum needs few partials
-    for (int k = blockIdx.z; k <= L.n[2]; k += gridDim.z) {
-        if (!inside) continue;
-        double acc = 0.0;
-        if (!np_is_dirichlet(L, i, j, k)) {
-            // z?lo / z?hi: weight of the cells on the low / high side of the node (0 outside a Neumann wall)
-            const double zxl = (L.face[0] == NP_FACE_NEUMANN && i == 0) ? 0.0 : 1.0, zxh = (L.face[3] == NP_FACE_NEUMANN && i == L.n[0]) ? 0.0 : 1.0;
-            const double zyl = (L.face[1] == NP_FACE_NEUMANN && j == 0) ? 0.0 : 1.0, zyh = (L.face[4] == NP_FACE_NEUMANN && j == L.n[1]) ? 0.0 : 1.0;
+    const int per = (L.n[2] + 1 + gridDim.z - 1) / gridDim.z;            // node planes per block
+    const int k0 = blockIdx.z * per, k1 = min(k0 + per - 1, L.n[2]);
+    if (inside && k0 <= k1) {
+        // weight of the cells on the low / high side of the node (0 outside a Neumann wall)
+        const double zxl = (L.face[0] == NP_FACE_NEUMANN && i == 0) ? 0.0 : 1.0, zxh = (L.face[3] == NP_FACE_NEUMANN && i == L.n[0]) ? 0.0 : 1.0;
+        const double zyl = (L.face[1] == NP_FACE_NEUMANN && j == 0) ? 0.0 : 1.0, zyh = (L.face[4] == NP_FACE_NEUMANN && j == L.n[1]) ? 0.0 : 1.0;
+        double fxy = 1.0;                                                  // x2 per Neumann face in x / y the node lies on
+        if (zxl == 0.0) fxy *= 2.0;
+        if (zxh == 0.0) fxy *= 2.0;
+        if (zyl == 0.0) fxy *= 2.0;
+        if (zyh == 0.0) fxy *= 2.0;
+        const bool dxy = (L.face[0] == NP_FACE_DIRICHLET && i == 0) || (L.face[3] == NP_FACE_DIRICHLET && i == L.n[0])
+                      || (L.face[1] == NP_FACE_DIRICHLET && j == 0) || (L.face[4] == NP_FACE_DIRICHLET && j == L.n[1]);
+        const long long y = u.sy;
+        // in-layer sums of cell layer c (cells (i-1..i, j-1..j, c))
+        auto layer = [&](int c, double& dx, double& dy, double& sz) {
+            const double* ux = u.p + np_foff(u, i, j, c, 0);
+            const double* uy = ux + u.sn; const double* uz = ux + 2 * u.sn;
+            dx = zyl * (ux[-y] - ux[-1 - y]) + zyh * (ux[0] - ux[-1]);
+            dy = zxl * (uy[-1] - uy[-1 - y]) + zxh * (uy[0] - uy[-y]);
+            sz = (zxl * zyl * uz[-1 - y] + zxh * zyl * uz[-y]) + (zxl * zyh * uz[-1] + zxh * zyh * uz[0]);
+        };
+        double dxm, dym, szm;
+        layer(k0 - 1, dxm, dym, szm);
+        for (int k = k0; k <= k1; ++k) {
+            double dxc, dyc, szc;
+            layer(k, dxc, dyc, szc);
             const double zzl = (L.face[2] == NP_FACE_NEUMANN && k == 0) ? 0.0 : 1.0, zzh = (L.face[5] == NP_FACE_NEUMANN && k == L.n[2]) ? 0.0 : 1.0;
-            const double* p = u.p + np_foff(u, i, j, k, 0);
-            const long long y = u.sy, z = u.sz;
-            const double* ux = p; const double* uy = p + u.sn; const double* uz = p + 2 * u.sn;
-            // cells (a,b,c), a,b,c in {-1,0}: offset a + y*b + z*c
-            double sx = zyl*zzl*(ux[-y-z] - ux[-1-y-z]) + zyh*zzl*(ux[-z] - ux[-1-z]) + zyl*zzh*(ux[-y] - ux[-1-y]) + zyh*zzh*(ux[0] - ux[-1]);
-            double sy_ = zxl*zzl*(uy[-1-z] - uy[-1-y-z]) + zxh*zzl*(uy[-z] - uy[-y-z]) + zxl*zzh*(uy[-1] - uy[-1-y]) + zxh*zzh*(uy[0] - uy[-y]);
-            double sz_ = zxl*zyl*(uz[-1-y] - uz[-1-y-z]) + zxh*zyl*(uz[-y] - uz[-y-z]) + zxl*zyh*(uz[-1] - uz[-1-z]) + zxh*zyh*(uz[0] - uz[-z]);
-            acc = 0.25 * (L.dxinv[0] * sx + L.dxinv[1] * sy_ + L.dxinv[2] * sz_);
-            if (zxl == 0.0) acc *= 2.0;
-            if (zxh == 0.0) acc *= 2.0;
-            if (zyl == 0.0) acc *= 2.0;
-            if (zyh == 0.0) acc *= 2.0;
+            double acc = 0.25 * (L.dxinv[0] * (zzl * dxm + zzh * dxc) + L.dxinv[1] * (zzl * dym + zzh * dyc) + L.dxinv[2] * (szc - szm)) * fxy;
             if (zzl == 0.0) acc *= 2.0;
             if (zzh == 0.0) acc *= 2.0;
+            if (dxy || (L.face[2] == NP_FACE_DIRICHLET && k == 0) || (L.face[5] == NP_FACE_DIRICHLET && k == L.n[2])) acc = 0.0;
+            rhs[np_noff(L, i, j, k)] = acc;
+            if (WSUM && i <= L.owned_hi[0] && j <= L.owned_hi[1] && k <= L.owned_hi[2]) tsum += np_neumann_weight(L, i, j, k) * acc;
+            dxm = dxc; dym = dyc; szm = szc;
         }
-        rhs[np_noff(L, i, j, k)] = acc;
-        if (WSUM && i <= L.owned_hi[0] && j <= L.owned_hi[1] && k <= L.owned_hi[2]) tsum += np_neumann_weight(L, i, j, k) * acc;
     }
     if (WSUM) {
         const double sm = np_block_reduce<false>(tsum);

@@ -745,7 +745,7 @@ int NpSolver::project(np_fab* vel, const np_fab* sigma, double rtol, double atol
     // ---- rhs = div(u*) ----
     np_fill_cell3(*this, uv);
     {   // rhs = div(u*) and, for singular problems, the partial sums of its solvability offset in the same pass
-        dim3 gd = grid_nodes(d0); gd.z = std::min<unsigned>(gd.z, 32u);
+        dim3 gd = grid_nodes(d0); gd.z = std::min<unsigned>(gd.z, 16u);     // 16 runs of node planes per column
         if (singular) { NP_LAUNCH(true, (k_divu<true>), gd, NP_BLK, 0, stream, d0, rhs, uv, part1); divu_npart = nblocks(gd); }
         else          { NP_LAUNCH(true, (k_divu<false>), gd, NP_BLK, 0, stream, d0, rhs, uv, part1); divu_npart = 0; }
         ++launches;
@@ -800,7 +800,7 @@ int NpSolver::apply_projection(np_fab* vel, const np_fab* vel_old, const np_fab*
     // ---- rhs = div(u*) ----
     np_fill_cell3(*this, uv);
     {
-        dim3 gd = grid_nodes(d0); gd.z = std::min<unsigned>(gd.z, 32u);
+        dim3 gd = grid_nodes(d0); gd.z = std::min<unsigned>(gd.z, 16u);     // 16 runs of node planes per column
         if (singular) { NP_LAUNCH(true, (k_divu<true>), gd, NP_BLK, 0, stream, d0, rhs, uv, part1); divu_npart = nblocks(gd); }
         else          { NP_LAUNCH(true, (k_divu<false>), gd, NP_BLK, 0, stream, d0, rhs, uv, part1); divu_npart = 0; }
         ++launches;
