@@ -238,7 +238,7 @@ def run_gpu(args):
     P = NodalProjector(vel, sig, geom, LPInfo(), boxes=boxes, rank=rank, nranks=world, nccl_comm=comm, lib=L,
                        profile_kernels=1, smooth_zchunk=args.smooth_zchunk, verbose=args.verbose,
                        **({"agg_min_local_nz": args.agg_min_local_nz} if args.agg_min_local_nz > 0 else {}),
-                       **({"overlap_halo": 0} if args.no_overlap else {}))
+                       **({"overlap_halo": 0} if args.no_overlap else {}), **({"p2p_halo": 0} if args.no_p2p else {}))
     P.setDomainBC(bclo, bchi)
     dof = n * n * n * G
     stream = torch.cuda.current_stream().cuda_stream
@@ -363,6 +363,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--smooth-zchunk", type=int, default=0, help="experiment knob: fixed smoother z-chunk on every level (0: the level rule)")
     ap.add_argument("--agg-min-local-nz", type=int, default=0, help="experiment knob: replicate MG levels whose slab is thinner than this (0: library default)")
+    ap.add_argument("--no-p2p", action="store_true", help="experiment knob: halo exchange through ncclSend/ncclRecv instead of peer memory")
     ap.add_argument("--no-overlap", action="store_true", help="experiment knob: halo exchange on the solver stream (overlap_halo=0)")
     ap.add_argument("--verbose", type=int, default=0, help="nodal_proj.verbose (4: per-launch smoother times on stderr)")
     args = ap.parse_args()

@@ -35,7 +35,7 @@ class np_options(C.Structure):
                 ("bottom_rtol", C.c_double), ("bottom_atol", C.c_double),
                 ("smooth_zchunk", C.c_int), ("interp_sigma_weighted", C.c_int), ("bottom_normalize", C.c_int),
                 ("agg_min_local_nz", C.c_int), ("use_graph", C.c_int), ("const_sigma_fastpath", C.c_int),
-                ("profile_kernels", C.c_int), ("overlap_halo", C.c_int)]
+                ("profile_kernels", C.c_int), ("overlap_halo", C.c_int), ("p2p_halo", C.c_int)]
 
 
 class np_stats(C.Structure):

@@ -142,6 +142,80 @@ __global__ void __launch_bounds__(256) k_fill_xy_planes(LevelDev L, double* x, i
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Halo exchange over peer memory (NVLink 5 / NVSwitch): this rank STORES its boundary planes straight into the ghost
+// planes of the neighbours' arrays (opened through CUDA IPC) and the ranks pace each other with four flags per rank
+// that the neighbours write: ready_from_{lo,hi} ("I no longer read the ghost planes you filled last time") and
+// done_from_{lo,hi} ("your ghost planes of this exchange have landed").  One launch per exchange replaces a grouped
+// ncclSend/ncclRecv (about 25 us of latency each on the small MG levels).  Every rank runs the same sequence of
+// exchanges, so a plain epoch counter identifies them.
+// ------------------------------------------------------------------------------------------------
+enum { NP_FLAG_READY_LO = 0, NP_FLAG_READY_HI = 1, NP_FLAG_DONE_LO = 2, NP_FLAG_DONE_HI = 3 };
+struct HaloP2P {
+    const double* send_lo; double* dst_lo; long long n_lo;     // my planes for the lower neighbour -> its array
+    const double* send_hi; double* dst_hi; long long n_hi;
+    unsigned long long* mine;                                  // my four flags (written by the neighbours)
+    unsigned long long* lo_flags; unsigned long long* hi_flags;   // the neighbours' flag arrays (null: no neighbour)
+    unsigned long long epoch;
+    unsigned int* counter;                                     // CTAs of this launch that finished their stores
+};
+__device__ __forceinline__ void np_flag_store(unsigned long long* p, unsigned long long v)
+{
+#ifdef NP_EMU
+    *p = v;
+#else
+    asm volatile("st.release.sys.global.u64 [%0], %1;" :: "l"(p), "l"(v) : "memory");
+#endif
+}
+__device__ __forceinline__ unsigned long long np_flag_load(const unsigned long long* p)
+{
+#ifdef NP_EMU
+    return *p;
+#else
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+#endif
+}
+__global__ void __launch_bounds__(256) k_halo_p2p(HaloP2P a)
+{
+    // 1) this kernel runs after everything that read my ghost planes: tell the neighbours they may overwrite them
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        if (a.lo_flags) np_flag_store(a.lo_flags + NP_FLAG_READY_HI, a.epoch);
+        if (a.hi_flags) np_flag_store(a.hi_flags + NP_FLAG_READY_LO, a.epoch);
+    }
+    // 2) wait until the neighbours have said the same about theirs
+    if (threadIdx.x == 0) {
+        if (a.lo_flags) while (np_flag_load(a.mine + NP_FLAG_READY_LO) < a.epoch) { }
+        if (a.hi_flags) while (np_flag_load(a.mine + NP_FLAG_READY_HI) < a.epoch) { }
+    }
+    __syncthreads();
+    // 3) my boundary planes -> their ghost planes (16-byte stores; plane sizes are even)
+    const long long t0 = blockIdx.x * (long long)blockDim.x + threadIdx.x, nt = (long long)gridDim.x * blockDim.x;
+    if (a.lo_flags) {
+        const double2* s2 = reinterpret_cast<const double2*>(a.send_lo); double2* d2 = reinterpret_cast<double2*>(a.dst_lo);
+        for (long long q = t0; q < a.n_lo / 2; q += nt) d2[q] = s2[q];
+    }
+    if (a.hi_flags) {
+        const double2* s2 = reinterpret_cast<const double2*>(a.send_hi); double2* d2 = reinterpret_cast<double2*>(a.dst_hi);
+        for (long long q = t0; q < a.n_hi / 2; q += nt) d2[q] = s2[q];
+    }
+    // 4) the last CTA to finish publishes "done" and 5) waits for the neighbours' planes to have landed here
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned int prev = atomicAdd(a.counter, 1u);
+        if (prev == gridDim.x - 1) {
+            *a.counter = 0u;
+            __threadfence_system();
+            if (a.lo_flags) np_flag_store(a.lo_flags + NP_FLAG_DONE_HI, a.epoch);
+            if (a.hi_flags) np_flag_store(a.hi_flags + NP_FLAG_DONE_LO, a.epoch);
+            if (a.lo_flags) while (np_flag_load(a.mine + NP_FLAG_DONE_LO) < a.epoch) { }
+            if (a.hi_flags) while (np_flag_load(a.mine + NP_FLAG_DONE_HI) < a.epoch) { }
+        }
+    }
+}
+
 // sigma ghost layer: periodic wrap, else copy of the adjacent interior cell (MLNodeLaplacian::FillBoundaryCoeff)
 // fill_z = 0 leaves the z ghost layers to the halo exchange (rank-interior faces).
 __global__ void __launch_bounds__(256) k_fill_sigma(LevelDev L, double* s, int per0, int per1, int per2, int zlo_local, int zhi_local)

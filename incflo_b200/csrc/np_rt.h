@@ -31,6 +31,9 @@ inline int stream_sync(np_stream_t) { return 0; }
 inline int stream_create(np_stream_t* s) { *s = nullptr; return 0; }
 inline int stream_destroy(np_stream_t) { return 0; }
 inline int stream_wait_event(np_stream_t, np_event_t) { return 0; }     // the emulation runs everything in program order
+inline int ipc_export(void*, void*) { return 1; }                         // no peer memory in the emulation: NCCL-style callbacks only
+inline int ipc_open(const void*, void**) { return 1; }
+inline int ipc_close(void*) { return 0; }
 inline int is_device_ptr(const void*) { return 1; }
 inline int event_create(np_event_t* e) { *e = new np_event_s(); return 0; }
 inline int event_destroy(np_event_t e) { delete e; return 0; }
@@ -63,6 +66,19 @@ inline int stream_sync(np_stream_t s) { return cudaStreamSynchronize(s) == cudaS
 inline int stream_create(np_stream_t* s) { return cudaStreamCreateWithFlags(s, cudaStreamNonBlocking) == cudaSuccess ? 0 : 1; }
 inline int stream_destroy(np_stream_t s) { return cudaStreamDestroy(s) == cudaSuccess ? 0 : 1; }
 inline int stream_wait_event(np_stream_t s, np_event_t e) { return cudaStreamWaitEvent(s, e, 0) == cudaSuccess ? 0 : 1; }
+// CUDA IPC: one process per GPU, so a neighbour's arrays are reached through exported allocation handles (64 bytes)
+inline int ipc_export(void* dev_ptr, void* handle64) {
+    cudaIpcMemHandle_t h;
+    if (cudaIpcGetMemHandle(&h, dev_ptr) != cudaSuccess) { cudaGetLastError(); return 1; }
+    static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    memcpy(handle64, &h, 64); return 0;
+}
+inline int ipc_open(const void* handle64, void** dev_ptr) {
+    cudaIpcMemHandle_t h; memcpy(&h, handle64, 64);
+    if (cudaIpcOpenMemHandle(dev_ptr, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); return 1; }
+    return 0;
+}
+inline int ipc_close(void* dev_ptr) { return cudaIpcCloseMemHandle(dev_ptr) == cudaSuccess ? 0 : 1; }
 inline int is_device_ptr(const void* p) {
     cudaPointerAttributes a;
     if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return 0; }

@@ -144,6 +144,7 @@ int NpSolver::create(const np_geom* g, int nboxes, const np_box* boxes, const in
     }
     if (opt.profile_kernels) { prof_ev.resize(2048); for (auto& e : prof_ev) np_rt::event_create(&e); }
     for (auto& L : lev) setup_level_bc(L);
+    if (nranks > 1 && opt.p2p_halo) setup_peer_halo();
 #ifndef NP_EMU
     cudaFuncSetAttribute(k_gs2<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GS_SMEM_BYTES);
     cudaFuncSetAttribute(k_gs2<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GS_SMEM_BYTES);
@@ -170,6 +171,10 @@ void NpSolver::destroy()
     if (bot_out) np_rt::dev_free(bot_out);
     if (h_bot_out) np_rt::host_free(h_bot_out);
     for (int e = 0; e < 4; ++e) if (ev[e]) np_rt::event_destroy(ev[e]);
+    for (void* m : peer.opened) np_rt::ipc_close(m);
+    peer.opened.clear(); peer.ok = false;
+    if (peer.flags) { np_rt::dev_free(peer.flags); peer.flags = nullptr; }
+    if (peer.counter) { np_rt::dev_free(peer.counter); peer.counter = nullptr; }
     if (have_comm_stream) { np_rt::stream_sync(comm_stream); np_rt::stream_destroy(comm_stream); have_comm_stream = false; }
     for (int e = 0; e < 2; ++e) if (ev_halo[e]) { np_rt::event_destroy(ev_halo[e]); ev_halo[e] = 0; }
     for (auto& e : prof_ev) np_rt::event_destroy(e);
@@ -225,6 +230,81 @@ static void z_neighbours(const NpSolver& S, int& lo, int& hi) {
     hi = r < R - 1 ? r + 1 : (per ? 0 : -1);
 }
 
+// Peer-memory halo exchange, set up once per handle (collective): every rank exports the IPC handles of the arrays that
+// are ever exchanged (cor, cor_alt, rescor of the sharded levels, sol) and of its flag words, all ranks gather them, and
+// each rank maps its two z-neighbours'.  Used only if EVERY rank succeeded; otherwise the NCCL path stays.
+int NpSolver::setup_peer_halo()
+{
+    if (!comm.allgather || !comm.allreduce) return 1;
+    for (auto& L : lev) if (!L.replicated) { peer.mine.push_back(L.cor); peer.mine.push_back(L.cor_alt); peer.mine.push_back(L.rescor); }
+    peer.mine.push_back(sol);
+    void* q = nullptr;
+    if (np_rt::dev_malloc(&q, 8 * sizeof(unsigned long long))) return 1;
+    peer.flags = (unsigned long long*)q; np_rt::memset_async(peer.flags, 0, 8 * sizeof(unsigned long long), stream);
+    if (np_rt::dev_malloc(&q, 4 * sizeof(unsigned int))) return 1;
+    peer.counter = (unsigned int*)q; np_rt::memset_async(peer.counter, 0, 4 * sizeof(unsigned int), stream);
+    const int na = (int)peer.mine.size() + 1;                       // + the flag words
+    std::vector<double> hsend((size_t)na * 8, 0.0), hrecv((size_t)na * 8 * comm.nranks, 0.0);
+    int good = 1;
+    for (int a = 0; a < na; ++a) {
+        void* p = a < na - 1 ? (void*)peer.mine[a] : (void*)peer.flags;
+        if (np_rt::ipc_export(p, &hsend[(size_t)a * 8])) good = 0;
+    }
+    double *dsend = nullptr, *drecv = nullptr;
+    if (alloc_d(&dsend, (long long)na * 8) || alloc_d(&drecv, (long long)na * 8 * comm.nranks)) return 1;
+    np_rt::copy_async(dsend, hsend.data(), hsend.size() * sizeof(double), stream);
+    if (comm.allgather(comm.ctx, dsend, drecv, (long long)na * 8, (void*)stream)) { err = NP_ERR_NCCL; good = 0; }
+    np_rt::copy_async(hrecv.data(), drecv, hrecv.size() * sizeof(double), stream);
+    np_rt::stream_sync(stream);
+    int lo, hi; z_neighbours(*this, lo, hi);
+    peer.lo.assign(na - 1, nullptr); peer.hi.assign(na - 1, nullptr);
+    auto open_rank = [&](int r, std::vector<double*>& arr, unsigned long long** fl) {
+        for (int a = 0; a < na && good; ++a) {
+            void* m = nullptr;
+            if (np_rt::ipc_open(&hrecv[((size_t)r * na + a) * 8], &m)) { good = 0; break; }
+            peer.opened.push_back(m);
+            if (a < na - 1) arr[a] = (double*)m; else *fl = (unsigned long long*)m;
+        }
+    };
+    if (good && lo >= 0) open_rank(lo, peer.lo, &peer.lo_flags);
+    if (good && hi >= 0) {
+        if (hi == lo) { peer.hi = peer.lo; peer.hi_flags = peer.lo_flags; }      // two ranks, periodic: one neighbour on both sides
+        else open_rank(hi, peer.hi, &peer.hi_flags);
+    }
+    // all or nothing: one max-allreduce of "somebody failed"
+    h_scal[16] = good ? 0.0 : 1.0;
+    np_rt::copy_async(scal + 16, h_scal + 16, sizeof(double), stream);
+    if (comm.allreduce(comm.ctx, scal + 16, 1, 1, (void*)stream)) good = 0;
+    np_rt::copy_async(h_scal + 16, scal + 16, sizeof(double), stream);
+    np_rt::stream_sync(stream);
+    np_rt::dev_free(dsend); np_rt::dev_free(drecv);
+    peer.ok = good && h_scal[16] == 0.0;
+    if (opt.verbose >= 1 && comm.rank == 0) std::printf("nodalproj: halo exchange over %s\n", peer.ok ? "peer memory (CUDA IPC, NVLink)" : "NCCL send/recv");
+    return peer.ok ? 0 : 1;
+}
+
+// one exchange of the z-boundary planes of x (level l) through peer memory; false: x is not registered, use NCCL
+bool NpSolver::halo_p2p(int l, double* x)
+{
+    if (!peer.ok) return false;
+    int id = -1;
+    for (int a = 0; a < (int)peer.mine.size(); ++a) if (peer.mine[a] == x) { id = a; break; }
+    if (id < 0) return false;
+    const LevelDev& d = lev[l].d;
+    const long long pl = d.nsz;
+    int lo, hi; z_neighbours(*this, lo, hi);
+    HaloP2P a{};
+    // to the lower rank: my planes 0,1 -> its n2, n2+1; to the upper rank: my plane n2-1 -> its -1 (all slabs are equal)
+    a.send_lo = x + pl * 1; a.n_lo = 2 * pl; a.dst_lo = lo >= 0 ? peer.lo[id] + pl * (long long)(d.n[2] + 1) : nullptr;
+    a.send_hi = x + pl * (long long)d.n[2]; a.n_hi = pl; a.dst_hi = hi >= 0 ? peer.hi[id] + 0 : nullptr;
+    a.mine = peer.flags; a.lo_flags = lo >= 0 ? peer.lo_flags : nullptr; a.hi_flags = hi >= 0 ? peer.hi_flags : nullptr;
+    a.epoch = ++peer.epoch; a.counter = peer.counter;
+    const long long chunks = (3 * pl / 2 + 255) / 256;                          // 16-byte stores per thread pass
+    const int nb = (int)std::min<long long>(64, std::max<long long>(1, chunks / 8));
+    NP_LAUNCH(false, k_halo_p2p, dim3(nb), dim3(256), 0, stream, a); ++launches;
+    return true;
+}
+
 // FillBoundary + nodalSync + applyBC on one nodal array
 void NpSolver::fill(int l, double* x)
 {
@@ -233,6 +313,7 @@ void NpSolver::fill(int l, double* x)
     const long long nshell = 3LL * ((long long)(d.n[1]+3)*(d.n[2]+3) + (long long)(d.n[0]+3)*(d.n[2]+3) + (long long)(d.n[0]+3)*(d.n[1]+3));
     NP_LAUNCH(false, k_fill_boundary, dim3(shell_blocks(nshell)), dim3(256), 0, stream, d, x); ++launches;
     if (is_sharded(*this, L)) {
+        if (halo_p2p(l, x)) return;
         int lo, hi; z_neighbours(*this, lo, hi);
         const long long pl = d.nsz;
         // to the lower rank: my planes 0,1 (its n2, n2+1); to the upper rank: my plane n2-1 (its -1)

@@ -58,6 +58,17 @@ struct NpSolver {
     np_stream_t comm_stream = 0;       // multi-GPU: halo exchange of the end chunks runs here, beside the interior chunks
     np_event_t ev_halo[2] = {0, 0};    // [0] end chunks done (solver stream), [1] exchange done (comm stream)
     bool have_comm_stream = false;
+    // peer-memory halo exchange (p2p_halo): arrays that take part, the neighbours' views of them, and the pacing flags
+    struct PeerHalo {
+        bool ok = false;
+        std::vector<double*> mine, lo, hi;          // registered local arrays and the same arrays of the lower / upper rank
+        std::vector<void*> opened;                  // IPC mappings to close
+        unsigned long long *flags = nullptr, *lo_flags = nullptr, *hi_flags = nullptr;
+        unsigned int* counter = nullptr;
+        unsigned long long epoch = 0;
+    } peer;
+    int setup_peer_halo();
+    bool halo_p2p(int l, double* x);
     std::vector<np_event_t> prof_ev;   // profile_kernels: start/stop pairs around level-0 smoother launches
     int prof_n = 0;
     np_stats stats{};

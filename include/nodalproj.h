@@ -81,6 +81,9 @@ typedef struct {
                                    while the interior chunks are relaxed (levels of >= 4 waves of CTAs only); default 0:
                                    measured 1.4 % slower than the plain order on 2 B200s; < 0: on every
                                    sharded level with three or more chunks (tests) */
+    int p2p_halo;               /* multi-GPU: halo planes are stored straight into the neighbours' arrays over NVLink (CUDA IPC
+                                   peer memory + flags, one kernel per exchange) instead of grouped ncclSend/ncclRecv;
+                                   default 1, falls back to NCCL when peer memory cannot be opened on every rank */
 } np_options;
 
 typedef struct {

@@ -141,6 +141,7 @@ template <class T> static inline T __shfl_sync(unsigned, T v, int l) {
 template <class T> static inline T __ldg(const T* p) { return *p; }
 static inline double __drcp_rn(double x) { return 1.0 / x; }
 static inline unsigned atomicAdd(unsigned* p, unsigned v) { unsigned o = *p; *p += v; return o; }
+static inline void __threadfence_system() {}
 static inline int atomicAdd(int* p, int v) { int o = *p; *p += v; return o; }
 static inline double atomicAdd(double* p, double v) { double o = *p; *p += v; return o; }
 static inline unsigned atomicInc(unsigned* p, unsigned lim) { unsigned o = *p; *p = (o >= lim) ? 0 : o + 1; return o; }
