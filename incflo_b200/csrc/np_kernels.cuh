@@ -397,7 +397,7 @@ __device__ __forceinline__ void np_cp_async_wait_all()
 #endif
 }
 
-// Cooperative plane loader shared by k_gs2 and k_stencil_cs: 198 of the 256 threads each own one of the 66
+// Cooperative plane loader shared by k_gs2 and k_stencil: 198 of the 256 threads each own one of the 66
 // columns (tile halo included) of three interleaved row sets, so a plane costs 12 cp.async per thread with
 // one add per address.  Source offsets are relative to the plane, destinations are split-layout slots.
 struct GsLoader {
