@@ -40,9 +40,9 @@ int np_set_bc(np_handle* h, const int lo[3], const int hi[3]) { return h ? h->S.
 
 int np_project(np_handle* h, int nlocal, np_fab* vel, const np_fab* sigma, double rtol, double atol, void* cuda_stream, np_stats* out)
 {
-    if (!h || nlocal != 1 || !vel || !sigma || !vel->p || !sigma->p) return NP_ERR_INVALID;
+    if (!h || nlocal != (int)h->S.lbox.size() || !vel || !sigma || !vel->p || !sigma->p) return NP_ERR_INVALID;
     h->S.stream = (np_stream_t)cuda_stream;
-    int rc = h->S.project(vel, sigma, rtol, atol);
+    int rc = nlocal == 1 ? h->S.project(vel, sigma, rtol, atol) : h->S.project_boxes(nlocal, vel, sigma, rtol, atol);
     if (out) *out = h->S.stats;
     return rc;
 }
@@ -51,6 +51,7 @@ int np_apply_projection(np_handle* h, np_fab* vel, const np_fab* vel_old, const 
                         const np_apply_args* args, double rtol, double atol, void* cuda_stream, np_stats* out)
 {
     if (!h || !vel || !density || !gp || !p || !args || !vel->p || !density->p || !gp->p || !p->p) return NP_ERR_INVALID;
+    if (h->S.lbox.size() != 1) return NP_ERR_INVALID;      // one box per rank only (several boxes: np_project)
     h->S.stream = (np_stream_t)cuda_stream;
     int rc = h->S.apply_projection(vel, vel_old, density, gp, p, args, rtol, atol);
     if (out) *out = h->S.stats;
@@ -61,26 +62,29 @@ int np_last_stats(np_handle* h, np_stats* out) { if (!h || !out) return NP_ERR_I
 
 int np_get_phi(np_handle* h, int local_box, np_fab* out)
 {
-    if (!h || local_box != 0 || !out) return NP_ERR_INVALID;
+    if (!h || local_box < 0 || local_box >= (int)h->S.lbox.size() || !out) return NP_ERR_INVALID;
     if (!h->S.have_result) return NP_ERR_STATE;
-    out->p = h->S.phi_out; out->ngrow = 1; out->ncomp = 1;
+    out->p = h->S.lbox.size() == 1 ? h->S.phi_out : h->S.mb_phi[local_box]; out->ngrow = 1; out->ncomp = 1;
     return NP_OK;
 }
 int np_get_gradphi(np_handle* h, int local_box, np_fab* out)
 {
-    if (!h || local_box != 0 || !out) return NP_ERR_INVALID;
+    if (!h || local_box < 0 || local_box >= (int)h->S.lbox.size() || !out) return NP_ERR_INVALID;
     if (!h->S.have_result) return NP_ERR_STATE;
-    out->p = h->S.gphi; out->ngrow = 1; out->ncomp = 3;
+    out->p = h->S.lbox.size() == 1 ? h->S.gphi : h->S.mb_gphi[local_box]; out->ngrow = 1; out->ncomp = 3;
     return NP_OK;
 }
 
 // copy internal results into a caller fab (host or device, any ngrow): interior (+ min(ngrow,1) ghosts).
 // Host destination: a fab with ngrow == 1 has exactly the internal layout -> one device-to-host copy; any other
 // ngrow is repacked on the device into the persistent staging buffer first.
-static int copy_out(NpSolver& S, np_fab* dst, const double* src_fab1, bool nodal, int ncomp)
+static int copy_out(NpSolver& S, int local_box, np_fab* dst, const double* src_fab1, bool nodal, int ncomp)
 {
-    const LevelDev& d = S.lev[0].d;
-    FabView v = nodal ? S.view_nodal(*dst, 0) : S.view_cell(*dst, 0, ncomp);
+    struct { int n[3]; } d;      // cells of the box the fab belongs to
+    for (int q = 0; q < 3; ++q) d.n[q] = S.lbox[local_box].hi[q] - S.lbox[local_box].lo[q] + 1;
+    FabView v; v.p = dst->p; v.ng = dst->ngrow;
+    v.sy = d.n[0] + (nodal ? 1 : 0) + 2 * dst->ngrow; v.sz = v.sy * (d.n[1] + (nodal ? 1 : 0) + 2 * dst->ngrow);
+    v.sn = v.sz * (d.n[2] + (nodal ? 1 : 0) + 2 * dst->ngrow);
     const long long nelem = v.sn * ncomp;
     bool host = false;
 #ifndef NP_EMU
@@ -105,15 +109,15 @@ static int copy_out(NpSolver& S, np_fab* dst, const double* src_fab1, bool nodal
 }
 int np_copy_phi(np_handle* h, int local_box, np_fab* dst)
 {
-    if (!h || local_box != 0 || !dst || !dst->p) return NP_ERR_INVALID;
+    if (!h || local_box < 0 || local_box >= (int)h->S.lbox.size() || !dst || !dst->p) return NP_ERR_INVALID;
     if (!h->S.have_result) return NP_ERR_STATE;
-    return copy_out(h->S, dst, h->S.phi_out, true, 1);
+    return copy_out(h->S, local_box, dst, h->S.lbox.size() == 1 ? h->S.phi_out : h->S.mb_phi[local_box], true, 1);
 }
 int np_copy_gradphi(np_handle* h, int local_box, np_fab* dst)
 {
-    if (!h || local_box != 0 || !dst || !dst->p || dst->ncomp < 3) return NP_ERR_INVALID;
+    if (!h || local_box < 0 || local_box >= (int)h->S.lbox.size() || !dst || !dst->p || dst->ncomp < 3) return NP_ERR_INVALID;
     if (!h->S.have_result) return NP_ERR_STATE;
-    return copy_out(h->S, dst, h->S.gphi, false, 3);
+    return copy_out(h->S, local_box, dst, h->S.lbox.size() == 1 ? h->S.gphi : h->S.mb_gphi[local_box], false, 3);
 }
 
 int np_is_device_pointer(const void* p)

@@ -1487,6 +1487,26 @@ __global__ void __launch_bounds__(256) k_copy_cell(int n0, int n1, FabView dst, 
     if (i >= n0 + ngc || j >= n1 + ngc) return;
     for (int n = 0; n < ncomp; ++n) dst.p[np_foff(dst, i, j, k, n)] = src.p[np_foff(src, i, j, k, n)];
 }
+// Several boxes per rank (np_project with nlocal > 1): one box of the caller's MultiFab <-> this rank's slab.
+// Indices are slab-local.  `dst` / `src` are views whose index origin (first valid cell / node) sits at dorg / sorg.
+// The region [rlo, rhi] is copied; with guard != 0 (gather of vel, whose ghost layer is part of the region) a cell is
+// taken only if it lies inside the box's valid range [vlo, vhi] or outside the problem domain [dlo, dhi] - the physical
+// ghost cells ApplyProjection prepared (zero / inflow); ghost cells over other boxes belong to those boxes.
+struct BoxCopy { int rlo[3], rhi[3], dorg[3], sorg[3], vlo[3], vhi[3], dlo[3], dhi[3]; int guard; };
+__global__ void __launch_bounds__(256) k_box_copy(FabView dst, FabView src, BoxCopy a, int ncomp)
+{
+    const int i = (int)(blockIdx.x * blockDim.x + threadIdx.x) + a.rlo[0];
+    const int j = (int)(blockIdx.y * blockDim.y + threadIdx.y) + a.rlo[1];
+    const int k = (int)blockIdx.z + a.rlo[2];
+    if (i > a.rhi[0] || j > a.rhi[1]) return;
+    if (a.guard) {
+        const bool in_box = i >= a.vlo[0] && i <= a.vhi[0] && j >= a.vlo[1] && j <= a.vhi[1] && k >= a.vlo[2] && k <= a.vhi[2];
+        const bool outside = i < a.dlo[0] || i > a.dhi[0] || j < a.dlo[1] || j > a.dhi[1] || k < a.dlo[2] || k > a.dhi[2];
+        if (!in_box && !outside) return;
+    }
+    for (int n = 0; n < ncomp; ++n)
+        dst.p[np_foff(dst, i - a.dorg[0], j - a.dorg[1], k - a.dorg[2], n)] = src.p[np_foff(src, i - a.sorg[0], j - a.sorg[1], k - a.sorg[2], n)];
+}
 __global__ void __launch_bounds__(256) k_copy_sigma_out(LevelDev L, const double* __restrict__ s, FabView dst)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;

@@ -60,15 +60,33 @@ int NpSolver::create(const np_geom* g, int nboxes, const np_box* boxes, const in
 {
     if (np_rt::init()) return NP_ERR_NO_DEVICE;
     geom = *g; opt = *o; comm = c; comm.rank = my_rank; comm.nranks = nranks;
-    // ---- box layout: one box (nranks == 1) or equal z-slabs ordered by rank ----
-    if (nboxes != nranks) return NP_ERR_INVALID;
+    // ---- box layout: the boxes of rank r tile the r-th of nranks equal z-slabs (one box per rank: used as it is;
+    //      several: gathered into the slab by np_project, see project_boxes) ----
+    if (nboxes < nranks) return NP_ERR_INVALID;
     const int nzl = g->ncell[2] / nranks;
     if (nzl * nranks != g->ncell[2]) return NP_ERR_INVALID;
-    for (int r = 0; r < nranks; ++r) {
-        const np_box& b = boxes[r];
-        if (owner[r] != r) return NP_ERR_INVALID;
-        if (b.lo[0] != 0 || b.lo[1] != 0 || b.hi[0] != g->ncell[0]-1 || b.hi[1] != g->ncell[1]-1) return NP_ERR_INVALID;
-        if (b.lo[2] != r*nzl || b.hi[2] != (r+1)*nzl-1) return NP_ERR_INVALID;
+    {
+        std::vector<long long> vol(nranks, 0);
+        for (int b = 0; b < nboxes; ++b) {
+            const np_box& bx = boxes[b];
+            const int r = owner[b];
+            if (r < 0 || r >= nranks) return NP_ERR_INVALID;
+            for (int d = 0; d < 3; ++d) if (bx.lo[d] > bx.hi[d]) return NP_ERR_INVALID;
+            if (bx.lo[0] < 0 || bx.lo[1] < 0 || bx.hi[0] >= g->ncell[0] || bx.hi[1] >= g->ncell[1]) return NP_ERR_INVALID;
+            if (bx.lo[2] < r * nzl || bx.hi[2] >= (r + 1) * nzl) return NP_ERR_INVALID;       // inside its owner's slab
+            vol[r] += (long long)(bx.hi[0] - bx.lo[0] + 1) * (bx.hi[1] - bx.lo[1] + 1) * (bx.hi[2] - bx.lo[2] + 1);
+        }
+        // inside the slab + total volume == slab volume + pairwise disjoint (checked for this rank's boxes) <=> exact tiling
+        for (int r = 0; r < nranks; ++r) if (vol[r] != (long long)g->ncell[0] * g->ncell[1] * nzl) return NP_ERR_INVALID;
+        lbox.clear();
+        for (int b = 0; b < nboxes; ++b) if (owner[b] == my_rank) {
+            np_box q = boxes[b]; q.lo[2] -= my_rank * nzl; q.hi[2] -= my_rank * nzl; lbox.push_back(q);
+        }
+        for (size_t a = 0; a < lbox.size(); ++a) for (size_t b = a + 1; b < lbox.size(); ++b) {
+            bool ov = true;
+            for (int d = 0; d < 3; ++d) if (lbox[a].hi[d] < lbox[b].lo[d] || lbox[b].hi[d] < lbox[a].lo[d]) ov = false;
+            if (ov) return NP_ERR_INVALID;
+        }
     }
     nloc[0] = g->ncell[0]; nloc[1] = g->ncell[1]; nloc[2] = nzl; koff = my_rank * nzl;
     for (int d = 0; d < 3; ++d) { bclo[d] = bchi[d] = g->periodic[d] ? NP_BC_PERIODIC : NP_BC_NEUMANN; }
@@ -164,8 +182,11 @@ void NpSolver::destroy()
     np_rt::stream_sync(stream);
     for (auto& L : lev) { np_rt::dev_free(L.sigma); np_rt::dev_free(L.res); np_rt::dev_free(L.cor); np_rt::dev_free(L.cor_alt); np_rt::dev_free(L.rescor); }
     lev.clear();
-    double* ds[] = {sol, rhs, gphi, phi_out, part0, part1, scal, xbuf_lo, xbuf_hi, agg_send, agg_recv, stage[0], stage[1], stage[2]};
+    double* ds[] = {sol, rhs, gphi, phi_out, part0, part1, scal, xbuf_lo, xbuf_hi, agg_send, agg_recv, stage[0], stage[1], stage[2], mb_vel, mb_sig};
     for (double* p : ds) if (p) np_rt::dev_free(p);
+    for (double* p : mb_phi) if (p) np_rt::dev_free(p);
+    for (double* p : mb_gphi) if (p) np_rt::dev_free(p);
+    mb_phi.clear(); mb_gphi.clear(); mb_vel = mb_sig = nullptr;
     for (int w = 0; w < 7; ++w) if (bw[w]) np_rt::dev_free(bw[w]);
     if (h_scal) np_rt::host_free(h_scal);
     if (bot_out) np_rt::dev_free(bot_out);
@@ -848,6 +869,102 @@ int NpSolver::project(np_fab* vel, const np_fab* sigma, double rtol, double atol
     if (np_rt::last_error()) { stats.status = NP_ERR_CUDA; return NP_ERR_CUDA; }
     if (err) { stats.status = err; return err; }
     have_result = true;
+    return rc;
+}
+
+// np_project with several boxes per rank.  AMReX hands the projector a MultiFab whose boxes (max_grid_size, default 32
+// cells in 3D) are spread over the ranks; here the boxes of a rank must tile its z-slab.  Each box's u* (valid cells and
+// the physical ghost cells outside the domain, which carry 0 or the inflow velocity) and sigma are gathered into
+// slab-shaped fabs, NodalProjector::project runs on the slab as for a one-box layout, and u, phi (nodal, 1 ghost) and
+// grad(phi) (cell, 3 comp, 1 ghost) are scattered back box by box; the ghost layers of the per-box results are the
+// neighbouring boxes' values, i.e. what FillBoundary leaves there in the reference.
+void NpSolver::box_copy(const FabView& dst, const int dorg[3], const FabView& src, const int sorg[3], const int rlo[3],
+                        const int rhi[3], int ncomp, const np_box* guard_valid)
+{
+    BoxCopy a;
+    for (int d = 0; d < 3; ++d) {
+        a.rlo[d] = rlo[d]; a.rhi[d] = rhi[d]; a.dorg[d] = dorg[d]; a.sorg[d] = sorg[d];
+        a.vlo[d] = guard_valid ? guard_valid->lo[d] : 0; a.vhi[d] = guard_valid ? guard_valid->hi[d] : 0;
+        a.dlo[d] = 0; a.dhi[d] = geom.ncell[d] - 1;
+    }
+    a.dlo[2] = -koff; a.dhi[2] = geom.ncell[2] - 1 - koff;       // the domain in slab-local z
+    a.guard = guard_valid ? 1 : 0;
+    if (rhi[0] < rlo[0] || rhi[1] < rlo[1] || rhi[2] < rlo[2]) return;
+    NP_LAUNCH(false, k_box_copy, dim3((rhi[0] - rlo[0] + 32) / 32, (rhi[1] - rlo[1] + 8) / 8, rhi[2] - rlo[2] + 1), NP_BLK, 0, stream,
+              dst, src, a, ncomp); ++launches;
+}
+static FabView box_view(double* p, const np_box& b, int ng, int nodal)
+{
+    FabView v; v.p = p; v.ng = ng;
+    v.sy = b.hi[0] - b.lo[0] + 1 + nodal + 2 * ng;
+    v.sz = v.sy * (b.hi[1] - b.lo[1] + 1 + nodal + 2 * ng);
+    v.sn = v.sz * (b.hi[2] - b.lo[2] + 1 + nodal + 2 * ng);
+    return v;
+}
+int NpSolver::project_boxes(int nlocal, np_fab* vel, const np_fab* sigma, double rtol, double atol)
+{
+    if (nlocal != (int)lbox.size()) return NP_ERR_INVALID;
+    const LevelDev& d0 = lev[0].d;
+    const int zero3[3] = {0, 0, 0};
+    np_box slab; for (int d = 0; d < 3; ++d) { slab.lo[d] = 0; slab.hi[d] = d0.n[d] - 1; }
+    const FabView us = box_view(nullptr, slab, 1, 0), ss = box_view(nullptr, slab, 0, 0);
+    if (!mb_vel) {
+        if (alloc_d(&mb_vel, us.sn * 3) || alloc_d(&mb_sig, ss.sn)) return NP_ERR_CUDA;
+        mb_phi.assign(nlocal, nullptr); mb_gphi.assign(nlocal, nullptr);
+        for (int b = 0; b < nlocal; ++b)
+            if (alloc_d(&mb_phi[b], box_view(nullptr, lbox[b], 1, 1).sn) || alloc_d(&mb_gphi[b], box_view(nullptr, lbox[b], 1, 0).sn * 3)) return NP_ERR_CUDA;
+    }
+    bool host = false;
+#ifndef NP_EMU
+    host = !np_rt::is_device_ptr(vel[0].p);
+#endif
+    // host callers: every box's vel is kept in a persistent device staging area (slot 0) until it is copied back
+    mb_stage_off.assign(nlocal + 1, 0);
+    long long smax = 0;
+    for (int b = 0; b < nlocal; ++b) {
+        if (!vel[b].p || !sigma[b].p || vel[b].ngrow < 1 || vel[b].ncomp < 3 || sigma[b].ncomp < 1) return NP_ERR_INVALID;
+        mb_stage_off[b + 1] = mb_stage_off[b] + box_view(nullptr, lbox[b], vel[b].ngrow, 0).sn * 3;
+        smax = std::max(smax, box_view(nullptr, lbox[b], sigma[b].ngrow, 0).sn);
+    }
+    double *stv = nullptr, *sts = nullptr;
+    if (host && (!(stv = stage_get(0, mb_stage_off[nlocal])) || !(sts = stage_get(1, smax)))) return NP_ERR_CUDA;
+    FabView usv = us; usv.p = mb_vel;
+    FabView ssv = ss; ssv.p = mb_sig;
+    zero(mb_vel, us.sn * 3);
+    long long gather_launches = 0;
+    for (int b = 0; b < nlocal; ++b) {
+        const np_box& bx = lbox[b];
+        FabView uv = box_view(vel[b].p, bx, vel[b].ngrow, 0), sv = box_view(sigma[b].p, bx, sigma[b].ngrow, 0);
+        if (host) {
+            uv.p = stv + mb_stage_off[b]; sv.p = sts;
+            np_rt::copy_async(uv.p, vel[b].p, (size_t)(uv.sn * 3) * sizeof(double), stream);
+            np_rt::copy_async(sv.p, sigma[b].p, (size_t)sv.sn * sizeof(double), stream);
+        }
+        int rlo[3], rhi[3];
+        for (int d = 0; d < 3; ++d) { rlo[d] = bx.lo[d] - 1; rhi[d] = bx.hi[d] + 1; }
+        box_copy(usv, zero3, uv, bx.lo, rlo, rhi, 3, &bx);
+        box_copy(ssv, zero3, sv, bx.lo, bx.lo, bx.hi, 1, nullptr);
+        gather_launches += 2;
+    }
+    np_fab vslab{mb_vel, 1, 3}, sslab{mb_sig, 0, 1};
+    const int rc = project(&vslab, &sslab, rtol, atol);
+    if (rc && !have_result) return rc;
+    // ---- scatter: u (valid cells), phi and grad(phi) with their ghost layers ----
+    FabView pv; pv.p = phi_out; pv.ng = 1; pv.sy = d0.n[0] + 3; pv.sz = pv.sy * (d0.n[1] + 3); pv.sn = pv.sz * (d0.n[2] + 3);
+    FabView gv = us; gv.p = gphi;
+    for (int b = 0; b < nlocal; ++b) {
+        const np_box& bx = lbox[b];
+        FabView uv = box_view(host ? stv + mb_stage_off[b] : vel[b].p, bx, vel[b].ngrow, 0);
+        box_copy(uv, bx.lo, usv, zero3, bx.lo, bx.hi, 3, nullptr);
+        if (host) np_rt::copy_async(vel[b].p, uv.p, (size_t)(uv.sn * 3) * sizeof(double), stream);
+        int rlo[3], rhi[3], nhi[3];
+        for (int d = 0; d < 3; ++d) { rlo[d] = bx.lo[d] - 1; rhi[d] = bx.hi[d] + 1; nhi[d] = bx.hi[d] + 2; }
+        box_copy(box_view(mb_phi[b], bx, 1, 1), bx.lo, pv, zero3, rlo, nhi, 1, nullptr);
+        box_copy(box_view(mb_gphi[b], bx, 1, 0), bx.lo, gv, zero3, rlo, rhi, 3, nullptr);
+    }
+    np_rt::stream_sync(stream);
+    stats.kernel_launches = launches + gather_launches;
+    if (np_rt::last_error()) { stats.status = NP_ERR_CUDA; return NP_ERR_CUDA; }
     return rc;
 }
 

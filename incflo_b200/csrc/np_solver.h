@@ -69,6 +69,16 @@ struct NpSolver {
     } peer;
     int setup_peer_halo();
     bool halo_p2p(int l, double* x);
+    // several boxes per rank: the caller's boxes tile this rank's z-slab; they are gathered into slab-shaped fabs
+    // (mb_vel: 3 comp, 1 ghost; mb_sig: 1 comp, 0 ghost), the projection runs on the slab, and u / phi / grad(phi)
+    // are scattered back into per-box fabs (mb_phi, mb_gphi: the library-owned results np_get_* hands out)
+    std::vector<np_box> lbox;       // this rank's boxes in BoxArray order, slab-local cell indices
+    double *mb_vel = nullptr, *mb_sig = nullptr;
+    std::vector<double*> mb_phi, mb_gphi;
+    std::vector<long long> mb_stage_off;   // host callers: offset of every box inside stage[0] (vel)
+    int project_boxes(int nlocal, np_fab* vel, const np_fab* sigma, double rtol, double atol);
+    void box_copy(const FabView& dst, const int dorg[3], const FabView& src, const int sorg[3], const int rlo[3], const int rhi[3],
+                  int ncomp, const np_box* guard_valid);
     std::vector<np_event_t> prof_ev;   // profile_kernels: start/stop pairs around level-0 smoother launches
     int prof_n = 0;
     np_stats stats{};

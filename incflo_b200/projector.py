@@ -123,13 +123,15 @@ class LPInfo:
 class NodalProjector:
     """Drop-in for amrex::NodalProjector on one AMR level.
 
-    boxes: list of (lo, hi) cell boxes of the level-0 BoxArray (one per rank, equal z-slabs), default one
-    box covering the domain.  nccl_comm: void* from capi np_nccl_comm_create when nranks > 1.
+    boxes: list of (lo, hi) cell boxes of the level-0 BoxArray, default one box covering the domain; owner: the
+    DistributionMapping (rank of every box), default box b -> rank b.  The boxes of rank r must tile the r-th of
+    nranks equal z-slabs.  With several boxes on this rank `vel` / `sigma` are lists of Fabs in BoxArray order (what
+    MFIter visits) and getPhi / getGradPhi return lists.  nccl_comm: void* from capi np_nccl_comm_create when nranks > 1.
     Extra keyword options are the `nodal_proj.*` ParmParse keys / implementation knobs of np_options.
     """
 
     def __init__(self, vel, sigma, geom, info=None, boxes=None, rank=0, nranks=1, nccl_comm=None, lib=None,
-                 **options):
+                 owner=None, **options):
         self.L = lib or capi.load()
         self.vel, self.sigma, self.geom = vel, sigma, geom
         info = info or LPInfo()
@@ -140,7 +142,9 @@ class NodalProjector:
         for b, (lo, hi) in enumerate(boxes):
             for d in range(3):
                 bx[b].lo[d], bx[b].hi[d] = int(lo[d]), int(hi[d])
-        owner = (C.c_int * len(boxes))(*range(len(boxes)))
+        owner = list(range(len(boxes))) if owner is None else [int(r) for r in owner]
+        self.local_boxes = [(tuple(lo), tuple(hi)) for (lo, hi), r in zip(boxes, owner) if r == rank]
+        owner = (C.c_int * len(boxes))(*owner)
         self.h = C.c_void_p()
         g = geom.c()
         capi.check(self.L, self.L.np_create(C.byref(self.h), C.byref(g), len(boxes), bx, owner, rank, nranks,
@@ -168,33 +172,46 @@ class NodalProjector:
 
     def project(self, rtol, atol, stream=None, raise_on_fail=True):
         st = capi.np_stats()
-        v, s = self.vel.c(), self.sigma.c()
-        rc = self.L.np_project(self.h, 1, C.byref(v), C.byref(s), rtol, atol, C.c_void_p(stream) if stream else None,
-                               C.byref(st))
+        if isinstance(self.vel, (list, tuple)):
+            nloc = len(self.vel)
+            v = (capi.np_fab * nloc)(*[f.c() for f in self.vel])
+            s = (capi.np_fab * nloc)(*[f.c() for f in self.sigma])
+            rc = self.L.np_project(self.h, nloc, v, s, rtol, atol, C.c_void_p(stream) if stream else None, C.byref(st))
+        else:
+            v, s = self.vel.c(), self.sigma.c()
+            rc = self.L.np_project(self.h, 1, C.byref(v), C.byref(s), rtol, atol, C.c_void_p(stream) if stream else None,
+                                   C.byref(st))
         self.stats = st
         if rc and raise_on_fail:
             capi.check(self.L, rc)      # reference behaviour: amrex::Abort("MLMG failed")
         return st
 
-    def _borrow(self, getter, ncell, ncomp, nodal):
+    def _borrow(self, getter, ncell, ncomp, nodal, box=0):
         f = capi.np_fab()
-        capi.check(self.L, getter(self.h, 0, C.byref(f)))
+        capi.check(self.L, getter(self.h, box, C.byref(f)))
         n = [x + (1 if nodal else 0) + 2 * f.ngrow for x in ncell]
         shape = (ncomp, n[2], n[1], n[0])
         if not hasattr(self.L, "np_emu_set_comm"):
             # the CUDA library hands back DEVICE pointers whatever the inputs were: zero-copy alias of the
             # projector-owned buffer (valid until the next project()/close())
             import torch
-            dev = self.vel.data.device if getattr(self.vel.data, "is_cuda", False) else torch.device("cuda", torch.cuda.current_device())
+            v0 = self.vel[0] if isinstance(self.vel, (list, tuple)) else self.vel
+            dev = v0.data.device if getattr(v0.data, "is_cuda", False) else torch.device("cuda", torch.cuda.current_device())
             return Fab(_alias_cuda(f.p, shape, dev), f.ngrow, nodal)
         arr = np.ctypeslib.as_array(C.cast(f.p, C.POINTER(C.c_double)), shape=shape)
         return Fab(arr, f.ngrow, nodal)
 
+    def _results(self, getter, ncomp, nodal):
+        if not isinstance(self.vel, (list, tuple)):
+            return self._borrow(getter, self.nloc, ncomp, nodal)
+        return [self._borrow(getter, tuple(h - l + 1 for l, h in zip(lo, hi)), ncomp, nodal, b)
+                for b, (lo, hi) in enumerate(self.local_boxes)]
+
     def getPhi(self):
-        return self._borrow(self.L.np_get_phi, self.nloc, 1, True)
+        return self._results(self.L.np_get_phi, 1, True)
 
     def getGradPhi(self):
-        return self._borrow(self.L.np_get_gradphi, self.nloc, 3, False)
+        return self._results(self.L.np_get_gradphi, 3, False)
 
     # ---- introspection ----
     @property

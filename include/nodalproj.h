@@ -102,15 +102,23 @@ typedef struct {
 void np_default_options(np_options* o);
 
 /* One handle per (geometry, box layout, rank).  all_boxes lists every box of the level-0 BoxArray with
- * its owner rank.  Supported layouts: one box covering the domain (nranks == 1), or nranks boxes that
- * are equal z-slabs ordered by rank.  nccl_comm: an initialised ncclComm_t (as void*) when nranks > 1. */
+ * its owner rank (the DistributionMapping).  Supported layouts: the domain is cut into nranks equal z-slabs,
+ * slab r belongs to rank r, and the boxes owned by rank r tile slab r exactly (any number of boxes per rank, e.g.
+ * amr.max_grid_size = 32; one box per rank is the zero-copy case).  This rank's boxes, in all_boxes order, are its
+ * "local boxes" 0..nlocal-1 below - the order MFIter visits them.  nccl_comm: an initialised ncclComm_t (as void*)
+ * when nranks > 1. */
 int np_create(np_handle** h, const np_geom* geom, int nboxes_global, const np_box* all_boxes,
               const int* owner_rank, int my_rank, int nranks, void* nccl_comm_or_null, const np_options* opt);
 int np_set_bc(np_handle* h, const int lo[3], const int hi[3]);
 
-/* vel: cell, 3 comp, >= 1 ghost, modified in place (ghost cells outside inflow faces carry the inflow
- * velocity, all other physical ghosts 0 — what ApplyProjection prepares at :139-146).
- * sigma: cell, 1 comp, any ghost count (ghosts are not read).  cuda_stream: cudaStream_t or NULL. */
+/* vel, sigma: arrays of nlocal fabs, one per local box.
+ * vel: cell, 3 comp, >= 1 ghost, valid cells modified in place (ghost cells outside inflow faces carry the inflow
+ * velocity, all other physical ghosts 0 - what ApplyProjection prepares at :139-146; ghost cells inside the domain
+ * are not read: the library does the FillBoundary).
+ * sigma: cell, 1 comp, any ghost count (ghosts are not read).  cuda_stream: cudaStream_t or NULL.
+ * nlocal == 1: the fabs are used in place.  nlocal > 1: the boxes are gathered into one slab-shaped device fab per
+ * rank (two extra streaming passes over u, one over sigma) and the results scattered back; np_stats' device timings
+ * cover the projection proper, not the gather / scatter. */
 int np_project(np_handle* h, int nlocal, np_fab* vel, const np_fab* sigma,
                double rtol, double atol, void* cuda_stream, np_stats* out);
 
@@ -136,8 +144,9 @@ typedef struct {
 int np_apply_projection(np_handle* h, np_fab* vel, const np_fab* vel_old, const np_fab* density, np_fab* gp, np_fab* p,
                         const np_apply_args* args, double rtol, double atol, void* cuda_stream, np_stats* out);
 
-/* Borrowed device pointers, valid until the next np_project / np_destroy.
- * phi: nodal, 1 comp, 1 ghost.  gradphi: cell, 3 comp, 1 ghost. */
+/* Borrowed device pointers to the results on local box `local_box`, valid until the next np_project / np_destroy.
+ * phi: nodal, 1 comp, 1 ghost.  gradphi: cell, 3 comp, 1 ghost.  Ghost layers hold the neighbouring boxes' / periodic
+ * images' values (what FillBoundary leaves in the reference). */
 int np_get_phi(np_handle* h, int local_box, np_fab* out);
 int np_get_gradphi(np_handle* h, int local_box, np_fab* out);
 /* Copy the results into caller-owned fabs (host or device pointers, any ngrow >= 0). */

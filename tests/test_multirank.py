@@ -24,7 +24,7 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, name, ncell, kw, agg_min, overlap, outdir):
+def _worker(rank, world, port, name, ncell, kw, agg_min, overlap, outdir, mbox=None):
     import torch
     import torch.distributed as dist
     from incflo_b200.projector import Fab, Geometry, LPInfo, NodalProjector
@@ -75,12 +75,34 @@ def _worker(rank, world, port, name, ncell, kw, agg_min, overlap, outdir):
     sig = Fab.from_array(prob["sigma"][sl], 0)
     geom = Geometry(ncell, prob["prob_lo"], prob["prob_hi"], [b == 0 for b in prob["bclo"]])
     boxes = [((0, 0, r * nzl), (ncell[0] - 1, ncell[1] - 1, (r + 1) * nzl - 1)) for r in range(world)]
-    P = NodalProjector(vel, sig, geom, LPInfo(), boxes=boxes, rank=rank, nranks=world, nccl_comm=1, lib=L,
+    owner = None
+    if mbox:        # several boxes per rank: every slab is chopped like amr.max_grid_size would
+        boxes, owner, mine = [], [], []
+        for r in range(world):
+            for k0 in range(r * nzl, (r + 1) * nzl, mbox[2]):
+                for j0 in range(0, ncell[1], mbox[1]):
+                    for i0 in range(0, ncell[0], mbox[0]):
+                        boxes.append(((i0, j0, k0), (i0 + mbox[0] - 1, j0 + mbox[1] - 1, k0 + mbox[2] - 1)))
+                        owner.append(r)
+        mine = [b for b, r in zip(boxes, owner) if r == rank]
+        cut = lambda a, lo, hi: a[..., lo[2]:hi[2] + 1, lo[1]:hi[1] + 1, lo[0]:hi[0] + 1]
+        vel = [Fab.from_array(cut(prob["vel"], lo, hi), 2) for lo, hi in mine]
+        sig = [Fab.from_array(cut(prob["sigma"], lo, hi), 0) for lo, hi in mine]
+    P = NodalProjector(vel, sig, geom, LPInfo(), boxes=boxes, owner=owner, rank=rank, nranks=world, nccl_comm=1, lib=L,
                        agg_min_local_nz=agg_min, overlap_halo=overlap)
     P.setDomainBC(prob["bclo"], prob["bchi"])
     st = P.project(1e-11, 1e-14)
-    np.savez(os.path.join(outdir, f"r{rank}.npz"), u=vel.numpy_valid(), phi=P.getPhi().numpy_valid()[0],
-             gp=P.getGradPhi().numpy_valid(), vc=st.n_vcycles, nlev=st.n_levels, bot=st.bottom_iters_total,
+    if mbox:        # put the boxes back together as this rank's slab
+        u = np.zeros((3, nzl, ncell[1], ncell[0])); gp = np.zeros_like(u); phi = np.zeros((nzl + 1, ncell[1] + 1, ncell[0] + 1))
+        for (lo, hi), fv, fp, fg in zip(mine, vel, P.getPhi(), P.getGradPhi()):
+            k0, k1 = lo[2] - rank * nzl, hi[2] - rank * nzl
+            u[:, k0:k1 + 1, lo[1]:hi[1] + 1, lo[0]:hi[0] + 1] = fv.numpy_valid()
+            gp[:, k0:k1 + 1, lo[1]:hi[1] + 1, lo[0]:hi[0] + 1] = fg.numpy_valid()
+            phi[k0:k1 + 2, lo[1]:hi[1] + 2, lo[0]:hi[0] + 2] = fp.numpy_valid()[0]
+    else:
+        u, phi, gp = vel.numpy_valid(), P.getPhi().numpy_valid()[0], P.getGradPhi().numpy_valid()
+    np.savez(os.path.join(outdir, f"r{rank}.npz"), u=u, phi=phi,
+             gp=gp, vc=st.n_vcycles, nlev=st.n_levels, bot=st.bottom_iters_total,
              hist=np.array([st.res_history[i] for i in range(st.n_vcycles)]),
              levels=np.array([P.level_ncell(l) for l in range(P.num_levels)]))
     P.close()
@@ -88,18 +110,19 @@ def _worker(rank, world, port, name, ncell, kw, agg_min, overlap, outdir):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("name,ncell,kw,agg_min,agg_level,overlap", [
-    ("double_shear", (16, 16, 64), dict(zwave=True, prob_hi=(1.0, 1.0, 4.0)), 16, 2, 0),
-    ("double_shear", (16, 16, 64), dict(zwave=True, prob_hi=(1.0, 1.0, 4.0)), 16, 2, -1),   # end chunks first + exchange beside the interior
-    ("rayleigh_taylor", (16, 16, 32), {}, 4, 3, -1),
+@pytest.mark.parametrize("name,ncell,kw,agg_min,agg_level,overlap,mbox", [
+    ("double_shear", (16, 16, 64), dict(zwave=True, prob_hi=(1.0, 1.0, 4.0)), 16, 2, 0, None),
+    ("double_shear", (16, 16, 64), dict(zwave=True, prob_hi=(1.0, 1.0, 4.0)), 16, 2, -1, None),   # end chunks first + exchange beside the interior
+    ("rayleigh_taylor", (16, 16, 32), {}, 4, 3, -1, None),
+    ("rayleigh_taylor", (16, 16, 32), {}, 4, 3, 0, (8, 8, 8)),     # 8 boxes per rank, gathered into the rank's slab
 ])
-def test_two_ranks_match_oracle(tmp_path, name, ncell, kw, agg_min, agg_level, overlap):
+def test_two_ranks_match_oracle(tmp_path, name, ncell, kw, agg_min, agg_level, overlap, mbox):
     import torch.multiprocessing as mp
     from oracle.oracle import Oracle, TILED
 
     nphelp.emu_lib()           # build once, before the ranks start
     world = 2
-    mp.spawn(_worker, args=(world, _free_port(), name, ncell, kw, agg_min, overlap, str(tmp_path)), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, _free_port(), name, ncell, kw, agg_min, overlap, str(tmp_path), mbox), nprocs=world, join=True)
     r = [np.load(tmp_path / f"r{k}.npz") for k in range(world)]
     nzl = ncell[2] // world
 

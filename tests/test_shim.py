@@ -23,11 +23,11 @@ def _build(libpath, exe):
                            "-Wl,-rpath," + libdir])
 
 
-def _run_and_check(libpath, tmp_path, n):
+def _run_and_check(libpath, tmp_path, n, max_grid=None):
     exe = str(tmp_path / "shim_driver")
     out = str(tmp_path / "out.bin")
     _build(libpath, exe)
-    subprocess.check_call([exe, str(n), out])
+    subprocess.check_call([exe, str(n), out] + (["100", str(max_grid)] if max_grid else []))
     raw = np.fromfile(out, dtype=np.uint8)
     hdr = raw[:8].view(np.int32)
     body = raw[8:].view(np.float64)
@@ -50,9 +50,20 @@ def test_shim_on_emulation(tmp_path):
     _run_and_check(nphelp.EMU_LIB, tmp_path, 16)
 
 
+def test_shim_on_emulation_multibox(tmp_path):
+    """amr.max_grid_size = 8 on 16^3: eight boxes on the rank, walked with MFIter."""
+    nphelp.emu_lib()
+    _run_and_check(nphelp.EMU_LIB, tmp_path, 16, 8)
+
+
 @pytest.mark.gpu
 def test_shim_on_gpu(tmp_path):
     _run_and_check(capi.LIB_PATH, tmp_path, 32)
+
+
+@pytest.mark.gpu
+def test_shim_on_gpu_multibox(tmp_path):
+    _run_and_check(capi.LIB_PATH, tmp_path, 32, 16)
 
 
 def test_shim_abort_on_mlmg_failure(tmp_path):
