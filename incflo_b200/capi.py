@@ -52,6 +52,18 @@ class np_apply_args(C.Structure):
                 ("zero_vel_ghosts", C.c_int)]
 
 
+class mp_options(C.Structure):
+    _fields_ = [("max_coarsening_level", C.c_int), ("maxiter", C.c_int), ("bottom_maxiter", C.c_int),
+                ("num_pre_smooth", C.c_int), ("num_post_smooth", C.c_int), ("num_final_smooth", C.c_int),
+                ("bottom_solver", C.c_int), ("verbose", C.c_int), ("bottom_verbose", C.c_int), ("maxorder", C.c_int),
+                ("bottom_rtol", C.c_double), ("bottom_atol", C.c_double), ("const_beta_fastpath", C.c_int)]
+
+
+# every symbol include/macproj.h declares
+MAC_SYMBOLS = ["mp_default_options", "mp_create", "mp_set_bc", "mp_update_beta", "mp_project", "mp_get_fluxes", "mp_copy_phi",
+               "mp_destroy", "mp_num_levels", "mp_level_ncell", "mp_get_beta", "mp_apply", "mp_smooth", "mp_restrict",
+               "mp_interp_add", "mp_bottom_solve"]
+
 # every symbol include/nodalproj.h declares
 SYMBOLS = ["np_default_options", "np_create", "np_set_bc", "np_project", "np_apply_projection", "np_get_phi", "np_get_gradphi",
            "np_copy_phi", "np_copy_gradphi", "np_destroy", "np_strerror", "np_num_levels", "np_level_ncell",
@@ -108,6 +120,25 @@ def load(path=None):
     L.np_nccl_comm_create.argtypes = [C.POINTER(C.c_void_p), C.c_void_p, C.c_int, C.c_int]
     L.np_nccl_comm_destroy.argtypes = [C.c_void_p]
     L.np_is_device_pointer.argtypes = [C.c_void_p]
+    # ---- MAC projection (include/macproj.h) ----
+    L.mp_create.argtypes = [C.POINTER(C.c_void_p), C.POINTER(np_geom), C.c_int, C.POINTER(np_box), C.POINTER(C.c_int),
+                            C.c_int, C.c_int, C.c_void_p, C.POINTER(mp_options)]
+    L.mp_set_bc.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    L.mp_update_beta.argtypes = [C.c_void_p, C.POINTER(np_fab)]
+    L.mp_project.argtypes = [C.c_void_p, C.POINTER(np_fab), C.POINTER(np_fab), C.c_double, C.c_double, C.c_void_p,
+                             C.POINTER(np_stats)]
+    L.mp_get_fluxes.argtypes = [C.c_void_p, C.POINTER(np_fab), C.POINTER(np_fab)]
+    L.mp_copy_phi.argtypes = [C.c_void_p, C.POINTER(np_fab)]
+    L.mp_destroy.argtypes = [C.c_void_p]
+    L.mp_destroy.restype = None
+    L.mp_num_levels.argtypes = [C.c_void_p]
+    L.mp_level_ncell.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int)]
+    L.mp_get_beta.argtypes = [C.c_void_p, C.c_int, C.POINTER(np_fab)]
+    L.mp_apply.argtypes = [C.c_void_p, C.c_int, C.POINTER(np_fab), C.POINTER(np_fab)]
+    L.mp_smooth.argtypes = [C.c_void_p, C.c_int, C.POINTER(np_fab), C.POINTER(np_fab), C.c_int]
+    L.mp_restrict.argtypes = [C.c_void_p, C.c_int, C.POINTER(np_fab), C.POINTER(np_fab)]
+    L.mp_interp_add.argtypes = [C.c_void_p, C.c_int, C.POINTER(np_fab), C.POINTER(np_fab)]
+    L.mp_bottom_solve.argtypes = [C.c_void_p, C.POINTER(np_fab), C.POINTER(np_fab), C.POINTER(C.c_int)]
     _libs[path] = L
     return L
 
@@ -115,6 +146,16 @@ def load(path=None):
 def check(L, rc):
     if rc != 0:
         raise NodalProjError(rc, L.np_strerror(rc).decode())
+
+
+def mac_default_options(L, **kw):
+    o = mp_options()
+    L.mp_default_options(C.byref(o))
+    for k, v in kw.items():
+        if not hasattr(o, k):
+            raise KeyError(k)
+        setattr(o, k, v)
+    return o
 
 
 def default_options(L, **kw):

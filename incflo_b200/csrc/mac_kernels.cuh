@@ -1,0 +1,435 @@
+// mac_kernels.cuh — fp64 sm_100a kernels of the MAC projection: the cell-centred
+// variable-coefficient 7-point operator of amrex::MLABecLaplacian (alpha = 0, beta = 1, face-centred b = 1/rho) as
+// amrex::MacProjector drives it from /root/reference/src/convection/incflo_compute_MAC_projected_velocities.cpp:36-131.
+//
+// HBM layout: a cell array of a level has NO ghost layer: (i,j,k) -> i + sx*(j + n1*k), sx = n0 rounded up to even, so an
+// aligned pair of cells (i even) is one 16-byte access.  Boundary conditions (MLCellLinOp::applyBC) are evaluated where a
+// stencil reaches across a domain face - periodic wrap, Neumann copy, Dirichlet polynomial ghost - instead of a ghost-fill
+// launch before every colour.  Face coefficients: bx (i in 0..n0) pitch fxs = n0+1 rounded up to even, rows j, planes k;
+// by pitch sx with n1+1 rows per plane; bz pitch sx, n2+1 planes.  A uniform b (constant density) is not read at all.
+#pragma once
+#include "np_kernels.cuh"
+
+enum { MAC_PER = 0, MAC_DIR = 1, MAC_NEU = 2 };
+
+struct MacLevel {
+    int n[3];
+    long long sx, sxy, ntot;      // cell pitch, plane pitch, allocation
+    long long fxs;                // row pitch of bx
+    double dxinv[3], dh[3];       // 1/dx, 1/dx^2
+    int bclo[3], bchi[3];
+    double dc0[3], dc1[3];        // Dirichlet ghost = dc0*phi0 + dc1*phi1 (mllinop_apply_bc, maxorder 3: -2, 1/3)
+    double flo[3], fhi[3];        // coefficient of the first interior cell in its ghost (smoother's boundary factors)
+    int const_beta; double beta0;
+};
+struct MacBeta { const double *bx, *by, *bz; };
+
+__host__ __device__ __forceinline__ long long mac_c(const MacLevel& L, int i, int j, int k) { return i + L.sx * (j + (long long)L.n[1] * k); }
+__host__ __device__ __forceinline__ long long mac_fx(const MacLevel& L, int i, int j, int k) { return i + L.fxs * (j + (long long)L.n[1] * k); }
+__host__ __device__ __forceinline__ long long mac_fy(const MacLevel& L, int i, int j, int k) { return i + L.sx * (j + (long long)(L.n[1] + 1) * k); }
+__host__ __device__ __forceinline__ long long mac_fz(const MacLevel& L, int i, int j, int k) { return i + L.sx * (j + (long long)L.n[1] * k); }
+
+// value of the neighbour of cell c (value xc) across its low / high side in direction d; `st` = element stride of d,
+// `idx` = the cell's index along d.  Inside the box a plain load; on a domain face the boundary condition.
+// `xw` is the array periodic images are read from: x itself, or a snapshot taken before the launch when the level has an
+// odd number of cells in a periodic direction (then the image has the cell's own colour and is being updated).
+__device__ __forceinline__ double mac_nb_lo(const MacLevel& L, const double* __restrict__ x, long long c, double xc, int d, int idx, long long st,
+                                            const double* __restrict__ xw)
+{
+    if (idx > 0) return x[c - st];
+    if (L.bclo[d] == MAC_PER) return xw[c + st * (L.n[d] - 1)];
+    if (L.bclo[d] == MAC_NEU) return xc;
+    return L.dc0[d] * xc + L.dc1[d] * x[c + st];
+}
+__device__ __forceinline__ double mac_nb_hi(const MacLevel& L, const double* __restrict__ x, long long c, double xc, int d, int idx, long long st,
+                                            const double* __restrict__ xw)
+{
+    if (idx < L.n[d] - 1) return x[c + st];
+    if (L.bchi[d] == MAC_PER) return xw[c - st * (L.n[d] - 1)];
+    if (L.bchi[d] == MAC_NEU) return xc;
+    return L.dc0[d] * xc + L.dc1[d] * x[c - st];
+}
+struct MacB6 { double xm, xp, ym, yp, zm, zp; };
+template <bool CB> __device__ __forceinline__ MacB6 mac_load_b(const MacLevel& L, const MacBeta& B, int i, int j, int k)
+{
+    MacB6 b;
+    if (CB) { b.xm = b.xp = b.ym = b.yp = b.zm = b.zp = L.beta0; return b; }
+    const long long fx = mac_fx(L, i, j, k), fy = mac_fy(L, i, j, k), fz = mac_fz(L, i, j, k);
+    b.xm = B.bx[fx]; b.xp = B.bx[fx + 1];
+    b.ym = B.by[fy]; b.yp = B.by[fy + L.sx];
+    b.zm = B.bz[fz]; b.zp = B.bz[fz + L.sxy];
+    return b;
+}
+
+// ------------------------------------------------------------------------------------------------
+// MLABecLaplacian::Fsmooth (abec_gsrb), one colour: cells with (i+j+k+colour) even.  A thread owns an aligned pair of
+// cells; exactly one of them has the colour.  It reads the pair as one 16-byte load (centre + one x neighbour), the
+// other five neighbours as scalars, and stores the pair as a whole (no half-written sectors).
+//   zero_in : phi is taken as 0 and not read (first pre-smooth after cor = 0: no memset, no read)
+//   add_to  : sol += phi for the pair after the update (last post-smooth of level 0 on the black pass: MLMG's sol += cor)
+//   boff    : device scalar subtracted from rhs on the fly (lazy makeSolvable of the level-0 residual), or null
+// ------------------------------------------------------------------------------------------------
+template <bool CB>
+__global__ void __launch_bounds__(256) k_mac_gsrb(MacLevel L, MacBeta B, double* __restrict__ phi, const double* __restrict__ rhs, int colour,
+                                                  int zero_in, double* __restrict__ add_to, const double* __restrict__ boff,
+                                                  const double* __restrict__ xw)
+{
+    const int i0 = 2 * (int)(blockIdx.x * blockDim.x + threadIdx.x);
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    const int k = blockIdx.z;
+    if (i0 >= L.n[0] || j >= L.n[1]) return;
+    const int a = (j + k + colour) & 1;
+    const int i = i0 + a;
+    const long long c0 = mac_c(L, i0, j, k);
+    const bool pair = i0 + 1 < L.n[0];
+    double p0 = 0.0, p1 = 0.0;
+    if (!zero_in) {
+        if (pair) { const double2 v = *reinterpret_cast<const double2*>(phi + c0); p0 = v.x; p1 = v.y; }
+        else p0 = phi[c0];
+    }
+    if (i < L.n[0]) {
+        const long long c = c0 + a;
+        const double xc = a ? p1 : p0;
+        double rho = 0.0;
+        const MacB6 b = mac_load_b<CB>(L, B, i, j, k);
+        if (!zero_in) {
+            const double xm = a ? p0 : mac_nb_lo(L, phi, c, xc, 0, i, 1, xw);
+            const double xp = (!a && pair) ? p1 : mac_nb_hi(L, phi, c, xc, 0, i, 1, xw);
+            const double ym = mac_nb_lo(L, phi, c, xc, 1, j, L.sx, xw), yp = mac_nb_hi(L, phi, c, xc, 1, j, L.sx, xw);
+            const double zm = mac_nb_lo(L, phi, c, xc, 2, k, L.sxy, xw), zp = mac_nb_hi(L, phi, c, xc, 2, k, L.sxy, xw);
+            rho = L.dh[0] * (b.xm * xm + b.xp * xp) + L.dh[1] * (b.ym * ym + b.yp * yp) + L.dh[2] * (b.zm * zm + b.zp * zp);
+        }
+        const double cf0 = i == 0 ? L.flo[0] : 0.0, cf3 = i == L.n[0] - 1 ? L.fhi[0] : 0.0;
+        const double cf1 = j == 0 ? L.flo[1] : 0.0, cf4 = j == L.n[1] - 1 ? L.fhi[1] : 0.0;
+        const double cf2 = k == 0 ? L.flo[2] : 0.0, cf5 = k == L.n[2] - 1 ? L.fhi[2] : 0.0;
+        const double gamma = L.dh[0] * (b.xm + b.xp) + L.dh[1] * (b.ym + b.yp) + L.dh[2] * (b.zm + b.zp);
+        const double g_m_d = gamma - (L.dh[0] * (b.xm * cf0 + b.xp * cf3) + L.dh[1] * (b.ym * cf1 + b.yp * cf4) + L.dh[2] * (b.zm * cf2 + b.zp * cf5));
+        double r = rhs[c];
+        if (boff) r -= *boff;
+        const double res = r - (gamma * xc - rho);
+        const double xn = xc + 1.15 / g_m_d * res;
+        if (a) p1 = xn; else p0 = xn;
+    }
+    if (pair) {
+        *reinterpret_cast<double2*>(phi + c0) = make_double2(p0, p1);
+        if (add_to) { double2 s = *reinterpret_cast<double2*>(add_to + c0); s.x += p0; s.y += p1; *reinterpret_cast<double2*>(add_to + c0) = s; }
+    } else {
+        phi[c0] = p0;
+        if (add_to) add_to[c0] += p0;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// MLABecLaplacian::Fapply (mlabeclap_adotx) and the residuals built on it:
+//   MODE 0: y = A x            MODE 1: y = (b - off) - A x  (MLMG::computeResidual / computeResOfCorrection)
+// REDUCE: per-block partials of max|y| and sum(y) (inf-norm for the convergence test, mean for makeSolvable).
+// ------------------------------------------------------------------------------------------------
+template <int MODE, bool REDUCE, bool CB>
+__global__ void __launch_bounds__(256) k_mac_adotx(MacLevel L, MacBeta B, double* __restrict__ y, const double* __restrict__ x,
+                                                   const double* __restrict__ bb, const double* __restrict__ boff,
+                                                   double* __restrict__ part_max, double* __restrict__ part_sum)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    const int k = blockIdx.z;
+    double out = 0.0;
+    const bool on = i < L.n[0] && j < L.n[1];
+    if (on) {
+        const long long c = mac_c(L, i, j, k);
+        const double xc = x[c];
+        const MacB6 b = mac_load_b<CB>(L, B, i, j, k);
+        const double xm = mac_nb_lo(L, x, c, xc, 0, i, 1, x), xp = mac_nb_hi(L, x, c, xc, 0, i, 1, x);
+        const double ym = mac_nb_lo(L, x, c, xc, 1, j, L.sx, x), yp = mac_nb_hi(L, x, c, xc, 1, j, L.sx, x);
+        const double zm = mac_nb_lo(L, x, c, xc, 2, k, L.sxy, x), zp = mac_nb_hi(L, x, c, xc, 2, k, L.sxy, x);
+        const double ax = -L.dh[0] * (b.xp * (xp - xc) - b.xm * (xc - xm)) - L.dh[1] * (b.yp * (yp - xc) - b.ym * (xc - ym))
+                        - L.dh[2] * (b.zp * (zp - xc) - b.zm * (xc - zm));
+        if (MODE == 0) out = ax;
+        else { double r = bb[c]; if (boff) r -= *boff; out = r - ax; }
+        y[c] = out;
+    }
+    if (REDUCE) {
+        const double m = np_block_reduce<true>(fabs(out));
+        const double s = np_block_reduce<false>(out);
+        if (threadIdx.x == 0 && threadIdx.y == 0) {
+            const long long q = blockIdx.x + gridDim.x * (blockIdx.y + (long long)gridDim.y * blockIdx.z);
+            part_max[q] = m; part_sum[q] = s;
+        }
+    }
+}
+// one block folds the partials: scal[0] = max, scal[2] = sum, scal[6] = sum / ncells (the solvability offset)
+__global__ void __launch_bounds__(1024) k_mac_reduce(const double* __restrict__ part_max, const double* __restrict__ part_sum, long long n,
+                                                     double* scal, double ncells)
+{
+    double m = 0.0, s = 0.0;
+    for (long long t = threadIdx.x; t < n; t += blockDim.x) { if (part_max) m = fmax(m, part_max[t]); if (part_sum) s += part_sum[t]; }
+    m = np_block_reduce<true>(m);
+    s = np_block_reduce<false>(s);
+    if (threadIdx.x == 0) { if (part_max) scal[0] = m; if (part_sum) { scal[2] = s; scal[6] = s / ncells; } }
+}
+
+// x -= *off (makeSolvable of the right-hand side, once per projection) with the inf-norm partials of the result
+__global__ void __launch_bounds__(256) k_mac_sub_norm(MacLevel L, double* __restrict__ x, const double* __restrict__ off, double* __restrict__ part_max)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    const int k = blockIdx.z;
+    double v = 0.0;
+    if (i < L.n[0] && j < L.n[1]) { const long long c = mac_c(L, i, j, k); v = x[c] - *off; x[c] = v; }
+    const double m = np_block_reduce<true>(fabs(v));
+    if (threadIdx.x == 0 && threadIdx.y == 0) part_max[blockIdx.x + gridDim.x * (blockIdx.y + (long long)gridDim.y * blockIdx.z)] = m;
+}
+// y += x over the cells of a level (MLMG's sol += cor when no post-smooth can carry it)
+__global__ void __launch_bounds__(256) k_mac_axpy_cell(MacLevel L, double* __restrict__ y, const double* __restrict__ x)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    const int k = blockIdx.z;
+    if (i < L.n[0] && j < L.n[1]) { const long long c = mac_c(L, i, j, k); y[c] += x[c]; }
+}
+
+// MLCellLinOp::restriction (amrex::average_down): mean of the 8 children; the fine offset (lazy makeSolvable) is not needed
+// here because only residuals of corrections are restricted.
+__global__ void __launch_bounds__(256) k_mac_restrict(MacLevel Lc, MacLevel Lf, double* __restrict__ crse, const double* __restrict__ fine)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    const int k = blockIdx.z;
+    if (i >= Lc.n[0] || j >= Lc.n[1]) return;
+    const long long f = mac_c(Lf, 2 * i, 2 * j, 2 * k);
+    const double2 a = *reinterpret_cast<const double2*>(fine + f), b = *reinterpret_cast<const double2*>(fine + f + Lf.sx);
+    const double2 c = *reinterpret_cast<const double2*>(fine + f + Lf.sxy), d = *reinterpret_cast<const double2*>(fine + f + Lf.sxy + Lf.sx);
+    crse[mac_c(Lc, i, j, k)] = 0.125 * (a.x + a.y + b.x + b.y + c.x + c.y + d.x + d.y);
+}
+// MLCellLinOp::interpolation (mlmg_lin_cc_interp_r2): fine += crse(parent), one aligned fine pair per thread
+__global__ void __launch_bounds__(256) k_mac_interp_add(MacLevel Lf, MacLevel Lc, double* __restrict__ fine, const double* __restrict__ crse)
+{
+    const int ic = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    const int k = blockIdx.z;
+    if (ic >= Lc.n[0] || j >= Lf.n[1]) return;
+    const double v = crse[mac_c(Lc, ic, j >> 1, k >> 1)];
+    double2* p = reinterpret_cast<double2*>(fine + mac_c(Lf, 2 * ic, j, k));
+    double2 f = *p; f.x += v; f.y += v; *p = f;
+}
+// amrex::average_down_faces: mean of the 4 fine faces on a coarse face, direction d
+__global__ void __launch_bounds__(256) k_mac_avgdown_face(MacLevel Lc, MacLevel Lf, double* __restrict__ bc, const double* __restrict__ bf, int d)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    const int k = blockIdx.z;
+    const int e0 = Lc.n[0] + (d == 0), e1 = Lc.n[1] + (d == 1);
+    if (i >= e0 || j >= e1) return;
+    if (d == 0) {
+        const long long f = mac_fx(Lf, 2 * i, 2 * j, 2 * k), r = Lf.fxs, p = Lf.fxs * Lf.n[1];
+        bc[mac_fx(Lc, i, j, k)] = 0.25 * (bf[f] + bf[f + r] + bf[f + p] + bf[f + p + r]);
+    } else if (d == 1) {
+        const long long f = mac_fy(Lf, 2 * i, 2 * j, 2 * k), p = Lf.sx * (Lf.n[1] + 1);
+        bc[mac_fy(Lc, i, j, k)] = 0.25 * (bf[f] + bf[f + 1] + bf[f + p] + bf[f + p + 1]);
+    } else {
+        const long long f = mac_fz(Lf, 2 * i, 2 * j, 2 * k);
+        bc[mac_fz(Lc, i, j, k)] = 0.25 * (bf[f] + bf[f + 1] + bf[f + Lf.sx] + bf[f + Lf.sx + 1]);
+    }
+}
+// MacProjector::updateBeta: the caller's face fab of direction d -> internal layout, with min / max partials so that a
+// uniform coefficient (constant density) is detected without another pass
+__global__ void __launch_bounds__(256) k_mac_copy_beta(MacLevel L, double* __restrict__ dst, FabView src, int d, double* __restrict__ pmin, double* __restrict__ pmax)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    const int k = blockIdx.z;
+    const int e0 = L.n[0] + (d == 0), e1 = L.n[1] + (d == 1);
+    double lo = 1e300, hi = -1e300;
+    if (i < e0 && j < e1) {
+        const double v = src.p[np_foff(src, i, j, k, 0)];
+        dst[d == 0 ? mac_fx(L, i, j, k) : d == 1 ? mac_fy(L, i, j, k) : mac_fz(L, i, j, k)] = v;
+        lo = hi = v;
+    }
+    const double mx = np_block_reduce<true>(hi), mn = -np_block_reduce<true>(-lo);
+    if (threadIdx.x == 0 && threadIdx.y == 0) {
+        const long long q = blockIdx.x + gridDim.x * (blockIdx.y + (long long)gridDim.y * blockIdx.z);
+        pmin[q] = mn; pmax[q] = mx;
+    }
+}
+__global__ void __launch_bounds__(1024) k_mac_reduce_minmax(const double* __restrict__ pmin, const double* __restrict__ pmax, long long n, double* out, int first)
+{
+    double lo = 1e300, hi = -1e300;
+    for (long long t = threadIdx.x; t < n; t += blockDim.x) { lo = fmin(lo, pmin[t]); hi = fmax(hi, pmax[t]); }
+    hi = np_block_reduce<true>(hi); lo = -np_block_reduce<true>(-lo);
+    if (threadIdx.x == 0) { out[0] = first ? lo : fmin(out[0], lo); out[1] = first ? hi : fmax(out[1], hi); }
+}
+
+// MacProjector::project: rhs = -div(umac) (amrex::computeDivergence) with the partial sums of its mean
+__global__ void __launch_bounds__(256) k_mac_divu(MacLevel L, double* __restrict__ rhs, FabView ux, FabView uy, FabView uz,
+                                                  double* __restrict__ part_max, double* __restrict__ part_sum)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    const int k = blockIdx.z;
+    double out = 0.0;
+    if (i < L.n[0] && j < L.n[1]) {
+        const double d = L.dxinv[0] * (ux.p[np_foff(ux, i + 1, j, k, 0)] - ux.p[np_foff(ux, i, j, k, 0)])
+                       + L.dxinv[1] * (uy.p[np_foff(uy, i, j + 1, k, 0)] - uy.p[np_foff(uy, i, j, k, 0)])
+                       + L.dxinv[2] * (uz.p[np_foff(uz, i, j, k + 1, 0)] - uz.p[np_foff(uz, i, j, k, 0)]);
+        out = -d;
+        rhs[mac_c(L, i, j, k)] = out;
+    }
+    const double m = np_block_reduce<true>(fabs(out));
+    const double s = np_block_reduce<false>(out);
+    if (threadIdx.x == 0 && threadIdx.y == 0) {
+        const long long q = blockIdx.x + gridDim.x * (blockIdx.y + (long long)gridDim.y * blockIdx.z);
+        part_max[q] = m; part_sum[q] = s;
+    }
+}
+// MLMG::getFluxes (mlabeclap_flux_x/y/z at face centres) and MacProjector::project's umac += flux.  One thread per cell does
+// its three low faces and, on the last cell of a direction, the high boundary face.
+//   ADD = true : u_d -= b_d * dphi/dx_d           ADD = false: flux_d = -b_d * dphi/dx_d   (getLinOp().getFluxes, :63)
+template <bool ADD, bool CB>
+__global__ void __launch_bounds__(256) k_mac_fluxes(MacLevel L, MacBeta B, const double* __restrict__ phi, FabView ux, FabView uy, FabView uz)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    const int k = blockIdx.z;
+    if (i >= L.n[0] || j >= L.n[1]) return;
+    const long long c = mac_c(L, i, j, k);
+    const double xc = phi[c];
+    const MacB6 b = mac_load_b<CB>(L, B, i, j, k);
+    const double fxm = -b.xm * L.dxinv[0] * (xc - mac_nb_lo(L, phi, c, xc, 0, i, 1, phi));
+    const double fym = -b.ym * L.dxinv[1] * (xc - mac_nb_lo(L, phi, c, xc, 1, j, L.sx, phi));
+    const double fzm = -b.zm * L.dxinv[2] * (xc - mac_nb_lo(L, phi, c, xc, 2, k, L.sxy, phi));
+    double* p;
+    p = ux.p + np_foff(ux, i, j, k, 0); *p = ADD ? *p + fxm : fxm;
+    p = uy.p + np_foff(uy, i, j, k, 0); *p = ADD ? *p + fym : fym;
+    p = uz.p + np_foff(uz, i, j, k, 0); *p = ADD ? *p + fzm : fzm;
+    if (i == L.n[0] - 1) { const double f = -b.xp * L.dxinv[0] * (mac_nb_hi(L, phi, c, xc, 0, i, 1, phi) - xc); p = ux.p + np_foff(ux, i + 1, j, k, 0); *p = ADD ? *p + f : f; }
+    if (j == L.n[1] - 1) { const double f = -b.yp * L.dxinv[1] * (mac_nb_hi(L, phi, c, xc, 1, j, L.sx, phi) - xc); p = uy.p + np_foff(uy, i, j + 1, k, 0); *p = ADD ? *p + f : f; }
+    if (k == L.n[2] - 1) { const double f = -b.zp * L.dxinv[2] * (mac_nb_hi(L, phi, c, xc, 2, k, L.sxy, phi) - xc); p = uz.p + np_foff(uz, i, j, k + 1, 0); *p = ADD ? *p + f : f; }
+}
+// cell fab (any ghost count) <-> internal cell array
+template <bool TO_FAB>
+__global__ void __launch_bounds__(256) k_mac_copy_cell(MacLevel L, double* __restrict__ x, FabView f)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    const int k = blockIdx.z;
+    if (i >= L.n[0] || j >= L.n[1]) return;
+    if (TO_FAB) f.p[np_foff(f, i, j, k, 0)] = x[mac_c(L, i, j, k)];
+    else x[mac_c(L, i, j, k)] = f.p[np_foff(f, i, j, k, 0)];
+}
+// face array of direction d, internal layout -> fab (test hook mp_get_beta)
+__global__ void __launch_bounds__(256) k_mac_beta_out(MacLevel L, const double* __restrict__ src, FabView dst, int d)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    const int k = blockIdx.z;
+    if (i >= L.n[0] + (d == 0) || j >= L.n[1] + (d == 1)) return;
+    dst.p[np_foff(dst, i, j, k, 0)] = L.const_beta ? L.beta0 : src[d == 0 ? mac_fx(L, i, j, k) : d == 1 ? mac_fy(L, i, j, k) : mac_fz(L, i, j, k)];
+}
+
+// ------------------------------------------------------------------------------------------------
+// Bottom solver: the whole BiCGStab / CG iteration of amrex::MLCGSolver on the coarsest level in ONE CTA (the level has
+// 2^3 .. a few 10^4 cells): reductions are block barriers, not launches.  x = 0 on entry, so r0 = b.
+// out[0] = MLCGSolver return code (0 ok, 1-4 breakdown, 8 not converged), out[1] = iterations.
+// ------------------------------------------------------------------------------------------------
+struct MacBottomArgs {
+    MacLevel L; MacBeta B;
+    double* x; const double* b;
+    double *r, *rh, *p, *v, *s, *t;
+    int maxiter, use_cg, singular;
+    double eps_rel, eps_abs;
+    int* out;
+};
+template <bool CB> __device__ __forceinline__ double mac_diag(const MacLevel& L, const MacBeta& B, int i, int j, int k)
+{
+    const MacB6 b = mac_load_b<CB>(L, B, i, j, k);
+    return L.dh[0] * (b.xm + b.xp) + L.dh[1] * (b.ym + b.yp) + L.dh[2] * (b.zm + b.zp);
+}
+template <bool CB> __device__ __forceinline__ double mac_ax(const MacLevel& L, const MacBeta& B, const double* x, int i, int j, int k)
+{
+    const long long c = mac_c(L, i, j, k);
+    const double xc = x[c];
+    const MacB6 b = mac_load_b<CB>(L, B, i, j, k);
+    const double xm = mac_nb_lo(L, x, c, xc, 0, i, 1, x), xp = mac_nb_hi(L, x, c, xc, 0, i, 1, x);
+    const double ym = mac_nb_lo(L, x, c, xc, 1, j, L.sx, x), yp = mac_nb_hi(L, x, c, xc, 1, j, L.sx, x);
+    const double zm = mac_nb_lo(L, x, c, xc, 2, k, L.sxy, x), zp = mac_nb_hi(L, x, c, xc, 2, k, L.sxy, x);
+    return -L.dh[0] * (b.xp * (xp - xc) - b.xm * (xc - xm)) - L.dh[1] * (b.yp * (yp - xc) - b.ym * (xc - ym)) - L.dh[2] * (b.zp * (zp - xc) - b.zm * (xc - zm));
+}
+#define MAC_FOR_CELLS(q, i, j, k, c) \
+    for (long long q = threadIdx.x; q < ncell; q += blockDim.x) { \
+        const int i = (int)(q % A.L.n[0]), j = (int)((q / A.L.n[0]) % A.L.n[1]), k = (int)(q / ((long long)A.L.n[0] * A.L.n[1])); \
+        const long long c = mac_c(A.L, i, j, k);
+#define MAC_END }
+
+template <bool CB>
+__global__ void __launch_bounds__(1024) k_mac_bottom(MacBottomArgs A)
+{
+    const long long ncell = (long long)A.L.n[0] * A.L.n[1] * A.L.n[2];
+    // makeSolvable(b): subtract the mean (singular problems); r = b (x = 0), normalised for BiCGStab
+    double mean = 0.0;
+    if (A.singular) {
+        double s = 0.0;
+        MAC_FOR_CELLS(q, i, j, k, c) s += A.b[c]; MAC_END
+        mean = np_block_reduce<false>(s) / (double)ncell;
+    }
+    double m = 0.0;
+    MAC_FOR_CELLS(q, i, j, k, c)
+        double v = A.b[c] - mean;
+        if (!A.use_cg) v /= mac_diag<CB>(A.L, A.B, i, j, k);
+        A.r[c] = v; A.rh[c] = v; A.x[c] = 0.0; m = fmax(m, fabs(v));
+    MAC_END
+    double rnorm = np_block_reduce<true>(m);
+    const double rnorm0 = rnorm;
+    int ret = 0, iter = 1;
+    if (rnorm0 == 0.0 || rnorm0 < A.eps_abs) { if (threadIdx.x == 0) { A.out[0] = 0; A.out[1] = 0; } return; }
+    double rho_1 = 0.0, alpha = 0.0, omega = 0.0;
+    if (!A.use_cg) {
+        for (; iter <= A.maxiter; ++iter) {
+            double s = 0.0;
+            MAC_FOR_CELLS(q, i, j, k, c) s += A.rh[c] * A.r[c]; MAC_END
+            const double rho = np_block_reduce<false>(s);
+            if (rho == 0.0) { ret = 1; break; }
+            if (iter == 1) { MAC_FOR_CELLS(q, i, j, k, c) A.p[c] = A.r[c]; MAC_END }
+            else { const double beta = (rho / rho_1) * (alpha / omega); MAC_FOR_CELLS(q, i, j, k, c) A.p[c] = A.r[c] + beta * (A.p[c] - omega * A.v[c]); MAC_END }
+            __syncthreads();
+            s = 0.0;
+            MAC_FOR_CELLS(q, i, j, k, c) const double v = mac_ax<CB>(A.L, A.B, A.p, i, j, k) / mac_diag<CB>(A.L, A.B, i, j, k); A.v[c] = v; s += A.rh[c] * v; MAC_END
+            const double rhTv = np_block_reduce<false>(s);
+            if (rhTv != 0.0) alpha = rho / rhTv; else { ret = 2; break; }
+            m = 0.0;
+            MAC_FOR_CELLS(q, i, j, k, c) A.x[c] += alpha * A.p[c]; const double v = A.r[c] - alpha * A.v[c]; A.s[c] = v; m = fmax(m, fabs(v)); MAC_END
+            rnorm = np_block_reduce<true>(m);
+            if (rnorm < A.eps_rel * rnorm0 || rnorm < A.eps_abs) break;
+            double tt = 0.0, ts = 0.0;          // the barrier inside the reduction above made s visible
+            MAC_FOR_CELLS(q, i, j, k, c) const double v = mac_ax<CB>(A.L, A.B, A.s, i, j, k) / mac_diag<CB>(A.L, A.B, i, j, k); A.t[c] = v; tt += v * v; ts += v * A.s[c]; MAC_END
+            tt = np_block_reduce<false>(tt); ts = np_block_reduce<false>(ts);
+            if (tt != 0.0) omega = ts / tt; else { ret = 3; break; }
+            m = 0.0;
+            MAC_FOR_CELLS(q, i, j, k, c) A.x[c] += omega * A.s[c]; const double v = A.s[c] - omega * A.t[c]; A.r[c] = v; m = fmax(m, fabs(v)); MAC_END
+            rnorm = np_block_reduce<true>(m);
+            if (rnorm < A.eps_rel * rnorm0 || rnorm < A.eps_abs) break;
+            if (omega == 0.0) { ret = 4; break; }
+            rho_1 = rho;
+        }
+    } else {
+        for (; iter <= A.maxiter; ++iter) {
+            double s = 0.0;
+            MAC_FOR_CELLS(q, i, j, k, c) s += A.r[c] * A.r[c]; MAC_END
+            const double rho = np_block_reduce<false>(s);
+            if (rho == 0.0) { ret = 1; break; }
+            if (iter == 1) { MAC_FOR_CELLS(q, i, j, k, c) A.p[c] = A.r[c]; MAC_END }
+            else { const double beta = rho / rho_1; MAC_FOR_CELLS(q, i, j, k, c) A.p[c] = A.r[c] + beta * A.p[c]; MAC_END }
+            __syncthreads();
+            s = 0.0;
+            MAC_FOR_CELLS(q, i, j, k, c) const double v = mac_ax<CB>(A.L, A.B, A.p, i, j, k); A.v[c] = v; s += A.p[c] * v; MAC_END
+            const double pw = np_block_reduce<false>(s);
+            if (pw != 0.0) alpha = rho / pw; else { ret = 1; break; }
+            m = 0.0;
+            MAC_FOR_CELLS(q, i, j, k, c) A.x[c] += alpha * A.p[c]; const double v = A.r[c] - alpha * A.v[c]; A.r[c] = v; m = fmax(m, fabs(v)); MAC_END
+            rnorm = np_block_reduce<true>(m);
+            if (rnorm < A.eps_rel * rnorm0 || rnorm < A.eps_abs) break;
+            rho_1 = rho;
+        }
+    }
+    if (ret == 0 && rnorm > A.eps_rel * rnorm0 && rnorm > A.eps_abs) ret = 8;
+    if (!((ret == 0 || ret == 8) && rnorm < rnorm0)) { MAC_FOR_CELLS(q, i, j, k, c) A.x[c] = 0.0; MAC_END }
+    if (threadIdx.x == 0) { A.out[0] = ret; A.out[1] = iter < A.maxiter ? iter : A.maxiter; }
+}

@@ -1,0 +1,562 @@
+// mac_solver.cu — host side of the MAC projection (amrex::MacProjector::project -> amrex::MLMG::solve on
+// amrex::MLABecLaplacian) and its C ABI (include/macproj.h).  All arithmetic is in mac_kernels.cuh.
+#include "np_solver.h"
+#include "mac_kernels.cuh"
+#include "../../include/macproj.h"
+#include <algorithm>
+#include <cmath>
+#include <new>
+#include <vector>
+
+struct MacLev {
+    MacLevel d{};
+    double *bx = nullptr, *by = nullptr, *bz = nullptr;
+    double *res = nullptr, *cor = nullptr, *rescor = nullptr;
+    MacBeta beta() const { return MacBeta{bx, by, bz}; }
+};
+
+struct MacSolver {
+    mp_options opt{};
+    np_geom geom{};
+    int bclo[3] = {0, 0, 0}, bchi[3] = {0, 0, 0};
+    std::vector<MacLev> lev;
+    double *sol = nullptr, *rhs = nullptr;
+    double *part0 = nullptr, *part1 = nullptr; long long npart = 0;
+    double *scal = nullptr, *h_scal = nullptr;
+    int *bot_out = nullptr, *h_bot_out = nullptr;
+    double* bw[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    double* stage[4] = {nullptr, nullptr, nullptr, nullptr}; long long stage_n[4] = {0, 0, 0, 0};
+    double* wrapbuf = nullptr; long long wrapbuf_n = 0;
+    np_stream_t stream = 0;
+    np_event_t ev[4] = {0, 0, 0, 0};
+    np_stats stats{};
+    bool singular = true, have_beta = false, have_result = false, bicg_failed_switch = false;
+    long long launches = 0;
+    int bottom_iters = 0;
+    int err = 0;
+
+    static dim3 blk() { return dim3(32, 8, 1); }
+    static dim3 grid_cells(const MacLevel& L) { return dim3((L.n[0] + 31) / 32, (L.n[1] + 7) / 8, L.n[2]); }
+    static dim3 grid_pairs(const MacLevel& L) { return dim3(((L.n[0] + 1) / 2 + 31) / 32, (L.n[1] + 7) / 8, L.n[2]); }
+    static long long nblk(dim3 g) { return (long long)g.x * g.y * g.z; }
+    static int alloc_d(double** p, long long n) { void* q = nullptr; if (np_rt::dev_malloc(&q, (size_t)n * sizeof(double))) return 1; *p = (double*)q; return 0; }
+    void zero(double* p, long long n) { np_rt::memset_async(p, 0, (size_t)n * sizeof(double), stream); }
+
+    void setup_bc()
+    {
+        singular = true;
+        for (int d = 0; d < 3; ++d) if (bclo[d] == NP_BC_DIRICHLET || bchi[d] == NP_BC_DIRICHLET) singular = false;
+        for (auto& L : lev) for (int d = 0; d < 3; ++d) {
+            L.d.bclo[d] = bclo[d]; L.d.bchi[d] = bchi[d];
+            const bool hi_order = std::min(L.d.n[d] + 1, opt.maxorder) >= 3;     // mllinop_apply_bc: NX = min(blen+1, maxorder)
+            L.d.dc0[d] = hi_order ? -2.0 : -1.0; L.d.dc1[d] = hi_order ? 1.0 / 3.0 : 0.0;
+            auto fac = [&](int t) { return t == NP_BC_PERIODIC ? 0.0 : t == NP_BC_NEUMANN ? 1.0 : L.d.dc0[d]; };
+            L.d.flo[d] = fac(bclo[d]); L.d.fhi[d] = fac(bchi[d]);
+        }
+    }
+
+    int create(const np_geom* g, int nboxes, const np_box* boxes, const int* owner, int my_rank, int nranks, const mp_options* o)
+    {
+        if (np_rt::init()) return NP_ERR_NO_DEVICE;
+        geom = *g; opt = *o;
+        if (nranks != 1 || my_rank != 0 || nboxes != 1 || owner[0] != 0) return NP_ERR_INVALID;
+        for (int d = 0; d < 3; ++d) if (boxes[0].lo[d] != 0 || boxes[0].hi[d] != g->ncell[d] - 1 || g->ncell[d] < 2) return NP_ERR_INVALID;
+        for (int d = 0; d < 3; ++d) bclo[d] = bchi[d] = g->periodic[d] ? NP_BC_PERIODIC : NP_BC_NEUMANN;
+        int n[3] = {g->ncell[0], g->ncell[1], g->ncell[2]};
+        double dxinv[3];
+        for (int d = 0; d < 3; ++d) dxinv[d] = g->ncell[d] / (g->prob_hi[d] - g->prob_lo[d]);
+        for (;;) {      // MLLinOp::defineGrids: coarsen by 2 while the box stays coarsenable (min width 2)
+            MacLev L;
+            for (int d = 0; d < 3; ++d) { L.d.n[d] = n[d]; L.d.dxinv[d] = dxinv[d]; L.d.dh[d] = dxinv[d] * dxinv[d]; }
+            L.d.sx = (n[0] + 1) & ~1LL; L.d.sxy = L.d.sx * n[1]; L.d.ntot = L.d.sxy * n[2] + 2;
+            L.d.fxs = (n[0] + 2) & ~1LL;
+            L.d.const_beta = 0; L.d.beta0 = 1.0;
+            lev.push_back(L);
+            if ((int)lev.size() > opt.max_coarsening_level) break;
+            bool ok = true;
+            for (int d = 0; d < 3; ++d) if (n[d] % 2 || n[d] < 4) ok = false;
+            if (!ok) break;
+            for (int d = 0; d < 3; ++d) { n[d] /= 2; dxinv[d] *= 0.5; }
+        }
+        for (auto& L : lev) {
+            const MacLevel& d = L.d;
+            if (alloc_d(&L.res, d.ntot) || alloc_d(&L.cor, d.ntot) || alloc_d(&L.rescor, d.ntot)) return NP_ERR_CUDA;
+            if (alloc_d(&L.bx, d.fxs * d.n[1] * d.n[2] + 2) || alloc_d(&L.by, d.sx * (d.n[1] + 1) * d.n[2] + 2) || alloc_d(&L.bz, d.sxy * (d.n[2] + 1) + 2)) return NP_ERR_CUDA;
+            zero(L.res, d.ntot); zero(L.cor, d.ntot); zero(L.rescor, d.ntot);
+        }
+        const MacLevel& d0 = lev[0].d;
+        if (alloc_d(&sol, d0.ntot) || alloc_d(&rhs, d0.ntot)) return NP_ERR_CUDA;
+        zero(sol, d0.ntot); zero(rhs, d0.ntot);
+        dim3 gmax((d0.n[0] + 32) / 32, (d0.n[1] + 8) / 8, d0.n[2] + 1);
+        npart = nblk(gmax) + 16;
+        if (alloc_d(&part0, npart) || alloc_d(&part1, npart) || alloc_d(&scal, 64)) return NP_ERR_CUDA;
+        void* q = nullptr;
+        if (np_rt::host_malloc(&q, 64 * sizeof(double))) return NP_ERR_CUDA;
+        h_scal = (double*)q;
+        if (np_rt::dev_malloc(&q, 8 * sizeof(int))) return NP_ERR_CUDA;
+        bot_out = (int*)q;
+        if (np_rt::host_malloc(&q, 8 * sizeof(int))) return NP_ERR_CUDA;
+        h_bot_out = (int*)q;
+        for (int w = 0; w < 6; ++w) { if (alloc_d(&bw[w], lev.back().d.ntot)) return NP_ERR_CUDA; zero(bw[w], lev.back().d.ntot); }
+        for (int e = 0; e < 4; ++e) np_rt::event_create(&ev[e]);
+        setup_bc();
+        np_rt::stream_sync(stream);
+        return np_rt::last_error() ? NP_ERR_CUDA : NP_OK;
+    }
+    void destroy()
+    {
+        np_rt::stream_sync(stream);
+        for (auto& L : lev) { double* a[] = {L.bx, L.by, L.bz, L.res, L.cor, L.rescor}; for (double* p : a) if (p) np_rt::dev_free(p); }
+        lev.clear();
+        double* a[] = {wrapbuf, sol, rhs, part0, part1, scal, stage[0], stage[1], stage[2], stage[3], bw[0], bw[1], bw[2], bw[3], bw[4], bw[5]};
+        for (double* p : a) if (p) np_rt::dev_free(p);
+        if (h_scal) np_rt::host_free(h_scal);
+        if (bot_out) np_rt::dev_free(bot_out);
+        if (h_bot_out) np_rt::host_free(h_bot_out);
+        for (int e = 0; e < 4; ++e) if (ev[e]) np_rt::event_destroy(ev[e]);
+    }
+
+    // ---- caller fabs ----
+    // view of a fab whose valid range starts at local index 0; nodal_dir = -1 (cell) or the direction a face fab is nodal in
+    FabView view(const np_fab& f, int l, int nodal_dir) const
+    {
+        const MacLevel& d = lev[l].d;
+        FabView v; v.p = f.p; v.ng = f.ngrow;
+        v.sy = d.n[0] + (nodal_dir == 0) + 2 * f.ngrow;
+        v.sz = v.sy * (d.n[1] + (nodal_dir == 1) + 2 * f.ngrow);
+        v.sn = v.sz * (d.n[2] + (nodal_dir == 2) + 2 * f.ngrow);
+        return v;
+    }
+    double* stage_get(int slot, long long n)
+    {
+        if (stage_n[slot] < n) {
+            if (stage[slot]) { np_rt::stream_sync(stream); np_rt::dev_free(stage[slot]); stage[slot] = nullptr; stage_n[slot] = 0; }
+            if (alloc_d(&stage[slot], n)) return nullptr;
+            stage_n[slot] = n;
+        }
+        return stage[slot];
+    }
+    // device-side view of a caller fab: device pointers are used in place, host fabs are staged (copied in when `in`)
+    bool import(const np_fab& f, int l, int nodal_dir, int slot, bool in, FabView* v, bool* staged)
+    {
+        *v = view(f, l, nodal_dir); *staged = false;
+#ifndef NP_EMU
+        if (!np_rt::is_device_ptr(f.p)) {
+            double* dev = stage_get(slot, v->sn);
+            if (!dev) return false;
+            if (in) np_rt::copy_async(dev, f.p, (size_t)v->sn * sizeof(double), stream);
+            v->p = dev; *staged = true;
+        }
+#endif
+        return true;
+    }
+    void export_back(const np_fab& f, const FabView& v, bool staged)
+    {
+        if (staged) np_rt::copy_async(f.p, v.p, (size_t)v.sn * sizeof(double), stream);
+    }
+
+    // ---- building blocks ----
+    void gsrb(int l, double* phi, const double* b, int colour, bool zero_in, double* add_to, const double* boff)
+    {
+        const MacLev& L = lev[l];
+        // a level with an odd number of cells in a periodic direction (only the coarsest can be): the periodic image of a cell
+        // has the cell's own colour, so images are read from a snapshot - the ghost cells applyBC filled before the sweep
+        const double* xw = phi;
+        bool odd_per = false;
+        for (int d = 0; d < 3; ++d) if (bclo[d] == NP_BC_PERIODIC && (L.d.n[d] & 1)) odd_per = true;
+        if (odd_per && !zero_in) {
+            if (!wrapbuf || wrapbuf_n < L.d.ntot) { if (wrapbuf) { np_rt::stream_sync(stream); np_rt::dev_free(wrapbuf); } wrapbuf = nullptr; wrapbuf_n = 0; if (alloc_d(&wrapbuf, L.d.ntot)) { err = NP_ERR_CUDA; return; } wrapbuf_n = L.d.ntot; }
+            np_rt::copy_async(wrapbuf, phi, (size_t)L.d.ntot * sizeof(double), stream);
+            xw = wrapbuf;
+        }
+        if (L.d.const_beta) NP_LAUNCH(false, (k_mac_gsrb<true>), grid_pairs(L.d), blk(), 0, stream, L.d, L.beta(), phi, b, colour, zero_in ? 1 : 0, add_to, boff, xw);
+        else NP_LAUNCH(false, (k_mac_gsrb<false>), grid_pairs(L.d), blk(), 0, stream, L.d, L.beta(), phi, b, colour, zero_in ? 1 : 0, add_to, boff, xw);
+        ++launches;
+    }
+    // MLCellLinOp::smooth: red then black (the boundary conditions are evaluated inside the kernels)
+    void smooth(int l, double* phi, const double* b, bool zero_in, double* add_to, const double* boff)
+    {
+        gsrb(l, phi, b, 0, zero_in, nullptr, boff);
+        gsrb(l, phi, b, 1, false, add_to, boff);
+    }
+    template <int MODE, bool REDUCE> void adotx(int l, double* y, const double* x, const double* b, const double* boff)
+    {
+        const MacLev& L = lev[l];
+        if (L.d.const_beta) NP_LAUNCH(REDUCE, (k_mac_adotx<MODE, REDUCE, true>), grid_cells(L.d), blk(), 0, stream, L.d, L.beta(), y, x, b, boff, part0, part1);
+        else NP_LAUNCH(REDUCE, (k_mac_adotx<MODE, REDUCE, false>), grid_cells(L.d), blk(), 0, stream, L.d, L.beta(), y, x, b, boff, part0, part1);
+        ++launches;
+    }
+    // fold the partials of the last reducing kernel over level-0 cells: scal[base] = max, scal[base+2] = sum, scal[base+6] = mean
+    void reduce(long long n, bool want_max, bool want_sum, int base)
+    {
+        const MacLevel& d0 = lev[0].d;
+        NP_LAUNCH(true, k_mac_reduce, dim3(1), dim3(1024), 0, stream, want_max ? (const double*)part0 : (const double*)nullptr,
+                  want_sum ? (const double*)part1 : (const double*)nullptr, n, scal + base, (double)d0.n[0] * d0.n[1] * d0.n[2]);
+        ++launches;
+    }
+    double fetch(int slot)
+    {
+        np_rt::copy_async(h_scal, scal, 16 * sizeof(double), stream);
+        np_rt::stream_sync(stream);
+        return h_scal[slot];
+    }
+    void restrict_to(int lc, double* crse, const double* fine)
+    {
+        NP_LAUNCH(false, k_mac_restrict, grid_cells(lev[lc].d), blk(), 0, stream, lev[lc].d, lev[lc - 1].d, crse, fine); ++launches;
+    }
+    void interp_add(int lf, double* fine, const double* crse)
+    {
+        const MacLevel& F = lev[lf].d;
+        NP_LAUNCH(false, k_mac_interp_add, dim3((lev[lf + 1].d.n[0] + 31) / 32, (F.n[1] + 7) / 8, F.n[2]), blk(), 0, stream, F, lev[lf + 1].d, fine, crse); ++launches;
+    }
+    int run_bottom(bool use_cg, int* iters)
+    {
+        MacLev& L = lev.back();
+        MacBottomArgs A;
+        A.L = L.d; A.B = L.beta(); A.x = L.cor; A.b = L.res;
+        A.r = bw[0]; A.rh = bw[1]; A.p = bw[2]; A.v = bw[3]; A.s = bw[4]; A.t = bw[5];
+        A.maxiter = opt.bottom_maxiter; A.use_cg = use_cg ? 1 : 0; A.singular = singular ? 1 : 0;
+        A.eps_rel = opt.bottom_rtol; A.eps_abs = opt.bottom_atol; A.out = bot_out;
+        const long long nc = (long long)L.d.n[0] * L.d.n[1] * L.d.n[2];
+        const int nth = nc <= 32 ? 32 : nc <= 256 ? 256 : 1024;
+        if (L.d.const_beta) NP_LAUNCH(true, (k_mac_bottom<true>), dim3(1), dim3(nth), 0, stream, A);
+        else NP_LAUNCH(true, (k_mac_bottom<false>), dim3(1), dim3(nth), 0, stream, A);
+        ++launches;
+        np_rt::copy_async(h_bot_out, bot_out, 2 * sizeof(int), stream);
+        np_rt::stream_sync(stream);
+        *iters = h_bot_out[1];
+        return h_bot_out[0];
+    }
+    // MLMG::bottomSolve
+    void bottom_solve()
+    {
+        const int l = (int)lev.size() - 1;
+        MacLev& L = lev[l];
+        if (opt.bottom_solver == NP_BOTTOM_SMOOTHER) {
+            if (opt.num_final_smooth <= 0) zero(L.cor, L.d.ntot);
+            for (int i = 0; i < opt.num_final_smooth; ++i) smooth(l, L.cor, L.res, i == 0, nullptr, nullptr);
+            return;
+        }
+        const bool cg_first = opt.bottom_solver == NP_BOTTOM_CG || (opt.bottom_solver == NP_BOTTOM_BICGCG && bicg_failed_switch);
+        int nit = 0;
+        int ret = run_bottom(cg_first, &nit);
+        bottom_iters += nit;
+        if (opt.bottom_verbose) fprintf(stderr, "[macproj] bottom %s: ret %d, %d iterations\n", cg_first ? "cg" : "bicgstab", ret, nit);
+        if (ret != 0 && ret != 9) {
+            if (opt.bottom_solver == NP_BOTTOM_BICGCG) {
+                ret = run_bottom(!cg_first, &nit); bottom_iters += nit;
+                if (ret == 0) bicg_failed_switch = cg_first ? false : true;
+            }
+            if (ret != 0) {
+                if (opt.num_final_smooth <= 0) zero(L.cor, L.d.ntot);
+                for (int i = 0; i < opt.num_final_smooth; ++i) smooth(l, L.cor, L.res, i == 0, nullptr, nullptr);
+            }
+        }
+    }
+    // MLMG::mgVcycle on lev[*].res -> lev[*].cor; the last post-smooth of level 0 also does MLMG's sol += cor
+    void vcycle(const double* off0)
+    {
+        const int nl = (int)lev.size();
+        for (int l = 0; l < nl - 1; ++l) {
+            MacLev& L = lev[l];
+            const double* off = l == 0 ? off0 : nullptr;
+            if (opt.num_pre_smooth <= 0) zero(L.cor, L.d.ntot);
+            for (int i = 0; i < opt.num_pre_smooth; ++i) smooth(l, L.cor, L.res, i == 0, nullptr, off);
+            adotx<1, false>(l, L.rescor, L.cor, L.res, off);              // computeResOfCorrection
+            restrict_to(l + 1, lev[l + 1].res, L.rescor);
+        }
+        bottom_solve();
+        for (int l = nl - 2; l >= 0; --l) {
+            MacLev& L = lev[l];
+            const double* off = l == 0 ? off0 : nullptr;
+            interp_add(l, L.cor, lev[l + 1].cor);                         // addInterpCorrection
+            for (int i = 0; i < opt.num_post_smooth; ++i)
+                smooth(l, L.cor, L.res, false, (l == 0 && i == opt.num_post_smooth - 1) ? sol : nullptr, off);
+            if (l == 0 && opt.num_post_smooth <= 0) add_cor_to_sol();
+        }
+        if (nl == 1) add_cor_to_sol();
+    }
+    void add_cor_to_sol()
+    {
+        // sol += cor as a pass of its own (only when no post-smooth can carry it)
+        const MacLevel& d = lev[0].d;
+        NP_LAUNCH(false, k_mac_axpy_cell, grid_cells(d), blk(), 0, stream, d, sol, (const double*)lev[0].cor); ++launches;
+    }
+    // MLMG::solve; `sol` holds the initial guess
+    int solve(double rtol, double atol, double rhsnorm0)
+    {
+        const MacLevel& d0 = lev[0].d;
+        const long long nb = nblk(grid_cells(d0));
+        bottom_iters = 0; bicg_failed_switch = false;
+        adotx<1, true>(0, lev[0].res, sol, rhs, nullptr);
+        reduce(nb, true, singular, 0);
+        const double resnorm0 = fetch(0);
+        const double max_norm = rhsnorm0 >= resnorm0 ? rhsnorm0 : resnorm0;
+        const double res_target = std::max(atol, std::max(rtol, 1e-16) * max_norm);
+        stats.rhs_norm0 = rhsnorm0; stats.res_norm0 = resnorm0; stats.n_vcycles = 0; stats.status = 0; stats.res_norm_final = resnorm0;
+        stats.n_levels = (int)lev.size(); stats.bottom_iters_total = 0;
+        if (!(resnorm0 > res_target)) return NP_OK;
+        bool converged = false;
+        int rc = NP_OK;
+        for (int iter = 0; iter < opt.maxiter; ++iter) {
+            vcycle(singular ? scal + 6 : nullptr);       // makeSolvable(res) is applied by the consumers of res (lazy offset)
+            adotx<1, true>(0, lev[0].res, sol, rhs, nullptr);
+            reduce(nb, true, singular, 0);
+            const double rn = fetch(0);
+            if (iter < 128) stats.res_history[iter] = rn;
+            stats.n_vcycles = iter + 1; stats.res_norm_final = rn;
+            if (opt.verbose >= 2) fprintf(stderr, "MLMG: Iteration %3d Fine resid/bnorm = %.6e\n", iter + 1, rn / max_norm);
+            if (rn <= res_target) { converged = true; break; }
+            if (!(rn <= 1e20 * max_norm)) { rc = NP_ERR_DIVERGED; break; }
+        }
+        if (!converged && rc == NP_OK) rc = NP_ERR_NOT_CONVERGED;
+        stats.bottom_iters_total = bottom_iters;
+        return rc;
+    }
+
+    int set_bc(const int lo[3], const int hi[3])
+    {
+        for (int d = 0; d < 3; ++d) {
+            if (lo[d] < 0 || lo[d] > 2 || hi[d] < 0 || hi[d] > 2) return NP_ERR_INVALID;
+            if ((lo[d] == NP_BC_PERIODIC) != (hi[d] == NP_BC_PERIODIC)) return NP_ERR_INVALID;
+            if ((lo[d] == NP_BC_PERIODIC) != (geom.periodic[d] != 0)) return NP_ERR_INVALID;
+            bclo[d] = lo[d]; bchi[d] = hi[d];
+        }
+        setup_bc();
+        return NP_OK;
+    }
+    // MacProjector::updateBeta + MLABecLaplacian::averageDownCoeffs
+    int update_beta(const np_fab beta[3])
+    {
+        MacLev& L0 = lev[0];
+        double* dst[3] = {L0.bx, L0.by, L0.bz};
+        for (int d = 0; d < 3; ++d) {
+            if (!beta[d].p || beta[d].ncomp < 1) return NP_ERR_INVALID;
+            FabView v; bool st;
+            if (!import(beta[d], 0, d, d, true, &v, &st)) return NP_ERR_CUDA;
+            dim3 g((L0.d.n[0] + (d == 0) + 31) / 32, (L0.d.n[1] + (d == 1) + 7) / 8, L0.d.n[2] + (d == 2));
+            NP_LAUNCH(true, k_mac_copy_beta, g, blk(), 0, stream, L0.d, dst[d], v, d, part0, part1); ++launches;
+            NP_LAUNCH(true, k_mac_reduce_minmax, dim3(1), dim3(1024), 0, stream, (const double*)part0, (const double*)part1, nblk(g), scal + 8, d == 0 ? 1 : 0); ++launches;
+        }
+        fetch(0);
+        const double bmin = h_scal[8], bmax = h_scal[9];
+        const bool is_const = opt.const_beta_fastpath && bmin == bmax;
+        for (auto& L : lev) { L.d.const_beta = is_const ? 1 : 0; L.d.beta0 = is_const ? bmin : 1.0; }
+        if (!is_const) {
+            for (size_t l = 1; l < lev.size(); ++l) {
+                const MacLevel &C = lev[l].d, &F = lev[l - 1].d;
+                const double* src[3] = {lev[l - 1].bx, lev[l - 1].by, lev[l - 1].bz};
+                double* dd[3] = {lev[l].bx, lev[l].by, lev[l].bz};
+                for (int d = 0; d < 3; ++d) {
+                    dim3 g((C.n[0] + (d == 0) + 31) / 32, (C.n[1] + (d == 1) + 7) / 8, C.n[2] + (d == 2));
+                    NP_LAUNCH(false, k_mac_avgdown_face, g, blk(), 0, stream, C, F, dd[d], src[d], d); ++launches;
+                }
+            }
+        }
+        stats.sigma_is_const = is_const ? 1 : 0;
+        have_beta = true;
+        return np_rt::last_error() ? NP_ERR_CUDA : NP_OK;
+    }
+    void finish_stats()
+    {
+        np_rt::event_record(ev[3], stream);
+        np_rt::stream_sync(stream);
+        stats.ms_setup = np_rt::event_ms(ev[0], ev[1]);
+        stats.ms_solve = np_rt::event_ms(ev[1], ev[2]);
+        stats.ms_finish = np_rt::event_ms(ev[2], ev[3]);
+        stats.ms_total = np_rt::event_ms(ev[0], ev[3]);
+        stats.kernel_launches = launches;
+    }
+    // MacProjector::setUMAC + project
+    int project(np_fab umac[3], np_fab* mac_phi, double rtol, double atol)
+    {
+        if (!have_beta) return NP_ERR_STATE;
+        for (int d = 0; d < 3; ++d) if (!umac[d].p || umac[d].ncomp < 1) return NP_ERR_INVALID;
+        if (mac_phi && (!mac_phi->p || mac_phi->ncomp < 1)) return NP_ERR_INVALID;
+        launches = 0; have_result = false;
+        const int is_const = stats.sigma_is_const;
+        stats = np_stats{}; stats.sigma_is_const = is_const;
+        const MacLevel& d0 = lev[0].d;
+        np_rt::event_record(ev[0], stream);
+        FabView uv[3]; bool st[3];
+        for (int d = 0; d < 3; ++d) if (!import(umac[d], 0, d, d, true, &uv[d], &st[d])) return NP_ERR_CUDA;
+        // rhs = -div(umac), its mean (solvability) and, after the mean is taken out, its inf-norm
+        const long long nb = nblk(grid_cells(d0));
+        NP_LAUNCH(true, k_mac_divu, grid_cells(d0), blk(), 0, stream, d0, rhs, uv[0], uv[1], uv[2], part0, part1); ++launches;
+        reduce(nb, true, singular, 16);
+        if (singular) {
+            NP_LAUNCH(true, k_mac_sub_norm, grid_cells(d0), blk(), 0, stream, d0, rhs, (const double*)(scal + 16 + 6), part0); ++launches;
+            reduce(nb, true, false, 16);
+        }
+        np_rt::copy_async(h_scal + 16, scal + 16, 8 * sizeof(double), stream);
+        // phi: 0, or the caller's mac_phi as the initial guess
+        FabView pv; bool pst = false;
+        if (mac_phi) {
+            if (!import(*mac_phi, 0, -1, 3, true, &pv, &pst)) return NP_ERR_CUDA;
+            NP_LAUNCH(false, (k_mac_copy_cell<false>), grid_cells(d0), blk(), 0, stream, d0, sol, pv); ++launches;
+        } else zero(sol, d0.ntot);
+        np_rt::stream_sync(stream);
+        const double rhsnorm0 = h_scal[16];
+        np_rt::event_record(ev[1], stream);
+        const int rc = solve(rtol, atol, rhsnorm0);
+        np_rt::event_record(ev[2], stream);
+        // umac += flux = -b grad(phi)
+        if (d0.const_beta) NP_LAUNCH(false, (k_mac_fluxes<true, true>), grid_cells(d0), blk(), 0, stream, d0, lev[0].beta(), (const double*)sol, uv[0], uv[1], uv[2]);
+        else NP_LAUNCH(false, (k_mac_fluxes<true, false>), grid_cells(d0), blk(), 0, stream, d0, lev[0].beta(), (const double*)sol, uv[0], uv[1], uv[2]);
+        ++launches;
+        for (int d = 0; d < 3; ++d) export_back(umac[d], uv[d], st[d]);
+        if (mac_phi) {
+            NP_LAUNCH(false, (k_mac_copy_cell<true>), grid_cells(d0), blk(), 0, stream, d0, sol, pv); ++launches;
+            export_back(*mac_phi, pv, pst);
+        }
+        finish_stats();
+        stats.status = rc;
+        if (np_rt::last_error()) { stats.status = NP_ERR_CUDA; return NP_ERR_CUDA; }
+        have_result = true;
+        return rc;
+    }
+    int get_fluxes(np_fab flux[3], const np_fab* phi)
+    {
+        if (!have_beta || !phi || !phi->p) return NP_ERR_STATE;
+        const MacLevel& d0 = lev[0].d;
+        FabView fv[3], pv; bool st[3], pst;
+        for (int d = 0; d < 3; ++d) { if (!flux[d].p) return NP_ERR_INVALID; if (!import(flux[d], 0, d, d, false, &fv[d], &st[d])) return NP_ERR_CUDA; }
+        if (!import(*phi, 0, -1, 3, true, &pv, &pst)) return NP_ERR_CUDA;
+        double* tmp = lev[0].rescor;                     // free outside a V-cycle
+        NP_LAUNCH(false, (k_mac_copy_cell<false>), grid_cells(d0), blk(), 0, stream, d0, tmp, pv);
+        if (d0.const_beta) NP_LAUNCH(false, (k_mac_fluxes<false, true>), grid_cells(d0), blk(), 0, stream, d0, lev[0].beta(), (const double*)tmp, fv[0], fv[1], fv[2]);
+        else NP_LAUNCH(false, (k_mac_fluxes<false, false>), grid_cells(d0), blk(), 0, stream, d0, lev[0].beta(), (const double*)tmp, fv[0], fv[1], fv[2]);
+        for (int d = 0; d < 3; ++d) export_back(flux[d], fv[d], st[d]);
+        np_rt::stream_sync(stream);
+        return np_rt::last_error() ? NP_ERR_CUDA : NP_OK;
+    }
+    // cell fab of level l (host or device, any ghosts) <-> internal array
+    int cell_in(int l, const np_fab& f, double* dst, int slot)
+    {
+        FabView v; bool st;
+        if (!f.p || !import(f, l, -1, slot, true, &v, &st)) return NP_ERR_INVALID;
+        NP_LAUNCH(false, (k_mac_copy_cell<false>), grid_cells(lev[l].d), blk(), 0, stream, lev[l].d, dst, v);
+        return NP_OK;
+    }
+    int cell_out(int l, np_fab& f, double* src, int slot)
+    {
+        FabView v; bool st;
+        if (!f.p || !import(f, l, -1, slot, false, &v, &st)) return NP_ERR_INVALID;
+        if (st) np_rt::memset_async(v.p, 0, (size_t)v.sn * sizeof(double), stream);
+        NP_LAUNCH(false, (k_mac_copy_cell<true>), grid_cells(lev[l].d), blk(), 0, stream, lev[l].d, src, v);
+        export_back(f, v, st);
+        np_rt::stream_sync(stream);
+        return np_rt::last_error() ? NP_ERR_CUDA : NP_OK;
+    }
+};
+
+struct mp_handle { MacSolver S; };
+
+extern "C" {
+
+void mp_default_options(mp_options* o)
+{
+    o->max_coarsening_level = 100; o->maxiter = 200; o->bottom_maxiter = 200; o->num_pre_smooth = 2; o->num_post_smooth = 2;
+    o->num_final_smooth = 8; o->bottom_solver = NP_BOTTOM_BICGCG; o->verbose = 0; o->bottom_verbose = 0; o->maxorder = 3;
+    o->bottom_rtol = 1e-4; o->bottom_atol = -1.0; o->const_beta_fastpath = 1;
+}
+int mp_create(mp_handle** h, const np_geom* geom, int nboxes_global, const np_box* all_boxes, const int* owner_rank,
+              int my_rank, int nranks, void* nccl_comm_or_null, const mp_options* opt)
+{
+    (void)nccl_comm_or_null;
+    if (!h || !geom || !all_boxes || !owner_rank) return NP_ERR_INVALID;
+    mp_options o; if (opt) o = *opt; else mp_default_options(&o);
+    mp_handle* p = new (std::nothrow) mp_handle();
+    if (!p) return NP_ERR_INVALID;
+    const int rc = p->S.create(geom, nboxes_global, all_boxes, owner_rank, my_rank, nranks, &o);
+    if (rc) { p->S.destroy(); delete p; return rc; }
+    *h = p;
+    return NP_OK;
+}
+int mp_set_bc(mp_handle* h, const int lo[3], const int hi[3]) { return h ? h->S.set_bc(lo, hi) : NP_ERR_INVALID; }
+int mp_update_beta(mp_handle* h, const np_fab beta[3]) { return h && beta ? h->S.update_beta(beta) : NP_ERR_INVALID; }
+int mp_project(mp_handle* h, np_fab umac[3], np_fab* mac_phi, double rtol, double atol, void* cuda_stream, np_stats* out)
+{
+    if (!h || !umac) return NP_ERR_INVALID;
+    h->S.stream = (np_stream_t)cuda_stream;
+    const int rc = h->S.project(umac, mac_phi, rtol, atol);
+    if (out) *out = h->S.stats;
+    return rc;
+}
+int mp_get_fluxes(mp_handle* h, np_fab flux[3], const np_fab* phi) { return h && flux ? h->S.get_fluxes(flux, phi) : NP_ERR_INVALID; }
+int mp_copy_phi(mp_handle* h, np_fab* dst)
+{
+    if (!h || !dst) return NP_ERR_INVALID;
+    if (!h->S.have_result) return NP_ERR_STATE;
+    return h->S.cell_out(0, *dst, h->S.sol, 3);
+}
+void mp_destroy(mp_handle* h) { if (h) { h->S.destroy(); delete h; } }
+int mp_num_levels(mp_handle* h) { return h ? (int)h->S.lev.size() : 0; }
+int mp_level_ncell(mp_handle* h, int l, int n[3])
+{
+    if (!h || l < 0 || l >= (int)h->S.lev.size()) return NP_ERR_INVALID;
+    for (int d = 0; d < 3; ++d) n[d] = h->S.lev[l].d.n[d];
+    return NP_OK;
+}
+
+// ---- kernel-level hooks ----
+#define MP_LEVEL_OK(h, l) ((h) && (l) >= 0 && (l) < (int)(h)->S.lev.size() && (h)->S.have_beta)
+int mp_get_beta(mp_handle* h, int l, np_fab beta[3])
+{
+    if (!MP_LEVEL_OK(h, l)) return NP_ERR_INVALID;
+    MacSolver& S = h->S; MacLev& L = S.lev[l];
+    const double* src[3] = {L.bx, L.by, L.bz};
+    for (int d = 0; d < 3; ++d) {
+        FabView v; bool st;
+        if (!S.import(beta[d], l, d, d, false, &v, &st)) return NP_ERR_CUDA;
+        dim3 g((L.d.n[0] + (d == 0) + 31) / 32, (L.d.n[1] + (d == 1) + 7) / 8, L.d.n[2] + (d == 2));
+        NP_LAUNCH(false, k_mac_beta_out, g, MacSolver::blk(), 0, S.stream, L.d, src[d], v, d);
+        S.export_back(beta[d], v, st);
+    }
+    np_rt::stream_sync(S.stream);
+    return np_rt::last_error() ? NP_ERR_CUDA : NP_OK;
+}
+int mp_apply(mp_handle* h, int l, const np_fab* x, np_fab* y)
+{
+    if (!MP_LEVEL_OK(h, l) || !x || !y) return NP_ERR_INVALID;
+    MacSolver& S = h->S; MacLev& L = S.lev[l];
+    if (S.cell_in(l, *x, L.cor, 0)) return NP_ERR_INVALID;
+    S.adotx<0, false>(l, L.rescor, L.cor, nullptr, nullptr);
+    return S.cell_out(l, *y, L.rescor, 1);
+}
+int mp_smooth(mp_handle* h, int l, np_fab* x, const np_fab* rhs, int ncalls)
+{
+    if (!MP_LEVEL_OK(h, l) || !x || !rhs) return NP_ERR_INVALID;
+    MacSolver& S = h->S; MacLev& L = S.lev[l];
+    if (S.cell_in(l, *x, L.cor, 0) || S.cell_in(l, *rhs, L.res, 1)) return NP_ERR_INVALID;
+    for (int i = 0; i < ncalls; ++i) S.smooth(l, L.cor, L.res, false, nullptr, nullptr);
+    return S.cell_out(l, *x, L.cor, 0);
+}
+int mp_restrict(mp_handle* h, int lc, const np_fab* fine, np_fab* crse)
+{
+    if (!MP_LEVEL_OK(h, lc) || lc < 1 || !fine || !crse) return NP_ERR_INVALID;
+    MacSolver& S = h->S;
+    if (S.cell_in(lc - 1, *fine, S.lev[lc - 1].rescor, 0)) return NP_ERR_INVALID;
+    S.restrict_to(lc, S.lev[lc].res, S.lev[lc - 1].rescor);
+    return S.cell_out(lc, *crse, S.lev[lc].res, 1);
+}
+int mp_interp_add(mp_handle* h, int lf, np_fab* fine, const np_fab* crse)
+{
+    if (!MP_LEVEL_OK(h, lf) || lf + 1 >= (int)h->S.lev.size() || !fine || !crse) return NP_ERR_INVALID;
+    MacSolver& S = h->S;
+    if (S.cell_in(lf, *fine, S.lev[lf].cor, 0) || S.cell_in(lf + 1, *crse, S.lev[lf + 1].cor, 1)) return NP_ERR_INVALID;
+    S.interp_add(lf, S.lev[lf].cor, S.lev[lf + 1].cor);
+    return S.cell_out(lf, *fine, S.lev[lf].cor, 0);
+}
+int mp_bottom_solve(mp_handle* h, const np_fab* b, np_fab* x, int* iters)
+{
+    if (!h || !h->S.have_beta || !b || !x) return NP_ERR_INVALID;
+    MacSolver& S = h->S; const int l = (int)S.lev.size() - 1;
+    if (S.cell_in(l, *b, S.lev[l].res, 0)) return NP_ERR_INVALID;
+    S.bottom_iters = 0; S.bicg_failed_switch = false;
+    S.bottom_solve();
+    if (iters) *iters = S.bottom_iters;
+    return S.cell_out(l, *x, S.lev[l].cor, 1);
+}
+
+} // extern "C"

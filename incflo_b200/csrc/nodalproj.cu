@@ -3,3 +3,4 @@
 #include "np_capi.cu"
 #include "np_capi_hooks.cu"
 #include "np_comm.cu"
+#include "mac_solver.cu"

@@ -1,0 +1,127 @@
+"""Host-side mirror of amrex::MacProjector as incflo drives it, over the C ABI of include/macproj.h.
+
+Call order of the reference (/root/reference/src/convection/incflo_compute_MAC_projected_velocities.cpp):
+
+    macproj = MacProjector(geom)                                  # incflo.cpp: macproj.reset(new MacProjector(Geom(0,finest_level)))
+    macproj.initProjector(lp_info, inv_rho)   or   macproj.updateBeta(inv_rho)           # :39-46
+    macproj.setDomainBC(bclo, bchi)                                                       # :44
+    macproj.setUMAC(mac_vec)                                                              # :115
+    macproj.project(rtol, atol)   or   macproj.project(mac_phi, rtol, atol)               # :127-131
+    macproj.getFluxes(fluxes, mac_phi)        # macproj->getLinOp().getFluxes(...)          :63
+
+Face Fabs (one box, FArrayBox layout): direction d has shape (1, nz+[d==2]+2g, ny+[d==1]+2g, nx+[d==0]+2g).
+"""
+import ctypes as C
+
+from . import capi
+from .projector import Fab, LPInfo
+
+
+def face_fab_zeros(ncell, d, ngrow=0, like="numpy", device="cuda"):
+    n = [int(x) + 2 * ngrow for x in ncell]
+    n[d] += 1
+    return Fab(Fab._alloc((1, n[2], n[1], n[0]), like, device), ngrow, nodal=False)
+
+
+def face_fab_from_array(arr, ngrow=0, like="numpy", device="cuda"):
+    """arr: [k, j, i] face values of one direction (no ghosts)."""
+    import numpy as np
+    a = np.asarray(arr, dtype=np.float64)
+    nz, ny, nx = a.shape
+    f = Fab(Fab._alloc((1, nz + 2 * ngrow, ny + 2 * ngrow, nx + 2 * ngrow), like, device), ngrow, nodal=False)
+    v = f.valid()
+    if like == "numpy":
+        v[...] = a[None]
+    else:
+        import torch
+        v.copy_(torch.from_numpy(np.ascontiguousarray(a[None])))
+    return f
+
+
+class MacProjector:
+    """Drop-in for amrex::MacProjector on one AMR level, one box."""
+
+    def __init__(self, geom, lib=None):
+        self.L = lib or capi.load()
+        self.geom = geom
+        self.h = None
+        self.umac = None
+        self.stats = None
+        self._bc = None
+
+    def needInitialization(self):
+        return self.h is None
+
+    def initProjector(self, lp_info, beta, **options):
+        info = lp_info or LPInfo()
+        options.setdefault("max_coarsening_level", min(info.max_coarsening_level, 100))
+        self.opt = capi.mac_default_options(self.L, **options)
+        bx = (capi.np_box * 1)()
+        for d in range(3):
+            bx[0].lo[d], bx[0].hi[d] = 0, self.geom.ncell[d] - 1
+        owner = (C.c_int * 1)(0)
+        h = C.c_void_p()
+        g = self.geom.c()
+        capi.check(self.L, self.L.mp_create(C.byref(h), C.byref(g), 1, bx, owner, 0, 1, None, C.byref(self.opt)))
+        self.h = h
+        if self._bc:
+            self.setDomainBC(*self._bc)
+        self.updateBeta(beta)
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.mp_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def setDomainBC(self, lo, hi):
+        self._bc = (tuple(lo), tuple(hi))
+        if self.h is not None:
+            capi.check(self.L, self.L.mp_set_bc(self.h, (C.c_int * 3)(*[int(x) for x in lo]), (C.c_int * 3)(*[int(x) for x in hi])))
+
+    def updateBeta(self, beta):
+        b = (capi.np_fab * 3)(*[f.c() for f in beta])
+        capi.check(self.L, self.L.mp_update_beta(self.h, b))
+
+    def setUMAC(self, umac):
+        self.umac = list(umac)
+
+    def project(self, *args, stream=None, raise_on_fail=True):
+        """project(rtol, atol) or project(mac_phi, rtol, atol) - the two overloads the reference uses."""
+        mac_phi = None
+        if len(args) == 3:
+            mac_phi, rtol, atol = args
+        else:
+            rtol, atol = args
+        u = (capi.np_fab * 3)(*[f.c() for f in self.umac])
+        st = capi.np_stats()
+        phi = mac_phi.c() if mac_phi is not None else None
+        rc = self.L.mp_project(self.h, u, C.byref(phi) if phi is not None else None, rtol, atol,
+                               C.c_void_p(stream) if stream else None, C.byref(st))
+        self.stats = st
+        if rc and raise_on_fail:
+            capi.check(self.L, rc)
+        return st
+
+    def getFluxes(self, fluxes, mac_phi):
+        f = (capi.np_fab * 3)(*[x.c() for x in fluxes])
+        p = mac_phi.c()
+        capi.check(self.L, self.L.mp_get_fluxes(self.h, f, C.byref(p)))
+
+    def copyPhi(self, dst):
+        d = dst.c()
+        capi.check(self.L, self.L.mp_copy_phi(self.h, C.byref(d)))
+
+    @property
+    def num_levels(self):
+        return self.L.mp_num_levels(self.h)
+
+    def level_ncell(self, l):
+        n = (C.c_int * 3)()
+        capi.check(self.L, self.L.mp_level_ncell(self.h, l, n))
+        return tuple(n)

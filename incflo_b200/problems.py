@@ -106,3 +106,102 @@ def double_shear_torch(ncell, prob_hi, koff, nz_local, device, ngrow=1, zwave=Tr
     if zwave:
         vel[2][inner] = 0.05 * torch.sin(TWOPI * x) * torch.sin(TWOPI * z / prob_hi[2])
     return vel
+
+
+# ---- MAC projection inputs: the same flows sampled at face centres, beta = 1/rho on faces ----
+def _face_coords(ncell, prob_lo, prob_hi, d):
+    """(z, y, x) coordinate arrays of the faces of direction d, broadcastable to the face array [k, j, i]."""
+    n = list(ncell)
+    dx = [(prob_hi[q] - prob_lo[q]) / ncell[q] for q in range(3)]
+    c = []
+    for q in range(3):
+        if q == d:
+            c.append(prob_lo[q] + np.arange(n[q] + 1) * dx[q])
+        else:
+            c.append(prob_lo[q] + (np.arange(n[q]) + 0.5) * dx[q])
+    return c[2][:, None, None], c[1][None, :, None], c[0][None, None, :]
+
+
+def mac_double_shear(ncell, prob_lo=(0, 0, 0), prob_hi=(1, 1, 1)):
+    """Double shear layer (/root/reference/src/prob/prob_init_fluid.cpp:470-475) + the z wave and perturbation of the
+    nodal configs at face centres; constant density (beta = 1), periodic."""
+    L = [prob_hi[d] - prob_lo[d] for d in range(3)]
+    umac, beta = [], []
+    for d in range(3):
+        z, y, x = _face_coords(ncell, prob_lo, prob_hi, d)
+        shape = np.broadcast_shapes(z.shape, y.shape, x.shape)
+        p = 0.1 * np.sin(TWOPI * x / L[0]) * np.sin(TWOPI * y / L[1]) * np.sin(TWOPI * z / L[2])
+        f = (np.tanh(30.0 * (0.25 - np.abs(y / L[1] - 0.5))), 0.05 * np.sin(TWOPI * x / L[0]),
+             0.05 * np.sin(TWOPI * x / L[0]) * np.sin(TWOPI * z / L[2]))[d]
+        umac.append(np.ascontiguousarray(np.broadcast_to(f + p, shape), dtype=np.float64))
+        beta.append(np.ones(shape))
+    return dict(umac=umac, beta=beta, bclo=(0, 0, 0), bchi=(0, 0, 0), prob_lo=tuple(prob_lo), prob_hi=tuple(prob_hi))
+
+
+def mac_rayleigh_taylor(ncell, prob_lo=(0, 0, 0), prob_hi=(0.5, 0.5, 1.0)):
+    """Rayleigh-Taylor density (/root/reference/src/prob/prob_init_fluid.cpp:295-321) on faces: beta = 1/rho, ratio 4;
+    periodic x/y, walls in z (Neumann, no flow through the wall faces); gravity kick + perturbation."""
+    L = [prob_hi[d] - prob_lo[d] for d in range(3)]
+    rho_1, rho_2, width = 0.5, 2.0, 0.005
+    sx, sy = 0.5 * (prob_lo[0] + prob_hi[0]), 0.5 * (prob_lo[1] + prob_hi[1])
+    umac, beta = [], []
+    for d in range(3):
+        z, y, x = _face_coords(ncell, prob_lo, prob_hi, d)
+        shape = np.broadcast_shapes(z.shape, y.shape, x.shape)
+        xw = prob_lo[0] + np.mod(x - prob_lo[0], L[0])       # the periodic image face carries the same density
+        yw = prob_lo[1] + np.mod(y - prob_lo[1], L[1])
+        r2d = np.minimum(np.hypot(xw - sx, yw - sy), 0.5 * L[0])
+        h = 0.5 - 0.01 * np.cos(2.0 * np.pi * r2d / L[0])
+        rho = rho_1 + ((rho_2 - rho_1) / 2.0) * (1.0 + np.tanh((z - h) / width))
+        p = 0.1 * np.sin(TWOPI * x / L[0]) * np.sin(TWOPI * y / L[1]) * np.sin(TWOPI * z / L[2])
+        f = np.broadcast_to((p, p, -0.1 + p)[d], shape).astype(np.float64).copy()
+        if d == 2:
+            f[0] = 0.0
+            f[-1] = 0.0
+        umac.append(np.ascontiguousarray(f))
+        beta.append(np.ascontiguousarray(np.broadcast_to(1.0 / rho, shape), dtype=np.float64))
+    return dict(umac=umac, beta=beta, bclo=(0, 0, NEUMANN), bchi=(0, 0, NEUMANN), prob_lo=tuple(prob_lo),
+                prob_hi=tuple(prob_hi))
+
+
+MAC_PROBLEMS = {"double_shear": mac_double_shear, "rayleigh_taylor": mac_rayleigh_taylor}
+
+
+def mac_problem_torch(name, ncell, prob_hi, device, ngrow=0):
+    """The MAC_PROBLEMS fields built directly on `device` as face-fab storage [1, nz(+1)+2g, ny(+1)+2g, nx(+1)+2g]
+    (zero ghosts): (umac[3], beta[3], bclo, bchi).  Same formulas as mac_double_shear / mac_rayleigh_taylor."""
+    import torch
+    f64 = dict(dtype=torch.float64, device=device)
+    g = ngrow
+    L = [float(prob_hi[d]) for d in range(3)]
+    dx = [L[d] / ncell[d] for d in range(3)]
+    umac, beta = [], []
+    for d in range(3):
+        n = [ncell[q] + (1 if q == d else 0) for q in range(3)]
+        c = [(torch.arange(n[q], **f64) + (0.0 if q == d else 0.5)) * dx[q] for q in range(3)]
+        x, y, z = c[0][None, None, :], c[1][None, :, None], c[2][:, None, None]
+        p = 0.1 * torch.sin(TWOPI * x / L[0]) * torch.sin(TWOPI * y / L[1]) * torch.sin(TWOPI * z / L[2])
+        if name == "double_shear":
+            f = (torch.tanh(30.0 * (0.25 - torch.abs(y / L[1] - 0.5))), 0.05 * torch.sin(TWOPI * x / L[0]),
+                 0.05 * torch.sin(TWOPI * x / L[0]) * torch.sin(TWOPI * z / L[2]))[d] + p
+            b = torch.ones((n[2], n[1], n[0]), **f64)
+        else:
+            xw, yw = torch.remainder(x, L[0]), torch.remainder(y, L[1])
+            r2d = torch.clamp(torch.hypot(xw - 0.5 * L[0], yw - 0.5 * L[1]).expand(1, n[1], n[0]), max=0.5 * L[0])
+            h = 0.5 - 0.01 * torch.cos(2.0 * np.pi * r2d / L[0])
+            rho = 0.5 + 0.75 * (1.0 + torch.tanh((z - h) / 0.005))
+            b = 1.0 / rho
+            f = ((p, p, -0.1 + p)[d]).expand(n[2], n[1], n[0]).clone()
+            if d == 2:
+                f[0] = 0.0
+                f[-1] = 0.0
+        uf = torch.zeros((1, n[2] + 2 * g, n[1] + 2 * g, n[0] + 2 * g), **f64)
+        bf = torch.zeros_like(uf)
+        inner = (0, slice(g, g + n[2]), slice(g, g + n[1]), slice(g, g + n[0]))
+        uf[inner] = f.expand(n[2], n[1], n[0])
+        bf[inner] = b.expand(n[2], n[1], n[0])
+        umac.append(uf)
+        beta.append(bf)
+        del f, b, p
+    bc = ((0, 0, 0), (0, 0, 0)) if name == "double_shear" else ((0, 0, NEUMANN), (0, 0, NEUMANN))
+    return umac, beta, bc[0], bc[1]

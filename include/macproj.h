@@ -1,0 +1,80 @@
+/* macproj.h — C ABI of the B200-native MAC projection (part of libnodalproj.so).  SURVEY.md 8(f) row 1.
+ *
+ * The second Poisson solve of every incflo time step: amrex::MacProjector on the cell-centred operator
+ * -div(b grad phi) with face-centred b = 1/rho (amrex::MLABecLaplacian, alpha = 0, beta = 1), which makes the
+ * face (MAC) velocities discretely divergence-free.  Entry points and the reference interface each one replaces
+ * (paths relative to the reference tree; the arithmetic lives in AMReX >= 20.11, which the reference does not vendor):
+ *
+ *   mp_create       <- MacProjector ctor + initProjector(lp_info, inv_rho)
+ *                      src/convection/incflo_compute_MAC_projected_velocities.cpp:39-43, "mac_proj.*" options
+ *                      src/incflo.H:316-344 (maxiter 200, bottom_maxiter 200, max_coarsening_level 100, rtol 1e-11, atol 1e-14)
+ *   mp_set_bc       <- MacProjector::setDomainBC                  ...MAC_projected_velocities.cpp:44
+ *                      (BC mapping: incflo::get_projection_bc, src/projection/incflo_apply_nodal_projection.cpp:6-36)
+ *   mp_update_beta  <- initProjector's beta / MacProjector::updateBeta(inv_rho)         ...:43, :46
+ *   mp_project      <- MacProjector::setUMAC(mac_vec) + project(rtol, atol)             ...:115, :131
+ *                      or project(mac_phi, rtol, atol) (initial guess in, solution out)  ...:127
+ *   mp_get_fluxes   <- macproj->getLinOp().getFluxes(m_fluxes, mac_phi, FaceCenter)     ...:63
+ *   mp_destroy      <- ~MacProjector
+ *
+ * Fabs use AMReX's FArrayBox layout (include/nodalproj.h).  A face fab of direction d is nodal in d: valid index range
+ * [lo, hi+1] in d, [lo, hi] in the other two.  Device or host pointers (host fabs are staged).  This round: one AMR level,
+ * ONE box covering the domain on one rank (nranks == 1); the z-slab multi-GPU layer of the nodal solver is not wired in yet.
+ * There is no CPU compute path: without a CUDA device mp_create fails with NP_ERR_NO_DEVICE.
+ */
+#ifndef MACPROJ_H
+#define MACPROJ_H
+#include "nodalproj.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct mp_handle mp_handle;
+
+typedef struct {
+    int max_coarsening_level;   /* mac_proj.mg_max_coarsening_level        default 100 */
+    int maxiter;                /* mac_proj.maxiter                        default 200 */
+    int bottom_maxiter;         /* mac_proj.bottom_maxiter                 default 200 */
+    int num_pre_smooth;         /* nu1                                     default 2 */
+    int num_post_smooth;        /* nu2                                     default 2 */
+    int num_final_smooth;       /* nuf (bottom fallback)                   default 8 */
+    int bottom_solver;          /* np_bottom, mac_proj.bottom_solver       default bicgcg */
+    int verbose;                /* mac_proj.verbose                        default 0 */
+    int bottom_verbose;         /* mac_proj.bottom_verbose                 default 0 */
+    int maxorder;               /* MLLinOp::setMaxOrder: Dirichlet ghost polynomial order, default 3 */
+    double bottom_rtol;         /* mac_proj.bottom_rtol                    default 1e-4 */
+    double bottom_atol;         /* mac_proj.bottom_atol                    default -1 */
+    int const_beta_fastpath;    /* skip every coefficient read when b is uniform (constant density); default 1 */
+} mp_options;
+
+void mp_default_options(mp_options* o);
+
+int mp_create(mp_handle** h, const np_geom* geom, int nboxes_global, const np_box* all_boxes, const int* owner_rank,
+              int my_rank, int nranks, void* nccl_comm_or_null, const mp_options* opt);
+int mp_set_bc(mp_handle* h, const int lo[3], const int hi[3]);
+/* beta[d]: face fab of direction d, 1 comp (inv_rho_x/y/z).  Copied into the solver's hierarchy (coarse levels =
+ * amrex::average_down_faces). */
+int mp_update_beta(mp_handle* h, const np_fab beta[3]);
+/* umac[d]: face fab of direction d, 1 comp, modified in place: umac -= b grad(phi) with div(b grad phi) = div(umac).
+ * mac_phi: NULL (phi starts from 0 and stays inside the handle) or a cell fab, 1 comp, any ghost count: initial guess
+ * in, solution out (valid cells). */
+int mp_project(mp_handle* h, np_fab umac[3], np_fab* mac_phi_or_null, double rtol, double atol, void* cuda_stream, np_stats* out);
+/* flux[d] = -b_d dphi/dx_d at face centres from a cell fab phi (homogeneous domain BCs as in the solve). */
+int mp_get_fluxes(mp_handle* h, np_fab flux[3], const np_fab* phi);
+int mp_copy_phi(mp_handle* h, np_fab* dst);          /* the last solution -> cell fab (valid cells) */
+void mp_destroy(mp_handle* h);
+int mp_num_levels(mp_handle* h);
+int mp_level_ncell(mp_handle* h, int mglev, int ncell[3]);
+
+/* ---- kernel-level test hooks: cell fabs are 1 comp, 0 ghosts, at MG level mglev; need mp_update_beta first ---- */
+int mp_get_beta(mp_handle* h, int mglev, np_fab beta[3]);                               /* averageDownCoeffs */
+int mp_apply(mp_handle* h, int mglev, const np_fab* x, np_fab* y);                      /* Fapply */
+int mp_smooth(mp_handle* h, int mglev, np_fab* x, const np_fab* rhs, int ncalls);       /* ncalls x (red, black) */
+int mp_restrict(mp_handle* h, int cmglev, const np_fab* fine, np_fab* crse);
+int mp_interp_add(mp_handle* h, int fmglev, np_fab* fine, const np_fab* crse);
+int mp_bottom_solve(mp_handle* h, const np_fab* b, np_fab* x, int* iters);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MACPROJ_H */

@@ -12,10 +12,10 @@ from incflo_b200 import capi
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def declared_functions():
-    src = open(os.path.join(ROOT, "include", "nodalproj.h")).read()
+def declared_functions(header="nodalproj.h", prefix="np_"):
+    src = open(os.path.join(ROOT, "include", header)).read()
     src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
-    return sorted(set(re.findall(r"\b(np_[a-z_0-9]+)\s*\(", src)))
+    return sorted(set(re.findall(r"\b(" + prefix + r"[a-z_0-9]+)\s*\(", src)))
 
 
 def product_lib():
@@ -26,11 +26,12 @@ def product_lib():
 
 def test_header_and_binding_agree():
     assert declared_functions() == sorted(capi.SYMBOLS)
+    assert declared_functions("macproj.h", "mp_") == sorted(capi.MAC_SYMBOLS)
 
 
 def test_library_exports_every_declared_symbol():
     L = product_lib()
-    missing = [s for s in declared_functions() if not hasattr(L, s)]
+    missing = [s for s in declared_functions() + declared_functions("macproj.h", "mp_") if not hasattr(L, s)]
     assert not missing, missing
 
 
