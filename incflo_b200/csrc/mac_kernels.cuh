@@ -120,41 +120,218 @@ __global__ void __launch_bounds__(256) k_mac_gsrb(MacLevel L, MacBeta B, double*
 }
 
 // ------------------------------------------------------------------------------------------------
+// One whole MLCellLinOp::smooth (red sweep, then black sweep) in ONE pass over the level.  Out of place: reads `in`,
+// writes `out`.  A block owns a tile of RB_TX x RB_TY cells and a chunk of zc planes and marches through the chunk with a
+// ring of four planes in shared memory, each holding the tile plus a halo of 2:
+//     step p:  load plane p (old values)  |  red cells of plane p-1 (tile + 1) updated in the ring  |  black cells of
+//              plane p-2 (tile) computed from the new reds around them and stored, with their red partners, as 16-byte pairs
+// Red cells one cell outside the tile / chunk are recomputed by the neighbouring blocks as well (that is what makes the
+// blocks independent); a red-black sweep does not depend on the order inside a colour, so the result is the reference's.
+// Periodic images are loaded through wrapped indices and treated like any halo cell; Neumann / Dirichlet ghosts are
+// evaluated from the ring where a stencil reaches across the face.  Needs an even number of cells in periodic directions.
+//   zero_in : `in` is taken as 0 (first pre-smooth)          crse : in += crse(parent) on load (addInterpCorrection fused)
+//   add_to  : add_to += out on store (MLMG's sol += cor)     boff : scalar subtracted from rhs (lazy makeSolvable)
+// ------------------------------------------------------------------------------------------------
+#define RB_TX 64
+#define RB_TY 16
+#define RB_PX (RB_TX + 4)
+#define RB_PY (RB_TY + 4)
+#define RB_PS (RB_PX * RB_PY)
+struct RbArgs {
+    double* out; const double* in; const double* rhs; const double* boff; double* add_to; const double* crse;
+    int zero_in, zc;
+};
+__device__ __forceinline__ int rb_wrap(int g, int n, int periodic) { return (g >= 0 && g < n) ? g : (periodic ? (g % n + n) % n : -1); }
+
+template <bool CB>
+__device__ __forceinline__ double rb_update(const MacLevel& L, const MacBeta& B, const double* ring, int q, int lx, int ly,
+                                            int gx, int gy, int gz, const double* __restrict__ rhs, double off)
+{
+    const double* P = ring + (q & 3) * RB_PS;
+    const int o = lx + RB_PX * ly;
+    const double xc = P[o];
+    const bool px = L.bclo[0] == MAC_PER, py = L.bclo[1] == MAC_PER, pz = L.bclo[2] == MAC_PER;
+    const double xm = (gx > 0 || px) ? P[o - 1] : (L.bclo[0] == MAC_NEU ? xc : L.dc0[0] * xc + L.dc1[0] * P[o + 1]);
+    const double xp = (gx < L.n[0] - 1 || px) ? P[o + 1] : (L.bchi[0] == MAC_NEU ? xc : L.dc0[0] * xc + L.dc1[0] * P[o - 1]);
+    const double ym = (gy > 0 || py) ? P[o - RB_PX] : (L.bclo[1] == MAC_NEU ? xc : L.dc0[1] * xc + L.dc1[1] * P[o + RB_PX]);
+    const double yp = (gy < L.n[1] - 1 || py) ? P[o + RB_PX] : (L.bchi[1] == MAC_NEU ? xc : L.dc0[1] * xc + L.dc1[1] * P[o - RB_PX]);
+    const double* Pm = ring + ((q - 1) & 3) * RB_PS; const double* Pp = ring + ((q + 1) & 3) * RB_PS;
+    const double zm = (gz > 0 || pz) ? Pm[o] : (L.bclo[2] == MAC_NEU ? xc : L.dc0[2] * xc + L.dc1[2] * Pp[o]);
+    const double zp = (gz < L.n[2] - 1 || pz) ? Pp[o] : (L.bchi[2] == MAC_NEU ? xc : L.dc0[2] * xc + L.dc1[2] * Pm[o]);
+    const MacB6 b = mac_load_b<CB>(L, B, gx, gy, gz);
+    const double rho = L.dh[0] * (b.xm * xm + b.xp * xp) + L.dh[1] * (b.ym * ym + b.yp * yp) + L.dh[2] * (b.zm * zm + b.zp * zp);
+    const double cf0 = gx == 0 ? L.flo[0] : 0.0, cf3 = gx == L.n[0] - 1 ? L.fhi[0] : 0.0;
+    const double cf1 = gy == 0 ? L.flo[1] : 0.0, cf4 = gy == L.n[1] - 1 ? L.fhi[1] : 0.0;
+    const double cf2 = gz == 0 ? L.flo[2] : 0.0, cf5 = gz == L.n[2] - 1 ? L.fhi[2] : 0.0;
+    const double gamma = L.dh[0] * (b.xm + b.xp) + L.dh[1] * (b.ym + b.yp) + L.dh[2] * (b.zm + b.zp);
+    const double g_m_d = gamma - (L.dh[0] * (b.xm * cf0 + b.xp * cf3) + L.dh[1] * (b.ym * cf1 + b.yp * cf4) + L.dh[2] * (b.zm * cf2 + b.zp * cf5));
+    const double r = rhs[mac_c(L, gx, gy, gz)] - off;
+    const double res = r - (gamma * xc - rho);
+    return xc + 1.15 / g_m_d * res;
+}
+
+template <bool CB>
+__global__ void __launch_bounds__(256) k_mac_rb2(MacLevel L, MacLevel Lc, MacBeta B, RbArgs A)
+{
+    __shared__ double ring[4 * RB_PS];
+    const int tid = threadIdx.x;
+    const int x0 = blockIdx.x * RB_TX, y0 = blockIdx.y * RB_TY, z0 = blockIdx.z * A.zc, z1 = min(z0 + A.zc, L.n[2]);
+    const int px = L.bclo[0] == MAC_PER, py = L.bclo[1] == MAC_PER, pz = L.bclo[2] == MAC_PER;
+    const double off = A.boff ? *A.boff : 0.0;
+    for (int p = z0 - 2; p <= z1 + 1; ++p) {
+        // ---- load plane p (old values; periodic images through wrapped indices; cells outside the domain are never read) ----
+        {
+            const int gz = rb_wrap(p, L.n[2], pz);
+            double* P = ring + (p & 3) * RB_PS;
+            if (gz >= 0) {
+                for (int q = tid; q < RB_PS; q += 256) {
+                    const int lx = q % RB_PX, ly = q / RB_PX;
+                    const int gx = rb_wrap(x0 - 2 + lx, L.n[0], px), gy = rb_wrap(y0 - 2 + ly, L.n[1], py);
+                    double v = 0.0;
+                    if (gx >= 0 && gy >= 0) {
+                        if (!A.zero_in) v = A.in[mac_c(L, gx, gy, gz)];
+                        if (A.crse) v += A.crse[mac_c(Lc, gx >> 1, gy >> 1, gz >> 1)];
+                    }
+                    P[q] = v;
+                }
+            }
+        }
+        __syncthreads();
+        // ---- red cells of plane p-1 over tile + 1 ----
+        {
+            const int qz = p - 1;
+            const int gz = rb_wrap(qz, L.n[2], pz);
+            if (gz >= 0 && qz >= z0 - 1 && qz <= z1) {
+                double* P = ring + (qz & 3) * RB_PS;
+                const int npair = (RB_TX + 2) / 2;                      // 33 pair slots per row, rows 1 .. RB_TY+2
+                for (int q = tid; q < npair * (RB_TY + 2); q += 256) {
+                    const int ly = 1 + q / npair, pr = q % npair;
+                    const int gy = rb_wrap(y0 - 2 + ly, L.n[1], py);
+                    if (gy < 0) continue;
+                    int lx = 1 + 2 * pr;
+                    int gx = rb_wrap(x0 - 2 + lx, L.n[0], px);
+                    // the red cell of the pair (lx, lx+1): parity of the wrapped global index (n is even in periodic directions)
+                    const int gxa = x0 - 2 + lx;                         // unwrapped parity is the same
+                    if ((gxa + (y0 - 2 + ly) + qz) & 1) { ++lx; gx = rb_wrap(x0 - 2 + lx, L.n[0], px); }
+                    if (lx > RB_TX + 2 || gx < 0) continue;
+                    P[lx + RB_PX * ly] = rb_update<CB>(L, B, ring, qz, lx, ly, gx, gy, gz, A.rhs, off);
+                }
+            }
+        }
+        __syncthreads();
+        // ---- black cells of plane p-2 over the tile, stored with their red partners ----
+        {
+            const int r = p - 2;
+            if (r >= z0 && r < z1) {
+                const double* P = ring + (r & 3) * RB_PS;
+                for (int q = tid; q < (RB_TX / 2) * RB_TY; q += 256) {
+                    const int ly = 2 + q / (RB_TX / 2), lx0 = 2 + 2 * (q % (RB_TX / 2));
+                    const int gx0 = x0 - 2 + lx0, gy = y0 - 2 + ly;
+                    if (gx0 >= L.n[0] || gy >= L.n[1]) continue;
+                    const int a = ((gx0 + gy + r) & 1) ? 0 : 1;          // which cell of the pair is black (odd parity)
+                    double v0 = P[lx0 + RB_PX * ly], v1 = P[lx0 + 1 + RB_PX * ly];
+                    if (gx0 + a < L.n[0]) {
+                        const double nb = rb_update<CB>(L, B, ring, r, lx0 + a, ly, gx0 + a, gy, r, A.rhs, off);
+                        if (a) v1 = nb; else v0 = nb;
+                    }
+                    const long long c = mac_c(L, gx0, gy, r);
+                    if (gx0 + 1 < L.n[0]) {
+                        *reinterpret_cast<double2*>(A.out + c) = make_double2(v0, v1);
+                        if (A.add_to) { double2 t = *reinterpret_cast<double2*>(A.add_to + c); t.x += v0; t.y += v1; *reinterpret_cast<double2*>(A.add_to + c) = t; }
+                    } else {
+                        A.out[c] = v0;
+                        if (A.add_to) A.add_to[c] += v0;
+                    }
+                }
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // MLABecLaplacian::Fapply (mlabeclap_adotx) and the residuals built on it:
 //   MODE 0: y = A x            MODE 1: y = (b - off) - A x  (MLMG::computeResidual / computeResOfCorrection)
 // REDUCE: per-block partials of max|y| and sum(y) (inf-norm for the convergence test, mean for makeSolvable).
 // ------------------------------------------------------------------------------------------------
+#define MAC_KZ 8     // planes one block of k_mac_adotx marches through
 template <int MODE, bool REDUCE, bool CB>
 __global__ void __launch_bounds__(256) k_mac_adotx(MacLevel L, MacBeta B, double* __restrict__ y, const double* __restrict__ x,
                                                    const double* __restrict__ bb, const double* __restrict__ boff,
                                                    double* __restrict__ part_max, double* __restrict__ part_sum)
 {
+    // a block marches through MAC_KZ planes: x(k-1), x(k), x(k+1) of a column roll through registers, so every plane is
+    // loaded once per block (not three times), and the block-wide reduction is paid once per MAC_KZ cells of a thread
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int j = blockIdx.y * blockDim.y + threadIdx.y;
-    const int k = blockIdx.z;
-    double out = 0.0;
+    const int k0 = blockIdx.z * MAC_KZ, k1 = min(k0 + MAC_KZ, L.n[2]);
+    double vmax = 0.0, vsum = 0.0;
     const bool on = i < L.n[0] && j < L.n[1];
     if (on) {
-        const long long c = mac_c(L, i, j, k);
-        const double xc = x[c];
-        const MacB6 b = mac_load_b<CB>(L, B, i, j, k);
-        const double xm = mac_nb_lo(L, x, c, xc, 0, i, 1, x), xp = mac_nb_hi(L, x, c, xc, 0, i, 1, x);
-        const double ym = mac_nb_lo(L, x, c, xc, 1, j, L.sx, x), yp = mac_nb_hi(L, x, c, xc, 1, j, L.sx, x);
-        const double zm = mac_nb_lo(L, x, c, xc, 2, k, L.sxy, x), zp = mac_nb_hi(L, x, c, xc, 2, k, L.sxy, x);
-        const double ax = -L.dh[0] * (b.xp * (xp - xc) - b.xm * (xc - xm)) - L.dh[1] * (b.yp * (yp - xc) - b.ym * (xc - ym))
-                        - L.dh[2] * (b.zp * (zp - xc) - b.zm * (xc - zm));
-        if (MODE == 0) out = ax;
-        else { double r = bb[c]; if (boff) r -= *boff; out = r - ax; }
-        y[c] = out;
-    }
-    if (REDUCE) {
-        const double m = np_block_reduce<true>(fabs(out));
-        const double s = np_block_reduce<false>(out);
-        if (threadIdx.x == 0 && threadIdx.y == 0) {
-            const long long q = blockIdx.x + gridDim.x * (blockIdx.y + (long long)gridDim.y * blockIdx.z);
-            part_max[q] = m; part_sum[q] = s;
+        const double off = (MODE == 1 && boff) ? *boff : 0.0;
+        long long c = mac_c(L, i, j, k0);
+        double xc = x[c];
+        double zm = mac_nb_lo(L, x, c, xc, 2, k0, L.sxy, x);
+        for (int k = k0; k < k1; ++k, c += L.sxy) {
+            const double zp = mac_nb_hi(L, x, c, xc, 2, k, L.sxy, x);
+            const MacB6 b = mac_load_b<CB>(L, B, i, j, k);
+            const double xm = mac_nb_lo(L, x, c, xc, 0, i, 1, x), xp = mac_nb_hi(L, x, c, xc, 0, i, 1, x);
+            const double ym = mac_nb_lo(L, x, c, xc, 1, j, L.sx, x), yp = mac_nb_hi(L, x, c, xc, 1, j, L.sx, x);
+            const double ax = -L.dh[0] * (b.xp * (xp - xc) - b.xm * (xc - xm)) - L.dh[1] * (b.yp * (yp - xc) - b.ym * (xc - ym))
+                            - L.dh[2] * (b.zp * (zp - xc) - b.zm * (xc - zm));
+            double out;
+            if (MODE == 0) out = ax;
+            else out = (bb[c] - off) - ax;
+            y[c] = out;
+            if (REDUCE) { vmax = fmax(vmax, fabs(out)); vsum += out; }
+            // roll (inside the chunk zp is a plain interior value; the boundary expression only occurs on the last plane)
+            zm = xc; xc = zp;
         }
     }
+    if (REDUCE) {
+        const double m = np_block_reduce<true>(vmax);
+        const double sm = np_block_reduce<false>(vsum);
+        if (threadIdx.x == 0 && threadIdx.y == 0) {
+            const long long q = blockIdx.x + gridDim.x * (blockIdx.y + (long long)gridDim.y * blockIdx.z);
+            part_max[q] = m; part_sum[q] = sm;
+        }
+    }
+}
+// MLMG::computeResOfCorrection + MLCellLinOp::restriction in one pass: crse = average_down(b - off - A x).  The residual of
+// the correction is only ever restricted, so it is never stored: a thread owns one coarse cell = 2x2x2 fine cells.
+template <bool CB>
+__global__ void __launch_bounds__(256) k_mac_resid_restrict(MacLevel Lc, MacLevel L, MacBeta B, double* __restrict__ crse, const double* __restrict__ x,
+                                                            const double* __restrict__ bb, const double* __restrict__ boff)
+{
+    const int ic = blockIdx.x * blockDim.x + threadIdx.x;
+    const int jc = blockIdx.y * blockDim.y + threadIdx.y;
+    const int kc = blockIdx.z;
+    if (ic >= Lc.n[0] || jc >= Lc.n[1]) return;
+    const double off = boff ? *boff : 0.0;
+    double acc = 0.0;
+#pragma unroll
+    for (int dk = 0; dk < 2; ++dk)
+#pragma unroll
+        for (int dj = 0; dj < 2; ++dj) {
+            const int i = 2 * ic, j = 2 * jc + dj, k = 2 * kc + dk;
+            const long long c = mac_c(L, i, j, k);
+            const double2 xv = *reinterpret_cast<const double2*>(x + c);
+            const double2 bv = *reinterpret_cast<const double2*>(bb + c);
+#pragma unroll
+            for (int di = 0; di < 2; ++di) {
+                const double xc = di ? xv.y : xv.x;
+                const long long cc = c + di;
+                const MacB6 b = mac_load_b<CB>(L, B, i + di, j, k);
+                const double xm = di ? xv.x : mac_nb_lo(L, x, cc, xc, 0, i, 1, x);
+                const double xp = di ? mac_nb_hi(L, x, cc, xc, 0, i + 1, 1, x) : xv.y;
+                const double ym = mac_nb_lo(L, x, cc, xc, 1, j, L.sx, x), yp = mac_nb_hi(L, x, cc, xc, 1, j, L.sx, x);
+                const double zm = mac_nb_lo(L, x, cc, xc, 2, k, L.sxy, x), zp = mac_nb_hi(L, x, cc, xc, 2, k, L.sxy, x);
+                const double ax = -L.dh[0] * (b.xp * (xp - xc) - b.xm * (xc - xm)) - L.dh[1] * (b.yp * (yp - xc) - b.ym * (xc - ym))
+                                - L.dh[2] * (b.zp * (zp - xc) - b.zm * (xc - zm));
+                acc += ((di ? bv.y : bv.x) - off) - ax;
+            }
+        }
+    crse[mac_c(Lc, ic, jc, kc)] = 0.125 * acc;
 }
 // one block folds the partials: scal[0] = max, scal[2] = sum, scal[6] = sum / ncells (the solvability offset)
 __global__ void __launch_bounds__(1024) k_mac_reduce(const double* __restrict__ part_max, const double* __restrict__ part_sum, long long n,

@@ -38,6 +38,7 @@ struct MacSolver {
     static dim3 blk() { return dim3(32, 8, 1); }
     static dim3 grid_cells(const MacLevel& L) { return dim3((L.n[0] + 31) / 32, (L.n[1] + 7) / 8, L.n[2]); }
     static dim3 grid_pairs(const MacLevel& L) { return dim3(((L.n[0] + 1) / 2 + 31) / 32, (L.n[1] + 7) / 8, L.n[2]); }
+    static dim3 grid_adotx(const MacLevel& L) { return dim3((L.n[0] + 31) / 32, (L.n[1] + 7) / 8, (L.n[2] + MAC_KZ - 1) / MAC_KZ); }
     static long long nblk(dim3 g) { return (long long)g.x * g.y * g.z; }
     static int alloc_d(double** p, long long n) { void* q = nullptr; if (np_rt::dev_malloc(&q, (size_t)n * sizeof(double))) return 1; *p = (double*)q; return 0; }
     void zero(double* p, long long n) { np_rt::memset_async(p, 0, (size_t)n * sizeof(double), stream); }
@@ -179,11 +180,47 @@ struct MacSolver {
         gsrb(l, phi, b, 0, zero_in, nullptr, boff);
         gsrb(l, phi, b, 1, false, add_to, boff);
     }
+    // levels large enough to fill the GPU run both colours in one out-of-place pass (k_mac_rb2)
+    bool fused_ok(int l) const
+    {
+        const MacLevel& d = lev[l].d;
+        if (opt.fused_rb_min_n <= 0 || d.n[0] < opt.fused_rb_min_n || (d.n[0] & 1)) return false;
+        for (int q = 0; q < 3; ++q) if (bclo[q] == NP_BC_PERIODIC && (d.n[q] & 1)) return false;
+        return true;
+    }
+    // one smooth of lev[l].cor against lev[l].res; with crse: cor += interpolation(crse) first (addInterpCorrection).
+    // The fused pass writes into lev[l].rescor and the two pointers are swapped, so lev[l].cor is always the current iterate.
+    void smooth_level(int l, bool zero_in, const double* crse, double* add_to, const double* boff)
+    {
+        MacLev& L = lev[l];
+        if (!fused_ok(l)) {
+            if (crse) interp_add(l, L.cor, crse);
+            smooth(l, L.cor, L.res, zero_in, add_to, boff);
+            return;
+        }
+        RbArgs A;
+        A.out = L.rescor; A.in = L.cor; A.rhs = L.res; A.boff = boff; A.add_to = add_to; A.crse = crse; A.zero_in = zero_in ? 1 : 0;
+        A.zc = std::min(32, std::max(4, L.d.n[2] / 8));
+        const dim3 g((L.d.n[0] + RB_TX - 1) / RB_TX, (L.d.n[1] + RB_TY - 1) / RB_TY, (L.d.n[2] + A.zc - 1) / A.zc);
+        const MacLevel& C = crse ? lev[l + 1].d : L.d;
+        if (L.d.const_beta) NP_LAUNCH(true, (k_mac_rb2<true>), g, dim3(256), 0, stream, L.d, C, L.beta(), A);
+        else NP_LAUNCH(true, (k_mac_rb2<false>), g, dim3(256), 0, stream, L.d, C, L.beta(), A);
+        ++launches;
+        std::swap(L.cor, L.rescor);
+    }
     template <int MODE, bool REDUCE> void adotx(int l, double* y, const double* x, const double* b, const double* boff)
     {
         const MacLev& L = lev[l];
-        if (L.d.const_beta) NP_LAUNCH(REDUCE, (k_mac_adotx<MODE, REDUCE, true>), grid_cells(L.d), blk(), 0, stream, L.d, L.beta(), y, x, b, boff, part0, part1);
-        else NP_LAUNCH(REDUCE, (k_mac_adotx<MODE, REDUCE, false>), grid_cells(L.d), blk(), 0, stream, L.d, L.beta(), y, x, b, boff, part0, part1);
+        if (L.d.const_beta) NP_LAUNCH(REDUCE, (k_mac_adotx<MODE, REDUCE, true>), grid_adotx(L.d), blk(), 0, stream, L.d, L.beta(), y, x, b, boff, part0, part1);
+        else NP_LAUNCH(REDUCE, (k_mac_adotx<MODE, REDUCE, false>), grid_adotx(L.d), blk(), 0, stream, L.d, L.beta(), y, x, b, boff, part0, part1);
+        ++launches;
+    }
+    // computeResOfCorrection + restriction: lev[l+1].res = average_down(lev[l].res - off - A lev[l].cor)
+    void resid_restrict(int l, const double* boff)
+    {
+        const MacLev& L = lev[l]; const MacLev& C = lev[l + 1];
+        if (L.d.const_beta) NP_LAUNCH(false, (k_mac_resid_restrict<true>), grid_cells(C.d), blk(), 0, stream, C.d, L.d, L.beta(), C.res, (const double*)L.cor, (const double*)L.res, boff);
+        else NP_LAUNCH(false, (k_mac_resid_restrict<false>), grid_cells(C.d), blk(), 0, stream, C.d, L.d, L.beta(), C.res, (const double*)L.cor, (const double*)L.res, boff);
         ++launches;
     }
     // fold the partials of the last reducing kernel over level-0 cells: scal[base] = max, scal[base+2] = sum, scal[base+6] = mean
@@ -261,17 +298,16 @@ struct MacSolver {
             MacLev& L = lev[l];
             const double* off = l == 0 ? off0 : nullptr;
             if (opt.num_pre_smooth <= 0) zero(L.cor, L.d.ntot);
-            for (int i = 0; i < opt.num_pre_smooth; ++i) smooth(l, L.cor, L.res, i == 0, nullptr, off);
-            adotx<1, false>(l, L.rescor, L.cor, L.res, off);              // computeResOfCorrection
-            restrict_to(l + 1, lev[l + 1].res, L.rescor);
+            for (int i = 0; i < opt.num_pre_smooth; ++i) smooth_level(l, i == 0, nullptr, nullptr, off);
+            resid_restrict(l, off);                                        // computeResOfCorrection + restriction, fused
         }
         bottom_solve();
         for (int l = nl - 2; l >= 0; --l) {
             MacLev& L = lev[l];
             const double* off = l == 0 ? off0 : nullptr;
-            interp_add(l, L.cor, lev[l + 1].cor);                         // addInterpCorrection
-            for (int i = 0; i < opt.num_post_smooth; ++i)
-                smooth(l, L.cor, L.res, false, (l == 0 && i == opt.num_post_smooth - 1) ? sol : nullptr, off);
+            if (opt.num_post_smooth <= 0) interp_add(l, L.cor, lev[l + 1].cor);
+            for (int i = 0; i < opt.num_post_smooth; ++i)                  // addInterpCorrection rides on the first post-smooth
+                smooth_level(l, false, i == 0 ? lev[l + 1].cor : nullptr, (l == 0 && i == opt.num_post_smooth - 1) ? sol : nullptr, off);
             if (l == 0 && opt.num_post_smooth <= 0) add_cor_to_sol();
         }
         if (nl == 1) add_cor_to_sol();
@@ -286,7 +322,7 @@ struct MacSolver {
     int solve(double rtol, double atol, double rhsnorm0)
     {
         const MacLevel& d0 = lev[0].d;
-        const long long nb = nblk(grid_cells(d0));
+        const long long nb = nblk(grid_adotx(d0));
         bottom_iters = 0; bicg_failed_switch = false;
         adotx<1, true>(0, lev[0].res, sol, rhs, nullptr);
         reduce(nb, true, singular, 0);
@@ -458,7 +494,7 @@ void mp_default_options(mp_options* o)
 {
     o->max_coarsening_level = 100; o->maxiter = 200; o->bottom_maxiter = 200; o->num_pre_smooth = 2; o->num_post_smooth = 2;
     o->num_final_smooth = 8; o->bottom_solver = NP_BOTTOM_BICGCG; o->verbose = 0; o->bottom_verbose = 0; o->maxorder = 3;
-    o->bottom_rtol = 1e-4; o->bottom_atol = -1.0; o->const_beta_fastpath = 1;
+    o->bottom_rtol = 1e-4; o->bottom_atol = -1.0; o->const_beta_fastpath = 1; o->fused_rb_min_n = 128;
 }
 int mp_create(mp_handle** h, const np_geom* geom, int nboxes_global, const np_box* all_boxes, const int* owner_rank,
               int my_rank, int nranks, void* nccl_comm_or_null, const mp_options* opt)
@@ -529,7 +565,7 @@ int mp_smooth(mp_handle* h, int l, np_fab* x, const np_fab* rhs, int ncalls)
     if (!MP_LEVEL_OK(h, l) || !x || !rhs) return NP_ERR_INVALID;
     MacSolver& S = h->S; MacLev& L = S.lev[l];
     if (S.cell_in(l, *x, L.cor, 0) || S.cell_in(l, *rhs, L.res, 1)) return NP_ERR_INVALID;
-    for (int i = 0; i < ncalls; ++i) S.smooth(l, L.cor, L.res, false, nullptr, nullptr);
+    for (int i = 0; i < ncalls; ++i) S.smooth_level(l, false, nullptr, nullptr, nullptr);
     return S.cell_out(l, *x, L.cor, 0);
 }
 int mp_restrict(mp_handle* h, int lc, const np_fab* fine, np_fab* crse)

@@ -45,6 +45,8 @@ typedef struct {
     double bottom_rtol;         /* mac_proj.bottom_rtol                    default 1e-4 */
     double bottom_atol;         /* mac_proj.bottom_atol                    default -1 */
     int const_beta_fastpath;    /* skip every coefficient read when b is uniform (constant density); default 1 */
+    int fused_rb_min_n;         /* levels with at least this many cells in x run the red and the black sweep of a smooth in
+                                   ONE pass (k_mac_rb2); smaller levels use one launch per colour; default 128, <= 0: never */
 } mp_options;
 
 void mp_default_options(mp_options* o);

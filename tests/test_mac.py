@@ -100,11 +100,14 @@ class Drv:
 
 @pytest.mark.parametrize("bclo,bchi", BCS)
 @pytest.mark.parametrize("const", [False, True])
-def test_mac_kernels(backend, bclo, bchi, const):
+@pytest.mark.parametrize("fused", [128, 2])
+def test_mac_kernels(backend, bclo, bchi, const, fused):
+    """fused = 2: every level that qualifies runs both colours of a smooth in one pass (k_mac_rb2) - tiles, z-chunks and
+    halos of 2 on tiny levels; 128 (the default): one launch per colour here."""
     rng = np.random.default_rng(7)
     ncell, hi = (16, 8, 12), (1.6, 1.0, 0.9)
     beta = random_beta(rng, ncell, bclo, const)
-    drv = Drv(ncell, hi, bclo, bchi, beta, backend)
+    drv = Drv(ncell, hi, bclo, bchi, beta, backend, fused_rb_min_n=fused)
     o = MacOracle(ncell, (0, 0, 0), hi, bclo, bchi)
     o.set_beta(*beta)
     assert drv.P.num_levels == o.num_levels == 2 + 1
@@ -146,9 +149,10 @@ CASES = [("double_shear", (32, 32, 16), dict(prob_hi=(1.0, 1.0, 0.5))), ("raylei
 
 
 @pytest.mark.parametrize("name,ncell,kw", CASES)
-def test_mac_project_matches_oracle(backend, name, ncell, kw):
+@pytest.mark.parametrize("fused", [128, 2])
+def test_mac_project_matches_oracle(backend, name, ncell, kw, fused):
     prob = problems.MAC_PROBLEMS[name](ncell, **kw)
-    drv = Drv(ncell, prob["prob_hi"], prob["bclo"], prob["bchi"], prob["beta"], backend)
+    drv = Drv(ncell, prob["prob_hi"], prob["bclo"], prob["bchi"], prob["beta"], backend, fused_rb_min_n=fused)
     st, u, phi = drv.project(prob["umac"], ng=1)
     o = MacOracle(ncell, prob["prob_lo"], prob["prob_hi"], prob["bclo"], prob["bchi"])
     o.set_beta(*prob["beta"]); o.set_umac(*prob["umac"])
@@ -180,7 +184,7 @@ def test_mac_project_dirichlet_and_guess(backend):
     umac[0][:, :, 0] = 1.0                      # inflow face values stay as given
     umac[1][:, 0, :] = 0.0; umac[1][:, -1, :] = 0.0
     umac[2][-1] = umac[2][0]
-    drv = Drv(ncell, hi, bclo, bchi, beta, backend)
+    drv = Drv(ncell, hi, bclo, bchi, beta, backend, fused_rb_min_n=2)
     st, u, phi = drv.project(umac)
     o = MacOracle(ncell, (0, 0, 0), hi, bclo, bchi)
     o.set_beta(*beta); o.set_umac(*umac)
@@ -227,3 +231,17 @@ def test_mac_host_fabs_on_gpu():
     assert st.n_vcycles == so.n_vcycles
     for a, b in zip(u, o.get_umac()):
         assert l2rel(a, b) < 1e-12
+
+
+@pytest.mark.parametrize("bclo,bchi", [BCS[0], BCS[3]])
+def test_mac_fused_smoother_tiles(backend, bclo, bchi):
+    """k_mac_rb2 across tile and chunk borders: 2 x 2 tiles of 64 x 16 cells, two z-chunks, three smooths in a row."""
+    rng = np.random.default_rng(11)
+    ncell, hi = (80, 24, 8), (1.0, 0.3, 0.1)
+    beta = random_beta(rng, ncell, bclo)
+    drv = Drv(ncell, hi, bclo, bchi, beta, backend, fused_rb_min_n=2)
+    o = MacOracle(ncell, (0, 0, 0), hi, bclo, bchi)
+    o.set_beta(*beta)
+    x = rng.standard_normal(ncell[::-1]); b = rng.standard_normal(ncell[::-1])
+    s, so = drv.smooth(0, x, b, 3), o.smooth(0, x, b, 3)
+    assert np.abs(s - so).max() <= 1e-13 * np.abs(so).max()
