@@ -347,8 +347,172 @@ def run_gpu(args):
         dist.destroy_process_group()
 
 
+# ---------------------------------------------------------------------------------------------------
+# --path mac: the MAC projection measured to the same contract.  One GPU this round.
+# Algorithmic bytes per cell and V-cycle, SURVEY 8(d) rules (each array once per kernel, reference schedule 2+2 smooths x
+# 2 colours): per level cor = 0 (8) + 8 colour sweeps x (cor r/w, rhs[, 3 face coefficients]) + residual of the correction
+# + restriction (9) + interpolation (17), x 8/7 for the coarse levels, + level 0's sol += cor (24), residual, norm (8).
+# ---------------------------------------------------------------------------------------------------
+MAC_METRIC = "mac_projection_dof_per_s_per_vcycle"
+MAC_BYTES = {True: (8 + 8 * 24 + 24 + 9 + 17) * 8 // 7 + 24 + 24 + 8, False: (8 + 8 * 48 + 48 + 9 + 17) * 8 // 7 + 24 + 48 + 8}
+
+
+def mac_config(args, sample=None):
+    n = args.ncell
+    if args.workload == "rayleigh_taylor":
+        wl = (f"MAC projection, synthetic {n}^3 cells, periodic x/y, walls (Neumann) in z, beta = 1/rho on faces with the "
+              f"Rayleigh-Taylor density (ratio 4), gravity kick + perturbation on the face velocities, rtol {RTOL:g} atol {ATOL:g}")
+    else:
+        wl = (f"MAC projection, synthetic {n}^3 cells, periodic, constant density (beta = 1), double_shear_layer + z-wave + "
+              f"perturbation sampled on faces, rtol {RTOL:g} atol {ATOL:g}")
+    c = {"workload": wl, "ncell_per_gpu": [n, n, n], "boxes": f"one {n}^3 box",
+         "l2": "inputs (>= 1 GB per array at 512^3) exceed the 126 MB L2; no explicit flush"}
+    if sample:
+        c["cpu_sample"] = sample
+    return c
+
+
+def cpu_mac_projection(n, workload, reps):
+    """The MAC oracle (CPU restatement of MacProjector / MLMG / MLABecLaplacian; red-black GS threaded over planes)."""
+    from incflo_b200 import problems
+    from oracle.mac import MacOracle
+    cores = os.cpu_count() or 1
+    ncell = (n, n, n)
+    hi = (1.0, 1.0, 1.0) if workload == "double_shear" else (0.5, 0.5, 0.5)
+    prob = problems.MAC_PROBLEMS[workload](ncell, prob_hi=hi)
+    total, vc = 0.0, 0
+    for _ in range(reps):
+        o = MacOracle(ncell, prob["prob_lo"], prob["prob_hi"], prob["bclo"], prob["bchi"], nthreads=cores)
+        o.set_beta(*prob["beta"]); o.set_umac(*prob["umac"])
+        t0 = time.perf_counter()
+        st = o.project(RTOL, ATOL)
+        total += time.perf_counter() - t0
+        vc += st.n_vcycles
+        if st.status != 0:
+            raise RuntimeError("MAC oracle did not converge")
+    return dict(value=(n ** 3) * vc / total, cores=cores, vcycles=vc // reps, ms_per_step=1e3 * total / reps,
+                sample=f"MAC {workload} {n}^3, one box, red-black GS threaded over z-planes on all host cores, rtol {RTOL:g}; "
+                       f"{reps} projection(s), {total:.1f} s")
+
+
+def run_reference_mac(args):
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    r = cpu_mac_projection(args.cpu_ncell, args.workload, args.steps)
+    line = {"impl": "reference", "metric": MAC_METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": 0, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic", "config": mac_config(args, r["sample"]),
+            "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"]},
+            "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0,
+            "note": "reference incflo+AMReX build unavailable on this box; this is oracle/mac_oracle.cpp"}
+    print(json.dumps(line), flush=True)
+
+
+def run_gpu_mac(args):
+    import torch
+    from incflo_b200 import capi, problems
+    from incflo_b200.mac_projector import MacProjector
+    from incflo_b200.projector import Fab, Geometry, LPInfo
+    if int(os.environ.get("WORLD_SIZE", "1")) > 1:
+        raise SystemExit("bench.py --path mac: one GPU this round (the z-slab layer is not wired into the MAC solver yet)")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; incflo_b200 has no CPU fallback")
+    torch.cuda.set_device(0)
+    dev = "cuda:0"
+    n = args.ncell
+    ncell = (n, n, n)
+    hi = (1.0, 1.0, 1.0) if args.workload == "double_shear" else (0.5, 0.5, 0.5)
+    umac0, beta, bclo, bchi = problems.mac_problem_torch(args.workload, ncell, hi, dev)
+    umac = [Fab(u.clone(), 0) for u in umac0]
+    P = MacProjector(Geometry(ncell, (0, 0, 0), hi, [b == 0 for b in bclo]), lib=capi.load())
+    P.setDomainBC(bclo, bchi)
+    P.initProjector(LPInfo().setMaxCoarseningLevel(100), [Fab(b, 0) for b in beta], profile_kernels=1, verbose=args.verbose)
+    P.setUMAC(umac)
+    stream = torch.cuda.current_stream().cuda_stream
+    dof = n ** 3
+
+    def step():
+        for f, u0 in zip(umac, umac0):
+            f.data.copy_(u0)
+        return P.project(RTOL, ATOL, stream=stream)
+
+    clocks = ClockSampler(0)
+    clocks.start()
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+    clocks.mark()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    vcycles = launches = n_smooth = 0
+    ms_smooth = ms_solve = 0.0
+    for _ in range(args.steps):
+        st = step()
+        vcycles += st.n_vcycles; launches += st.kernel_launches
+        ms_smooth += st.ms_smooth0; n_smooth += st.n_smooth0; ms_solve += st.ms_solve
+        hist = [st.res_history[i] / max(st.rhs_norm0, 1e-300) for i in range(st.n_vcycles)]
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    clk = clocks.stop()
+    const_beta = bool(st.sigma_is_const)
+
+    # e2e: host (pinned) face fabs through the same call; umac H2D + D2H every step, beta H2D through updateBeta, phi D2H
+    e2e = None
+    if not args.no_e2e:
+        hu0 = [u.cpu() for u in umac0]
+        hu = [Fab(torch.empty_like(u).pin_memory(), 0) for u in hu0]
+        hb = [Fab(b.cpu().pin_memory(), 0) for b in beta]
+        hphi = Fab(torch.zeros((1, n, n, n), dtype=torch.float64).pin_memory(), 0)
+        P.setUMAC(hu)
+        h2d = sum(f.data.numel() * 8 for f in hu) + sum(f.data.numel() * 8 for f in hb)
+        d2h = sum(f.data.numel() * 8 for f in hu) + hphi.data.numel() * 8
+        tot_ms, tot_vc = 0.0, 0
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        for it in range(1 + args.e2e_steps):
+            for f, u0 in zip(hu, hu0):
+                f.data.copy_(u0)
+            torch.cuda.synchronize()
+            a.record()
+            P.updateBeta(hb)
+            st2 = P.project(RTOL, ATOL, stream=stream)
+            P.copyPhi(hphi)
+            b.record()
+            torch.cuda.synchronize()
+            if it >= 1:
+                tot_ms += a.elapsed_time(b); tot_vc += st2.n_vcycles
+        e2e = {"value": dof * tot_vc / (tot_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+               "steps": args.e2e_steps, "ms_per_step": tot_ms / args.e2e_steps}
+
+    peak, peak_src = read_peaks()
+    per_cell = 2 * (24 if const_beta else 48)            # one smooth = red + black sweep: cor r/w, rhs[, bx, by, bz] each
+    avg_ms = ms_smooth / max(n_smooth, 1)
+    achieved = per_cell * dof / (avg_ms * 1e-3) / 1e9 if avg_ms > 0 else 0.0
+    roof = {"bound": "hbm", "kernel": ("k_mac_gsrb<const beta> x 2 (red, black), level 0" if const_beta
+                                       else "k_mac_rb2<variable beta> (red + black in one pass), level 0"),
+            "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+            "algorithmic_bytes_per_launch": per_cell * dof, "avg_launch_ms": avg_ms, "launches_timed": int(n_smooth),
+            "share_of_step": ms_smooth / ms,
+            "vcycle_algorithmic": {"bytes_per_dof": MAC_BYTES[const_beta],
+                                   "achieved_gbs": MAC_BYTES[const_beta] * dof * vcycles / (ms_solve * 1e-3) / 1e9}}
+    roof["vcycle_algorithmic"]["frac"] = roof["vcycle_algorithmic"]["achieved_gbs"] / peak
+    line = {"metric": MAC_METRIC, "value": dof * vcycles / (ms * 1e-3), "unit": UNIT, "n_gpus": 1, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic", "config": mac_config(args), "vcycles_per_step": vcycles / args.steps,
+            "mg_levels": st.n_levels, "ms_per_vcycle": ms / vcycles, "ms_solve_per_vcycle": ms_solve / vcycles,
+            "rel_res_history": hist, "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof}
+    if not args.no_cpu:
+        r = cpu_mac_projection(args.cpu_ncell, args.workload, 1)
+        line["cpu_baseline"] = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"],
+                                "vcycles": r["vcycles"]}
+    print(json.dumps(line), flush=True)
+    P.close()
+
+
 def main():
     ap = argparse.ArgumentParser()
+    ap.add_argument("--path", default="nodal", choices=["nodal", "mac"],
+                    help="nodal: the nodal projection (BASELINE metric, default); mac: the MAC projection (SURVEY 8(f) row 1)")
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
@@ -367,7 +531,9 @@ def main():
     ap.add_argument("--no-overlap", action="store_true", help="experiment knob: halo exchange on the solver stream (overlap_halo=0)")
     ap.add_argument("--verbose", type=int, default=0, help="nodal_proj.verbose (4: per-launch smoother times on stderr)")
     args = ap.parse_args()
-    if args.impl == "reference":
+    if args.path == "mac":
+        run_reference_mac(args) if args.impl == "reference" else run_gpu_mac(args)
+    elif args.impl == "reference":
         run_reference(args)
     else:
         run_gpu(args)

@@ -27,6 +27,7 @@ struct MacSolver {
     double* bw[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     double* stage[4] = {nullptr, nullptr, nullptr, nullptr}; long long stage_n[4] = {0, 0, 0, 0};
     double* wrapbuf = nullptr; long long wrapbuf_n = 0;
+    std::vector<np_event_t> prof_ev; int prof_n = 0;     // profile_kernels: start/stop pairs around the level-0 smooths
     np_stream_t stream = 0;
     np_event_t ev[4] = {0, 0, 0, 0};
     np_stats stats{};
@@ -100,6 +101,7 @@ struct MacSolver {
         h_bot_out = (int*)q;
         for (int w = 0; w < 6; ++w) { if (alloc_d(&bw[w], lev.back().d.ntot)) return NP_ERR_CUDA; zero(bw[w], lev.back().d.ntot); }
         for (int e = 0; e < 4; ++e) np_rt::event_create(&ev[e]);
+        if (opt.profile_kernels) { prof_ev.resize(4096); for (auto& e : prof_ev) np_rt::event_create(&e); }
         setup_bc();
         np_rt::stream_sync(stream);
         return np_rt::last_error() ? NP_ERR_CUDA : NP_OK;
@@ -115,6 +117,8 @@ struct MacSolver {
         if (bot_out) np_rt::dev_free(bot_out);
         if (h_bot_out) np_rt::host_free(h_bot_out);
         for (int e = 0; e < 4; ++e) if (ev[e]) np_rt::event_destroy(ev[e]);
+        for (auto& e : prof_ev) np_rt::event_destroy(e);
+        prof_ev.clear();
     }
 
     // ---- caller fabs ----
@@ -185,12 +189,20 @@ struct MacSolver {
     {
         const MacLevel& d = lev[l].d;
         if (opt.fused_rb_min_n <= 0 || d.n[0] < opt.fused_rb_min_n || (d.n[0] & 1)) return false;
+        if (d.const_beta && !opt.fused_rb_const) return false;
         for (int q = 0; q < 3; ++q) if (bclo[q] == NP_BC_PERIODIC && (d.n[q] & 1)) return false;
         return true;
     }
     // one smooth of lev[l].cor against lev[l].res; with crse: cor += interpolation(crse) first (addInterpCorrection).
     // The fused pass writes into lev[l].rescor and the two pointers are swapped, so lev[l].cor is always the current iterate.
     void smooth_level(int l, bool zero_in, const double* crse, double* add_to, const double* boff)
+    {
+        const bool prof = opt.profile_kernels && l == 0 && prof_n + 2 <= (int)prof_ev.size();
+        if (prof) np_rt::event_record(prof_ev[prof_n++], stream);
+        smooth_level_impl(l, zero_in, crse, add_to, boff);
+        if (prof) np_rt::event_record(prof_ev[prof_n++], stream);
+    }
+    void smooth_level_impl(int l, bool zero_in, const double* crse, double* add_to, const double* boff)
     {
         MacLev& L = lev[l];
         if (!fused_ok(l)) {
@@ -402,6 +414,8 @@ struct MacSolver {
         stats.ms_finish = np_rt::event_ms(ev[2], ev[3]);
         stats.ms_total = np_rt::event_ms(ev[0], ev[3]);
         stats.kernel_launches = launches;
+        stats.n_smooth0 = prof_n / 2; stats.ms_smooth0 = 0.0;
+        for (int e = 0; e + 1 < prof_n; e += 2) stats.ms_smooth0 += np_rt::event_ms(prof_ev[e], prof_ev[e + 1]);
     }
     // MacProjector::setUMAC + project
     int project(np_fab umac[3], np_fab* mac_phi, double rtol, double atol)
@@ -409,7 +423,7 @@ struct MacSolver {
         if (!have_beta) return NP_ERR_STATE;
         for (int d = 0; d < 3; ++d) if (!umac[d].p || umac[d].ncomp < 1) return NP_ERR_INVALID;
         if (mac_phi && (!mac_phi->p || mac_phi->ncomp < 1)) return NP_ERR_INVALID;
-        launches = 0; have_result = false;
+        launches = 0; have_result = false; prof_n = 0;
         const int is_const = stats.sigma_is_const;
         stats = np_stats{}; stats.sigma_is_const = is_const;
         const MacLevel& d0 = lev[0].d;
@@ -494,7 +508,7 @@ void mp_default_options(mp_options* o)
 {
     o->max_coarsening_level = 100; o->maxiter = 200; o->bottom_maxiter = 200; o->num_pre_smooth = 2; o->num_post_smooth = 2;
     o->num_final_smooth = 8; o->bottom_solver = NP_BOTTOM_BICGCG; o->verbose = 0; o->bottom_verbose = 0; o->maxorder = 3;
-    o->bottom_rtol = 1e-4; o->bottom_atol = -1.0; o->const_beta_fastpath = 1; o->fused_rb_min_n = 128;
+    o->bottom_rtol = 1e-4; o->bottom_atol = -1.0; o->const_beta_fastpath = 1; o->fused_rb_min_n = 128; o->fused_rb_const = 0; o->profile_kernels = 0;
 }
 int mp_create(mp_handle** h, const np_geom* geom, int nboxes_global, const np_box* all_boxes, const int* owner_rank,
               int my_rank, int nranks, void* nccl_comm_or_null, const mp_options* opt)

@@ -47,6 +47,9 @@ typedef struct {
     int const_beta_fastpath;    /* skip every coefficient read when b is uniform (constant density); default 1 */
     int fused_rb_min_n;         /* levels with at least this many cells in x run the red and the black sweep of a smooth in
                                    ONE pass (k_mac_rb2); smaller levels use one launch per colour; default 128, <= 0: never */
+    int fused_rb_const;         /* 1: also when b is uniform; default 0 - with no coefficients to read the one-pass kernel is
+                                   bound by its instruction count and measured slower than two launches */
+    int profile_kernels;        /* bracket every level-0 smooth with CUDA events (np_stats.ms_smooth0 / n_smooth0); default 0 */
 } mp_options;
 
 void mp_default_options(mp_options* o);

@@ -107,7 +107,7 @@ def test_mac_kernels(backend, bclo, bchi, const, fused):
     rng = np.random.default_rng(7)
     ncell, hi = (16, 8, 12), (1.6, 1.0, 0.9)
     beta = random_beta(rng, ncell, bclo, const)
-    drv = Drv(ncell, hi, bclo, bchi, beta, backend, fused_rb_min_n=fused)
+    drv = Drv(ncell, hi, bclo, bchi, beta, backend, fused_rb_min_n=fused, fused_rb_const=1)
     o = MacOracle(ncell, (0, 0, 0), hi, bclo, bchi)
     o.set_beta(*beta)
     assert drv.P.num_levels == o.num_levels == 2 + 1
@@ -152,7 +152,7 @@ CASES = [("double_shear", (32, 32, 16), dict(prob_hi=(1.0, 1.0, 0.5))), ("raylei
 @pytest.mark.parametrize("fused", [128, 2])
 def test_mac_project_matches_oracle(backend, name, ncell, kw, fused):
     prob = problems.MAC_PROBLEMS[name](ncell, **kw)
-    drv = Drv(ncell, prob["prob_hi"], prob["bclo"], prob["bchi"], prob["beta"], backend, fused_rb_min_n=fused)
+    drv = Drv(ncell, prob["prob_hi"], prob["bclo"], prob["bchi"], prob["beta"], backend, fused_rb_min_n=fused, fused_rb_const=1)
     st, u, phi = drv.project(prob["umac"], ng=1)
     o = MacOracle(ncell, prob["prob_lo"], prob["prob_hi"], prob["bclo"], prob["bchi"])
     o.set_beta(*prob["beta"]); o.set_umac(*prob["umac"])
@@ -184,7 +184,7 @@ def test_mac_project_dirichlet_and_guess(backend):
     umac[0][:, :, 0] = 1.0                      # inflow face values stay as given
     umac[1][:, 0, :] = 0.0; umac[1][:, -1, :] = 0.0
     umac[2][-1] = umac[2][0]
-    drv = Drv(ncell, hi, bclo, bchi, beta, backend, fused_rb_min_n=2)
+    drv = Drv(ncell, hi, bclo, bchi, beta, backend, fused_rb_min_n=2, fused_rb_const=1)
     st, u, phi = drv.project(umac)
     o = MacOracle(ncell, (0, 0, 0), hi, bclo, bchi)
     o.set_beta(*beta); o.set_umac(*umac)
@@ -239,7 +239,7 @@ def test_mac_fused_smoother_tiles(backend, bclo, bchi):
     rng = np.random.default_rng(11)
     ncell, hi = (80, 24, 8), (1.0, 0.3, 0.1)
     beta = random_beta(rng, ncell, bclo)
-    drv = Drv(ncell, hi, bclo, bchi, beta, backend, fused_rb_min_n=2)
+    drv = Drv(ncell, hi, bclo, bchi, beta, backend, fused_rb_min_n=2, fused_rb_const=1)
     o = MacOracle(ncell, (0, 0, 0), hi, bclo, bchi)
     o.set_beta(*beta)
     x = rng.standard_normal(ncell[::-1]); b = rng.standard_normal(ncell[::-1])
