@@ -250,6 +250,172 @@ __global__ void __launch_bounds__(256) k_mac_rb2(MacLevel L, MacLevel Lc, MacBet
 }
 
 // ------------------------------------------------------------------------------------------------
+// k_mac_rb3: the same one-pass smooth as k_mac_rb2 for levels whose x / y extents are multiples of the tile (every large
+// level of a 2^n grid), with all index work hoisted out of the plane loop.  A thread owns two aligned cell pairs of the tile
+// (rows ty and ty+8), at most two cells of the halo-2 frame to load and at most one cell of the tile+1 ring to relax; their
+// shared-memory offsets, wrapped in-plane global offsets and boundary flags are computed once.  Per plane a thread issues
+// two 16-byte loads + <= 2 scalar loads, <= 3 red and 2 black updates (a branch-free body when no domain face is near)
+// and two 16-byte stores.
+// ------------------------------------------------------------------------------------------------
+enum { RBF_XLO = 1, RBF_XHI = 2, RBF_YLO = 4, RBF_YHI = 8, RBF_ZLO = 16, RBF_ZHI = 32 };
+struct RbCell { int so; int go; int gfx; int flags; };     // smem offset, in-plane cell offset, in-plane bx offset, RBF_*
+
+template <bool CB>
+__device__ __forceinline__ double rb3_update(const MacLevel& L, const MacBeta& B, const double* __restrict__ P, const double* __restrict__ Pm,
+                                             const double* __restrict__ Pp, const RbCell& cl, int zflags, long long zc, long long zfx, long long zfy,
+                                             const double* __restrict__ rhs, double off)
+{
+    const int o = cl.so;
+    const double xc = P[o];
+    double bxm, bxp, bym, byp, bzm, bzp;
+    if (CB) { bxm = bxp = bym = byp = bzm = bzp = L.beta0; }
+    else {
+        const double* px = B.bx + zfx + cl.gfx; bxm = px[0]; bxp = px[1];
+        const double* py = B.by + zfy + cl.go;  bym = py[0]; byp = py[L.sx];
+        const double* pz = B.bz + zc + cl.go;   bzm = pz[0]; bzp = pz[L.sxy];
+    }
+    const double gamma = L.dh[0] * (bxm + bxp) + L.dh[1] * (bym + byp) + L.dh[2] * (bzm + bzp);
+    const double r = rhs[zc + cl.go] - off;
+    const int fl = cl.flags | zflags;
+    double xm = P[o - 1], xp = P[o + 1], ym = P[o - RB_PX], yp = P[o + RB_PX], zm = Pm[o], zp = Pp[o];
+    double g_m_d = gamma;
+    if (fl) {       // a Neumann / Dirichlet face next to the cell: ghost values from the boundary condition
+        double delta = 0.0;
+        if (fl & RBF_XLO) { xm = L.bclo[0] == MAC_NEU ? xc : L.dc0[0] * xc + L.dc1[0] * xp; delta += L.dh[0] * bxm * L.flo[0]; }
+        if (fl & RBF_XHI) { xp = L.bchi[0] == MAC_NEU ? xc : L.dc0[0] * xc + L.dc1[0] * P[o - 1]; delta += L.dh[0] * bxp * L.fhi[0]; }
+        if (fl & RBF_YLO) { ym = L.bclo[1] == MAC_NEU ? xc : L.dc0[1] * xc + L.dc1[1] * yp; delta += L.dh[1] * bym * L.flo[1]; }
+        if (fl & RBF_YHI) { yp = L.bchi[1] == MAC_NEU ? xc : L.dc0[1] * xc + L.dc1[1] * P[o - RB_PX]; delta += L.dh[1] * byp * L.fhi[1]; }
+        if (fl & RBF_ZLO) { zm = L.bclo[2] == MAC_NEU ? xc : L.dc0[2] * xc + L.dc1[2] * zp; delta += L.dh[2] * bzm * L.flo[2]; }
+        if (fl & RBF_ZHI) { zp = L.bchi[2] == MAC_NEU ? xc : L.dc0[2] * xc + L.dc1[2] * Pm[o]; delta += L.dh[2] * bzp * L.fhi[2]; }
+        g_m_d = gamma - delta;
+    }
+    const double rho = L.dh[0] * (bxm * xm + bxp * xp) + L.dh[1] * (bym * ym + byp * yp) + L.dh[2] * (bzm * zm + bzp * zp);
+    const double res = r - (gamma * xc - rho);
+    return xc + 1.15 / g_m_d * res;
+}
+
+__device__ __forceinline__ int rb3_flags(const MacLevel& L, int gx, int gy)
+{
+    int f = 0;
+    if (L.bclo[0] != MAC_PER) { if (gx == 0) f |= RBF_XLO; if (gx == L.n[0] - 1) f |= RBF_XHI; }
+    if (L.bclo[1] != MAC_PER) { if (gy == 0) f |= RBF_YLO; if (gy == L.n[1] - 1) f |= RBF_YHI; }
+    return f;
+}
+
+template <bool CB>
+__global__ void __launch_bounds__(256) k_mac_rb3(MacLevel L, MacLevel Lc, MacBeta B, RbArgs A)
+{
+    __shared__ __align__(16) double ring[4 * RB_PS];
+    const int tid = threadIdx.x, tx = tid & 31, ty = tid >> 5;
+    const int x0 = blockIdx.x * RB_TX, y0 = blockIdx.y * RB_TY, z0 = blockIdx.z * A.zc, z1 = min(z0 + A.zc, L.n[2]);
+    const int px = L.bclo[0] == MAC_PER, py = L.bclo[1] == MAC_PER, pz = L.bclo[2] == MAC_PER;
+    const double off = A.boff ? *A.boff : 0.0;
+    const int sx = (int)L.sx, fxs = (int)L.fxs, sxc = (int)Lc.sx;
+    // ---- the thread's fixed cells ----
+    RbCell own[2][2];           // [pair][cell of the pair]
+    int par[2], pco[2];         // parity of (gx0 + gy); in-plane offset of the pair's coarse parent
+    for (int m = 0; m < 2; ++m) {
+        const int lx0 = 2 + 2 * tx, ly = 2 + ty + 8 * m, gx0 = x0 + 2 * tx, gy = y0 + ty + 8 * m;
+        par[m] = (gx0 + gy) & 1;
+        pco[m] = (gx0 >> 1) + sxc * (gy >> 1);
+        for (int a = 0; a < 2; ++a) {
+            own[m][a].so = lx0 + a + RB_PX * ly; own[m][a].go = gx0 + a + sx * gy; own[m][a].gfx = gx0 + a + fxs * gy;
+            own[m][a].flags = rb3_flags(L, gx0 + a, gy);
+        }
+    }
+    // halo-2 frame: rows 0,1 and 18,19 (68 wide), columns 0,1,66,67 of rows 2..17: 336 cells, threads take tid and tid + 256
+    int fso[2], fgo[2], fpc[2];
+    for (int e = 0; e < 2; ++e) {
+        const int f = tid + 256 * e;
+        fso[e] = -1; fgo[e] = -1; fpc[e] = 0;
+        if (f < 336) {
+            int lx, ly;
+            if (f < 272) { const int rr = f / RB_PX; lx = f - rr * RB_PX; ly = rr < 2 ? rr : RB_PY - 4 + rr; }
+            else { const int g = f - 272; ly = 2 + (g >> 2); const int cidx = g & 3; lx = cidx < 2 ? cidx : RB_PX - 4 + cidx; }
+            const int gx = rb_wrap(x0 - 2 + lx, L.n[0], px), gy = rb_wrap(y0 - 2 + ly, L.n[1], py);
+            fso[e] = lx + RB_PX * ly;
+            if (gx >= 0 && gy >= 0) { fgo[e] = gx + sx * gy; fpc[e] = (gx >> 1) + sxc * (gy >> 1); }
+        }
+    }
+    // tile+1 ring: rows 1 and 18 (lx 1..66), columns 1 and 66 of rows 2..17: 164 cells, one per thread
+    RbCell rc; rc.so = -1; rc.go = -1; rc.gfx = 0; rc.flags = 0;
+    int rpar = 0;
+    if (tid < 164) {
+        int lx, ly;
+        if (tid < 132) { const int rr = tid / 66; lx = 1 + tid - rr * 66; ly = rr ? RB_PY - 2 : 1; }
+        else { const int g = tid - 132; ly = 2 + (g >> 1); lx = (g & 1) ? RB_PX - 2 : 1; }
+        const int gxu = x0 - 2 + lx, gyu = y0 - 2 + ly;
+        const int gx = rb_wrap(gxu, L.n[0], px), gy = rb_wrap(gyu, L.n[1], py);
+        rpar = (gxu + gyu) & 1;
+        if (gx >= 0 && gy >= 0) { rc.so = lx + RB_PX * ly; rc.go = gx + sx * gy; rc.gfx = gx + fxs * gy; rc.flags = rb3_flags(L, gx, gy); }
+    }
+    const long long fxz = L.fxs * (long long)L.n[1], fyz = L.sx * (long long)(L.n[1] + 1);
+
+    for (int p = z0 - 2; p <= z1 + 1; ++p) {
+        // ---- load plane p ----
+        {
+            const int gz = rb_wrap(p, L.n[2], pz);
+            if (gz >= 0) {
+                double* P = ring + (p & 3) * RB_PS;
+                const long long zc = L.sxy * (long long)gz, zcc = Lc.sxy * (long long)(gz >> 1);
+                for (int m = 0; m < 2; ++m) {
+                    double2 v = make_double2(0.0, 0.0);
+                    if (!A.zero_in) v = *reinterpret_cast<const double2*>(A.in + zc + own[m][0].go);
+                    if (A.crse) { const double cv = A.crse[zcc + pco[m]]; v.x += cv; v.y += cv; }
+                    *reinterpret_cast<double2*>(P + own[m][0].so) = v;
+                }
+                for (int e = 0; e < 2; ++e) if (fso[e] >= 0) {
+                    double v = 0.0;
+                    if (fgo[e] >= 0) { if (!A.zero_in) v = A.in[zc + fgo[e]]; if (A.crse) v += A.crse[zcc + fpc[e]]; }
+                    P[fso[e]] = v;
+                }
+            }
+        }
+        __syncthreads();
+        // ---- red cells of plane p-1: own pairs + ring ----
+        {
+            const int q = p - 1;
+            const int gz = rb_wrap(q, L.n[2], pz);
+            if (gz >= 0 && q >= z0 - 1 && q <= z1) {
+                double* P = ring + (q & 3) * RB_PS;
+                const double* Pm = ring + ((q - 1) & 3) * RB_PS; const double* Pp = ring + ((q + 1) & 3) * RB_PS;
+                const int zfl = pz ? 0 : ((gz == 0 ? RBF_ZLO : 0) | (gz == L.n[2] - 1 ? RBF_ZHI : 0));
+                const long long zc = L.sxy * (long long)gz, zfx = fxz * gz, zfy = fyz * gz;
+                double nv[3]; int no[3] = {-1, -1, -1};
+                for (int m = 0; m < 2; ++m) {
+                    const RbCell& cl = own[m][(par[m] + q) & 1];
+                    nv[m] = rb3_update<CB>(L, B, P, Pm, Pp, cl, zfl, zc, zfx, zfy, A.rhs, off); no[m] = cl.so;
+                }
+                if (rc.so >= 0 && (((rpar + q) & 1) == 0)) { nv[2] = rb3_update<CB>(L, B, P, Pm, Pp, rc, zfl, zc, zfx, zfy, A.rhs, off); no[2] = rc.so; }
+                // reds only read blacks, so the in-place writes of other threads cannot be seen by this phase's reads
+                for (int m = 0; m < 3; ++m) if (no[m] >= 0) P[no[m]] = nv[m];
+            }
+        }
+        __syncthreads();
+        // ---- black cells of plane p-2, stored with their red partners ----
+        {
+            const int r = p - 2;
+            if (r >= z0 && r < z1) {
+                const double* P = ring + (r & 3) * RB_PS;
+                const double* Pm = ring + ((r - 1) & 3) * RB_PS; const double* Pp = ring + ((r + 1) & 3) * RB_PS;
+                const int zfl = pz ? 0 : ((r == 0 ? RBF_ZLO : 0) | (r == L.n[2] - 1 ? RBF_ZHI : 0));
+                const long long zc = L.sxy * (long long)r, zfx = fxz * r, zfy = fyz * r;
+                for (int m = 0; m < 2; ++m) {
+                    const int a = 1 - ((par[m] + r) & 1);
+                    double2 v = *reinterpret_cast<const double2*>(P + own[m][0].so);
+                    const double nb = rb3_update<CB>(L, B, P, Pm, Pp, own[m][a], zfl, zc, zfx, zfy, A.rhs, off);
+                    if (a) v.y = nb; else v.x = nb;
+                    const long long c = zc + own[m][0].go;
+                    *reinterpret_cast<double2*>(A.out + c) = v;
+                    if (A.add_to) { double2 t = *reinterpret_cast<double2*>(A.add_to + c); t.x += v.x; t.y += v.y; *reinterpret_cast<double2*>(A.add_to + c) = t; }
+                }
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // MLABecLaplacian::Fapply (mlabeclap_adotx) and the residuals built on it:
 //   MODE 0: y = A x            MODE 1: y = (b - off) - A x  (MLMG::computeResidual / computeResOfCorrection)
 // REDUCE: per-block partials of max|y| and sum(y) (inf-norm for the convergence test, mean for makeSolvable).

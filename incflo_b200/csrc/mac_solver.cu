@@ -215,7 +215,11 @@ struct MacSolver {
         A.zc = std::min(32, std::max(4, L.d.n[2] / 8));
         const dim3 g((L.d.n[0] + RB_TX - 1) / RB_TX, (L.d.n[1] + RB_TY - 1) / RB_TY, (L.d.n[2] + A.zc - 1) / A.zc);
         const MacLevel& C = crse ? lev[l + 1].d : L.d;
-        if (L.d.const_beta) NP_LAUNCH(true, (k_mac_rb2<true>), g, dim3(256), 0, stream, L.d, C, L.beta(), A);
+        const bool whole_tiles = L.d.n[0] % RB_TX == 0 && L.d.n[1] % RB_TY == 0;      // hoisted-index variant
+        if (whole_tiles) {
+            if (L.d.const_beta) NP_LAUNCH(true, (k_mac_rb3<true>), g, dim3(256), 0, stream, L.d, C, L.beta(), A);
+            else NP_LAUNCH(true, (k_mac_rb3<false>), g, dim3(256), 0, stream, L.d, C, L.beta(), A);
+        } else if (L.d.const_beta) NP_LAUNCH(true, (k_mac_rb2<true>), g, dim3(256), 0, stream, L.d, C, L.beta(), A);
         else NP_LAUNCH(true, (k_mac_rb2<false>), g, dim3(256), 0, stream, L.d, C, L.beta(), A);
         ++launches;
         std::swap(L.cor, L.rescor);

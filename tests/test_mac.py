@@ -145,7 +145,8 @@ def test_mac_bottom_solve(backend, bclo, bchi):
     assert np.abs(x - xo).max() <= 1e-7 * np.abs(xo).max()
 
 
-CASES = [("double_shear", (32, 32, 16), dict(prob_hi=(1.0, 1.0, 0.5))), ("rayleigh_taylor", (16, 16, 32), {})]
+CASES = [("double_shear", (32, 32, 16), dict(prob_hi=(1.0, 1.0, 0.5))), ("rayleigh_taylor", (16, 16, 32), {}),
+         ("rayleigh_taylor", (64, 16, 32), dict(prob_hi=(2.0, 0.5, 1.0)))]      # whole 64 x 16 tiles: k_mac_rb3 on level 0
 
 
 @pytest.mark.parametrize("name,ncell,kw", CASES)
@@ -233,11 +234,13 @@ def test_mac_host_fabs_on_gpu():
         assert l2rel(a, b) < 1e-12
 
 
-@pytest.mark.parametrize("bclo,bchi", [BCS[0], BCS[3]])
-def test_mac_fused_smoother_tiles(backend, bclo, bchi):
-    """k_mac_rb2 across tile and chunk borders: 2 x 2 tiles of 64 x 16 cells, two z-chunks, three smooths in a row."""
+@pytest.mark.parametrize("bclo,bchi", [BCS[0], BCS[3], BCS[2]])
+@pytest.mark.parametrize("ncell", [(80, 24, 8), (128, 32, 8)])
+def test_mac_fused_smoother_tiles(backend, bclo, bchi, ncell):
+    """The one-pass smoother across tile and chunk borders: 2 x 2 tiles of 64 x 16 cells, two z-chunks, three smooths in a
+    row.  (80, 24, 8): partial tiles -> k_mac_rb2; (128, 32, 8): whole tiles -> k_mac_rb3 (hoisted indices)."""
     rng = np.random.default_rng(11)
-    ncell, hi = (80, 24, 8), (1.0, 0.3, 0.1)
+    hi = (1.0, 0.3, 0.1)
     beta = random_beta(rng, ncell, bclo)
     drv = Drv(ncell, hi, bclo, bchi, beta, backend, fused_rb_min_n=2, fused_rb_const=1)
     o = MacOracle(ncell, (0, 0, 0), hi, bclo, bchi)
