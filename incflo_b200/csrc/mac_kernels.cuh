@@ -263,7 +263,7 @@ struct RbCell { int so; int go; int gfx; int flags; };     // smem offset, in-pl
 template <bool CB>
 __device__ __forceinline__ double rb3_update(const MacLevel& L, const MacBeta& B, const double* __restrict__ P, const double* __restrict__ Pm,
                                              const double* __restrict__ Pp, const RbCell& cl, int zflags, long long zc, long long zfx, long long zfy,
-                                             const double* __restrict__ rhs, double off)
+                                             double rhs_c, double off)
 {
     const int o = cl.so;
     const double xc = P[o];
@@ -275,7 +275,7 @@ __device__ __forceinline__ double rb3_update(const MacLevel& L, const MacBeta& B
         const double* pz = B.bz + zc + cl.go;   bzm = pz[0]; bzp = pz[L.sxy];
     }
     const double gamma = L.dh[0] * (bxm + bxp) + L.dh[1] * (bym + byp) + L.dh[2] * (bzm + bzp);
-    const double r = rhs[zc + cl.go] - off;
+    const double r = rhs_c - off;
     const int fl = cl.flags | zflags;
     double xm = P[o - 1], xp = P[o + 1], ym = P[o - RB_PX], yp = P[o + RB_PX], zm = Pm[o], zp = Pp[o];
     double g_m_d = gamma;
@@ -312,17 +312,25 @@ __global__ void __launch_bounds__(256) k_mac_rb3(MacLevel L, MacLevel Lc, MacBet
     const double off = A.boff ? *A.boff : 0.0;
     const int sx = (int)L.sx, fxs = (int)L.fxs, sxc = (int)Lc.sx;
     // ---- the thread's fixed cells ----
-    RbCell own[2][2];           // [pair][cell of the pair]
-    int par[2], pco[2];         // parity of (gx0 + gy); in-plane offset of the pair's coarse parent
-    for (int m = 0; m < 2; ++m) {
-        const int lx0 = 2 + 2 * tx, ly = 2 + ty + 8 * m, gx0 = x0 + 2 * tx, gy = y0 + ty + 8 * m;
-        par[m] = (gx0 + gy) & 1;
-        pco[m] = (gx0 >> 1) + sxc * (gy >> 1);
-        for (int a = 0; a < 2; ++a) {
-            own[m][a].so = lx0 + a + RB_PX * ly; own[m][a].go = gx0 + a + sx * gy; own[m][a].gfx = gx0 + a + fxs * gy;
-            own[m][a].flags = rb3_flags(L, gx0 + a, gy);
-        }
+    RbCell own0, own1;          // first cell of the thread's two pairs (the second cell is +1 in every offset)
+    int of0[2], of1[2];         // boundary flags of the two cells of each pair
+    int par0, par1, pco0, pco1; // parity of (gx0 + gy); in-plane offset of the pair's coarse parent
+    {
+        const int lx0 = 2 + 2 * tx, gx0 = x0 + 2 * tx;
+        const int ly0 = 2 + ty, gy0 = y0 + ty, ly1 = ly0 + 8, gy1 = gy0 + 8;
+        par0 = (gx0 + gy0) & 1; par1 = (gx0 + gy1) & 1;
+        pco0 = (gx0 >> 1) + sxc * (gy0 >> 1); pco1 = (gx0 >> 1) + sxc * (gy1 >> 1);
+        own0.so = lx0 + RB_PX * ly0; own0.go = gx0 + sx * gy0; own0.gfx = gx0 + fxs * gy0; own0.flags = 0;
+        own1.so = lx0 + RB_PX * ly1; own1.go = gx0 + sx * gy1; own1.gfx = gx0 + fxs * gy1; own1.flags = 0;
+        of0[0] = rb3_flags(L, gx0, gy0); of0[1] = rb3_flags(L, gx0 + 1, gy0);
+        of1[0] = rb3_flags(L, gx0, gy1); of1[1] = rb3_flags(L, gx0 + 1, gy1);
     }
+    auto cell_of = [&](int m, int a) {
+        RbCell c = m ? own1 : own0;
+        c.so += a; c.go += a; c.gfx += a;
+        c.flags = m ? (a ? of1[1] : of1[0]) : (a ? of0[1] : of0[0]);
+        return c;
+    };
     // halo-2 frame: rows 0,1 and 18,19 (68 wide), columns 0,1,66,67 of rows 2..17: 336 cells, threads take tid and tid + 256
     int fso[2], fgo[2], fpc[2];
     for (int e = 0; e < 2; ++e) {
@@ -351,25 +359,54 @@ __global__ void __launch_bounds__(256) k_mac_rb3(MacLevel L, MacLevel Lc, MacBet
     }
     const long long fxz = L.fxs * (long long)L.n[1], fyz = L.sx * (long long)(L.n[1] + 1);
 
+    // plane loads run one step ahead: the values of plane p+1 travel in registers while plane p is relaxed
+    double2 pre_own[2]; double pre_fr[2];
+    auto fetch_plane = [&](int p) {
+        const int gz = rb_wrap(p, L.n[2], pz);
+        pre_own[0] = pre_own[1] = make_double2(0.0, 0.0); pre_fr[0] = pre_fr[1] = 0.0;
+        if (gz < 0 || p > z1 + 1) return;
+        const long long zc = L.sxy * (long long)gz, zcc = Lc.sxy * (long long)(gz >> 1);
+#pragma unroll
+        for (int m = 0; m < 2; ++m) {
+            double2 v = make_double2(0.0, 0.0);
+            if (!A.zero_in) v = *reinterpret_cast<const double2*>(A.in + zc + (m ? own1.go : own0.go));
+            if (A.crse) { const double cv = A.crse[zcc + (m ? pco1 : pco0)]; v.x += cv; v.y += cv; }
+            pre_own[m] = v;
+        }
+        for (int e = 0; e < 2; ++e) if (fso[e] >= 0 && fgo[e] >= 0) {
+            double v = 0.0;
+            if (!A.zero_in) v = A.in[zc + fgo[e]];
+            if (A.crse) v += A.crse[zcc + fpc[e]];
+            pre_fr[e] = v;
+        }
+    };
+    // so do the right-hand sides of the cells relaxed in the next step: reds of plane p (own pairs + ring), blacks of plane p-1
+    double rr0 = 0.0, rr1 = 0.0, rrr = 0.0, rk0 = 0.0, rk1 = 0.0;
+    auto fetch_rhs = [&](int p) {           // for the step that will load plane p: red plane p-1, black plane p-2
+        if (!CB) return;                    // variable coefficients: the registers are needed elsewhere (measured slower)
+        const int q = p - 1, r = p - 2;
+        const int gzq = rb_wrap(q, L.n[2], pz);
+        if (gzq >= 0 && q >= z0 - 1 && q <= z1) {
+            const long long zc = L.sxy * (long long)gzq;
+            rr0 = A.rhs[zc + own0.go + ((par0 + q) & 1)]; rr1 = A.rhs[zc + own1.go + ((par1 + q) & 1)];
+            if (rc.so >= 0 && (((rpar + q) & 1) == 0)) rrr = A.rhs[zc + rc.go];
+        }
+        if (r >= z0 && r < z1) {
+            const long long zc = L.sxy * (long long)r;
+            rk0 = A.rhs[zc + own0.go + 1 - ((par0 + r) & 1)]; rk1 = A.rhs[zc + own1.go + 1 - ((par1 + r) & 1)];
+        }
+    };
+    fetch_plane(z0 - 2);
     for (int p = z0 - 2; p <= z1 + 1; ++p) {
-        // ---- load plane p ----
+        const double cr0 = rr0, cr1 = rr1, crr = rrr, ck0 = rk0, ck1 = rk1;      // this step's right-hand sides
+        // ---- plane p: registers -> ring; start the loads of plane p+1 ----
         {
-            const int gz = rb_wrap(p, L.n[2], pz);
-            if (gz >= 0) {
-                double* P = ring + (p & 3) * RB_PS;
-                const long long zc = L.sxy * (long long)gz, zcc = Lc.sxy * (long long)(gz >> 1);
-                for (int m = 0; m < 2; ++m) {
-                    double2 v = make_double2(0.0, 0.0);
-                    if (!A.zero_in) v = *reinterpret_cast<const double2*>(A.in + zc + own[m][0].go);
-                    if (A.crse) { const double cv = A.crse[zcc + pco[m]]; v.x += cv; v.y += cv; }
-                    *reinterpret_cast<double2*>(P + own[m][0].so) = v;
-                }
-                for (int e = 0; e < 2; ++e) if (fso[e] >= 0) {
-                    double v = 0.0;
-                    if (fgo[e] >= 0) { if (!A.zero_in) v = A.in[zc + fgo[e]]; if (A.crse) v += A.crse[zcc + fpc[e]]; }
-                    P[fso[e]] = v;
-                }
-            }
+            double* P = ring + (p & 3) * RB_PS;
+            *reinterpret_cast<double2*>(P + own0.so) = pre_own[0];
+            *reinterpret_cast<double2*>(P + own1.so) = pre_own[1];
+            for (int e = 0; e < 2; ++e) if (fso[e] >= 0) P[fso[e]] = pre_fr[e];
+            fetch_plane(p + 1);
+            fetch_rhs(p + 1);
         }
         __syncthreads();
         // ---- red cells of plane p-1: own pairs + ring ----
@@ -381,14 +418,12 @@ __global__ void __launch_bounds__(256) k_mac_rb3(MacLevel L, MacLevel Lc, MacBet
                 const double* Pm = ring + ((q - 1) & 3) * RB_PS; const double* Pp = ring + ((q + 1) & 3) * RB_PS;
                 const int zfl = pz ? 0 : ((gz == 0 ? RBF_ZLO : 0) | (gz == L.n[2] - 1 ? RBF_ZHI : 0));
                 const long long zc = L.sxy * (long long)gz, zfx = fxz * gz, zfy = fyz * gz;
-                double nv[3]; int no[3] = {-1, -1, -1};
-                for (int m = 0; m < 2; ++m) {
-                    const RbCell& cl = own[m][(par[m] + q) & 1];
-                    nv[m] = rb3_update<CB>(L, B, P, Pm, Pp, cl, zfl, zc, zfx, zfy, A.rhs, off); no[m] = cl.so;
-                }
-                if (rc.so >= 0 && (((rpar + q) & 1) == 0)) { nv[2] = rb3_update<CB>(L, B, P, Pm, Pp, rc, zfl, zc, zfx, zfy, A.rhs, off); no[2] = rc.so; }
-                // reds only read blacks, so the in-place writes of other threads cannot be seen by this phase's reads
-                for (int m = 0; m < 3; ++m) if (no[m] >= 0) P[no[m]] = nv[m];
+                // reds only read blacks (and their own value), so the in-place writes of other threads cannot be seen here
+                const RbCell c0 = cell_of(0, (par0 + q) & 1), c1 = cell_of(1, (par1 + q) & 1);
+                const double n0 = rb3_update<CB>(L, B, P, Pm, Pp, c0, zfl, zc, zfx, zfy, CB ? cr0 : A.rhs[zc + c0.go], off);
+                const double n1 = rb3_update<CB>(L, B, P, Pm, Pp, c1, zfl, zc, zfx, zfy, CB ? cr1 : A.rhs[zc + c1.go], off);
+                P[c0.so] = n0; P[c1.so] = n1;
+                if (rc.so >= 0 && (((rpar + q) & 1) == 0)) P[rc.so] = rb3_update<CB>(L, B, P, Pm, Pp, rc, zfl, zc, zfx, zfy, CB ? crr : A.rhs[zc + rc.go], off);
             }
         }
         __syncthreads();
@@ -400,12 +435,14 @@ __global__ void __launch_bounds__(256) k_mac_rb3(MacLevel L, MacLevel Lc, MacBet
                 const double* Pm = ring + ((r - 1) & 3) * RB_PS; const double* Pp = ring + ((r + 1) & 3) * RB_PS;
                 const int zfl = pz ? 0 : ((r == 0 ? RBF_ZLO : 0) | (r == L.n[2] - 1 ? RBF_ZHI : 0));
                 const long long zc = L.sxy * (long long)r, zfx = fxz * r, zfy = fyz * r;
+#pragma unroll
                 for (int m = 0; m < 2; ++m) {
-                    const int a = 1 - ((par[m] + r) & 1);
-                    double2 v = *reinterpret_cast<const double2*>(P + own[m][0].so);
-                    const double nb = rb3_update<CB>(L, B, P, Pm, Pp, own[m][a], zfl, zc, zfx, zfy, A.rhs, off);
+                    const int a = 1 - (((m ? par1 : par0) + r) & 1);
+                    double2 v = *reinterpret_cast<const double2*>(P + (m ? own1.so : own0.so));
+                    const RbCell cb = cell_of(m, a);
+                    const double nb = rb3_update<CB>(L, B, P, Pm, Pp, cb, zfl, zc, zfx, zfy, CB ? (m ? ck1 : ck0) : A.rhs[zc + cb.go], off);
                     if (a) v.y = nb; else v.x = nb;
-                    const long long c = zc + own[m][0].go;
+                    const long long c = zc + (m ? own1.go : own0.go);
                     *reinterpret_cast<double2*>(A.out + c) = v;
                     if (A.add_to) { double2 t = *reinterpret_cast<double2*>(A.add_to + c); t.x += v.x; t.y += v.y; *reinterpret_cast<double2*>(A.add_to + c) = t; }
                 }
