@@ -16,11 +16,46 @@ from oracle.oracle import Oracle, TILED
 ROOT = nphelp.ROOT
 
 
-def _build(libpath, exe):
+def _build(libpath, exe, src="shim_driver.cpp"):
     libdir, libname = os.path.dirname(libpath), os.path.basename(libpath)[3:-3]
     subprocess.check_call(["g++", "-std=c++17", "-O1", "-I" + os.path.join(ROOT, "include"), "-I" + os.path.join(ROOT, "tests", "mock_amrex"),
-                           os.path.join(ROOT, "tests", "shim", "shim_driver.cpp"), "-o", exe, "-L" + libdir, "-l" + libname,
+                           os.path.join(ROOT, "tests", "shim", src), "-o", exe, "-L" + libdir, "-l" + libname,
                            "-Wl,-rpath," + libdir])
+
+
+def _run_mac_and_check(libpath, tmp_path, n):
+    """include/MacProjectorB200.H driven like incflo::compute_MAC_projected_velocities, against the MAC oracle."""
+    from oracle.mac import MacOracle, face_shapes
+    exe, out = str(tmp_path / "mac_shim_driver"), str(tmp_path / "mac_out.bin")
+    _build(libpath, exe, "mac_shim_driver.cpp")
+    subprocess.check_call([exe, str(n), out])
+    raw = np.fromfile(out, dtype=np.uint8)
+    hdr, body = raw[:8].view(np.int32), raw[8:].view(np.float64)
+    shapes = face_shapes((n, n, n))
+    u, pos = [], 0
+    for s in shapes:
+        cnt = int(np.prod(s)); u.append(body[pos:pos + cnt].reshape(s)); pos += cnt
+    phi = body[pos:].reshape(n, n, n)
+    prob = problems.mac_double_shear((n, n, n))
+    o = MacOracle((n, n, n))
+    o.set_beta(*prob["beta"]); o.set_umac(*prob["umac"])
+    so = o.project(1e-11, 1e-14)
+    l2 = lambda a, b: np.linalg.norm(a - b) / np.linalg.norm(b)
+    assert hdr[0] == n and hdr[1] == so.n_vcycles
+    for a, b in zip(u, o.get_umac()):
+        assert l2(a, b) < 1e-11
+    po = o.get_phi()
+    assert l2(phi - phi.mean(), po - po.mean()) < 1e-10
+
+
+def test_mac_shim_on_emulation(tmp_path):
+    nphelp.emu_lib()
+    _run_mac_and_check(nphelp.EMU_LIB, tmp_path, 16)
+
+
+@pytest.mark.gpu
+def test_mac_shim_on_gpu(tmp_path):
+    _run_mac_and_check(capi.LIB_PATH, tmp_path, 32)
 
 
 def _run_and_check(libpath, tmp_path, n, max_grid=None):
