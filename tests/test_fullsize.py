@@ -168,3 +168,54 @@ def test_mid_size_parity_with_oracle(name, ncell, kw):
     phi, po = P.getPhi().numpy_valid()[0], o.get_phi()
     assert l2(phi - phi.mean(), po - po.mean()) <= 1e-10
     o.close(); P.close()
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# MAC projection at full size: 512^3 cells, both coefficient paths.  Unlike the nodal projection
+# the MAC projection is EXACT: the discrete divergence of the result is zero to the solver tolerance, a second projection
+# has nothing left to do, and the operator is linear.
+# ---------------------------------------------------------------------------------------------------------------------
+def _mac_setup(workload):
+    import torch
+    from incflo_b200.mac_projector import MacProjector
+    torch.cuda.set_device(0)
+    ncell = (N, N, N)
+    hi = (1.0, 1.0, 1.0) if workload == "double_shear" else (0.5, 0.5, 0.5)
+    umac, beta, bclo, bchi = problems.mac_problem_torch(workload, ncell, hi, "cuda:0")
+    P = MacProjector(Geometry(ncell, (0, 0, 0), hi, [b == 0 for b in bclo]), lib=capi.load())
+    P.setDomainBC(bclo, bchi)
+    P.initProjector(LPInfo().setMaxCoarseningLevel(100), [Fab(b, 0) for b in beta])
+    return torch, P, umac, hi
+
+
+def _mac_div(torch, u, hi):
+    dx = [hi[d] / N for d in range(3)]
+    return ((u[0][0, :, :, 1:] - u[0][0, :, :, :-1]) / dx[0] + (u[1][0, :, 1:, :] - u[1][0, :, :-1, :]) / dx[1]
+            + (u[2][0, 1:, :, :] - u[2][0, :-1, :, :]) / dx[2])
+
+
+@pytest.mark.parametrize("workload,max_vc", [("double_shear", 12), ("rayleigh_taylor", 13)])
+def test_mac_fullsize_exact_projection(workload, max_vc):
+    torch, P, umac, hi = _mac_setup(workload)
+    u0 = [u.clone() for u in umac]
+    d0 = float(_mac_div(torch, umac, hi).abs().max())
+    P.setUMAC([Fab(u, 0) for u in umac])
+    st = P.project(RTOL, ATOL)
+    assert st.status == 0 and st.n_levels == 9 and st.n_vcycles <= max_vc
+    assert st.sigma_is_const == (1 if workload == "double_shear" else 0)
+    hist = [st.res_history[i] for i in range(st.n_vcycles)]
+    assert all(b < 0.2 * a for a, b in zip(hist, hist[1:]))                 # at least a factor 5 per V-cycle
+    d1 = float(_mac_div(torch, umac, hi).abs().max())
+    assert d1 <= 2e-11 * d0                                                  # exact discrete projection
+    # idempotent: the projected field needs no V-cycle and is returned unchanged
+    u1 = [u.clone() for u in umac]
+    st2 = P.project(RTOL, ATOL)
+    assert st2.n_vcycles == 0 and all(torch.equal(a, b) for a, b in zip(umac, u1))
+    # linear: P(2.5 u) = 2.5 P(u)
+    for u, s in zip(umac, u0):
+        u.copy_(s).mul_(2.5)
+    st3 = P.project(RTOL, ATOL)
+    assert st3.n_vcycles == st.n_vcycles
+    for a, b in zip(umac, u1):
+        assert float((a - 2.5 * b).norm() / b.norm()) < 1e-10
+    P.close()
