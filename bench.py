@@ -47,13 +47,13 @@ def read_peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def read_traffic(const_sigma):
+def read_traffic(const_sigma, key_const="k_gs2_const", key_var="k_gs2_var"):
     """ncu-measured DRAM bytes per launch of the dominant kernel, if a capture was summarised."""
     p = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     if os.path.exists(p):
         with open(p) as f:
             d = json.load(f)
-        return d.get("k_gs2_const" if const_sigma else "k_gs2_var")
+        return d.get(key_const if const_sigma else key_var)
     return None
 
 
@@ -354,7 +354,7 @@ def run_gpu(args):
 # + restriction (9) + interpolation (17), x 8/7 for the coarse levels, + level 0's sol += cor (24), residual, norm (8).
 # ---------------------------------------------------------------------------------------------------
 MAC_METRIC = "mac_projection_dof_per_s_per_vcycle"
-MAC_BYTES = {True: (8 + 8 * 24 + 24 + 9 + 17) * 8 // 7 + 24 + 24 + 8, False: (8 + 8 * 48 + 48 + 9 + 17) * 8 // 7 + 24 + 48 + 8}
+MAC_BYTES = {True: round((8 + 8 * 24 + 24 + 9 + 17) * 8 / 7) + 24 + 24 + 8, False: round((8 + 8 * 48 + 48 + 9 + 17) * 8 / 7) + 24 + 48 + 8}
 
 
 def mac_config(args, sample=None):
@@ -488,9 +488,10 @@ def run_gpu_mac(args):
     per_cell = 2 * (24 if const_beta else 48)            # one smooth = red + black sweep: cor r/w, rhs[, bx, by, bz] each
     avg_ms = ms_smooth / max(n_smooth, 1)
     achieved = per_cell * dof / (avg_ms * 1e-3) / 1e9 if avg_ms > 0 else 0.0
-    roof = {"bound": "hbm", "kernel": ("k_mac_gsrb<const beta> x 2 (red, black), level 0" if const_beta
-                                       else "k_mac_rb2<variable beta> (red + black in one pass), level 0"),
-            "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+    roof = {"bound": "hbm", "kernel": f"k_mac_rb3<{'const' if const_beta else 'variable'} beta> (red + black sweep of one smooth in one pass), level 0",
+            "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+            "traffic": read_traffic(const_beta, "k_mac_rb3_const", "k_mac_rb3_var"), "peak_source": peak_src,
+            "fused_pass_bytes_per_launch": (24 if const_beta else 48) * dof,
             "algorithmic_bytes_per_launch": per_cell * dof, "avg_launch_ms": avg_ms, "launches_timed": int(n_smooth),
             "share_of_step": ms_smooth / ms,
             "vcycle_algorithmic": {"bytes_per_dof": MAC_BYTES[const_beta],

@@ -207,10 +207,14 @@ def test_mac_fullsize_exact_projection(workload, max_vc):
     assert all(b < 0.2 * a for a, b in zip(hist, hist[1:]))                 # at least a factor 5 per V-cycle
     d1 = float(_mac_div(torch, umac, hi).abs().max())
     assert d1 <= 2e-11 * d0                                                  # exact discrete projection
-    # idempotent: the projected field needs no V-cycle and is returned unchanged
+    # idempotent: projecting the projected field again (its divergence is 1e-11 of the original, so the relative
+    # tolerance now refers to round-off) changes it by no more than that
     u1 = [u.clone() for u in umac]
     st2 = P.project(RTOL, ATOL)
-    assert st2.n_vcycles == 0 and all(torch.equal(a, b) for a, b in zip(umac, u1))
+    assert st2.status == 0
+    for a, b in zip(umac, u1):
+        assert float((a - b).norm() / b.norm()) < 1e-10
+    assert float(_mac_div(torch, umac, hi).abs().max()) <= 2e-11 * d0
     # linear: P(2.5 u) = 2.5 P(u)
     for u, s in zip(umac, u0):
         u.copy_(s).mul_(2.5)
