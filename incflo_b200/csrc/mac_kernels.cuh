@@ -258,7 +258,11 @@ __global__ void __launch_bounds__(256) k_mac_rb2(MacLevel L, MacLevel Lc, MacBet
 // and two 16-byte stores.
 // ------------------------------------------------------------------------------------------------
 enum { RBF_XLO = 1, RBF_XHI = 2, RBF_YLO = 4, RBF_YHI = 8, RBF_ZLO = 16, RBF_ZHI = 32 };
-struct RbCell { int so; int go; int gfx; int flags; };     // smem offset, in-plane cell offset, in-plane bx offset, RBF_*
+struct RbCell { int so; int go; int gfx; int flags; int dxm; };   // smem offset, in-plane cell offset, in-plane bx offset, RBF_*, offset of the x-lo neighbour
+// k_mac_rb3's ring planes keep the even and the odd columns of a row in separate halves, so the cells of one colour in a row
+// (and their x neighbours, which all have the other parity) are contiguous: no shared-memory bank conflicts in the sweeps
+#define RB3_SO(lx, ly) (((lx) >> 1) + ((lx) & 1) * (RB_PX / 2) + RB_PX * (ly))
+#define RB3_DXM(lx) (((lx) & 1) ? -(RB_PX / 2) : (RB_PX / 2 - 1))
 
 template <bool CB>
 __device__ __forceinline__ double rb3_update(const MacLevel& L, const MacBeta& B, const double* __restrict__ P, const double* __restrict__ Pm,
@@ -277,12 +281,13 @@ __device__ __forceinline__ double rb3_update(const MacLevel& L, const MacBeta& B
     const double gamma = L.dh[0] * (bxm + bxp) + L.dh[1] * (bym + byp) + L.dh[2] * (bzm + bzp);
     const double r = rhs_c - off;
     const int fl = cl.flags | zflags;
-    double xm = P[o - 1], xp = P[o + 1], ym = P[o - RB_PX], yp = P[o + RB_PX], zm = Pm[o], zp = Pp[o];
+    double xm = P[o + cl.dxm], xp = P[o + cl.dxm + 1], ym = P[o - RB_PX], yp = P[o + RB_PX], zm = Pm[o], zp = Pp[o];
+    const double xm0 = xm;
     double g_m_d = gamma;
     if (fl) {       // a Neumann / Dirichlet face next to the cell: ghost values from the boundary condition
         double delta = 0.0;
         if (fl & RBF_XLO) { xm = L.bclo[0] == MAC_NEU ? xc : L.dc0[0] * xc + L.dc1[0] * xp; delta += L.dh[0] * bxm * L.flo[0]; }
-        if (fl & RBF_XHI) { xp = L.bchi[0] == MAC_NEU ? xc : L.dc0[0] * xc + L.dc1[0] * P[o - 1]; delta += L.dh[0] * bxp * L.fhi[0]; }
+        if (fl & RBF_XHI) { xp = L.bchi[0] == MAC_NEU ? xc : L.dc0[0] * xc + L.dc1[0] * xm0; delta += L.dh[0] * bxp * L.fhi[0]; }
         if (fl & RBF_YLO) { ym = L.bclo[1] == MAC_NEU ? xc : L.dc0[1] * xc + L.dc1[1] * yp; delta += L.dh[1] * bym * L.flo[1]; }
         if (fl & RBF_YHI) { yp = L.bchi[1] == MAC_NEU ? xc : L.dc0[1] * xc + L.dc1[1] * P[o - RB_PX]; delta += L.dh[1] * byp * L.fhi[1]; }
         if (fl & RBF_ZLO) { zm = L.bclo[2] == MAC_NEU ? xc : L.dc0[2] * xc + L.dc1[2] * zp; delta += L.dh[2] * bzm * L.flo[2]; }
@@ -320,14 +325,14 @@ __global__ void __launch_bounds__(256) k_mac_rb3(MacLevel L, MacLevel Lc, MacBet
         const int ly0 = 2 + ty, gy0 = y0 + ty, ly1 = ly0 + 8, gy1 = gy0 + 8;
         par0 = (gx0 + gy0) & 1; par1 = (gx0 + gy1) & 1;
         pco0 = (gx0 >> 1) + sxc * (gy0 >> 1); pco1 = (gx0 >> 1) + sxc * (gy1 >> 1);
-        own0.so = lx0 + RB_PX * ly0; own0.go = gx0 + sx * gy0; own0.gfx = gx0 + fxs * gy0; own0.flags = 0;
-        own1.so = lx0 + RB_PX * ly1; own1.go = gx0 + sx * gy1; own1.gfx = gx0 + fxs * gy1; own1.flags = 0;
+        own0.so = RB3_SO(lx0, ly0); own0.dxm = RB3_DXM(lx0); own0.go = gx0 + sx * gy0; own0.gfx = gx0 + fxs * gy0; own0.flags = 0;
+        own1.so = RB3_SO(lx0, ly1); own1.dxm = RB3_DXM(lx0); own1.go = gx0 + sx * gy1; own1.gfx = gx0 + fxs * gy1; own1.flags = 0;
         of0[0] = rb3_flags(L, gx0, gy0); of0[1] = rb3_flags(L, gx0 + 1, gy0);
         of1[0] = rb3_flags(L, gx0, gy1); of1[1] = rb3_flags(L, gx0 + 1, gy1);
     }
     auto cell_of = [&](int m, int a) {
         RbCell c = m ? own1 : own0;
-        c.so += a; c.go += a; c.gfx += a;
+        c.so += a * (RB_PX / 2); c.go += a; c.gfx += a; c.dxm = a ? -(RB_PX / 2) : (RB_PX / 2 - 1);
         c.flags = m ? (a ? of1[1] : of1[0]) : (a ? of0[1] : of0[0]);
         return c;
     };
@@ -341,12 +346,12 @@ __global__ void __launch_bounds__(256) k_mac_rb3(MacLevel L, MacLevel Lc, MacBet
             if (f < 272) { const int rr = f / RB_PX; lx = f - rr * RB_PX; ly = rr < 2 ? rr : RB_PY - 4 + rr; }
             else { const int g = f - 272; ly = 2 + (g >> 2); const int cidx = g & 3; lx = cidx < 2 ? cidx : RB_PX - 4 + cidx; }
             const int gx = rb_wrap(x0 - 2 + lx, L.n[0], px), gy = rb_wrap(y0 - 2 + ly, L.n[1], py);
-            fso[e] = lx + RB_PX * ly;
+            fso[e] = RB3_SO(lx, ly);
             if (gx >= 0 && gy >= 0) { fgo[e] = gx + sx * gy; fpc[e] = (gx >> 1) + sxc * (gy >> 1); }
         }
     }
     // tile+1 ring: rows 1 and 18 (lx 1..66), columns 1 and 66 of rows 2..17: 164 cells, one per thread
-    RbCell rc; rc.so = -1; rc.go = -1; rc.gfx = 0; rc.flags = 0;
+    RbCell rc; rc.so = -1; rc.go = -1; rc.gfx = 0; rc.flags = 0; rc.dxm = 0;
     int rpar = 0;
     if (tid < 164) {
         int lx, ly;
@@ -355,7 +360,7 @@ __global__ void __launch_bounds__(256) k_mac_rb3(MacLevel L, MacLevel Lc, MacBet
         const int gxu = x0 - 2 + lx, gyu = y0 - 2 + ly;
         const int gx = rb_wrap(gxu, L.n[0], px), gy = rb_wrap(gyu, L.n[1], py);
         rpar = (gxu + gyu) & 1;
-        if (gx >= 0 && gy >= 0) { rc.so = lx + RB_PX * ly; rc.go = gx + sx * gy; rc.gfx = gx + fxs * gy; rc.flags = rb3_flags(L, gx, gy); }
+        if (gx >= 0 && gy >= 0) { rc.so = RB3_SO(lx, ly); rc.dxm = RB3_DXM(lx); rc.go = gx + sx * gy; rc.gfx = gx + fxs * gy; rc.flags = rb3_flags(L, gx, gy); }
     }
     const long long fxz = L.fxs * (long long)L.n[1], fyz = L.sx * (long long)(L.n[1] + 1);
 
@@ -402,8 +407,8 @@ __global__ void __launch_bounds__(256) k_mac_rb3(MacLevel L, MacLevel Lc, MacBet
         // ---- plane p: registers -> ring; start the loads of plane p+1 ----
         {
             double* P = ring + (p & 3) * RB_PS;
-            *reinterpret_cast<double2*>(P + own0.so) = pre_own[0];
-            *reinterpret_cast<double2*>(P + own1.so) = pre_own[1];
+            P[own0.so] = pre_own[0].x; P[own0.so + RB_PX / 2] = pre_own[0].y;
+            P[own1.so] = pre_own[1].x; P[own1.so + RB_PX / 2] = pre_own[1].y;
             for (int e = 0; e < 2; ++e) if (fso[e] >= 0) P[fso[e]] = pre_fr[e];
             fetch_plane(p + 1);
             fetch_rhs(p + 1);
@@ -438,7 +443,8 @@ __global__ void __launch_bounds__(256) k_mac_rb3(MacLevel L, MacLevel Lc, MacBet
 #pragma unroll
                 for (int m = 0; m < 2; ++m) {
                     const int a = 1 - (((m ? par1 : par0) + r) & 1);
-                    double2 v = *reinterpret_cast<const double2*>(P + (m ? own1.so : own0.so));
+                    const int so = m ? own1.so : own0.so;
+                    double2 v = make_double2(P[so], P[so + RB_PX / 2]);
                     const RbCell cb = cell_of(m, a);
                     const double nb = rb3_update<CB>(L, B, P, Pm, Pp, cb, zfl, zc, zfx, zfy, CB ? (m ? ck1 : ck0) : A.rhs[zc + cb.go], off);
                     if (a) v.y = nb; else v.x = nb;
