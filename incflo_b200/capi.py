@@ -63,7 +63,7 @@ class mp_options(C.Structure):
 # every symbol include/macproj.h declares
 MAC_SYMBOLS = ["mp_default_options", "mp_create", "mp_set_bc", "mp_update_beta", "mp_project", "mp_get_fluxes", "mp_copy_phi",
                "mp_destroy", "mp_num_levels", "mp_level_ncell", "mp_get_beta", "mp_apply", "mp_smooth", "mp_restrict",
-               "mp_interp_add", "mp_bottom_solve"]
+               "mp_interp_add", "mp_bottom_solve", "mp_update_beta_boxes", "mp_project_boxes", "mp_get_fluxes_boxes"]
 
 # every symbol include/nodalproj.h declares
 SYMBOLS = ["np_default_options", "np_create", "np_set_bc", "np_project", "np_apply_projection", "np_get_phi", "np_get_gradphi",
@@ -130,6 +130,10 @@ def load(path=None):
                              C.POINTER(np_stats)]
     L.mp_get_fluxes.argtypes = [C.c_void_p, C.POINTER(np_fab), C.POINTER(np_fab)]
     L.mp_copy_phi.argtypes = [C.c_void_p, C.POINTER(np_fab)]
+    L.mp_update_beta_boxes.argtypes = [C.c_void_p, C.c_int, C.POINTER(np_fab), C.POINTER(np_fab), C.POINTER(np_fab)]
+    L.mp_project_boxes.argtypes = [C.c_void_p, C.c_int, C.POINTER(np_fab), C.POINTER(np_fab), C.POINTER(np_fab), C.POINTER(np_fab),
+                                   C.c_double, C.c_double, C.c_void_p, C.POINTER(np_stats)]
+    L.mp_get_fluxes_boxes.argtypes = [C.c_void_p, C.c_int, C.POINTER(np_fab), C.POINTER(np_fab), C.POINTER(np_fab), C.POINTER(np_fab)]
     L.mp_destroy.argtypes = [C.c_void_p]
     L.mp_destroy.restype = None
     L.mp_num_levels.argtypes = [C.c_void_p]

@@ -27,6 +27,8 @@ struct MacSolver {
     double* bw[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     double* stage[4] = {nullptr, nullptr, nullptr, nullptr}; long long stage_n[4] = {0, 0, 0, 0};
     double* wrapbuf = nullptr; long long wrapbuf_n = 0;
+    std::vector<np_box> lbox;                            // the caller's boxes (one rank: they tile the domain)
+    double* mb_f[3] = {nullptr, nullptr, nullptr}; double* mb_phi = nullptr;   // several boxes: domain-shaped gather buffers
     std::vector<np_event_t> prof_ev; int prof_n = 0;     // profile_kernels: start/stop pairs around the level-0 smooths
     np_stream_t stream = 0;
     np_event_t ev[4] = {0, 0, 0, 0};
@@ -61,8 +63,27 @@ struct MacSolver {
     {
         if (np_rt::init()) return NP_ERR_NO_DEVICE;
         geom = *g; opt = *o;
-        if (nranks != 1 || my_rank != 0 || nboxes != 1 || owner[0] != 0) return NP_ERR_INVALID;
-        for (int d = 0; d < 3; ++d) if (boxes[0].lo[d] != 0 || boxes[0].hi[d] != g->ncell[d] - 1 || g->ncell[d] < 2) return NP_ERR_INVALID;
+        if (nranks != 1 || my_rank != 0 || nboxes < 1) return NP_ERR_INVALID;
+        for (int d = 0; d < 3; ++d) if (g->ncell[d] < 2) return NP_ERR_INVALID;
+        {   // the boxes must tile the domain: inside it, pairwise disjoint, volumes adding up (one box: the domain itself)
+            long long vol = 0;
+            lbox.assign(boxes, boxes + nboxes);
+            for (int b = 0; b < nboxes; ++b) {
+                if (owner[b] != 0) return NP_ERR_INVALID;
+                long long v = 1;
+                for (int d = 0; d < 3; ++d) {
+                    if (boxes[b].lo[d] < 0 || boxes[b].hi[d] >= g->ncell[d] || boxes[b].lo[d] > boxes[b].hi[d]) return NP_ERR_INVALID;
+                    v *= boxes[b].hi[d] - boxes[b].lo[d] + 1;
+                }
+                vol += v;
+                for (int a = 0; a < b; ++a) {
+                    bool ov = true;
+                    for (int d = 0; d < 3; ++d) if (boxes[a].hi[d] < boxes[b].lo[d] || boxes[b].hi[d] < boxes[a].lo[d]) ov = false;
+                    if (ov) return NP_ERR_INVALID;
+                }
+            }
+            if (vol != (long long)g->ncell[0] * g->ncell[1] * g->ncell[2]) return NP_ERR_INVALID;
+        }
         for (int d = 0; d < 3; ++d) bclo[d] = bchi[d] = g->periodic[d] ? NP_BC_PERIODIC : NP_BC_NEUMANN;
         int n[3] = {g->ncell[0], g->ncell[1], g->ncell[2]};
         double dxinv[3];
@@ -111,7 +132,7 @@ struct MacSolver {
         np_rt::stream_sync(stream);
         for (auto& L : lev) { double* a[] = {L.bx, L.by, L.bz, L.res, L.cor, L.rescor}; for (double* p : a) if (p) np_rt::dev_free(p); }
         lev.clear();
-        double* a[] = {wrapbuf, sol, rhs, part0, part1, scal, stage[0], stage[1], stage[2], stage[3], bw[0], bw[1], bw[2], bw[3], bw[4], bw[5]};
+        double* a[] = {mb_f[0], mb_f[1], mb_f[2], mb_phi, wrapbuf, sol, rhs, part0, part1, scal, stage[0], stage[1], stage[2], stage[3], bw[0], bw[1], bw[2], bw[3], bw[4], bw[5]};
         for (double* p : a) if (p) np_rt::dev_free(p);
         if (h_scal) np_rt::host_free(h_scal);
         if (bot_out) np_rt::dev_free(bot_out);
@@ -484,6 +505,86 @@ struct MacSolver {
         np_rt::stream_sync(stream);
         return np_rt::last_error() ? NP_ERR_CUDA : NP_OK;
     }
+    // ---- several boxes (amr.max_grid_size chops the level): the boxes' fabs are gathered into domain-shaped device fabs,
+    //      the projection runs on those as for one box, and the results are scattered back (faces shared by two boxes are
+    //      written to both) ----
+    int boxes_copy(bool to_domain, int nodal_dir, int nlocal, const np_fab* fabs, double* dom, int slot)
+    {
+        if (nlocal != (int)lbox.size()) return NP_ERR_INVALID;
+        const MacLevel& d0 = lev[0].d;
+        FabView dv; dv.p = dom; dv.ng = 0;
+        dv.sy = d0.n[0] + (nodal_dir == 0); dv.sz = dv.sy * (d0.n[1] + (nodal_dir == 1)); dv.sn = dv.sz * (d0.n[2] + (nodal_dir == 2));
+        const int zero3[3] = {0, 0, 0};
+        for (int b = 0; b < nlocal; ++b) {
+            const np_box& bx = lbox[b];
+            const np_fab& f = fabs[b];
+            if (!f.p || f.ncomp < 1) return NP_ERR_INVALID;
+            FabView bv; bv.p = f.p; bv.ng = f.ngrow;
+            bv.sy = bx.hi[0] - bx.lo[0] + 1 + (nodal_dir == 0) + 2 * f.ngrow;
+            bv.sz = bv.sy * (bx.hi[1] - bx.lo[1] + 1 + (nodal_dir == 1) + 2 * f.ngrow);
+            bv.sn = bv.sz * (bx.hi[2] - bx.lo[2] + 1 + (nodal_dir == 2) + 2 * f.ngrow);
+            bool staged = false;
+#ifndef NP_EMU
+            if (!np_rt::is_device_ptr(f.p)) {       // host fab: through the staging buffer (ghost cells survive the round trip)
+                double* dev = stage_get(slot, bv.sn);
+                if (!dev) return NP_ERR_CUDA;
+                np_rt::copy_async(dev, f.p, (size_t)bv.sn * sizeof(double), stream);
+                bv.p = dev; staged = true;
+            }
+#endif
+            BoxCopy a;
+            for (int d = 0; d < 3; ++d) {
+                a.rlo[d] = bx.lo[d]; a.rhi[d] = bx.hi[d] + (nodal_dir == d ? 1 : 0);
+                a.dorg[d] = to_domain ? zero3[d] : bx.lo[d]; a.sorg[d] = to_domain ? bx.lo[d] : zero3[d];
+                a.vlo[d] = a.vhi[d] = a.dlo[d] = a.dhi[d] = 0;
+            }
+            a.guard = 0;
+            const dim3 g((a.rhi[0] - a.rlo[0] + 32) / 32, (a.rhi[1] - a.rlo[1] + 8) / 8, a.rhi[2] - a.rlo[2] + 1);
+            if (to_domain) NP_LAUNCH(false, k_box_copy, g, blk(), 0, stream, dv, bv, a, 1);
+            else NP_LAUNCH(false, k_box_copy, g, blk(), 0, stream, bv, dv, a, 1);
+            if (staged && !to_domain) np_rt::copy_async(f.p, bv.p, (size_t)bv.sn * sizeof(double), stream);
+        }
+        return NP_OK;
+    }
+    int ensure_box_buffers()
+    {
+        const MacLevel& d0 = lev[0].d;
+        for (int d = 0; d < 3; ++d)
+            if (!mb_f[d] && alloc_d(&mb_f[d], (long long)(d0.n[0] + (d == 0)) * (d0.n[1] + (d == 1)) * (d0.n[2] + (d == 2)))) return NP_ERR_CUDA;
+        if (!mb_phi && alloc_d(&mb_phi, (long long)d0.n[0] * d0.n[1] * d0.n[2])) return NP_ERR_CUDA;
+        return NP_OK;
+    }
+    int update_beta_boxes(int nlocal, const np_fab* const b[3])
+    {
+        if (ensure_box_buffers()) return NP_ERR_CUDA;
+        np_fab dom[3];
+        for (int d = 0; d < 3; ++d) { const int rc = boxes_copy(true, d, nlocal, b[d], mb_f[d], d); if (rc) return rc; dom[d] = np_fab{mb_f[d], 0, 1}; }
+        return update_beta(dom);
+    }
+    int project_boxes(int nlocal, np_fab* const u[3], np_fab* phi, double rtol, double atol)
+    {
+        if (ensure_box_buffers()) return NP_ERR_CUDA;
+        np_fab dom[3], pd{mb_phi, 0, 1};
+        for (int d = 0; d < 3; ++d) { const int rc = boxes_copy(true, d, nlocal, u[d], mb_f[d], d); if (rc) return rc; dom[d] = np_fab{mb_f[d], 0, 1}; }
+        if (phi) { const int rc = boxes_copy(true, -1, nlocal, phi, mb_phi, 3); if (rc) return rc; }
+        const int rc = project(dom, phi ? &pd : nullptr, rtol, atol);
+        if (rc && !have_result) return rc;
+        for (int d = 0; d < 3; ++d) { const int r2 = boxes_copy(false, d, nlocal, u[d], mb_f[d], d); if (r2) return r2; }
+        if (phi) { const int r2 = boxes_copy(false, -1, nlocal, phi, mb_phi, 3); if (r2) return r2; }
+        np_rt::stream_sync(stream);
+        return np_rt::last_error() ? NP_ERR_CUDA : rc;
+    }
+    int get_fluxes_boxes(int nlocal, np_fab* const fl[3], const np_fab* phi)
+    {
+        if (ensure_box_buffers() || !phi) return NP_ERR_INVALID;
+        np_fab dom[3], pd{mb_phi, 0, 1};
+        for (int d = 0; d < 3; ++d) dom[d] = np_fab{mb_f[d], 0, 1};
+        int rc = boxes_copy(true, -1, nlocal, phi, mb_phi, 3);
+        if (!rc) rc = get_fluxes(dom, &pd);
+        for (int d = 0; d < 3 && !rc; ++d) rc = boxes_copy(false, d, nlocal, fl[d], mb_f[d], d);
+        np_rt::stream_sync(stream);
+        return rc;
+    }
     // cell fab of level l (host or device, any ghosts) <-> internal array
     int cell_in(int l, const np_fab& f, double* dst, int slot)
     {
@@ -538,6 +639,28 @@ int mp_project(mp_handle* h, np_fab umac[3], np_fab* mac_phi, double rtol, doubl
     return rc;
 }
 int mp_get_fluxes(mp_handle* h, np_fab flux[3], const np_fab* phi) { return h && flux ? h->S.get_fluxes(flux, phi) : NP_ERR_INVALID; }
+int mp_update_beta_boxes(mp_handle* h, int nlocal, const np_fab* bx, const np_fab* by, const np_fab* bz)
+{
+    if (!h || !bx || !by || !bz) return NP_ERR_INVALID;
+    const np_fab* const b[3] = {bx, by, bz};
+    return h->S.update_beta_boxes(nlocal, b);
+}
+int mp_project_boxes(mp_handle* h, int nlocal, np_fab* ux, np_fab* uy, np_fab* uz, np_fab* mac_phi, double rtol, double atol,
+                     void* cuda_stream, np_stats* out)
+{
+    if (!h || !ux || !uy || !uz) return NP_ERR_INVALID;
+    h->S.stream = (np_stream_t)cuda_stream;
+    np_fab* const u[3] = {ux, uy, uz};
+    const int rc = h->S.project_boxes(nlocal, u, mac_phi, rtol, atol);
+    if (out) *out = h->S.stats;
+    return rc;
+}
+int mp_get_fluxes_boxes(mp_handle* h, int nlocal, np_fab* fx, np_fab* fy, np_fab* fz, const np_fab* phi)
+{
+    if (!h || !fx || !fy || !fz) return NP_ERR_INVALID;
+    np_fab* const f[3] = {fx, fy, fz};
+    return h->S.get_fluxes_boxes(nlocal, f, phi);
+}
 int mp_copy_phi(mp_handle* h, np_fab* dst)
 {
     if (!h || !dst) return NP_ERR_INVALID;

@@ -39,11 +39,15 @@ def face_fab_from_array(arr, ngrow=0, like="numpy", device="cuda"):
 
 
 class MacProjector:
-    """Drop-in for amrex::MacProjector on one AMR level, one box."""
+    """Drop-in for amrex::MacProjector on one AMR level, one rank.
 
-    def __init__(self, geom, lib=None):
+    boxes: list of (lo, hi) cell boxes of the level's BoxArray (default: one box covering the domain).  With several
+    boxes every per-direction argument (beta[d], umac[d], fluxes[d]) and mac_phi is a LIST of Fabs in BoxArray order."""
+
+    def __init__(self, geom, lib=None, boxes=None):
         self.L = lib or capi.load()
         self.geom = geom
+        self.boxes = boxes or [((0, 0, 0), tuple(n - 1 for n in geom.ncell))]
         self.h = None
         self.umac = None
         self.stats = None
@@ -56,13 +60,15 @@ class MacProjector:
         info = lp_info or LPInfo()
         options.setdefault("max_coarsening_level", min(info.max_coarsening_level, 100))
         self.opt = capi.mac_default_options(self.L, **options)
-        bx = (capi.np_box * 1)()
-        for d in range(3):
-            bx[0].lo[d], bx[0].hi[d] = 0, self.geom.ncell[d] - 1
-        owner = (C.c_int * 1)(0)
+        nb = len(self.boxes)
+        bx = (capi.np_box * nb)()
+        for b, (lo, hi) in enumerate(self.boxes):
+            for d in range(3):
+                bx[b].lo[d], bx[b].hi[d] = int(lo[d]), int(hi[d])
+        owner = (C.c_int * nb)(*([0] * nb))
         h = C.c_void_p()
         g = self.geom.c()
-        capi.check(self.L, self.L.mp_create(C.byref(h), C.byref(g), 1, bx, owner, 0, 1, None, C.byref(self.opt)))
+        capi.check(self.L, self.L.mp_create(C.byref(h), C.byref(g), nb, bx, owner, 0, 1, None, C.byref(self.opt)))
         self.h = h
         if self._bc:
             self.setDomainBC(*self._bc)
@@ -84,7 +90,13 @@ class MacProjector:
         if self.h is not None:
             capi.check(self.L, self.L.mp_set_bc(self.h, (C.c_int * 3)(*[int(x) for x in lo]), (C.c_int * 3)(*[int(x) for x in hi])))
 
+    def _arr(self, fabs):
+        return (capi.np_fab * len(fabs))(*[f.c() for f in fabs])
+
     def updateBeta(self, beta):
+        if len(self.boxes) > 1:
+            capi.check(self.L, self.L.mp_update_beta_boxes(self.h, len(self.boxes), *[self._arr(beta[d]) for d in range(3)]))
+            return
         b = (capi.np_fab * 3)(*[f.c() for f in beta])
         capi.check(self.L, self.L.mp_update_beta(self.h, b))
 
@@ -98,17 +110,26 @@ class MacProjector:
             mac_phi, rtol, atol = args
         else:
             rtol, atol = args
-        u = (capi.np_fab * 3)(*[f.c() for f in self.umac])
         st = capi.np_stats()
-        phi = mac_phi.c() if mac_phi is not None else None
-        rc = self.L.mp_project(self.h, u, C.byref(phi) if phi is not None else None, rtol, atol,
-                               C.c_void_p(stream) if stream else None, C.byref(st))
+        if len(self.boxes) > 1:
+            rc = self.L.mp_project_boxes(self.h, len(self.boxes), *[self._arr(self.umac[d]) for d in range(3)],
+                                         self._arr(mac_phi) if mac_phi is not None else None, rtol, atol,
+                                         C.c_void_p(stream) if stream else None, C.byref(st))
+        else:
+            u = (capi.np_fab * 3)(*[f.c() for f in self.umac])
+            phi = mac_phi.c() if mac_phi is not None else None
+            rc = self.L.mp_project(self.h, u, C.byref(phi) if phi is not None else None, rtol, atol,
+                                   C.c_void_p(stream) if stream else None, C.byref(st))
         self.stats = st
         if rc and raise_on_fail:
             capi.check(self.L, rc)
         return st
 
     def getFluxes(self, fluxes, mac_phi):
+        if len(self.boxes) > 1:
+            capi.check(self.L, self.L.mp_get_fluxes_boxes(self.h, len(self.boxes), *[self._arr(fluxes[d]) for d in range(3)],
+                                                          self._arr(mac_phi)))
+            return
         f = (capi.np_fab * 3)(*[x.c() for x in fluxes])
         p = mac_phi.c()
         capi.check(self.L, self.L.mp_get_fluxes(self.h, f, C.byref(p)))

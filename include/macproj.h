@@ -17,8 +17,9 @@
  *   mp_destroy      <- ~MacProjector
  *
  * Fabs use AMReX's FArrayBox layout (include/nodalproj.h).  A face fab of direction d is nodal in d: valid index range
- * [lo, hi+1] in d, [lo, hi] in the other two.  Device or host pointers (host fabs are staged).  This round: one AMR level,
- * ONE box covering the domain on one rank (nranks == 1); the z-slab multi-GPU layer of the nodal solver is not wired in yet.
+ * [lo, hi+1] in d, [lo, hi] in the other two.  Device or host pointers (host fabs are staged).  This round: one AMR level
+ * on ONE rank (nranks == 1; any number of boxes tiling the domain, see the *_boxes entry points); the z-slab multi-GPU
+ * layer of the nodal solver is not wired in yet.
  * There is no CPU compute path: without a CUDA device mp_create fails with NP_ERR_NO_DEVICE.
  */
 #ifndef MACPROJ_H
@@ -67,6 +68,15 @@ int mp_project(mp_handle* h, np_fab umac[3], np_fab* mac_phi_or_null, double rto
 /* flux[d] = -b_d dphi/dx_d at face centres from a cell fab phi (homogeneous domain BCs as in the solve). */
 int mp_get_fluxes(mp_handle* h, np_fab flux[3], const np_fab* phi);
 int mp_copy_phi(mp_handle* h, np_fab* dst);          /* the last solution -> cell fab (valid cells) */
+
+/* Several boxes (amr.max_grid_size chops the level; the boxes given to mp_create must tile the domain, all on this rank):
+ * arrays of nlocal fabs per direction, in all_boxes order.  The boxes are gathered into domain-shaped device fabs, the
+ * one-box path runs on those, and the results are scattered back (a face shared by two boxes is written to both):
+ * bit-identical to the one-box calls, one extra streaming pass over every fab on either side. */
+int mp_update_beta_boxes(mp_handle* h, int nlocal, const np_fab* bx, const np_fab* by, const np_fab* bz);
+int mp_project_boxes(mp_handle* h, int nlocal, np_fab* ux, np_fab* uy, np_fab* uz, np_fab* mac_phi_or_null, double rtol, double atol,
+                     void* cuda_stream, np_stats* out);
+int mp_get_fluxes_boxes(mp_handle* h, int nlocal, np_fab* fx, np_fab* fy, np_fab* fz, const np_fab* phi);
 void mp_destroy(mp_handle* h);
 int mp_num_levels(mp_handle* h);
 int mp_level_ncell(mp_handle* h, int mglev, int ncell[3]);

@@ -23,12 +23,12 @@ def _build(libpath, exe, src="shim_driver.cpp"):
                            "-Wl,-rpath," + libdir])
 
 
-def _run_mac_and_check(libpath, tmp_path, n):
+def _run_mac_and_check(libpath, tmp_path, n, max_grid=None):
     """include/MacProjectorB200.H driven like incflo::compute_MAC_projected_velocities, against the MAC oracle."""
     from oracle.mac import MacOracle, face_shapes
     exe, out = str(tmp_path / "mac_shim_driver"), str(tmp_path / "mac_out.bin")
     _build(libpath, exe, "mac_shim_driver.cpp")
-    subprocess.check_call([exe, str(n), out])
+    subprocess.check_call([exe, str(n), out] + ([str(max_grid)] if max_grid else []))
     raw = np.fromfile(out, dtype=np.uint8)
     hdr, body = raw[:8].view(np.int32), raw[8:].view(np.float64)
     shapes = face_shapes((n, n, n))
@@ -48,14 +48,15 @@ def _run_mac_and_check(libpath, tmp_path, n):
     assert l2(phi - phi.mean(), po - po.mean()) < 1e-10
 
 
-def test_mac_shim_on_emulation(tmp_path):
+@pytest.mark.parametrize("max_grid", [None, 8])
+def test_mac_shim_on_emulation(tmp_path, max_grid):
     nphelp.emu_lib()
-    _run_mac_and_check(nphelp.EMU_LIB, tmp_path, 16)
+    _run_mac_and_check(nphelp.EMU_LIB, tmp_path, 16, max_grid)
 
 
 @pytest.mark.gpu
 def test_mac_shim_on_gpu(tmp_path):
-    _run_mac_and_check(capi.LIB_PATH, tmp_path, 32)
+    _run_mac_and_check(capi.LIB_PATH, tmp_path, 32, 16)
 
 
 def _run_and_check(libpath, tmp_path, n, max_grid=None):
