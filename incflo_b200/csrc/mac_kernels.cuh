@@ -412,6 +412,18 @@ __global__ void __launch_bounds__(256) k_mac_rb3(MacLevel L, MacLevel Lc, MacBet
             for (int e = 0; e < 2; ++e) if (fso[e] >= 0) P[fso[e]] = pre_fr[e];
             fetch_plane(p + 1);
             fetch_rhs(p + 1);
+            if (!CB) {      // variable coefficients: pull the lines the next step's red sweep (plane p) reads into L1 now; the black
+                            // sweep of that plane, one step later, finds them there
+                const int gzn = rb_wrap(p, L.n[2], pz);
+                if (gzn >= 0 && p <= z1) {
+                    const long long zc = L.sxy * (long long)gzn, zfx = fxz * gzn, zfy = fyz * gzn;
+                    np_prefetch_l1(B.bx + zfx + own0.gfx); np_prefetch_l1(B.bx + zfx + own1.gfx);
+                    np_prefetch_l1(B.by + zfy + own0.go); np_prefetch_l1(B.by + zfy + own0.go + L.sx);
+                    np_prefetch_l1(B.by + zfy + own1.go); np_prefetch_l1(B.by + zfy + own1.go + L.sx);
+                    np_prefetch_l1(B.bz + zc + L.sxy + own0.go); np_prefetch_l1(B.bz + zc + L.sxy + own1.go);
+                    np_prefetch_l1(A.rhs + zc + own0.go); np_prefetch_l1(A.rhs + zc + own1.go);
+                }
+            }
         }
         __syncthreads();
         // ---- red cells of plane p-1: own pairs + ring ----
