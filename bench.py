@@ -357,7 +357,7 @@ MAC_METRIC = "mac_projection_dof_per_s_per_vcycle"
 MAC_BYTES = {True: round((8 + 8 * 24 + 24 + 9 + 17) * 8 / 7) + 24 + 24 + 8, False: round((8 + 8 * 48 + 48 + 9 + 17) * 8 / 7) + 24 + 48 + 8}
 
 
-def mac_config(args, sample=None):
+def mac_config(args, sample=None, G=1):
     n = args.ncell
     if args.workload == "rayleigh_taylor":
         wl = (f"MAC projection, synthetic {n}^3 cells, periodic x/y, walls (Neumann) in z, beta = 1/rho on faces with the "
@@ -365,7 +365,9 @@ def mac_config(args, sample=None):
     else:
         wl = (f"MAC projection, synthetic {n}^3 cells, periodic, constant density (beta = 1), double_shear_layer + z-wave + "
               f"perturbation sampled on faces, rtol {RTOL:g} atol {ATOL:g}")
-    c = {"workload": wl, "ncell_per_gpu": [n, n, n], "boxes": f"one {n}^3 box",
+    if G > 1:
+        wl += f"; weak scaling: {n}x{n}x{n * G} domain in {G} z-slabs, one per GPU (halo planes, norms and coarse-level gather over NCCL)"
+    c = {"workload": wl, "ncell_per_gpu": [n, n, n], "boxes": f"one {n}^3 box per GPU",
          "l2": "inputs (>= 1 GB per array at 512^3) exceed the 126 MB L2; no explicit flush"}
     if sample:
         c["cpu_sample"] = sample
@@ -378,7 +380,7 @@ def cpu_mac_projection(n, workload, reps):
     from oracle.mac import MacOracle
     cores = os.cpu_count() or 1
     ncell = (n, n, n)
-    hi = (1.0, 1.0, 1.0) if workload == "double_shear" else (0.5, 0.5, 0.5)
+    hi = (1.0, 1.0, 1.0)
     prob = problems.MAC_PROBLEMS[workload](ncell, prob_hi=hi)
     total, vc = 0.0, 0
     for _ in range(reps):
@@ -409,38 +411,63 @@ def run_reference_mac(args):
 
 
 def run_gpu_mac(args):
+    import ctypes as C
     import torch
+    import torch.distributed as dist
     from incflo_b200 import capi, problems
     from incflo_b200.mac_projector import MacProjector
     from incflo_b200.projector import Fab, Geometry, LPInfo
-    if int(os.environ.get("WORLD_SIZE", "1")) > 1:
-        raise SystemExit("bench.py --path mac: one GPU this round (the z-slab layer is not wired into the MAC solver yet)")
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; incflo_b200 has no CPU fallback")
-    torch.cuda.set_device(0)
-    dev = "cuda:0"
-    n = args.ncell
-    ncell = (n, n, n)
-    hi = (1.0, 1.0, 1.0) if args.workload == "double_shear" else (0.5, 0.5, 0.5)
-    umac0, beta, bclo, bchi = problems.mac_problem_torch(args.workload, ncell, hi, dev)
+    torch.cuda.set_device(local)
+    dev = f"cuda:{local}"
+    L = capi.load()
+    comm = None
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device(dev))
+        idbuf = torch.zeros(128, dtype=torch.uint8)
+        if rank == 0:
+            raw = (C.c_ubyte * 128)()
+            capi.check(L, L.np_nccl_unique_id(raw))
+            idbuf = torch.tensor(list(raw), dtype=torch.uint8)
+        idd = idbuf.to(dev)
+        dist.broadcast(idd, 0)
+        raw = (C.c_ubyte * 128)(*idd.cpu().tolist())
+        cptr = C.c_void_p()
+        capi.check(L, L.np_nccl_comm_create(C.byref(cptr), raw, rank, world))
+        comm = cptr.value
+    n, G = args.ncell, world
+    ncell = (n, n, n * G)                        # weak scaling: one n^3 slab per GPU, stacked in z
+    hi = (1.0, 1.0, float(G))
+    umac0, beta, bclo, bchi = problems.mac_problem_torch(args.workload, ncell, hi, dev, koff=rank * n, nz_local=n)
     umac = [Fab(u.clone(), 0) for u in umac0]
-    P = MacProjector(Geometry(ncell, (0, 0, 0), hi, [b == 0 for b in bclo]), lib=capi.load())
+    P = MacProjector(Geometry(ncell, (0, 0, 0), hi, [b == 0 for b in bclo]), lib=L, rank=rank, nranks=world, nccl_comm=comm)
     P.setDomainBC(bclo, bchi)
     P.initProjector(LPInfo().setMaxCoarseningLevel(100), [Fab(b, 0) for b in beta], profile_kernels=1, verbose=args.verbose)
     P.setUMAC(umac)
     stream = torch.cuda.current_stream().cuda_stream
-    dof = n ** 3
+    dof = n ** 3 * G
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
 
     def step():
         for f, u0 in zip(umac, umac0):
             f.data.copy_(u0)
         return P.project(RTOL, ATOL, stream=stream)
 
-    clocks = ClockSampler(0)
-    clocks.start()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
     for _ in range(args.warmup):
         step()
-    torch.cuda.synchronize()
+    barrier()
     clocks.mark()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
@@ -452,9 +479,13 @@ def run_gpu_mac(args):
         ms_smooth += st.ms_smooth0; n_smooth += st.n_smooth0; ms_solve += st.ms_solve
         hist = [st.res_history[i] / max(st.rhs_norm0, 1e-300) for i in range(st.n_vcycles)]
     e1.record()
-    torch.cuda.synchronize()
+    barrier()
     ms = e0.elapsed_time(e1)
-    clk = clocks.stop()
+    clk = clocks.stop() if rank == 0 else None
+    tmax = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    ms = float(tmax.item())
     const_beta = bool(st.sigma_is_const)
 
     # e2e: host (pinned) face fabs through the same call; umac H2D + D2H every step, beta H2D through updateBeta, phi D2H
@@ -472,46 +503,62 @@ def run_gpu_mac(args):
         for it in range(1 + args.e2e_steps):
             for f, u0 in zip(hu, hu0):
                 f.data.copy_(u0)
-            torch.cuda.synchronize()
+            barrier()
             a.record()
             P.updateBeta(hb)
             st2 = P.project(RTOL, ATOL, stream=stream)
             P.copyPhi(hphi)
             b.record()
-            torch.cuda.synchronize()
+            barrier()
             if it >= 1:
-                tot_ms += a.elapsed_time(b); tot_vc += st2.n_vcycles
+                tm = torch.tensor([a.elapsed_time(b)], dtype=torch.float64, device=dev)
+                if world > 1:
+                    dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+                tot_ms += float(tm.item()); tot_vc += st2.n_vcycles
         e2e = {"value": dof * tot_vc / (tot_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                "steps": args.e2e_steps, "ms_per_step": tot_ms / args.e2e_steps}
 
+    if rank != 0:
+        P.close()
+        if comm:
+            L.np_nccl_comm_destroy(C.c_void_p(comm))
+        dist.destroy_process_group()
+        return
+    dof_gpu = n ** 3                              # roofline figures are per GPU
     peak, peak_src = read_peaks()
     per_cell = 2 * (24 if const_beta else 48)            # one smooth = red + black sweep: cor r/w, rhs[, bx, by, bz] each
     avg_ms = ms_smooth / max(n_smooth, 1)
-    achieved = per_cell * dof / (avg_ms * 1e-3) / 1e9 if avg_ms > 0 else 0.0
-    roof = {"bound": "hbm", "kernel": f"k_mac_rb3<{'const' if const_beta else 'variable'} beta> (red + black sweep of one smooth in one pass), level 0",
+    achieved = per_cell * dof_gpu / (avg_ms * 1e-3) / 1e9 if avg_ms > 0 else 0.0
+    kname = (f"k_mac_rb3<{'const' if const_beta else 'variable'} beta> (red + black sweep of one smooth in one pass), level 0" if world == 1 else
+             f"k_mac_gsrb<{'const' if const_beta else 'variable'} beta> x 2 with a halo-plane exchange before each colour (one smooth of a slab), level 0")
+    roof = {"bound": "hbm", "kernel": kname,
             "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
             "traffic": read_traffic(const_beta, "k_mac_rb3_const", "k_mac_rb3_var"), "peak_source": peak_src,
-            "fused_pass_bytes_per_launch": (24 if const_beta else 48) * dof,
-            "frac_fused_pass": (24 if const_beta else 48) * dof / (avg_ms * 1e-3) / 1e9 / peak if avg_ms > 0 else 0.0,
+            "fused_pass_bytes_per_launch": (24 if const_beta else 48) * dof_gpu,
+            "frac_fused_pass": (24 if const_beta else 48) * dof_gpu / (avg_ms * 1e-3) / 1e9 / peak if avg_ms > 0 else 0.0,
             "note": "achieved / frac use the SURVEY 8(d) accounting (every colour sweep of the reference schedule is a pass); the kernel "
                     "does both sweeps in one pass, so frac_fused_pass (its compulsory bytes / time / peak) is the figure that says how far "
                     "the kernel itself is from the HBM roofline",
-            "algorithmic_bytes_per_launch": per_cell * dof, "avg_launch_ms": avg_ms, "launches_timed": int(n_smooth),
+            "algorithmic_bytes_per_launch": per_cell * dof_gpu, "avg_launch_ms": avg_ms, "launches_timed": int(n_smooth),
             "share_of_step": ms_smooth / ms,
             "vcycle_algorithmic": {"bytes_per_dof": MAC_BYTES[const_beta],
-                                   "achieved_gbs": MAC_BYTES[const_beta] * dof * vcycles / (ms_solve * 1e-3) / 1e9}}
+                                   "achieved_gbs": MAC_BYTES[const_beta] * dof_gpu * vcycles / (ms_solve * 1e-3) / 1e9}}
     roof["vcycle_algorithmic"]["frac"] = roof["vcycle_algorithmic"]["achieved_gbs"] / peak
-    line = {"metric": MAC_METRIC, "value": dof * vcycles / (ms * 1e-3), "unit": UNIT, "n_gpus": 1, "steps": args.steps,
+    line = {"metric": MAC_METRIC, "value": dof * vcycles / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f64", "data": "synthetic", "config": mac_config(args), "vcycles_per_step": vcycles / args.steps,
+            "dtype": "f64", "data": "synthetic", "config": mac_config(args, G=world), "vcycles_per_step": vcycles / args.steps,
             "mg_levels": st.n_levels, "ms_per_vcycle": ms / vcycles, "ms_solve_per_vcycle": ms_solve / vcycles,
             "rel_res_history": hist, "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof}
-    if not args.no_cpu:
+    if world == 1 and not args.no_cpu:
         r = cpu_mac_projection(args.cpu_ncell, args.workload, 1)
         line["cpu_baseline"] = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"],
                                 "vcycles": r["vcycles"]}
     print(json.dumps(line), flush=True)
     P.close()
+    if world > 1:
+        if comm:
+            L.np_nccl_comm_destroy(C.c_void_p(comm))
+        dist.destroy_process_group()
 
 
 def main():

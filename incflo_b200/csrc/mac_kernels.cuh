@@ -10,7 +10,8 @@
 #pragma once
 #include "np_kernels.cuh"
 
-enum { MAC_PER = 0, MAC_DIR = 1, MAC_NEU = 2 };
+enum { MAC_PER = 0, MAC_DIR = 1, MAC_NEU = 2, MAC_REMOTE = 3 };   // REMOTE: a z face shared with the neighbouring rank's slab:
+                                                                  // the neighbour value is in the ghost plane the halo exchange filled
 
 struct MacLevel {
     int n[3];
@@ -21,6 +22,8 @@ struct MacLevel {
     double dc0[3], dc1[3];        // Dirichlet ghost = dc0*phi0 + dc1*phi1 (mllinop_apply_bc, maxorder 3: -2, 1/3)
     double flo[3], fhi[3];        // coefficient of the first interior cell in its ghost (smoother's boundary factors)
     int const_beta; double beta0;
+    int koff;                     // global z index of local plane 0 (colour parity of a slab); 0 on one rank / replicated levels
+    int kcoff;                    // plane of the next coarser level's array that holds the parent of local plane 0
 };
 struct MacBeta { const double *bx, *by, *bz; };
 
@@ -36,7 +39,7 @@ __host__ __device__ __forceinline__ long long mac_fz(const MacLevel& L, int i, i
 __device__ __forceinline__ double mac_nb_lo(const MacLevel& L, const double* __restrict__ x, long long c, double xc, int d, int idx, long long st,
                                             const double* __restrict__ xw)
 {
-    if (idx > 0) return x[c - st];
+    if (idx > 0 || L.bclo[d] == MAC_REMOTE) return x[c - st];
     if (L.bclo[d] == MAC_PER) return xw[c + st * (L.n[d] - 1)];
     if (L.bclo[d] == MAC_NEU) return xc;
     return L.dc0[d] * xc + L.dc1[d] * x[c + st];
@@ -44,7 +47,7 @@ __device__ __forceinline__ double mac_nb_lo(const MacLevel& L, const double* __r
 __device__ __forceinline__ double mac_nb_hi(const MacLevel& L, const double* __restrict__ x, long long c, double xc, int d, int idx, long long st,
                                             const double* __restrict__ xw)
 {
-    if (idx < L.n[d] - 1) return x[c + st];
+    if (idx < L.n[d] - 1 || L.bchi[d] == MAC_REMOTE) return x[c + st];
     if (L.bchi[d] == MAC_PER) return xw[c - st * (L.n[d] - 1)];
     if (L.bchi[d] == MAC_NEU) return xc;
     return L.dc0[d] * xc + L.dc1[d] * x[c - st];
@@ -78,7 +81,7 @@ __global__ void __launch_bounds__(256) k_mac_gsrb(MacLevel L, MacBeta B, double*
     const int j = blockIdx.y * blockDim.y + threadIdx.y;
     const int k = blockIdx.z;
     if (i0 >= L.n[0] || j >= L.n[1]) return;
-    const int a = (j + k + colour) & 1;
+    const int a = (j + k + L.koff + colour) & 1;
     const int i = i0 + a;
     const long long c0 = mac_c(L, i0, j, k);
     const bool pair = i0 + 1 < L.n[0];
@@ -605,7 +608,7 @@ __global__ void __launch_bounds__(256) k_mac_interp_add(MacLevel Lf, MacLevel Lc
     const int j = blockIdx.y * blockDim.y + threadIdx.y;
     const int k = blockIdx.z;
     if (ic >= Lc.n[0] || j >= Lf.n[1]) return;
-    const double v = crse[mac_c(Lc, ic, j >> 1, k >> 1)];
+    const double v = crse[mac_c(Lc, ic, j >> 1, (k >> 1) + Lf.kcoff)];
     double2* p = reinterpret_cast<double2*>(fine + mac_c(Lf, 2 * ic, j, k));
     double2 f = *p; f.x += v; f.y += v; *p = f;
 }

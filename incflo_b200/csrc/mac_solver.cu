@@ -11,7 +11,9 @@
 struct MacLev {
     MacLevel d{};
     double *bx = nullptr, *by = nullptr, *bz = nullptr;
-    double *res = nullptr, *cor = nullptr, *rescor = nullptr;
+    double *res = nullptr, *cor = nullptr, *rescor = nullptr;   // every cell array has one spare plane below and above (ghost planes
+                                                                 // of a slab: k = -1 and k = n2)
+    bool replicated = false;      // multi-GPU: this level holds the whole domain on every rank
     MacBeta beta() const { return MacBeta{bx, by, bz}; }
 };
 
@@ -19,6 +21,9 @@ struct MacSolver {
     mp_options opt{};
     np_geom geom{};
     int bclo[3] = {0, 0, 0}, bchi[3] = {0, 0, 0};
+    NpComm comm;                  // z-slab sharding: halo planes, reductions, the gather onto the replicated coarse levels
+    int agg_lev = -1;             // first replicated level, -1: none (one rank)
+    double *agg_send = nullptr, *agg_recv = nullptr;
     std::vector<MacLev> lev;
     double *sol = nullptr, *rhs = nullptr;
     double *part0 = nullptr, *part1 = nullptr; long long npart = 0;
@@ -45,6 +50,33 @@ struct MacSolver {
     static long long nblk(dim3 g) { return (long long)g.x * g.y * g.z; }
     static int alloc_d(double** p, long long n) { void* q = nullptr; if (np_rt::dev_malloc(&q, (size_t)n * sizeof(double))) return 1; *p = (double*)q; return 0; }
     void zero(double* p, long long n) { np_rt::memset_async(p, 0, (size_t)n * sizeof(double), stream); }
+    // cell array of a level with one ghost plane on either side in z; the returned pointer is plane 0
+    int alloc_cell(double** p, const MacLevel& d)
+    {
+        double* q = nullptr;
+        if (alloc_d(&q, d.ntot + 2 * d.sxy)) return 1;
+        np_rt::memset_async(q, 0, (size_t)(d.ntot + 2 * d.sxy) * sizeof(double), stream);
+        *p = q + d.sxy;
+        return 0;
+    }
+    static void free_cell(double* p, const MacLevel& d) { if (p) np_rt::dev_free(p - d.sxy); }
+    bool sharded(int l) const { return comm.nranks > 1 && !lev[l].replicated; }
+    void z_neighbours(int& lo, int& hi) const
+    {
+        const int r = comm.rank, R = comm.nranks;
+        const bool per = bclo[2] == NP_BC_PERIODIC;
+        lo = r > 0 ? r - 1 : (per ? R - 1 : -1);
+        hi = r < R - 1 ? r + 1 : (per ? 0 : -1);
+    }
+    // ghost planes of a cell array of a sharded level: my plane 0 -> the lower rank's plane n2, my plane n2-1 -> the upper rank's -1
+    void halo(int l, double* x)
+    {
+        if (!sharded(l)) return;
+        const MacLevel& d = lev[l].d;
+        int lo, hi; z_neighbours(lo, hi);
+        if (comm.sendrecv(comm.ctx, x, d.sxy, x - d.sxy, d.sxy, x + d.sxy * (long long)(d.n[2] - 1), d.sxy, x + d.sxy * (long long)d.n[2], d.sxy,
+                          lo, hi, (void*)stream)) err = NP_ERR_NCCL;
+    }
 
     void setup_bc()
     {
@@ -52,20 +84,39 @@ struct MacSolver {
         for (int d = 0; d < 3; ++d) if (bclo[d] == NP_BC_DIRICHLET || bchi[d] == NP_BC_DIRICHLET) singular = false;
         for (auto& L : lev) for (int d = 0; d < 3; ++d) {
             L.d.bclo[d] = bclo[d]; L.d.bchi[d] = bchi[d];
+            if (d == 2 && comm.nranks > 1 && !L.replicated) {      // slab faces shared with a neighbouring rank (periodic z: all of them)
+                const bool per = bclo[2] == NP_BC_PERIODIC;
+                if (per || comm.rank > 0) L.d.bclo[2] = MAC_REMOTE;
+                if (per || comm.rank < comm.nranks - 1) L.d.bchi[2] = MAC_REMOTE;
+            }
             const bool hi_order = std::min(L.d.n[d] + 1, opt.maxorder) >= 3;     // mllinop_apply_bc: NX = min(blen+1, maxorder)
             L.d.dc0[d] = hi_order ? -2.0 : -1.0; L.d.dc1[d] = hi_order ? 1.0 / 3.0 : 0.0;
-            auto fac = [&](int t) { return t == NP_BC_PERIODIC ? 0.0 : t == NP_BC_NEUMANN ? 1.0 : L.d.dc0[d]; };
-            L.d.flo[d] = fac(bclo[d]); L.d.fhi[d] = fac(bchi[d]);
+            auto fac = [&](int t) { return (t == NP_BC_PERIODIC || t == MAC_REMOTE) ? 0.0 : t == NP_BC_NEUMANN ? 1.0 : L.d.dc0[d]; };
+            L.d.flo[d] = fac(L.d.bclo[d]); L.d.fhi[d] = fac(L.d.bchi[d]);
         }
     }
 
-    int create(const np_geom* g, int nboxes, const np_box* boxes, const int* owner, int my_rank, int nranks, const mp_options* o)
+    int create(const np_geom* g, int nboxes, const np_box* boxes, const int* owner, int my_rank, int nranks, const NpComm& c, const mp_options* o)
     {
         if (np_rt::init()) return NP_ERR_NO_DEVICE;
-        geom = *g; opt = *o;
-        if (nranks != 1 || my_rank != 0 || nboxes < 1) return NP_ERR_INVALID;
+        geom = *g; opt = *o; comm = c; comm.rank = my_rank; comm.nranks = nranks;
+        if (nranks < 1 || my_rank < 0 || my_rank >= nranks || nboxes < 1) return NP_ERR_INVALID;
         for (int d = 0; d < 3; ++d) if (g->ncell[d] < 2) return NP_ERR_INVALID;
-        {   // the boxes must tile the domain: inside it, pairwise disjoint, volumes adding up (one box: the domain itself)
+        int nloc[3] = {g->ncell[0], g->ncell[1], g->ncell[2]};
+        int koff = 0;
+        if (nranks > 1) {
+            // one box per rank: equal z-slabs ordered by rank (the nodal solver's layout)
+            const int nzl = g->ncell[2] / nranks;
+            if (nboxes != nranks || nzl * nranks != g->ncell[2] || (nzl & 1)) return NP_ERR_INVALID;
+            for (int r = 0; r < nranks; ++r) {
+                const np_box& b = boxes[r];
+                if (owner[r] != r || b.lo[0] != 0 || b.lo[1] != 0 || b.hi[0] != g->ncell[0] - 1 || b.hi[1] != g->ncell[1] - 1
+                    || b.lo[2] != r * nzl || b.hi[2] != (r + 1) * nzl - 1) return NP_ERR_INVALID;
+            }
+            nloc[2] = nzl; koff = my_rank * nzl;
+            np_box mine = boxes[my_rank]; mine.lo[2] = 0; mine.hi[2] = nzl - 1;
+            lbox.assign(1, mine);
+        } else {   // one rank: the boxes must tile the domain: inside it, pairwise disjoint, volumes adding up
             long long vol = 0;
             lbox.assign(boxes, boxes + nboxes);
             for (int b = 0; b < nboxes; ++b) {
@@ -85,34 +136,53 @@ struct MacSolver {
             if (vol != (long long)g->ncell[0] * g->ncell[1] * g->ncell[2]) return NP_ERR_INVALID;
         }
         for (int d = 0; d < 3; ++d) bclo[d] = bchi[d] = g->periodic[d] ? NP_BC_PERIODIC : NP_BC_NEUMANN;
-        int n[3] = {g->ncell[0], g->ncell[1], g->ncell[2]};
+        // ---- MG levels (MLLinOp::defineGrids on the GLOBAL box: coarsen by 2 while it stays coarsenable, min width 2).  A slab is
+        //      coarsened locally while it keeps at least agg_min_local_nz planes; below that the level is replicated on every
+        //      rank (one all-gather on the way down, nothing on the way up), so the hierarchy is the one-box hierarchy ----
+        int n[3] = {nloc[0], nloc[1], nloc[2]};
+        int nglob2 = g->ncell[2];
         double dxinv[3];
         for (int d = 0; d < 3; ++d) dxinv[d] = g->ncell[d] / (g->prob_hi[d] - g->prob_lo[d]);
-        for (;;) {      // MLLinOp::defineGrids: coarsen by 2 while the box stays coarsenable (min width 2)
+        bool replicated = false;
+        int ko = koff;
+        for (;;) {
             MacLev L;
             for (int d = 0; d < 3; ++d) { L.d.n[d] = n[d]; L.d.dxinv[d] = dxinv[d]; L.d.dh[d] = dxinv[d] * dxinv[d]; }
             L.d.sx = (n[0] + 1) & ~1LL; L.d.sxy = L.d.sx * n[1]; L.d.ntot = L.d.sxy * n[2] + 2;
             L.d.fxs = (n[0] + 2) & ~1LL;
-            L.d.const_beta = 0; L.d.beta0 = 1.0;
+            L.d.const_beta = 0; L.d.beta0 = 1.0; L.d.koff = ko; L.d.kcoff = 0;
+            L.replicated = replicated;
             lev.push_back(L);
             if ((int)lev.size() > opt.max_coarsening_level) break;
+            const int gn[3] = {n[0], n[1], replicated || nranks == 1 ? n[2] : nglob2};
             bool ok = true;
-            for (int d = 0; d < 3; ++d) if (n[d] % 2 || n[d] < 4) ok = false;
+            for (int d = 0; d < 3; ++d) if (gn[d] % 2 || gn[d] < 4) ok = false;
             if (!ok) break;
-            for (int d = 0; d < 3; ++d) { n[d] /= 2; dxinv[d] *= 0.5; }
+            bool to_replica = false;
+            if (nranks > 1 && !replicated) {
+                if (n[2] % 2) return NP_ERR_INVALID;            // a slab that cannot be halved cannot hand its part of the coarse level over
+                if (n[2] / 2 < opt.agg_min_local_nz || (n[2] / 2) % 2) to_replica = true;
+            }
+            if (to_replica) {
+                replicated = true; agg_lev = (int)lev.size();
+                lev.back().d.kcoff = ko / 2;                     // parents of this slab start at plane koff/2 of the replicated level
+                n[2] = nglob2 / 2; ko = 0;
+            } else { n[2] /= 2; ko /= 2; }
+            n[0] /= 2; n[1] /= 2; nglob2 /= 2;
+            for (int d = 0; d < 3; ++d) dxinv[d] *= 0.5;
         }
+        if (nranks > 1 && !lev.back().replicated) return NP_ERR_INVALID;   // the bottom solver needs the whole coarsest level
         for (auto& L : lev) {
             const MacLevel& d = L.d;
-            if (alloc_d(&L.res, d.ntot) || alloc_d(&L.cor, d.ntot) || alloc_d(&L.rescor, d.ntot)) return NP_ERR_CUDA;
+            if (alloc_cell(&L.res, d) || alloc_cell(&L.cor, d) || alloc_cell(&L.rescor, d)) return NP_ERR_CUDA;
             if (alloc_d(&L.bx, d.fxs * d.n[1] * d.n[2] + 2) || alloc_d(&L.by, d.sx * (d.n[1] + 1) * d.n[2] + 2) || alloc_d(&L.bz, d.sxy * (d.n[2] + 1) + 2)) return NP_ERR_CUDA;
-            zero(L.res, d.ntot); zero(L.cor, d.ntot); zero(L.rescor, d.ntot);
         }
         const MacLevel& d0 = lev[0].d;
-        if (alloc_d(&sol, d0.ntot) || alloc_d(&rhs, d0.ntot)) return NP_ERR_CUDA;
-        zero(sol, d0.ntot); zero(rhs, d0.ntot);
+        if (alloc_cell(&sol, d0) || alloc_cell(&rhs, d0)) return NP_ERR_CUDA;
         dim3 gmax((d0.n[0] + 32) / 32, (d0.n[1] + 8) / 8, d0.n[2] + 1);
         npart = nblk(gmax) + 16;
         if (alloc_d(&part0, npart) || alloc_d(&part1, npart) || alloc_d(&scal, 64)) return NP_ERR_CUDA;
+        zero(scal, 64);
         void* q = nullptr;
         if (np_rt::host_malloc(&q, 64 * sizeof(double))) return NP_ERR_CUDA;
         h_scal = (double*)q;
@@ -121,6 +191,15 @@ struct MacSolver {
         if (np_rt::host_malloc(&q, 8 * sizeof(int))) return NP_ERR_CUDA;
         h_bot_out = (int*)q;
         for (int w = 0; w < 6; ++w) { if (alloc_d(&bw[w], lev.back().d.ntot)) return NP_ERR_CUDA; zero(bw[w], lev.back().d.ntot); }
+        if (agg_lev >= 0) {
+            // staging for the gather onto the first replicated level: this rank's part of that level (cells, or one of its face
+            // arrays with the extra row / plane), and the parts of all ranks
+            const MacLevel& C = lev[agg_lev].d;
+            const long long nzc = C.n[2] / nranks;
+            const long long m = std::max(C.fxs, C.sx) * (long long)(C.n[1] + 1) * (nzc + 1) + 2;
+            if (alloc_d(&agg_send, m) || alloc_d(&agg_recv, m * nranks)) return NP_ERR_CUDA;
+            zero(agg_send, m); zero(agg_recv, m * nranks);
+        }
         for (int e = 0; e < 4; ++e) np_rt::event_create(&ev[e]);
         if (opt.profile_kernels) { prof_ev.resize(4096); for (auto& e : prof_ev) np_rt::event_create(&e); }
         setup_bc();
@@ -130,9 +209,13 @@ struct MacSolver {
     void destroy()
     {
         np_rt::stream_sync(stream);
-        for (auto& L : lev) { double* a[] = {L.bx, L.by, L.bz, L.res, L.cor, L.rescor}; for (double* p : a) if (p) np_rt::dev_free(p); }
+        if (!lev.empty()) { free_cell(sol, lev[0].d); free_cell(rhs, lev[0].d); }
+        for (auto& L : lev) {
+            double* a[] = {L.bx, L.by, L.bz}; for (double* p : a) if (p) np_rt::dev_free(p);
+            free_cell(L.res, L.d); free_cell(L.cor, L.d); free_cell(L.rescor, L.d);
+        }
         lev.clear();
-        double* a[] = {mb_f[0], mb_f[1], mb_f[2], mb_phi, wrapbuf, sol, rhs, part0, part1, scal, stage[0], stage[1], stage[2], stage[3], bw[0], bw[1], bw[2], bw[3], bw[4], bw[5]};
+        double* a[] = {agg_send, agg_recv, mb_f[0], mb_f[1], mb_f[2], mb_phi, wrapbuf, part0, part1, scal, stage[0], stage[1], stage[2], stage[3], bw[0], bw[1], bw[2], bw[3], bw[4], bw[5]};
         for (double* p : a) if (p) np_rt::dev_free(p);
         if (h_scal) np_rt::host_free(h_scal);
         if (bot_out) np_rt::dev_free(bot_out);
@@ -202,7 +285,9 @@ struct MacSolver {
     // MLCellLinOp::smooth: red then black (the boundary conditions are evaluated inside the kernels)
     void smooth(int l, double* phi, const double* b, bool zero_in, double* add_to, const double* boff)
     {
+        if (!zero_in) halo(l, phi);                // applyBC's FillBoundary across the slab faces, before each colour
         gsrb(l, phi, b, 0, zero_in, nullptr, boff);
+        halo(l, phi);
         gsrb(l, phi, b, 1, false, add_to, boff);
     }
     // levels large enough to fill the GPU run both colours in one out-of-place pass (k_mac_rb2)
@@ -210,6 +295,7 @@ struct MacSolver {
     {
         const MacLevel& d = lev[l].d;
         if (opt.fused_rb_min_n <= 0 || d.n[0] < opt.fused_rb_min_n || (d.n[0] & 1)) return false;
+        if (sharded(l)) return false;              // a slab exchanges its ghost planes before each colour: one launch per colour
         if (d.const_beta && !opt.fused_rb_const) return false;
         for (int q = 0; q < 3; ++q) if (bclo[q] == NP_BC_PERIODIC && (d.n[q] & 1)) return false;
         return true;
@@ -252,21 +338,38 @@ struct MacSolver {
         else NP_LAUNCH(REDUCE, (k_mac_adotx<MODE, REDUCE, false>), grid_adotx(L.d), blk(), 0, stream, L.d, L.beta(), y, x, b, boff, part0, part1);
         ++launches;
     }
-    // computeResOfCorrection + restriction: lev[l+1].res = average_down(lev[l].res - off - A lev[l].cor)
+    // computeResOfCorrection + restriction: lev[l+1].res = average_down(lev[l].res - off - A lev[l].cor).  From the last sharded
+    // level onto the first replicated one: every rank restricts its slab into the staging buffer and one all-gather puts the
+    // slabs together on every rank (planes are contiguous, slabs are stacked in rank order).
     void resid_restrict(int l, const double* boff)
     {
         const MacLev& L = lev[l]; const MacLev& C = lev[l + 1];
-        if (L.d.const_beta) NP_LAUNCH(false, (k_mac_resid_restrict<true>), grid_cells(C.d), blk(), 0, stream, C.d, L.d, L.beta(), C.res, (const double*)L.cor, (const double*)L.res, boff);
-        else NP_LAUNCH(false, (k_mac_resid_restrict<false>), grid_cells(C.d), blk(), 0, stream, C.d, L.d, L.beta(), C.res, (const double*)L.cor, (const double*)L.res, boff);
+        halo(l, L.cor);
+        MacLevel Cl = C.d;                       // shape of the part of the coarse level this rank produces
+        double* out = C.res;
+        const bool gather = sharded(l) && C.replicated;
+        if (gather) { Cl.n[2] = L.d.n[2] / 2; out = agg_send; }
+        if (L.d.const_beta) NP_LAUNCH(false, (k_mac_resid_restrict<true>), grid_cells(Cl), blk(), 0, stream, Cl, L.d, L.beta(), out, (const double*)L.cor, (const double*)L.res, boff);
+        else NP_LAUNCH(false, (k_mac_resid_restrict<false>), grid_cells(Cl), blk(), 0, stream, Cl, L.d, L.beta(), out, (const double*)L.cor, (const double*)L.res, boff);
         ++launches;
+        if (gather && comm.allgather(comm.ctx, agg_send, C.res, Cl.sxy * (long long)Cl.n[2], (void*)stream)) err = NP_ERR_NCCL;
     }
     // fold the partials of the last reducing kernel over level-0 cells: scal[base] = max, scal[base+2] = sum, scal[base+6] = mean
     void reduce(long long n, bool want_max, bool want_sum, int base)
     {
         const MacLevel& d0 = lev[0].d;
+        const double ncells = (double)geom.ncell[0] * geom.ncell[1] * geom.ncell[2];
         NP_LAUNCH(true, k_mac_reduce, dim3(1), dim3(1024), 0, stream, want_max ? (const double*)part0 : (const double*)nullptr,
-                  want_sum ? (const double*)part1 : (const double*)nullptr, n, scal + base, (double)d0.n[0] * d0.n[1] * d0.n[2]);
+                  want_sum ? (const double*)part1 : (const double*)nullptr, n, scal + base, ncells);
         ++launches;
+        (void)d0;
+        if (comm.nranks > 1) {                    // level 0 is sharded: max and sum over the ranks, then the mean of the whole domain
+            if (want_max && comm.allreduce(comm.ctx, scal + base, 1, 1, (void*)stream)) err = NP_ERR_NCCL;
+            if (want_sum) {
+                if (comm.allreduce(comm.ctx, scal + base + 2, 1, 0, (void*)stream)) err = NP_ERR_NCCL;
+                NP_LAUNCH(false, k_div_scalar, dim3(1), dim3(32), 0, stream, scal + base, 2, 6, ncells); ++launches;
+            }
+        }
     }
     double fetch(int slot)
     {
@@ -361,6 +464,7 @@ struct MacSolver {
         const MacLevel& d0 = lev[0].d;
         const long long nb = nblk(grid_adotx(d0));
         bottom_iters = 0; bicg_failed_switch = false;
+        halo(0, sol);
         adotx<1, true>(0, lev[0].res, sol, rhs, nullptr);
         reduce(nb, true, singular, 0);
         const double resnorm0 = fetch(0);
@@ -373,6 +477,7 @@ struct MacSolver {
         int rc = NP_OK;
         for (int iter = 0; iter < opt.maxiter; ++iter) {
             vcycle(singular ? scal + 6 : nullptr);       // makeSolvable(res) is applied by the consumers of res (lazy offset)
+            halo(0, sol);
             adotx<1, true>(0, lev[0].res, sol, rhs, nullptr);
             reduce(nb, true, singular, 0);
             const double rn = fetch(0);
@@ -411,6 +516,11 @@ struct MacSolver {
             NP_LAUNCH(true, k_mac_copy_beta, g, blk(), 0, stream, L0.d, dst[d], v, d, part0, part1); ++launches;
             NP_LAUNCH(true, k_mac_reduce_minmax, dim3(1), dim3(1024), 0, stream, (const double*)part0, (const double*)part1, nblk(g), scal + 8, d == 0 ? 1 : 0); ++launches;
         }
+        if (comm.nranks > 1) {                    // (-min, max) over the ranks in one max-allreduce
+            NP_LAUNCH(false, k_negate_one, dim3(1), dim3(32), 0, stream, scal + 8); ++launches;
+            if (comm.allreduce(comm.ctx, scal + 8, 2, 1, (void*)stream)) err = NP_ERR_NCCL;
+            NP_LAUNCH(false, k_negate_one, dim3(1), dim3(32), 0, stream, scal + 8); ++launches;
+        }
         fetch(0);
         const double bmin = h_scal[8], bmax = h_scal[9];
         const bool is_const = opt.const_beta_fastpath && bmin == bmax;
@@ -420,14 +530,30 @@ struct MacSolver {
                 const MacLevel &C = lev[l].d, &F = lev[l - 1].d;
                 const double* src[3] = {lev[l - 1].bx, lev[l - 1].by, lev[l - 1].bz};
                 double* dd[3] = {lev[l].bx, lev[l].by, lev[l].bz};
+                const bool gather = (int)l == agg_lev;      // from the last sharded level onto the first replicated one
+                MacLevel Cl = C;
+                if (gather) Cl.n[2] = F.n[2] / 2;
                 for (int d = 0; d < 3; ++d) {
-                    dim3 g((C.n[0] + (d == 0) + 31) / 32, (C.n[1] + (d == 1) + 7) / 8, C.n[2] + (d == 2));
-                    NP_LAUNCH(false, k_mac_avgdown_face, g, blk(), 0, stream, C, F, dd[d], src[d], d); ++launches;
+                    dim3 g((Cl.n[0] + (d == 0) + 31) / 32, (Cl.n[1] + (d == 1) + 7) / 8, Cl.n[2] + (d == 2));
+                    NP_LAUNCH(false, k_mac_avgdown_face, g, blk(), 0, stream, Cl, F, gather ? agg_send : dd[d], src[d], d); ++launches;
+                    if (!gather) continue;
+                    const long long plane = d == 0 ? Cl.fxs * Cl.n[1] : d == 1 ? Cl.sx * (Cl.n[1] + 1) : Cl.sxy;
+                    if (d < 2) {      // slabs of x / y faces stack up plane by plane: gather straight into the level's array
+                        if (comm.allgather(comm.ctx, agg_send, dd[d], plane * Cl.n[2], (void*)stream)) err = NP_ERR_NCCL;
+                    } else {          // z faces: every slab brings its top plane too; keep the lower n2 planes of each and the last one's top
+                        const long long cnt = plane * (Cl.n[2] + 1);
+                        if (comm.allgather(comm.ctx, agg_send, agg_recv, cnt, (void*)stream)) err = NP_ERR_NCCL;
+                        for (int r = 0; r < comm.nranks; ++r)
+                            np_rt::copy_async(dd[2] + plane * Cl.n[2] * r, agg_recv + cnt * r, (size_t)(plane * Cl.n[2]) * sizeof(double), stream);
+                        np_rt::copy_async(dd[2] + plane * Cl.n[2] * comm.nranks, agg_recv + cnt * (comm.nranks - 1) + plane * Cl.n[2],
+                                          (size_t)plane * sizeof(double), stream);
+                    }
                 }
             }
         }
         stats.sigma_is_const = is_const ? 1 : 0;
         have_beta = true;
+        if (err) return err;
         return np_rt::last_error() ? NP_ERR_CUDA : NP_OK;
     }
     void finish_stats()
@@ -448,7 +574,7 @@ struct MacSolver {
         if (!have_beta) return NP_ERR_STATE;
         for (int d = 0; d < 3; ++d) if (!umac[d].p || umac[d].ncomp < 1) return NP_ERR_INVALID;
         if (mac_phi && (!mac_phi->p || mac_phi->ncomp < 1)) return NP_ERR_INVALID;
-        launches = 0; have_result = false; prof_n = 0;
+        launches = 0; have_result = false; prof_n = 0; err = 0;
         const int is_const = stats.sigma_is_const;
         stats = np_stats{}; stats.sigma_is_const = is_const;
         const MacLevel& d0 = lev[0].d;
@@ -476,6 +602,7 @@ struct MacSolver {
         const int rc = solve(rtol, atol, rhsnorm0);
         np_rt::event_record(ev[2], stream);
         // umac += flux = -b grad(phi)
+        halo(0, sol);
         if (d0.const_beta) NP_LAUNCH(false, (k_mac_fluxes<true, true>), grid_cells(d0), blk(), 0, stream, d0, lev[0].beta(), (const double*)sol, uv[0], uv[1], uv[2]);
         else NP_LAUNCH(false, (k_mac_fluxes<true, false>), grid_cells(d0), blk(), 0, stream, d0, lev[0].beta(), (const double*)sol, uv[0], uv[1], uv[2]);
         ++launches;
@@ -487,6 +614,7 @@ struct MacSolver {
         finish_stats();
         stats.status = rc;
         if (np_rt::last_error()) { stats.status = NP_ERR_CUDA; return NP_ERR_CUDA; }
+        if (err) { stats.status = err; return err; }
         have_result = true;
         return rc;
     }
@@ -499,6 +627,7 @@ struct MacSolver {
         if (!import(*phi, 0, -1, 3, true, &pv, &pst)) return NP_ERR_CUDA;
         double* tmp = lev[0].rescor;                     // free outside a V-cycle
         NP_LAUNCH(false, (k_mac_copy_cell<false>), grid_cells(d0), blk(), 0, stream, d0, tmp, pv);
+        halo(0, tmp);
         if (d0.const_beta) NP_LAUNCH(false, (k_mac_fluxes<false, true>), grid_cells(d0), blk(), 0, stream, d0, lev[0].beta(), (const double*)tmp, fv[0], fv[1], fv[2]);
         else NP_LAUNCH(false, (k_mac_fluxes<false, false>), grid_cells(d0), blk(), 0, stream, d0, lev[0].beta(), (const double*)tmp, fv[0], fv[1], fv[2]);
         for (int d = 0; d < 3; ++d) export_back(flux[d], fv[d], st[d]);
@@ -613,17 +742,21 @@ void mp_default_options(mp_options* o)
 {
     o->max_coarsening_level = 100; o->maxiter = 200; o->bottom_maxiter = 200; o->num_pre_smooth = 2; o->num_post_smooth = 2;
     o->num_final_smooth = 8; o->bottom_solver = NP_BOTTOM_BICGCG; o->verbose = 0; o->bottom_verbose = 0; o->maxorder = 3;
-    o->bottom_rtol = 1e-4; o->bottom_atol = -1.0; o->const_beta_fastpath = 1; o->fused_rb_min_n = 128; o->fused_rb_const = 1; o->profile_kernels = 0;
+    o->bottom_rtol = 1e-4; o->bottom_atol = -1.0; o->const_beta_fastpath = 1; o->fused_rb_min_n = 128; o->fused_rb_const = 1; o->profile_kernels = 0; o->agg_min_local_nz = 32;
 }
 int mp_create(mp_handle** h, const np_geom* geom, int nboxes_global, const np_box* all_boxes, const int* owner_rank,
               int my_rank, int nranks, void* nccl_comm_or_null, const mp_options* opt)
 {
-    (void)nccl_comm_or_null;
     if (!h || !geom || !all_boxes || !owner_rank) return NP_ERR_INVALID;
     mp_options o; if (opt) o = *opt; else mp_default_options(&o);
     mp_handle* p = new (std::nothrow) mp_handle();
     if (!p) return NP_ERR_INVALID;
-    const int rc = p->S.create(geom, nboxes_global, all_boxes, owner_rank, my_rank, nranks, &o);
+    NpComm c;
+    if (nranks > 1) {
+        np_comm_fill_nccl(c, nccl_comm_or_null);
+        if (!c.sendrecv) { delete p; return NP_ERR_NCCL; }
+    }
+    const int rc = p->S.create(geom, nboxes_global, all_boxes, owner_rank, my_rank, nranks, c, &o);
     if (rc) { p->S.destroy(); delete p; return rc; }
     *h = p;
     return NP_OK;
@@ -698,6 +831,7 @@ int mp_apply(mp_handle* h, int l, const np_fab* x, np_fab* y)
     if (!MP_LEVEL_OK(h, l) || !x || !y) return NP_ERR_INVALID;
     MacSolver& S = h->S; MacLev& L = S.lev[l];
     if (S.cell_in(l, *x, L.cor, 0)) return NP_ERR_INVALID;
+    S.halo(l, L.cor);
     S.adotx<0, false>(l, L.rescor, L.cor, nullptr, nullptr);
     return S.cell_out(l, *y, L.rescor, 1);
 }

@@ -44,10 +44,20 @@ class MacProjector:
     boxes: list of (lo, hi) cell boxes of the level's BoxArray (default: one box covering the domain).  With several
     boxes every per-direction argument (beta[d], umac[d], fluxes[d]) and mac_phi is a LIST of Fabs in BoxArray order."""
 
-    def __init__(self, geom, lib=None, boxes=None):
+    def __init__(self, geom, lib=None, boxes=None, rank=0, nranks=1, nccl_comm=None):
+        """nranks > 1 (one GPU each): `geom` is the whole domain, the level is cut into nranks equal z-slabs, this rank
+        holds slab `rank` (its fabs have ncell[2] / nranks planes), nccl_comm: void* from capi np_nccl_comm_create."""
         self.L = lib or capi.load()
         self.geom = geom
-        self.boxes = boxes or [((0, 0, 0), tuple(n - 1 for n in geom.ncell))]
+        self.rank, self.nranks, self.nccl_comm = rank, nranks, nccl_comm
+        if nranks > 1:
+            nzl = geom.ncell[2] // nranks
+            self.all_boxes = [((0, 0, r * nzl), (geom.ncell[0] - 1, geom.ncell[1] - 1, (r + 1) * nzl - 1)) for r in range(nranks)]
+            self.owner = list(range(nranks))
+            self.boxes = [self.all_boxes[rank]]
+        else:
+            self.boxes = boxes or [((0, 0, 0), tuple(n - 1 for n in geom.ncell))]
+            self.all_boxes, self.owner = self.boxes, [0] * len(self.boxes)
         self.h = None
         self.umac = None
         self.stats = None
@@ -60,15 +70,16 @@ class MacProjector:
         info = lp_info or LPInfo()
         options.setdefault("max_coarsening_level", min(info.max_coarsening_level, 100))
         self.opt = capi.mac_default_options(self.L, **options)
-        nb = len(self.boxes)
+        nb = len(self.all_boxes)
         bx = (capi.np_box * nb)()
-        for b, (lo, hi) in enumerate(self.boxes):
+        for b, (lo, hi) in enumerate(self.all_boxes):
             for d in range(3):
                 bx[b].lo[d], bx[b].hi[d] = int(lo[d]), int(hi[d])
-        owner = (C.c_int * nb)(*([0] * nb))
+        owner = (C.c_int * nb)(*self.owner)
         h = C.c_void_p()
         g = self.geom.c()
-        capi.check(self.L, self.L.mp_create(C.byref(h), C.byref(g), nb, bx, owner, 0, 1, None, C.byref(self.opt)))
+        capi.check(self.L, self.L.mp_create(C.byref(h), C.byref(g), nb, bx, owner, self.rank, self.nranks,
+                                            C.c_void_p(self.nccl_comm) if self.nccl_comm else None, C.byref(self.opt)))
         self.h = h
         if self._bc:
             self.setDomainBC(*self._bc)

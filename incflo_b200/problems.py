@@ -167,9 +167,10 @@ def mac_rayleigh_taylor(ncell, prob_lo=(0, 0, 0), prob_hi=(0.5, 0.5, 1.0)):
 MAC_PROBLEMS = {"double_shear": mac_double_shear, "rayleigh_taylor": mac_rayleigh_taylor}
 
 
-def mac_problem_torch(name, ncell, prob_hi, device, ngrow=0):
+def mac_problem_torch(name, ncell, prob_hi, device, ngrow=0, koff=0, nz_local=None):
     """The MAC_PROBLEMS fields built directly on `device` as face-fab storage [1, nz(+1)+2g, ny(+1)+2g, nx(+1)+2g]
-    (zero ghosts): (umac[3], beta[3], bclo, bchi).  Same formulas as mac_double_shear / mac_rayleigh_taylor."""
+    (zero ghosts): (umac[3], beta[3], bclo, bchi).  Same formulas as mac_double_shear / mac_rayleigh_taylor.
+    koff / nz_local select a z-slab of the domain `ncell` (multi-GPU): planes koff .. koff + nz_local."""
     import torch
     f64 = dict(dtype=torch.float64, device=device)
     g = ngrow
@@ -177,8 +178,10 @@ def mac_problem_torch(name, ncell, prob_hi, device, ngrow=0):
     dx = [L[d] / ncell[d] for d in range(3)]
     umac, beta = [], []
     for d in range(3):
-        n = [ncell[q] + (1 if q == d else 0) for q in range(3)]
-        c = [(torch.arange(n[q], **f64) + (0.0 if q == d else 0.5)) * dx[q] for q in range(3)]
+        nzl = ncell[2] if nz_local is None else nz_local
+        n = [ncell[0], ncell[1], nzl]
+        n[d] += 1
+        c = [(torch.arange(n[q], **f64) + (koff if q == 2 else 0) + (0.0 if q == d else 0.5)) * dx[q] for q in range(3)]
         x, y, z = c[0][None, None, :], c[1][None, :, None], c[2][:, None, None]
         p = 0.1 * torch.sin(TWOPI * x / L[0]) * torch.sin(TWOPI * y / L[1]) * torch.sin(TWOPI * z / L[2])
         if name == "double_shear":
@@ -193,8 +196,10 @@ def mac_problem_torch(name, ncell, prob_hi, device, ngrow=0):
             b = 1.0 / rho
             f = ((p, p, -0.1 + p)[d]).expand(n[2], n[1], n[0]).clone()
             if d == 2:
-                f[0] = 0.0
-                f[-1] = 0.0
+                if koff == 0:
+                    f[0] = 0.0
+                if koff + nzl == ncell[2]:
+                    f[-1] = 0.0
         uf = torch.zeros((1, n[2] + 2 * g, n[1] + 2 * g, n[0] + 2 * g), **f64)
         bf = torch.zeros_like(uf)
         inner = (0, slice(g, g + n[2]), slice(g, g + n[1]), slice(g, g + n[0]))

@@ -17,9 +17,10 @@
  *   mp_destroy      <- ~MacProjector
  *
  * Fabs use AMReX's FArrayBox layout (include/nodalproj.h).  A face fab of direction d is nodal in d: valid index range
- * [lo, hi+1] in d, [lo, hi] in the other two.  Device or host pointers (host fabs are staged).  This round: one AMR level
- * on ONE rank (nranks == 1; any number of boxes tiling the domain, see the *_boxes entry points); the z-slab multi-GPU
- * layer of the nodal solver is not wired in yet.
+ * [lo, hi+1] in d, [lo, hi] in the other two.  Device or host pointers (host fabs are staged).  One AMR level.  One rank: any number
+ * of boxes tiling the domain (the *_boxes entry points).  Several ranks (one GPU each): one box per rank, equal z-slabs
+ * ordered by rank with an even number of planes; halo planes, norms and the gather onto the replicated coarse levels go
+ * through NCCL (nccl_comm: an initialised ncclComm_t, e.g. from np_nccl_comm_create).
  * There is no CPU compute path: without a CUDA device mp_create fails with NP_ERR_NO_DEVICE.
  */
 #ifndef MACPROJ_H
@@ -48,8 +49,8 @@ typedef struct {
     int const_beta_fastpath;    /* skip every coefficient read when b is uniform (constant density); default 1 */
     int fused_rb_min_n;         /* levels with at least this many cells in x run the red and the black sweep of a smooth in
                                    ONE pass (k_mac_rb2); smaller levels use one launch per colour; default 128, <= 0: never */
-    int fused_rb_const;         /* 1: also when b is uniform; default 0 - with no coefficients to read the one-pass kernel is
-                                   bound by its instruction count and measured slower than two launches */
+    int fused_rb_const;         /* 1 (default): also when b is uniform; 0: one launch per colour there */
+    int agg_min_local_nz;       /* multi-GPU: replicate MG levels whose slab would be thinner than this; default 32 */
     int profile_kernels;        /* bracket every level-0 smooth with CUDA events (np_stats.ms_smooth0 / n_smooth0); default 0 */
 } mp_options;
 

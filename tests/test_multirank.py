@@ -150,3 +150,111 @@ def test_two_ranks_match_oracle(tmp_path, name, ncell, kw, agg_min, agg_level, o
     assert l2(u, o.get_vel()) < 1e-11 and l2(gp, o.get_gradphi()) < 1e-10
     po = o.get_phi()
     assert l2(phi - phi.mean(), po - po.mean()) < 1e-10
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# MAC projection on two ranks (z-slabs): halo planes before each colour, sum / max over the ranks, the gather of the
+# restricted residual and of the coarse face coefficients onto the replicated levels - against the one-box MAC oracle
+# (a red-black sweep does not depend on the partition, so counts and history must be the single-box ones).
+# ---------------------------------------------------------------------------------------------------------------------
+def _mac_worker(rank, world, port, name, ncell, kw, agg_min, outdir):
+    import torch
+    import torch.distributed as dist
+    from incflo_b200.mac_projector import MacProjector, face_fab_from_array
+    from incflo_b200.projector import Fab, Geometry, LPInfo
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    L = nphelp.emu_lib()
+
+    def view(ptr, n):
+        return torch.from_numpy(np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_double)), shape=(n,)))
+
+    SR = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_longlong, C.c_void_p, C.c_longlong, C.c_void_p, C.c_longlong, C.c_void_p,
+                     C.c_longlong, C.c_int, C.c_int)
+    AR = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.c_int)
+    AG = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_longlong)
+
+    def sendrecv(slo, nslo, rlo, nrlo, shi, nshi, rhi, nrhi, lo, hi):
+        reqs = []
+        if lo >= 0:
+            reqs.append(dist.isend(view(slo, nslo).clone(), lo, tag=1))
+            reqs.append(dist.irecv(view(rlo, nrlo), lo, tag=2))
+        if hi >= 0:
+            reqs.append(dist.isend(view(shi, nshi).clone(), hi, tag=2))
+            reqs.append(dist.irecv(view(rhi, nrhi), hi, tag=1))
+        for r in reqs:
+            r.wait()
+        return 0
+
+    def allreduce(buf, n, op):
+        dist.all_reduce(view(buf, n), op=dist.ReduceOp.MAX if op == 1 else dist.ReduceOp.SUM)
+        return 0
+
+    def allgather(send, recv, cnt):
+        dist.all_gather_into_tensor(view(recv, cnt * world), view(send, cnt).clone())
+        return 0
+
+    cbs = (SR(sendrecv), AR(allreduce), AG(allgather))
+    L.np_emu_set_comm.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    L.np_emu_set_comm(C.cast(cbs[0], C.c_void_p), C.cast(cbs[1], C.c_void_p), C.cast(cbs[2], C.c_void_p))
+
+    nzl = ncell[2] // world
+    prob = problems.MAC_PROBLEMS[name](ncell, **kw)
+    k0, k1 = rank * nzl, (rank + 1) * nzl
+    cut = lambda a, d: a[k0:k1 + (1 if d == 2 else 0)]
+    geom = Geometry(ncell, prob["prob_lo"], prob["prob_hi"], [b == 0 for b in prob["bclo"]])
+    P = MacProjector(geom, lib=L, rank=rank, nranks=world, nccl_comm=1)
+    P.setDomainBC(prob["bclo"], prob["bchi"])
+    P.initProjector(LPInfo().setMaxCoarseningLevel(100), [face_fab_from_array(cut(prob["beta"][d], d)) for d in range(3)],
+                    agg_min_local_nz=agg_min)
+    fu = [face_fab_from_array(cut(prob["umac"][d], d), 1) for d in range(3)]
+    P.setUMAC(fu)
+    fphi = Fab.zeros((ncell[0], ncell[1], nzl), 1, 1)
+    st = P.project(fphi, 1e-11, 1e-14)
+    np.savez(os.path.join(outdir, f"m{rank}.npz"), u=fu[0].numpy_valid()[0], v=fu[1].numpy_valid()[0], w=fu[2].numpy_valid()[0],
+             phi=fphi.numpy_valid()[0], vc=st.n_vcycles, nlev=st.n_levels, bot=st.bottom_iters_total, const=st.sigma_is_const,
+             hist=np.array([st.res_history[i] for i in range(st.n_vcycles)]),
+             levels=np.array([P.level_ncell(l) for l in range(P.num_levels)]))
+    P.close()
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("name,ncell,kw,agg_min,agg_level", [
+    ("double_shear", (16, 16, 64), dict(prob_hi=(1.0, 1.0, 4.0)), 16, 2),     # uniform beta, periodic z: every slab face is remote
+    ("rayleigh_taylor", (16, 16, 32), {}, 8, 2),                             # variable beta (coefficient gather), walls in z
+    ("rayleigh_taylor", (16, 16, 32), {}, 4, 3),                             # two sharded coarse levels before the gather
+])
+def test_mac_two_ranks_match_oracle(tmp_path, name, ncell, kw, agg_min, agg_level):
+    import torch.multiprocessing as mp
+    from oracle.mac import MacOracle
+
+    nphelp.emu_lib()
+    world = 2
+    mp.spawn(_mac_worker, args=(world, _free_port(), name, ncell, kw, agg_min, str(tmp_path)), nprocs=world, join=True)
+    r = [np.load(tmp_path / f"m{k}.npz") for k in range(world)]
+    nzl = ncell[2] // world
+    prob = problems.MAC_PROBLEMS[name](ncell, **kw)
+    o = MacOracle(ncell, prob["prob_lo"], prob["prob_hi"], prob["bclo"], prob["bchi"])
+    o.set_beta(*prob["beta"]); o.set_umac(*prob["umac"])
+    so = o.project(1e-11, 1e-14)
+
+    def l2(a, b):
+        return np.linalg.norm(a - b) / np.linalg.norm(b)
+
+    assert int(r[0]["vc"]) == int(r[1]["vc"]) == so.n_vcycles and int(r[0]["nlev"]) == so.n_levels
+    assert int(r[0]["bot"]) == so.bottom_iters_total
+    assert r[0]["levels"][agg_level][2] == ncell[2] >> agg_level and r[0]["levels"][agg_level - 1][2] == nzl >> (agg_level - 1)
+    for i in range(so.n_vcycles):
+        assert abs(r[0]["hist"][i] - so.res_history[i]) <= 1e-6 * so.res_history[i] + 1e-14 * so.rhs_norm0
+    uo = o.get_umac()
+    assert l2(np.concatenate([r[k]["u"] for k in range(world)], axis=0), uo[0]) < 1e-12
+    assert l2(np.concatenate([r[k]["v"] for k in range(world)], axis=0), uo[1]) < 1e-12
+    w = np.concatenate([r[0]["w"][:-1], r[1]["w"]], axis=0)               # the shared face plane is held by both ranks
+    assert np.abs(r[0]["w"][-1] - r[1]["w"][0]).max() <= 1e-13 * np.abs(w).max()
+    assert l2(w, uo[2]) < 1e-12
+    phi = np.concatenate([r[k]["phi"] for k in range(world)], axis=0)
+    po = o.get_phi()
+    assert l2(phi - phi.mean(), po - po.mean()) < 1e-10

@@ -19,7 +19,7 @@ ap.add_argument("--verbose", type=int, default=0)
 a = ap.parse_args()
 torch.cuda.set_device(0)
 n = (a.ncell,) * 3
-hi = (1.0, 1.0, 1.0) if a.workload == "double_shear" else (0.5, 0.5, 0.5)
+hi = (1.0, 1.0, 1.0)
 umac, beta, bclo, bchi = problems.mac_problem_torch(a.workload, n, hi, "cuda:0")
 u0 = [u.clone() for u in umac]
 P = MacProjector(Geometry(n, (0, 0, 0), hi, [b == 0 for b in bclo]), lib=capi.load())
