@@ -310,13 +310,28 @@ __device__ __forceinline__ int rb3_flags(const MacLevel& L, int gx, int gy)
     return f;
 }
 
+// plane index of the ring's plane p in the arrays of k_mac_rb3: inside the slab p itself; across a periodic face the wrapped
+// plane; across a face shared with the neighbouring rank one of the two ghost planes the halo exchange filled (p = -2, -1, n2,
+// n2+1: plain addresses below / above the slab); RB_NOPLANE outside a physical face
+#define RB_NOPLANE (-(1 << 30))
+__device__ __forceinline__ int rb3_zmap(const MacLevel& L, int p)
+{
+    const int n = L.n[2];
+    if (p >= 0 && p < n) return p;
+    const int bc = p < 0 ? L.bclo[2] : L.bchi[2];
+    if (bc == MAC_REMOTE) return (p >= -2 && p < n + 2) ? p : RB_NOPLANE;
+    if (bc == MAC_PER) return (p % n + n) % n;
+    return RB_NOPLANE;
+}
+
 template <bool CB>
 __global__ void __launch_bounds__(256) k_mac_rb3(MacLevel L, MacLevel Lc, MacBeta B, RbArgs A)
 {
     __shared__ __align__(16) double ring[4 * RB_PS];
     const int tid = threadIdx.x, tx = tid & 31, ty = tid >> 5;
     const int x0 = blockIdx.x * RB_TX, y0 = blockIdx.y * RB_TY, z0 = blockIdx.z * A.zc, z1 = min(z0 + A.zc, L.n[2]);
-    const int px = L.bclo[0] == MAC_PER, py = L.bclo[1] == MAC_PER, pz = L.bclo[2] == MAC_PER;
+    const int px = L.bclo[0] == MAC_PER, py = L.bclo[1] == MAC_PER;
+    const bool zlo_phys = L.bclo[2] == MAC_NEU || L.bclo[2] == MAC_DIR, zhi_phys = L.bchi[2] == MAC_NEU || L.bchi[2] == MAC_DIR;
     const double off = A.boff ? *A.boff : 0.0;
     const int sx = (int)L.sx, fxs = (int)L.fxs, sxc = (int)Lc.sx;
     // ---- the thread's fixed cells ----
@@ -326,7 +341,7 @@ __global__ void __launch_bounds__(256) k_mac_rb3(MacLevel L, MacLevel Lc, MacBet
     {
         const int lx0 = 2 + 2 * tx, gx0 = x0 + 2 * tx;
         const int ly0 = 2 + ty, gy0 = y0 + ty, ly1 = ly0 + 8, gy1 = gy0 + 8;
-        par0 = (gx0 + gy0) & 1; par1 = (gx0 + gy1) & 1;
+        par0 = (gx0 + gy0 + L.koff) & 1; par1 = (gx0 + gy1 + L.koff) & 1;
         pco0 = (gx0 >> 1) + sxc * (gy0 >> 1); pco1 = (gx0 >> 1) + sxc * (gy1 >> 1);
         own0.so = RB3_SO(lx0, ly0); own0.dxm = RB3_DXM(lx0); own0.go = gx0 + sx * gy0; own0.gfx = gx0 + fxs * gy0; own0.flags = 0;
         own1.so = RB3_SO(lx0, ly1); own1.dxm = RB3_DXM(lx0); own1.go = gx0 + sx * gy1; own1.gfx = gx0 + fxs * gy1; own1.flags = 0;
@@ -362,7 +377,7 @@ __global__ void __launch_bounds__(256) k_mac_rb3(MacLevel L, MacLevel Lc, MacBet
         else { const int g = tid - 132; ly = 2 + (g >> 1); lx = (g & 1) ? RB_PX - 2 : 1; }
         const int gxu = x0 - 2 + lx, gyu = y0 - 2 + ly;
         const int gx = rb_wrap(gxu, L.n[0], px), gy = rb_wrap(gyu, L.n[1], py);
-        rpar = (gxu + gyu) & 1;
+        rpar = (gxu + gyu + L.koff) & 1;
         if (gx >= 0 && gy >= 0) { rc.so = RB3_SO(lx, ly); rc.dxm = RB3_DXM(lx); rc.go = gx + sx * gy; rc.gfx = gx + fxs * gy; rc.flags = rb3_flags(L, gx, gy); }
     }
     const long long fxz = L.fxs * (long long)L.n[1], fyz = L.sx * (long long)(L.n[1] + 1);
@@ -370,9 +385,9 @@ __global__ void __launch_bounds__(256) k_mac_rb3(MacLevel L, MacLevel Lc, MacBet
     // plane loads run one step ahead: the values of plane p+1 travel in registers while plane p is relaxed
     double2 pre_own[2]; double pre_fr[2];
     auto fetch_plane = [&](int p) {
-        const int gz = rb_wrap(p, L.n[2], pz);
+        const int gz = rb3_zmap(L, p);
         pre_own[0] = pre_own[1] = make_double2(0.0, 0.0); pre_fr[0] = pre_fr[1] = 0.0;
-        if (gz < 0 || p > z1 + 1) return;
+        if (gz == RB_NOPLANE || p > z1 + 1) return;
         const long long zc = L.sxy * (long long)gz, zcc = Lc.sxy * (long long)(gz >> 1);
 #pragma unroll
         for (int m = 0; m < 2; ++m) {
@@ -393,8 +408,8 @@ __global__ void __launch_bounds__(256) k_mac_rb3(MacLevel L, MacLevel Lc, MacBet
     auto fetch_rhs = [&](int p) {           // for the step that will load plane p: red plane p-1, black plane p-2
         if (!CB) return;                    // variable coefficients: the registers are needed elsewhere (measured slower)
         const int q = p - 1, r = p - 2;
-        const int gzq = rb_wrap(q, L.n[2], pz);
-        if (gzq >= 0 && q >= z0 - 1 && q <= z1) {
+        const int gzq = rb3_zmap(L, q);
+        if (gzq != RB_NOPLANE && q >= z0 - 1 && q <= z1) {
             const long long zc = L.sxy * (long long)gzq;
             rr0 = A.rhs[zc + own0.go + ((par0 + q) & 1)]; rr1 = A.rhs[zc + own1.go + ((par1 + q) & 1)];
             if (rc.so >= 0 && (((rpar + q) & 1) == 0)) rrr = A.rhs[zc + rc.go];
@@ -417,8 +432,8 @@ __global__ void __launch_bounds__(256) k_mac_rb3(MacLevel L, MacLevel Lc, MacBet
             fetch_rhs(p + 1);
             if (!CB) {      // variable coefficients: pull the lines the next step's red sweep (plane p) reads into L1 now; the black
                             // sweep of that plane, one step later, finds them there
-                const int gzn = rb_wrap(p, L.n[2], pz);
-                if (gzn >= 0 && p <= z1) {
+                const int gzn = rb3_zmap(L, p);
+                if (gzn != RB_NOPLANE && p <= z1) {
                     const long long zc = L.sxy * (long long)gzn, zfx = fxz * gzn, zfy = fyz * gzn;
                     np_prefetch_l1(B.bx + zfx + own0.gfx); np_prefetch_l1(B.bx + zfx + own1.gfx);
                     np_prefetch_l1(B.by + zfy + own0.go); np_prefetch_l1(B.by + zfy + own0.go + L.sx);
@@ -432,11 +447,11 @@ __global__ void __launch_bounds__(256) k_mac_rb3(MacLevel L, MacLevel Lc, MacBet
         // ---- red cells of plane p-1: own pairs + ring ----
         {
             const int q = p - 1;
-            const int gz = rb_wrap(q, L.n[2], pz);
-            if (gz >= 0 && q >= z0 - 1 && q <= z1) {
+            const int gz = rb3_zmap(L, q);
+            if (gz != RB_NOPLANE && q >= z0 - 1 && q <= z1) {
                 double* P = ring + (q & 3) * RB_PS;
                 const double* Pm = ring + ((q - 1) & 3) * RB_PS; const double* Pp = ring + ((q + 1) & 3) * RB_PS;
-                const int zfl = pz ? 0 : ((gz == 0 ? RBF_ZLO : 0) | (gz == L.n[2] - 1 ? RBF_ZHI : 0));
+                const int zfl = ((zlo_phys && gz == 0) ? RBF_ZLO : 0) | ((zhi_phys && gz == L.n[2] - 1) ? RBF_ZHI : 0);
                 const long long zc = L.sxy * (long long)gz, zfx = fxz * gz, zfy = fyz * gz;
                 // reds only read blacks (and their own value), so the in-place writes of other threads cannot be seen here
                 const RbCell c0 = cell_of(0, (par0 + q) & 1), c1 = cell_of(1, (par1 + q) & 1);
@@ -453,7 +468,7 @@ __global__ void __launch_bounds__(256) k_mac_rb3(MacLevel L, MacLevel Lc, MacBet
             if (r >= z0 && r < z1) {
                 const double* P = ring + (r & 3) * RB_PS;
                 const double* Pm = ring + ((r - 1) & 3) * RB_PS; const double* Pp = ring + ((r + 1) & 3) * RB_PS;
-                const int zfl = pz ? 0 : ((r == 0 ? RBF_ZLO : 0) | (r == L.n[2] - 1 ? RBF_ZHI : 0));
+                const int zfl = ((zlo_phys && r == 0) ? RBF_ZLO : 0) | ((zhi_phys && r == L.n[2] - 1) ? RBF_ZHI : 0);
                 const long long zc = L.sxy * (long long)r, zfx = fxz * r, zfy = fyz * r;
 #pragma unroll
                 for (int m = 0; m < 2; ++m) {

@@ -50,16 +50,17 @@ struct MacSolver {
     static long long nblk(dim3 g) { return (long long)g.x * g.y * g.z; }
     static int alloc_d(double** p, long long n) { void* q = nullptr; if (np_rt::dev_malloc(&q, (size_t)n * sizeof(double))) return 1; *p = (double*)q; return 0; }
     void zero(double* p, long long n) { np_rt::memset_async(p, 0, (size_t)n * sizeof(double), stream); }
-    // cell array of a level with one ghost plane on either side in z; the returned pointer is plane 0
+    // cell array of a level with two ghost planes on either side in z (planes -2, -1 and n2, n2+1 of a slab); the returned
+    // pointer is plane 0
     int alloc_cell(double** p, const MacLevel& d)
     {
         double* q = nullptr;
-        if (alloc_d(&q, d.ntot + 2 * d.sxy)) return 1;
-        np_rt::memset_async(q, 0, (size_t)(d.ntot + 2 * d.sxy) * sizeof(double), stream);
-        *p = q + d.sxy;
+        if (alloc_d(&q, d.ntot + 4 * d.sxy)) return 1;
+        np_rt::memset_async(q, 0, (size_t)(d.ntot + 4 * d.sxy) * sizeof(double), stream);
+        *p = q + 2 * d.sxy;
         return 0;
     }
-    static void free_cell(double* p, const MacLevel& d) { if (p) np_rt::dev_free(p - d.sxy); }
+    static void free_cell(double* p, const MacLevel& d) { if (p) np_rt::dev_free(p - 2 * d.sxy); }
     bool sharded(int l) const { return comm.nranks > 1 && !lev[l].replicated; }
     void z_neighbours(int& lo, int& hi) const
     {
@@ -68,13 +69,15 @@ struct MacSolver {
         lo = r > 0 ? r - 1 : (per ? R - 1 : -1);
         hi = r < R - 1 ? r + 1 : (per ? 0 : -1);
     }
-    // ghost planes of a cell array of a sharded level: my plane 0 -> the lower rank's plane n2, my plane n2-1 -> the upper rank's -1
-    void halo(int l, double* x)
+    // ghost planes of a cell array of a sharded level, `depth` (1 or 2) planes per side: my planes 0.. -> the lower rank's planes
+    // n2.., my planes ..n2-1 -> the upper rank's planes ..-1
+    void halo(int l, double* x, int depth = 1)
     {
         if (!sharded(l)) return;
         const MacLevel& d = lev[l].d;
+        const long long m = d.sxy * depth;
         int lo, hi; z_neighbours(lo, hi);
-        if (comm.sendrecv(comm.ctx, x, d.sxy, x - d.sxy, d.sxy, x + d.sxy * (long long)(d.n[2] - 1), d.sxy, x + d.sxy * (long long)d.n[2], d.sxy,
+        if (comm.sendrecv(comm.ctx, x, m, x - m, m, x + d.sxy * (long long)d.n[2] - m, m, x + d.sxy * (long long)d.n[2], m,
                           lo, hi, (void*)stream)) err = NP_ERR_NCCL;
     }
 
@@ -295,7 +298,10 @@ struct MacSolver {
     {
         const MacLevel& d = lev[l].d;
         if (opt.fused_rb_min_n <= 0 || d.n[0] < opt.fused_rb_min_n || (d.n[0] & 1)) return false;
-        if (sharded(l)) return false;              // a slab exchanges its ghost planes before each colour: one launch per colour
+        // a slab can run the one-pass smoother on two ghost planes per side (the reds of the planes next to the slab are
+        // recomputed there); that needs the right-hand side on one ghost plane too and, for variable coefficients, ghost
+        // coefficient planes, which are not kept: those slabs exchange one plane before each colour and use one launch per colour
+        if (sharded(l) && !(d.const_beta && d.n[0] % RB_TX == 0 && d.n[1] % RB_TY == 0 && d.n[2] >= 4)) return false;
         if (d.const_beta && !opt.fused_rb_const) return false;
         for (int q = 0; q < 3; ++q) if (bclo[q] == NP_BC_PERIODIC && (d.n[q] & 1)) return false;
         return true;
@@ -316,6 +322,10 @@ struct MacSolver {
             if (crse) interp_add(l, L.cor, crse);
             smooth(l, L.cor, L.res, zero_in, add_to, boff);
             return;
+        }
+        if (sharded(l)) {                        // interpolation as a pass of its own (its parents may live on another rank's
+            if (crse) { interp_add(l, L.cor, crse); crse = nullptr; }      // planes), then both ghost planes of the iterate
+            if (!zero_in) halo(l, L.cor, 2);
         }
         RbArgs A;
         A.out = L.rescor; A.in = L.cor; A.rhs = L.res; A.boff = boff; A.add_to = add_to; A.crse = crse; A.zero_in = zero_in ? 1 : 0;
@@ -353,6 +363,7 @@ struct MacSolver {
         else NP_LAUNCH(false, (k_mac_resid_restrict<false>), grid_cells(Cl), blk(), 0, stream, Cl, L.d, L.beta(), out, (const double*)L.cor, (const double*)L.res, boff);
         ++launches;
         if (gather && comm.allgather(comm.ctx, agg_send, C.res, Cl.sxy * (long long)Cl.n[2], (void*)stream)) err = NP_ERR_NCCL;
+        halo(l + 1, C.res);                      // the one-pass smoother relaxes the reds of the first ghost plane too
     }
     // fold the partials of the last reducing kernel over level-0 cells: scal[base] = max, scal[base+2] = sum, scal[base+6] = mean
     void reduce(long long n, bool want_max, bool want_sum, int base)
@@ -466,6 +477,7 @@ struct MacSolver {
         bottom_iters = 0; bicg_failed_switch = false;
         halo(0, sol);
         adotx<1, true>(0, lev[0].res, sol, rhs, nullptr);
+        halo(0, lev[0].res);
         reduce(nb, true, singular, 0);
         const double resnorm0 = fetch(0);
         const double max_norm = rhsnorm0 >= resnorm0 ? rhsnorm0 : resnorm0;
@@ -479,6 +491,7 @@ struct MacSolver {
             vcycle(singular ? scal + 6 : nullptr);       // makeSolvable(res) is applied by the consumers of res (lazy offset)
             halo(0, sol);
             adotx<1, true>(0, lev[0].res, sol, rhs, nullptr);
+            halo(0, lev[0].res);
             reduce(nb, true, singular, 0);
             const double rn = fetch(0);
             if (iter < 128) stats.res_history[iter] = rn;

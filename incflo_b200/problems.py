@@ -164,7 +164,17 @@ def mac_rayleigh_taylor(ncell, prob_lo=(0, 0, 0), prob_hi=(0.5, 0.5, 1.0)):
                 prob_hi=tuple(prob_hi))
 
 
-MAC_PROBLEMS = {"double_shear": mac_double_shear, "rayleigh_taylor": mac_rayleigh_taylor}
+def mac_double_shear_walls(ncell, prob_lo=(0, 0, 0), prob_hi=(1, 1, 1)):
+    """mac_double_shear between slip walls in z (Neumann, no flow through the wall faces): uniform beta with physical z faces."""
+    d = mac_double_shear(ncell, prob_lo, prob_hi)
+    d["umac"] = [np.array(u) for u in d["umac"]]
+    d["umac"][2][0] = 0.0
+    d["umac"][2][-1] = 0.0
+    d["bclo"], d["bchi"] = (0, 0, NEUMANN), (0, 0, NEUMANN)
+    return d
+
+
+MAC_PROBLEMS = {"double_shear": mac_double_shear, "rayleigh_taylor": mac_rayleigh_taylor, "double_shear_walls": mac_double_shear_walls}
 
 
 def mac_problem_torch(name, ncell, prob_hi, device, ngrow=0, koff=0, nz_local=None):

@@ -208,7 +208,7 @@ def _mac_worker(rank, world, port, name, ncell, kw, agg_min, outdir):
     P = MacProjector(geom, lib=L, rank=rank, nranks=world, nccl_comm=1)
     P.setDomainBC(prob["bclo"], prob["bchi"])
     P.initProjector(LPInfo().setMaxCoarseningLevel(100), [face_fab_from_array(cut(prob["beta"][d], d)) for d in range(3)],
-                    agg_min_local_nz=agg_min)
+                    agg_min_local_nz=agg_min, fused_rb_min_n=64)
     fu = [face_fab_from_array(cut(prob["umac"][d], d), 1) for d in range(3)]
     P.setUMAC(fu)
     fphi = Fab.zeros((ncell[0], ncell[1], nzl), 1, 1)
@@ -226,6 +226,9 @@ def _mac_worker(rank, world, port, name, ncell, kw, agg_min, outdir):
     ("double_shear", (16, 16, 64), dict(prob_hi=(1.0, 1.0, 4.0)), 16, 2),     # uniform beta, periodic z: every slab face is remote
     ("rayleigh_taylor", (16, 16, 32), {}, 8, 2),                             # variable beta (coefficient gather), walls in z
     ("rayleigh_taylor", (16, 16, 32), {}, 4, 3),                             # two sharded coarse levels before the gather
+    ("double_shear", (64, 16, 32), dict(prob_hi=(4.0, 1.0, 2.0)), 8, 2),     # whole 64 x 16 tiles, uniform beta: the one-pass
+                                                                             # smoother on two ghost planes per slab side
+    ("double_shear_walls", (64, 16, 32), dict(prob_hi=(4.0, 1.0, 2.0)), 8, 2),   # the same between walls: physical and shared z faces
 ])
 def test_mac_two_ranks_match_oracle(tmp_path, name, ncell, kw, agg_min, agg_level):
     import torch.multiprocessing as mp
