@@ -152,6 +152,8 @@ CASES = [("double_shear", (32, 32, 16), dict(prob_hi=(1.0, 1.0, 0.5))), ("raylei
 @pytest.mark.parametrize("name,ncell,kw", CASES)
 @pytest.mark.parametrize("fused", [128, 2])
 def test_mac_project_matches_oracle(backend, name, ncell, kw, fused):
+    if ncell[0] == 64 and fused != 2:
+        pytest.skip("the whole-tile case is there for the one-pass smoother")
     prob = problems.MAC_PROBLEMS[name](ncell, **kw)
     drv = Drv(ncell, prob["prob_hi"], prob["bclo"], prob["bchi"], prob["beta"], backend, fused_rb_min_n=fused, fused_rb_const=1)
     st, u, phi = drv.project(prob["umac"], ng=1)
@@ -250,7 +252,7 @@ def test_mac_fused_smoother_tiles(backend, bclo, bchi, ncell):
     assert np.abs(s - so).max() <= 1e-13 * np.abs(so).max()
 
 
-@pytest.mark.parametrize("host", [False, True])
+@pytest.mark.parametrize("host", [False, pytest.param(True, marks=pytest.mark.gpu)])
 def test_mac_multibox_equals_onebox(backend, host):
     """amr.max_grid_size chops the level: per-box face fabs (shared faces duplicated, 1 ghost layer of junk) through the
     *_boxes entry points must give bit-identical umac / phi / fluxes to the one-box call.  host=True on the GPU: host fabs."""

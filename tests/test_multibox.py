@@ -93,7 +93,7 @@ def test_multibox_equals_onebox(backend, name, ncell, maxgrid):
     assert np.array_equal(u, u1) and np.array_equal(phi, phi1) and np.array_equal(gp, gp1)
 
 
-@pytest.mark.parametrize("host", [False, True])
+@pytest.mark.parametrize("host", [False, pytest.param(True, marks=pytest.mark.gpu)])
 def test_multibox_inflow_ghosts(backend, host):
     """Inflow ghost cells of the boxes that touch the x-lo face must reach the divergence; ghost cells over other boxes
     (stale in AMReX until FillBoundary) must not.  host=True on the GPU: host fabs in, staged per box."""
