@@ -178,7 +178,11 @@ struct MacSolver {
         for (auto& L : lev) {
             const MacLevel& d = L.d;
             if (alloc_cell(&L.res, d) || alloc_cell(&L.cor, d) || alloc_cell(&L.rescor, d)) return NP_ERR_CUDA;
-            if (alloc_d(&L.bx, d.fxs * d.n[1] * d.n[2] + 2) || alloc_d(&L.by, d.sx * (d.n[1] + 1) * d.n[2] + 2) || alloc_d(&L.bz, d.sxy * (d.n[2] + 1) + 2)) return NP_ERR_CUDA;
+            // face coefficients: one spare plane below and above (ghost planes of a slab for the one-pass smoother)
+            const long long px_ = d.fxs * d.n[1], py_ = d.sx * (d.n[1] + 1), pz_ = d.sxy;
+            if (alloc_d(&L.bx, px_ * (d.n[2] + 2) + 2) || alloc_d(&L.by, py_ * (d.n[2] + 2) + 2) || alloc_d(&L.bz, pz_ * (d.n[2] + 3) + 2)) return NP_ERR_CUDA;
+            zero(L.bx, px_ * (d.n[2] + 2) + 2); zero(L.by, py_ * (d.n[2] + 2) + 2); zero(L.bz, pz_ * (d.n[2] + 3) + 2);
+            L.bx += px_; L.by += py_; L.bz += pz_;
         }
         const MacLevel& d0 = lev[0].d;
         if (alloc_cell(&sol, d0) || alloc_cell(&rhs, d0)) return NP_ERR_CUDA;
@@ -214,7 +218,9 @@ struct MacSolver {
         np_rt::stream_sync(stream);
         if (!lev.empty()) { free_cell(sol, lev[0].d); free_cell(rhs, lev[0].d); }
         for (auto& L : lev) {
-            double* a[] = {L.bx, L.by, L.bz}; for (double* p : a) if (p) np_rt::dev_free(p);
+            if (L.bx) np_rt::dev_free(L.bx - L.d.fxs * L.d.n[1]);
+            if (L.by) np_rt::dev_free(L.by - L.d.sx * (L.d.n[1] + 1));
+            if (L.bz) np_rt::dev_free(L.bz - L.d.sxy);
             free_cell(L.res, L.d); free_cell(L.cor, L.d); free_cell(L.rescor, L.d);
         }
         lev.clear();
@@ -298,10 +304,10 @@ struct MacSolver {
     {
         const MacLevel& d = lev[l].d;
         if (opt.fused_rb_min_n <= 0 || d.n[0] < opt.fused_rb_min_n || (d.n[0] & 1)) return false;
-        // a slab can run the one-pass smoother on two ghost planes per side (the reds of the planes next to the slab are
-        // recomputed there); that needs the right-hand side on one ghost plane too and, for variable coefficients, ghost
-        // coefficient planes, which are not kept: those slabs exchange one plane before each colour and use one launch per colour
-        if (sharded(l) && !(d.const_beta && d.n[0] % RB_TX == 0 && d.n[1] % RB_TY == 0 && d.n[2] >= 4)) return false;
+        // a slab runs the one-pass smoother on two ghost planes per side (the reds of the planes next to the slab are recomputed
+        // there, from the right-hand side and the coefficients of one ghost plane); only the hoisted-index kernel knows about
+        // ghost planes, so other slabs exchange one plane before each colour and use one launch per colour
+        if (sharded(l) && !(d.n[0] % RB_TX == 0 && d.n[1] % RB_TY == 0 && d.n[2] >= 4)) return false;
         if (d.const_beta && !opt.fused_rb_const) return false;
         for (int q = 0; q < 3; ++q) if (bclo[q] == NP_BC_PERIODIC && (d.n[q] & 1)) return false;
         return true;
@@ -562,6 +568,19 @@ struct MacSolver {
                                           (size_t)plane * sizeof(double), stream);
                     }
                 }
+            }
+        }
+        if (!is_const && comm.nranks > 1) {
+            // ghost coefficient planes of the slabs (once per updateBeta): x / y faces of the neighbour's nearest cell plane; z faces:
+            // the far face of that plane (the near one is the shared face both ranks hold)
+            int lo, hi; z_neighbours(lo, hi);
+            for (size_t l = 0; l < lev.size(); ++l) if (sharded((int)l)) {
+                MacLev& L = lev[l]; const MacLevel& d = L.d;
+                const long long px_ = d.fxs * d.n[1], py_ = d.sx * (d.n[1] + 1), pz_ = d.sxy, n2 = d.n[2];
+                int rc = comm.sendrecv(comm.ctx, L.bx, px_, L.bx - px_, px_, L.bx + px_ * (n2 - 1), px_, L.bx + px_ * n2, px_, lo, hi, (void*)stream);
+                rc |= comm.sendrecv(comm.ctx, L.by, py_, L.by - py_, py_, L.by + py_ * (n2 - 1), py_, L.by + py_ * n2, py_, lo, hi, (void*)stream);
+                rc |= comm.sendrecv(comm.ctx, L.bz + pz_, pz_, L.bz - pz_, pz_, L.bz + pz_ * (n2 - 1), pz_, L.bz + pz_ * (n2 + 1), pz_, lo, hi, (void*)stream);
+                if (rc) err = NP_ERR_NCCL;
             }
         }
         stats.sigma_is_const = is_const ? 1 : 0;

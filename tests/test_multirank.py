@@ -229,6 +229,7 @@ def _mac_worker(rank, world, port, name, ncell, kw, agg_min, outdir):
     ("double_shear", (64, 16, 32), dict(prob_hi=(4.0, 1.0, 2.0)), 8, 2),     # whole 64 x 16 tiles, uniform beta: the one-pass
                                                                              # smoother on two ghost planes per slab side
     ("double_shear_walls", (64, 16, 32), dict(prob_hi=(4.0, 1.0, 2.0)), 8, 2),   # the same between walls: physical and shared z faces
+    ("rayleigh_taylor", (64, 16, 32), dict(prob_hi=(2.0, 0.5, 1.0)), 8, 2),      # variable beta: ghost coefficient planes
 ])
 def test_mac_two_ranks_match_oracle(tmp_path, name, ncell, kw, agg_min, agg_level):
     import torch.multiprocessing as mp
