@@ -500,29 +500,54 @@ __global__ void __launch_bounds__(256) k_mac_adotx(MacLevel L, MacBeta B, double
                                                    double* __restrict__ part_max, double* __restrict__ part_sum)
 {
     // a block marches through MAC_KZ planes: x(k-1), x(k), x(k+1) of a column roll through registers, so every plane is
-    // loaded once per block (not three times), and the block-wide reduction is paid once per MAC_KZ cells of a thread
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    // loaded once per block (not three times), and the block-wide reduction is paid once per MAC_KZ cells of a thread.  A
+    // thread owns an aligned pair of cells: every access away from a domain face is a 16-byte one.
+    const int i0 = 2 * (int)(blockIdx.x * blockDim.x + threadIdx.x);
     const int j = blockIdx.y * blockDim.y + threadIdx.y;
     const int k0 = blockIdx.z * MAC_KZ, k1 = min(k0 + MAC_KZ, L.n[2]);
     double vmax = 0.0, vsum = 0.0;
-    const bool on = i < L.n[0] && j < L.n[1];
+    const bool on = i0 < L.n[0] && j < L.n[1];
     if (on) {
+        const bool pair = i0 + 1 < L.n[0];
         const double off = (MODE == 1 && boff) ? *boff : 0.0;
-        long long c = mac_c(L, i, j, k0);
-        double xc = x[c];
-        double zm = mac_nb_lo(L, x, c, xc, 2, k0, L.sxy, x);
+        long long c = mac_c(L, i0, j, k0);
+        auto ld2 = [&](const double* p) { return pair ? *reinterpret_cast<const double2*>(p) : make_double2(p[0], 0.0); };
+        // both cells' neighbours across the low / high side of direction d (1: y, 2: z): one 16-byte load inside, the boundary
+        // expression cell by cell on a domain face
+        auto nb2 = [&](const double2& xc, long long cc, int d, int idx, long long st, bool hi) {
+            const bool inside = hi ? (idx < L.n[d] - 1 || L.bchi[d] == MAC_REMOTE) : (idx > 0 || L.bclo[d] == MAC_REMOTE);
+            if (inside) return ld2(x + (hi ? cc + st : cc - st));
+            double2 r;
+            r.x = hi ? mac_nb_hi(L, x, cc, xc.x, d, idx, st, x) : mac_nb_lo(L, x, cc, xc.x, d, idx, st, x);
+            r.y = pair ? (hi ? mac_nb_hi(L, x, cc + 1, xc.y, d, idx, st, x) : mac_nb_lo(L, x, cc + 1, xc.y, d, idx, st, x)) : 0.0;
+            return r;
+        };
+        double2 xc = ld2(x + c);
+        double2 zm = nb2(xc, c, 2, k0, L.sxy, false);
         for (int k = k0; k < k1; ++k, c += L.sxy) {
-            const double zp = mac_nb_hi(L, x, c, xc, 2, k, L.sxy, x);
-            const MacB6 b = mac_load_b<CB>(L, B, i, j, k);
-            const double xm = mac_nb_lo(L, x, c, xc, 0, i, 1, x), xp = mac_nb_hi(L, x, c, xc, 0, i, 1, x);
-            const double ym = mac_nb_lo(L, x, c, xc, 1, j, L.sx, x), yp = mac_nb_hi(L, x, c, xc, 1, j, L.sx, x);
-            const double ax = -L.dh[0] * (b.xp * (xp - xc) - b.xm * (xc - xm)) - L.dh[1] * (b.yp * (yp - xc) - b.ym * (xc - ym))
-                            - L.dh[2] * (b.zp * (zp - xc) - b.zm * (xc - zm));
-            double out;
-            if (MODE == 0) out = ax;
-            else out = (bb[c] - off) - ax;
-            y[c] = out;
-            if (REDUCE) { vmax = fmax(vmax, fabs(out)); vsum += out; }
+            const double2 zp = nb2(xc, c, 2, k, L.sxy, true);
+            const double2 ym = nb2(xc, c, 1, j, L.sx, false), yp = nb2(xc, c, 1, j, L.sx, true);
+            const double xm0 = mac_nb_lo(L, x, c, xc.x, 0, i0, 1, x);
+            const double xp1 = pair ? mac_nb_hi(L, x, c + 1, xc.y, 0, i0 + 1, 1, x) : 0.0;
+            const double xp0 = pair ? xc.y : mac_nb_hi(L, x, c, xc.x, 0, i0, 1, x);
+            double2 bv = make_double2(0.0, 0.0);
+            if (MODE == 1) bv = ld2(bb + c);
+            double2 out;
+            {
+                const MacB6 b = mac_load_b<CB>(L, B, i0, j, k);
+                const double ax = -L.dh[0] * (b.xp * (xp0 - xc.x) - b.xm * (xc.x - xm0)) - L.dh[1] * (b.yp * (yp.x - xc.x) - b.ym * (xc.x - ym.x))
+                                - L.dh[2] * (b.zp * (zp.x - xc.x) - b.zm * (xc.x - zm.x));
+                out.x = MODE == 0 ? ax : (bv.x - off) - ax;
+            }
+            out.y = 0.0;
+            if (pair) {
+                const MacB6 b = mac_load_b<CB>(L, B, i0 + 1, j, k);
+                const double ax = -L.dh[0] * (b.xp * (xp1 - xc.y) - b.xm * (xc.y - xc.x)) - L.dh[1] * (b.yp * (yp.y - xc.y) - b.ym * (xc.y - ym.y))
+                                - L.dh[2] * (b.zp * (zp.y - xc.y) - b.zm * (xc.y - zm.y));
+                out.y = MODE == 0 ? ax : (bv.y - off) - ax;
+                *reinterpret_cast<double2*>(y + c) = out;
+            } else y[c] = out.x;
+            if (REDUCE) { vmax = fmax(vmax, fmax(fabs(out.x), fabs(out.y))); vsum += out.x + out.y; }
             // roll (inside the chunk zp is a plain interior value; the boundary expression only occurs on the last plane)
             zm = xc; xc = zp;
         }

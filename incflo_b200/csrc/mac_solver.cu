@@ -46,7 +46,7 @@ struct MacSolver {
     static dim3 blk() { return dim3(32, 8, 1); }
     static dim3 grid_cells(const MacLevel& L) { return dim3((L.n[0] + 31) / 32, (L.n[1] + 7) / 8, L.n[2]); }
     static dim3 grid_pairs(const MacLevel& L) { return dim3(((L.n[0] + 1) / 2 + 31) / 32, (L.n[1] + 7) / 8, L.n[2]); }
-    static dim3 grid_adotx(const MacLevel& L) { return dim3((L.n[0] + 31) / 32, (L.n[1] + 7) / 8, (L.n[2] + MAC_KZ - 1) / MAC_KZ); }
+    static dim3 grid_adotx(const MacLevel& L) { return dim3(((L.n[0] + 1) / 2 + 31) / 32, (L.n[1] + 7) / 8, (L.n[2] + MAC_KZ - 1) / MAC_KZ); }
     static long long nblk(dim3 g) { return (long long)g.x * g.y * g.z; }
     static int alloc_d(double** p, long long n) { void* q = nullptr; if (np_rt::dev_malloc(&q, (size_t)n * sizeof(double))) return 1; *p = (double*)q; return 0; }
     void zero(double* p, long long n) { np_rt::memset_async(p, 0, (size_t)n * sizeof(double), stream); }
