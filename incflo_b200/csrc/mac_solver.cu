@@ -794,16 +794,16 @@ int mp_create(mp_handle** h, const np_geom* geom, int nboxes_global, const np_bo
     return NP_OK;
 }
 int mp_set_bc(mp_handle* h, const int lo[3], const int hi[3]) { return h ? h->S.set_bc(lo, hi) : NP_ERR_INVALID; }
-int mp_update_beta(mp_handle* h, const np_fab beta[3]) { return h && beta ? h->S.update_beta(beta) : NP_ERR_INVALID; }
+int mp_update_beta(mp_handle* h, const np_fab beta[3]) { return h && beta && h->S.lbox.size() == 1 ? h->S.update_beta(beta) : NP_ERR_INVALID; }
 int mp_project(mp_handle* h, np_fab umac[3], np_fab* mac_phi, double rtol, double atol, void* cuda_stream, np_stats* out)
 {
-    if (!h || !umac) return NP_ERR_INVALID;
+    if (!h || !umac || h->S.lbox.size() != 1) return NP_ERR_INVALID;      // several boxes: mp_project_boxes
     h->S.stream = (np_stream_t)cuda_stream;
     const int rc = h->S.project(umac, mac_phi, rtol, atol);
     if (out) *out = h->S.stats;
     return rc;
 }
-int mp_get_fluxes(mp_handle* h, np_fab flux[3], const np_fab* phi) { return h && flux ? h->S.get_fluxes(flux, phi) : NP_ERR_INVALID; }
+int mp_get_fluxes(mp_handle* h, np_fab flux[3], const np_fab* phi) { return h && flux && h->S.lbox.size() == 1 ? h->S.get_fluxes(flux, phi) : NP_ERR_INVALID; }
 int mp_update_beta_boxes(mp_handle* h, int nlocal, const np_fab* bx, const np_fab* by, const np_fab* bz)
 {
     if (!h || !bx || !by || !bz) return NP_ERR_INVALID;
