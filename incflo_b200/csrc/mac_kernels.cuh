@@ -533,15 +533,25 @@ __global__ void __launch_bounds__(256) k_mac_adotx(MacLevel L, MacBeta B, double
             double2 bv = make_double2(0.0, 0.0);
             if (MODE == 1) bv = ld2(bb + c);
             double2 out;
+            MacB6 b0, b1;
+            if (CB || !pair) { b0 = mac_load_b<CB>(L, B, i0, j, k); b1 = b0; }
+            else {      // the coefficients of both cells with 16-byte loads: three x faces, two rows of y faces, two planes of z faces
+                const long long fx = mac_fx(L, i0, j, k), fy = mac_fy(L, i0, j, k), fz = mac_fz(L, i0, j, k);
+                const double2 bx01 = *reinterpret_cast<const double2*>(B.bx + fx); const double bx2 = B.bx[fx + 2];
+                const double2 bym = *reinterpret_cast<const double2*>(B.by + fy), byp = *reinterpret_cast<const double2*>(B.by + fy + L.sx);
+                const double2 bzm = *reinterpret_cast<const double2*>(B.bz + fz), bzp = *reinterpret_cast<const double2*>(B.bz + fz + L.sxy);
+                b0.xm = bx01.x; b0.xp = bx01.y; b0.ym = bym.x; b0.yp = byp.x; b0.zm = bzm.x; b0.zp = bzp.x;
+                b1.xm = bx01.y; b1.xp = bx2;    b1.ym = bym.y; b1.yp = byp.y; b1.zm = bzm.y; b1.zp = bzp.y;
+            }
             {
-                const MacB6 b = mac_load_b<CB>(L, B, i0, j, k);
+                const MacB6& b = b0;
                 const double ax = -L.dh[0] * (b.xp * (xp0 - xc.x) - b.xm * (xc.x - xm0)) - L.dh[1] * (b.yp * (yp.x - xc.x) - b.ym * (xc.x - ym.x))
                                 - L.dh[2] * (b.zp * (zp.x - xc.x) - b.zm * (xc.x - zm.x));
                 out.x = MODE == 0 ? ax : (bv.x - off) - ax;
             }
             out.y = 0.0;
             if (pair) {
-                const MacB6 b = mac_load_b<CB>(L, B, i0 + 1, j, k);
+                const MacB6& b = b1;
                 const double ax = -L.dh[0] * (b.xp * (xp1 - xc.y) - b.xm * (xc.y - xc.x)) - L.dh[1] * (b.yp * (yp.y - xc.y) - b.ym * (xc.y - ym.y))
                                 - L.dh[2] * (b.zp * (zp.y - xc.y) - b.zm * (xc.y - zm.y));
                 out.y = MODE == 0 ? ax : (bv.y - off) - ax;
@@ -581,11 +591,21 @@ __global__ void __launch_bounds__(256) k_mac_resid_restrict(MacLevel Lc, MacLeve
             const long long c = mac_c(L, i, j, k);
             const double2 xv = *reinterpret_cast<const double2*>(x + c);
             const double2 bv = *reinterpret_cast<const double2*>(bb + c);
+            MacB6 bp[2];
+            if (CB) { bp[0] = mac_load_b<CB>(L, B, i, j, k); bp[1] = bp[0]; }
+            else {      // the coefficients of the pair with 16-byte loads
+                const long long fx = mac_fx(L, i, j, k), fy = mac_fy(L, i, j, k), fz = mac_fz(L, i, j, k);
+                const double2 bx01 = *reinterpret_cast<const double2*>(B.bx + fx); const double bx2 = B.bx[fx + 2];
+                const double2 bym = *reinterpret_cast<const double2*>(B.by + fy), byp = *reinterpret_cast<const double2*>(B.by + fy + L.sx);
+                const double2 bzm = *reinterpret_cast<const double2*>(B.bz + fz), bzp = *reinterpret_cast<const double2*>(B.bz + fz + L.sxy);
+                bp[0].xm = bx01.x; bp[0].xp = bx01.y; bp[0].ym = bym.x; bp[0].yp = byp.x; bp[0].zm = bzm.x; bp[0].zp = bzp.x;
+                bp[1].xm = bx01.y; bp[1].xp = bx2;    bp[1].ym = bym.y; bp[1].yp = byp.y; bp[1].zm = bzm.y; bp[1].zp = bzp.y;
+            }
 #pragma unroll
             for (int di = 0; di < 2; ++di) {
                 const double xc = di ? xv.y : xv.x;
                 const long long cc = c + di;
-                const MacB6 b = mac_load_b<CB>(L, B, i + di, j, k);
+                const MacB6 b = bp[di];
                 const double xm = di ? xv.x : mac_nb_lo(L, x, cc, xc, 0, i, 1, x);
                 const double xp = di ? mac_nb_hi(L, x, cc, xc, 0, i + 1, 1, x) : xv.y;
                 const double ym = mac_nb_lo(L, x, cc, xc, 1, j, L.sx, x), yp = mac_nb_hi(L, x, cc, xc, 1, j, L.sx, x);
