@@ -224,8 +224,8 @@ def _mac_worker(rank, world, port, name, ncell, kw, agg_min, outdir):
 
 @pytest.mark.parametrize("name,ncell,kw,agg_min,agg_level", [
     ("double_shear", (16, 16, 64), dict(prob_hi=(1.0, 1.0, 4.0)), 16, 2),     # uniform beta, periodic z: every slab face is remote
-    ("rayleigh_taylor", (16, 16, 32), {}, 8, 2),                             # variable beta (coefficient gather), walls in z
-    ("rayleigh_taylor", (16, 16, 32), {}, 4, 3),                             # two sharded coarse levels before the gather
+    ("rayleigh_taylor", (16, 16, 32), {}, 4, 3),                             # variable beta (coefficient gather), walls in z,
+                                                                             # two sharded coarse levels before the gather
     ("double_shear", (64, 16, 32), dict(prob_hi=(4.0, 1.0, 2.0)), 8, 2),     # whole 64 x 16 tiles, uniform beta: the one-pass
                                                                              # smoother on two ghost planes per slab side
     ("double_shear_walls", (64, 16, 32), dict(prob_hi=(4.0, 1.0, 2.0)), 8, 2),   # the same between walls: physical and shared z faces
