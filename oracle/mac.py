@@ -154,3 +154,29 @@ class MacOracle:
         x = np.zeros_like(b)
         it = self.L.mor_bottom_solve(self.h, _p(b), _p(x))
         return x, it
+
+    # ---- general ABecLaplacian solve (scalar diffusion; SURVEY.md 8(f) row 3 groundwork, CPU only) ----
+    def set_scalars(self, alpha, beta):
+        self.L.mor_set_scalars(self.h, C.c_double(alpha), C.c_double(beta))
+
+    def set_acoef(self, a):
+        a = np.ascontiguousarray(a, dtype=np.float64)
+        self.L.mor_set_acoef(self.h, _p(a))
+
+    def solve_abec(self, rhs, rtol, atol, bcvals=None):
+        """(alpha a - beta div b grad) phi = rhs; phi starts from set_phi() (or 0); bcvals: dict face -> 2-D array of Dirichlet
+        values, faces 'xlo','ylo','zlo','xhi','yhi','zhi', arrays indexed [higher transverse dir][lower transverse dir]."""
+        r = np.ascontiguousarray(rhs, dtype=np.float64)
+        self.L.mor_set_rhs(self.h, _p(r))
+        keep, ptrs = [], []
+        for f in ("xlo", "ylo", "zlo", "xhi", "yhi", "zhi"):
+            v = (bcvals or {}).get(f)
+            if v is None:
+                ptrs.append(None)
+            else:
+                a = np.ascontiguousarray(v, dtype=np.float64)
+                keep.append(a)
+                ptrs.append(_p(a))
+        st = Stats()
+        self.L.mor_solve_abec(self.h, C.c_double(rtol), C.c_double(atol), *ptrs, C.byref(st))
+        return st

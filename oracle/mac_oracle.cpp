@@ -43,6 +43,7 @@ struct Level {
     int n[3]; double dxinv[3];
     long long sx, sy, ntot;
     std::vector<double> bx, by, bz;
+    std::vector<double> a;      // cell coefficient of the alpha term (MLABecLaplacian::setACoeffs), empty: none
     long long c(int i, int j, int k) const { return (i + 1) + sx * ((j + 1) + sy * (long long)(k + 1)); }
     long long fx(int i, int j, int k) const { return i + (long long)(n[0] + 1) * (j + (long long)n[1] * k); }
     long long fy(int i, int j, int k) const { return i + (long long)n[0] * (j + (long long)(n[1] + 1) * k); }
@@ -64,6 +65,7 @@ typedef std::vector<double> V;
 
 struct Solver {
     Options opt; std::vector<Level> lev; int bclo[3], bchi[3]; bool singular = true;
+    double alpha = 0.0, bscal = 1.0;      // MLABecLaplacian::setScalars(alpha, beta): (alpha a - beta div b grad) phi = rhs
     std::vector<V> res, cor, rescor;
     V sol, rhs, umac[3];
     int bottom_iters = 0; bool bicg_failed_switch = false;
@@ -126,11 +128,12 @@ struct Solver {
     void adotx(int l, V& y, const V& x) const
     {
         const Level& L = lev[l];
-        const double dhx = L.dxinv[0] * L.dxinv[0], dhy = L.dxinv[1] * L.dxinv[1], dhz = L.dxinv[2] * L.dxinv[2];
+        const double dhx = bscal * L.dxinv[0] * L.dxinv[0], dhy = bscal * L.dxinv[1] * L.dxinv[1], dhz = bscal * L.dxinv[2] * L.dxinv[2];
+        const bool ha = alpha != 0.0 && !L.a.empty();
         pfor(L.n[2], (long long)L.n[0] * L.n[1], [&](int k) {
             for (int j = 0; j < L.n[1]; ++j) for (int i = 0; i < L.n[0]; ++i) {
                 const long long c = L.c(i, j, k);
-                y[c] = -dhx * (L.bx[L.fx(i + 1, j, k)] * (x[c + 1] - x[c]) - L.bx[L.fx(i, j, k)] * (x[c] - x[c - 1]))
+                y[c] = (ha ? alpha * L.a[c] * x[c] : 0.0) - dhx * (L.bx[L.fx(i + 1, j, k)] * (x[c + 1] - x[c]) - L.bx[L.fx(i, j, k)] * (x[c] - x[c - 1]))
                        - dhy * (L.by[L.fy(i, j + 1, k)] * (x[c + L.sx] - x[c]) - L.by[L.fy(i, j, k)] * (x[c] - x[c - L.sx]))
                        - dhz * (L.bz[L.fz(i, j, k + 1)] * (x[c + L.sx * L.sy] - x[c]) - L.bz[L.fz(i, j, k)] * (x[c] - x[c - L.sx * L.sy]));
             }
@@ -148,7 +151,8 @@ struct Solver {
     void gsrb(int l, V& phi, const V& b, int redblack) const
     {
         const Level& L = lev[l];
-        const double dhx = L.dxinv[0] * L.dxinv[0], dhy = L.dxinv[1] * L.dxinv[1], dhz = L.dxinv[2] * L.dxinv[2];
+        const double dhx = bscal * L.dxinv[0] * L.dxinv[0], dhy = bscal * L.dxinv[1] * L.dxinv[1], dhz = bscal * L.dxinv[2] * L.dxinv[2];
+        const bool ha = alpha != 0.0 && !L.a.empty();
         const double omega = 1.15;
         const double f0 = bc_fac(0, 0, L.n[0]), f3 = bc_fac(0, 1, L.n[0]), f1 = bc_fac(1, 0, L.n[1]), f4 = bc_fac(1, 1, L.n[1]),
                      f2 = bc_fac(2, 0, L.n[2]), f5 = bc_fac(2, 1, L.n[2]);
@@ -160,7 +164,7 @@ struct Solver {
                              bzm = L.bz[L.fz(i, j, k)], bzp = L.bz[L.fz(i, j, k + 1)];
                 const double cf0 = i == 0 ? f0 : 0.0, cf3 = i == L.n[0] - 1 ? f3 : 0.0, cf1 = j == 0 ? f1 : 0.0, cf4 = j == L.n[1] - 1 ? f4 : 0.0,
                              cf2 = k == 0 ? f2 : 0.0, cf5 = k == L.n[2] - 1 ? f5 : 0.0;
-                const double gamma = dhx * (bxm + bxp) + dhy * (bym + byp) + dhz * (bzm + bzp);
+                const double gamma = (ha ? alpha * L.a[c] : 0.0) + dhx * (bxm + bxp) + dhy * (bym + byp) + dhz * (bzm + bzp);
                 const double g_m_d = gamma - (dhx * (bxm * cf0 + bxp * cf3) + dhy * (bym * cf1 + byp * cf4) + dhz * (bzm * cf2 + bzp * cf5));
                 const double rho = dhx * (bxm * phi[c - 1] + bxp * phi[c + 1]) + dhy * (bym * phi[c - L.sx] + byp * phi[c + L.sx])
                                  + dhz * (bzm * phi[c - sz] + bzp * phi[c + sz]);
@@ -198,6 +202,7 @@ struct Solver {
     {
         for (size_t l = 1; l < lev.size(); ++l) {
             Level& C = lev[l]; const Level& F = lev[l - 1];
+            if (!F.a.empty()) { C.a = C.make(); restriction((int)l, C.a, F.a); }      // MLABecLaplacian::averageDownCoeffs: a by average_down
             for (int k = 0; k < C.n[2]; ++k) for (int j = 0; j < C.n[1]; ++j) for (int i = 0; i <= C.n[0]; ++i) {
                 double s = 0; for (int c = 0; c < 2; ++c) for (int b = 0; b < 2; ++b) s += F.bx[F.fx(2 * i, 2 * j + b, 2 * k + c)];
                 C.bx[C.fx(i, j, k)] = 0.25 * s;
@@ -216,9 +221,10 @@ struct Solver {
     void normalize(int l, V& x) const
     {
         const Level& L = lev[l];
-        const double dhx = L.dxinv[0] * L.dxinv[0], dhy = L.dxinv[1] * L.dxinv[1], dhz = L.dxinv[2] * L.dxinv[2];
+        const double dhx = bscal * L.dxinv[0] * L.dxinv[0], dhy = bscal * L.dxinv[1] * L.dxinv[1], dhz = bscal * L.dxinv[2] * L.dxinv[2];
+        const bool ha = alpha != 0.0 && !L.a.empty();
         for (int k = 0; k < L.n[2]; ++k) for (int j = 0; j < L.n[1]; ++j) for (int i = 0; i < L.n[0]; ++i)
-            x[L.c(i, j, k)] /= dhx * (L.bx[L.fx(i, j, k)] + L.bx[L.fx(i + 1, j, k)]) + dhy * (L.by[L.fy(i, j, k)] + L.by[L.fy(i, j + 1, k)])
+            x[L.c(i, j, k)] /= (ha ? alpha * L.a[L.c(i, j, k)] : 0.0) + dhx * (L.bx[L.fx(i, j, k)] + L.bx[L.fx(i + 1, j, k)]) + dhy * (L.by[L.fy(i, j, k)] + L.by[L.fy(i, j + 1, k)])
                              + dhz * (L.bz[L.fz(i, j, k)] + L.bz[L.fz(i, j, k + 1)]);
     }
     template <class F> void for_valid(const Level& L, F f) const
@@ -406,6 +412,36 @@ struct Solver {
         st.t_solve = std::chrono::duration<double>(t2 - t1).count();
         st.t_total = std::chrono::duration<double>(t3 - t0).count();
     }
+    // A general MLABecLaplacian solve (the scalar diffusion solves of the reference, SURVEY.md 8(f) row 3:
+    // /root/reference/src/diffusion/DiffusionScalarOp.cpp:189-250 - alpha = 1, beta = dt, a = rho, b = eta on faces,
+    // setLevelBC(phi) with the Dirichlet values in phi's ghost cells).  `sol` holds the initial guess, `rhs` the right-hand
+    // side; bcv[f] (f = x-lo, y-lo, z-lo, x-hi, y-hi, z-hi) the Dirichlet values on the faces of side f or null (0).
+    // MLMG evaluates the first residual with the inhomogeneous ghost  c0 phi0 + c1 phi1 + c_bc value  and iterates on the
+    // homogeneous correction equation; moving the boundary term to the right-hand side once is the same thing.
+    void solve_abec(double rtol, double atol, Stats& st, const double* const bcv[6])
+    {
+        singular = true;
+        for (int d = 0; d < 3; ++d) if (bclo[d] == DIRICHLET || bchi[d] == DIRICHLET) singular = false;
+        if (alpha != 0.0 && !lev[0].a.empty()) singular = false;
+        average_down_beta();
+        const Level& L = lev[0];
+        for (int d = 0; d < 3; ++d) for (int side = 0; side < 2; ++side) {
+            const double* v = bcv[d + 3 * side];
+            if (!v || (side ? bchi[d] : bclo[d]) != DIRICHLET) continue;
+            const int a = (d + 1) % 3, b = (d + 2) % 3;
+            const double cbc = std::min(L.n[d] + 1, opt.maxorder) >= 3 ? 8.0 / 3.0 : 2.0;      // weight of the wall value in the ghost
+            const double dh = bscal * L.dxinv[d] * L.dxinv[d];
+            // face arrays of side values are indexed [q][p] with p the lower of the two transverse directions (x fastest)
+            const int t0 = std::min(a, b), t1 = std::max(a, b);
+            for (int q = 0; q < L.n[t1]; ++q) for (int p = 0; p < L.n[t0]; ++p) {
+                int idx[3]; idx[d] = side ? L.n[d] - 1 : 0; idx[t0] = p; idx[t1] = q;
+                int fidx[3] = {idx[0], idx[1], idx[2]}; if (side) fidx[d] += 1;
+                const double bf = d == 0 ? L.bx[L.fx(fidx[0], fidx[1], fidx[2])] : d == 1 ? L.by[L.fy(fidx[0], fidx[1], fidx[2])] : L.bz[L.fz(fidx[0], fidx[1], fidx[2])];
+                rhs[L.c(idx[0], idx[1], idx[2])] += dh * bf * cbc * v[p + (long long)L.n[t0] * q];
+            }
+        }
+        solve(rtol, atol, st);
+    }
     void scatter(int l, V& dst, const double* src) const
     {
         const Level& L = lev[l]; long long q = 0;
@@ -473,6 +509,19 @@ void mor_project(void* h, double rtol, double atol, int have_guess, mor_stats* o
     out->rhs_norm0 = st.rhs_norm0; out->res_norm0 = st.res_norm0; out->res_norm_final = st.res_norm_final;
     std::memcpy(out->res_history, st.res_history, sizeof(st.res_history));
     out->t_setup = st.t_setup; out->t_solve = st.t_solve; out->t_total = st.t_total;
+}
+// ---- general ABecLaplacian solve (scalar diffusion; CPU groundwork only, no CUDA counterpart yet) ----
+void mor_set_scalars(void* h, double alpha, double beta) { auto* s = (Solver*)h; s->alpha = alpha; s->bscal = beta; }
+void mor_set_acoef(void* h, const double* a) { auto* s = (Solver*)h; s->lev[0].a = s->lev[0].make(); s->scatter(0, s->lev[0].a, a); }
+void mor_set_rhs(void* h, const double* r) { auto* s = (Solver*)h; s->scatter(0, s->rhs, r); }
+void mor_solve_abec(void* h, double rtol, double atol, const double* xlo, const double* ylo, const double* zlo, const double* xhi,
+                    const double* yhi, const double* zhi, mor_stats* out)
+{
+    auto* s = (Solver*)h; Stats st; const double* bcv[6] = {xlo, ylo, zlo, xhi, yhi, zhi};
+    s->solve_abec(rtol, atol, st, bcv);
+    out->n_vcycles = st.n_vcycles; out->bottom_iters_total = st.bottom_iters_total; out->status = st.status; out->n_levels = st.n_levels;
+    out->rhs_norm0 = st.rhs_norm0; out->res_norm0 = st.res_norm0; out->res_norm_final = st.res_norm_final;
+    std::memcpy(out->res_history, st.res_history, sizeof(st.res_history));
 }
 // kernel-level hooks
 void mor_apply(void* h, int l, const double* x, double* y)
