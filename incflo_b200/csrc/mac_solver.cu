@@ -653,6 +653,7 @@ struct MacSolver {
     int get_fluxes(np_fab flux[3], const np_fab* phi)
     {
         if (!have_beta || !phi || !phi->p) return NP_ERR_STATE;
+        err = 0;
         const MacLevel& d0 = lev[0].d;
         FabView fv[3], pv; bool st[3], pst;
         for (int d = 0; d < 3; ++d) { if (!flux[d].p) return NP_ERR_INVALID; if (!import(flux[d], 0, d, d, false, &fv[d], &st[d])) return NP_ERR_CUDA; }
@@ -664,6 +665,7 @@ struct MacSolver {
         else NP_LAUNCH(false, (k_mac_fluxes<false, false>), grid_cells(d0), blk(), 0, stream, d0, lev[0].beta(), (const double*)tmp, fv[0], fv[1], fv[2]);
         for (int d = 0; d < 3; ++d) export_back(flux[d], fv[d], st[d]);
         np_rt::stream_sync(stream);
+        if (err) return err;
         return np_rt::last_error() ? NP_ERR_CUDA : NP_OK;
     }
     // ---- several boxes (amr.max_grid_size chops the level): the boxes' fabs are gathered into domain-shaped device fabs,
