@@ -557,7 +557,7 @@ __global__ void __launch_bounds__(256) k_mac_adotx(MacLevel L, MacBeta B, double
                 out.y = MODE == 0 ? ax : (bv.y - off) - ax;
                 *reinterpret_cast<double2*>(y + c) = out;
             } else y[c] = out.x;
-            if (REDUCE) { vmax = fmax(vmax, fmax(fabs(out.x), fabs(out.y))); vsum += out.x + out.y; }
+            if (REDUCE) { vmax = np_absmax(np_absmax(vmax, out.x), out.y); vsum += out.x + out.y; }
             // roll (inside the chunk zp is a plain interior value; the boundary expression only occurs on the last plane)
             zm = xc; xc = zp;
         }

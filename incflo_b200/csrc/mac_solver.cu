@@ -490,6 +490,8 @@ struct MacSolver {
         const double res_target = std::max(atol, std::max(rtol, 1e-16) * max_norm);
         stats.rhs_norm0 = rhsnorm0; stats.res_norm0 = resnorm0; stats.n_vcycles = 0; stats.status = 0; stats.res_norm_final = resnorm0;
         stats.n_levels = (int)lev.size(); stats.bottom_iters_total = 0;
+        // NaN / Inf in umac, beta or the initial guess: AMReX's MLMG fails; never report success on it
+        if (!(resnorm0 == resnorm0) || !(rhsnorm0 == rhsnorm0) || std::isinf(resnorm0) || std::isinf(rhsnorm0)) { stats.status = NP_ERR_DIVERGED; return NP_ERR_DIVERGED; }
         if (!(resnorm0 > res_target)) return NP_OK;
         bool converged = false;
         int rc = NP_OK;
@@ -503,6 +505,7 @@ struct MacSolver {
             if (iter < 128) stats.res_history[iter] = rn;
             stats.n_vcycles = iter + 1; stats.res_norm_final = rn;
             if (opt.verbose >= 2) fprintf(stderr, "MLMG: Iteration %3d Fine resid/bnorm = %.6e\n", iter + 1, rn / max_norm);
+            if (err) { rc = err; break; }                 // a failed exchange / collective: stop issuing them
             if (rn <= res_target) { converged = true; break; }
             if (!(rn <= 1e20 * max_norm)) { rc = NP_ERR_DIVERGED; break; }
         }

@@ -77,6 +77,12 @@ __device__ __forceinline__ double np_warp_max(double v) {
     return v;
 }
 // result valid in every thread; fixed summation order -> deterministic
+// running max of |v| that does not lose a NaN: fmax() drops NaN operands, so a NaN entry becomes +Inf, which every later
+// fmax keeps and the host turns into NP_ERR_DIVERGED (AMReX's MLMG fails on such input)
+__device__ __forceinline__ double np_absmax(double m, double v) {
+    const double a = fabs(v);
+    return (a == a) ? fmax(m, a) : INFINITY;
+}
 template <bool IS_MAX> __device__ __forceinline__ double np_block_reduce(double v) {
     __shared__ double red[33];
     const int tid = threadIdx.x + blockDim.x * (threadIdx.y + blockDim.y * threadIdx.z);
@@ -1007,7 +1013,7 @@ __device__ __forceinline__ void st_run(const LevelDev& L, const StCoef& C, doubl
                         }
                         y[o] = v;
                         if (REDUCE) {
-                            tmax = fmax(tmax, fabs(v));
+                            tmax = np_absmax(tmax, v);
                             tsum += ((FULL || wone) ? wz : np_wgt_xy(L, gi + a, gj + r) * wz) * v;      // boundary threads redo the weight
                         }
                     }

@@ -618,7 +618,7 @@ int NpSolver::solve(double rtol, double atol)
     const double max_norm = rhsnorm0 >= resnorm0 ? rhsnorm0 : resnorm0;
     const double res_target = std::max(atol, std::max(rtol, 1e-16) * max_norm);
     stats.rhs_norm0 = rhsnorm0; stats.res_norm0 = resnorm0; stats.res_norm_final = resnorm0;
-    if (!(resnorm0 == resnorm0)) { stats.status = NP_ERR_DIVERGED; return stats.status; }
+    if (!(resnorm0 == resnorm0) || std::isinf(resnorm0)) { stats.status = NP_ERR_DIVERGED; return stats.status; }     // NaN / Inf in u* or sigma
     if (resnorm0 <= res_target) return NP_OK;
     bool converged = false;
     for (int iter = 0; iter < opt.maxiter; ++iter) {

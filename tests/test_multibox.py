@@ -97,6 +97,8 @@ def test_multibox_equals_onebox(backend, name, ncell, maxgrid):
 def test_multibox_inflow_ghosts(backend, host):
     """Inflow ghost cells of the boxes that touch the x-lo face must reach the divergence; ghost cells over other boxes
     (stale in AMReX until FillBoundary) must not.  host=True on the GPU: host fabs in, staged per box."""
+    if host and backend["like"] == "numpy":
+        pytest.skip("host fabs are a case of the CUDA build only (the emulation has one kind of memory)")
     rng = np.random.default_rng(5)
     ncell = (32, 16, 8)
     bclo, bchi = (2, 2, 0), (1, 2, 0)

@@ -117,3 +117,14 @@ def test_copy_out_and_host_fabs(backend, host_out):
         capi.check(drv.L, drv.L.np_copy_phi(drv.h, 0, C.byref(fp.c())))
         capi.check(drv.L, drv.L.np_copy_gradphi(drv.h, 0, C.byref(fg.c())))
         assert np.array_equal(fp.numpy_valid()[0], phi) and np.array_equal(fg.numpy_valid(), gp)
+
+
+def test_project_nan_input_is_reported(backend):
+    """A NaN in u* must come back as NP_ERR_DIVERGED, not as a converged zero-cycle solve (fmax-based norms drop NaNs)."""
+    ncell = (16, 16, 16)
+    prob = problems.PROBLEMS["taylor_green"](ncell)
+    vel = prob["vel"].copy()
+    vel[1, 3, 4, 5] = np.nan
+    drv = nphelp.Driver(ncell, prob["prob_lo"], prob["prob_hi"], prob["bclo"], prob["bchi"], **backend)
+    st, *_ = drv.project(vel, prob["sigma"], 1e-11, 1e-14, raise_on_fail=False)
+    assert st.status == 6
