@@ -9,7 +9,7 @@ Two comparisons each (SURVEY.md 8(c) "parity definition"):
   * oracle with the SAME smoother ordering (TILED): same V-cycle and bottom-iteration counts, residual history,
     u / grad(phi) / phi-minus-mean within 1e-10 relative L2 at rtol 1e-11;
   * oracle with the REFERENCE's ordering (lexicographic Gauss-Seidel, AMReX-default 32^3 boxes) at a tolerance both
-    reach (rtol 1e-13; 1e-12 from 256^3 up, where the fp64 round-off floor of the residual sits just above 1e-13):
+    reach (rtol 1e-13; 3e-12 at 256^3 and 1e-11 at 512^3, where the fp64 round-off floor of the residual is 1.2e-12 / ~5e-12):
     fields within 1e-10, V-cycle counts within +-1 (both counts are printed and, with NP_PARITY_LOG set, logged).
 The oracle is the checker here, never the thing measured.  Nothing reads /root/reference at run time."""
 import json
@@ -104,7 +104,8 @@ def test_config_same_ordering(tag, name, ncell, kw):
 def test_config_vs_reference_ordering(tag, name, ncell, kw):
     from oracle.oracle import LEX, chop_boxes
     prob = problems.PROBLEMS[name](ncell, **kw)
-    rtol = 1e-12 if ncell[0] * ncell[1] * ncell[2] >= 256 ** 3 else 1e-13
+    # measured on the B200: at 256^3 the relative residual stalls at 1.2e-12 (fp64 round-off of A phi grows like 1/h^2)
+    rtol = 3e-12 if ncell[0] * ncell[1] * ncell[2] >= 256 ** 3 else 1e-13
     g = _gpu_project(prob, ncell, rtol, 0.0)
     o = _oracle_project(prob, ncell, rtol, 0.0, smoother=LEX, boxes=chop_boxes(ncell, 32))
     eu, eg, ep = _compare(g, o, tag + f" vs oracle LEX / 32^3 boxes rtol {rtol:g}")
@@ -123,9 +124,9 @@ def test_512_vs_reference_ordering(name):
     ncell = (512, 512, 512)
     kw = dict(zwave=True) if name == "double_shear" else dict(prob_hi=(0.5, 0.5, 0.5))
     prob = problems.PROBLEMS[name](ncell, **kw)
-    g = _gpu_project(prob, ncell, 1e-12, 0.0)
-    o = _oracle_project(prob, ncell, 1e-12, 0.0, smoother=LEX, boxes=chop_boxes(ncell, 32))
-    eu, eg, ep = _compare(g, o, f"{name} 512^3 vs oracle LEX / 32^3 boxes rtol 1e-12")
+    g = _gpu_project(prob, ncell, 1e-11, 0.0)
+    o = _oracle_project(prob, ncell, 1e-11, 0.0, smoother=LEX, boxes=chop_boxes(ncell, 32))
+    eu, eg, ep = _compare(g, o, f"{name} 512^3 vs oracle LEX / 32^3 boxes rtol 1e-11")
     assert g["st"].status == 0 and o["st"].status == 0
     assert abs(g["st"].n_vcycles - o["st"].n_vcycles) <= 1
     assert eu <= TOL and eg <= TOL and ep <= TOL
