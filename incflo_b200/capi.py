@@ -12,7 +12,7 @@ LIB_PATH = os.path.join(_HERE, "libnodalproj.so")
 
 NP_BC_PERIODIC, NP_BC_DIRICHLET, NP_BC_NEUMANN = 0, 1, 2
 NP_BOTTOM_BICGCG, NP_BOTTOM_BICGSTAB, NP_BOTTOM_CG, NP_BOTTOM_SMOOTHER = 0, 1, 2, 3
-NP_OK, NP_ERR_INVALID, NP_ERR_NO_DEVICE, NP_ERR_CUDA, NP_ERR_NCCL, NP_ERR_NOT_CONVERGED, NP_ERR_DIVERGED, NP_ERR_STATE = range(8)
+NP_OK, NP_ERR_INVALID, NP_ERR_NO_DEVICE, NP_ERR_CUDA, NP_ERR_NCCL, NP_ERR_NOT_CONVERGED, NP_ERR_DIVERGED, NP_ERR_STATE, NP_ERR_TOO_LARGE = range(9)
 
 
 class np_box(C.Structure):
@@ -71,7 +71,7 @@ SYMBOLS = ["np_default_options", "np_create", "np_set_bc", "np_project", "np_app
            "np_copy_phi", "np_copy_gradphi", "np_destroy", "np_strerror", "np_num_levels", "np_level_ncell",
            "np_last_stats", "np_set_sigma", "np_get_sigma", "np_apply", "np_smooth", "np_restrict",
            "np_interp_add", "np_divu", "np_mknewu", "np_bottom_solve", "np_vcycle", "np_dot",
-           "np_nccl_unique_id", "np_nccl_comm_create", "np_nccl_comm_destroy", "np_is_device_pointer"]
+           "np_nccl_unique_id", "np_nccl_comm_create", "np_nccl_comm_destroy", "np_is_device_pointer", "np_apply_noalloc"]
 
 _libs = {}
 
@@ -110,6 +110,7 @@ def load(path=None):
     L.np_set_sigma.argtypes = [C.c_void_p, C.POINTER(np_fab)]
     L.np_get_sigma.argtypes = [C.c_void_p, C.c_int, C.POINTER(np_fab)]
     L.np_apply.argtypes = [C.c_void_p, C.c_int, C.POINTER(np_fab), C.POINTER(np_fab)]
+    L.np_apply_noalloc.argtypes = [C.c_void_p, C.c_int, C.POINTER(np_fab), C.POINTER(np_fab)]
     L.np_smooth.argtypes = [C.c_void_p, C.c_int, C.POINTER(np_fab), C.POINTER(np_fab), C.c_int]
     L.np_restrict.argtypes = [C.c_void_p, C.c_int, C.POINTER(np_fab), C.POINTER(np_fab)]
     L.np_interp_add.argtypes = [C.c_void_p, C.c_int, C.POINTER(np_fab), C.POINTER(np_fab)]

@@ -3,4 +3,5 @@
 #include "np_capi.cu"
 #include "np_capi_hooks.cu"
 #include "np_comm.cu"
+#include "np_noalloc.cu"
 #include "mac_solver.cu"

@@ -142,6 +142,7 @@ const char* np_strerror(int code)
     case NP_ERR_NOT_CONVERGED: return "MLMG failed to converge";
     case NP_ERR_DIVERGED: return "MLMG failing so lets stop here";
     case NP_ERR_STATE: return "nodalproj: call order";
+    case NP_ERR_TOO_LARGE: return "nodalproj: level too large for the fixed no-allocation scratch (np_apply_noalloc: 2 padded nodal arrays must fit NP_NOALLOC_MAX_DOUBLES = 2^20 doubles)";
     default: return "nodalproj: unknown error";
     }
 }

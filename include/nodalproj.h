@@ -52,7 +52,8 @@ enum {
     NP_ERR_NCCL = 4,
     NP_ERR_NOT_CONVERGED = 5,  /* MLMG: "failed to converge" after maxiter V-cycles */
     NP_ERR_DIVERGED = 6,       /* residual > 1e20 * max_norm, or NaN */
-    NP_ERR_STATE = 7           /* call order (e.g. np_get_phi before np_project) */
+    NP_ERR_STATE = 7,          /* call order (e.g. np_get_phi before np_project) */
+    NP_ERR_TOO_LARGE = 8       /* np_apply_noalloc: the level does not fit the fixed scratch (NP_NOALLOC_MAX_DOUBLES) */
 };
 
 /* The solver's whole option surface = the reference's "nodal_proj.*" keys (+ LPInfo) and the knobs
@@ -168,6 +169,15 @@ int np_last_stats(np_handle* h, np_stats* out);
 int np_set_sigma(np_handle* h, const np_fab* sigma);                                   /* K8 */
 int np_get_sigma(np_handle* h, int mglev, np_fab* dst);                                /* dst: cell, 1 comp */
 int np_apply(np_handle* h, int mglev, const np_fab* x, np_fab* y);                     /* K2  y = A x */
+/* np_apply without any device allocation (np_apply cudaMallocs two staging arrays per call).  NO COUNTERPART IN THE
+ * REFERENCE: added for callers that cannot call cudaMalloc (CUDA-graph capture,
+ * tight serving loops, harnesses that forbid it).  The two internal-layout temporaries live in one file-scope device
+ * array of NP_NOALLOC_MAX_DOUBLES doubles (8 MiB per GPU that loads the library, held until exit); a level whose padded
+ * nodal array (n0+3 rounded up to even) x (n1+3) x (n2+3) exceeds half of that (above 77^3 cells; 64^3 fits) is refused with
+ * NP_ERR_TOO_LARGE.  x, y: DEVICE fabs (host fabs: NP_ERR_INVALID); one rank or a replicated level.  Same result as
+ * np_apply bit for bit.  All calls share the array: calls that overlap on one GPU race; it is cleared at every call. */
+#define NP_NOALLOC_MAX_DOUBLES (1 << 20)
+int np_apply_noalloc(np_handle* h, int mglev, const np_fab* x, np_fab* y);
 int np_smooth(np_handle* h, int mglev, np_fab* x, const np_fab* rhs, int ncalls);      /* K3  ncalls x Fsmooth */
 int np_restrict(np_handle* h, int cmglev, const np_fab* fine, np_fab* crse);           /* K4 */
 int np_interp_add(np_handle* h, int fmglev, np_fab* fine, const np_fab* crse);         /* K5 */

@@ -4,4 +4,5 @@
 #include "../../incflo_b200/csrc/np_capi.cu"
 #include "../../incflo_b200/csrc/np_capi_hooks.cu"
 #include "np_comm_emu.cpp"
+#include "../../incflo_b200/csrc/np_noalloc.cu"
 #include "../../incflo_b200/csrc/mac_solver.cu"
