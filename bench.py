@@ -184,106 +184,150 @@ def workload_config(args, G, sample=None):
 # ---------------------------------------------------------------------------------------------------
 # GPU arm
 # ---------------------------------------------------------------------------------------------------
-def run_gpu(args):
-    import ctypes as C
-    import torch
-    import torch.distributed as dist
-    from incflo_b200 import capi, problems
-    from incflo_b200.projector import Fab, Geometry, LPInfo, NodalProjector
+class _Ctx:
+    """Per-process state of the GPU arm: device, library, communicator."""
 
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device; incflo_b200 has no CPU fallback (use --impl reference for the CPU arm)")
-    torch.cuda.set_device(local)
-    dev = f"cuda:{local}"
-    L = capi.load()
-    comm = None
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=torch.device(dev))
-        idbuf = torch.zeros(128, dtype=torch.uint8)
-        if rank == 0:
-            raw = (C.c_ubyte * 128)()
-            capi.check(L, L.np_nccl_unique_id(raw))
-            idbuf = torch.tensor(list(raw), dtype=torch.uint8)
-        idd = idbuf.to(dev)
-        dist.broadcast(idd, 0)
-        raw = (C.c_ubyte * 128)(*idd.cpu().tolist())
-        cptr = C.c_void_p()
-        capi.check(L, L.np_nccl_comm_create(C.byref(cptr), raw, rank, world))
-        comm = cptr.value
+    def __init__(self):
+        import ctypes as C
+        import torch
+        import torch.distributed as dist
+        from incflo_b200 import capi
+        self.C, self.torch, self.dist, self.capi = C, torch, dist, capi
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py: no CUDA device; incflo_b200 has no CPU fallback (use --impl reference for the CPU arm)")
+        torch.cuda.set_device(self.local)
+        self.dev = f"cuda:{self.local}"
+        self.L = capi.load()
+        self.comm = None
+        if self.world > 1:
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            dist.init_process_group("nccl", device_id=torch.device(self.dev))
+            idbuf = torch.zeros(128, dtype=torch.uint8)
+            if self.rank == 0:
+                raw = (C.c_ubyte * 128)()
+                capi.check(self.L, self.L.np_nccl_unique_id(raw))
+                idbuf = torch.tensor(list(raw), dtype=torch.uint8)
+            idd = idbuf.to(self.dev)
+            dist.broadcast(idd, 0)
+            raw = (C.c_ubyte * 128)(*idd.cpu().tolist())
+            cptr = C.c_void_p()
+            capi.check(self.L, self.L.np_nccl_comm_create(C.byref(cptr), raw, self.rank, self.world))
+            self.comm = cptr.value
+        self.stream = torch.cuda.current_stream().cuda_stream
 
-    n, G, g = args.ncell, world, args.vel_ngrow
-    ncell = (n, n, n * G)
-    prob_hi = (1.0, 1.0, float(G))
-    koff = rank * n
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def max_over_ranks(self, v):
+        t = self.torch.tensor([v], dtype=self.torch.float64, device=self.dev)
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def close(self):
+        if self.world > 1:
+            if self.comm:
+                self.L.np_nccl_comm_destroy(self.C.c_void_p(self.comm))
+            self.dist.destroy_process_group()
+
+
+def _nodal_problem(ctx, workload, nloc, G, g, world=None, rank=None):
+    """u* (pristine, with g ghost layers), sigma fab, BCs, geometry pieces of one rank's n^3 (or nloc) slab."""
+    import numpy as np
+    from incflo_b200 import problems
+    from incflo_b200.projector import Fab
+    torch, dev = ctx.torch, ctx.dev
+    rank = ctx.rank if rank is None else rank
+    nx, ny, nz = nloc
+    ncell = (nx, ny, nz * G)
+    prob_hi = (1.0, float(ny) / nx, float(nz * G) / nx)          # isotropic cells, x extent 1
+    koff = rank * nz
     bclo = bchi = (0, 0, 0)
-    if args.workload == "rayleigh_taylor":
-        # BASELINE configs[3]: variable density (ratio 4), sigma = dt/rho, periodic x/y, walls in z; unit-cube cells
-        import numpy as np
-        pr = problems.rayleigh_taylor(ncell, prob_hi=prob_hi, koff=koff, nz_local=n)
-        vel0 = torch.zeros((3, n + 2 * g, n + 2 * g, n + 2 * g), dtype=torch.float64, device=dev)
-        vel0[:, g:g + n, g:g + n, g:g + n] = torch.from_numpy(pr["vel"]).to(dev)
+    if workload == "rayleigh_taylor":
+        pr = problems.rayleigh_taylor(ncell, prob_hi=prob_hi, koff=koff, nz_local=nz)
+        vel0 = torch.zeros((3, nz + 2 * g, ny + 2 * g, nx + 2 * g), dtype=torch.float64, device=dev)
+        vel0[:, g:g + nz, g:g + ny, g:g + nx] = torch.from_numpy(pr["vel"]).to(dev)
         sig = Fab(torch.from_numpy(np.ascontiguousarray(pr["sigma"][None])).to(dev), 0)
         bclo, bchi = pr["bclo"], pr["bchi"]
-        del pr
     else:
-        vel0 = problems.double_shear_torch(ncell, prob_hi, koff, n, dev, ngrow=g)     # pristine u*
-        sig = Fab(torch.ones((1, n, n, n), dtype=torch.float64, device=dev), 0)
-    vel = Fab(vel0.clone(), g)
-    geom = Geometry(ncell, (0, 0, 0), prob_hi, [b == 0 for b in bclo])
-    boxes = [((0, 0, r * n), (n - 1, n - 1, (r + 1) * n - 1)) for r in range(G)]
-    P = NodalProjector(vel, sig, geom, LPInfo(), boxes=boxes, rank=rank, nranks=world, nccl_comm=comm, lib=L,
-                       profile_kernels=1, smooth_zchunk=args.smooth_zchunk, verbose=args.verbose,
-                       **({"agg_min_local_nz": args.agg_min_local_nz} if args.agg_min_local_nz > 0 else {}),
-                       **({"overlap_halo": 0} if args.no_overlap else {}), **({"p2p_halo": 0} if args.no_p2p else {}))
-    P.setDomainBC(bclo, bchi)
-    dof = n * n * n * G
-    stream = torch.cuda.current_stream().cuda_stream
+        vel0 = problems.double_shear_torch(ncell, prob_hi, koff, nz, dev, ngrow=g)
+        sig = Fab(torch.ones((1, nz, ny, nx), dtype=torch.float64, device=dev), 0)
+    return dict(ncell=ncell, prob_hi=prob_hi, bclo=bclo, bchi=bchi, vel0=vel0, sig=sig)
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
+
+def _make_projector(ctx, args, pb, nloc, G, vel, rank=None, nranks=None, comm="ctx", **extra):
+    from incflo_b200.projector import Geometry, LPInfo, NodalProjector
+    rank = ctx.rank if rank is None else rank
+    nranks = ctx.world if nranks is None else nranks
+    nx, ny, nz = nloc
+    geom = Geometry(pb["ncell"], (0, 0, 0), pb["prob_hi"], [b == 0 for b in pb["bclo"]])
+    boxes = [((0, 0, r * nz), (nx - 1, ny - 1, (r + 1) * nz - 1)) for r in range(G)]
+    kw = dict(profile_kernels=1, smooth_zchunk=args.smooth_zchunk, verbose=args.verbose)
+    if args.agg_min_local_nz > 0:
+        kw["agg_min_local_nz"] = args.agg_min_local_nz
+    if args.no_overlap:
+        kw["overlap_halo"] = 0
+    if args.no_p2p:
+        kw["p2p_halo"] = 0
+    kw.update(extra)
+    P = NodalProjector(vel, pb["sig"], geom, LPInfo(), boxes=boxes, rank=rank, nranks=nranks,
+                       nccl_comm=ctx.comm if comm == "ctx" else comm, lib=ctx.L, **kw)
+    P.setDomainBC(pb["bclo"], pb["bchi"])
+    return P
+
+
+def _measure_nodal(ctx, args, workload, n, steps, warmup, e2e_steps, ctor=False, clocks=None):
+    """One workload: device-resident timed loop (value), host-fab loop (e2e), optional constructor cost.  All ranks call it."""
+    import time as _t
+    from incflo_b200.projector import Fab
+    torch, C, capi, L, dev = ctx.torch, ctx.C, ctx.capi, ctx.L, ctx.dev
+    G, g = ctx.world, args.vel_ngrow
+    nloc = (n, n, n)
+    pb = _nodal_problem(ctx, workload, nloc, G, g)
+    vel0, sig = pb["vel0"], pb["sig"]
+    vel = Fab(vel0.clone(), g)
+    L.np_cache_clear()
+    torch.cuda.synchronize()
+    t0 = _t.perf_counter()
+    P = _make_projector(ctx, args, pb, nloc, G, vel)
+    torch.cuda.synchronize()
+    ms_create_cold = 1e3 * (_t.perf_counter() - t0)
+    dof = n * n * n * G
 
     def step():
         vel.data.copy_(vel0)
-        return P.project(RTOL, ATOL, stream=stream)
+        return P.project(RTOL, ATOL, stream=ctx.stream)
 
-    clocks = ClockSampler(local)
-    if rank == 0:
-        clocks.start()                        # nvidia-smi needs a moment to come up: start it before the warm-up
-    for _ in range(args.warmup):
+    for _ in range(warmup):
         step()
-    barrier()
-    clocks.mark()
+    ctx.barrier()
+    if clocks:
+        clocks.mark()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     vcycles = launches = 0
-    ms_smooth = n_smooth = 0.0
-    ms_solve = 0.0
+    ms_smooth = n_smooth = ms_solve = 0.0
     hist = None
-    for _ in range(args.steps):
+    for _ in range(steps):
         st = step()
         vcycles += st.n_vcycles; launches += st.kernel_launches
         ms_smooth += st.ms_smooth0; n_smooth += st.n_smooth0; ms_solve += st.ms_solve
         hist = [st.res_history[i] / max(st.rhs_norm0, 1e-300) for i in range(st.n_vcycles)]
     e1.record()
-    barrier()
-    ms = e0.elapsed_time(e1)
-    clk = clocks.stop() if rank == 0 else None
-    t = torch.tensor([ms], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.item())
-    const_sigma = bool(st.sigma_is_const)
-    levels = st.n_levels
+    ctx.barrier()
+    ms = ctx.max_over_ranks(e0.elapsed_time(e1))
+    clk = clocks.stop() if clocks else None
+    out = dict(dof=dof, ms=ms, vcycles=vcycles, launches=int(launches), ms_smooth=ms_smooth, n_smooth=n_smooth, ms_solve=ms_solve,
+               hist=hist, const_sigma=bool(st.sigma_is_const), levels=st.n_levels, steps=steps, warmup=warmup, clocks=clk,
+               ms_create_cold=ms_create_cold)
 
     # ---- e2e: host (pinned) fabs through the same C-ABI call; H2D + D2H inside the timed region ----
-    e2e = None
-    if not args.no_e2e:
+    if e2e_steps > 0:
         hv0 = vel0.cpu()                                            # pristine host copy (pageable)
         hv = Fab(torch.empty_like(hv0).pin_memory(), g)
         hs = Fab(sig.data.cpu().pin_memory(), 0)
@@ -294,57 +338,210 @@ def run_gpu(args):
         d2h = hv.data.numel() * 8 + hphi.data.numel() * 8 + hgp.data.numel() * 8
         tot_ms, tot_vc = 0.0, 0
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        for it in range(1 + args.e2e_steps):
+        for it in range(1 + e2e_steps):
             hv.data.copy_(hv0)                                      # untimed host-side reset of the in/out buffer
-            barrier()
+            ctx.barrier()
             a.record()
-            st2 = P.project(RTOL, ATOL, stream=stream)
+            st2 = P.project(RTOL, ATOL, stream=ctx.stream)
             capi.check(L, L.np_copy_phi(P.h, 0, C.byref(hphi.c())))
             capi.check(L, L.np_copy_gradphi(P.h, 0, C.byref(hgp.c())))
             b.record()
-            barrier()
+            ctx.barrier()
             if it >= 1:
-                tm = torch.tensor([a.elapsed_time(b)], dtype=torch.float64, device=dev)
-                if world > 1:
-                    dist.all_reduce(tm, op=dist.ReduceOp.MAX)
-                tot_ms += float(tm.item()); tot_vc += st2.n_vcycles
-        e2e = {"value": dof * tot_vc / (tot_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-               "steps": args.e2e_steps, "ms_per_step": tot_ms / args.e2e_steps}
+                tot_ms += ctx.max_over_ranks(a.elapsed_time(b)); tot_vc += st2.n_vcycles
+        out["e2e"] = {"value": dof * tot_vc / (tot_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                      "steps": e2e_steps, "ms_per_step": tot_ms / e2e_steps}
+        if ctor:
+            # What incflo::ApplyProjection does every time step (reference :148-166): construct, setDomainBC, project, read phi
+            # and grad(phi), destroy.  Wall clock around the whole sequence (cudaMalloc / IPC / all-gather are host-synchronous),
+            # max over ranks; first with the handle cache cleared before every construction, then with it (the default).
+            def full_call():
+                Pn = _make_projector(ctx, args, pb, nloc, G, hv)
+                Pn.sigma = hs
+                stn = Pn.project(RTOL, ATOL, stream=ctx.stream)
+                capi.check(L, L.np_copy_phi(Pn.h, 0, C.byref(hphi.c())))
+                capi.check(L, L.np_copy_gradphi(Pn.h, 0, C.byref(hgp.c())))
+                Pn.close()
+                return stn.n_vcycles
+            P.close()
+            res = {}
+            for tag, clear in (("cold", True), ("cached", False)):
+                tt, vc = 0.0, 0
+                for it in range(1 + e2e_steps):
+                    hv.data.copy_(hv0)
+                    if clear:
+                        L.np_cache_clear()
+                    ctx.barrier()
+                    t0 = _t.perf_counter()
+                    v = full_call()
+                    torch.cuda.synchronize()
+                    dt = ctx.max_over_ranks(1e3 * (_t.perf_counter() - t0))
+                    if it >= 1:
+                        tt += dt; vc += v
+                res[tag] = {"value": dof * vc / (tt * 1e-3), "ms_per_step": tt / e2e_steps}
+            # construction alone, device-synchronised wall clock
+            L.np_cache_clear()
+            tc = []
+            for it in range(3):
+                torch.cuda.synchronize(); ctx.barrier()
+                t0 = _t.perf_counter()
+                Pn = _make_projector(ctx, args, pb, nloc, G, hv)
+                torch.cuda.synchronize()
+                t1 = _t.perf_counter()
+                Pn.close()
+                torch.cuda.synchronize()
+                tc.append((ctx.max_over_ranks(1e3 * (t1 - t0)), ctx.max_over_ranks(1e3 * (_t.perf_counter() - t1))))
+            out["e2e_with_ctor"] = {"unit": UNIT, "value": res["cached"]["value"], "ms_per_step": res["cached"]["ms_per_step"],
+                                    "value_cache_off": res["cold"]["value"], "ms_per_step_cache_off": res["cold"]["ms_per_step"],
+                                    "ms_create_first": tc[0][0], "ms_create_cached": min(tc[1][0], tc[2][0]), "ms_destroy_cached": min(tc[1][1], tc[2][1]),
+                                    "note": "np_create + np_set_bc + np_project + np_copy_phi/gradphi + np_destroy per step with host fabs "
+                                            "(what incflo::ApplyProjection does every time step); wall clock, max over ranks; "
+                                            "cache_off = np_cache_clear before every construction"}
+            L.np_cache_clear()
+            P = None
+    if P is not None:
+        P.close()
+    L.np_cache_clear()
+    del vel, vel0, sig, pb
+    torch.cuda.empty_cache()
+    return out
 
+
+def _roofline(out, n, G, peak, peak_src):
+    const_sigma = out["const_sigma"]
+    nodes = (n + 1) ** 3
+    per_node = 2 * (24 if const_sigma else 32)                  # 2 GS sweeps x (read cor, rhs[, sigma]; write cor)
+    alg_bytes = per_node * nodes
+    avg_ms = out["ms_smooth"] / max(out["n_smooth"], 1)
+    achieved = alg_bytes / (avg_ms * 1e-3) / 1e9 if avg_ms > 0 else 0.0
+    compulsory = (24 if const_sigma else 32) * nodes            # what the fused 2-sweep pass must move
+    bpd = 342 if const_sigma else 432
+    roof = {"bound": "hbm", "kernel": f"k_gs2<{'const' if const_sigma else 'variable'} sigma> (fused 2-sweep Gauss-Seidel), level 0",
+            "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+            "traffic": read_traffic(const_sigma) if n == 512 else None,
+            "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes, "avg_launch_ms": avg_ms,
+            "launches_timed": int(out["n_smooth"]), "share_of_step": out["ms_smooth"] / out["ms"],
+            "fused_pass_bytes_per_launch": compulsory,
+            "frac_fused_pass": compulsory / (avg_ms * 1e-3) / 1e9 / peak if avg_ms > 0 else 0.0,
+            "vcycle_algorithmic": {"bytes_per_dof": bpd,
+                                   "achieved_gbs": bpd * out["dof"] / G * out["vcycles"] / (out["ms_solve"] * 1e-3) / 1e9,
+                                   "note": "SURVEY 8(d) accounting over the solve phase, per GPU"}}
+    roof["vcycle_algorithmic"]["frac"] = roof["vcycle_algorithmic"]["achieved_gbs"] / peak
+    roof["vcycle_algorithmic"]["frac_of_8TBs_datasheet"] = roof["vcycle_algorithmic"]["achieved_gbs"] / 8000.0
+    return roof
+
+
+def _multi_gpu_parity(ctx, args):
+    """Hardware check of the sharded path before anything is timed (N > 1): a 128 x 128 x (64 N) problem of both workloads is
+    projected on N z-slabs (peer-memory or NCCL halos, replicated coarse levels) and the same global problem on rank 0
+    alone; u, grad(phi) and phi-minus-mean must agree to 1e-10 relative L2 (north_star tolerance; both solves run to a
+    tolerance near the fp64 floor so that the comparison is not limited by where each stops)."""
+    from incflo_b200.projector import Fab
+    torch, dist, dev, G = ctx.torch, ctx.dist, ctx.dev, ctx.world
+    nloc, g, rtol = (128, 128, 64), 1, 1e-12
+    rec = {"problem": f"128x128x{64 * G} cells in {G} z-slabs vs the same problem on one GPU, rtol {rtol:g}", "tolerance": 1e-10,
+           "halo": "nccl" if args.no_p2p else "p2p (CUDA IPC peer memory; falls back to NCCL if a rank cannot map its neighbours)"}
+    worst = 0.0
+    for workload in ("double_shear", "rayleigh_taylor"):
+        pb = _nodal_problem(ctx, workload, nloc, G, g)
+        vel = Fab(pb["vel0"].clone(), g)
+        P = _make_projector(ctx, args, pb, nloc, G, vel, profile_kernels=0)
+        st = P.project(rtol, 0.0, stream=ctx.stream, raise_on_fail=False)
+        phi = P.getPhi().valid()[0].contiguous().clone()            # local nodes k = 0 .. nz (the top plane duplicates the next rank's first)
+        gp = P.getGradPhi().valid().contiguous().clone()
+        u = vel.valid().contiguous().clone()
+        P.close()
+        parts = {}
+        for name, t in (("u", u), ("gp", gp), ("phi", phi[:-1].contiguous())):
+            bufs = [torch.empty_like(t) for _ in range(G)] if ctx.rank == 0 else None
+            dist.gather(t, bufs, dst=0)
+            if ctx.rank == 0:
+                parts[name] = torch.cat(bufs, dim=-3)
+        hist_n = [st.res_history[i] / max(st.rhs_norm0, 1e-300) for i in range(st.n_vcycles)]
+        w = {"vcycles_sharded": st.n_vcycles, "status_sharded": st.status}
+        if ctx.rank == 0:
+            pb1 = _nodal_problem(ctx, workload, (nloc[0], nloc[1], nloc[2] * G), 1, g, rank=0)
+            vel1 = Fab(pb1["vel0"].clone(), g)
+            P1 = _make_projector(ctx, args, pb1, (nloc[0], nloc[1], nloc[2] * G), 1, vel1, rank=0, nranks=1, comm=None, profile_kernels=0)
+            st1 = P1.project(rtol, 0.0, stream=ctx.stream, raise_on_fail=False)
+            phi1 = P1.getPhi().valid()[0][:-1]
+            gp1 = P1.getGradPhi().valid()
+            u1 = vel1.valid()
+
+            def l2(a, b):
+                return float((a - b).norm() / b.norm())
+            e = {"u": l2(parts["u"], u1), "gradphi": l2(parts["gp"], gp1),
+                 "phi_minus_mean": l2(parts["phi"] - parts["phi"].mean(), phi1 - phi1.mean())}
+            hist_1 = [st1.res_history[i] / max(st1.rhs_norm0, 1e-300) for i in range(st1.n_vcycles)]
+            w.update(vcycles_one_gpu=st1.n_vcycles, status_one_gpu=st1.status, rel_l2=e,
+                     rel_res_history_sharded=hist_n, rel_res_history_one_gpu=hist_1)
+            worst = max(worst, max(e.values()))
+            if st.status != 0 or st1.status != 0:
+                worst = float("inf")
+            P1.close()
+        rec[workload] = w
+        ctx.L.np_cache_clear()
+    rec["max_rel_l2"] = worst
+    ok = torch.tensor([1.0 if (ctx.rank != 0 or worst <= 1e-10) else 0.0], device=dev)
+    dist.broadcast(ok, 0)
+    rec["pass"] = bool(ok.item() > 0)
+    return rec
+
+
+def run_gpu(args):
+    ctx = _Ctx()
+    rank, world = ctx.rank, ctx.world
+    n, G = args.ncell, world
+    parity = None
+    if world > 1 and not args.no_parity:
+        parity = _multi_gpu_parity(ctx, args)
+        if not parity["pass"]:
+            if rank == 0:
+                print(json.dumps({"metric": METRIC, "error": "multi-GPU parity check failed", "multi_gpu_parity": parity}), flush=True)
+            ctx.close()
+            raise SystemExit(3)
+    clocks = ClockSampler(ctx.local) if rank == 0 else None
+    if clocks:
+        clocks.start()                        # nvidia-smi needs a moment to come up: start it before the warm-up
+    out = _measure_nodal(ctx, args, args.workload, n, args.steps, args.warmup, 0 if args.no_e2e else args.e2e_steps,
+                         ctor=not args.no_e2e, clocks=clocks)
+    # the other BASELINE configs as sub-records of the same line (N = 1 only): configs[3] Rayleigh-Taylor 512^3 (variable sigma)
+    # and configs[1] 256^3; `value` / `config` stay configs[2]
+    extra = {}
+    if world == 1 and not args.no_workloads and args.workload == "double_shear" and n == 512:
+        for tag, wl, nn, stp, wu in (("rayleigh_taylor_512", "rayleigh_taylor", 512, 2, 3), ("double_shear_256", "double_shear", 256, 3, 3)):
+            extra[tag] = (nn, _measure_nodal(ctx, args, wl, nn, stp, wu, 0))
     if rank == 0:
         peak, peak_src = read_peaks()
-        nodes = (n + 1) ** 3
-        per_node = 2 * (24 if const_sigma else 32)                  # 2 GS sweeps x (read cor, rhs[, sigma]; write cor)
-        alg_bytes = per_node * nodes
-        avg_ms = ms_smooth / max(n_smooth, 1)
-        achieved = alg_bytes / (avg_ms * 1e-3) / 1e9 if avg_ms > 0 else 0.0
-        compulsory = (24 if const_sigma else 32) * nodes            # what the fused 2-sweep pass must move
-        roof = {"bound": "hbm", "kernel": f"k_gs2<{'const' if const_sigma else 'variable'} sigma> (fused 2-sweep Gauss-Seidel), level 0",
-                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": read_traffic(const_sigma),
-                "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes, "avg_launch_ms": avg_ms,
-                "launches_timed": int(n_smooth), "share_of_step": ms_smooth / ms,
-                "fused_pass_bytes_per_launch": compulsory,
-                "frac_fused_pass": compulsory / (avg_ms * 1e-3) / 1e9 / peak if avg_ms > 0 else 0.0,
-                "vcycle_algorithmic": {"bytes_per_dof": 342 if const_sigma else 432,
-                                       "achieved_gbs": (342 if const_sigma else 432) * dof / G * vcycles / (ms_solve * 1e-3) / 1e9,
-                                       "note": "SURVEY 8(d) accounting over the solve phase, per GPU"}}
-        roof["vcycle_algorithmic"]["frac"] = roof["vcycle_algorithmic"]["achieved_gbs"] / peak
-        line = {"metric": METRIC, "value": dof * vcycles / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        ms, vcycles = out["ms"], out["vcycles"]
+        line = {"metric": METRIC, "value": out["dof"] * vcycles / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_config(args, G),
-                "vcycles_per_step": vcycles / args.steps, "mg_levels": levels, "ms_per_vcycle": ms / vcycles,
-                "ms_solve_per_vcycle": ms_solve / vcycles, "rel_res_history": hist,
-                "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof}
+                "vcycles_per_step": vcycles / args.steps, "mg_levels": out["levels"], "ms_per_vcycle": ms / vcycles,
+                "ms_solve_per_vcycle": out["ms_solve"] / vcycles, "rel_res_history": out["hist"],
+                "clocks": out["clocks"], "e2e": out.get("e2e"), "gpu_launches": out["launches"],
+                "launches_per_vcycle": out["launches"] / vcycles,
+                "roofline": _roofline(out, n, G, peak, peak_src)}
+        if "e2e_with_ctor" in out:
+            line["e2e_with_ctor"] = out["e2e_with_ctor"]
+        if parity:
+            line["multi_gpu_parity"] = parity
+        if extra:
+            line["workloads"] = {}
+            for tag, (nn, o) in extra.items():
+                r = _roofline(o, nn, 1, peak, peak_src)
+                line["workloads"][tag] = {
+                    "value": o["dof"] * o["vcycles"] / (o["ms"] * 1e-3), "unit": UNIT, "steps": o["steps"], "warmup": o["warmup"],
+                    "vcycles": o["vcycles"] / o["steps"], "ms_per_step": o["ms"] / o["steps"], "ms_per_vcycle": o["ms"] / o["vcycles"],
+                    "ms_solve_per_vcycle": o["ms_solve"] / o["vcycles"], "mg_levels": o["levels"], "rel_res_history": o["hist"],
+                    "launches_per_vcycle": o["launches"] / o["vcycles"],
+                    "roofline": {k: r[k] for k in ("kernel", "frac", "frac_fused_pass", "avg_launch_ms", "share_of_step", "vcycle_algorithmic")}}
         if world == 1 and not args.no_cpu:
             r = cpu_projection(args.cpu_ncell, 1, 0)
             line["cpu_baseline"] = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port",
                                     "sample": r["sample"], "vcycles": r["vcycles"]}
         print(json.dumps(line), flush=True)
-    P.close()
-    if world > 1:
-        if comm:
-            L.np_nccl_comm_destroy(C.c_void_p(comm))
-        dist.destroy_process_group()
+    ctx.close()
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -577,6 +774,8 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-workloads", action="store_true", help="skip the Rayleigh-Taylor 512^3 / double shear 256^3 sub-records (N = 1)")
+    ap.add_argument("--no-parity", action="store_true", help="skip the multi-GPU parity check that precedes the timed region (N > 1)")
     ap.add_argument("--smooth-zchunk", type=int, default=0, help="experiment knob: fixed smoother z-chunk on every level (0: the level rule)")
     ap.add_argument("--agg-min-local-nz", type=int, default=0, help="experiment knob: replicate MG levels whose slab is thinner than this (0: library default)")
     ap.add_argument("--no-p2p", action="store_true", help="experiment knob: halo exchange through ncclSend/ncclRecv instead of peer memory")

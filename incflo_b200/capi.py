@@ -71,7 +71,7 @@ SYMBOLS = ["np_default_options", "np_create", "np_set_bc", "np_project", "np_app
            "np_copy_phi", "np_copy_gradphi", "np_destroy", "np_strerror", "np_num_levels", "np_level_ncell",
            "np_last_stats", "np_set_sigma", "np_get_sigma", "np_apply", "np_smooth", "np_restrict",
            "np_interp_add", "np_divu", "np_mknewu", "np_bottom_solve", "np_vcycle", "np_dot",
-           "np_nccl_unique_id", "np_nccl_comm_create", "np_nccl_comm_destroy", "np_is_device_pointer", "np_apply_noalloc"]
+           "np_nccl_unique_id", "np_nccl_comm_create", "np_nccl_comm_destroy", "np_is_device_pointer", "np_apply_noalloc", "np_cache_clear"]
 
 _libs = {}
 

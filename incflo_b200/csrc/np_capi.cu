@@ -1,7 +1,60 @@
 // np_capi.cu — the extern "C" boundary declared in include/nodalproj.h.
 #include "np_solver.h"
 #include "np_kernels.cuh"
+#include <cstring>
+#include <mutex>
 #include <new>
+#include <vector>
+
+// ------------------------------------------------------------------------------------------------
+// Handle cache.  The reference builds a fresh NodalProjector inside every ApplyProjection
+// (/root/reference/src/projection/incflo_apply_nodal_projection.cpp:134, 148-151), i.e. np_create / np_destroy run every
+// time step.  np_create allocates ~9 GB at 512^3, opens CUDA-IPC mappings and all-gathers handles; none of that
+// depends on anything but (geometry, BoxArray, DistributionMapping, rank layout, communicator, options).  np_destroy
+// therefore parks the handle (one slot per process) and np_create hands it out again when the key matches exactly; the
+// handle is reset to the state a fresh one has, so the API stays stateless.  A different key evicts (really destroys)
+// the parked handle.  np_cache_clear() / NP_HANDLE_CACHE=0 release / disable it.  With several ranks create / destroy /
+// clear are collective, as they already were (peer-memory mappings of the neighbours stay valid only while every rank
+// keeps its handle).
+// ------------------------------------------------------------------------------------------------
+namespace {
+struct NpCacheKey {
+    np_geom g; std::vector<np_box> boxes; std::vector<int> owner; int rank, nranks; void* comm; np_options o; int device;
+    // field by field: the structs have padding holes that a caller's stack copy leaves undefined
+    static bool same(const np_geom& a, const np_geom& b) {
+        for (int d = 0; d < 3; ++d)
+            if (a.ncell[d] != b.ncell[d] || a.prob_lo[d] != b.prob_lo[d] || a.prob_hi[d] != b.prob_hi[d] || a.periodic[d] != b.periodic[d]) return false;
+        return true;
+    }
+    static bool same(const np_options& a, const np_options& b) {
+        return a.max_coarsening_level == b.max_coarsening_level && a.maxiter == b.maxiter && a.bottom_maxiter == b.bottom_maxiter
+            && a.num_pre_smooth == b.num_pre_smooth && a.num_post_smooth == b.num_post_smooth && a.num_final_smooth == b.num_final_smooth
+            && a.bottom_solver == b.bottom_solver && a.verbose == b.verbose && a.bottom_verbose == b.bottom_verbose
+            && a.bottom_rtol == b.bottom_rtol && a.bottom_atol == b.bottom_atol && a.smooth_zchunk == b.smooth_zchunk
+            && a.interp_sigma_weighted == b.interp_sigma_weighted && a.bottom_normalize == b.bottom_normalize
+            && a.agg_min_local_nz == b.agg_min_local_nz && a.use_graph == b.use_graph && a.const_sigma_fastpath == b.const_sigma_fastpath
+            && a.profile_kernels == b.profile_kernels && a.overlap_halo == b.overlap_halo && a.p2p_halo == b.p2p_halo;
+    }
+    bool operator==(const NpCacheKey& b) const {
+        if (!same(g, b.g) || !same(o, b.o) || boxes.size() != b.boxes.size() || owner != b.owner) return false;
+        for (size_t q = 0; q < boxes.size(); ++q)
+            for (int d = 0; d < 3; ++d) if (boxes[q].lo[d] != b.boxes[q].lo[d] || boxes[q].hi[d] != b.boxes[q].hi[d]) return false;
+        return rank == b.rank && nranks == b.nranks && comm == b.comm && device == b.device;
+    }
+};
+std::mutex g_cache_mu;
+np_handle* g_cached = nullptr;
+bool cache_enabled() { const char* e = std::getenv("NP_HANDLE_CACHE"); return !(e && e[0] == '0'); }
+int current_device()
+{
+#ifdef NP_EMU
+    return 0;
+#else
+    int d = -1; if (cudaGetDevice(&d) != cudaSuccess) { cudaGetLastError(); return -1; } return d;
+#endif
+}
+void really_destroy(np_handle* h) { if (!h) return; h->S.destroy(); delete (NpCacheKey*)h->cache_key; delete h; }
+} // namespace
 
 
 
@@ -23,15 +76,31 @@ int np_create(np_handle** h, const np_geom* geom, int nboxes_global, const np_bo
 {
     if (!h || !geom || !all_boxes || !owner_rank || nranks < 1 || my_rank < 0 || my_rank >= nranks) return NP_ERR_INVALID;
     np_options o; if (opt) o = *opt; else np_default_options(&o);
+    NpCacheKey* key = new (std::nothrow) NpCacheKey();
+    if (!key) return NP_ERR_INVALID;
+    key->g = *geom;
+    key->boxes.assign(all_boxes, all_boxes + nboxes_global); key->owner.assign(owner_rank, owner_rank + nboxes_global);
+    key->rank = my_rank; key->nranks = nranks; key->comm = nccl_comm_or_null; key->o = o; key->device = current_device();
+    if (cache_enabled()) {
+        std::lock_guard<std::mutex> lk(g_cache_mu);
+        if (g_cached && *(NpCacheKey*)g_cached->cache_key == *key) {
+            np_handle* q = g_cached; g_cached = nullptr;
+            delete key;
+            q->S.reset_for_reuse();
+            *h = q;
+            return NP_OK;
+        }
+    }
     np_handle* p = new (std::nothrow) np_handle();
-    if (!p) return NP_ERR_INVALID;
+    if (!p) { delete key; return NP_ERR_INVALID; }
+    p->cache_key = key;
     NpComm c;
     if (nranks > 1) {
         np_comm_fill_nccl(c, nccl_comm_or_null);
-        if (!c.sendrecv) { delete p; return NP_ERR_NCCL; }
+        if (!c.sendrecv) { delete key; delete p; return NP_ERR_NCCL; }
     }
     int rc = p->S.create(geom, nboxes_global, all_boxes, owner_rank, my_rank, nranks, c, &o);
-    if (rc) { p->S.destroy(); delete p; return rc; }
+    if (rc) { really_destroy(p); return rc; }
     *h = p;
     return NP_OK;
 }
@@ -129,7 +198,25 @@ int np_is_device_pointer(const void* p)
 #endif
 }
 
-void np_destroy(np_handle* h) { if (h) { h->S.destroy(); delete h; } }
+void np_destroy(np_handle* h)
+{
+    if (!h) return;
+    np_handle* evict = h;
+    if (cache_enabled() && h->cache_key && !h->S.err) {
+        np_rt::stream_sync(h->S.stream);
+        std::lock_guard<std::mutex> lk(g_cache_mu);
+        evict = g_cached; g_cached = h;
+    }
+    really_destroy(evict);
+}
+
+int np_cache_clear(void)
+{
+    np_handle* q;
+    { std::lock_guard<std::mutex> lk(g_cache_mu); q = g_cached; g_cached = nullptr; }
+    really_destroy(q);
+    return NP_OK;
+}
 
 const char* np_strerror(int code)
 {

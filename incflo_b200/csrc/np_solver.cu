@@ -202,6 +202,43 @@ void NpSolver::destroy()
     prof_ev.clear();
 }
 
+// A cached handle is handed out again by np_create (np_capi.cu): every array is cleared and every flag reset, so the handle
+// is in exactly the state create() leaves, without the cudaMalloc / IPC / all-gather work (cudaMemsetAsync of ~9 GB at
+// 512^3 takes a few milliseconds, the allocations it replaces a few hundred).
+void NpSolver::reset_for_reuse()
+{
+    stream = 0;
+    for (int d = 0; d < 3; ++d) { last_bclo[d] = bclo[d]; last_bchi[d] = bchi[d]; }
+    reuse_pending = true;            // see ensure_clean()
+    for (auto& L : lev) { L.cor_ghost_clean = false; L.d.const_sigma = 0; L.d.sigma0 = 1.0; }
+    for (int d = 0; d < 3; ++d) bclo[d] = bchi[d] = geom.periodic[d] ? NP_BC_PERIODIC : NP_BC_NEUMANN;
+    singular = true;
+    for (auto& L : lev) setup_level_bc(L);
+    have_sigma = have_result = false; bicg_failed_switch = false;
+    stats = np_stats{}; err = 0; launches = 0; divu_npart = 0; red_n = 0; prof_n = 0; lvl0_off = nullptr; wtot = 1.0;
+}
+
+// First use of a handle that came back from the cache.  Every valid node / cell of every array is written before it is
+// read, and so is every ghost value that a boundary fill or halo exchange produces; the only memory whose content
+// survives from the previous use and can be seen again are ghost values next to faces whose boundary-condition kind
+// changed (they are "left alone" under one kind and filled under another, e.g. the ghost cells of grad(phi) handed back to
+// the caller).  With the same BCs as last time - every time step of an incflo run - nothing needs clearing; otherwise
+// all arrays are cleared as create() does.
+void NpSolver::ensure_clean()
+{
+    if (!reuse_pending) return;
+    reuse_pending = false;
+    bool same = true;
+    for (int d = 0; d < 3; ++d) if (bclo[d] != last_bclo[d] || bchi[d] != last_bchi[d]) same = false;
+    if (same) return;
+    for (auto& L : lev) { zero(L.res, L.d.ntot); zero(L.cor, L.d.ntot); zero(L.cor_alt, L.d.ntot); zero(L.rescor, L.d.ntot); zero(L.sigma, L.d.ctot); }
+    const LevelDev& d0 = lev[0].d;
+    zero(sol, d0.ntot); zero(rhs, d0.ntot);
+    zero(gphi, (long long)(d0.n[0]+2) * (d0.n[1]+2) * (d0.n[2]+2) * 3);
+    zero(phi_out, (long long)(d0.n[0]+3) * (d0.n[1]+3) * (d0.n[2]+3));
+    for (int w = 0; w < 7; ++w) zero(bw[w], lev.back().d.ntot);
+}
+
 // Per-level face types and ghost maps from the domain BCs and this rank's position in the slab stack.
 void NpSolver::setup_level_bc(NpLevel& L)
 {
@@ -693,6 +730,7 @@ static void fill_sigma_level(NpSolver& S, int l)
 
 int NpSolver::set_sigma(const FabView& s)
 {
+    ensure_clean();
     const LevelDev& d0 = lev[0].d;
     dim3 gmm = grid_cells(d0); gmm.z = std::min<unsigned>(gmm.z, 16u);
     NP_LAUNCH(true, k_minmax_cell, gmm, NP_BLK, 0, stream, d0.n[0], d0.n[1], d0.n[2], s, part0, part1); ++launches;
@@ -825,6 +863,7 @@ int NpSolver::project(np_fab* vel, const np_fab* sigma, double rtol, double atol
 {
     if (vel->ngrow < 1 || vel->ncomp < 3 || sigma->ncomp < 1) return NP_ERR_INVALID;
     err = 0; launches = 0; have_result = false; prof_n = 0;
+    ensure_clean();
     const LevelDev& d0 = lev[0].d;
     np_rt::event_record(ev[0], stream);
     // ---- inputs ----
@@ -981,6 +1020,7 @@ int NpSolver::apply_projection(np_fab* vel, const np_fab* vel_old, const np_fab*
     if (!np_rt::is_device_ptr(vel->p) || !np_rt::is_device_ptr(rho->p) || !np_rt::is_device_ptr(gp->p) || !np_rt::is_device_ptr(p->p)
         || (use_old && !np_rt::is_device_ptr(vel_old->p))) return NP_ERR_INVALID;
     err = 0; launches = 0; have_result = false; prof_n = 0;
+    ensure_clean();
     const LevelDev& d0 = lev[0].d;
     np_rt::event_record(ev[0], stream);
     FabView uv = view_cell(*vel, 0, 3), rv = view_cell(*rho, 0, 1), gv = view_cell(*gp, 0, 3), pv = view_nodal(*p, 0);

@@ -94,6 +94,9 @@ struct NpSolver {
     int create(const np_geom* g, int nboxes, const np_box* boxes, const int* owner, int my_rank, int nranks,
                const NpComm& c, const np_options* o);
     void destroy();
+    void ensure_clean();             // handle cache: clears the arrays on the first use after reuse iff the BCs changed
+    bool reuse_pending = false; int last_bclo[3] = {0,0,0}, last_bchi[3] = {0,0,0};
+    void reset_for_reuse();          // handle cache: back to the state create() leaves (same arrays, all cleared)
     int set_bc(const int lo[3], const int hi[3]);
     void setup_level_bc(NpLevel& L);
 
@@ -127,7 +130,7 @@ struct NpSolver {
     int export_fab(const np_fab& f, long long nelem, double* dev, bool staged);
 };
 
-struct np_handle { NpSolver S; };
+struct np_handle { NpSolver S; void* cache_key = nullptr; };     // cache_key: np_capi.cu, handle cache
 
 #define NP_BLK dim3(32, 8, 1)
 static inline dim3 grid_nodes(const LevelDev& L) { return dim3((L.n[0] + 1 + 31) / 32, (L.n[1] + 1 + 7) / 8, L.n[2] + 1); }

@@ -158,7 +158,16 @@ int np_copy_gradphi(np_handle* h, int local_box, np_fab* dst);
  * from its side or the results must be fetched with np_copy_*. */
 int np_is_device_pointer(const void* p);
 
+/* np_destroy parks the handle in a one-slot cache instead of freeing it; the next np_create with the same geometry,
+ * BoxArray, owner map, rank layout, communicator, options and device gets it back, reset to the state of a fresh handle
+ * (the reference constructs a NodalProjector inside every ApplyProjection,
+ * /root/reference/src/projection/incflo_apply_nodal_projection.cpp:148-151: with the cache that costs a state reset (and
+ * a clearing of the arrays only if the BC kinds differ from the previous use) instead of ~13 GB of cudaMalloc at 512^3,
+ * the CUDA-IPC exchange and an all-gather per time step).  A create with any other key frees the
+ * parked handle.  np_cache_clear frees it now (collective across ranks, like create / destroy); the environment
+ * variable NP_HANDLE_CACHE=0 turns the cache off. */
 void np_destroy(np_handle* h);
+int np_cache_clear(void);
 const char* np_strerror(int code);
 int np_num_levels(np_handle* h);
 int np_level_ncell(np_handle* h, int mglev, int ncell_local[3]);

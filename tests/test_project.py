@@ -128,3 +128,45 @@ def test_project_nan_input_is_reported(backend):
     drv = nphelp.Driver(ncell, prob["prob_lo"], prob["prob_hi"], prob["bclo"], prob["bchi"], **backend)
     st, *_ = drv.project(vel, prob["sigma"], 1e-11, 1e-14, raise_on_fail=False)
     assert st.status == 6
+
+
+def test_handle_cache_reuse_is_stateless(backend):
+    """np_destroy parks the handle, the next np_create with the same key gets it back reset: same address, and the second
+    use (other BC kind, other sigma) gives bit-identical results to a fresh handle (NP_HANDLE_CACHE=0 style: cache cleared)."""
+    rng = np.random.default_rng(11)
+    ncell = (16, 16, 16)
+    L = backend["lib"]
+    prob = problems.PROBLEMS["taylor_green"](ncell)
+    geom_kw = dict(prob_lo=(0, 0, 0), prob_hi=(1, 1, 1))
+
+    def run(bclo, bchi, vel, sigma):
+        drv = nphelp.Driver(ncell, geom_kw["prob_lo"], geom_kw["prob_hi"], bclo, bchi, **backend)
+        addr = drv.h.value if hasattr(drv.h, "value") else int(drv.h)
+        st, u, phi, gp = drv.project(vel, sigma, 1e-11, 1e-14)
+        drv.P.close()
+        return addr, st.n_vcycles, u, phi, gp
+
+    sig2 = rng.uniform(0.5, 2.0, ncell[::-1])
+    vel2 = rng.standard_normal((3,) + ncell[::-1])
+    L.np_cache_clear()
+    a1, *_ = run((0, 0, 0), (0, 0, 0), prob["vel"], prob["sigma"])
+    a2, vc2, u2, phi2, gp2 = run((0, 0, 0), (0, 0, 0), vel2, sig2)          # same key: the parked handle comes back
+    assert a2 == a1
+    L.np_cache_clear()
+    a3, vc3, u3, phi3, gp3 = run((0, 0, 0), (0, 0, 0), vel2, sig2)          # fresh handle
+    assert vc2 == vc3 and np.array_equal(u2, u3) and np.array_equal(phi2, phi3) and np.array_equal(gp2, gp3)
+    # same key, other BC kinds than the previous use (non-periodic geometry): the arrays are cleared, results equal a fresh handle's
+    def run_np(bclo, bchi):
+        drv = nphelp.Driver(ncell, (0, 0, 0), (1, 1, 1), bclo, bchi, **backend)
+        st, u, phi, gp = drv.project(vel2, sig2, 1e-11, 1e-14)
+        drv.P.close()
+        return st.n_vcycles, u, phi, gp
+    run_np((2, 2, 2), (1, 2, 2))
+    r1 = run_np((1, 2, 2), (2, 1, 2))
+    L.np_cache_clear()
+    r2 = run_np((1, 2, 2), (2, 1, 2))
+    assert r1[0] == r2[0] and all(np.array_equal(a, b) for a, b in zip(r1[1:], r2[1:]))
+    # another geometry evicts the parked handle and works
+    drv = nphelp.Driver((16, 16, 8), **backend)
+    drv.P.close()
+    L.np_cache_clear()
