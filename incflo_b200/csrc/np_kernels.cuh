@@ -691,11 +691,45 @@ __device__ __forceinline__ void gs2_run(const LevelDev& L, const GsArgs& A, doub
     };
     if (CS && grp == 0) load_rhs(0);
 
+    // variable sigma: the 3 x 9 cells (gi-1+c, gj-1+q) of a cell layer around this thread's block.  Addresses cost more than
+    // the loads if they are formed per element (ncu: a third of the kernel's instructions were IMAD / LEA): the thread keeps
+    // one pointer to its first cell in layer -1; a full tile then uses row pointers and immediate column offsets, any other
+    // tile 9 + 3 precomputed element offsets with the indices clamped into the array (clamped cells only feed nodes
+    // outside the domain, which are never updated).
+    const double* sig_t = nullptr;
+    int sro[9], sco[3];
+    if (!CS) {
+        if (FULL) sig_t = sig + (long long)gi + L.csy * (long long)gj;          // cell (gi-1, gj-1) of layer -1
+        else {
+            sig_t = sig;
+#pragma unroll
+            for (int q = 0; q < 9; ++q) sro[q] = (int)(L.csy * (long long)(min(gj - 1 + q, L.n[1]) + 1));
+#pragma unroll
+            for (int c = 0; c < 3; ++c) sco[c] = min(gi - 1 + c, L.n[0]) + 1;
+        }
+    }
+    auto load_sig = [&](double (&S)[3][9], int kc) {                            // cell layer kc (k index), -1 <= kc <= n2
+        const double* sb = sig_t + L.csz * (long long)(kc + 1);
+        if (FULL) {
+#pragma unroll
+            for (int q = 0; q < 9; ++q) {
+#pragma unroll
+                for (int c = 0; c < 3; ++c) S[c][q] = sb[c];
+                sb += L.csy;
+            }
+        } else {
+#pragma unroll
+            for (int q = 0; q < 9; ++q)
+#pragma unroll
+                for (int c = 0; c < 3; ++c) S[c][q] = sb[sro[q] + sco[c]];
+        }
+    };
+
     for (int t = 0; t <= nk + 1; ++t) {
         if (t + 2 <= nk) load_plane(t + 2);
         np_cp_async_commit();
         const int p = t - 2 * grp;
-        const bool on = (p >= 0 && p <= nk - 1);
+        const bool on = (p >= 0 && p <= nk - 1) && (FULL || act != 0u);     // a thread whose block lies outside the level only keeps the barriers
         const int k = kb + p;
         double* Pc = on ? slot(p) : ring;
         const bool zdir = !FULL && on && ((L.face[2] == NP_FACE_DIRICHLET && k == 0) || (L.face[5] == NP_FACE_DIRICHLET && k == L.n[2]));
@@ -754,9 +788,14 @@ __device__ __forceinline__ void gs2_run(const LevelDev& L, const GsArgs& A, doub
                 // being relaxed (one CTA per SM leaves a large L1), so the loads at the top of the next step are hits
 #pragma unroll
                 for (int r = 0; r < 8; ++r) np_prefetch_l1(rhs + gbase + L.nsz + L.nsy * r);
-                const double* sn = sig + L.csz * (long long)(k + 2) + (min(gi, L.n[0]) + 1);
+                const double* sn = sig_t + L.csz * (long long)(k + 2);
+                if (FULL) {
 #pragma unroll
-                for (int q = 0; q < 9; ++q) np_prefetch_l1(sn + L.csy * (long long)(min(gj - 1 + q, L.n[1]) + 1));
+                    for (int q = 0; q < 9; ++q) { np_prefetch_l1(sn + 1); sn += L.csy; }
+                } else {
+#pragma unroll
+                    for (int q = 0; q < 9; ++q) np_prefetch_l1(sn + sro[q] + sco[1]);
+                }
             }
             if (on) {
                 const double* rp = rhs + gbase;
@@ -768,26 +807,13 @@ __device__ __forceinline__ void gs2_run(const LevelDev& L, const GsArgs& A, doub
                 // cells (gi-1+c, gj-1+q) of the layers below (k-1) and above (k) plane k; indices clamped into the array
                 // (clamped cells only feed nodes outside the domain, which are never updated)
                 double S[3][9];
-                const double* sb = sig + L.csz * (long long)k;                  // layer k-1 starts at csz*k
-#pragma unroll
-                for (int c = 0; c < 3; ++c)
-#pragma unroll
-                    for (int q = 0; q < 9; ++q) {
-                        const int ci = min(gi - 1 + c, L.n[0]), cj = min(gj - 1 + q, L.n[1]);
-                        S[c][q] = sb[(ci + 1) + L.csy * (long long)(cj + 1)];
-                    }
+                load_sig(S, k - 1);                                             // cells below plane k
                 gs_zpart_var(L.c, B, S, slot(p - 1), ofs);
 #pragma unroll
                 for (int c = 0; c < 3; ++c)
 #pragma unroll
                     for (int q = 0; q < 9; ++q) V[c][q] = S[c][q];
-#pragma unroll
-                for (int c = 0; c < 3; ++c)
-#pragma unroll
-                    for (int q = 0; q < 9; ++q) {
-                        const int ci = min(gi - 1 + c, L.n[0]), cj = min(gj - 1 + q, L.n[1]);
-                        S[c][q] = sb[L.csz + (ci + 1) + L.csy * (long long)(cj + 1)];
-                    }
+                load_sig(S, k);                                                 // cells above
                 gs_zpart_var(L.c, B, S, slot(p + 1), ofs);
 #pragma unroll
                 for (int c = 0; c < 3; ++c)
@@ -844,6 +870,8 @@ __global__ void __launch_bounds__(256, CS ? 2 : 1) k_gs2(LevelDev L, GsArgs A)
     if (full) gs2_run<CS, true>(L, A, ring);
     else      gs2_run<CS, false>(L, A, ring);
 }
+
+#include "np_gs3.cuh"
 
 // ------------------------------------------------------------------------------------------------
 // K2, constant sigma: y = A x  (MODE 0)  or  y = (b - *boff) - A x  (MODE 1), marching in z.

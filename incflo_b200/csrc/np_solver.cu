@@ -59,6 +59,8 @@ int NpSolver::create(const np_geom* g, int nboxes, const np_box* boxes, const in
                      const NpComm& c, const np_options* o)
 {
     if (np_rt::init()) return NP_ERR_NO_DEVICE;
+    if (const char* e = std::getenv("NP_GS_VARIANT")) gs_variant_c = std::atoi(e);        // experiment knobs: which smoother kernel
+    if (const char* e = std::getenv("NP_GSV_VARIANT")) gs_variant_v = std::atoi(e);
     geom = *g; opt = *o; comm = c; comm.rank = my_rank; comm.nranks = nranks;
     // ---- box layout: the boxes of rank r tile the r-th of nranks equal z-slabs (one box per rank: used as it is;
     //      several: gathered into the slab by np_project, see project_boxes) ----
@@ -166,6 +168,10 @@ int NpSolver::create(const np_geom* g, int nboxes, const np_box* boxes, const in
 #ifndef NP_EMU
     cudaFuncSetAttribute(k_gs2<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GS_SMEM_BYTES);
     cudaFuncSetAttribute(k_gs2<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GS_SMEM_BYTES);
+#define NP_GS3_ATTR(BW, BH, CS, MINB) cudaFuncSetAttribute(k_gs3<BW, BH, CS, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G3<BW, BH>::SMEM_BYTES)
+    NP_GS3_ATTR(2, 8, true, 2); NP_GS3_ATTR(2, 4, true, 1); NP_GS3_ATTR(4, 8, true, 2); NP_GS3_ATTR(4, 4, true, 2);
+    NP_GS3_ATTR(2, 8, false, 1); NP_GS3_ATTR(2, 4, false, 1); NP_GS3_ATTR(4, 4, false, 1); NP_GS3_ATTR(2, 8, false, 2);
+#undef NP_GS3_ATTR
     cudaFuncSetAttribute(k_stencil<0, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ST_SMEM_BYTES);
     cudaFuncSetAttribute(k_stencil<1, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ST_SMEM_BYTES);
     cudaFuncSetAttribute(k_stencil<1, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ST_SMEM_BYTES);
@@ -494,12 +500,29 @@ void NpSolver::smooth(int l, bool zero_in, double* add_to)
         gc.a_exy = 2.0 * d.c.f2x2ymz * sg * dinv; gc.a_exz = 2.0 * d.c.f2xmy2z * sg * dinv; gc.a_eyz = 2.0 * d.c.fmx2y2z * sg * dinv;
         gc.a_c = d.c.fxyz * sg * dinv;
     }
+#define NP_GS3(BW, BH, CS, MINB) NP_LAUNCH(true, (k_gs3<BW, BH, CS, MINB>), g, dim3(G3<BW, BH>::CTA), (G3<BW, BH>::SMEM_BYTES), stream, d, ga)
     auto launch = [&](int nz) {
         const dim3 g(grid.x, grid.y, nz);
-        if (d.const_sigma) NP_LAUNCH(true, (k_gs2<true>), g, dim3(256), smem, stream, d, ga);
-        else               NP_LAUNCH(true, (k_gs2<false>), g, dim3(256), smem, stream, d, ga);
+        if (d.const_sigma) {
+            switch (gs_variant_c) {
+            case 1: NP_GS3(2, 8, true, 2); break;
+            case 2: NP_GS3(2, 4, true, 1); break;
+            case 3: NP_GS3(4, 8, true, 2); break;
+            case 4: NP_GS3(4, 4, true, 2); break;
+            default: NP_LAUNCH(true, (k_gs2<true>), g, dim3(256), smem, stream, d, ga); break;
+            }
+        } else {
+            switch (gs_variant_v) {
+            case 1: NP_GS3(2, 8, false, 1); break;
+            case 2: NP_GS3(2, 4, false, 1); break;
+            case 3: NP_GS3(4, 4, false, 1); break;
+            case 4: NP_GS3(2, 8, false, 2); break;
+            default: NP_LAUNCH(true, (k_gs2<false>), g, dim3(256), smem, stream, d, ga); break;
+            }
+        }
         ++launches;
     };
+#undef NP_GS3
     // Sharded level: relax the two end z-chunks first and ship their planes to the neighbours on the comm stream while
     // the interior chunks are relaxed (FillBoundary overlapped with the interior work).  The end chunks write the
     // planes that are sent (k = 0, 1, n2-1) as long as a chunk has two planes, which gs_zchunk guarantees.

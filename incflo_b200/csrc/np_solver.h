@@ -90,6 +90,7 @@ struct NpSolver {
     double wtot = 1.0;              // sum of the dot-mask weights over the domain (singular problems)
     const double* lvl0_off = nullptr;   // device scalar subtracted from lev[0].res by its consumers (lazy makeSolvable)
     int err = 0;
+    int gs_variant_c = 0, gs_variant_v = 0;   // which smoother kernel runs for constant / variable sigma (0: k_gs2)
 
     int create(const np_geom* g, int nboxes, const np_box* boxes, const int* owner, int my_rank, int nranks,
                const NpComm& c, const np_options* o);
