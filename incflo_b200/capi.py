@@ -64,7 +64,8 @@ class mp_options(C.Structure):
 # every symbol include/macproj.h declares
 MAC_SYMBOLS = ["mp_default_options", "mp_create", "mp_set_bc", "mp_update_beta", "mp_project", "mp_get_fluxes", "mp_copy_phi",
                "mp_destroy", "mp_num_levels", "mp_level_ncell", "mp_get_beta", "mp_apply", "mp_smooth", "mp_restrict",
-               "mp_interp_add", "mp_bottom_solve", "mp_update_beta_boxes", "mp_project_boxes", "mp_get_fluxes_boxes"]
+               "mp_interp_add", "mp_bottom_solve", "mp_update_beta_boxes", "mp_project_boxes", "mp_get_fluxes_boxes",
+               "mp_set_scalars", "mp_set_acoeffs", "mp_solve"]
 
 # every symbol include/nodalproj.h declares
 SYMBOLS = ["np_default_options", "np_create", "np_set_bc", "np_project", "np_apply_projection", "np_get_phi", "np_get_gradphi",
@@ -130,6 +131,10 @@ def load(path=None):
     L.mp_update_beta.argtypes = [C.c_void_p, C.POINTER(np_fab)]
     L.mp_project.argtypes = [C.c_void_p, C.POINTER(np_fab), C.POINTER(np_fab), C.c_double, C.c_double, C.c_void_p,
                              C.POINTER(np_stats)]
+    L.mp_set_scalars.argtypes = [C.c_void_p, C.c_double, C.c_double]
+    L.mp_set_acoeffs.argtypes = [C.c_void_p, C.POINTER(np_fab)]
+    L.mp_solve.argtypes = [C.c_void_p, C.POINTER(np_fab), C.POINTER(np_fab), C.POINTER(np_fab), C.c_double, C.c_double, C.c_void_p,
+                           C.POINTER(np_stats)]
     L.mp_get_fluxes.argtypes = [C.c_void_p, C.POINTER(np_fab), C.POINTER(np_fab)]
     L.mp_copy_phi.argtypes = [C.c_void_p, C.POINTER(np_fab)]
     L.mp_update_beta_boxes.argtypes = [C.c_void_p, C.c_int, C.POINTER(np_fab), C.POINTER(np_fab), C.POINTER(np_fab)]

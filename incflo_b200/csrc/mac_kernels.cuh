@@ -24,7 +24,11 @@ struct MacLevel {
     int const_beta; double beta0;
     int koff;                     // global z index of local plane 0 (colour parity of a slab); 0 on one rank / replicated levels
     int kcoff;                    // plane of the next coarser level's array that holds the parent of local plane 0
+    // MLABecLaplacian's alpha * a term (the scalar / velocity-component diffusion solves): cell array
+    // in the layout of the level's cell arrays, or null (alpha = 0: the MAC projection).  dh[] then carries beta / dx^2.
+    double ascal; const double* acoef;
 };
+__device__ __forceinline__ double mac_aterm(const MacLevel& L, long long c) { return L.acoef ? L.ascal * L.acoef[c] : 0.0; }
 struct MacBeta { const double *bx, *by, *bz; };
 
 __host__ __device__ __forceinline__ long long mac_c(const MacLevel& L, int i, int j, int k) { return i + L.sx * (j + (long long)L.n[1] * k); }
@@ -105,7 +109,7 @@ __global__ void __launch_bounds__(256) k_mac_gsrb(MacLevel L, MacBeta B, double*
         const double cf0 = i == 0 ? L.flo[0] : 0.0, cf3 = i == L.n[0] - 1 ? L.fhi[0] : 0.0;
         const double cf1 = j == 0 ? L.flo[1] : 0.0, cf4 = j == L.n[1] - 1 ? L.fhi[1] : 0.0;
         const double cf2 = k == 0 ? L.flo[2] : 0.0, cf5 = k == L.n[2] - 1 ? L.fhi[2] : 0.0;
-        const double gamma = L.dh[0] * (b.xm + b.xp) + L.dh[1] * (b.ym + b.yp) + L.dh[2] * (b.zm + b.zp);
+        const double gamma = mac_aterm(L, c) + L.dh[0] * (b.xm + b.xp) + L.dh[1] * (b.ym + b.yp) + L.dh[2] * (b.zm + b.zp);
         const double g_m_d = gamma - (L.dh[0] * (b.xm * cf0 + b.xp * cf3) + L.dh[1] * (b.ym * cf1 + b.yp * cf4) + L.dh[2] * (b.zm * cf2 + b.zp * cf5));
         double r = rhs[c];
         if (boff) r -= *boff;
@@ -545,14 +549,14 @@ __global__ void __launch_bounds__(256) k_mac_adotx(MacLevel L, MacBeta B, double
             }
             {
                 const MacB6& b = b0;
-                const double ax = -L.dh[0] * (b.xp * (xp0 - xc.x) - b.xm * (xc.x - xm0)) - L.dh[1] * (b.yp * (yp.x - xc.x) - b.ym * (xc.x - ym.x))
+                const double ax = mac_aterm(L, c) * xc.x - L.dh[0] * (b.xp * (xp0 - xc.x) - b.xm * (xc.x - xm0)) - L.dh[1] * (b.yp * (yp.x - xc.x) - b.ym * (xc.x - ym.x))
                                 - L.dh[2] * (b.zp * (zp.x - xc.x) - b.zm * (xc.x - zm.x));
                 out.x = MODE == 0 ? ax : (bv.x - off) - ax;
             }
             out.y = 0.0;
             if (pair) {
                 const MacB6& b = b1;
-                const double ax = -L.dh[0] * (b.xp * (xp1 - xc.y) - b.xm * (xc.y - xc.x)) - L.dh[1] * (b.yp * (yp.y - xc.y) - b.ym * (xc.y - ym.y))
+                const double ax = mac_aterm(L, c + 1) * xc.y - L.dh[0] * (b.xp * (xp1 - xc.y) - b.xm * (xc.y - xc.x)) - L.dh[1] * (b.yp * (yp.y - xc.y) - b.ym * (xc.y - ym.y))
                                 - L.dh[2] * (b.zp * (zp.y - xc.y) - b.zm * (xc.y - zm.y));
                 out.y = MODE == 0 ? ax : (bv.y - off) - ax;
                 *reinterpret_cast<double2*>(y + c) = out;
@@ -610,7 +614,7 @@ __global__ void __launch_bounds__(256) k_mac_resid_restrict(MacLevel Lc, MacLeve
                 const double xp = di ? mac_nb_hi(L, x, cc, xc, 0, i + 1, 1, x) : xv.y;
                 const double ym = mac_nb_lo(L, x, cc, xc, 1, j, L.sx, x), yp = mac_nb_hi(L, x, cc, xc, 1, j, L.sx, x);
                 const double zm = mac_nb_lo(L, x, cc, xc, 2, k, L.sxy, x), zp = mac_nb_hi(L, x, cc, xc, 2, k, L.sxy, x);
-                const double ax = -L.dh[0] * (b.xp * (xp - xc) - b.xm * (xc - xm)) - L.dh[1] * (b.yp * (yp - xc) - b.ym * (xc - ym))
+                const double ax = mac_aterm(L, cc) * xc - L.dh[0] * (b.xp * (xp - xc) - b.xm * (xc - xm)) - L.dh[1] * (b.yp * (yp - xc) - b.ym * (xc - ym))
                                 - L.dh[2] * (b.zp * (zp - xc) - b.zm * (xc - zm));
                 acc += ((di ? bv.y : bv.x) - off) - ax;
             }
@@ -791,6 +795,30 @@ __global__ void __launch_bounds__(256) k_mac_beta_out(MacLevel L, const double* 
 // 2^3 .. a few 10^4 cells): reductions are block barriers, not launches.  x = 0 on entry, so r0 = b.
 // out[0] = MLCGSolver return code (0 ok, 1-4 breakdown, 8 not converged), out[1] = iterations.
 // ------------------------------------------------------------------------------------------------
+// MLMG with inhomogeneous Dirichlet data (MLCellLinOp::setLevelBC: the boundary values sit in the ghost cells of phi): the
+// ghost of the first interior cell is  dc0 phi0 + dc1 phi1 + cbc value  (maxorder 3: cbc = 8/3).  MLMG evaluates the first
+// residual with it and iterates on the homogeneous correction equation; moving  dh b_face cbc value  to the right-hand side
+// once is the same thing.  One launch per Dirichlet face; phi is the caller's fab (>= 1 ghost cell).
+__global__ void __launch_bounds__(256) k_mac_dirichlet_rhs(MacLevel L, MacBeta B, double* __restrict__ rhs, FabView phi, int d, int side, double cbc)
+{
+    const int a = (d + 1) % 3, b = (d + 2) % 3, t0 = a < b ? a : b, t1 = a < b ? b : a;
+    const int p = blockIdx.x * blockDim.x + threadIdx.x, q = blockIdx.y * blockDim.y + threadIdx.y;
+    if (p >= L.n[t0] || q >= L.n[t1]) return;
+    int idx[3]; idx[d] = side ? L.n[d] - 1 : 0; idx[t0] = p; idx[t1] = q;
+    int gh[3] = {idx[0], idx[1], idx[2]}; gh[d] += side ? 1 : -1;                 // the ghost cell that carries the wall value
+    int fi[3] = {idx[0], idx[1], idx[2]}; if (side) fi[d] += 1;                  // the face
+    double bf = L.beta0;
+    if (!L.const_beta) bf = d == 0 ? B.bx[mac_fx(L, fi[0], fi[1], fi[2])] : d == 1 ? B.by[mac_fy(L, fi[0], fi[1], fi[2])] : B.bz[mac_fz(L, fi[0], fi[1], fi[2])];
+    rhs[mac_c(L, idx[0], idx[1], idx[2])] += L.dh[d] * bf * cbc * phi.p[np_foff(phi, gh[0], gh[1], gh[2], 0)];
+}
+// rhs = rho * tracer (DiffusionScalarOp::diffuse_scalar, /root/reference/src/diffusion/DiffusionScalarOp.cpp:207-217)
+__global__ void __launch_bounds__(256) k_mac_rho_times(MacLevel L, double* __restrict__ rhs, FabView rho, FabView tra)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y * blockDim.y + threadIdx.y, k = blockIdx.z;
+    if (i >= L.n[0] || j >= L.n[1]) return;
+    rhs[mac_c(L, i, j, k)] = rho.p[np_foff(rho, i, j, k, 0)] * tra.p[np_foff(tra, i, j, k, 0)];
+}
+
 struct MacBottomArgs {
     MacLevel L; MacBeta B;
     double* x; const double* b;
@@ -802,7 +830,7 @@ struct MacBottomArgs {
 template <bool CB> __device__ __forceinline__ double mac_diag(const MacLevel& L, const MacBeta& B, int i, int j, int k)
 {
     const MacB6 b = mac_load_b<CB>(L, B, i, j, k);
-    return L.dh[0] * (b.xm + b.xp) + L.dh[1] * (b.ym + b.yp) + L.dh[2] * (b.zm + b.zp);
+    return mac_aterm(L, mac_c(L, i, j, k)) + L.dh[0] * (b.xm + b.xp) + L.dh[1] * (b.ym + b.yp) + L.dh[2] * (b.zm + b.zp);
 }
 template <bool CB> __device__ __forceinline__ double mac_ax(const MacLevel& L, const MacBeta& B, const double* x, int i, int j, int k)
 {
@@ -812,7 +840,7 @@ template <bool CB> __device__ __forceinline__ double mac_ax(const MacLevel& L, c
     const double xm = mac_nb_lo(L, x, c, xc, 0, i, 1, x), xp = mac_nb_hi(L, x, c, xc, 0, i, 1, x);
     const double ym = mac_nb_lo(L, x, c, xc, 1, j, L.sx, x), yp = mac_nb_hi(L, x, c, xc, 1, j, L.sx, x);
     const double zm = mac_nb_lo(L, x, c, xc, 2, k, L.sxy, x), zp = mac_nb_hi(L, x, c, xc, 2, k, L.sxy, x);
-    return -L.dh[0] * (b.xp * (xp - xc) - b.xm * (xc - xm)) - L.dh[1] * (b.yp * (yp - xc) - b.ym * (xc - ym)) - L.dh[2] * (b.zp * (zp - xc) - b.zm * (xc - zm));
+    return mac_aterm(L, c) * xc - L.dh[0] * (b.xp * (xp - xc) - b.xm * (xc - xm)) - L.dh[1] * (b.yp * (yp - xc) - b.ym * (xc - ym)) - L.dh[2] * (b.zp * (zp - xc) - b.zm * (xc - zm));
 }
 #define MAC_FOR_CELLS(q, i, j, k, c) \
     for (long long q = threadIdx.x; q < ncell; q += blockDim.x) { \

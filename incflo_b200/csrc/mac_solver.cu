@@ -13,6 +13,7 @@ struct MacLev {
     double *bx = nullptr, *by = nullptr, *bz = nullptr;
     double *res = nullptr, *cor = nullptr, *rescor = nullptr;   // every cell array has one spare plane below and above (ghost planes
                                                                  // of a slab: k = -1 and k = n2)
+    double* a = nullptr;          // MLABecLaplacian's a coefficient (cell array without ghost planes), allocated by set_acoeffs
     bool replicated = false;      // multi-GPU: this level holds the whole domain on every rank
     MacBeta beta() const { return MacBeta{bx, by, bz}; }
 };
@@ -42,6 +43,8 @@ struct MacSolver {
     long long launches = 0;
     int bottom_iters = 0;
     int err = 0;
+    double alpha = 0.0, bscal = 1.0;      // MLABecLaplacian::setScalars (the MAC projection: 0, 1)
+    bool have_a = false;
 
     static dim3 blk() { return dim3(32, 8, 1); }
     static dim3 grid_cells(const MacLevel& L) { return dim3((L.n[0] + 31) / 32, (L.n[1] + 7) / 8, L.n[2]); }
@@ -85,6 +88,7 @@ struct MacSolver {
     {
         singular = true;
         for (int d = 0; d < 3; ++d) if (bclo[d] == NP_BC_DIRICHLET || bchi[d] == NP_BC_DIRICHLET) singular = false;
+        if (alpha != 0.0 && have_a) singular = false;
         for (auto& L : lev) for (int d = 0; d < 3; ++d) {
             L.d.bclo[d] = bclo[d]; L.d.bchi[d] = bchi[d];
             if (d == 2 && comm.nranks > 1 && !L.replicated) {      // slab faces shared with a neighbouring rank (periodic z: all of them)
@@ -222,6 +226,7 @@ struct MacSolver {
             if (L.by) np_rt::dev_free(L.by - L.d.sx * (L.d.n[1] + 1));
             if (L.bz) np_rt::dev_free(L.bz - L.d.sxy);
             free_cell(L.res, L.d); free_cell(L.cor, L.d); free_cell(L.rescor, L.d);
+            if (L.a) np_rt::dev_free(L.a);
         }
         lev.clear();
         double* a[] = {agg_send, agg_recv, mb_f[0], mb_f[1], mb_f[2], mb_phi, wrapbuf, part0, part1, scal, stage[0], stage[1], stage[2], stage[3], bw[0], bw[1], bw[2], bw[3], bw[4], bw[5]};
@@ -303,6 +308,7 @@ struct MacSolver {
     bool fused_ok(int l) const
     {
         const MacLevel& d = lev[l].d;
+        if (d.acoef) return false;            // the one-pass smoother knows the alpha = 0 operator only
         if (opt.fused_rb_min_n <= 0 || d.n[0] < opt.fused_rb_min_n || (d.n[0] & 1)) return false;
         // a slab runs the one-pass smoother on two ghost planes per side (the reds of the planes next to the slab are recomputed
         // there, from the right-hand side and the coefficients of one ghost plane); only the hoisted-index kernel knows about
@@ -653,6 +659,88 @@ struct MacSolver {
         have_result = true;
         return rc;
     }
+    // ---- MLABecLaplacian beyond the MAC projection: alpha a - beta div(b grad), inhomogeneous Dirichlet data ----
+    // (the scalar and velocity-component diffusion solves, /root/reference/src/diffusion/DiffusionScalarOp.cpp:139-260, :262-380)
+    int set_scalars(double a_alpha, double a_beta)
+    {
+        alpha = a_alpha; bscal = a_beta;
+        for (auto& L : lev) {
+            for (int d = 0; d < 3; ++d) L.d.dh[d] = bscal * L.d.dxinv[d] * L.d.dxinv[d];
+            L.d.ascal = alpha; L.d.acoef = (alpha != 0.0 && have_a) ? L.a : nullptr;
+        }
+        setup_bc();
+        return NP_OK;
+    }
+    // MLABecLaplacian::setACoeffs + averageDownCoeffs (a by average_down)
+    int set_acoeffs(const np_fab* a)
+    {
+        if (!a || !a->p || a->ncomp < 1) return NP_ERR_INVALID;
+        if (comm.nranks > 1) return NP_ERR_INVALID;          // one rank this round (the coarse a would need the gather the face coefficients have)
+        for (auto& L : lev) if (!L.a && alloc_d(&L.a, L.d.ntot)) return NP_ERR_CUDA;
+        FabView v; bool st;
+        if (!import(*a, 0, -1, 3, true, &v, &st)) return NP_ERR_CUDA;
+        NP_LAUNCH(false, (k_mac_copy_cell<false>), grid_cells(lev[0].d), blk(), 0, stream, lev[0].d, lev[0].a, v); ++launches;
+        for (size_t l = 1; l < lev.size(); ++l) restrict_to((int)l, lev[l].a, lev[l - 1].a);
+        np_rt::stream_sync(stream);
+        have_a = true;
+        return set_scalars(alpha, bscal);
+    }
+    // MLMG::solve(phi, rhs): phi carries the initial guess in its valid cells and, on Dirichlet faces, the boundary values in
+    // its first ghost layer (setLevelBC(phi)); on return its valid cells hold the solution.  rho != null: rhs = rho * rhs_or_tracer
+    // (diffuse_scalar forms rho * tracer).
+    int solve_abec(np_fab* phi, const np_fab* rhs_in, const np_fab* rho, double rtol, double atol)
+    {
+        if (!have_beta) return NP_ERR_STATE;
+        if (!phi || !phi->p || !rhs_in || !rhs_in->p) return NP_ERR_INVALID;
+        launches = 0; have_result = false; prof_n = 0; err = 0;
+        const int is_const = stats.sigma_is_const;
+        stats = np_stats{}; stats.sigma_is_const = is_const;
+        const MacLevel& d0 = lev[0].d;
+        bool any_dir = false;
+        for (int d = 0; d < 3; ++d) if (bclo[d] == NP_BC_DIRICHLET || bchi[d] == NP_BC_DIRICHLET) any_dir = true;
+        if (any_dir && phi->ngrow < 1) return NP_ERR_INVALID;
+        np_rt::event_record(ev[0], stream);
+        FabView pv, rv, dv; bool pst, rst, dst;
+        if (!import(*phi, 0, -1, 3, true, &pv, &pst) || !import(*rhs_in, 0, -1, 0, true, &rv, &rst)) return NP_ERR_CUDA;
+        if (rho) {
+            if (!rho->p || !import(*rho, 0, -1, 1, true, &dv, &dst)) return NP_ERR_CUDA;
+            NP_LAUNCH(false, k_mac_rho_times, grid_cells(d0), blk(), 0, stream, d0, rhs, dv, rv); ++launches;
+        } else { NP_LAUNCH(false, (k_mac_copy_cell<false>), grid_cells(d0), blk(), 0, stream, d0, rhs, rv); ++launches; }
+        NP_LAUNCH(false, (k_mac_copy_cell<false>), grid_cells(d0), blk(), 0, stream, d0, sol, pv); ++launches;
+        for (int d = 0; d < 3; ++d) for (int side = 0; side < 2; ++side) {
+            if ((side ? bchi[d] : bclo[d]) != NP_BC_DIRICHLET) continue;
+            const int a = (d + 1) % 3, b = (d + 2) % 3, t0 = std::min(a, b), t1 = std::max(a, b);
+            const double cbc = std::min(d0.n[d] + 1, opt.maxorder) >= 3 ? 8.0 / 3.0 : 2.0;
+            NP_LAUNCH(false, k_mac_dirichlet_rhs, dim3((d0.n[t0] + 31) / 32, (d0.n[t1] + 7) / 8, 1), blk(), 0, stream, d0, lev[0].beta(), rhs, pv, d, side, cbc); ++launches;
+        }
+        // inf-norm of the right-hand side (MLMG's bnorm), after the mean is taken out when the operator is singular
+        const long long nb = nblk(grid_cells(d0));
+        zero(lev[0].rescor, d0.ntot);
+        NP_LAUNCH(true, (k_mac_adotx<1, true, true>), grid_adotx(d0), blk(), 0, stream, zero_op(d0), lev[0].beta(), lev[0].rescor, (const double*)lev[0].rescor,
+                  (const double*)rhs, (const double*)nullptr, part0, part1); ++launches;       // y = rhs - 0: the reducing pass gives max |rhs| and its sum
+        reduce(nblk(grid_adotx(d0)), true, singular, 16);
+        if (singular) {
+            NP_LAUNCH(true, k_mac_sub_norm, grid_cells(d0), blk(), 0, stream, d0, rhs, (const double*)(scal + 16 + 6), part0); ++launches;
+            reduce(nb, true, false, 16);
+        }
+        np_rt::copy_async(h_scal + 16, scal + 16, 8 * sizeof(double), stream);
+        np_rt::stream_sync(stream);
+        const double rhsnorm0 = h_scal[16];
+        np_rt::event_record(ev[1], stream);
+        const int rc = solve(rtol, atol, rhsnorm0);
+        np_rt::event_record(ev[2], stream);
+        NP_LAUNCH(false, (k_mac_copy_cell<true>), grid_cells(d0), blk(), 0, stream, d0, sol, pv); ++launches;
+        export_back(*phi, pv, pst);
+        finish_stats();
+        stats.status = rc;
+        if (np_rt::last_error()) { stats.status = NP_ERR_CUDA; return NP_ERR_CUDA; }
+        if (err) { stats.status = err; return err; }
+        have_result = true;
+        return rc;
+    }
+    // the level-0 descriptor with a zero operator (alpha = 0, b = 0): k_mac_adotx<1, REDUCE> on it is the plain reduction of b
+    static MacLevel zero_op(MacLevel d) { d.const_beta = 1; d.beta0 = 0.0; d.acoef = nullptr; d.ascal = 0.0; return d; }
+
     int get_fluxes(np_fab flux[3], const np_fab* phi)
     {
         if (!have_beta || !phi || !phi->p) return NP_ERR_STATE;
@@ -805,6 +893,16 @@ int mp_project(mp_handle* h, np_fab umac[3], np_fab* mac_phi, double rtol, doubl
     if (!h || !umac || h->S.lbox.size() != 1) return NP_ERR_INVALID;      // several boxes: mp_project_boxes
     h->S.stream = (np_stream_t)cuda_stream;
     const int rc = h->S.project(umac, mac_phi, rtol, atol);
+    if (out) *out = h->S.stats;
+    return rc;
+}
+int mp_set_scalars(mp_handle* h, double alpha, double beta) { return h ? h->S.set_scalars(alpha, beta) : NP_ERR_INVALID; }
+int mp_set_acoeffs(mp_handle* h, const np_fab* a) { return h && h->S.lbox.size() == 1 ? h->S.set_acoeffs(a) : NP_ERR_INVALID; }
+int mp_solve(mp_handle* h, np_fab* phi, const np_fab* rhs, const np_fab* rho_or_null, double rtol, double atol, void* cuda_stream, np_stats* out)
+{
+    if (!h || h->S.lbox.size() != 1) return NP_ERR_INVALID;
+    h->S.stream = (np_stream_t)cuda_stream;
+    const int rc = h->S.solve_abec(phi, rhs, rho_or_null, rtol, atol);
     if (out) *out = h->S.stats;
     return rc;
 }

@@ -70,6 +70,22 @@ int mp_project(mp_handle* h, np_fab umac[3], np_fab* mac_phi_or_null, double rto
 int mp_get_fluxes(mp_handle* h, np_fab flux[3], const np_fab* phi);
 int mp_copy_phi(mp_handle* h, np_fab* dst);          /* the last solution -> cell fab (valid cells) */
 
+/* ---- the same MLMG / MLABecLaplacian machinery as the reference's implicit diffusion solves use it,
+ *      (alpha a - beta div(b grad)) phi = rhs,   DiffusionScalarOp::diffuse_scalar and ::diffuse_vel_components
+ *      (src/diffusion/DiffusionScalarOp.cpp:139-260, :262-380: alpha = 1, beta = dt, a = rho, b = eta averaged to faces).
+ *   mp_set_scalars  <- MLABecLaplacian::setScalars(1.0, dt)                 DiffusionScalarOp.cpp:179, :315
+ *   mp_set_acoeffs  <- setACoeffs(lev, density)  (cell fab, 1 comp; coarse levels by average_down)   :181, :317
+ *   mp_update_beta  <- setBCoeffs(lev, b)        (face fabs)                                         :197, :324
+ *   mp_set_bc       <- setDomainBC (constructor, :52-53: Dirichlet at inflow / no-slip faces, Neumann else)
+ *   mp_solve        <- setLevelBC(lev, &phi) + MLMG::solve(phi, rhs, rtol, atol)                      :227, :250
+ * phi: cell fab, 1 comp: initial guess in the valid cells and, next to Dirichlet faces, the wall values in the first ghost
+ * layer (what setLevelBC reads; needs ngrow >= 1 then); solution out.  rhs: cell fab.  rho_or_null: when given, the
+ * right-hand side is rho * rhs (diffuse_scalar passes the tracer and the density, :207-217) and no rhs fab has to be
+ * formed.  One rank, one box this round; alpha != 0 runs the one-launch-per-colour smoother. */
+int mp_set_scalars(mp_handle* h, double alpha, double beta);
+int mp_set_acoeffs(mp_handle* h, const np_fab* a);
+int mp_solve(mp_handle* h, np_fab* phi, const np_fab* rhs, const np_fab* rho_or_null, double rtol, double atol, void* cuda_stream, np_stats* out);
+
 /* Several boxes (amr.max_grid_size chops the level; the boxes given to mp_create must tile the domain, all on this rank):
  * arrays of nlocal fabs per direction, in all_boxes order.  The boxes are gathered into domain-shaped device fabs, the
  * one-box path runs on those, and the results are scattered back (a face shared by two boxes is written to both):
