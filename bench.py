@@ -758,10 +758,156 @@ def run_gpu_mac(args):
         dist.destroy_process_group()
 
 
+# ---------------------------------------------------------------------------------------------------
+# --path diffusion: the implicit scalar diffusion solve, (rho - dt div(eta grad)) s = rho s_old, one
+# GPU.  Workload: Rayleigh-Taylor density (ratio 4), eta = mu0 (1 + tanh profile) on faces (variable) or uniform, periodic x / y,
+# walls in z (Neumann), tracer = a blob + the RT perturbation.  Bytes per cell and V-cycle, SURVEY 8(d) rules on the reference
+# schedule (2 + 2 smooths x 2 colours; each colour sweep reads cor, rhs, a[, 3 face arrays] and writes cor).
+# ---------------------------------------------------------------------------------------------------
+DIFF_METRIC = "scalar_diffusion_dof_per_s_per_vcycle"
+DIFF_BYTES = {True: round((8 + 8 * 32 + 32 + 9 + 17) * 8 / 7) + 24 + 32 + 8, False: round((8 + 8 * 56 + 56 + 9 + 17) * 8 / 7) + 24 + 56 + 8}
+
+
+def _diffusion_problem(n, dev, variable_eta, torch):
+    f64 = dict(dtype=torch.float64, device=dev)
+    g = (torch.arange(n, **f64) + 0.5) / n
+    x, y, z = g[None, None, :], g[None, :, None], g[:, None, None]
+    r2d = torch.clamp(torch.hypot(x - 0.5, y - 0.5), max=0.5)
+    h = 0.5 - 0.01 * torch.cos(2 * 3.141592653589793 * r2d)
+    rho = (0.5 + 0.75 * (1.0 + torch.tanh((z - h) / 0.005))).expand(n, n, n).contiguous()
+    tracer = (torch.exp(-((x - 0.5) ** 2 + (y - 0.5) ** 2 + (z - 0.4) ** 2) / 0.02)
+              + 0.1 * torch.sin(6.283185307179586 * x) * torch.sin(6.283185307179586 * y) * torch.sin(6.283185307179586 * z)).contiguous()
+    mu0 = 1.0e-3
+    faces = []
+    for d in range(3):
+        shp = [n, n, n]; shp[2 - d] += 1
+        if variable_eta:
+            zz = (torch.arange(shp[0], **f64) + (0.0 if d == 2 else 0.5)) / n
+            faces.append((mu0 * (1.0 + 0.5 * torch.tanh((zz - 0.5) / 0.05)))[:, None, None].expand(*shp).contiguous()[None])
+        else:
+            faces.append(torch.full([1] + shp, mu0, **f64))
+    return rho[None].contiguous(), tracer[None].contiguous(), faces
+
+
+def run_gpu_diffusion(args):
+    import ctypes as C
+    import torch
+    from incflo_b200 import capi
+    from incflo_b200.diffusion import DiffusionScalarOp
+    from incflo_b200.projector import Fab, Geometry
+    if int(os.environ.get("WORLD_SIZE", "1")) > 1:
+        raise SystemExit("bench.py --path diffusion: one GPU this round")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; incflo_b200 has no CPU fallback")
+    torch.cuda.set_device(0)
+    dev, n, dt = "cuda:0", args.ncell, 0.01
+    variable = args.workload == "rayleigh_taylor"
+    rho, tr0, faces = _diffusion_problem(n, dev, variable, torch)
+    bclo = bchi = (0, 0, 2)
+    op = DiffusionScalarOp(Geometry((n, n, n), (0, 0, 0), (1, 1, 1), [True, True, False]), bclo, bchi, lib=capi.load(), like="torch", device=dev,
+                           profile_kernels=1)
+    frho, feta = Fab(rho, 0), [[Fab(f, 0) for f in faces]]
+    ftr = Fab(tr0.clone(), 0)
+    stream = torch.cuda.current_stream().cuda_stream
+    dof = n ** 3
+
+    def step():
+        ftr.data.copy_(tr0)
+        return op.diffuse_scalar(ftr, frho, feta, dt, RTOL, ATOL, stream=stream)[0]
+
+    clocks = ClockSampler(0); clocks.start()
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize(); clocks.mark()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    vcycles = launches = n_smooth = 0
+    ms_smooth = ms_solve = 0.0
+    for _ in range(args.steps):
+        st = step()
+        vcycles += st.n_vcycles; launches += st.kernel_launches; ms_solve += st.ms_solve
+        ms_smooth += st.ms_smooth0; n_smooth += st.n_smooth0
+        hist = [st.res_history[i] / max(st.rhs_norm0, 1e-300) for i in range(st.n_vcycles)]
+    e1.record(); torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    clk = clocks.stop()
+    const_b = bool(st.sigma_is_const)
+    # e2e: host (pinned) fabs: tracer up and down, rho and the three face arrays up, every step
+    hrho, htr0 = Fab(rho.cpu().pin_memory(), 0), tr0.cpu()
+    htr = Fab(torch.empty_like(htr0).pin_memory(), 0)
+    heta = [[Fab(f.cpu().pin_memory(), 0) for f in faces]]
+    h2d = htr.data.numel() * 8 * 2 + hrho.data.numel() * 8 * 2 + sum(f.data.numel() * 8 for f in heta[0])
+    d2h = htr.data.numel() * 8
+    tot_ms, tot_vc = 0.0, 0
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for it in range(1 + args.e2e_steps):
+        htr.data.copy_(htr0)
+        torch.cuda.synchronize()
+        a.record()
+        st2 = op.diffuse_scalar(htr, hrho, heta, dt, RTOL, ATOL, stream=stream)[0]
+        b.record(); torch.cuda.synchronize()
+        if it >= 1:
+            tot_ms += a.elapsed_time(b); tot_vc += st2.n_vcycles
+    e2e = {"value": dof * tot_vc / (tot_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+           "steps": args.e2e_steps, "ms_per_step": tot_ms / args.e2e_steps}
+    peak, peak_src = read_peaks()
+    per_cell = 2 * (32 if const_b else 56)
+    avg_ms = ms_smooth / max(n_smooth, 1)
+    achieved = per_cell * dof / (avg_ms * 1e-3) / 1e9 if avg_ms > 0 else 0.0
+    roof = {"bound": "hbm", "kernel": f"k_mac_gsrb<{'const' if const_b else 'variable'} b> x 2 (red + black sweep of one smooth, alpha a term), level 0",
+            "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+            "algorithmic_bytes_per_launch": per_cell * dof, "avg_launch_ms": avg_ms, "launches_timed": int(n_smooth),
+            "share_of_step": ms_smooth / ms,
+            "vcycle_algorithmic": {"bytes_per_dof": DIFF_BYTES[const_b], "achieved_gbs": DIFF_BYTES[const_b] * dof * vcycles / (ms_solve * 1e-3) / 1e9}}
+    roof["vcycle_algorithmic"]["frac"] = roof["vcycle_algorithmic"]["achieved_gbs"] / peak
+    wl = (f"scalar diffusion (rho - dt div(eta grad)) s = rho s_old, {n}^3 cells, periodic x/y, walls (Neumann) in z, Rayleigh-Taylor density "
+          f"(ratio 4), eta {'varying in z' if variable else 'uniform'}, dt {dt}, rtol {RTOL:g} atol {ATOL:g}")
+    line = {"metric": DIFF_METRIC, "value": dof * vcycles / (ms * 1e-3), "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": wl, "ncell_per_gpu": [n, n, n], "boxes": f"one {n}^3 box", "l2": "inputs exceed the 126 MB L2; no explicit flush"},
+            "vcycles_per_step": vcycles / args.steps, "mg_levels": st.n_levels, "ms_per_vcycle": ms / vcycles, "ms_solve_per_vcycle": ms_solve / vcycles,
+            "rel_res_history": hist, "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof}
+    if not args.no_cpu:
+        line["cpu_baseline"] = cpu_diffusion(args.cpu_ncell, variable, dt)
+    print(json.dumps(line), flush=True)
+    op.close()
+
+
+def cpu_diffusion(n, variable, dt):
+    """The MAC oracle's general MLABecLaplacian solve (oracle/mac_oracle.cpp: solve_abec) on the host cores, same problem family."""
+    import torch
+    from oracle.mac import MacOracle
+    rho, tr0, faces = _diffusion_problem(n, "cpu", variable, torch)
+    rho, tr0 = rho[0].numpy(), tr0[0].numpy()
+    cores = os.cpu_count() or 1
+    o = MacOracle((n, n, n), (0, 0, 0), (1, 1, 1), (0, 0, 2), (0, 0, 2), nthreads=cores)
+    o.set_scalars(1.0, dt); o.set_acoef(rho); o.set_beta(*[f[0].numpy() for f in faces]); o.set_phi(tr0)
+    t0 = time.perf_counter()
+    st = o.solve_abec(rho * tr0, RTOL, ATOL)
+    dt_s = time.perf_counter() - t0
+    if st.status != 0:
+        raise RuntimeError("diffusion oracle did not converge")
+    return {"value": n ** 3 * st.n_vcycles / dt_s, "unit": UNIT, "cores": cores, "kind": "port", "vcycles": st.n_vcycles,
+            "sample": f"scalar diffusion {n}^3, one box, red-black GS threaded over z-planes on all host cores, rtol {RTOL:g}; 1 solve, {dt_s:.1f} s"}
+
+
+def run_reference_diffusion(args):
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    r = cpu_diffusion(args.cpu_ncell, args.workload == "rayleigh_taylor", 0.01)
+    line = {"impl": "reference", "metric": DIFF_METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": 1, "warmup": 0,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "scalar diffusion, oracle port", "cpu_sample": r["sample"]}, "cpu_baseline": r,
+            "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0,
+            "note": "reference incflo+AMReX build unavailable on this box; this is oracle/mac_oracle.cpp (solve_abec)"}
+    print(json.dumps(line), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--path", default="nodal", choices=["nodal", "mac"],
-                    help="nodal: the nodal projection (BASELINE metric, default); mac: the MAC projection (SURVEY 8(f) row 1)")
+    ap.add_argument("--path", default="nodal", choices=["nodal", "mac", "diffusion"],
+                    help="nodal: the nodal projection (BASELINE metric, default); mac: the MAC projection (SURVEY 8(f) row 1); "
+                         "diffusion: the implicit scalar diffusion solve (8(f) row 3)")
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
@@ -784,6 +930,8 @@ def main():
     args = ap.parse_args()
     if args.path == "mac":
         run_reference_mac(args) if args.impl == "reference" else run_gpu_mac(args)
+    elif args.path == "diffusion":
+        run_reference_diffusion(args) if args.impl == "reference" else run_gpu_diffusion(args)
     elif args.impl == "reference":
         run_reference(args)
     else:

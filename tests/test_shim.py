@@ -59,6 +59,39 @@ def test_mac_shim_on_gpu(tmp_path):
     _run_mac_and_check(capi.LIB_PATH, tmp_path, 32, 16)
 
 
+def _run_diffusion_and_check(libpath, tmp_path, n):
+    """include/DiffusionSolverB200.H driven like DiffusionScalarOp::diffuse_scalar, against the oracle's solve_abec."""
+    from oracle.mac import MacOracle
+    exe, out = str(tmp_path / "diffusion_shim_driver"), str(tmp_path / "diff_out.bin")
+    _build(libpath, exe, "diffusion_shim_driver.cpp")
+    subprocess.check_call([exe, str(n), out])
+    raw = np.fromfile(out, dtype=np.uint8)
+    hdr, tr = raw[:8].view(np.int32), raw[8:].view(np.float64).reshape(n, n, n)
+    g = (np.arange(n) + 0.5) / n
+    x, y, z = g[None, None, :], g[None, :, None], g[:, None, None]
+    t0 = np.broadcast_to(x * y * (1.0 - z), (n, n, n)).copy()
+    rho = np.broadcast_to(1.0 + 0.5 * np.sin(2 * np.pi * x) * np.cos(2 * np.pi * y), (n, n, n)).copy()
+    zf = np.arange(n + 1) / n
+    eta = [np.broadcast_to((0.02 + 0.01 * np.cos(2 * np.pi * z)), (n, n, n + 1)).copy(),
+           np.broadcast_to((0.02 + 0.01 * np.cos(2 * np.pi * z)), (n, n + 1, n)).copy(),
+           np.broadcast_to((0.02 + 0.01 * np.cos(2 * np.pi * zf))[:, None, None], (n + 1, n, n)).copy()]
+    o = MacOracle((n, n, n), (0, 0, 0), (1, 1, 1), (1, 2, 0), (2, 2, 0), maxorder=2)
+    o.set_scalars(1.0, 0.01); o.set_acoef(rho); o.set_beta(*eta); o.set_phi(t0)
+    so = o.solve_abec(rho * t0, 1e-11, 1e-14, dict(xlo=np.ones((n, n))))
+    assert so.status == 0 and hdr[0] == n and hdr[1] == so.n_vcycles
+    assert np.linalg.norm(tr - o.get_phi()) / np.linalg.norm(o.get_phi()) < 1e-10
+
+
+def test_diffusion_shim_on_emulation(tmp_path):
+    nphelp.emu_lib()
+    _run_diffusion_and_check(nphelp.EMU_LIB, tmp_path, 16)
+
+
+@pytest.mark.gpu
+def test_diffusion_shim_on_gpu(tmp_path):
+    _run_diffusion_and_check(capi.LIB_PATH, tmp_path, 32)
+
+
 def _run_and_check(libpath, tmp_path, n, max_grid=None):
     exe = str(tmp_path / "shim_driver")
     out = str(tmp_path / "out.bin")
