@@ -184,6 +184,33 @@ def workload_config(args, G, sample=None):
 # ---------------------------------------------------------------------------------------------------
 # GPU arm
 # ---------------------------------------------------------------------------------------------------
+def _bind_to_gpu_numa_node(torch, local):
+    """What `mpirun --bind-to numa` / a job script does for an MPI rank: run this process on the cores of the NUMA node its GPU
+    hangs off, so that the pinned host fabs of the e2e leg (first touched by this process) live in that node's memory and
+    the host<->device copies do not cross the socket interconnect.  Returns a description, or None when nothing was changed."""
+    try:
+        pr = torch.cuda.get_device_properties(local)
+        bus = f"{pr.pci_domain_id:04x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0"
+        with open(f"/sys/bus/pci/devices/{bus}/numa_node") as f:
+            node = int(f.read().strip())
+        if node < 0:
+            return None
+        with open(f"/sys/devices/system/node/node{node}/cpulist") as f:
+            txt = f.read().strip()
+        cpus = set()
+        for part in txt.split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        allowed = os.sched_getaffinity(0)
+        mine = cpus & allowed
+        if not mine or mine == allowed:
+            return {"node": node, "bound": False, "cpus_allowed": len(allowed)}
+        os.sched_setaffinity(0, mine)
+        return {"node": node, "bound": True, "cpus": len(mine)}
+    except Exception as e:                      # no sysfs / no such attribute: leave the placement to the launcher
+        return {"bound": False, "why": str(e)[:80]}
+
+
 class _Ctx:
     """Per-process state of the GPU arm: device, library, communicator."""
 
@@ -200,6 +227,7 @@ class _Ctx:
             raise SystemExit("bench.py: no CUDA device; incflo_b200 has no CPU fallback (use --impl reference for the CPU arm)")
         torch.cuda.set_device(self.local)
         self.dev = f"cuda:{self.local}"
+        self.numa = _bind_to_gpu_numa_node(torch, self.local) if not os.environ.get("NP_BENCH_NO_NUMA") else None
         self.L = capi.load()
         self.comm = None
         if self.world > 1:
@@ -520,7 +548,7 @@ def run_gpu(args):
                 "vcycles_per_step": vcycles / args.steps, "mg_levels": out["levels"], "ms_per_vcycle": ms / vcycles,
                 "ms_solve_per_vcycle": out["ms_solve"] / vcycles, "rel_res_history": out["hist"],
                 "clocks": out["clocks"], "e2e": out.get("e2e"), "gpu_launches": out["launches"],
-                "launches_per_vcycle": out["launches"] / vcycles,
+                "launches_per_vcycle": out["launches"] / vcycles, "host_numa_binding": ctx.numa,
                 "roofline": _roofline(out, n, G, peak, peak_src)}
         if "e2e_with_ctor" in out:
             line["e2e_with_ctor"] = out["e2e_with_ctor"]

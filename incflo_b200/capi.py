@@ -72,7 +72,7 @@ SYMBOLS = ["np_default_options", "np_create", "np_set_bc", "np_project", "np_app
            "np_copy_phi", "np_copy_gradphi", "np_destroy", "np_strerror", "np_num_levels", "np_level_ncell",
            "np_last_stats", "np_set_sigma", "np_get_sigma", "np_apply", "np_smooth", "np_restrict",
            "np_interp_add", "np_divu", "np_mknewu", "np_bottom_solve", "np_vcycle", "np_dot",
-           "np_nccl_unique_id", "np_nccl_comm_create", "np_nccl_comm_destroy", "np_is_device_pointer", "np_apply_noalloc", "np_cache_clear"]
+           "np_nccl_unique_id", "np_nccl_comm_create", "np_nccl_comm_destroy", "np_is_device_pointer", "np_apply_noalloc", "np_cache_clear", "np_resid_restrict"]
 
 _libs = {}
 
@@ -115,6 +115,7 @@ def load(path=None):
     L.np_smooth.argtypes = [C.c_void_p, C.c_int, C.POINTER(np_fab), C.POINTER(np_fab), C.c_int]
     L.np_restrict.argtypes = [C.c_void_p, C.c_int, C.POINTER(np_fab), C.POINTER(np_fab)]
     L.np_interp_add.argtypes = [C.c_void_p, C.c_int, C.POINTER(np_fab), C.POINTER(np_fab)]
+    L.np_resid_restrict.argtypes = [C.c_void_p, C.c_int, C.POINTER(np_fab), C.POINTER(np_fab), C.POINTER(np_fab)]
     L.np_divu.argtypes = [C.c_void_p, C.POINTER(np_fab), C.POINTER(np_fab)]
     L.np_mknewu.argtypes = [C.c_void_p, C.POINTER(np_fab), C.POINTER(np_fab), C.POINTER(np_fab)]
     L.np_bottom_solve.argtypes = [C.c_void_p, C.POINTER(np_fab), C.POINTER(np_fab), C.POINTER(C.c_int)]

@@ -109,6 +109,20 @@ int np_restrict(np_handle* h, int lc, const np_fab* fine, np_fab* crse)
     return fab_out(S, lc, tc.p, crse);
 }
 
+// K2 + K4 fused (k_resid_restrict + k_restrict_faces): crse = R(res - A cor) on level l -> l + 1
+int np_resid_restrict(np_handle* h, int l, const np_fab* cor, const np_fab* res, np_fab* crse)
+{
+    if (bad_level(h, l) || bad_level(h, l + 1)) return NP_ERR_INVALID;
+    NpSolver& S = h->S; if (!S.have_sigma) return NP_ERR_STATE;
+    if (S.lev[l + 1].replicated != S.lev[l].replicated) return NP_ERR_INVALID;
+    NpLevel& L = S.lev[l];
+    int rc = fab_in(S, l, cor, L.cor); if (rc) return rc;
+    rc = fab_in(S, l, res, L.res); if (rc) return rc;
+    L.cor_ghost_clean = false;
+    S.resid_restrict(l, nullptr);
+    return fab_out(S, l + 1, S.lev[l + 1].res, crse);
+}
+
 int np_interp_add(np_handle* h, int lf, np_fab* fine, const np_fab* crse)
 {
     if (bad_level(h, lf) || bad_level(h, lf + 1)) return NP_ERR_INVALID;

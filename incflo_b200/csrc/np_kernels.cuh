@@ -901,15 +901,31 @@ __device__ __forceinline__ double np_wgt_xy(const LevelDev& L, int i, int j)
     return w;
 }
 // FULL: the tile lies inside the domain, no face is Dirichlet and every dot-mask weight is 1: the masks fold away.
-template <int MODE, bool REDUCE, bool CS, bool FULL>
+// RR (MLMG::computeResOfCorrection + MLNodeLaplacian::restriction in one pass, "the residual is never stored"): the tile
+// strides are RR_SX x RR_SY = 62 x 30 so that neighbouring tiles overlap by two fine nodes; a tile then holds the whole 3 x 3
+// fine neighbourhood of its 31 x 15 coarse nodes (fine 2I = i0+2 .. i0+62).  The z part of the full weighting (1/4, 1/2, 1/4)
+// is accumulated in registers while the planes go by; at every odd fine plane the accumulated tile goes through shared
+// memory for the x / y part and one coarse plane is stored.  Coarse nodes ON the faces of the box need ghost residuals
+// (periodic images, Neumann mirrors, the neighbour rank's planes): the kernel stores the fine residual on the boundary shell
+// only (nodes within one of a face) and k_restrict_faces finishes those coarse nodes after the usual ghost fill.
+#define RR_SX 62
+#define RR_SY 30
+#define RR_TP 66                                        // pitch of the accumulated tile (even: 16-byte row pairs)
+struct RrArgs { LevelDev Lc; double* crse; int kcz; };   // coarse level descriptor / array, coarse planes per z-chunk
+template <int MODE, bool REDUCE, bool CS, bool FULL, bool RR = false>
 __device__ __forceinline__ void st_run(const LevelDev& L, const StCoef& C, double* __restrict__ y, const double* __restrict__ x,
                                        const double* __restrict__ b, const double* __restrict__ boff,
                                        double* __restrict__ part_max, double* __restrict__ part_sum, int zc,
-                                       const double* __restrict__ sig, double* ring)
+                                       const double* __restrict__ sig, double* ring, const RrArgs* rr = nullptr)
 {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int i0 = blockIdx.x * GS_TX, j0 = blockIdx.y * GS_TY, kb = blockIdx.z * zc;
-    const int nkl = min(kb + zc - 1, L.n[2]) - kb + 1;       // output planes kb .. kb+nkl-1
+    const int i0 = blockIdx.x * (RR ? RR_SX : GS_TX), j0 = blockIdx.y * (RR ? RR_SY : GS_TY);
+    // RR: this CTA produces the coarse planes Ka .. Kb (1 <= K <= nc2 - 1) from the fine planes 2 Ka - 1 .. 2 Kb + 1; the first
+    // and the last chunk also run the fine planes 0 and n2 (their residual is part of the stored shell)
+    const int Ka = RR ? 1 + (int)blockIdx.z * rr->kcz : 0, Kb = RR ? min(Ka + rr->kcz - 1, rr->Lc.n[2] - 1) : 0;
+    const int kb = RR ? (Ka == 1 ? 0 : 2 * Ka - 1) : (int)blockIdx.z * zc;
+    const int nkl = RR ? (Kb == rr->Lc.n[2] - 1 ? L.n[2] : 2 * Kb + 1) - kb + 1
+                       : min(kb + zc - 1, L.n[2]) - kb + 1;       // output planes kb .. kb+nkl-1
     const int gi = i0 + 2 * lane, gj = j0 + 4 * warp;
     const int row0 = 4 * warp + 1;
     const double off = (MODE == 1 && boff) ? boff[0] : 0.0;
@@ -940,6 +956,12 @@ __device__ __forceinline__ void st_run(const LevelDev& L, const StCoef& C, doubl
 #pragma unroll
         for (int r = 0; r < 4; ++r) { A1[a][r] = 0.0; A2[a][r] = 0.0; }
     double tmax = 0.0, tsum = 0.0;
+    double acc[2][4];                                    // RR: z-weighted residual of the coarse plane in the making
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+        for (int r = 0; r < 4; ++r) acc[a][r] = 0.0;
+    double* T = ring + ST_RING * GS_PLANE;               // RR: the accumulated tile, 32 rows x RR_TP
 
     load_plane(kb - 1); np_cp_async_commit();
     load_plane(kb);     np_cp_async_commit();
@@ -1028,10 +1050,13 @@ __device__ __forceinline__ void st_run(const LevelDev& L, const StCoef& C, doubl
                 if (k > L.owned_hi[2]) wz = 0.0;
                 if ((L.face[2] == NP_FACE_NEUMANN && k == 0) || (L.face[5] == NP_FACE_NEUMANN && k == L.n[2])) wz *= 0.5;
             }
+            double vv[2][4];                             // RR: the residual of this plane (0 outside the level / on Dirichlet faces)
+            const bool kshell = RR && (k <= 1 || k >= L.n[2] - 1);
 #pragma unroll
             for (int a = 0; a < 2; ++a)
 #pragma unroll
                 for (int r = 0; r < 4; ++r) {
+                    vv[a][r] = 0.0;
                     if (FULL || ((act >> (a * 4 + r)) & 1u)) {
                         const long long o = gbase + a + L.nsy * r;
                         double v = 0.0;
@@ -1039,13 +1064,49 @@ __device__ __forceinline__ void st_run(const LevelDev& L, const StCoef& C, doubl
                             const double ax = A1[a][r] + Dn[a][r];
                             v = (MODE == 1) ? (bv[a][r] - off) - ax : ax;
                         }
-                        y[o] = v;
+                        if (!RR) y[o] = v;
+                        else {
+                            vv[a][r] = v;
+                            const int i = gi + a, j = gj + r;
+                            if (kshell || i <= 1 || i >= L.n[0] - 1 || j <= 1 || j >= L.n[1] - 1) y[o] = v;      // boundary shell only
+                        }
                         if (REDUCE) {
                             tmax = np_absmax(tmax, v);
                             tsum += ((FULL || wone) ? wz : np_wgt_xy(L, gi + a, gj + r) * wz) * v;      // boundary threads redo the weight
                         }
                     }
                 }
+            if (RR) {
+                const bool odd = (k & 1) != 0;
+                const double wk = odd ? 0.25 : 0.5;
+#pragma unroll
+                for (int a = 0; a < 2; ++a)
+#pragma unroll
+                    for (int r = 0; r < 4; ++r) acc[a][r] += wk * vv[a][r];
+                if (odd) {
+                    const int K = (k - 1) >> 1;          // fine planes 2K-1, 2K, 2K+1 are in: coarse plane K
+                    if (K >= Ka && K <= Kb) {            // (uniform over the CTA)
+#pragma unroll
+                        for (int r = 0; r < 4; ++r)
+                            *reinterpret_cast<double2*>(T + (4 * warp + r) * RR_TP + 2 * lane) = make_double2(acc[0][r], acc[1][r]);
+                        __syncthreads();                 // the next write of T is two steps (two loop barriers) away
+                        const LevelDev& Lc = rr->Lc;
+                        for (int t = tid; t < 31 * 15; t += 256) {
+                            const int m = t % 31, rw = t / 31;
+                            const int I = (i0 >> 1) + 1 + m, J = (j0 >> 1) + 1 + rw;
+                            if (I <= Lc.n[0] - 1 && J <= Lc.n[1] - 1) {
+                                const double* tp = T + (2 * rw + 2) * RR_TP + (2 * m + 2);
+                                rr->crse[np_noff(Lc, I, J, K)] = 0.25 * tp[0] + 0.125 * ((tp[-1] + tp[1]) + (tp[-RR_TP] + tp[RR_TP]))
+                                    + 0.0625 * ((tp[-RR_TP - 1] + tp[-RR_TP + 1]) + (tp[RR_TP - 1] + tp[RR_TP + 1]));
+                            }
+                        }
+                    }
+#pragma unroll
+                    for (int a = 0; a < 2; ++a)
+#pragma unroll
+                        for (int r = 0; r < 4; ++r) acc[a][r] = 0.25 * vv[a][r];
+                }
+            }
         }
 #pragma unroll
         for (int a = 0; a < 2; ++a)
@@ -1080,6 +1141,47 @@ __global__ void __launch_bounds__(256, CS ? 2 : 1) k_stencil(LevelDev L, StCoef 
             && !(L.face[1] == NP_FACE_NEUMANN && j0 == 0) && !(L.face[4] == NP_FACE_NEUMANN && j1 == L.n[1]);
     if (full) st_run<MODE, REDUCE, CS, true>(L, C, y, x, b, boff, part_max, part_sum, zc, sig, ring);
     else      st_run<MODE, REDUCE, CS, false>(L, C, y, x, b, boff, part_max, part_sum, zc, sig, ring);
+}
+
+#define RR_SMEM_BYTES (ST_SMEM_BYTES + 32 * RR_TP * 8)
+// K2 + K4 fused: crse(interior) = R(b - *boff - A x); y receives the residual on the boundary shell only (see st_run, RR)
+template <bool CS>
+__global__ void __launch_bounds__(256, CS ? 2 : 1) k_resid_restrict(LevelDev L, StCoef C, double* __restrict__ y, const double* __restrict__ x,
+                                                                    const double* __restrict__ b, const double* __restrict__ boff,
+                                                                    const double* __restrict__ sig, RrArgs rr)
+{
+    NP_DYN_SMEM(double, ring);
+    const int i0 = blockIdx.x * RR_SX, j0 = blockIdx.y * RR_SY;
+    bool full = i0 + GS_TX - 1 <= L.n[0] && j0 + GS_TY - 1 <= L.n[1];
+#pragma unroll
+    for (int f = 0; f < 6; ++f) full = full && L.face[f] != NP_FACE_DIRICHLET;
+    if (full) st_run<1, false, CS, true, true>(L, C, y, x, b, boff, nullptr, nullptr, 0, sig, ring, &rr);
+    else      st_run<1, false, CS, false, true>(L, C, y, x, b, boff, nullptr, nullptr, 0, sig, ring, &rr);
+}
+// the coarse nodes on the six faces of the box (I = 0, nc0, J = 0, nc1, K = 0, nc2) from the fine residual stored on the
+// boundary shell, whose ghosts k_fill_boundary / the halo exchange have filled: plain mlndlap_restriction there
+__global__ void __launch_bounds__(256) k_restrict_faces(LevelDev Lc, LevelDev Lf, double* __restrict__ crse, const double* __restrict__ fine)
+{
+    const int e0 = Lc.n[0] + 1, e1 = Lc.n[1] + 1, e2 = Lc.n[2] + 1;
+    const long long g0 = 2LL * e1 * e2, g1 = 2LL * e0 * e2, g2 = 2LL * e0 * e1;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < g0 + g1 + g2; t += (long long)gridDim.x * blockDim.x) {
+        int i, j, k;
+        if (t < g0)           { long long q = t;           const int sd = (int)(q % 2); q /= 2; j = (int)(q % e1); k = (int)(q / e1); i = sd ? Lc.n[0] : 0; }
+        else if (t < g0 + g1) { long long q = t - g0;      const int sd = (int)(q % 2); q /= 2; i = (int)(q % e0); k = (int)(q / e0); j = sd ? Lc.n[1] : 0; }
+        else                  { long long q = t - g0 - g1; const int sd = (int)(q % 2); q /= 2; i = (int)(q % e0); j = (int)(q / e0); k = sd ? Lc.n[2] : 0; }
+        double v = 0.0;
+        if (!np_is_dirichlet(Lf, 2*i, 2*j, 2*k)) {
+            GlobX f{fine + np_noff(Lf, 2*i, 2*j, 2*k), Lf.nsy, Lf.nsz};
+            const double faces = (f(-1,0,0) + f(1,0,0)) + (f(0,-1,0) + f(0,1,0)) + (f(0,0,-1) + f(0,0,1));
+            const double edges = ((f(-1,-1,0) + f(1,-1,0)) + (f(-1,1,0) + f(1,1,0)))
+                               + ((f(-1,0,-1) + f(1,0,-1)) + (f(-1,0,1) + f(1,0,1)))
+                               + ((f(0,-1,-1) + f(0,1,-1)) + (f(0,-1,1) + f(0,1,1)));
+            const double corners = ((f(-1,-1,-1) + f(1,-1,-1)) + (f(-1,1,-1) + f(1,1,-1)))
+                                 + ((f(-1,-1,1) + f(1,-1,1)) + (f(-1,1,1) + f(1,1,1)));
+            v = 0.125 * f(0,0,0) + 0.0625 * faces + 0.03125 * edges + 0.015625 * corners;
+        }
+        crse[np_noff(Lc, i, j, k)] = v;
+    }
 }
 
 // ------------------------------------------------------------------------------------------------

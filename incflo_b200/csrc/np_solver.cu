@@ -59,6 +59,7 @@ int NpSolver::create(const np_geom* g, int nboxes, const np_box* boxes, const in
                      const NpComm& c, const np_options* o)
 {
     if (np_rt::init()) return NP_ERR_NO_DEVICE;
+    if (const char* e = std::getenv("NP_FUSED_RR")) fused_rr = std::atoi(e) != 0;        // experiment knob: 0 = residual and restriction as two kernels
     if (const char* e = std::getenv("NP_GS_VARIANT")) gs_variant_c = std::atoi(e);        // experiment knobs: which smoother kernel
     if (const char* e = std::getenv("NP_GSV_VARIANT")) gs_variant_v = std::atoi(e);
     geom = *g; opt = *o; comm = c; comm.rank = my_rank; comm.nranks = nranks;
@@ -172,6 +173,8 @@ int NpSolver::create(const np_geom* g, int nboxes, const np_box* boxes, const in
     NP_GS3_ATTR(2, 8, true, 2); NP_GS3_ATTR(2, 4, true, 1); NP_GS3_ATTR(4, 8, true, 2); NP_GS3_ATTR(4, 4, true, 2);
     NP_GS3_ATTR(2, 8, false, 1); NP_GS3_ATTR(2, 4, false, 1); NP_GS3_ATTR(4, 4, false, 1); NP_GS3_ATTR(2, 8, false, 2);
 #undef NP_GS3_ATTR
+    cudaFuncSetAttribute(k_resid_restrict<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RR_SMEM_BYTES);
+    cudaFuncSetAttribute(k_resid_restrict<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RR_SMEM_BYTES);
     cudaFuncSetAttribute(k_stencil<0, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ST_SMEM_BYTES);
     cudaFuncSetAttribute(k_stencil<1, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ST_SMEM_BYTES);
     cudaFuncSetAttribute(k_stencil<1, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ST_SMEM_BYTES);
@@ -630,8 +633,11 @@ void NpSolver::vcycle(bool add_to_sol)
         NpLevel& L = lev[l];
         if (opt.num_pre_smooth == 0) { zero(L.cor, L.d.ntot); L.cor_ghost_clean = true; }
         for (int i = 0; i < opt.num_pre_smooth; ++i) smooth(l, i == 0, nullptr);      // cor = 0 is implied by zero_in
-        residual(l, L.rescor, L.cor, L.res, false, l == 0 ? lvl0_off : nullptr);   // computeResOfCorrection
-        restrict_to(l + 1, lev[l + 1].res, L.rescor);
+        if (fused_rr) resid_restrict(l, l == 0 ? lvl0_off : nullptr);              // computeResOfCorrection + restriction, one pass
+        else {
+            residual(l, L.rescor, L.cor, L.res, false, l == 0 ? lvl0_off : nullptr);
+            restrict_to(l + 1, lev[l + 1].res, L.rescor);
+        }
     }
     stats.bottom_iters_total += bottom_solve();
     for (int l = nl - 2; l >= 0; --l) {
@@ -716,6 +722,36 @@ void NpSolver::restrict_to_replica(int lc, double* crse, const double* fine)
     NP_LAUNCH(false, k_restrict, grid_nodes(dl), NP_BLK, 0, stream, dl, lev[lc - 1].d, agg_send, fine); ++launches;
     if (comm.allgather(comm.ctx, agg_send, agg_recv, dl.ntot, (void*)stream)) err = NP_ERR_NCCL;
     NP_LAUNCH(false, k_assemble_nodal, grid_nodes(dc), NP_BLK, 0, stream, dc, dl, crse, (const double*)agg_recv, comm.nranks); ++launches;
+}
+// MLMG::computeResOfCorrection + MLNodeLaplacian::restriction as one pass over level l (k_resid_restrict): the residual of the
+// correction is restricted on the fly and stored on the boundary shell only; the coarse nodes on the faces of the box, which
+// need ghost residuals (periodic images, mirrors, the neighbour rank's planes), come from that shell after the usual ghost
+// fill (k_restrict_faces).  Result: lev[l + 1].res (through the all-gather when level l + 1 is the first replicated one).
+void NpSolver::resid_restrict(int l, const double* boff)
+{
+    NpLevel& F = lev[l]; NpLevel& Cn = lev[l + 1];
+    const LevelDev& df = F.d;
+    if (!F.cor_ghost_clean) fill(l, F.cor);
+    const bool to_replica = Cn.replicated && !F.replicated;
+    const LevelDev dc = to_replica ? local_coarse_of(F) : Cn.d;
+    RrArgs rr; rr.Lc = dc; rr.crse = to_replica ? agg_send : Cn.res;
+    const int tx = std::max((df.n[0] - 1 + RR_SX - 1) / RR_SX, (dc.n[0] - 2) / 31 + 1);       // every fine node and every interior coarse node
+    const int ty = std::max((df.n[1] - 1 + RR_SY - 1) / RR_SY, (dc.n[1] - 2) / 15 + 1);
+    const int nck = std::max(dc.n[2] - 1, 1);                                                 // interior coarse planes
+    const int nch_want = (888 + tx * ty - 1) / (tx * ty);
+    rr.kcz = std::min(32, std::max(2, (nck + nch_want - 1) / nch_want));
+    const dim3 grid(std::max(tx, 1), std::max(ty, 1), (nck + rr.kcz - 1) / rr.kcz);
+    const StCoef c = st_coef(df);
+    if (df.const_sigma) NP_LAUNCH(true, (k_resid_restrict<true>), grid, dim3(256), RR_SMEM_BYTES, stream, df, c, F.rescor, (const double*)F.cor, (const double*)F.res, boff, (const double*)F.sigma, rr);
+    else                NP_LAUNCH(true, (k_resid_restrict<false>), grid, dim3(256), RR_SMEM_BYTES, stream, df, c, F.rescor, (const double*)F.cor, (const double*)F.res, boff, (const double*)F.sigma, rr);
+    ++launches;
+    fill(l, F.rescor);                     // ghosts of the shell: periodic images, mirrors, the neighbours' planes
+    const long long nface = 2LL * ((long long)(dc.n[1] + 1) * (dc.n[2] + 1) + (long long)(dc.n[0] + 1) * (dc.n[2] + 1) + (long long)(dc.n[0] + 1) * (dc.n[1] + 1));
+    NP_LAUNCH(false, k_restrict_faces, dim3(shell_blocks(nface)), dim3(256), 0, stream, dc, df, rr.crse, (const double*)F.rescor); ++launches;
+    if (to_replica) {
+        if (comm.allgather(comm.ctx, agg_send, agg_recv, dc.ntot, (void*)stream)) err = NP_ERR_NCCL;
+        NP_LAUNCH(false, k_assemble_nodal, grid_nodes(Cn.d), NP_BLK, 0, stream, Cn.d, dc, Cn.res, (const double*)agg_recv, comm.nranks); ++launches;
+    }
 }
 void NpSolver::avgdown_sigma_to_replica(int lc)
 {

@@ -108,6 +108,8 @@ struct NpSolver {
     void smooth(int l, bool zero_in, double* add_to);              // on lev[l].cor / res
     void restrict_to(int lc, double* crse, double* fine);          // fine gets its ghosts filled
     void restrict_to_replica(int lc, double* crse, const double* fine);
+    void resid_restrict(int l, const double* boff);                // lev[l+1].res = R(lev[l].res - *boff - A lev[l].cor), one pass
+    bool fused_rr = true;
     void avgdown_sigma_to_replica(int lc);
     void interp_add(int lf, double* fine, const double* crse);
     void make_solvable(int l, double* x);

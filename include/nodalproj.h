@@ -189,6 +189,7 @@ int np_apply(np_handle* h, int mglev, const np_fab* x, np_fab* y);              
 int np_apply_noalloc(np_handle* h, int mglev, const np_fab* x, np_fab* y);
 int np_smooth(np_handle* h, int mglev, np_fab* x, const np_fab* rhs, int ncalls);      /* K3  ncalls x Fsmooth */
 int np_restrict(np_handle* h, int cmglev, const np_fab* fine, np_fab* crse);           /* K4 */
+int np_resid_restrict(np_handle* h, int mglev, const np_fab* cor, const np_fab* res, np_fab* crse);   /* K2 + K4 fused: crse = R(res - A cor) */
 int np_interp_add(np_handle* h, int fmglev, np_fab* fine, const np_fab* crse);         /* K5 */
 int np_divu(np_handle* h, const np_fab* vel, np_fab* rhs);                             /* K1 */
 int np_mknewu(np_handle* h, const np_fab* phi, np_fab* vel, np_fab* gradphi);          /* K7 (sigma from np_set_sigma) */

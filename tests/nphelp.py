@@ -75,6 +75,11 @@ class Driver:
         capi.check(self.L, self.L.np_restrict(self.h, lc, C.byref(ff.c()), C.byref(fc.c())))
         return fc.numpy_valid()[0]
 
+    def resid_restrict(self, l, cor, res):
+        fc, fr, fo = self.nfab(l, cor), self.nfab(l, res), self.nfab(l + 1)
+        capi.check(self.L, self.L.np_resid_restrict(self.h, l, C.byref(fc.c()), C.byref(fr.c()), C.byref(fo.c())))
+        return fo.numpy_valid()[0]
+
     def interp_add(self, lf, fine, crse):
         ff, fc = self.nfab(lf, fine), self.nfab(lf + 1, crse)
         capi.check(self.L, self.L.np_interp_add(self.h, lf, C.byref(ff.c()), C.byref(fc.c())))

@@ -327,3 +327,24 @@ def test_mac_multibox_equals_onebox(backend, host):
         f = paste(fl[d], d, umac[d].shape)
         assert np.abs(f - (u1[d] - umac[d])).max() <= 1e-9 * np.abs(f).max()
     P.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("const", [True, False])
+def test_mac_one_pass_smoother_is_deterministic_on_gpu(const):
+    """Race proxy for k_mac_rb3 (compute-sanitizer is closed on this pool): 20 repeats of two one-pass smooths on whole tiles
+    (128 x 32 x 24 cells, three z-chunks) must be bitwise identical."""
+    import torch
+    torch.cuda.set_device(0)
+    rng = np.random.default_rng(8)
+    ncell, hi = (128, 32, 24), (4.0, 1.0, 0.75)
+    bclo = bchi = (0, 0, 0)
+    beta = random_beta(rng, ncell, bclo, const)
+    drv = Drv(ncell, hi, bclo, bchi, beta, dict(lib=capi.load(), like="cuda", device="cuda:0"), fused_rb_min_n=2, fused_rb_const=1)
+    x, b = rng.standard_normal(ncell[::-1]), rng.standard_normal(ncell[::-1])
+    ref = None
+    for rep in range(20):
+        s = drv.smooth(0, x, b, 2)
+        if ref is None:
+            ref = s
+        assert np.array_equal(s, ref), rep

@@ -51,6 +51,12 @@ def main():
         torch.cuda.synchronize()
         return e0.elapsed_time(e1)
 
+    if os.environ.get("NP_TIME_APPLY"):          # the operator kernel under `ncu --metrics gpu__time_duration.sum -k regex:k_stencil`
+        y = Fab.zeros(nl, 1, 1, True, "torch", dev)
+        for _ in range(4):
+            capi.check(L, L.np_apply(P.h, lev, C.byref(x.c()), C.byref(y.c())))
+        torch.cuda.synchronize()
+        return
     run(2)
     t = {nc: min(run(nc) for _ in range(3)) for nc in (0, 1, 2, 3, 5, 21)}
     print("  hook call ms by ncalls:", {k: round(v, 4) for k, v in t.items()},
