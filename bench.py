@@ -300,6 +300,8 @@ def _make_projector(ctx, args, pb, nloc, G, vel, rank=None, nranks=None, comm="c
         kw["agg_min_local_nz"] = args.agg_min_local_nz
     if args.no_overlap:
         kw["overlap_halo"] = 0
+    if args.overlap:
+        kw["overlap_halo"] = 1
     if args.no_p2p:
         kw["p2p_halo"] = 0
     kw.update(extra)
@@ -953,6 +955,7 @@ def main():
     ap.add_argument("--smooth-zchunk", type=int, default=0, help="experiment knob: fixed smoother z-chunk on every level (0: the level rule)")
     ap.add_argument("--agg-min-local-nz", type=int, default=0, help="experiment knob: replicate MG levels whose slab is thinner than this (0: library default)")
     ap.add_argument("--no-p2p", action="store_true", help="experiment knob: halo exchange through ncclSend/ncclRecv instead of peer memory")
+    ap.add_argument("--overlap", action="store_true", help="experiment knob: overlap_halo=1 (end z-chunks first, their planes exchanged beside the interior chunks)")
     ap.add_argument("--no-overlap", action="store_true", help="experiment knob: halo exchange on the solver stream (overlap_halo=0)")
     ap.add_argument("--verbose", type=int, default=0, help="nodal_proj.verbose (4: per-launch smoother times on stderr)")
     args = ap.parse_args()

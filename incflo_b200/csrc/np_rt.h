@@ -29,6 +29,7 @@ inline int memset_async(void* p, int v, size_t n, np_stream_t) { std::memset(p, 
 inline int copy_async(void* d, const void* s, size_t n, np_stream_t) { std::memmove(d, s, n); return 0; }
 inline int stream_sync(np_stream_t) { return 0; }
 inline int stream_create(np_stream_t* s) { *s = nullptr; return 0; }
+inline int stream_create_high_priority(np_stream_t* s) { *s = nullptr; return 0; }
 inline int stream_destroy(np_stream_t) { return 0; }
 inline int stream_wait_event(np_stream_t, np_event_t) { return 0; }     // the emulation runs everything in program order
 inline int ipc_export(void*, void*) { return 1; }                         // no peer memory in the emulation: NCCL-style callbacks only
@@ -64,6 +65,10 @@ inline int memset_async(void* p, int v, size_t n, np_stream_t s) { return cudaMe
 inline int copy_async(void* d, const void* s, size_t n, np_stream_t st) { return cudaMemcpyAsync(d, s, n, cudaMemcpyDefault, st) == cudaSuccess ? 0 : 1; }
 inline int stream_sync(np_stream_t s) { return cudaStreamSynchronize(s) == cudaSuccess ? 0 : 1; }
 inline int stream_create(np_stream_t* s) { return cudaStreamCreateWithFlags(s, cudaStreamNonBlocking) == cudaSuccess ? 0 : 1; }
+inline int stream_create_high_priority(np_stream_t* s) {     // the halo kernels must get SM slots while a big kernel of the main stream runs
+    int lo = 0, hi = 0; cudaDeviceGetStreamPriorityRange(&lo, &hi);
+    return cudaStreamCreateWithPriority(s, cudaStreamNonBlocking, hi) == cudaSuccess ? 0 : 1;
+}
 inline int stream_destroy(np_stream_t s) { return cudaStreamDestroy(s) == cudaSuccess ? 0 : 1; }
 inline int stream_wait_event(np_stream_t s, np_event_t e) { return cudaStreamWaitEvent(s, e, 0) == cudaSuccess ? 0 : 1; }
 // CUDA IPC: one process per GPU, so a neighbour's arrays are reached through exported allocation handles (64 bytes)

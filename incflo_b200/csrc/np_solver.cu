@@ -160,7 +160,7 @@ int NpSolver::create(const np_geom* g, int nboxes, const np_box* boxes, const in
     }
     for (int e = 0; e < 4; ++e) np_rt::event_create(&ev[e]);
     if (nranks > 1 && opt.overlap_halo) {
-        have_comm_stream = np_rt::stream_create(&comm_stream) == 0;
+        have_comm_stream = np_rt::stream_create_high_priority(&comm_stream) == 0;
         np_rt::event_create(&ev_halo[0]); np_rt::event_create(&ev_halo[1]);
     }
     if (opt.profile_kernels) { prof_ev.resize(2048); for (auto& e : prof_ev) np_rt::event_create(&e); }
@@ -351,7 +351,7 @@ int NpSolver::setup_peer_halo()
 }
 
 // one exchange of the z-boundary planes of x (level l) through peer memory; false: x is not registered, use NCCL
-bool NpSolver::halo_p2p(int l, double* x)
+bool NpSolver::halo_p2p(int l, double* x, np_stream_t on)
 {
     if (!peer.ok) return false;
     int id = -1;
@@ -368,7 +368,7 @@ bool NpSolver::halo_p2p(int l, double* x)
     a.epoch = ++peer.epoch; a.counter = peer.counter;
     const long long chunks = (3 * pl / 2 + 255) / 256;                          // 16-byte stores per thread pass
     const int nb = (int)std::min<long long>(64, std::max<long long>(1, chunks / 8));
-    NP_LAUNCH(false, k_halo_p2p, dim3(nb), dim3(256), 0, stream, a); ++launches;
+    NP_LAUNCH(false, k_halo_p2p, dim3(nb), dim3(256), 0, on, a); ++launches;
     return true;
 }
 
@@ -380,7 +380,7 @@ void NpSolver::fill(int l, double* x)
     const long long nshell = 3LL * ((long long)(d.n[1]+3)*(d.n[2]+3) + (long long)(d.n[0]+3)*(d.n[2]+3) + (long long)(d.n[0]+3)*(d.n[1]+3));
     NP_LAUNCH(false, k_fill_boundary, dim3(shell_blocks(nshell)), dim3(256), 0, stream, d, x); ++launches;
     if (is_sharded(*this, L)) {
-        if (halo_p2p(l, x)) return;
+        if (halo_p2p(l, x, stream)) return;
         int lo, hi; z_neighbours(*this, lo, hi);
         const long long pl = d.nsz;
         // to the lower rank: my planes 0,1 (its n2, n2+1); to the upper rank: my plane n2-1 (its -1)
@@ -542,10 +542,12 @@ void NpSolver::smooth(int l, bool zero_in, double* add_to)
         const long long per = 3LL * (d.n[1] + 3) + 3LL * (d.n[0] + 3);
         NP_LAUNCH(false, k_fill_xy_planes, dim3(shell_blocks(per * 2)), dim3(256), 0, comm_stream, d, xo, 0, 2); ++launches;
         NP_LAUNCH(false, k_fill_xy_planes, dim3(shell_blocks(per)), dim3(256), 0, comm_stream, d, xo, d.n[2] - 1, 1); ++launches;
-        int lo, hi; z_neighbours(*this, lo, hi);
-        const long long pl = d.nsz;
-        if (comm.sendrecv(comm.ctx, xo + pl * 1, 2 * pl, xo + 0, pl, xo + pl * (long long)d.n[2], pl,
-                          xo + pl * (long long)(d.n[2] + 1), 2 * pl, lo, hi, (void*)comm_stream)) err = NP_ERR_NCCL;
+        if (!halo_p2p(l, xo, comm_stream)) {          // peer-memory stores beside the interior chunks; NCCL if peer memory is unavailable
+            int lo, hi; z_neighbours(*this, lo, hi);
+            const long long pl = d.nsz;
+            if (comm.sendrecv(comm.ctx, xo + pl * 1, 2 * pl, xo + 0, pl, xo + pl * (long long)d.n[2], pl,
+                              xo + pl * (long long)(d.n[2] + 1), 2 * pl, lo, hi, (void*)comm_stream)) err = NP_ERR_NCCL;
+        }
         np_rt::event_record(ev_halo[1], comm_stream);
         ga.zmap0 = 1; ga.zmapS = 1; launch(nch - 2);
         if (prof) { np_rt::event_record(prof_ev[prof_n + 1], stream); prof_n += 2; }

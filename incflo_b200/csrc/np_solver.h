@@ -68,7 +68,7 @@ struct NpSolver {
         unsigned long long epoch = 0;
     } peer;
     int setup_peer_halo();
-    bool halo_p2p(int l, double* x);
+    bool halo_p2p(int l, double* x, np_stream_t on);
     // several boxes per rank: the caller's boxes tile this rank's z-slab; they are gathered into slab-shaped fabs
     // (mb_vel: 3 comp, 1 ghost; mb_sig: 1 comp, 0 ghost), the projection runs on the slab, and u / phi / grad(phi)
     // are scattered back into per-box fabs (mb_phi, mb_gphi: the library-owned results np_get_* hands out)
