@@ -799,24 +799,8 @@ DIFF_BYTES = {True: round((8 + 8 * 32 + 32 + 9 + 17) * 8 / 7) + 24 + 32 + 8, Fal
 
 
 def _diffusion_problem(n, dev, variable_eta, torch):
-    f64 = dict(dtype=torch.float64, device=dev)
-    g = (torch.arange(n, **f64) + 0.5) / n
-    x, y, z = g[None, None, :], g[None, :, None], g[:, None, None]
-    r2d = torch.clamp(torch.hypot(x - 0.5, y - 0.5), max=0.5)
-    h = 0.5 - 0.01 * torch.cos(2 * 3.141592653589793 * r2d)
-    rho = (0.5 + 0.75 * (1.0 + torch.tanh((z - h) / 0.005))).expand(n, n, n).contiguous()
-    tracer = (torch.exp(-((x - 0.5) ** 2 + (y - 0.5) ** 2 + (z - 0.4) ** 2) / 0.02)
-              + 0.1 * torch.sin(6.283185307179586 * x) * torch.sin(6.283185307179586 * y) * torch.sin(6.283185307179586 * z)).contiguous()
-    mu0 = 1.0e-3
-    faces = []
-    for d in range(3):
-        shp = [n, n, n]; shp[2 - d] += 1
-        if variable_eta:
-            zz = (torch.arange(shp[0], **f64) + (0.0 if d == 2 else 0.5)) / n
-            faces.append((mu0 * (1.0 + 0.5 * torch.tanh((zz - 0.5) / 0.05)))[:, None, None].expand(*shp).contiguous()[None])
-        else:
-            faces.append(torch.full([1] + shp, mu0, **f64))
-    return rho[None].contiguous(), tracer[None].contiguous(), faces
+    from incflo_b200 import problems
+    return problems.diffusion_problem_torch(n, dev, variable_eta)
 
 
 def run_gpu_diffusion(args):

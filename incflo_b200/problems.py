@@ -220,3 +220,28 @@ def mac_problem_torch(name, ncell, prob_hi, device, ngrow=0, koff=0, nz_local=No
         del f, b, p
     bc = ((0, 0, 0), (0, 0, 0)) if name == "double_shear" else ((0, 0, NEUMANN), (0, 0, NEUMANN))
     return umac, beta, bc[0], bc[1]
+
+
+def diffusion_problem_torch(n, dev, variable_eta):
+    """Scalar diffusion workload of bench.py --path diffusion and tests/test_fullsize.py: Rayleigh-Taylor density (ratio 4, the
+    interface of /root/reference/src/prob/prob_init_fluid.cpp's init_rayleigh_taylor), a Gaussian blob plus a sine mode as the
+    tracer, eta uniform or varying in z.  Returns (rho [1,n,n,n], tracer [1,n,n,n], [bx, by, bz] face arrays [1,...])."""
+    import torch
+    f64 = dict(dtype=torch.float64, device=dev)
+    g = (torch.arange(n, **f64) + 0.5) / n
+    x, y, z = g[None, None, :], g[None, :, None], g[:, None, None]
+    r2d = torch.clamp(torch.hypot(x - 0.5, y - 0.5), max=0.5)
+    h = 0.5 - 0.01 * torch.cos(2 * 3.141592653589793 * r2d)
+    rho = (0.5 + 0.75 * (1.0 + torch.tanh((z - h) / 0.005))).expand(n, n, n).contiguous()
+    tracer = (torch.exp(-((x - 0.5) ** 2 + (y - 0.5) ** 2 + (z - 0.4) ** 2) / 0.02)
+              + 0.1 * torch.sin(6.283185307179586 * x) * torch.sin(6.283185307179586 * y) * torch.sin(6.283185307179586 * z)).contiguous()
+    mu0 = 1.0e-3
+    faces = []
+    for d in range(3):
+        shp = [n, n, n]; shp[2 - d] += 1
+        if variable_eta:
+            zz = (torch.arange(shp[0], **f64) + (0.0 if d == 2 else 0.5)) / n
+            faces.append((mu0 * (1.0 + 0.5 * torch.tanh((zz - 0.5) / 0.05)))[:, None, None].expand(*shp).contiguous()[None])
+        else:
+            faces.append(torch.full([1] + shp, mu0, **f64))
+    return rho[None].contiguous(), tracer[None].contiguous(), faces

@@ -223,3 +223,44 @@ def test_mac_fullsize_exact_projection(workload, max_vc):
     for a, b in zip(umac, u1):
         assert float((a - 2.5 * b).norm() / b.norm()) < 1e-10
     P.close()
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# Scalar diffusion at full size: (rho - dt div(eta grad)) s = rho s_old on 512^3 cells, periodic
+# x / y, Neumann walls in z.  Size-independent properties of the implicit step: the returned field solves the system (checked
+# with the operator hook), the step conserves sum(rho s) (the flux terms telescope to zero without Dirichlet faces), it obeys
+# the discrete maximum principle (M-matrix, rows of the right-hand side are rho s_old), and it is linear in s_old.
+# ---------------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("variable_eta", [False, True])
+def test_scalar_diffusion_fullsize_properties(variable_eta):
+    import torch
+    from incflo_b200.diffusion import DiffusionScalarOp
+    torch.cuda.set_device(0)
+    dev, dt = "cuda:0", 0.01
+    rho, tr0, faces = problems.diffusion_problem_torch(N, dev, variable_eta)
+    L = capi.load()
+    op = DiffusionScalarOp(Geometry((N, N, N), (0, 0, 0), (1, 1, 1), [True, True, False]), (0, 0, 2), (0, 0, 2), lib=L, like="torch", device=dev)
+    frho, feta = Fab(rho, 0), [[Fab(f, 0) for f in faces]]
+    ftr = Fab(tr0.clone(), 0)
+    st = op.diffuse_scalar(ftr, frho, feta, dt, RTOL, ATOL)[0]
+    assert st.status == 0 and st.n_levels == 9 and st.n_vcycles <= 9
+    assert st.sigma_is_const == (0 if variable_eta else 1)
+    hist = [st.res_history[i] for i in range(st.n_vcycles)]
+    assert all(b < 0.2 * a for a, b in zip(hist, hist[1:]))
+    # solves the system: || rho s_old - A s ||_inf <= rtol || rho s_old ||_inf (recomputed with the operator hook)
+    y = Fab.zeros((N, N, N), 1, 0, False, "torch", dev)
+    capi.check(L, L.mp_apply(op.P.h, 0, C.byref(ftr.c()), C.byref(y.c())))
+    rhs = rho * tr0
+    assert float((rhs - y.data).abs().max()) <= 1.5 * RTOL * float(rhs.abs().max())
+    # conservation and the maximum principle
+    assert abs(float((rho * ftr.data).sum() - rhs.sum())) <= 1e-10 * float(rhs.abs().sum())
+    assert float(ftr.data.min()) >= float(tr0.min()) - 1e-10 and float(ftr.data.max()) <= float(tr0.max()) + 1e-10
+    # the step moved something (otherwise the checks above are empty): the sharp Gaussian loses height
+    assert float((ftr.data - tr0).abs().max()) > 1e-4
+    # linear in s_old
+    s1 = ftr.data.clone()
+    ftr.data.copy_(tr0).mul_(-2.0)
+    st2 = op.diffuse_scalar(ftr, frho, feta, dt, RTOL, ATOL)[0]
+    assert st2.status == 0 and st2.n_vcycles == st.n_vcycles
+    assert float((ftr.data + 2.0 * s1).norm() / s1.norm()) < 1e-10
+    op.close()
