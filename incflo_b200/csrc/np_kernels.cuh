@@ -872,6 +872,7 @@ __global__ void __launch_bounds__(256, CS ? 2 : 1) k_gs2(LevelDev L, GsArgs A)
 }
 
 #include "np_gs3.cuh"
+#include "np_gs_small.cuh"
 
 // ------------------------------------------------------------------------------------------------
 // K2, constant sigma: y = A x  (MODE 0)  or  y = (b - *boff) - A x  (MODE 1), marching in z.
@@ -1305,6 +1306,8 @@ __global__ void __launch_bounds__(128) k_interp_add_w(LevelDev Lf, LevelDev Lc, 
                 fine[np_noff(Lf, i + a, j + b, k + c)] += v[c][b][a];
             }
 }
+
+#include "np_interp_w.cuh"
 
 // K5, plain trilinear (constant sigma, or interp_sigma_weighted = 0): one thread per COARSE node (I,J,K) updates the
 // 2x2x2 fine nodes (2I-1..2I, 2J-1..2J, 2K-1..2K) from the coarse nodes (I-1..I, J-1..J, K-1..K); fine pairs in x are

@@ -60,6 +60,8 @@ int NpSolver::create(const np_geom* g, int nboxes, const np_box* boxes, const in
 {
     if (np_rt::init()) return NP_ERR_NO_DEVICE;
     if (const char* e = std::getenv("NP_FUSED_RR")) fused_rr = std::atoi(e) != 0;        // experiment knob: 0 = residual and restriction as two kernels
+    if (const char* e = std::getenv("NP_GS_SMALL")) gs_small = std::atoi(e);
+    if (const char* e = std::getenv("NP_INTERP_MARCH")) interp_march = std::atoi(e) != 0;
     if (const char* e = std::getenv("NP_GS_VARIANT")) gs_variant_c = std::atoi(e);        // experiment knobs: which smoother kernel
     if (const char* e = std::getenv("NP_GSV_VARIANT")) gs_variant_v = std::atoi(e);
     geom = *g; opt = *o; comm = c; comm.rank = my_rank; comm.nranks = nranks;
@@ -169,6 +171,8 @@ int NpSolver::create(const np_geom* g, int nboxes, const np_box* boxes, const in
 #ifndef NP_EMU
     cudaFuncSetAttribute(k_gs2<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GS_SMEM_BYTES);
     cudaFuncSetAttribute(k_gs2<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GS_SMEM_BYTES);
+    cudaFuncSetAttribute(k_gs_small<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GS_SMEM_BYTES);
+    cudaFuncSetAttribute(k_gs_small<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GS_SMEM_BYTES);
 #define NP_GS3_ATTR(BW, BH, CS, MINB) cudaFuncSetAttribute(k_gs3<BW, BH, CS, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G3<BW, BH>::SMEM_BYTES)
     NP_GS3_ATTR(2, 8, true, 2); NP_GS3_ATTR(2, 4, true, 1); NP_GS3_ATTR(4, 8, true, 2); NP_GS3_ATTR(4, 4, true, 2);
     NP_GS3_ATTR(2, 8, false, 1); NP_GS3_ATTR(2, 4, false, 1); NP_GS3_ATTR(4, 4, false, 1); NP_GS3_ATTR(2, 8, false, 2);
@@ -506,6 +510,13 @@ void NpSolver::smooth(int l, bool zero_in, double* add_to)
 #define NP_GS3(BW, BH, CS, MINB) NP_LAUNCH(true, (k_gs3<BW, BH, CS, MINB>), g, dim3(G3<BW, BH>::CTA), (G3<BW, BH>::SMEM_BYTES), stream, d, ga)
     auto launch = [&](int nz) {
         const dim3 g(grid.x, grid.y, nz);
+        // a launch of at most one CTA per SM is a chain of plane steps with nothing to hide behind: the 2 x 2-block kernel
+        if (gs_small && (long long)g.x * g.y * g.z <= (long long)gs_small * np_rt::sm_count()) {
+            if (d.const_sigma) NP_LAUNCH(true, (k_gs_small<true>), g, dim3(GSS_CTA), smem, stream, d, ga);
+            else               NP_LAUNCH(true, (k_gs_small<false>), g, dim3(GSS_CTA), smem, stream, d, ga);
+            ++launches;
+            return;
+        }
         if (d.const_sigma) {
             switch (gs_variant_c) {
             case 1: NP_GS3(2, 8, true, 2); break;
@@ -579,7 +590,14 @@ void NpSolver::interp_add(int lf, double* fine, const double* crse)
 {
     const LevelDev& df = lev[lf].d; const LevelDev& dc = lev[lf + 1].d;
     const int koffc = (lev[lf + 1].replicated && !lev[lf].replicated) ? lev[lf].koff / 2 : 0;
-    if (opt.interp_sigma_weighted && !df.const_sigma)
+    if (opt.interp_sigma_weighted && !df.const_sigma && interp_march) {
+        // z-marching form: 31 x 7 coarse cells per CTA and plane, a run of coarse planes per CTA (about six CTAs per SM in all)
+        const int nc0 = df.n[0] / 2, nc1 = df.n[1] / 2, nc2 = df.n[2] / 2;
+        const int tx = (nc0 + IW_TX - 1) / IW_TX, ty = (nc1 + 1 + IW_TY - 1) / IW_TY;
+        const int nch_want = (6 * np_rt::sm_count() + tx * ty - 1) / (tx * ty);
+        const int kcz = std::min(32, std::max(std::min(4, nc2), (nc2 + nch_want - 1) / nch_want));
+        NP_LAUNCH(true, k_interp_add_w2, dim3(tx, ty, (nc2 + kcz - 1) / kcz), dim3(256), 0, stream, df, dc, fine, crse, (const double*)lev[lf].sigma, koffc, kcz);
+    } else if (opt.interp_sigma_weighted && !df.const_sigma)
         NP_LAUNCH(false, k_interp_add_w, dim3((df.n[0] / 2 + 1 + 31) / 32, (df.n[1] / 2 + 1 + 3) / 4, df.n[2] / 2 + 1), dim3(32, 4, 1), 0, stream, df, dc, fine, crse, (const double*)lev[lf].sigma, koffc);
     else
         NP_LAUNCH(false, k_interp_add_tri, dim3((df.n[0] / 2 + 1 + 31) / 32, (df.n[1] / 2 + 1 + 7) / 8, df.n[2] / 2 + 1), NP_BLK, 0, stream, df, dc, fine, crse, koffc);

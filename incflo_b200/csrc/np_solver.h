@@ -91,6 +91,8 @@ struct NpSolver {
     const double* lvl0_off = nullptr;   // device scalar subtracted from lev[0].res by its consumers (lazy makeSolvable)
     int err = 0;
     int gs_variant_c = 0, gs_variant_v = 0;   // which smoother kernel runs for constant / variable sigma (0: k_gs2)
+    bool interp_march = true;                 // sigma-weighted prolongation: k_interp_add_w2 (z-marching); env NP_INTERP_MARCH=0: k_interp_add_w
+    int gs_small = 0;                         // smoother launches of <= gs_small * (SM count) CTAs run k_gs_small (env NP_GS_SMALL; 0: never = default: measured slower than k_gs2)
 
     int create(const np_geom* g, int nboxes, const np_box* boxes, const int* owner, int my_rank, int nranks,
                const NpComm& c, const np_options* o);

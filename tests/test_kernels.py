@@ -55,6 +55,21 @@ def test_apply_restrict_interp_sigma(backend, bclo, bchi, const_sigma):
 
 
 @pytest.mark.parametrize("bclo,bchi", BCS)
+@pytest.mark.parametrize("ncell", [(136, 36, 24), (64, 16, 40)])
+def test_weighted_interpolation_multi_tile(backend, bclo, bchi, ncell):
+    """k_interp_add_w2 (sigma-weighted prolongation marching in z: 31 x 7 coarse cells per CTA, values of the neighbouring
+    threads through shared memory, aligned pair stores) on levels with several tiles in x and y and several z-chunks, against
+    the oracle's per-node definition (mlndlap_interpadd_aa) on every level pair."""
+    rng = np.random.default_rng(33)
+    sigma = rng.uniform(0.5, 2.0, ncell[::-1])
+    drv, orc = make(backend, ncell, bclo, bchi, sigma, prob_hi=(1.7, 0.45, 0.6))
+    for l in range(1, orc.num_levels):
+        f = nodal(rng, orc.nshape(l - 1), bclo, bchi)
+        c = nodal(rng, orc.nshape(l), bclo, bchi)
+        assert relerr(drv.interp_add(l - 1, f, c), orc.interp_add(l - 1, f, c)) < 1e-13, l
+
+
+@pytest.mark.parametrize("bclo,bchi", BCS)
 @pytest.mark.parametrize("ncell", [(16, 8, 12), (136, 68, 8), (8, 8, 72)])
 @pytest.mark.parametrize("const_sigma", [False, True])
 def test_fused_residual_restriction(backend, bclo, bchi, ncell, const_sigma):
