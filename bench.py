@@ -304,6 +304,8 @@ def _make_projector(ctx, args, pb, nloc, G, vel, rank=None, nranks=None, comm="c
         kw["overlap_halo"] = 1
     if args.no_p2p:
         kw["p2p_halo"] = 0
+    if args.no_graph:
+        kw["use_graph"] = 0
     kw.update(extra)
     P = NodalProjector(vel, pb["sig"], geom, LPInfo(), boxes=boxes, rank=rank, nranks=nranks,
                        nccl_comm=ctx.comm if comm == "ctx" else comm, lib=ctx.L, **kw)
@@ -340,12 +342,12 @@ def _measure_nodal(ctx, args, workload, n, steps, warmup, e2e_steps, ctor=False,
         clocks.mark()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    vcycles = launches = 0
+    vcycles = launches = replays = captures = 0
     ms_smooth = n_smooth = ms_solve = 0.0
     hist = None
     for _ in range(steps):
         st = step()
-        vcycles += st.n_vcycles; launches += st.kernel_launches
+        vcycles += st.n_vcycles; launches += st.kernel_launches; replays += st.graph_replays; captures += st.graph_captures
         ms_smooth += st.ms_smooth0; n_smooth += st.n_smooth0; ms_solve += st.ms_solve
         hist = [st.res_history[i] / max(st.rhs_norm0, 1e-300) for i in range(st.n_vcycles)]
     e1.record()
@@ -354,6 +356,7 @@ def _measure_nodal(ctx, args, workload, n, steps, warmup, e2e_steps, ctor=False,
     clk = clocks.stop() if clocks else None
     out = dict(dof=dof, ms=ms, vcycles=vcycles, launches=int(launches), ms_smooth=ms_smooth, n_smooth=n_smooth, ms_solve=ms_solve,
                hist=hist, const_sigma=bool(st.sigma_is_const), levels=st.n_levels, steps=steps, warmup=warmup, clocks=clk,
+               graph=dict(replays=int(replays), captures=int(captures)),
                ms_create_cold=ms_create_cold)
 
     # ---- e2e: host (pinned) fabs through the same C-ABI call; H2D + D2H inside the timed region ----
@@ -551,6 +554,8 @@ def run_gpu(args):
                 "ms_solve_per_vcycle": out["ms_solve"] / vcycles, "rel_res_history": out["hist"],
                 "clocks": out["clocks"], "e2e": out.get("e2e"), "gpu_launches": out["launches"],
                 "launches_per_vcycle": out["launches"] / vcycles, "host_numa_binding": ctx.numa,
+                "cuda_graph": dict(out["graph"], note="MLMG iterations of the timed region replayed as one CUDA-graph launch each (np_options.use_graph, "
+                                                      "one rank only); gpu_launches counts the kernels inside the graphs too"),
                 "roofline": _roofline(out, n, G, peak, peak_src)}
         if "e2e_with_ctor" in out:
             line["e2e_with_ctor"] = out["e2e_with_ctor"]
@@ -564,7 +569,7 @@ def run_gpu(args):
                     "value": o["dof"] * o["vcycles"] / (o["ms"] * 1e-3), "unit": UNIT, "steps": o["steps"], "warmup": o["warmup"],
                     "vcycles": o["vcycles"] / o["steps"], "ms_per_step": o["ms"] / o["steps"], "ms_per_vcycle": o["ms"] / o["vcycles"],
                     "ms_solve_per_vcycle": o["ms_solve"] / o["vcycles"], "mg_levels": o["levels"], "rel_res_history": o["hist"],
-                    "launches_per_vcycle": o["launches"] / o["vcycles"],
+                    "launches_per_vcycle": o["launches"] / o["vcycles"], "cuda_graph": o["graph"],
                     "roofline": {k: r[k] for k in ("kernel", "frac", "frac_fused_pass", "avg_launch_ms", "share_of_step", "vcycle_algorithmic")}}
         if world == 1 and not args.no_cpu:
             r = cpu_projection(args.cpu_ncell, 1, 0)
@@ -939,6 +944,7 @@ def main():
     ap.add_argument("--smooth-zchunk", type=int, default=0, help="experiment knob: fixed smoother z-chunk on every level (0: the level rule)")
     ap.add_argument("--agg-min-local-nz", type=int, default=0, help="experiment knob: replicate MG levels whose slab is thinner than this (0: library default)")
     ap.add_argument("--no-p2p", action="store_true", help="experiment knob: halo exchange through ncclSend/ncclRecv instead of peer memory")
+    ap.add_argument("--no-graph", action="store_true", help="experiment knob: np_options.use_graph = 0 (launch the MLMG iteration kernel by kernel)")
     ap.add_argument("--overlap", action="store_true", help="experiment knob: overlap_halo=1 (end z-chunks first, their planes exchanged beside the interior chunks)")
     ap.add_argument("--no-overlap", action="store_true", help="experiment knob: halo exchange on the solver stream (overlap_halo=0)")
     ap.add_argument("--verbose", type=int, default=0, help="nodal_proj.verbose (4: per-launch smoother times on stderr)")

@@ -44,7 +44,7 @@ class np_stats(C.Structure):
                 ("res_history", C.c_double * 128),
                 ("ms_setup", C.c_double), ("ms_solve", C.c_double), ("ms_finish", C.c_double), ("ms_total", C.c_double),
                 ("kernel_launches", C.c_longlong), ("sigma_is_const", C.c_int),
-                ("n_smooth0", C.c_int), ("ms_smooth0", C.c_double)]
+                ("n_smooth0", C.c_int), ("ms_smooth0", C.c_double), ("graph_replays", C.c_int), ("graph_captures", C.c_int)]
 
 
 class np_apply_args(C.Structure):

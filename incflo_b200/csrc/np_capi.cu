@@ -68,7 +68,7 @@ void np_default_options(np_options* o)
     o->bottom_solver = NP_BOTTOM_BICGCG; o->verbose = 0; o->bottom_verbose = 0;
     o->bottom_rtol = 1e-4; o->bottom_atol = -1.0;
     o->smooth_zchunk = 0; o->interp_sigma_weighted = 1; o->bottom_normalize = 1;
-    o->agg_min_local_nz = 64; o->use_graph = 0; o->const_sigma_fastpath = 1; o->profile_kernels = 0; o->overlap_halo = 0; o->p2p_halo = 1;
+    o->agg_min_local_nz = 64; o->use_graph = 1; o->const_sigma_fastpath = 1; o->profile_kernels = 0; o->overlap_halo = 0; o->p2p_halo = 1;
 }
 
 int np_create(np_handle** h, const np_geom* geom, int nboxes_global, const np_box* all_boxes,

@@ -43,6 +43,13 @@ inline float event_ms(np_event_t a, np_event_t b) { return std::chrono::duration
 inline int last_error() { return 0; }
 inline const char* last_error_string() { return "emu"; }
 inline int sm_count() { return 4; }
+// CUDA graphs do not exist in the emulation: every call fails and the solver keeps launching kernel by kernel
+typedef void* np_graph_t;
+inline int capture_begin(np_stream_t) { return 1; }
+inline int capture_end(np_stream_t, np_graph_t*) { return 1; }
+inline int graph_launch(np_graph_t, np_stream_t) { return 1; }
+inline int graph_destroy(np_graph_t) { return 0; }
+inline int event_record_in_graph(np_event_t e, np_stream_t s) { return event_record(e, s); }
 } // namespace np_rt
 #else
 #include <cuda_runtime.h>
@@ -96,5 +103,21 @@ inline float event_ms(np_event_t a, np_event_t b) { float ms = 0; cudaEventSynch
 inline int last_error() { return cudaGetLastError() == cudaSuccess ? 0 : 1; }
 inline const char* last_error_string() { return cudaGetErrorString(cudaPeekAtLastError()); }
 inline int sm_count() { int dev = 0, n = 148; cudaGetDevice(&dev); cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev); return n; }
+// CUDA graph of a launch sequence: captured from a private stream (the caller's may be the legacy default stream, which
+// cannot be captured), replayed on the caller's
+typedef cudaGraphExec_t np_graph_t;
+inline int capture_begin(np_stream_t s) { return cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal) == cudaSuccess ? 0 : 1; }
+inline int capture_end(np_stream_t s, np_graph_t* out) {
+    cudaGraph_t g = nullptr; *out = nullptr;
+    if (cudaStreamEndCapture(s, &g) != cudaSuccess || !g) { cudaGetLastError(); return 1; }
+    const cudaError_t e = cudaGraphInstantiate(out, g, 0);
+    cudaGraphDestroy(g);
+    if (e != cudaSuccess) { cudaGetLastError(); *out = nullptr; return 1; }
+    return 0;
+}
+inline int graph_launch(np_graph_t g, np_stream_t s) { return cudaGraphLaunch(g, s) == cudaSuccess ? 0 : 1; }
+inline int graph_destroy(np_graph_t g) { return cudaGraphExecDestroy(g) == cudaSuccess ? 0 : 1; }
+// inside a capture a plain cudaEventRecord only marks a dependency; this one becomes a node that records the event at every replay
+inline int event_record_in_graph(np_event_t e, np_stream_t s) { return cudaEventRecordWithFlags(e, s, cudaEventRecordExternal) == cudaSuccess ? 0 : 1; }
 } // namespace np_rt
 #endif

@@ -213,6 +213,10 @@ void NpSolver::destroy()
     for (int e = 0; e < 2; ++e) if (ev_halo[e]) { np_rt::event_destroy(ev_halo[e]); ev_halo[e] = 0; }
     for (auto& e : prof_ev) np_rt::event_destroy(e);
     prof_ev.clear();
+    drop_graph();
+    for (auto& e : gprof_ev) np_rt::event_destroy(e);
+    gprof_ev.clear();
+    if (have_cap_stream) { np_rt::stream_destroy(cap_stream); have_cap_stream = false; }
 }
 
 // A cached handle is handed out again by np_create (np_capi.cu): every array is cleared and every flag reset, so the handle
@@ -229,6 +233,7 @@ void NpSolver::reset_for_reuse()
     for (auto& L : lev) setup_level_bc(L);
     have_sigma = have_result = false; bicg_failed_switch = false;
     stats = np_stats{}; err = 0; launches = 0; divu_npart = 0; red_n = 0; prof_n = 0; lvl0_off = nullptr; wtot = 1.0;
+    graph_off = false; g_ms_smooth = 0.0; g_n_smooth = 0;      // (the captured graph stays: its key decides whether it still fits)
 }
 
 // First use of a handle that came back from the cache.  Every valid node / cell of every array is written before it is
@@ -458,6 +463,7 @@ double NpSolver::finish_norm(int l, bool want_off)
         }
     }
     np_rt::copy_async(h_scal, scal, sizeof(double), stream);
+    if (in_capture) return 0.0;              // read after the graph has run
     np_rt::stream_sync(stream);
     return h_scal[0];
 }
@@ -492,8 +498,11 @@ void NpSolver::smooth(int l, bool zero_in, double* add_to)
     if (!zero_in && !L.cor_ghost_clean) fill(l, L.cor);
     const dim3 grid((d.n[0] + 1 + GS_WX - 1) / GS_WX, (d.n[1] + 1 + GS_WY - 1) / GS_WY, (d.n[2] + 1 + L.zc - 1) / L.zc);
     const size_t smem = GS_SMEM_BYTES;
-    const bool prof = (l == 0 && opt.profile_kernels && prof_n + 2 <= (int)prof_ev.size());
+    // profile_kernels: event pairs around the level-0 launches; inside a graph capture they become event-record nodes
+    const bool gprof = (l == 0 && opt.profile_kernels && in_capture && itg.n_prof + 1 <= (int)gprof_ev.size() / 2);
+    const bool prof = (l == 0 && opt.profile_kernels && !in_capture && prof_n + 2 <= (int)prof_ev.size());
     if (prof) np_rt::event_record(prof_ev[prof_n], stream);
+    if (gprof) np_rt::event_record_in_graph(gprof_ev[2 * itg.n_prof], stream);
     GsArgs ga{};
     ga.xout = add_to ? add_to : L.cor_alt; ga.xin = L.cor; ga.rhs = L.res; ga.sig = L.sigma;
     ga.boff = (l == 0) ? lvl0_off : nullptr; ga.addto = add_to; ga.zc = L.zc; ga.zero_in = zero_in ? 1 : 0;
@@ -562,6 +571,7 @@ void NpSolver::smooth(int l, bool zero_in, double* add_to)
         np_rt::event_record(ev_halo[1], comm_stream);
         ga.zmap0 = 1; ga.zmapS = 1; launch(nch - 2);
         if (prof) { np_rt::event_record(prof_ev[prof_n + 1], stream); prof_n += 2; }
+    if (gprof) { np_rt::event_record_in_graph(gprof_ev[2 * itg.n_prof + 1], stream); ++itg.n_prof; }
         std::swap(L.cor, L.cor_alt);
         np_rt::stream_wait_event(stream, ev_halo[1]);
         const long long nshell = 3LL * ((long long)(d.n[1]+3)*(d.n[2]+3) + (long long)(d.n[0]+3)*(d.n[2]+3) + (long long)(d.n[0]+3)*(d.n[1]+3));
@@ -571,6 +581,7 @@ void NpSolver::smooth(int l, bool zero_in, double* add_to)
     }
     launch(nch);
     if (prof) { np_rt::event_record(prof_ev[prof_n + 1], stream); prof_n += 2; }
+    if (gprof) { np_rt::event_record_in_graph(gprof_ev[2 * itg.n_prof + 1], stream); ++itg.n_prof; }
     if (add_to) { L.cor_ghost_clean = false; return; }
     std::swap(L.cor, L.cor_alt);
     fill(l, L.cor);                 // nodalSync (+ the ghosts the next operation needs)
@@ -620,6 +631,7 @@ int NpSolver::bottom_solve()
         int nth = (int)std::min<long long>(1024, std::max<long long>(64, ((nv + 31) / 32) * 32));
         NP_LAUNCH(true, k_bottom_solve, dim3(1), dim3(nth), 0, stream, a); ++launches;
         np_rt::copy_async(h_bot_out, bot_out, 2 * sizeof(int), stream);
+        if (in_capture) return 0;            // the status is looked at after the graph has run (iterate_graph)
         np_rt::stream_sync(stream);
         iters += h_bot_out[1];
         return h_bot_out[0];
@@ -671,6 +683,64 @@ void NpSolver::vcycle(bool add_to_sol)
     else if (add_to_sol && opt.num_post_smooth == 0) { NP_LAUNCH(false, k_add, grid_nodes(lev[0].d), NP_BLK, 0, stream, lev[0].d, sol, (const double*)lev[0].cor); ++launches; }
 }
 
+void NpSolver::drop_graph()
+{
+    if (itg.exec) np_rt::graph_destroy(itg.exec);
+    itg.exec = nullptr; itg.key.clear(); itg.launches = 0; itg.n_prof = 0;
+}
+
+// One MLMG iteration (mgVcycle with sol += cor, the new residual, its norm and the next solvability offset) replayed from a
+// CUDA graph; captured on first use and whenever anything baked into it has changed.  lvl0_off is set by the caller.
+int NpSolver::iterate_graph(const double* rhs_off, double* resnorm)
+{
+    if (!opt.use_graph || graph_off || comm.nranks > 1 || lev.size() < 2) return 1;
+    std::vector<unsigned char> key;
+    auto put = [&](const void* p, size_t n) { key.insert(key.end(), (const unsigned char*)p, (const unsigned char*)p + n); };
+    for (const NpLevel& L : lev) {
+        put(&L.d, sizeof(LevelDev)); put(&L.sigma, sizeof(double*)); put(&L.res, sizeof(double*)); put(&L.cor, sizeof(double*));
+        put(&L.cor_alt, sizeof(double*)); put(&L.rescor, sizeof(double*)); put(&L.zc, sizeof(int));
+    }
+    put(&sol, sizeof(double*)); put(&rhs, sizeof(double*)); put(&rhs_off, sizeof(double*)); put(&lvl0_off, sizeof(double*));
+    put(&opt, sizeof(np_options)); put(&wtot, sizeof(double));
+    const int sw[8] = {singular ? 1 : 0, bicg_failed_switch ? 1 : 0, fused_rr ? 1 : 0, interp_march ? 1 : 0, gs_variant_c, gs_variant_v, gs_small, 0};
+    put(sw, sizeof(sw));
+    if (!itg.exec || key != itg.key) {
+        drop_graph();
+        if (!have_cap_stream) { if (np_rt::stream_create(&cap_stream)) { graph_off = true; return 1; } have_cap_stream = true; }
+        if (opt.profile_kernels && gprof_ev.empty()) { gprof_ev.resize(2 * 16); for (auto& e : gprof_ev) np_rt::event_create(&e); }
+        // the smoother swaps cor / cor_alt; a V-cycle does not depend on what they held before, so the host state is put
+        // back after the capture and every replay starts from the same assignment
+        std::vector<double*> save;
+        for (NpLevel& L : lev) { save.push_back(L.cor); save.push_back(L.cor_alt); L.cor_ghost_clean = false; }
+        const long long l0 = launches;
+        const np_stream_t user = stream;
+        bool ok = np_rt::capture_begin(cap_stream) == 0;
+        if (ok) {
+            stream = cap_stream; in_capture = true;
+            vcycle(true);
+            residual(0, lev[0].res, sol, rhs, true, rhs_off);
+            finish_norm(0, singular);
+            in_capture = false; stream = user;
+            ok = np_rt::capture_end(cap_stream, &itg.exec) == 0 && !err;
+        }
+        itg.launches = launches - l0; launches = l0;
+        for (size_t q = 0; q < lev.size(); ++q) { lev[q].cor = save[2 * q]; lev[q].cor_alt = save[2 * q + 1]; lev[q].cor_ghost_clean = false; }
+        if (!ok) { drop_graph(); np_rt::last_error(); graph_off = true; return 1; }
+        itg.key = key; ++stats.graph_captures;
+    }
+    if (np_rt::graph_launch(itg.exec, stream)) { np_rt::last_error(); drop_graph(); graph_off = true; return 1; }
+    launches += itg.launches; ++stats.graph_replays;
+    np_rt::stream_sync(stream);
+    for (int q = 0; q < itg.n_prof; ++q) { g_ms_smooth += np_rt::event_ms(gprof_ev[2 * q], gprof_ev[2 * q + 1]); ++g_n_smooth; }
+    for (NpLevel& L : lev) L.cor_ghost_clean = false;
+    if (opt.bottom_solver != NP_BOTTOM_SMOOTHER) {
+        if (h_bot_out[0] != 0 && h_bot_out[0] != 9) return 2;
+        stats.bottom_iters_total += h_bot_out[1];
+    }
+    *resnorm = h_scal[0];
+    return 0;
+}
+
 // MLMG::solve with the zero initial guess NodalProjector uses
 int NpSolver::solve(double rtol, double atol)
 {
@@ -679,6 +749,7 @@ int NpSolver::solve(double rtol, double atol)
     zero(sol, d0.ntot);
     bicg_failed_switch = false;
     stats.bottom_iters_total = 0; stats.n_vcycles = 0; stats.status = NP_OK; stats.n_levels = (int)lev.size();
+    stats.graph_replays = 0; stats.graph_captures = 0;
     for (int i = 0; i < 128; ++i) stats.res_history[i] = 0.0;
     wtot = 1.0;
     for (int dd = 0; dd < 3; ++dd) wtot *= (double)geom.ncell[dd];   // sum of the dot-mask weights (periodic / Neumann dims)
@@ -711,10 +782,21 @@ int NpSolver::solve(double rtol, double atol)
         // MLMG makes the residual solvable before every V-cycle; here the offset (scal[6], left by finish_norm)
         // is subtracted on the fly by the level-0 consumers of res instead of in a separate pass
         lvl0_off = singular ? scal + 6 : nullptr;
-        vcycle(true);
+        double rn = 0.0;
+        const int grc = iterate_graph(rhs_off, &rn);
+        if (grc == 2) {
+            // a bottom solve inside the graph asked for MLMG's fallback (other Krylov method, final smooths), which the graph
+            // does not hold: start again kernel by kernel (rhs is still intact; its offset is removed in place this time)
+            lvl0_off = nullptr; graph_off = true;
+            return solve(rtol, atol);
+        }
+        if (grc != 0) {
+            vcycle(true);
+            lvl0_off = nullptr;
+            residual(0, L0.res, sol, rhs, true, rhs_off);
+            rn = finish_norm(0, singular);
+        }
         lvl0_off = nullptr;
-        residual(0, L0.res, sol, rhs, true, rhs_off);
-        const double rn = finish_norm(0, singular);
         if (iter < 128) stats.res_history[iter] = rn;
         stats.n_vcycles = iter + 1; stats.res_norm_final = rn;
         if (opt.verbose >= 2 && comm.rank == 0) std::printf("MLMG: Iteration %3d Fine resid/bnorm = %.6e\n", iter + 1, rn / max_norm);
@@ -929,7 +1011,7 @@ void NpSolver::finish_stats()
     stats.ms_finish = np_rt::event_ms(ev[2], ev[3]);
     stats.ms_total = np_rt::event_ms(ev[0], ev[3]);
     stats.kernel_launches = launches;
-    stats.n_smooth0 = prof_n / 2; stats.ms_smooth0 = 0.0;
+    stats.n_smooth0 = prof_n / 2 + g_n_smooth; stats.ms_smooth0 = g_ms_smooth;
     for (int e = 0; e < prof_n; e += 2) stats.ms_smooth0 += np_rt::event_ms(prof_ev[e], prof_ev[e + 1]);
     if (opt.verbose >= 4) {     // per-launch times of the level-0 smoother (first V-cycle: zero-input, plain, plain, add-to)
         fprintf(stderr, "[nodalproj] level-0 smoother launches (ms):");
@@ -941,7 +1023,7 @@ void NpSolver::finish_stats()
 int NpSolver::project(np_fab* vel, const np_fab* sigma, double rtol, double atol)
 {
     if (vel->ngrow < 1 || vel->ncomp < 3 || sigma->ncomp < 1) return NP_ERR_INVALID;
-    err = 0; launches = 0; have_result = false; prof_n = 0;
+    err = 0; launches = 0; have_result = false; prof_n = 0; g_ms_smooth = 0.0; g_n_smooth = 0;
     ensure_clean();
     const LevelDev& d0 = lev[0].d;
     np_rt::event_record(ev[0], stream);
@@ -1098,7 +1180,7 @@ int NpSolver::apply_projection(np_fab* vel, const np_fab* vel_old, const np_fab*
     // device fabs only (a CUDA build of the caller); a CPU caller keeps its own passes and uses np_project
     if (!np_rt::is_device_ptr(vel->p) || !np_rt::is_device_ptr(rho->p) || !np_rt::is_device_ptr(gp->p) || !np_rt::is_device_ptr(p->p)
         || (use_old && !np_rt::is_device_ptr(vel_old->p))) return NP_ERR_INVALID;
-    err = 0; launches = 0; have_result = false; prof_n = 0;
+    err = 0; launches = 0; have_result = false; prof_n = 0; g_ms_smooth = 0.0; g_n_smooth = 0;
     ensure_clean();
     const LevelDev& d0 = lev[0].d;
     np_rt::event_record(ev[0], stream);

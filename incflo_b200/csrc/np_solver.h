@@ -79,6 +79,23 @@ struct NpSolver {
     int project_boxes(int nlocal, np_fab* vel, const np_fab* sigma, double rtol, double atol);
     void box_copy(const FabView& dst, const int dorg[3], const FabView& src, const int sorg[3], const int rlo[3], const int rhi[3],
                   int ncomp, const np_box* guard_valid);
+    // np_options.use_graph: one MLMG iteration (V-cycle, residual, norm reduction, the two status copies) as a CUDA graph.
+    // The graph bakes in every kernel argument, so it carries a key (level descriptors with BCs and coefficients, array
+    // pointers, options, solver switches) and is captured again when the key changes.  One rank only (the peer-memory halo
+    // kernel takes the exchange epoch as an argument).
+    struct IterGraph {
+        np_rt::np_graph_t exec = nullptr;
+        std::vector<unsigned char> key;
+        long long launches = 0;        // kernel launches inside the graph
+        int n_prof = 0;                // profile_kernels: event pairs recorded by the graph
+    } itg;
+    np_stream_t cap_stream = 0; bool have_cap_stream = false;
+    bool in_capture = false;
+    bool graph_off = false;            // capture failed, or a bottom solve inside the graph needed the fallback path
+    std::vector<np_event_t> gprof_ev;  // profile_kernels inside the graph
+    double g_ms_smooth = 0.0; int g_n_smooth = 0;
+    int iterate_graph(const double* rhs_off, double* resnorm);   // 0: done; 1: no graph (run the plain path); 2: bottom solve failed
+    void drop_graph();
     std::vector<np_event_t> prof_ev;   // profile_kernels: start/stop pairs around level-0 smoother launches
     int prof_n = 0;
     np_stats stats{};

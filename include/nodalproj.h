@@ -75,7 +75,10 @@ typedef struct {
     int interp_sigma_weighted;  /* 1: mlndlap_interpadd_aa weights (default); 0: plain trilinear */
     int bottom_normalize;       /* 1: MLCGSolver's Lp.normalize (default) */
     int agg_min_local_nz;       /* multi-GPU: replicate MG levels whose slab is thinner than this; default 64 */
-    int use_graph;              /* reserved (CUDA-graph capture of the V-cycle is not implemented); ignored */
+    int use_graph;              /* 1 (default): one MLMG iteration (V-cycle + residual + norm) is captured as a CUDA graph on first
+                                   use and replayed; captured again when BCs, coefficients or options change; one rank only
+                                   (several ranks: ignored).  A bottom solve that needs MLMG's fallback path restarts the
+                                   solve without the graph.  0: launch kernel by kernel */
     int const_sigma_fastpath;   /* use the constant-coefficient kernels when sigma is uniform; default 1 */
     int profile_kernels;        /* bracket every level-0 smoother launch with CUDA events (np_stats.ms_smooth0); default 0 */
     int overlap_halo;           /* multi-GPU: smooth the end z-chunks first and exchange their planes on a second stream
@@ -98,6 +101,9 @@ typedef struct {
     /* profile_kernels: summed device time and count of the level-0 smoother launches of the last np_project */
     int n_smooth0;
     double ms_smooth0;
+    int graph_replays;           /* use_graph: MLMG iterations of the last np_project that ran as one CUDA-graph launch each
+                                    (their kernels are still counted in kernel_launches) */
+    int graph_captures;          /* ... and how many times the graph had to be captured for it */
 } np_stats;
 
 void np_default_options(np_options* o);

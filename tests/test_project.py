@@ -9,7 +9,7 @@ import numpy as np
 import pytest
 
 import nphelp
-from incflo_b200 import problems
+from incflo_b200 import capi, problems
 from oracle.oracle import Oracle, TILED, LEX
 
 BIG = 1 << 30
@@ -170,3 +170,45 @@ def test_handle_cache_reuse_is_stateless(backend):
     drv = nphelp.Driver((16, 16, 8), **backend)
     drv.P.close()
     L.np_cache_clear()
+
+
+@pytest.mark.gpu
+def test_iteration_graph_matches_kernel_by_kernel_path():
+    """np_options.use_graph: one MLMG iteration replayed from a CUDA graph gives bit-identical fields, counts and residual
+    histories to the kernel-by-kernel path; the graph is captured again when what it bakes in changes (constant -> variable
+    sigma, other BCs through the handle cache); a bottom solve that needs MLMG's fallback path (here: bottom_maxiter 1)
+    restarts the solve without the graph and still agrees."""
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("needs a GPU")
+    backend = dict(lib=capi.load(), like="torch", device="cuda")
+    L = backend["lib"]
+    rng = np.random.default_rng(17)
+    ncell = (32, 32, 64)
+    vel = rng.standard_normal((3,) + ncell[::-1])
+    sig_c = np.full(ncell[::-1], 0.8)
+    sig_v = rng.uniform(0.5, 2.0, ncell[::-1])
+
+    def run(use_graph, cases, **opts):
+        out = []
+        for bclo, bchi, sigma in cases:
+            drv = nphelp.Driver(ncell, (0, 0, 0), (1, 1, 2), bclo, bchi, use_graph=use_graph, **opts, **backend)
+            st, u, phi, gp = drv.project(vel, sigma, 1e-11, 1e-14)
+            out.append((st.status, st.n_vcycles, st.bottom_iters_total, [st.res_history[i] for i in range(st.n_vcycles)], u, phi, gp,
+                        st.kernel_launches))
+            drv.P.close()                                   # parks the handle: the next case reuses it, graph included
+        L.np_cache_clear()
+        return out
+
+    per, walls = ((0, 0, 0), (0, 0, 0)), ((2, 1, 2), (2, 2, 1))
+    cases = [(*per, sig_c), (*per, sig_c), (*per, sig_v), (*walls, sig_v), (*walls, sig_c)]
+    plain, graph = run(0, cases), run(1, cases)
+    for p, g in zip(plain, graph):
+        assert p[0] == 0 and g[0] == 0
+        assert p[1] == g[1] and p[2] == g[2] and p[3] == g[3] and p[7] == g[7]
+        assert all(np.array_equal(a, b) for a, b in zip(p[4:7], g[4:7]))
+    # fallback: one bottom iteration cannot converge -> MLMG smooths the bottom level instead; the graph path restarts kernel by kernel
+    pf, gf = run(0, cases[:1], bottom_maxiter=1), run(1, cases[:1], bottom_maxiter=1)
+    assert pf[0][0] == 0 and gf[0][0] == 0 and pf[0][1] == gf[0][1]
+    for a, b in zip(pf[0][4:7], gf[0][4:7]):
+        assert np.linalg.norm(a - b) <= 1e-12 * max(np.linalg.norm(a), 1e-300)
