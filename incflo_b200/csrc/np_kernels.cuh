@@ -162,7 +162,8 @@ struct HaloP2P {
     const double* send_hi; double* dst_hi; long long n_hi;
     unsigned long long* mine;                                  // my four flags (written by the neighbours)
     unsigned long long* lo_flags; unsigned long long* hi_flags;   // the neighbours' flag arrays (null: no neighbour)
-    unsigned long long epoch;
+    unsigned long long* epoch_word;                            // my count of finished exchanges (device memory, so that a CUDA
+                                                               // graph can replay the launch: nothing changes in its arguments)
     unsigned int* counter;                                     // CTAs of this launch that finished their stores
 };
 __device__ __forceinline__ void np_flag_store(unsigned long long* p, unsigned long long v)
@@ -185,15 +186,19 @@ __device__ __forceinline__ unsigned long long np_flag_load(const unsigned long l
 }
 __global__ void __launch_bounds__(256) k_halo_p2p(HaloP2P a)
 {
+    // the number of this exchange: every rank runs the same sequence of exchanges, so the counts agree.  The word is advanced
+    // by the last CTA to finish, i.e. after every CTA of this launch has read it.
+    unsigned long long epoch = 0;
+    if (threadIdx.x == 0) epoch = *(volatile unsigned long long*)a.epoch_word + 1ull;
     // 1) this kernel runs after everything that read my ghost planes: tell the neighbours they may overwrite them
     if (blockIdx.x == 0 && threadIdx.x == 0) {
-        if (a.lo_flags) np_flag_store(a.lo_flags + NP_FLAG_READY_HI, a.epoch);
-        if (a.hi_flags) np_flag_store(a.hi_flags + NP_FLAG_READY_LO, a.epoch);
+        if (a.lo_flags) np_flag_store(a.lo_flags + NP_FLAG_READY_HI, epoch);
+        if (a.hi_flags) np_flag_store(a.hi_flags + NP_FLAG_READY_LO, epoch);
     }
     // 2) wait until the neighbours have said the same about theirs
     if (threadIdx.x == 0) {
-        if (a.lo_flags) while (np_flag_load(a.mine + NP_FLAG_READY_LO) < a.epoch) { }
-        if (a.hi_flags) while (np_flag_load(a.mine + NP_FLAG_READY_HI) < a.epoch) { }
+        if (a.lo_flags) while (np_flag_load(a.mine + NP_FLAG_READY_LO) < epoch) { }
+        if (a.hi_flags) while (np_flag_load(a.mine + NP_FLAG_READY_HI) < epoch) { }
     }
     __syncthreads();
     // 3) my boundary planes -> their ghost planes (16-byte stores; plane sizes are even)
@@ -213,11 +218,12 @@ __global__ void __launch_bounds__(256) k_halo_p2p(HaloP2P a)
         const unsigned int prev = atomicAdd(a.counter, 1u);
         if (prev == gridDim.x - 1) {
             *a.counter = 0u;
+            *(volatile unsigned long long*)a.epoch_word = epoch;
             __threadfence_system();
-            if (a.lo_flags) np_flag_store(a.lo_flags + NP_FLAG_DONE_HI, a.epoch);
-            if (a.hi_flags) np_flag_store(a.hi_flags + NP_FLAG_DONE_LO, a.epoch);
-            if (a.lo_flags) while (np_flag_load(a.mine + NP_FLAG_DONE_LO) < a.epoch) { }
-            if (a.hi_flags) while (np_flag_load(a.mine + NP_FLAG_DONE_HI) < a.epoch) { }
+            if (a.lo_flags) np_flag_store(a.lo_flags + NP_FLAG_DONE_HI, epoch);
+            if (a.hi_flags) np_flag_store(a.hi_flags + NP_FLAG_DONE_LO, epoch);
+            if (a.lo_flags) while (np_flag_load(a.mine + NP_FLAG_DONE_LO) < epoch) { }
+            if (a.hi_flags) while (np_flag_load(a.mine + NP_FLAG_DONE_HI) < epoch) { }
         }
     }
 }

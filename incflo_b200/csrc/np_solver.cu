@@ -374,7 +374,7 @@ bool NpSolver::halo_p2p(int l, double* x, np_stream_t on)
     a.send_lo = x + pl * 1; a.n_lo = 2 * pl; a.dst_lo = lo >= 0 ? peer.lo[id] + pl * (long long)(d.n[2] + 1) : nullptr;
     a.send_hi = x + pl * (long long)d.n[2]; a.n_hi = pl; a.dst_hi = hi >= 0 ? peer.hi[id] + 0 : nullptr;
     a.mine = peer.flags; a.lo_flags = lo >= 0 ? peer.lo_flags : nullptr; a.hi_flags = hi >= 0 ? peer.hi_flags : nullptr;
-    a.epoch = ++peer.epoch; a.counter = peer.counter;
+    a.epoch_word = peer.flags + 4; a.counter = peer.counter;        // words 0..3: the flags the neighbours write; word 4: my exchange count
     const long long chunks = (3 * pl / 2 + 255) / 256;                          // 16-byte stores per thread pass
     const int nb = (int)std::min<long long>(64, std::max<long long>(1, chunks / 8));
     NP_LAUNCH(false, k_halo_p2p, dim3(nb), dim3(256), 0, on, a); ++launches;
@@ -693,7 +693,11 @@ void NpSolver::drop_graph()
 // CUDA graph; captured on first use and whenever anything baked into it has changed.  lvl0_off is set by the caller.
 int NpSolver::iterate_graph(const double* rhs_off, double* resnorm)
 {
-    if (!opt.use_graph || graph_off || comm.nranks > 1 || lev.size() < 2) return 1;
+    if (!opt.use_graph || graph_off || lev.size() < 2 || have_comm_stream) return 1;
+    // several ranks: the exchanges inside the graph are the same launches in the same order as on the plain path (the halo
+    // kernel counts its exchanges on the device), so ranks may even mix the two; the first iteration of a handle runs plain so
+    // that NCCL has set up every collective it needs before one is captured
+    if (comm.nranks > 1 && !graph_warm) { graph_warm = true; return 1; }
     std::vector<unsigned char> key;
     auto put = [&](const void* p, size_t n) { key.insert(key.end(), (const unsigned char*)p, (const unsigned char*)p + n); };
     for (const NpLevel& L : lev) {
@@ -702,7 +706,7 @@ int NpSolver::iterate_graph(const double* rhs_off, double* resnorm)
     }
     put(&sol, sizeof(double*)); put(&rhs, sizeof(double*)); put(&rhs_off, sizeof(double*)); put(&lvl0_off, sizeof(double*));
     put(&opt, sizeof(np_options)); put(&wtot, sizeof(double));
-    const int sw[8] = {singular ? 1 : 0, bicg_failed_switch ? 1 : 0, fused_rr ? 1 : 0, interp_march ? 1 : 0, gs_variant_c, gs_variant_v, gs_small, 0};
+    const int sw[8] = {singular ? 1 : 0, bicg_failed_switch ? 1 : 0, fused_rr ? 1 : 0, interp_march ? 1 : 0, gs_variant_c, gs_variant_v, gs_small, peer.ok ? 1 : 0};
     put(sw, sizeof(sw));
     if (!itg.exec || key != itg.key) {
         drop_graph();

@@ -65,7 +65,6 @@ struct NpSolver {
         std::vector<void*> opened;                  // IPC mappings to close
         unsigned long long *flags = nullptr, *lo_flags = nullptr, *hi_flags = nullptr;
         unsigned int* counter = nullptr;
-        unsigned long long epoch = 0;
     } peer;
     int setup_peer_halo();
     bool halo_p2p(int l, double* x, np_stream_t on);
@@ -92,6 +91,7 @@ struct NpSolver {
     np_stream_t cap_stream = 0; bool have_cap_stream = false;
     bool in_capture = false;
     bool graph_off = false;            // capture failed, or a bottom solve inside the graph needed the fallback path
+    bool graph_warm = false;           // several ranks: the first MLMG iteration of the handle has run kernel by kernel
     std::vector<np_event_t> gprof_ev;  // profile_kernels inside the graph
     double g_ms_smooth = 0.0; int g_n_smooth = 0;
     int iterate_graph(const double* rhs_off, double* resnorm);   // 0: done; 1: no graph (run the plain path); 2: bottom solve failed

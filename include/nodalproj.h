@@ -76,8 +76,8 @@ typedef struct {
     int bottom_normalize;       /* 1: MLCGSolver's Lp.normalize (default) */
     int agg_min_local_nz;       /* multi-GPU: replicate MG levels whose slab is thinner than this; default 64 */
     int use_graph;              /* 1 (default): one MLMG iteration (V-cycle + residual + norm) is captured as a CUDA graph on first
-                                   use and replayed; captured again when BCs, coefficients or options change; one rank only
-                                   (several ranks: ignored).  A bottom solve that needs MLMG's fallback path restarts the
+                                   use and replayed; captured again when BCs, coefficients or options change; with several ranks
+                                   the halo kernels and NCCL collectives are part of the graph.  A bottom solve that needs MLMG's fallback path restarts the
                                    solve without the graph.  0: launch kernel by kernel */
     int const_sigma_fastpath;   /* use the constant-coefficient kernels when sigma is uniform; default 1 */
     int profile_kernels;        /* bracket every level-0 smoother launch with CUDA events (np_stats.ms_smooth0); default 0 */
