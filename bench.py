@@ -679,7 +679,8 @@ def run_gpu_mac(args):
     umac = [Fab(u.clone(), 0) for u in umac0]
     P = MacProjector(Geometry(ncell, (0, 0, 0), hi, [b == 0 for b in bclo]), lib=L, rank=rank, nranks=world, nccl_comm=comm)
     P.setDomainBC(bclo, bchi)
-    P.initProjector(LPInfo().setMaxCoarseningLevel(100), [Fab(b, 0) for b in beta], profile_kernels=1, verbose=args.verbose)
+    P.initProjector(LPInfo().setMaxCoarseningLevel(100), [Fab(b, 0) for b in beta], profile_kernels=1, verbose=args.verbose,
+                    use_graph=0 if args.no_graph else 1)
     P.setUMAC(umac)
     stream = torch.cuda.current_stream().cuda_stream
     dof = n ** 3 * G
@@ -824,7 +825,7 @@ def run_gpu_diffusion(args):
     rho, tr0, faces = _diffusion_problem(n, dev, variable, torch)
     bclo = bchi = (0, 0, 2)
     op = DiffusionScalarOp(Geometry((n, n, n), (0, 0, 0), (1, 1, 1), [True, True, False]), bclo, bchi, lib=capi.load(), like="torch", device=dev,
-                           profile_kernels=1)
+                           profile_kernels=1, use_graph=0 if args.no_graph else 1)
     frho, feta = Fab(rho, 0), [[Fab(f, 0) for f in faces]]
     ftr = Fab(tr0.clone(), 0)
     stream = torch.cuda.current_stream().cuda_stream

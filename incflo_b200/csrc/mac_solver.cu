@@ -8,6 +8,8 @@
 #include <new>
 #include <vector>
 
+enum { MP_RESTART = -77 };        // MacSolver::solve: a bottom solve inside the iteration graph needed MLMG's fallback path
+
 struct MacLev {
     MacLevel d{};
     double *bx = nullptr, *by = nullptr, *bz = nullptr;
@@ -45,6 +47,11 @@ struct MacSolver {
     int err = 0;
     double alpha = 0.0, bscal = 1.0;      // MLABecLaplacian::setScalars (the MAC projection: 0, 1)
     bool have_a = false;
+    // mp_options.use_graph: one MLMG iteration as a CUDA graph, keyed on what it bakes in (as NpSolver::iterate_graph); one rank
+    struct IterGraph { np_rt::np_graph_t exec = nullptr; std::vector<unsigned char> key; long long launches = 0; int n_prof = 0; } itg;
+    np_stream_t cap_stream = 0; bool have_cap_stream = false, in_capture = false, graph_off = false;
+    std::vector<np_event_t> gprof_ev; double g_ms_smooth = 0.0; int g_n_smooth = 0;
+    void drop_graph() { if (itg.exec) np_rt::graph_destroy(itg.exec); itg = IterGraph{}; }
 
     static dim3 blk() { return dim3(32, 8, 1); }
     static dim3 grid_cells(const MacLevel& L) { return dim3((L.n[0] + 31) / 32, (L.n[1] + 7) / 8, L.n[2]); }
@@ -237,6 +244,10 @@ struct MacSolver {
         for (int e = 0; e < 4; ++e) if (ev[e]) np_rt::event_destroy(ev[e]);
         for (auto& e : prof_ev) np_rt::event_destroy(e);
         prof_ev.clear();
+        drop_graph();
+        for (auto& e : gprof_ev) np_rt::event_destroy(e);
+        gprof_ev.clear();
+        if (have_cap_stream) { np_rt::stream_destroy(cap_stream); have_cap_stream = false; }
     }
 
     // ---- caller fabs ----
@@ -322,10 +333,13 @@ struct MacSolver {
     // The fused pass writes into lev[l].rescor and the two pointers are swapped, so lev[l].cor is always the current iterate.
     void smooth_level(int l, bool zero_in, const double* crse, double* add_to, const double* boff)
     {
-        const bool prof = opt.profile_kernels && l == 0 && prof_n + 2 <= (int)prof_ev.size();
+        const bool prof = opt.profile_kernels && !in_capture && l == 0 && prof_n + 2 <= (int)prof_ev.size();
+        const bool gprof = opt.profile_kernels && in_capture && l == 0 && itg.n_prof + 1 <= (int)gprof_ev.size() / 2;
         if (prof) np_rt::event_record(prof_ev[prof_n++], stream);
+        if (gprof) np_rt::event_record_in_graph(gprof_ev[2 * itg.n_prof], stream);
         smooth_level_impl(l, zero_in, crse, add_to, boff);
         if (prof) np_rt::event_record(prof_ev[prof_n++], stream);
+        if (gprof) { np_rt::event_record_in_graph(gprof_ev[2 * itg.n_prof + 1], stream); ++itg.n_prof; }
     }
     void smooth_level_impl(int l, bool zero_in, const double* crse, double* add_to, const double* boff)
     {
@@ -397,6 +411,7 @@ struct MacSolver {
     double fetch(int slot)
     {
         np_rt::copy_async(h_scal, scal, 16 * sizeof(double), stream);
+        if (in_capture) return 0.0;          // read after the graph has run
         np_rt::stream_sync(stream);
         return h_scal[slot];
     }
@@ -423,6 +438,7 @@ struct MacSolver {
         else NP_LAUNCH(true, (k_mac_bottom<false>), dim3(1), dim3(nth), 0, stream, A);
         ++launches;
         np_rt::copy_async(h_bot_out, bot_out, 2 * sizeof(int), stream);
+        if (in_capture) { *iters = 0; return 0; }      // looked at after the graph has run (iterate_graph)
         np_rt::stream_sync(stream);
         *iters = h_bot_out[1];
         return h_bot_out[0];
@@ -481,6 +497,56 @@ struct MacSolver {
         const MacLevel& d = lev[0].d;
         NP_LAUNCH(false, k_mac_axpy_cell, grid_cells(d), blk(), 0, stream, d, sol, (const double*)lev[0].cor); ++launches;
     }
+    // one MLMG iteration (V-cycle with sol += cor, new residual, its norm and mean) replayed from a CUDA graph.
+    // 0: done, *rn set; 1: no graph, run the plain path; 2: the bottom solve asked for MLMG's fallback path
+    int iterate_graph(const double* off0, long long nb, double* rn)
+    {
+        if (!opt.use_graph || graph_off || comm.nranks > 1 || lev.size() < 2) return 1;
+        std::vector<unsigned char> key;
+        auto put = [&](const void* p, size_t n) { key.insert(key.end(), (const unsigned char*)p, (const unsigned char*)p + n); };
+        for (const MacLev& L : lev) {
+            put(&L.d, sizeof(MacLevel)); put(&L.bx, sizeof(double*)); put(&L.by, sizeof(double*)); put(&L.bz, sizeof(double*));
+            put(&L.res, sizeof(double*)); put(&L.cor, sizeof(double*)); put(&L.rescor, sizeof(double*)); put(&L.a, sizeof(double*));
+        }
+        put(&sol, sizeof(double*)); put(&rhs, sizeof(double*)); put(&off0, sizeof(double*)); put(&opt, sizeof(mp_options));
+        put(&wrapbuf, sizeof(double*)); put(&wrapbuf_n, sizeof(long long));
+        const double sc[2] = {alpha, bscal}; put(sc, sizeof(sc));
+        const int sw[4] = {singular ? 1 : 0, bicg_failed_switch ? 1 : 0, have_a ? 1 : 0, 0}; put(sw, sizeof(sw));
+        if (!itg.exec || key != itg.key) {
+            drop_graph();
+            if (!have_cap_stream) { if (np_rt::stream_create(&cap_stream)) { graph_off = true; return 1; } have_cap_stream = true; }
+            if (opt.profile_kernels && gprof_ev.empty()) { gprof_ev.resize(2 * 16); for (auto& e : gprof_ev) np_rt::event_create(&e); }
+            std::vector<double*> save;
+            for (MacLev& L : lev) { save.push_back(L.cor); save.push_back(L.rescor); }
+            const long long l0 = launches; const np_stream_t user = stream; const int err0 = err; const int bi0 = bottom_iters;
+            bool ok = np_rt::capture_begin(cap_stream) == 0;
+            if (ok) {
+                stream = cap_stream; in_capture = true;
+                vcycle(off0);
+                halo(0, sol);
+                adotx<1, true>(0, lev[0].res, sol, rhs, nullptr);
+                halo(0, lev[0].res);
+                reduce(nb, true, singular, 0);
+                fetch(0);
+                in_capture = false; stream = user;
+                ok = np_rt::capture_end(cap_stream, &itg.exec) == 0 && err == err0;
+            }
+            itg.launches = launches - l0; launches = l0; bottom_iters = bi0;
+            for (size_t q = 0; q < lev.size(); ++q) { lev[q].cor = save[2 * q]; lev[q].rescor = save[2 * q + 1]; }
+            if (!ok) { drop_graph(); np_rt::last_error(); err = err0; graph_off = true; return 1; }     // e.g. a scratch allocation inside the V-cycle
+            itg.key = key; ++stats.graph_captures;
+        }
+        if (np_rt::graph_launch(itg.exec, stream)) { np_rt::last_error(); drop_graph(); graph_off = true; return 1; }
+        launches += itg.launches; ++stats.graph_replays;
+        np_rt::stream_sync(stream);
+        for (int q = 0; q < itg.n_prof; ++q) { g_ms_smooth += np_rt::event_ms(gprof_ev[2 * q], gprof_ev[2 * q + 1]); ++g_n_smooth; }
+        if (opt.bottom_solver != NP_BOTTOM_SMOOTHER) {
+            if (h_bot_out[0] != 0 && h_bot_out[0] != 9) return 2;
+            bottom_iters += h_bot_out[1];
+        }
+        *rn = h_scal[0];
+        return 0;
+    }
     // MLMG::solve; `sol` holds the initial guess
     int solve(double rtol, double atol, double rhsnorm0)
     {
@@ -502,12 +568,17 @@ struct MacSolver {
         bool converged = false;
         int rc = NP_OK;
         for (int iter = 0; iter < opt.maxiter; ++iter) {
+            double rn = 0.0;
+            const int grc = iterate_graph(singular ? scal + 6 : nullptr, nb, &rn);
+            if (grc == 2) { graph_off = true; return MP_RESTART; }      // the caller restores the initial guess and solves again, kernel by kernel
+            if (grc != 0) {
             vcycle(singular ? scal + 6 : nullptr);       // makeSolvable(res) is applied by the consumers of res (lazy offset)
             halo(0, sol);
             adotx<1, true>(0, lev[0].res, sol, rhs, nullptr);
             halo(0, lev[0].res);
             reduce(nb, true, singular, 0);
-            const double rn = fetch(0);
+            rn = fetch(0);
+            }
             if (iter < 128) stats.res_history[iter] = rn;
             stats.n_vcycles = iter + 1; stats.res_norm_final = rn;
             if (opt.verbose >= 2) fprintf(stderr, "MLMG: Iteration %3d Fine resid/bnorm = %.6e\n", iter + 1, rn / max_norm);
@@ -606,7 +677,7 @@ struct MacSolver {
         stats.ms_finish = np_rt::event_ms(ev[2], ev[3]);
         stats.ms_total = np_rt::event_ms(ev[0], ev[3]);
         stats.kernel_launches = launches;
-        stats.n_smooth0 = prof_n / 2; stats.ms_smooth0 = 0.0;
+        stats.n_smooth0 = prof_n / 2 + g_n_smooth; stats.ms_smooth0 = g_ms_smooth;
         for (int e = 0; e + 1 < prof_n; e += 2) stats.ms_smooth0 += np_rt::event_ms(prof_ev[e], prof_ev[e + 1]);
     }
     // MacProjector::setUMAC + project
@@ -615,7 +686,7 @@ struct MacSolver {
         if (!have_beta) return NP_ERR_STATE;
         for (int d = 0; d < 3; ++d) if (!umac[d].p || umac[d].ncomp < 1) return NP_ERR_INVALID;
         if (mac_phi && (!mac_phi->p || mac_phi->ncomp < 1)) return NP_ERR_INVALID;
-        launches = 0; have_result = false; prof_n = 0; err = 0;
+        launches = 0; have_result = false; prof_n = 0; err = 0; g_ms_smooth = 0.0; g_n_smooth = 0;
         const int is_const = stats.sigma_is_const;
         stats = np_stats{}; stats.sigma_is_const = is_const;
         const MacLevel& d0 = lev[0].d;
@@ -633,14 +704,17 @@ struct MacSolver {
         np_rt::copy_async(h_scal + 16, scal + 16, 8 * sizeof(double), stream);
         // phi: 0, or the caller's mac_phi as the initial guess
         FabView pv; bool pst = false;
-        if (mac_phi) {
-            if (!import(*mac_phi, 0, -1, 3, true, &pv, &pst)) return NP_ERR_CUDA;
-            NP_LAUNCH(false, (k_mac_copy_cell<false>), grid_cells(d0), blk(), 0, stream, d0, sol, pv); ++launches;
-        } else zero(sol, d0.ntot);
+        if (mac_phi && !import(*mac_phi, 0, -1, 3, true, &pv, &pst)) return NP_ERR_CUDA;
+        auto initial_guess = [&]() {
+            if (mac_phi) { NP_LAUNCH(false, (k_mac_copy_cell<false>), grid_cells(d0), blk(), 0, stream, d0, sol, pv); ++launches; }
+            else zero(sol, d0.ntot);
+        };
+        initial_guess();
         np_rt::stream_sync(stream);
         const double rhsnorm0 = h_scal[16];
         np_rt::event_record(ev[1], stream);
-        const int rc = solve(rtol, atol, rhsnorm0);
+        int rc = solve(rtol, atol, rhsnorm0);
+        if (rc == MP_RESTART) { initial_guess(); rc = solve(rtol, atol, rhsnorm0); }
         np_rt::event_record(ev[2], stream);
         // umac += flux = -b grad(phi)
         halo(0, sol);
@@ -692,7 +766,7 @@ struct MacSolver {
     {
         if (!have_beta) return NP_ERR_STATE;
         if (!phi || !phi->p || !rhs_in || !rhs_in->p) return NP_ERR_INVALID;
-        launches = 0; have_result = false; prof_n = 0; err = 0;
+        launches = 0; have_result = false; prof_n = 0; err = 0; g_ms_smooth = 0.0; g_n_smooth = 0;
         const int is_const = stats.sigma_is_const;
         stats = np_stats{}; stats.sigma_is_const = is_const;
         const MacLevel& d0 = lev[0].d;
@@ -727,7 +801,11 @@ struct MacSolver {
         np_rt::stream_sync(stream);
         const double rhsnorm0 = h_scal[16];
         np_rt::event_record(ev[1], stream);
-        const int rc = solve(rtol, atol, rhsnorm0);
+        int rc = solve(rtol, atol, rhsnorm0);
+        if (rc == MP_RESTART) {                  // back to the caller's initial guess (pv still holds it), kernel by kernel
+            NP_LAUNCH(false, (k_mac_copy_cell<false>), grid_cells(d0), blk(), 0, stream, d0, sol, pv); ++launches;
+            rc = solve(rtol, atol, rhsnorm0);
+        }
         np_rt::event_record(ev[2], stream);
         NP_LAUNCH(false, (k_mac_copy_cell<true>), grid_cells(d0), blk(), 0, stream, d0, sol, pv); ++launches;
         export_back(*phi, pv, pst);
@@ -867,7 +945,7 @@ void mp_default_options(mp_options* o)
 {
     o->max_coarsening_level = 100; o->maxiter = 200; o->bottom_maxiter = 200; o->num_pre_smooth = 2; o->num_post_smooth = 2;
     o->num_final_smooth = 8; o->bottom_solver = NP_BOTTOM_BICGCG; o->verbose = 0; o->bottom_verbose = 0; o->maxorder = 3;
-    o->bottom_rtol = 1e-4; o->bottom_atol = -1.0; o->const_beta_fastpath = 1; o->fused_rb_min_n = 128; o->fused_rb_const = 1; o->profile_kernels = 0; o->agg_min_local_nz = 32;
+    o->bottom_rtol = 1e-4; o->bottom_atol = -1.0; o->const_beta_fastpath = 1; o->fused_rb_min_n = 128; o->fused_rb_const = 1; o->profile_kernels = 0; o->agg_min_local_nz = 32; o->use_graph = 1;
 }
 int mp_create(mp_handle** h, const np_geom* geom, int nboxes_global, const np_box* all_boxes, const int* owner_rank,
               int my_rank, int nranks, void* nccl_comm_or_null, const mp_options* opt)

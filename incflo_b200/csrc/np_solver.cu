@@ -718,6 +718,7 @@ int NpSolver::iterate_graph(const double* rhs_off, double* resnorm)
         for (NpLevel& L : lev) { save.push_back(L.cor); save.push_back(L.cor_alt); L.cor_ghost_clean = false; }
         const long long l0 = launches;
         const np_stream_t user = stream;
+        const int err0 = err;
         bool ok = np_rt::capture_begin(cap_stream) == 0;
         if (ok) {
             stream = cap_stream; in_capture = true;
@@ -729,7 +730,7 @@ int NpSolver::iterate_graph(const double* rhs_off, double* resnorm)
         }
         itg.launches = launches - l0; launches = l0;
         for (size_t q = 0; q < lev.size(); ++q) { lev[q].cor = save[2 * q]; lev[q].cor_alt = save[2 * q + 1]; lev[q].cor_ghost_clean = false; }
-        if (!ok) { drop_graph(); np_rt::last_error(); graph_off = true; return 1; }
+        if (!ok) { drop_graph(); np_rt::last_error(); err = err0; graph_off = true; return 1; }
         itg.key = key; ++stats.graph_captures;
     }
     if (np_rt::graph_launch(itg.exec, stream)) { np_rt::last_error(); drop_graph(); graph_off = true; return 1; }

@@ -164,3 +164,35 @@ def test_abec_quadratic_is_reproduced(backend):
     assert st.status == 0
     assert np.abs(fphi.numpy_valid()[0] - exact).max() <= 1e-10
     op.close()
+
+
+@pytest.mark.gpu
+def test_diffusion_iteration_graph_matches_kernel_by_kernel_path():
+    """mp_options.use_graph on the diffusion solve (alpha a term, Dirichlet data, initial guess): bitwise equal to the
+    kernel-by-kernel path; the second tracer component replays the graph captured for the first one's successor key."""
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("needs a GPU")
+    rng = np.random.default_rng(9)
+    ncell, hi = (64, 32, 32), (2.0, 1.0, 1.0)
+    bclo, bchi = (1, 2, 0), (2, 2, 0)
+    rho = rng.uniform(0.5, 2.0, ncell[::-1])
+    tr_g = rng.uniform(0.0, 1.0, (2,) + tuple(n + 2 for n in ncell[::-1]))
+    eta = [average_cellcenter_to_face(rng.uniform(0.01, 0.05, tuple(n + 2 for n in ncell[::-1]))) for _ in range(2)]
+
+    def run(use_graph):
+        op = DiffusionScalarOp(Geometry(ncell, (0, 0, 0), hi, [b == 0 for b in bclo]), bclo, bchi, lib=capi.load(), like="torch", device="cuda",
+                               use_graph=use_graph)
+        ftr = Fab.zeros(ncell, 2, 1, False, "torch", "cuda")
+        nphelp.assign(ftr.data, tr_g)
+        stats = op.diffuse_scalar(ftr, Fab.from_array(rho, 0, False, "torch", "cuda"),
+                                  [[face_fab_from_array(b, 0, "torch", "cuda") for b in eta[c]] for c in range(2)], 0.01)
+        out = ftr.numpy_valid().copy()
+        res = [(s.status, s.n_vcycles, s.bottom_iters_total, s.graph_replays) for s in stats]
+        op.close()
+        return out, res
+
+    (a, ra), (b, rb) = run(0), run(1)
+    assert np.array_equal(a, b)
+    for x, y in zip(ra, rb):
+        assert x[:3] == y[:3] and x[0] == 0 and x[3] == 0 and y[3] == y[1]

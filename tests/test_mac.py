@@ -348,3 +348,49 @@ def test_mac_one_pass_smoother_is_deterministic_on_gpu(const):
         if ref is None:
             ref = s
         assert np.array_equal(s, ref), rep
+
+
+@pytest.mark.gpu
+def test_mac_iteration_graph_matches_kernel_by_kernel_path():
+    """mp_options.use_graph: the MLMG iteration replayed from a CUDA graph gives bit-identical umac / phi, counts and residual
+    histories to the kernel-by-kernel path (uniform and variable beta, the one-pass and the colour-per-launch smoother, walls
+    with a Dirichlet face, an initial guess, updateBeta between projections of one handle); a bottom solve that needs MLMG's
+    fallback (bottom_maxiter 1) makes the solve start again without the graph from the same initial guess."""
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("needs a GPU")
+    backend = dict(lib=capi.load(), like="torch", device="cuda")
+    rng = np.random.default_rng(41)
+    ncell, hi = (128, 32, 32), (4.0, 1.0, 1.0)
+    umac0 = [rng.standard_normal(s) for s in face_shapes(ncell)]
+    guess = rng.standard_normal(ncell[::-1])
+
+    def run(use_graph, bclo, bchi, **opts):
+        out = []
+        d = Drv(ncell, hi, bclo, bchi, random_beta(rng_b(), ncell, bclo, const=True), backend, use_graph=use_graph, **opts)
+        for const, g in ((True, None), (False, None), (False, guess)):
+            d.P.updateBeta([d.face(b) for b in random_beta(rng_b(), ncell, bclo, const=const)])
+            um = [u.copy() for u in umac0]
+            if bclo[0] == 0: um[0][:, :, -1] = um[0][:, :, 0]
+            if bclo[1] == 0: um[1][:, -1, :] = um[1][:, 0, :]
+            if bclo[2] == 0: um[2][-1, :, :] = um[2][0, :, :]
+            st, u, phi = d.project(um, phi_guess=g, raise_on_fail=False)
+            out.append((st.status, st.n_vcycles, st.bottom_iters_total, [st.res_history[i] for i in range(st.n_vcycles)], u, phi,
+                        st.graph_replays))
+        d.P.close()
+        return out
+
+    def rng_b():
+        return np.random.default_rng(43)
+
+    for bclo, bchi in (BCS[0], BCS[3]):
+        for opts in (dict(), dict(fused_rb_min_n=100000)):
+            plain, graph = run(0, bclo, bchi, **opts), run(1, bclo, bchi, **opts)
+            for p, g in zip(plain, graph):
+                assert p[0] == 0 and g[0] == 0 and p[6] == 0 and g[6] == g[1] > 0
+                assert p[1] == g[1] and p[2] == g[2] and p[3] == g[3]
+                assert all(np.array_equal(a, b) for a, b in zip(p[4], g[4])) and np.array_equal(p[5], g[5])
+    pf, gf = run(0, *BCS[3], bottom_maxiter=1), run(1, *BCS[3], bottom_maxiter=1)
+    for p, g in zip(pf, gf):
+        assert p[0] == g[0] and p[1] == g[1] and g[6] <= 1
+        assert all(np.array_equal(a, b) for a, b in zip(p[4], g[4])) and np.array_equal(p[5], g[5])
