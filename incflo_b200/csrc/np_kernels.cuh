@@ -1666,6 +1666,7 @@ __global__ void __launch_bounds__(256) k_copy_sigma_out(LevelDev L, const double
 // level is tiny (3^3 .. 33^3 nodes), so the ~7 reductions and 2 operator applications per iteration are
 // block barriers instead of kernel launches / allreduces.  Vectors live in HBM (L2-resident).
 // ------------------------------------------------------------------------------------------------
+#define NP_BOTTOM_SMEM_MAX (160 * 1024)      // bytes of dynamic shared memory k_bottom_solve may use for its eight vectors
 struct BottomArgs {
     LevelDev L;
     double* x; const double* b;             // solution (out), right-hand side (in; not modified)
@@ -1673,6 +1674,7 @@ struct BottomArgs {
     const double* sig;
     int maxiter; double eps_rel, eps_abs;
     int singular, normalize, type;          // type: 0 BiCGStab, 1 CG
+    int in_smem;                            // 1: the vectors live in dynamic shared memory (8 * L.ntot doubles)
     int* out;                               // out[0] = ret code, out[1] = iterations
 };
 
@@ -1684,15 +1686,16 @@ struct BottomCtx {
         tid = threadIdx.x; nth = blockDim.x;
         nvalid = (long long)(a.L.n[0] + 1) * (a.L.n[1] + 1) * (a.L.n[2] + 1);
     }
-    __device__ __forceinline__ void ijk(long long q, int& i, int& j, int& k) const {
-        const int e0 = A.L.n[0] + 1, e1 = A.L.n[1] + 1;
-        i = (int)(q % e0); j = (int)((q / e0) % e1); k = (int)(q / ((long long)e0 * e1));
+    __device__ __forceinline__ void ijk(long long q, int& i, int& j, int& k) const {      // (the level has < 2^31 nodes: 32-bit divisions)
+        const int e0 = A.L.n[0] + 1, e1 = A.L.n[1] + 1, q32 = (int)q;
+        const int t = q32 / e0;
+        i = q32 - t * e0; k = t / e1; j = t - k * e1;
     }
     __device__ void fill(double* x) const {
         const LevelDev& L = A.L;
         const int e0 = L.n[0] + 3, e1 = L.n[1] + 3, e2 = L.n[2] + 3;
-        for (long long q = tid; q < (long long)e0 * e1 * e2; q += nth) {
-            const int i = (int)(q % e0) - 1, j = (int)((q / e0) % e1) - 1, k = (int)(q / ((long long)e0 * e1)) - 1;
+        for (int q = tid; q < e0 * e1 * e2; q += nth) {
+            const int t = q / e0, i = q - t * e0 - 1, k = t / e1 - 1, j = t - (k + 1) * e1 - 1;
             const int si = np_map_index(i, L.n[0], L.map_lo[0], L.map_hi[0]);
             const int sj = np_map_index(j, L.n[1], L.map_lo[1], L.map_hi[1]);
             const int sk = np_map_index(k, L.n[2], L.map_lo[2], L.map_hi[2]);
@@ -1776,90 +1779,100 @@ __global__ void __launch_bounds__(1024) k_bottom_solve(BottomArgs A)
     const LevelDev& L = A.L;
     const int tid = C.tid, nth = C.nth;
     const long long ntot = L.ntot;
+    // the eight vectors of the iteration: in shared memory when the level fits (the usual 3^3 .. 9^3-node bottom level: every
+    // phase of an iteration is then a barrier away from the next instead of an L2 round trip - 67 -> ~10 us per bottom solve
+    // at 3^3 nodes), else the caller's work arrays in HBM
+    NP_DYN_SMEM(double, bsm);
+    double *X = A.x, *BB = A.bb, *R = A.r, *RH = A.rh, *P = A.p, *V = A.v, *S = A.s, *T = A.t;
+    if (A.in_smem) { X = bsm; BB = X + ntot; R = BB + ntot; RH = R + ntot; P = RH + ntot; V = P + ntot; S = V + ntot; T = S + ntot;
+                     for (long long q = tid; q < ntot; q += nth) { R[q] = 0.0; RH[q] = 0.0; V[q] = 0.0; T[q] = 0.0; } }
     // bb = b (made solvable when the operator is singular: MLMG::bottomSolve -> makeSolvable)
-    for (long long q = tid; q < ntot; q += nth) { A.bb[q] = A.b[q]; A.x[q] = 0.0; A.p[q] = 0.0; A.s[q] = 0.0; }
+    for (long long q = tid; q < ntot; q += nth) { BB[q] = A.b[q]; X[q] = 0.0; P[q] = 0.0; S[q] = 0.0; }
     __syncthreads();
     if (A.singular) {
-        double wtot; double sum = C.wsum(A.bb, wtot);
+        double wtot; double sum = C.wsum(BB, wtot);
         const double off = sum / wtot;
-        for (long long q = tid; q < C.nvalid; q += nth) { int i, j, k; C.ijk(q, i, j, k); A.bb[np_noff(L, i, j, k)] -= off; }
+        for (long long q = tid; q < C.nvalid; q += nth) { int i, j, k; C.ijk(q, i, j, k); BB[np_noff(L, i, j, k)] -= off; }
         __syncthreads();
     }
     int ret = 0, iter = 1;
     double rnorm, rnorm0;
     if (A.type == 0) {
         // ---------------- BiCGStab (MLCGSolver::solve_bicgstab), initial guess 0 -> r = b ----------------
-        for (long long q = tid; q < C.nvalid; q += nth) { int i, j, k; C.ijk(q, i, j, k); const long long o = np_noff(L, i, j, k); A.r[o] = A.bb[o]; }
+        for (long long q = tid; q < C.nvalid; q += nth) { int i, j, k; C.ijk(q, i, j, k); const long long o = np_noff(L, i, j, k); R[o] = BB[o]; }
         __syncthreads();
-        if (A.normalize) C.normalize_vec(A.r);
-        for (long long q = tid; q < C.nvalid; q += nth) { int i, j, k; C.ijk(q, i, j, k); const long long o = np_noff(L, i, j, k); A.rh[o] = A.r[o]; }
+        if (A.normalize) C.normalize_vec(R);
+        for (long long q = tid; q < C.nvalid; q += nth) { int i, j, k; C.ijk(q, i, j, k); const long long o = np_noff(L, i, j, k); RH[o] = R[o]; }
         __syncthreads();
-        rnorm = C.norminf(A.r); rnorm0 = rnorm;
-        if (rnorm0 == 0.0 || rnorm0 < A.eps_abs) { if (tid == 0) { A.out[0] = 0; A.out[1] = 0; } return; }
+        rnorm = C.norminf(R); rnorm0 = rnorm;
+        if (rnorm0 == 0.0 || rnorm0 < A.eps_abs) { if (A.in_smem) for (long long q = tid; q < ntot; q += nth) A.x[q] = 0.0;
+            if (tid == 0) { A.out[0] = 0; A.out[1] = 0; } return; }
         double rho_1 = 0.0, alpha = 0.0, omega = 0.0;
         for (; iter <= A.maxiter; ++iter) {
-            const double rho = C.dot(A.rh, A.r);
+            const double rho = C.dot(RH, R);
             if (rho == 0.0) { ret = 1; break; }
             if (iter == 1) {
-                for (long long q = tid; q < C.nvalid; q += nth) { int i, j, k; C.ijk(q, i, j, k); const long long o = np_noff(L, i, j, k); A.p[o] = A.r[o]; }
+                for (long long q = tid; q < C.nvalid; q += nth) { int i, j, k; C.ijk(q, i, j, k); const long long o = np_noff(L, i, j, k); P[o] = R[o]; }
             } else {
                 const double beta = (rho / rho_1) * (alpha / omega);
                 for (long long q = tid; q < C.nvalid; q += nth) { int i, j, k; C.ijk(q, i, j, k); const long long o = np_noff(L, i, j, k);
-                    const double pv = A.p[o] - omega * A.v[o]; A.p[o] = A.r[o] + beta * pv; }
+                    const double pv = P[o] - omega * V[o]; P[o] = R[o] + beta * pv; }
             }
             __syncthreads();
-            C.apply(A.v, A.p, A.normalize);
-            const double rhTv = C.dot(A.rh, A.v);
+            C.apply(V, P, A.normalize);
+            const double rhTv = C.dot(RH, V);
             if (rhTv != 0.0) alpha = rho / rhTv; else { ret = 2; break; }
             for (long long q = tid; q < C.nvalid; q += nth) { int i, j, k; C.ijk(q, i, j, k); const long long o = np_noff(L, i, j, k);
-                A.x[o] += alpha * A.p[o]; A.s[o] = A.r[o] - alpha * A.v[o]; }
+                X[o] += alpha * P[o]; S[o] = R[o] - alpha * V[o]; }
             __syncthreads();
-            rnorm = C.norminf(A.s);
+            rnorm = C.norminf(S);
             if (rnorm < A.eps_rel * rnorm0 || rnorm < A.eps_abs) break;
-            C.apply(A.t, A.s, A.normalize);
-            const double tt = C.dot(A.t, A.t), ts = C.dot(A.t, A.s);
+            C.apply(T, S, A.normalize);
+            const double tt = C.dot(T, T), ts = C.dot(T, S);
             if (tt != 0.0) omega = ts / tt; else { ret = 3; break; }
             for (long long q = tid; q < C.nvalid; q += nth) { int i, j, k; C.ijk(q, i, j, k); const long long o = np_noff(L, i, j, k);
-                A.x[o] += omega * A.s[o]; A.r[o] = A.s[o] - omega * A.t[o]; }
+                X[o] += omega * S[o]; R[o] = S[o] - omega * T[o]; }
             __syncthreads();
-            rnorm = C.norminf(A.r);
+            rnorm = C.norminf(R);
             if (rnorm < A.eps_rel * rnorm0 || rnorm < A.eps_abs) break;
             if (omega == 0.0) { ret = 4; break; }
             rho_1 = rho;
         }
     } else {
         // ---------------- CG (MLCGSolver::solve_cg) ----------------
-        for (long long q = tid; q < C.nvalid; q += nth) { int i, j, k; C.ijk(q, i, j, k); const long long o = np_noff(L, i, j, k); A.r[o] = A.bb[o]; }
+        for (long long q = tid; q < C.nvalid; q += nth) { int i, j, k; C.ijk(q, i, j, k); const long long o = np_noff(L, i, j, k); R[o] = BB[o]; }
         __syncthreads();
-        rnorm = C.norminf(A.r); rnorm0 = rnorm;
-        if (rnorm0 == 0.0 || rnorm0 < A.eps_abs) { if (tid == 0) { A.out[0] = 0; A.out[1] = 0; } return; }
+        rnorm = C.norminf(R); rnorm0 = rnorm;
+        if (rnorm0 == 0.0 || rnorm0 < A.eps_abs) { if (A.in_smem) for (long long q = tid; q < ntot; q += nth) A.x[q] = 0.0;
+            if (tid == 0) { A.out[0] = 0; A.out[1] = 0; } return; }
         double rho_1 = 0.0;
         for (; iter <= A.maxiter; ++iter) {
-            const double rho = C.dot(A.r, A.r);
+            const double rho = C.dot(R, R);
             if (rho == 0.0) { ret = 1; break; }
             if (iter == 1) {
-                for (long long q = tid; q < C.nvalid; q += nth) { int i, j, k; C.ijk(q, i, j, k); const long long o = np_noff(L, i, j, k); A.p[o] = A.r[o]; }
+                for (long long q = tid; q < C.nvalid; q += nth) { int i, j, k; C.ijk(q, i, j, k); const long long o = np_noff(L, i, j, k); P[o] = R[o]; }
             } else {
                 const double beta = rho / rho_1;
-                for (long long q = tid; q < C.nvalid; q += nth) { int i, j, k; C.ijk(q, i, j, k); const long long o = np_noff(L, i, j, k); A.p[o] = A.r[o] + beta * A.p[o]; }
+                for (long long q = tid; q < C.nvalid; q += nth) { int i, j, k; C.ijk(q, i, j, k); const long long o = np_noff(L, i, j, k); P[o] = R[o] + beta * P[o]; }
             }
             __syncthreads();
-            C.apply(A.v, A.p, false);
-            const double pw = C.dot(A.p, A.v);
+            C.apply(V, P, false);
+            const double pw = C.dot(P, V);
             double alpha;
             if (pw != 0.0) alpha = rho / pw; else { ret = 1; break; }
             for (long long q = tid; q < C.nvalid; q += nth) { int i, j, k; C.ijk(q, i, j, k); const long long o = np_noff(L, i, j, k);
-                A.x[o] += alpha * A.p[o]; A.r[o] -= alpha * A.v[o]; }
+                X[o] += alpha * P[o]; R[o] -= alpha * V[o]; }
             __syncthreads();
-            rnorm = C.norminf(A.r);
+            rnorm = C.norminf(R);
             if (rnorm < A.eps_rel * rnorm0 || rnorm < A.eps_abs) break;
             rho_1 = rho;
         }
     }
     if (ret == 0 && rnorm > A.eps_rel * rnorm0 && rnorm > A.eps_abs) ret = 8;
     if (!((ret == 0 || ret == 8) && rnorm < rnorm0)) {
-        for (long long q = tid; q < ntot; q += nth) A.x[q] = 0.0;     // sol = sorig (= 0)
+        for (long long q = tid; q < ntot; q += nth) X[q] = 0.0;     // sol = sorig (= 0)
     }
+    if (A.in_smem) { __syncthreads(); for (long long q = tid; q < ntot; q += nth) A.x[q] = X[q]; }
     if (tid == 0) { A.out[0] = ret; A.out[1] = iter < A.maxiter ? iter : A.maxiter; }
 }
 

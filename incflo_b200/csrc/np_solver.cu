@@ -171,6 +171,7 @@ int NpSolver::create(const np_geom* g, int nboxes, const np_box* boxes, const in
 #ifndef NP_EMU
     cudaFuncSetAttribute(k_gs2<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GS_SMEM_BYTES);
     cudaFuncSetAttribute(k_gs2<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GS_SMEM_BYTES);
+    cudaFuncSetAttribute(k_bottom_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NP_BOTTOM_SMEM_MAX);
     cudaFuncSetAttribute(k_gs_small<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GS_SMEM_BYTES);
     cudaFuncSetAttribute(k_gs_small<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GS_SMEM_BYTES);
 #define NP_GS3_ATTR(BW, BH, CS, MINB) cudaFuncSetAttribute(k_gs3<BW, BH, CS, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G3<BW, BH>::SMEM_BYTES)
@@ -629,7 +630,9 @@ int NpSolver::bottom_solve()
         a.singular = singular ? 1 : 0; a.normalize = opt.bottom_normalize; a.type = type; a.out = bot_out;
         const long long nv = (long long)(L.d.n[0] + 1) * (L.d.n[1] + 1) * (L.d.n[2] + 1);
         int nth = (int)std::min<long long>(1024, std::max<long long>(64, ((nv + 31) / 32) * 32));
-        NP_LAUNCH(true, k_bottom_solve, dim3(1), dim3(nth), 0, stream, a); ++launches;
+        const size_t bsm = (size_t)8 * L.d.ntot * sizeof(double);
+        a.in_smem = bsm <= NP_BOTTOM_SMEM_MAX ? 1 : 0;
+        NP_LAUNCH(true, k_bottom_solve, dim3(1), dim3(nth), a.in_smem ? bsm : (size_t)0, stream, a); ++launches;
         np_rt::copy_async(h_bot_out, bot_out, 2 * sizeof(int), stream);
         if (in_capture) return 0;            // the status is looked at after the graph has run (iterate_graph)
         np_rt::stream_sync(stream);

@@ -15,6 +15,8 @@ BYTES = {
     "k_gs2": (8 + 8 + sig + 8) * N,                    # x, rhs, (sigma), write x   [zero-input launches read one array less, add-to ones one more]
     "k_stencil": (8 + 8 + sig + 8) * N,                # x, b, (sigma), write y
     "k_restrict": 8 * N + 8 * (257 ** 3),
+    "k_resid_restrict": (8 + 8 + sig) * N + 8 * (257 ** 3),   # cor, res, (sigma) in; coarse res out (the fine residual is stored on the shell only)
+    "k_interp_add_w2": 16 * N + 8 * C + 8 * (257 ** 3),
     "k_interp_add_tri": 16 * N + 8 * (257 ** 3),
     "k_interp_add_w": 16 * N + 8 * C + 8 * (257 ** 3),
     "k_divu": 24 * (516 ** 3) + 8 * N,
