@@ -550,6 +550,7 @@ struct MacSolver {
     // MLMG::solve; `sol` holds the initial guess
     int solve(double rtol, double atol, double rhsnorm0)
     {
+        np_rt::Range nvtx_solve("MLMG::solve");
         const MacLevel& d0 = lev[0].d;
         const long long nb = nblk(grid_adotx(d0));
         bottom_iters = 0; bicg_failed_switch = false;
@@ -683,6 +684,7 @@ struct MacSolver {
     // MacProjector::setUMAC + project
     int project(np_fab umac[3], np_fab* mac_phi, double rtol, double atol)
     {
+        np_rt::Range nvtx_proj("MacProjector::project");
         if (!have_beta) return NP_ERR_STATE;
         for (int d = 0; d < 3; ++d) if (!umac[d].p || umac[d].ncomp < 1) return NP_ERR_INVALID;
         if (mac_phi && (!mac_phi->p || mac_phi->ncomp < 1)) return NP_ERR_INVALID;
@@ -764,6 +766,7 @@ struct MacSolver {
     // (diffuse_scalar forms rho * tracer).
     int solve_abec(np_fab* phi, const np_fab* rhs_in, const np_fab* rho, double rtol, double atol)
     {
+        np_rt::Range nvtx_solve("DiffusionScalarOp::solve");
         if (!have_beta) return NP_ERR_STATE;
         if (!phi || !phi->p || !rhs_in || !rhs_in->p) return NP_ERR_INVALID;
         launches = 0; have_result = false; prof_n = 0; err = 0; g_ms_smooth = 0.0; g_n_smooth = 0;

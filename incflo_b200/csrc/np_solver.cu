@@ -663,6 +663,7 @@ int NpSolver::bottom_solve()
 // to sol inside the last post-smooth (MLMG::oneIter's sol += cor)
 void NpSolver::vcycle(bool add_to_sol)
 {
+    np_rt::Range nvtx_vc("MLMG::mgVcycle");
     const int nl = (int)lev.size();
     for (int l = 0; l < nl - 1; ++l) {
         NpLevel& L = lev[l];
@@ -752,6 +753,7 @@ int NpSolver::iterate_graph(const double* rhs_off, double* resnorm)
 // MLMG::solve with the zero initial guess NodalProjector uses
 int NpSolver::solve(double rtol, double atol)
 {
+    np_rt::Range nvtx_solve("MLMG::solve");
     NpLevel& L0 = lev[0];
     const LevelDev& d0 = L0.d;
     zero(sol, d0.ntot);
@@ -789,6 +791,7 @@ int NpSolver::solve(double rtol, double atol)
     for (int iter = 0; iter < opt.maxiter; ++iter) {
         // MLMG makes the residual solvable before every V-cycle; here the offset (scal[6], left by finish_norm)
         // is subtracted on the fly by the level-0 consumers of res instead of in a separate pass
+        np_rt::Range nvtx_iter("MLMG::oneIter");
         lvl0_off = singular ? scal + 6 : nullptr;
         double rn = 0.0;
         const int grc = iterate_graph(rhs_off, &rn);
@@ -1030,6 +1033,7 @@ void NpSolver::finish_stats()
 
 int NpSolver::project(np_fab* vel, const np_fab* sigma, double rtol, double atol)
 {
+    np_rt::Range nvtx_proj("NodalProjector::project");
     if (vel->ngrow < 1 || vel->ncomp < 3 || sigma->ncomp < 1) return NP_ERR_INVALID;
     err = 0; launches = 0; have_result = false; prof_n = 0; g_ms_smooth = 0.0; g_n_smooth = 0;
     ensure_clean();
