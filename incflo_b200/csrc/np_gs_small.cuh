@@ -8,9 +8,14 @@
 // steps; k_gs2's 2 x 8 blocks in registers make that stream about 700 instructions per thread with 8 warps per SM to
 // hide it behind (2 us per step, 22-27 us per launch whatever the level size).  Here a thread owns a 2 x 2 block - one node
 // of every colour - and a CTA has 2 x 512 threads, so a colour step is one update per thread and 32 warps share the SM.
-// Values are exchanged through the ring only (no register blocking): more shared-memory traffic per update, which does
-// not matter where nothing else runs on the SM.
+// Values are exchanged through shared memory only (no register blocking): more shared-memory traffic per update, which does
+// not matter where nothing else runs on the SM.  A small level's chunk has at most 12 planes (zc <= 9), so the whole chunk
+// is brought into shared memory by one bulk cp.async phase before the march (no per-step loader, no per-step wait), and
+// the right-hand side of a thread's four nodes is fetched one step ahead into registers.
 #pragma once
+
+#define GSS_MAX_ZC 9                     // (zc + 3) planes of GS_PLANE doubles must fit 227 KB of shared memory
+#define GSS_SMEM_BYTES(zc) ((size_t)((zc) + 3) * GS_PLANE * 8)
 
 #define GSS_GT 512                       // threads per sweep group: 32 x 16 blocks of 2 x 2 nodes
 #define GSS_CTA (2 * GSS_GT)
@@ -57,27 +62,41 @@ __global__ void __launch_bounds__(GSS_CTA, 1) k_gs_small(LevelDev L, GsArgs A)
         act |= (unsigned)v << q; dir |= (unsigned)dd << q; wrt |= (unsigned)w << q;
     }
 
-    // plane loader: the 66 x 34 elements of a tile plane (halo included) over all threads of the CTA; elements beyond the
-    // level's ghost layer, and everything when the input is known to be zero, are zero-filled
-    auto slot = [&](int p) -> double* { return ring + ((p + 1) % GS_RING) * GS_PLANE; };     // p >= -1
-    auto load_plane = [&](int p) {                                                           // planes -1 .. nk
-        const double* sp = xin + L.nsz * (long long)(kb + p + 1);
-        double* dp = slot(p);
-        for (int e = tid; e < 66 * 34; e += GSS_CTA) {
+    // bulk load: planes -1 .. nk of the tile (66 x 34 elements each, halo included) over all threads of the CTA; elements
+    // beyond the level's ghost layer, and everything when the input is known to be zero, are zero-filled
+    auto slot = [&](int p) -> double* { return ring + (p + 1) * GS_PLANE; };               // p >= -1
+    {
+        int dsto[3]; long long srco[3]; bool val[3];
+#pragma unroll
+        for (int m = 0; m < 3; ++m) {
+            const int e = tid + m * GSS_CTA;
             const int row = e / 66, col = e - 66 * row;       // lj = row - 1, li = col - 1
             const int i = i0 + col - 1, j = j0 + row - 1;
-            const bool valid = !A.zero_in && i <= L.n[0] + 1 && j <= L.n[1] + 1;
-            np_cp_async8(dp + gss_at(col - 1, row - 1), valid ? sp + (L.nsy * (long long)(j + 1) + (i + 1)) : sp, valid);
+            val[m] = e < 66 * 34 && !A.zero_in && i <= L.n[0] + 1 && j <= L.n[1] + 1;
+            dsto[m] = e < 66 * 34 ? gss_at(col - 1, row - 1) : -1;
+            srco[m] = val[m] ? L.nsy * (long long)(j + 1) + (i + 1) : 0;
         }
+        for (int p = -1; p <= nk; ++p) {
+            const double* sp = xin + L.nsz * (long long)(kb + p + 1);
+            double* dp = slot(p);
+#pragma unroll
+            for (int m = 0; m < 3; ++m) if (dsto[m] >= 0) np_cp_async8(dp + dsto[m], sp + srco[m], val[m]);
+        }
+        np_cp_async_commit();
+    }
+    // right-hand side of this thread's nodes, one plane ahead
+    double rh[4] = {0.0, 0.0, 0.0, 0.0};
+    auto load_rhs = [&](int pn) {
+        const long long o = np_noff(L, gi, gj, kb + pn);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) if ((act >> q) & 1u) rh[q] = rhs[o + L.nsy * (q >> 1) + (q & 1)];
     };
-    load_plane(-1); load_plane(0); load_plane(1);
-    np_cp_async_commit(); np_cp_async_wait_all();
+    if (act != 0u) load_rhs(0);
+    np_cp_async_wait_all();
     __syncthreads();
 
     double xn[4] = {0.0, 0.0, 0.0, 0.0};
     for (int t = 0; t <= nk + 1; ++t) {
-        if (t + 2 <= nk) load_plane(t + 2);
-        np_cp_async_commit();
         const int p = t - 2 * grp;
         const bool on = (p >= 0 && p <= nk - 1) && act != 0u;
         const int k = kb + p;
@@ -101,7 +120,7 @@ __global__ void __launch_bounds__(GSS_CTA, 1) k_gs_small(LevelDev L, GsArgs A)
                 for (int q = 0; q < 4; ++q) {
                     const int a = q & 1, b = q >> 1;
                     if ((act >> q) & 1u) {
-                        const double rv = rhs[gbase + L.nsy * b + a] - roff;
+                        const double rv = rh[q] - roff;
                         const double oop = C.a_fz * S[b + 1][a + 1] + C.a_exz * (S[b + 1][a] + S[b + 1][a + 2]) + C.a_eyz * (S[b][a + 1] + S[b + 2][a + 1])
                                          + C.a_c * ((S[b][a] + S[b][a + 2]) + (S[b + 2][a] + S[b + 2][a + 2]));
                         B[q] = fma(rv, C.dinv, -oop);
@@ -125,7 +144,7 @@ __global__ void __launch_bounds__(GSS_CTA, 1) k_gs_small(LevelDev L, GsArgs A)
                     V[q][0] = Sl[0][b][a] + Sl[1][b][a];         V[q][1] = Sl[0][b][a + 1] + Sl[1][b][a + 1];
                     V[q][2] = Sl[0][b + 1][a] + Sl[1][b + 1][a]; V[q][3] = Sl[0][b + 1][a + 1] + Sl[1][b + 1][a + 1];
                     if ((act >> q) & 1u) {
-                        double bv = rhs[gbase + L.nsy * b + a] - roff;
+                        double bv = rh[q] - roff;
 #pragma unroll
                         for (int z = 0; z < 2; ++z) {
                             const double* P = z ? Pp : Pm;
@@ -143,6 +162,7 @@ __global__ void __launch_bounds__(GSS_CTA, 1) k_gs_small(LevelDev L, GsArgs A)
             }
         }
 
+        if (act != 0u && p + 1 >= 0 && p + 1 <= nk - 1) load_rhs(p + 1);      // rh is free now: the next plane's values fly across the colour steps
         // ---- the four colour steps: colour q is node q of every block ----
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
@@ -161,7 +181,6 @@ __global__ void __launch_bounds__(GSS_CTA, 1) k_gs_small(LevelDev L, GsArgs A)
             if (q == 0 || q == 2) __syncwarp();
             else if (q == 1) np_group_barrier512(grp);
         }
-        np_cp_async_wait_all();
         __syncthreads();
         if (on && grp == 1 && p < nkw) {
 #pragma unroll

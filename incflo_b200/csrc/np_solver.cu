@@ -172,8 +172,8 @@ int NpSolver::create(const np_geom* g, int nboxes, const np_box* boxes, const in
     cudaFuncSetAttribute(k_gs2<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GS_SMEM_BYTES);
     cudaFuncSetAttribute(k_gs2<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GS_SMEM_BYTES);
     cudaFuncSetAttribute(k_bottom_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NP_BOTTOM_SMEM_MAX);
-    cudaFuncSetAttribute(k_gs_small<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GS_SMEM_BYTES);
-    cudaFuncSetAttribute(k_gs_small<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GS_SMEM_BYTES);
+    cudaFuncSetAttribute(k_gs_small<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GSS_SMEM_BYTES(GSS_MAX_ZC));
+    cudaFuncSetAttribute(k_gs_small<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GSS_SMEM_BYTES(GSS_MAX_ZC));
 #define NP_GS3_ATTR(BW, BH, CS, MINB) cudaFuncSetAttribute(k_gs3<BW, BH, CS, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G3<BW, BH>::SMEM_BYTES)
     NP_GS3_ATTR(2, 8, true, 2); NP_GS3_ATTR(2, 4, true, 1); NP_GS3_ATTR(4, 8, true, 2); NP_GS3_ATTR(4, 4, true, 2);
     NP_GS3_ATTR(2, 8, false, 1); NP_GS3_ATTR(2, 4, false, 1); NP_GS3_ATTR(4, 4, false, 1); NP_GS3_ATTR(2, 8, false, 2);
@@ -521,9 +521,9 @@ void NpSolver::smooth(int l, bool zero_in, double* add_to)
     auto launch = [&](int nz) {
         const dim3 g(grid.x, grid.y, nz);
         // a launch of at most one CTA per SM is a chain of plane steps with nothing to hide behind: the 2 x 2-block kernel
-        if (gs_small && (long long)g.x * g.y * g.z <= (long long)gs_small * np_rt::sm_count()) {
-            if (d.const_sigma) NP_LAUNCH(true, (k_gs_small<true>), g, dim3(GSS_CTA), smem, stream, d, ga);
-            else               NP_LAUNCH(true, (k_gs_small<false>), g, dim3(GSS_CTA), smem, stream, d, ga);
+        if (gs_small && ga.zc <= GSS_MAX_ZC && (long long)g.x * g.y * g.z <= (long long)gs_small * np_rt::sm_count()) {
+            if (d.const_sigma) NP_LAUNCH(true, (k_gs_small<true>), g, dim3(GSS_CTA), GSS_SMEM_BYTES(ga.zc), stream, d, ga);
+            else               NP_LAUNCH(true, (k_gs_small<false>), g, dim3(GSS_CTA), GSS_SMEM_BYTES(ga.zc), stream, d, ga);
             ++launches;
             return;
         }
