@@ -152,6 +152,8 @@ def run_reference(args):
     if rank != 0:
         return
     n = args.cpu_ncell
+    if n is None:       # the workload itself when the whole run stays within a few minutes, else a bounded sample of it
+        n = 512 if (args.steps + min(args.warmup, 1)) * 26.0 <= 240.0 else 256
     r = cpu_projection(n, args.steps, min(args.warmup, 1))
     line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": r["ms_per_step"], "higher_is_better": True,
@@ -572,7 +574,7 @@ def run_gpu(args):
                     "launches_per_vcycle": o["launches"] / o["vcycles"], "cuda_graph": o["graph"],
                     "roofline": {k: r[k] for k in ("kernel", "frac", "frac_fused_pass", "avg_launch_ms", "share_of_step", "vcycle_algorithmic")}}
         if world == 1 and not args.no_cpu:
-            r = cpu_projection(args.cpu_ncell, 1, 0)
+            r = cpu_projection(args.cpu_ncell or 512, 1, 0)      # the workload itself: one 512^3 projection, ~25 s on 16 cores
             line["cpu_baseline"] = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port",
                                     "sample": r["sample"], "vcycles": r["vcycles"]}
         print(json.dumps(line), flush=True)
@@ -934,7 +936,9 @@ def main():
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--ncell", type=int, default=512, help="cells per side per GPU (512: configs[2]; 256: configs[1])")
     ap.add_argument("--vel-ngrow", type=int, default=2, help="ghost layers of the velocity fab (incflo nghost_state: 2 MOL / 3 Godunov)")
-    ap.add_argument("--cpu-ncell", type=int, default=256, help="size of the bounded CPU sample")
+    ap.add_argument("--cpu-ncell", type=int, default=None,
+                    help="size of the CPU run (oracle): default 512 for the nodal path (the workload itself, ~25 s per projection on 16 cores; "
+                         "--impl reference falls back to a 256^3 sample when steps x 26 s would exceed four minutes), 256 for --path mac / diffusion")
     ap.add_argument("--workload", default="double_shear", choices=["double_shear", "rayleigh_taylor"],
                     help="double_shear: BASELINE configs[2] (constant density, default); rayleigh_taylor: configs[3] (variable sigma)")
     ap.add_argument("--e2e-steps", type=int, default=2)
@@ -950,6 +954,8 @@ def main():
     ap.add_argument("--no-overlap", action="store_true", help="experiment knob: halo exchange on the solver stream (overlap_halo=0)")
     ap.add_argument("--verbose", type=int, default=0, help="nodal_proj.verbose (4: per-launch smoother times on stderr)")
     args = ap.parse_args()
+    if args.cpu_ncell is None and args.path in ("mac", "diffusion"):
+        args.cpu_ncell = 256
     if args.path == "mac":
         run_reference_mac(args) if args.impl == "reference" else run_gpu_mac(args)
     elif args.path == "diffusion":
