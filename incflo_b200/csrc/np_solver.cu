@@ -61,6 +61,7 @@ int NpSolver::create(const np_geom* g, int nboxes, const np_box* boxes, const in
     if (np_rt::init()) return NP_ERR_NO_DEVICE;
     if (const char* e = std::getenv("NP_FUSED_RR")) fused_rr = std::atoi(e) != 0;        // experiment knob: 0 = residual and restriction as two kernels
     if (const char* e = std::getenv("NP_GS_SMALL")) gs_small = std::atoi(e);
+    if (const char* e = std::getenv("NP_GS_SMALL_VARIANT")) gs_small_variant = std::atoi(e);
     if (const char* e = std::getenv("NP_INTERP_MARCH")) interp_march = std::atoi(e) != 0;
     if (const char* e = std::getenv("NP_GS_VARIANT")) gs_variant_c = std::atoi(e);        // experiment knobs: which smoother kernel
     if (const char* e = std::getenv("NP_GSV_VARIANT")) gs_variant_v = std::atoi(e);
@@ -527,8 +528,9 @@ void NpSolver::smooth(int l, bool zero_in, double* add_to)
             ++launches;
             return;
         }
+        const bool small_launch = (long long)g.x * g.y * g.z <= (long long)np_rt::sm_count();
         if (d.const_sigma) {
-            switch (gs_variant_c) {
+            switch (small_launch && gs_small_variant ? gs_small_variant : gs_variant_c) {
             case 1: NP_GS3(2, 8, true, 2); break;
             case 2: NP_GS3(2, 4, true, 1); break;
             case 3: NP_GS3(4, 8, true, 2); break;
@@ -536,7 +538,7 @@ void NpSolver::smooth(int l, bool zero_in, double* add_to)
             default: NP_LAUNCH(true, (k_gs2<true>), g, dim3(256), smem, stream, d, ga); break;
             }
         } else {
-            switch (gs_variant_v) {
+            switch (small_launch && gs_small_variant ? gs_small_variant : gs_variant_v) {
             case 1: NP_GS3(2, 8, false, 1); break;
             case 2: NP_GS3(2, 4, false, 1); break;
             case 3: NP_GS3(4, 4, false, 1); break;

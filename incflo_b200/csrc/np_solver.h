@@ -108,6 +108,8 @@ struct NpSolver {
     const double* lvl0_off = nullptr;   // device scalar subtracted from lev[0].res by its consumers (lazy makeSolvable)
     int err = 0;
     int gs_variant_c = 0, gs_variant_v = 0;   // which smoother kernel runs for constant / variable sigma (0: k_gs2)
+    int gs_small_variant = 2;                 // smoother launches of at most one CTA per SM run this k_gs3 variant (2: 2 x 4 blocks, 512 threads:
+                                              // half the instruction stream per warp and plane step; env NP_GS_SMALL_VARIANT; 0: as the large launches)
     bool interp_march = true;                 // sigma-weighted prolongation: k_interp_add_w2 (z-marching); env NP_INTERP_MARCH=0: k_interp_add_w
     int gs_small = 0;                         // smoother launches of <= gs_small * (SM count) CTAs run k_gs_small (env NP_GS_SMALL; 0: never = default: measured slower than k_gs2)
 
