@@ -266,8 +266,16 @@ __device__ __forceinline__ void gs3_run(const LevelDev& L, const GsArgs& A, doub
     const int tid = threadIdx.x;
     const int grp = tid / G::GT;                         // 0: first sweep (plane t), 1: second sweep (plane t-2)
     const int tg = tid - grp * G::GT;
-    const int lx = tg % G::NLX, ty = tg / G::NLX;
     const int i0 = blockIdx.x * GS_WX, j0 = blockIdx.y * GS_WY, kb = (A.zmap0 + (int)blockIdx.z * A.zmapS) * zc;
+    // Which row block a warp owns.  On a tile that is not full only the first act_ty row blocks have nodes; warps go to the four
+    // schedulers of the SM round-robin, so the second sweep group's row blocks are rotated to start on the scheduler after the
+    // first group's last busy one (a small level is a chain of plane steps bound by the issue slots of its busiest scheduler).
+    const int lx = tg % G::NLX;
+    int ty = tg / G::NLX;
+    if (!FULL && grp == 1) {
+        const int act_ty = (min(GS_TY, L.n[1] + 1 - j0) + BH - 1) / BH;
+        if (act_ty < G::NTY) ty = (ty - act_ty % G::NTY + G::NTY) % G::NTY;
+    }
     const int nk  = min(kb + zc, L.n[2]) - kb + 1;       // relaxed planes p = 0..nk-1 (global k = kb+p)
     const int nkw = min(kb + zc - 1, L.n[2]) - kb + 1;   // written planes
     const int gi = i0 + BW * lx, gj = j0 + BH * ty;      // first node of this thread's block
