@@ -764,8 +764,14 @@ def run_gpu_mac(args):
     per_cell = 2 * (24 if const_beta else 48)            # one smooth = red + black sweep: cor r/w, rhs[, bx, by, bz] each
     avg_ms = ms_smooth / max(n_smooth, 1)
     achieved = per_cell * dof_gpu / (avg_ms * 1e-3) / 1e9 if avg_ms > 0 else 0.0
-    kname = (f"k_mac_rb3<{'const' if const_beta else 'variable'} beta> (red + black sweep of one smooth in one pass), level 0" if world == 1 else
-             f"k_mac_gsrb<{'const' if const_beta else 'variable'} beta> x 2 with a halo-plane exchange before each colour (one smooth of a slab), level 0")
+    # slabs made of whole 64 x 16 tiles (every benchmark size) run the one-pass smoother on every rank count; the timed region
+    # of a smooth then also holds the two-plane exchange of the iterate that precedes the launch on a sharded level
+    whole_tiles = n % 64 == 0 and n % 16 == 0
+    kb = 'const' if const_beta else 'variable'
+    if whole_tiles:
+        kname = f"k_mac_rb3<{kb} beta> (red + black sweep of one smooth in one pass), level 0" + ("" if world == 1 else " + the two-plane halo exchange before it")
+    else:
+        kname = f"k_mac_gsrb<{kb} beta> x 2 (one launch per colour" + (")" if world == 1 else ", a halo-plane exchange before each)") + ", level 0"
     roof = {"bound": "hbm", "kernel": kname,
             "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
             "traffic": read_traffic(const_beta, "k_mac_rb3_const", "k_mac_rb3_var"), "peak_source": peak_src,

@@ -163,7 +163,8 @@ struct HaloP2P {
     unsigned long long* mine;                                  // my four flags (written by the neighbours)
     unsigned long long* lo_flags; unsigned long long* hi_flags;   // the neighbours' flag arrays (null: no neighbour)
     unsigned long long* epoch_word;                            // my count of finished exchanges (device memory, so that a CUDA
-                                                               // graph can replay the launch: nothing changes in its arguments)
+                                                               // graph can replay the launch: nothing changes in its arguments);
+                                                               // epoch_word[1]: error word (first exchange a wait gave up on)
     unsigned int* counter;                                     // CTAs of this launch that finished their stores
 };
 __device__ __forceinline__ void np_flag_store(unsigned long long* p, unsigned long long v)
@@ -184,6 +185,24 @@ __device__ __forceinline__ unsigned long long np_flag_load(const unsigned long l
     return v;
 #endif
 }
+// Wait until *p >= epoch.  Every rank runs the same sequence of exchanges, so the wait is short; if a neighbour never gets there
+// (it returned early on an error of its own, or died), the spin gives up after NP_SPIN_BUDGET clocks (about ten seconds),
+// records the exchange in this rank's error word (checked by the host after the solve: NP_ERR_NCCL) and every later wait of
+// this rank returns at once, so that the stream drains instead of hanging the GPU.
+#define NP_SPIN_BUDGET 20000000000ll
+__device__ __forceinline__ void np_wait_flag(const unsigned long long* p, unsigned long long epoch, unsigned long long* errw)
+{
+    if (*(volatile unsigned long long*)errw != 0ull) return;
+#ifdef NP_EMU
+    (void)p; (void)epoch;
+#else
+    const long long t0 = clock64();
+    unsigned n = 0;
+    while (np_flag_load(p) < epoch) {
+        if ((++n & 4095u) == 0u && clock64() - t0 > NP_SPIN_BUDGET) { *(volatile unsigned long long*)errw = epoch; __threadfence_system(); return; }
+    }
+#endif
+}
 __global__ void __launch_bounds__(256) k_halo_p2p(HaloP2P a)
 {
     // the number of this exchange: every rank runs the same sequence of exchanges, so the counts agree.  The word is advanced
@@ -197,8 +216,8 @@ __global__ void __launch_bounds__(256) k_halo_p2p(HaloP2P a)
     }
     // 2) wait until the neighbours have said the same about theirs
     if (threadIdx.x == 0) {
-        if (a.lo_flags) while (np_flag_load(a.mine + NP_FLAG_READY_LO) < epoch) { }
-        if (a.hi_flags) while (np_flag_load(a.mine + NP_FLAG_READY_HI) < epoch) { }
+        if (a.lo_flags) np_wait_flag(a.mine + NP_FLAG_READY_LO, epoch, a.epoch_word + 1);
+        if (a.hi_flags) np_wait_flag(a.mine + NP_FLAG_READY_HI, epoch, a.epoch_word + 1);
     }
     __syncthreads();
     // 3) my boundary planes -> their ghost planes (16-byte stores; plane sizes are even)
@@ -222,8 +241,8 @@ __global__ void __launch_bounds__(256) k_halo_p2p(HaloP2P a)
             __threadfence_system();
             if (a.lo_flags) np_flag_store(a.lo_flags + NP_FLAG_DONE_HI, epoch);
             if (a.hi_flags) np_flag_store(a.hi_flags + NP_FLAG_DONE_LO, epoch);
-            if (a.lo_flags) while (np_flag_load(a.mine + NP_FLAG_DONE_LO) < epoch) { }
-            if (a.hi_flags) while (np_flag_load(a.mine + NP_FLAG_DONE_HI) < epoch) { }
+            if (a.lo_flags) np_wait_flag(a.mine + NP_FLAG_DONE_LO, epoch, a.epoch_word + 1);
+            if (a.hi_flags) np_wait_flag(a.mine + NP_FLAG_DONE_HI, epoch, a.epoch_word + 1);
         }
     }
 }

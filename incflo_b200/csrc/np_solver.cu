@@ -1018,7 +1018,13 @@ void np_fill_cell3(NpSolver& S, FabView u)
 void NpSolver::finish_stats()
 {
     np_rt::event_record(ev[3], stream);
+    // peer-memory halos: did a wait for a neighbour give up (k_halo_p2p, np_wait_flag)?  The word stays set: the handle is dead.
+    if (peer.ok) np_rt::copy_async(h_scal + 18, peer.flags + 5, sizeof(unsigned long long), stream);
     np_rt::stream_sync(stream);
+    if (peer.ok) {
+        unsigned long long w; memcpy(&w, h_scal + 18, sizeof(w));
+        if (w != 0ull) { if (!err) err = NP_ERR_NCCL; if (opt.verbose >= 1) fprintf(stderr, "[nodalproj] rank %d: a neighbour never reached halo exchange %llu\n", comm.rank, w); }
+    }
     stats.ms_setup = np_rt::event_ms(ev[0], ev[1]);
     stats.ms_solve = np_rt::event_ms(ev[1], ev[2]);
     stats.ms_finish = np_rt::event_ms(ev[2], ev[3]);
