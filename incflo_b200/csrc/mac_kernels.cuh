@@ -271,13 +271,16 @@ struct RbCell { int so; int go; int gfx; int flags; int dxm; };   // smem offset
 #define RB3_SO(lx, ly) (((lx) >> 1) + ((lx) & 1) * (RB_PX / 2) + RB_PX * (ly))
 #define RB3_DXM(lx) (((lx) & 1) ? -(RB_PX / 2) : (RB_PX / 2 - 1))
 
-template <bool CB>
+// HA: the operator has MLABecLaplacian's alpha * a term (the diffusion solves): one more cell value in the diagonal
+template <bool CB, bool HA>
 __device__ __forceinline__ double rb3_update(const MacLevel& L, const MacBeta& B, const double* __restrict__ P, const double* __restrict__ Pm,
                                              const double* __restrict__ Pp, const RbCell& cl, int zflags, long long zc, long long zfx, long long zfy,
                                              double rhs_c, double off)
 {
     const int o = cl.so;
     const double xc = P[o];
+    double at = 0.0;
+    if (HA) at = L.ascal * L.acoef[zc + cl.go];
     double bxm, bxp, bym, byp, bzm, bzp;
     if (CB) { bxm = bxp = bym = byp = bzm = bzp = L.beta0; }
     else {
@@ -285,7 +288,8 @@ __device__ __forceinline__ double rb3_update(const MacLevel& L, const MacBeta& B
         const double* py = B.by + zfy + cl.go;  bym = py[0]; byp = py[L.sx];
         const double* pz = B.bz + zc + cl.go;   bzm = pz[0]; bzp = pz[L.sxy];
     }
-    const double gamma = L.dh[0] * (bxm + bxp) + L.dh[1] * (bym + byp) + L.dh[2] * (bzm + bzp);
+    const double gamma = HA ? at + L.dh[0] * (bxm + bxp) + L.dh[1] * (bym + byp) + L.dh[2] * (bzm + bzp)
+                            : L.dh[0] * (bxm + bxp) + L.dh[1] * (bym + byp) + L.dh[2] * (bzm + bzp);
     const double r = rhs_c - off;
     const int fl = cl.flags | zflags;
     double xm = P[o + cl.dxm], xp = P[o + cl.dxm + 1], ym = P[o - RB_PX], yp = P[o + RB_PX], zm = Pm[o], zp = Pp[o];
@@ -328,7 +332,7 @@ __device__ __forceinline__ int rb3_zmap(const MacLevel& L, int p)
     return RB_NOPLANE;
 }
 
-template <bool CB>
+template <bool CB, bool HA = false>
 __global__ void __launch_bounds__(256) k_mac_rb3(MacLevel L, MacLevel Lc, MacBeta B, RbArgs A)
 {
     __shared__ __align__(16) double ring[4 * RB_PS];
@@ -434,6 +438,10 @@ __global__ void __launch_bounds__(256) k_mac_rb3(MacLevel L, MacLevel Lc, MacBet
             for (int e = 0; e < 2; ++e) if (fso[e] >= 0) P[fso[e]] = pre_fr[e];
             fetch_plane(p + 1);
             fetch_rhs(p + 1);
+            if (HA) {       // the a values the next step's red sweep (plane p) and, one step later, its black sweep read: into L1 now
+                const int gza = rb3_zmap(L, p);
+                if (gza != RB_NOPLANE && p <= z1) { const long long za = L.sxy * (long long)gza; np_prefetch_l1(L.acoef + za + own0.go); np_prefetch_l1(L.acoef + za + own1.go); }
+            }
             if (!CB) {      // variable coefficients: pull the lines the next step's red sweep (plane p) reads into L1 now; the black
                             // sweep of that plane, one step later, finds them there
                 const int gzn = rb3_zmap(L, p);
@@ -459,10 +467,10 @@ __global__ void __launch_bounds__(256) k_mac_rb3(MacLevel L, MacLevel Lc, MacBet
                 const long long zc = L.sxy * (long long)gz, zfx = fxz * gz, zfy = fyz * gz;
                 // reds only read blacks (and their own value), so the in-place writes of other threads cannot be seen here
                 const RbCell c0 = cell_of(0, (par0 + q) & 1), c1 = cell_of(1, (par1 + q) & 1);
-                const double n0 = rb3_update<CB>(L, B, P, Pm, Pp, c0, zfl, zc, zfx, zfy, CB ? cr0 : A.rhs[zc + c0.go], off);
-                const double n1 = rb3_update<CB>(L, B, P, Pm, Pp, c1, zfl, zc, zfx, zfy, CB ? cr1 : A.rhs[zc + c1.go], off);
+                const double n0 = rb3_update<CB, HA>(L, B, P, Pm, Pp, c0, zfl, zc, zfx, zfy, CB ? cr0 : A.rhs[zc + c0.go], off);
+                const double n1 = rb3_update<CB, HA>(L, B, P, Pm, Pp, c1, zfl, zc, zfx, zfy, CB ? cr1 : A.rhs[zc + c1.go], off);
                 P[c0.so] = n0; P[c1.so] = n1;
-                if (rc.so >= 0 && (((rpar + q) & 1) == 0)) P[rc.so] = rb3_update<CB>(L, B, P, Pm, Pp, rc, zfl, zc, zfx, zfy, CB ? crr : A.rhs[zc + rc.go], off);
+                if (rc.so >= 0 && (((rpar + q) & 1) == 0)) P[rc.so] = rb3_update<CB, HA>(L, B, P, Pm, Pp, rc, zfl, zc, zfx, zfy, CB ? crr : A.rhs[zc + rc.go], off);
             }
         }
         __syncthreads();
@@ -480,7 +488,7 @@ __global__ void __launch_bounds__(256) k_mac_rb3(MacLevel L, MacLevel Lc, MacBet
                     const int so = m ? own1.so : own0.so;
                     double2 v = make_double2(P[so], P[so + RB_PX / 2]);
                     const RbCell cb = cell_of(m, a);
-                    const double nb = rb3_update<CB>(L, B, P, Pm, Pp, cb, zfl, zc, zfx, zfy, CB ? (m ? ck1 : ck0) : A.rhs[zc + cb.go], off);
+                    const double nb = rb3_update<CB, HA>(L, B, P, Pm, Pp, cb, zfl, zc, zfx, zfy, CB ? (m ? ck1 : ck0) : A.rhs[zc + cb.go], off);
                     if (a) v.y = nb; else v.x = nb;
                     const long long c = zc + (m ? own1.go : own0.go);
                     *reinterpret_cast<double2*>(A.out + c) = v;

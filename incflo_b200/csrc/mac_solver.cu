@@ -5,6 +5,7 @@
 #include "../../include/macproj.h"
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <new>
 #include <vector>
 
@@ -114,6 +115,7 @@ struct MacSolver {
     {
         if (np_rt::init()) return NP_ERR_NO_DEVICE;
         geom = *g; opt = *o; comm = c; comm.rank = my_rank; comm.nranks = nranks;
+        if (const char* e = std::getenv("NP_MAC_FUSED_MIN_N")) opt.fused_rb_min_n = std::atoi(e);      // experiment knob (A/B of the one-pass smoother)
         if (nranks < 1 || my_rank < 0 || my_rank >= nranks || nboxes < 1) return NP_ERR_INVALID;
         for (int d = 0; d < 3; ++d) if (g->ncell[d] < 2) return NP_ERR_INVALID;
         int nloc[3] = {g->ncell[0], g->ncell[1], g->ncell[2]};
@@ -319,7 +321,11 @@ struct MacSolver {
     bool fused_ok(int l) const
     {
         const MacLevel& d = lev[l].d;
-        if (d.acoef) return false;            // the one-pass smoother knows the alpha = 0 operator only
+        // alpha * a (the diffusion solves): the whole-tile kernel only, and only where it pays - measured at 512^3 / 256^3 with
+        // Rayleigh-Taylor density: one pass instead of a launch per colour is 2.20 against 2.73 ms per smooth on a 512^3 level with
+        // variable b (1.74 / 1.79 uniform) but 0.247 against 0.224 ms on a 256^3 level: the extra coefficient stream costs the
+        // latency-bound one-pass kernel more than the second pass costs the streaming one there
+        if (d.acoef && (!(d.n[0] % RB_TX == 0 && d.n[1] % RB_TY == 0) || d.n[0] < 4 * opt.fused_rb_min_n)) return false;
         if (opt.fused_rb_min_n <= 0 || d.n[0] < opt.fused_rb_min_n || (d.n[0] & 1)) return false;
         // a slab runs the one-pass smoother on two ghost planes per side (the reds of the planes next to the slab are recomputed
         // there, from the right-hand side and the coefficients of one ghost plane); only the hoisted-index kernel knows about
@@ -359,7 +365,10 @@ struct MacSolver {
         const dim3 g((L.d.n[0] + RB_TX - 1) / RB_TX, (L.d.n[1] + RB_TY - 1) / RB_TY, (L.d.n[2] + A.zc - 1) / A.zc);
         const MacLevel& C = crse ? lev[l + 1].d : L.d;
         const bool whole_tiles = L.d.n[0] % RB_TX == 0 && L.d.n[1] % RB_TY == 0;      // hoisted-index variant
-        if (whole_tiles) {
+        if (whole_tiles && L.d.acoef) {          // MLABecLaplacian with alpha * a (the diffusion solves)
+            if (L.d.const_beta) NP_LAUNCH(true, (k_mac_rb3<true, true>), g, dim3(256), 0, stream, L.d, C, L.beta(), A);
+            else NP_LAUNCH(true, (k_mac_rb3<false, true>), g, dim3(256), 0, stream, L.d, C, L.beta(), A);
+        } else if (whole_tiles) {
             if (L.d.const_beta) NP_LAUNCH(true, (k_mac_rb3<true>), g, dim3(256), 0, stream, L.d, C, L.beta(), A);
             else NP_LAUNCH(true, (k_mac_rb3<false>), g, dim3(256), 0, stream, L.d, C, L.beta(), A);
         } else if (L.d.const_beta) NP_LAUNCH(true, (k_mac_rb2<true>), g, dim3(256), 0, stream, L.d, C, L.beta(), A);

@@ -80,6 +80,45 @@ def test_abec_operator_and_smoother_hooks(backend, bclo, bchi, const_b):
 
 
 @pytest.mark.parametrize("bclo,bchi", BCS)
+@pytest.mark.parametrize("const_b", [False, True])
+@pytest.mark.parametrize("ncell", [(128, 32, 8), (64, 16, 16)])
+def test_abec_one_pass_smoother(backend, bclo, bchi, const_b, ncell):
+    """The one-pass two-colour smoother with the alpha a term (k_mac_rb3<., true>: levels made of whole 64 x 16 tiles; forced
+    onto these small grids with fused_rb_min_n = 2): smooth hook and a whole solve with Dirichlet data against the oracle."""
+    rng = np.random.default_rng(13)
+    hi = (2.0, 0.5, 0.25)
+    like, dev = backend["like"], backend.get("device", "cuda")
+    beta = random_beta(rng, ncell, bclo, const_b)
+    a = rng.uniform(0.5, 2.0, ncell[::-1])
+    alpha, bscal = 1.1, 0.03
+    op = DiffusionScalarOp(Geometry(ncell, (0, 0, 0), hi, [b == 0 for b in bclo]), bclo, bchi, lib=backend["lib"], like=like, device=dev,
+                           bottom_solver=0, fused_rb_min_n=2)
+    op._init([face_fab_from_array(b, 0, like, dev) for b in beta])
+    L, h = op.L, op.P.h
+    capi.check(L, L.mp_set_scalars(h, alpha, bscal))
+    fa = Fab.from_array(a, 0, False, like, dev)
+    capi.check(L, L.mp_set_acoeffs(h, C.byref(fa.c())))
+    o = MacOracle(ncell, (0, 0, 0), hi, bclo, bchi)
+    o.set_scalars(alpha, bscal); o.set_acoef(a); o.set_beta(*beta)
+    x, b = rng.standard_normal(ncell[::-1]), rng.standard_normal(ncell[::-1])
+    fx, fb = Fab.from_array(x, 0, False, like, dev), Fab.from_array(b, 0, False, like, dev)
+    capi.check(L, L.mp_smooth(h, 0, C.byref(fx.c()), C.byref(fb.c()), 2))
+    so = o.smooth(0, x, b, 2)
+    assert np.abs(fx.numpy_valid()[0] - so).max() <= 1e-13 * np.abs(so).max()
+    rhs = rng.standard_normal(ncell[::-1])
+    phi_g = rng.standard_normal(tuple(n + 2 for n in ncell[::-1]))
+    fphi = Fab.zeros(ncell, 1, 1, False, like, dev)
+    nphelp.assign(fphi.data, phi_g[None])
+    st = op.solve(fphi, Fab.from_array(rhs, 0, False, like, dev), alpha, bscal, fa, [face_fab_from_array(b, 0, like, dev) for b in beta], 1e-11, 1e-14)
+    o.set_phi(phi_g[1:-1, 1:-1, 1:-1])
+    s2 = o.solve_abec(rhs, 1e-11, 1e-14, ghost_face_values(phi_g, bclo, bchi))
+    assert st.status == 0 and s2.status == 0
+    assert st.n_vcycles == s2.n_vcycles and st.bottom_iters_total == s2.bottom_iters_total
+    assert l2rel(fphi.numpy_valid()[0], o.get_phi()) <= 1e-10
+    op.close()
+
+
+@pytest.mark.parametrize("bclo,bchi", BCS)
 def test_abec_solve_matches_oracle(backend, bclo, bchi):
     """mp_solve with variable a and b, an initial guess and inhomogeneous Dirichlet values in the ghost cells."""
     rng = np.random.default_rng(5)
