@@ -325,7 +325,7 @@ struct MacSolver {
         // Rayleigh-Taylor density: one pass instead of a launch per colour is 2.20 against 2.73 ms per smooth on a 512^3 level with
         // variable b (1.74 / 1.79 uniform) but 0.247 against 0.224 ms on a 256^3 level: the extra coefficient stream costs the
         // latency-bound one-pass kernel more than the second pass costs the streaming one there
-        if (d.acoef && (!(d.n[0] % RB_TX == 0 && d.n[1] % RB_TY == 0) || d.n[0] < 4 * opt.fused_rb_min_n)) return false;
+        if (d.acoef && (!(d.n[0] % RB_TX == 0 && d.n[1] % RB_TY == 0) || d.n[0] < 2 * opt.fused_rb_min_n)) return false;
         if (opt.fused_rb_min_n <= 0 || d.n[0] < opt.fused_rb_min_n || (d.n[0] & 1)) return false;
         // a slab runs the one-pass smoother on two ghost planes per side (the reds of the planes next to the slab are recomputed
         // there, from the right-hand side and the coefficients of one ghost plane); only the hoisted-index kernel knows about
@@ -957,7 +957,7 @@ void mp_default_options(mp_options* o)
 {
     o->max_coarsening_level = 100; o->maxiter = 200; o->bottom_maxiter = 200; o->num_pre_smooth = 2; o->num_post_smooth = 2;
     o->num_final_smooth = 8; o->bottom_solver = NP_BOTTOM_BICGCG; o->verbose = 0; o->bottom_verbose = 0; o->maxorder = 3;
-    o->bottom_rtol = 1e-4; o->bottom_atol = -1.0; o->const_beta_fastpath = 1; o->fused_rb_min_n = 128; o->fused_rb_const = 1; o->profile_kernels = 0; o->agg_min_local_nz = 32; o->use_graph = 1;
+    o->bottom_rtol = 1e-4; o->bottom_atol = -1.0; o->const_beta_fastpath = 1; o->fused_rb_min_n = 256; o->fused_rb_const = 1; o->profile_kernels = 0; o->agg_min_local_nz = 32; o->use_graph = 1;
 }
 int mp_create(mp_handle** h, const np_geom* geom, int nboxes_global, const np_box* all_boxes, const int* owner_rank,
               int my_rank, int nranks, void* nccl_comm_or_null, const mp_options* opt)

@@ -48,7 +48,9 @@ typedef struct {
     double bottom_atol;         /* mac_proj.bottom_atol                    default -1 */
     int const_beta_fastpath;    /* skip every coefficient read when b is uniform (constant density); default 1 */
     int fused_rb_min_n;         /* levels with at least this many cells in x run the red and the black sweep of a smooth in
-                                   ONE pass (k_mac_rb2); smaller levels use one launch per colour; default 128, <= 0: never */
+                                   ONE pass (k_mac_rb3 / k_mac_rb2); smaller levels use one launch per colour; default 256 (measured:
+                                   a 128^3 level is faster with two launches), <= 0: never.  With MLABecLaplacian's alpha * a term
+                                   (mp_set_acoeffs) the one-pass kernel runs from twice this size up, on whole-tile levels */
     int fused_rb_const;         /* 1 (default): also when b is uniform; 0: one launch per colour there */
     int agg_min_local_nz;       /* multi-GPU: replicate MG levels whose slab would be thinner than this; default 32 */
     int profile_kernels;        /* bracket every level-0 smooth with CUDA events (np_stats.ms_smooth0 / n_smooth0); default 0 */

@@ -384,7 +384,7 @@ def test_mac_iteration_graph_matches_kernel_by_kernel_path():
         return np.random.default_rng(43)
 
     for bclo, bchi in (BCS[0], BCS[3]):
-        for opts in (dict(), dict(fused_rb_min_n=100000)):
+        for opts in (dict(fused_rb_min_n=64), dict(fused_rb_min_n=100000)):
             plain, graph = run(0, bclo, bchi, **opts), run(1, bclo, bchi, **opts)
             for p, g in zip(plain, graph):
                 assert p[0] == 0 and g[0] == 0 and p[6] == 0 and g[6] == g[1] > 0
