@@ -682,7 +682,7 @@ def run_gpu_mac(args):
     P = MacProjector(Geometry(ncell, (0, 0, 0), hi, [b == 0 for b in bclo]), lib=L, rank=rank, nranks=world, nccl_comm=comm)
     P.setDomainBC(bclo, bchi)
     P.initProjector(LPInfo().setMaxCoarseningLevel(100), [Fab(b, 0) for b in beta], profile_kernels=1, verbose=args.verbose,
-                    use_graph=0 if args.no_graph else 1)
+                    use_graph=0 if args.no_graph else 1, p2p_halo=0 if args.no_p2p else 1)
     P.setUMAC(umac)
     stream = torch.cuda.current_stream().cuda_stream
     dof = n ** 3 * G

@@ -58,7 +58,7 @@ class mp_options(C.Structure):
                 ("bottom_solver", C.c_int), ("verbose", C.c_int), ("bottom_verbose", C.c_int), ("maxorder", C.c_int),
                 ("bottom_rtol", C.c_double), ("bottom_atol", C.c_double), ("const_beta_fastpath", C.c_int),
                 ("fused_rb_min_n", C.c_int), ("fused_rb_const", C.c_int), ("agg_min_local_nz", C.c_int),
-                ("profile_kernels", C.c_int), ("use_graph", C.c_int)]
+                ("profile_kernels", C.c_int), ("use_graph", C.c_int), ("p2p_halo", C.c_int)]
 
 
 # every symbol include/macproj.h declares

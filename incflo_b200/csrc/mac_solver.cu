@@ -50,7 +50,7 @@ struct MacSolver {
     bool have_a = false;
     // mp_options.use_graph: one MLMG iteration as a CUDA graph, keyed on what it bakes in (as NpSolver::iterate_graph); one rank
     struct IterGraph { np_rt::np_graph_t exec = nullptr; std::vector<unsigned char> key; long long launches = 0; int n_prof = 0; } itg;
-    np_stream_t cap_stream = 0; bool have_cap_stream = false, in_capture = false, graph_off = false;
+    np_stream_t cap_stream = 0; bool have_cap_stream = false, in_capture = false, graph_off = false, graph_warm = false;
     std::vector<np_event_t> gprof_ev; double g_ms_smooth = 0.0; int g_n_smooth = 0;
     void drop_graph() { if (itg.exec) np_rt::graph_destroy(itg.exec); itg = IterGraph{}; }
 
@@ -80,12 +80,86 @@ struct MacSolver {
         lo = r > 0 ? r - 1 : (per ? R - 1 : -1);
         hi = r < R - 1 ? r + 1 : (per ? 0 : -1);
     }
+    // Peer-memory halo exchange (the nodal solver's: NpSolver::setup_peer_halo, k_halo_p2p): every rank exports the CUDA-IPC handles
+    // of the cell arrays that are exchanged inside a solve (cor, rescor, res of the sharded levels, sol) and of its flag words,
+    // all ranks gather them, each rank maps its two z-neighbours'.  Used only if EVERY rank succeeded; else grouped ncclSend/ncclRecv.
+    NpSolver::PeerHalo peer;
+    std::vector<long long> peer_off;         // offset of a registered array from the base of its allocation (its two low ghost planes)
+    int setup_peer()
+    {
+        if (!comm.allgather || !comm.allreduce) return 1;
+        auto reg = [&](double* p, const MacLevel& d) { peer.mine.push_back(p); peer_off.push_back(2 * d.sxy); };
+        for (auto& L : lev) if (!L.replicated) { reg(L.cor, L.d); reg(L.rescor, L.d); reg(L.res, L.d); }
+        reg(sol, lev[0].d);
+        void* q = nullptr;
+        if (np_rt::dev_malloc(&q, 8 * sizeof(unsigned long long))) return 1;
+        peer.flags = (unsigned long long*)q; np_rt::memset_async(peer.flags, 0, 8 * sizeof(unsigned long long), stream);
+        if (np_rt::dev_malloc(&q, 4 * sizeof(unsigned int))) return 1;
+        peer.counter = (unsigned int*)q; np_rt::memset_async(peer.counter, 0, 4 * sizeof(unsigned int), stream);
+        const int na = (int)peer.mine.size() + 1;                       // + the flag words
+        std::vector<double> hsend((size_t)na * 8, 0.0), hrecv((size_t)na * 8 * comm.nranks, 0.0);
+        int good = 1;
+        for (int a = 0; a < na; ++a) {
+            void* p = a < na - 1 ? (void*)(peer.mine[a] - peer_off[a]) : (void*)peer.flags;
+            if (np_rt::ipc_export(p, &hsend[(size_t)a * 8])) good = 0;
+        }
+        double *dsend = nullptr, *drecv = nullptr;
+        if (alloc_d(&dsend, (long long)na * 8) || alloc_d(&drecv, (long long)na * 8 * comm.nranks)) return 1;
+        np_rt::copy_async(dsend, hsend.data(), hsend.size() * sizeof(double), stream);
+        if (comm.allgather(comm.ctx, dsend, drecv, (long long)na * 8, (void*)stream)) { err = NP_ERR_NCCL; good = 0; }
+        np_rt::copy_async(hrecv.data(), drecv, hrecv.size() * sizeof(double), stream);
+        np_rt::stream_sync(stream);
+        int lo, hi; z_neighbours(lo, hi);
+        peer.lo.assign(na - 1, nullptr); peer.hi.assign(na - 1, nullptr);
+        auto open_rank = [&](int r, std::vector<double*>& arr, unsigned long long** fl) {
+            for (int a = 0; a < na && good; ++a) {
+                void* m = nullptr;
+                if (np_rt::ipc_open(&hrecv[((size_t)r * na + a) * 8], &m)) { good = 0; break; }
+                peer.opened.push_back(m);
+                if (a < na - 1) arr[a] = (double*)m + peer_off[a]; else *fl = (unsigned long long*)m;
+            }
+        };
+        if (good && lo >= 0) open_rank(lo, peer.lo, &peer.lo_flags);
+        if (good && hi >= 0) {
+            if (hi == lo) { peer.hi = peer.lo; peer.hi_flags = peer.lo_flags; }      // two ranks, periodic: one neighbour on both sides
+            else open_rank(hi, peer.hi, &peer.hi_flags);
+        }
+        h_scal[40] = good ? 0.0 : 1.0;                                  // all or nothing: one max-allreduce of "somebody failed"
+        np_rt::copy_async(scal + 40, h_scal + 40, sizeof(double), stream);
+        if (comm.allreduce(comm.ctx, scal + 40, 1, 1, (void*)stream)) good = 0;
+        np_rt::copy_async(h_scal + 40, scal + 40, sizeof(double), stream);
+        np_rt::stream_sync(stream);
+        np_rt::dev_free(dsend); np_rt::dev_free(drecv);
+        peer.ok = good && h_scal[40] == 0.0;
+        np_rt::last_error();
+        return peer.ok ? 0 : 1;
+    }
+    bool halo_p2p(const MacLevel& d, double* x, int depth)
+    {
+        if (!peer.ok) return false;
+        int id = -1;
+        for (int a = 0; a < (int)peer.mine.size(); ++a) if (peer.mine[a] == x) { id = a; break; }
+        if (id < 0) return false;
+        const long long m = d.sxy * depth;
+        int lo, hi; z_neighbours(lo, hi);
+        HaloP2P a{};
+        // to the lower rank: my planes 0 .. depth-1 -> its planes n2 ..; to the upper rank: my planes n2-depth .. n2-1 -> its planes -depth .. -1
+        a.send_lo = x; a.n_lo = m; a.dst_lo = lo >= 0 ? peer.lo[id] + d.sxy * (long long)d.n[2] : nullptr;
+        a.send_hi = x + d.sxy * (long long)d.n[2] - m; a.n_hi = m; a.dst_hi = hi >= 0 ? peer.hi[id] - m : nullptr;
+        a.mine = peer.flags; a.lo_flags = lo >= 0 ? peer.lo_flags : nullptr; a.hi_flags = hi >= 0 ? peer.hi_flags : nullptr;
+        a.epoch_word = peer.flags + 4; a.counter = peer.counter;
+        const long long chunks = (m + 255) / 256;
+        const int nb = (int)std::min<long long>(64, std::max<long long>(1, chunks / 8));
+        NP_LAUNCH(false, k_halo_p2p, dim3(nb), dim3(256), 0, stream, a); ++launches;
+        return true;
+    }
     // ghost planes of a cell array of a sharded level, `depth` (1 or 2) planes per side: my planes 0.. -> the lower rank's planes
     // n2.., my planes ..n2-1 -> the upper rank's planes ..-1
     void halo(int l, double* x, int depth = 1)
     {
         if (!sharded(l)) return;
         const MacLevel& d = lev[l].d;
+        if (halo_p2p(d, x, depth)) return;
         const long long m = d.sxy * depth;
         int lo, hi; z_neighbours(lo, hi);
         if (comm.sendrecv(comm.ctx, x, m, x - m, m, x + d.sxy * (long long)d.n[2] - m, m, x + d.sxy * (long long)d.n[2], m,
@@ -224,6 +298,7 @@ struct MacSolver {
         if (opt.profile_kernels) { prof_ev.resize(4096); for (auto& e : prof_ev) np_rt::event_create(&e); }
         setup_bc();
         np_rt::stream_sync(stream);
+        if (nranks > 1 && opt.p2p_halo) setup_peer();        // collective; falls back to NCCL when any rank cannot map its neighbours
         return np_rt::last_error() ? NP_ERR_CUDA : NP_OK;
     }
     void destroy()
@@ -247,6 +322,10 @@ struct MacSolver {
         for (auto& e : prof_ev) np_rt::event_destroy(e);
         prof_ev.clear();
         drop_graph();
+        for (void* m : peer.opened) np_rt::ipc_close(m);
+        peer.opened.clear(); peer.ok = false;
+        if (peer.flags) { np_rt::dev_free(peer.flags); peer.flags = nullptr; }
+        if (peer.counter) { np_rt::dev_free(peer.counter); peer.counter = nullptr; }
         for (auto& e : gprof_ev) np_rt::event_destroy(e);
         gprof_ev.clear();
         if (have_cap_stream) { np_rt::stream_destroy(cap_stream); have_cap_stream = false; }
@@ -510,7 +589,8 @@ struct MacSolver {
     // 0: done, *rn set; 1: no graph, run the plain path; 2: the bottom solve asked for MLMG's fallback path
     int iterate_graph(const double* off0, long long nb, double* rn)
     {
-        if (!opt.use_graph || graph_off || comm.nranks > 1 || lev.size() < 2) return 1;
+        if (!opt.use_graph || graph_off || lev.size() < 2) return 1;
+        if (comm.nranks > 1 && !graph_warm) { graph_warm = true; return 1; }      // (as NpSolver::iterate_graph: NCCL set up before a capture)
         std::vector<unsigned char> key;
         auto put = [&](const void* p, size_t n) { key.insert(key.end(), (const unsigned char*)p, (const unsigned char*)p + n); };
         for (const MacLev& L : lev) {
@@ -520,7 +600,7 @@ struct MacSolver {
         put(&sol, sizeof(double*)); put(&rhs, sizeof(double*)); put(&off0, sizeof(double*)); put(&opt, sizeof(mp_options));
         put(&wrapbuf, sizeof(double*)); put(&wrapbuf_n, sizeof(long long));
         const double sc[2] = {alpha, bscal}; put(sc, sizeof(sc));
-        const int sw[4] = {singular ? 1 : 0, bicg_failed_switch ? 1 : 0, have_a ? 1 : 0, 0}; put(sw, sizeof(sw));
+        const int sw[4] = {singular ? 1 : 0, bicg_failed_switch ? 1 : 0, have_a ? 1 : 0, peer.ok ? 1 : 0}; put(sw, sizeof(sw));
         if (!itg.exec || key != itg.key) {
             drop_graph();
             if (!have_cap_stream) { if (np_rt::stream_create(&cap_stream)) { graph_off = true; return 1; } have_cap_stream = true; }
@@ -681,7 +761,9 @@ struct MacSolver {
     void finish_stats()
     {
         np_rt::event_record(ev[3], stream);
+        if (peer.ok) np_rt::copy_async(h_scal + 42, peer.flags + 5, sizeof(unsigned long long), stream);     // did a halo wait give up? (np_wait_flag)
         np_rt::stream_sync(stream);
+        if (peer.ok) { unsigned long long w; memcpy(&w, h_scal + 42, sizeof(w)); if (w != 0ull && !err) err = NP_ERR_NCCL; }
         stats.ms_setup = np_rt::event_ms(ev[0], ev[1]);
         stats.ms_solve = np_rt::event_ms(ev[1], ev[2]);
         stats.ms_finish = np_rt::event_ms(ev[2], ev[3]);
@@ -957,7 +1039,7 @@ void mp_default_options(mp_options* o)
 {
     o->max_coarsening_level = 100; o->maxiter = 200; o->bottom_maxiter = 200; o->num_pre_smooth = 2; o->num_post_smooth = 2;
     o->num_final_smooth = 8; o->bottom_solver = NP_BOTTOM_BICGCG; o->verbose = 0; o->bottom_verbose = 0; o->maxorder = 3;
-    o->bottom_rtol = 1e-4; o->bottom_atol = -1.0; o->const_beta_fastpath = 1; o->fused_rb_min_n = 256; o->fused_rb_const = 1; o->profile_kernels = 0; o->agg_min_local_nz = 32; o->use_graph = 1;
+    o->bottom_rtol = 1e-4; o->bottom_atol = -1.0; o->const_beta_fastpath = 1; o->fused_rb_min_n = 256; o->fused_rb_const = 1; o->profile_kernels = 0; o->agg_min_local_nz = 32; o->use_graph = 1; o->p2p_halo = 1;
 }
 int mp_create(mp_handle** h, const np_geom* geom, int nboxes_global, const np_box* all_boxes, const int* owner_rank,
               int my_rank, int nranks, void* nccl_comm_or_null, const mp_options* opt)

@@ -54,8 +54,11 @@ typedef struct {
     int fused_rb_const;         /* 1 (default): also when b is uniform; 0: one launch per colour there */
     int agg_min_local_nz;       /* multi-GPU: replicate MG levels whose slab would be thinner than this; default 32 */
     int profile_kernels;        /* bracket every level-0 smooth with CUDA events (np_stats.ms_smooth0 / n_smooth0); default 0 */
-    int use_graph;              /* 1 (default): one MLMG iteration is captured as a CUDA graph and replayed, as np_options.use_graph
-                                   (one rank only; several ranks: ignored); 0: launch kernel by kernel */
+    int use_graph;              /* 1 (default): one MLMG iteration is captured as a CUDA graph and replayed, as np_options.use_graph;
+                                   0: launch kernel by kernel */
+    int p2p_halo;               /* multi-GPU: 1 (default): halo planes are stored straight into the neighbours' arrays over NVLink (CUDA IPC
+                                   peer memory + flags, k_halo_p2p), as np_options.p2p_halo; falls back to grouped ncclSend/ncclRecv when
+                                   peer memory cannot be opened on every rank; 0: NCCL */
 } mp_options;
 
 void mp_default_options(mp_options* o);
