@@ -61,3 +61,34 @@ def test_no_cpu_fallback():
 def test_missing_library_fails_loudly(tmp_path):
     with pytest.raises(ImportError):
         capi.load(str(tmp_path / "libnodalproj.so"))
+
+
+def test_struct_layouts_match_the_headers(tmp_path):
+    """The ctypes mirrors of the POD structs (np_geom, np_box, np_fab, np_options, np_stats, np_apply_args, mp_options) have the
+    size and the field offsets a C compiler gives the declarations in include/*.h."""
+    import ctypes as C
+    import shutil
+    import subprocess
+    from incflo_b200 import capi
+    if not shutil.which("gcc"):
+        pytest.skip("no C compiler")
+    structs = {"np_geom": capi.np_geom, "np_box": capi.np_box, "np_fab": capi.np_fab, "np_options": capi.np_options,
+               "np_stats": capi.np_stats, "np_apply_args": capi.np_apply_args, "mp_options": capi.mp_options}
+    lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "nodalproj.h"', '#include "macproj.h"', 'int main(void) {']
+    for name, cls in structs.items():
+        lines.append(f'  printf("{name} size %zu\\n", sizeof({name}));')
+        for fname, _ in cls._fields_:
+            lines.append(f'  printf("{name} {fname} %zu\\n", offsetof({name}, {fname}));')
+    lines += ['  return 0;', '}']
+    src = tmp_path / "layout.c"
+    src.write_text("\n".join(lines))
+    exe = tmp_path / "layout"
+    subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), "-o", str(exe), str(src)], check=True)
+    out = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split("\n")
+    for ln in out:
+        if not ln.strip():
+            continue
+        name, field, val = ln.split()
+        cls = structs[name]
+        want = C.sizeof(cls) if field == "size" else getattr(cls, field).offset
+        assert int(val) == want, (name, field, int(val), want)
