@@ -270,11 +270,23 @@ __device__ __forceinline__ void gs3_run(const LevelDev& L, const GsArgs& A, doub
     // Which row block a warp owns.  On a tile that is not full only the first act_ty row blocks have nodes; warps go to the four
     // schedulers of the SM round-robin, so the second sweep group's row blocks are rotated to start on the scheduler after the
     // first group's last busy one (a small level is a chain of plane steps bound by the issue slots of its busiest scheduler).
-    const int lx = tg % G::NLX;
+    // A thin tile (at most 32 live columns, BW = 2: sixteen lanes hold them) packs two row blocks into a warp, so half as many
+    // warps are busy and each still owns whole rows (the __syncwarp between colours 0 -> 1 and 2 -> 3 stays sufficient).
+    int lx = tg % G::NLX;
     int ty = tg / G::NLX;
-    if (!FULL && grp == 1) {
+    bool dead = false;                                   // a thread without a row block (thin tiles only)
+    if (!FULL) {
         const int act_ty = (min(GS_TY, L.n[1] + 1 - j0) + BH - 1) / BH;
-        if (act_ty < G::NTY) ty = (ty - act_ty % G::NTY + G::NTY) % G::NTY;
+        if (G::NLX == 32) {
+            constexpr int NWG = G::GT / 32;              // warps per sweep group (= NTY)
+            const bool thin = min(GS_TX, L.n[0] + 1 - i0) <= 32;
+            const int busy = thin ? (act_ty + 1) / 2 : act_ty;
+            int w = tg >> 5;
+            const int lane = tg & 31;
+            if (grp == 1 && busy < NWG) w = (w - busy % NWG + NWG) % NWG;
+            if (thin) { lx = lane & 15; ty = 2 * w + (lane >> 4); if (ty >= G::NTY) { dead = true; ty = 0; } }
+            else ty = w;
+        } else if (grp == 1 && act_ty < G::NTY) ty = (ty - act_ty % G::NTY + G::NTY) % G::NTY;
     }
     const int nk  = min(kb + zc, L.n[2]) - kb + 1;       // relaxed planes p = 0..nk-1 (global k = kb+p)
     const int nkw = min(kb + zc - 1, L.n[2]) - kb + 1;   // written planes
@@ -288,7 +300,7 @@ __device__ __forceinline__ void gs3_run(const LevelDev& L, const GsArgs& A, doub
 #pragma unroll
         for (int r = 0; r < BH; ++r) {
             const int i = gi + a, j = gj + r;
-            const bool v = FULL || (i <= L.n[0] && j <= L.n[1]);
+            const bool v = FULL || (!dead && i <= L.n[0] && j <= L.n[1]);
             const bool dd = !FULL && v && ((L.face[0] == NP_FACE_DIRICHLET && i == 0) || (L.face[3] == NP_FACE_DIRICHLET && i == L.n[0])
                                || (L.face[1] == NP_FACE_DIRICHLET && j == 0) || (L.face[4] == NP_FACE_DIRICHLET && j == L.n[1]));
             const bool w = v && (BW * lx + a < GS_WX) && (BH * ty + r < GS_WY);
