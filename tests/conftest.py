@@ -13,6 +13,17 @@ def pytest_configure(config):
 import pytest  # noqa: E402
 
 
+@pytest.hookimpl(tryfirst=True)
+def pytest_collection_modifyitems(config, items):
+    """A GPU-only parameter value (e.g. host fabs handed to the CUDA library) combined with the CPU-emulation backend is not
+    a GPU test: take its gpu mark away, so that every test `-m gpu` selects drives CUDA, and skip it everywhere."""
+    for it in items:
+        cs = getattr(it, "callspec", None)
+        if cs is not None and cs.params.get("backend") == "emu" and it.get_closest_marker("gpu") is not None:
+            it.own_markers = [m for m in it.own_markers if m.name != "gpu"]
+            it.add_marker(pytest.mark.skip(reason="GPU-only parameter on the emulation backend"))
+
+
 @pytest.fixture(params=["emu", pytest.param("gpu", marks=pytest.mark.gpu)])
 def backend(request):
     """Which build of the product sources a parity test drives through the C ABI.
